@@ -1,0 +1,447 @@
+/* TEST INFRASTRUCTURE ONLY — see bsg_oracle.h.  Plain-C restatement of the reference rules.
+ *
+ * Cell codes follow the reference enums so that observation planes index the same way:
+ *   tic_tac_toe / connect_four: 0 empty, 1 nought (player 1), 2 cross (player 0)
+ *       (open_spiel/games/tic_tac_toe.h:44-48, connect_four.h:54-58)
+ *   breakthrough: 0 empty, 1 black (player 0), 2 white (player 1)  (breakthrough.h:45-49)
+ *   hex: the signed 9-value enum of hex.h:51-61 (-4..4)
+ */
+#include "bsg_oracle.h"
+
+#include <string.h>
+
+#include "philox_ref.h"
+
+enum { E = 0, O = 1, X = 2 };           /* ttt / c4 cell codes */
+enum { BT_E = 0, BT_B = 1, BT_W = 2 };  /* breakthrough cell codes */
+enum {                                   /* hex.h:51-61 */
+  HX_EMPTY = 0, HX_WWEST = -3, HX_WEAST = -2, HX_WWIN = -4, HX_WHITE = -1,
+  HX_BNORTH = 3, HX_BSOUTH = 2, HX_BWIN = 4, HX_BLACK = 1
+};
+
+uint32_t orc_draw(uint64_t seed, uint64_t playout, uint32_t t) {
+  return oracle_draw(seed, playout, t);
+}
+
+/* Static facts (tic_tac_toe.h:100-110, connect_four.h:105-118,
+ * breakthrough.cc:383-385 + breakthrough.h:100-115, hex.h:98-118). */
+int orc_num_distinct_actions(int game, int n) {
+  switch (game) {
+    case ORC_TTT: return 9;
+    case ORC_C4: return 7;
+    case ORC_BT: return 8 * 8 * 6 * 2;
+    default: return n * n;
+  }
+}
+int orc_max_game_length(int game, int n) {
+  switch (game) {
+    case ORC_TTT: return 9;
+    case ORC_C4: return 42;
+    case ORC_BT: return 2 * (2 * 8 - 3) * 8 + 1; /* breakthrough.h:116-118 */
+    default: return n * n;
+  }
+}
+int orc_obs_size(int game, int n) {
+  switch (game) {
+    case ORC_TTT: return 27;
+    case ORC_C4: return 126;
+    case ORC_BT: return 192;
+    default: return 9 * n * n;
+  }
+}
+
+/* ---------------------------------------------------------------- tic_tac_toe */
+/* player 0 = cross, player 1 = nought (tic_tac_toe.cc:55-65). */
+static int ttt_mark(int player) { return player == 0 ? X : O; }
+
+/* tic_tac_toe.cc:108-118: the eight lines, tested for one player. */
+static int ttt_has_line(const int* b, int player) {
+  static const int L[8][3] = {{0, 1, 2}, {3, 4, 5}, {6, 7, 8}, {0, 3, 6},
+                              {1, 4, 7}, {2, 5, 8}, {0, 4, 8}, {2, 4, 6}};
+  int c = ttt_mark(player);
+  for (int i = 0; i < 8; ++i)
+    if (b[L[i][0]] == c && b[L[i][1]] == c && b[L[i][2]] == c) return 1;
+  return 0;
+}
+
+/* tic_tac_toe.cc:80-88 */
+static int ttt_apply(orc_state* s, int a) {
+  if (a < 0 || a >= 9 || s->cells[a] != E) return -1;
+  s->cells[a] = ttt_mark(s->cur_player);
+  if (ttt_has_line(s->cells, s->cur_player)) s->outcome = s->cur_player;
+  s->cur_player = 1 - s->cur_player;
+  s->num_moves += 1;
+  return 0;
+}
+
+/* ---------------------------------------------------------------- connect_four */
+#define C4_ROWS 6
+#define C4_COLS 7
+static int c4_at(const orc_state* s, int r, int c) { return s->cells[r * C4_COLS + c]; }
+
+/* connect_four.cc:130-142 */
+static int c4_line_dir(const orc_state* s, int player, int row, int col, int dr, int dc) {
+  if (row + 3 * dr >= C4_ROWS || col + 3 * dc >= C4_COLS || row + 3 * dr < 0 || col + 3 * dc < 0)
+    return 0;
+  int c = ttt_mark(player);
+  for (int i = 0; i < 4; ++i) {
+    if (c4_at(s, row, col) != c) return 0;
+    row += dr;
+    col += dc;
+  }
+  return 1;
+}
+/* connect_four.cc:123-128, 144-152 */
+static int c4_has_line(const orc_state* s, int player) {
+  int c = ttt_mark(player);
+  for (int col = 0; col < C4_COLS; ++col)
+    for (int row = 0; row < C4_ROWS; ++row)
+      if (c4_at(s, row, col) == c &&
+          (c4_line_dir(s, player, row, col, 0, 1) || c4_line_dir(s, player, row, col, -1, -1) ||
+           c4_line_dir(s, player, row, col, -1, 0) || c4_line_dir(s, player, row, col, -1, 1)))
+        return 1;
+  return 0;
+}
+/* connect_four.cc:154-159 */
+static int c4_is_full(const orc_state* s) {
+  for (int col = 0; col < C4_COLS; ++col)
+    if (c4_at(s, C4_ROWS - 1, col) == E) return 0;
+  return 1;
+}
+/* connect_four.cc:93-106: gravity drop, win tested before draw. */
+static int c4_apply(orc_state* s, int a) {
+  if (a < 0 || a >= C4_COLS || c4_at(s, C4_ROWS - 1, a) != E) return -1;
+  int row = 0;
+  while (c4_at(s, row, a) != E) ++row;
+  s->cells[row * C4_COLS + a] = ttt_mark(s->cur_player);
+  if (c4_has_line(s, s->cur_player)) s->outcome = s->cur_player;
+  else if (c4_is_full(s)) s->outcome = 2;
+  s->cur_player = 1 - s->cur_player;
+  s->num_moves += 1;
+  return 0;
+}
+
+/* ---------------------------------------------------------------- breakthrough (8x8) */
+#define BT_N 8
+/* breakthrough.cc:35-40: direction offsets for black (0..2) then white (3..5). */
+static const int kBtDRow[6] = {1, 1, 1, -1, -1, -1};
+static const int kBtDCol[6] = {-1, 0, 1, -1, 0, 1};
+static int bt_in(int r, int c) { return r >= 0 && r < BT_N && c >= 0 && c < BT_N; }
+static int bt_mine(int player) { return player == 0 ? BT_B : BT_W; }
+static int bt_theirs(int player) { return player == 0 ? BT_W : BT_B; }
+
+/* breakthrough.cc:217-256 with the action id of spiel_utils.cc:45-58 over bases {8,8,6,2}:
+ * id = ((r*8 + c)*6 + dir)*2 + capture. */
+static int bt_legal(const orc_state* s, int* out) {
+  int n = 0;
+  int p = s->cur_player;
+  for (int r = 0; r < BT_N; ++r)
+    for (int c = 0; c < BT_N; ++c) {
+      if (s->cells[r * BT_N + c] != bt_mine(p)) continue;
+      for (int o = 0; o < 3; ++o) {
+        int dir = p * 3 + o;
+        int rp = r + kBtDRow[dir], cp = c + kBtDCol[dir];
+        if (!bt_in(rp, cp)) continue;
+        int target = s->cells[rp * BT_N + cp];
+        if (target == BT_E) out[n++] = ((r * BT_N + c) * 6 + dir) * 2 + 0;
+        else if ((o == 0 || o == 2) && target == bt_theirs(p))
+          out[n++] = ((r * BT_N + c) * 6 + dir) * 2 + 1;
+      }
+    }
+  return n;
+}
+
+/* breakthrough.cc:152-192.  The reference moves whatever the id decodes to and only checks
+ * bounds and colours; the oracle additionally rejects ids that are not in the legal list. */
+static int bt_apply(orc_state* s, int a) {
+  int legal[128];
+  int n = bt_legal(s, legal), ok = 0;
+  for (int i = 0; i < n; ++i) ok |= (legal[i] == a);
+  if (!ok) return -1;
+  int cap = a % 2, dir = (a / 2) % 6, c1 = (a / 12) % BT_N, r1 = a / (12 * BT_N);
+  int r2 = r1 + kBtDRow[dir], c2 = c1 + kBtDCol[dir];
+  (void)cap;
+  if (s->cells[r2 * BT_N + c2] == BT_W) s->pieces[1]--;
+  else if (s->cells[r2 * BT_N + c2] == BT_B) s->pieces[0]--;
+  s->cells[r2 * BT_N + c2] = s->cells[r1 * BT_N + c1];
+  s->cells[r1 * BT_N + c1] = BT_E;
+  if (s->cur_player == 0 && r2 == BT_N - 1) s->outcome = 0;
+  else if (s->cur_player == 1 && r2 == 0) s->outcome = 1;
+  s->cur_player = 1 - s->cur_player;
+  s->num_moves += 1;
+  return 0;
+}
+
+/* ---------------------------------------------------------------- hex */
+/* hex.cc:206-222: six neighbours with bounds and column-wrap guards. */
+static int hex_adjacent(int cell, int n, int* out) {
+  int cand[6] = {cell - n, cell - n + 1, cell - 1, cell + 1, cell + n - 1, cell + n};
+  int k = 0;
+  for (int i = 0; i < 6; ++i) {
+    int v = cand[i];
+    if (v < 0 || v >= n * n) continue;
+    if (v % n == 0 && cell % n == n - 1) continue;
+    if (v % n == n - 1 && cell % n == 0) continue;
+    out[k++] = v;
+  }
+  return k;
+}
+
+/* hex.cc:55-121: label of a new stone from board edges and neighbours' labels. */
+static int hex_new_label(const orc_state* s, int player, int move) {
+  int n = s->board_size, nb[6];
+  int k = hex_adjacent(move, n, nb);
+  if (player == 0) {
+    int north = 0, south = 0;
+    if (move < n) north = 1;
+    else if (move >= n * (n - 1)) south = 1;
+    for (int i = 0; i < k; ++i) {
+      if (s->cells[nb[i]] == HX_BNORTH) north = 1;
+      else if (s->cells[nb[i]] == HX_BSOUTH) south = 1;
+    }
+    if (north && south) return HX_BWIN;
+    if (north) return HX_BNORTH;
+    if (south) return HX_BSOUTH;
+    return HX_BLACK;
+  } else {
+    int west = 0, east = 0;
+    if (move % n == 0) west = 1;
+    else if (move % n == n - 1) east = 1;
+    for (int i = 0; i < k; ++i) {
+      if (s->cells[nb[i]] == HX_WWEST) west = 1;
+      else if (s->cells[nb[i]] == HX_WEAST) east = 1;
+    }
+    if (west && east) return HX_WWIN;
+    if (west) return HX_WWEST;
+    if (east) return HX_WEAST;
+    return HX_WHITE;
+  }
+}
+
+/* hex.cc:149-184: place, then flood the edge label through plain stones of the mover. */
+static int hex_apply(orc_state* s, int a) {
+  int n = s->board_size;
+  if (a < 0 || a >= n * n || s->cells[a] != HX_EMPTY) return -1;
+  int label = hex_new_label(s, s->cur_player, a);
+  s->cells[a] = label;
+  if (label == HX_BWIN) s->outcome = 0;
+  else if (label == HX_WWIN) s->outcome = 1;
+  else if (label != HX_BLACK && label != HX_WHITE) {
+    int plain = s->cur_player == 0 ? HX_BLACK : HX_WHITE;
+    int stack[ORC_MAX_CELLS], top = 0, nb[6];
+    stack[top++] = a;
+    while (top > 0) {
+      int cell = stack[--top];
+      int k = hex_adjacent(cell, n, nb);
+      for (int i = 0; i < k; ++i)
+        if (s->cells[nb[i]] == plain) {
+          s->cells[nb[i]] = label;
+          stack[top++] = nb[i];
+        }
+    }
+  }
+  s->cur_player = 1 - s->cur_player;
+  s->num_moves += 1;
+  return 0;
+}
+
+/* ---------------------------------------------------------------- generic API */
+void orc_init(orc_state* s, int game, int board_size) {
+  memset(s, 0, sizeof(*s));
+  s->game = game;
+  s->outcome = -1;
+  s->board_size = game == ORC_HEX ? (board_size > 0 ? board_size : 11) : 0;
+  if (game == ORC_BT) {
+    /* breakthrough.cc:119-142: black on rows 0-1, white on rows 6-7, black (player 0) first. */
+    for (int r = 0; r < BT_N; ++r)
+      for (int c = 0; c < BT_N; ++c)
+        s->cells[r * BT_N + c] = (r <= 1) ? BT_B : (r >= BT_N - 2 ? BT_W : BT_E);
+    s->pieces[0] = s->pieces[1] = 2 * BT_N;
+  }
+}
+
+int orc_is_terminal(const orc_state* s) {
+  switch (s->game) {
+    case ORC_TTT: return s->outcome != -1 || s->num_moves == 9;     /* tic_tac_toe.cc:139-141 */
+    case ORC_C4: return s->outcome != -1;                           /* connect_four.cc:176-178 */
+    case ORC_BT: return s->outcome >= 0 || s->pieces[0] == 0 || s->pieces[1] == 0; /* :306-308 */
+    default: return s->outcome != -1;                               /* hex.cc:248 */
+  }
+}
+
+int orc_current_player(const orc_state* s) {
+  return orc_is_terminal(s) ? ORC_TERMINAL_PLAYER : s->cur_player;
+}
+
+int orc_legal_actions(const orc_state* s, int* out) {
+  if (orc_is_terminal(s)) return 0;
+  int n = 0;
+  switch (s->game) {
+    case ORC_TTT: /* tic_tac_toe.cc:90-100 */
+      for (int c = 0; c < 9; ++c) if (s->cells[c] == E) out[n++] = c;
+      return n;
+    case ORC_C4: /* connect_four.cc:108-116 */
+      for (int c = 0; c < C4_COLS; ++c) if (c4_at(s, C4_ROWS - 1, c) == E) out[n++] = c;
+      return n;
+    case ORC_BT:
+      return bt_legal(s, out);
+    default: /* hex.cc:186-196 */
+      for (int c = 0; c < s->board_size * s->board_size; ++c)
+        if (s->cells[c] == HX_EMPTY) out[n++] = c;
+      return n;
+  }
+}
+
+int orc_apply(orc_state* s, int a) {
+  if (orc_is_terminal(s)) return -1;
+  switch (s->game) {
+    case ORC_TTT: return ttt_apply(s, a);
+    case ORC_C4: return c4_apply(s, a);
+    case ORC_BT: return bt_apply(s, a);
+    default: return hex_apply(s, a);
+  }
+}
+
+void orc_returns(const orc_state* s, int ret[2]) {
+  int w = -1;
+  if (s->game == ORC_BT) {
+    /* breakthrough.cc:310-318 */
+    if (s->outcome == 0 || s->pieces[1] == 0) w = 0;
+    else if (s->outcome == 1 || s->pieces[0] == 0) w = 1;
+  } else if (s->outcome == 0 || s->outcome == 1) {
+    w = s->outcome;
+  }
+  ret[0] = w == 0 ? 1 : (w == 1 ? -1 : 0);
+  ret[1] = -ret[0];
+}
+
+void orc_observation(const orc_state* s, int player, uint8_t* out) {
+  int ncell, plane;
+  switch (s->game) {
+    case ORC_TTT: /* tic_tac_toe.cc:165-175: plane = raw cell code, not player-relative */
+      memset(out, 0, 27);
+      for (int c = 0; c < 9; ++c) out[s->cells[c] * 9 + c] = 1;
+      return;
+    case ORC_C4: /* connect_four.cc:198-221: nought->(p==0?0:1), cross->(p==1?0:1), empty->2 */
+      memset(out, 0, 126);
+      for (int c = 0; c < 42; ++c) {
+        int v = s->cells[c];
+        plane = v == O ? (player == 0 ? 0 : 1) : (v == X ? (player == 1 ? 0 : 1) : 2);
+        out[plane * 42 + c] = 1;
+      }
+      return;
+    case ORC_BT: /* breakthrough.cc:284-304,326-340: black 0, white 1, empty 2 */
+      memset(out, 0, 192);
+      for (int c = 0; c < 64; ++c) {
+        int v = s->cells[c];
+        plane = v == BT_B ? 0 : (v == BT_W ? 1 : 2);
+        out[plane * 64 + c] = 1;
+      }
+      return;
+    default: /* hex.cc:266-277: plane = state - kMinValueCellState(-4) */
+      ncell = s->board_size * s->board_size;
+      memset(out, 0, 9 * ncell);
+      for (int c = 0; c < ncell; ++c) out[(s->cells[c] + 4) * ncell + c] = 1;
+      return;
+  }
+}
+
+static int orc_from_history(orc_state* s, int game, int board_size, const int64_t* hist, int n) {
+  orc_init(s, game, board_size);
+  for (int i = 0; i < n; ++i)
+    if (orc_apply(s, (int)hist[i]) != 0) return -1;
+  return 0;
+}
+
+static int orc_replay_from(orc_state* s, const uint32_t* r_table, uint64_t seed, uint64_t playout,
+                           int max_steps, int64_t* actions_out, int* len_out, int* terminal_out,
+                           int* ret0_out) {
+  int legal[128], t = 0, ret[2];
+  while (!orc_is_terminal(s) && t < max_steps) {
+    int n = orc_legal_actions(s, legal);
+    if (n == 0) return -1;
+    uint32_t r = r_table ? r_table[t] : oracle_draw(seed, playout, (uint32_t)t);
+    int a = legal[r % (uint32_t)n];
+    if (actions_out) actions_out[t] = a;
+    orc_apply(s, a);
+    ++t;
+  }
+  orc_returns(s, ret);
+  *len_out = t;
+  *terminal_out = orc_is_terminal(s);
+  *ret0_out = ret[0];
+  return 0;
+}
+
+int orc_replay(int game, int board_size, const int64_t* hist, int n_hist, const uint32_t* r_table,
+               uint64_t seed, uint64_t playout, int max_steps, int64_t* actions_out, int* len_out,
+               int* terminal_out, int* ret0_out) {
+  orc_state s;
+  if (orc_from_history(&s, game, board_size, hist, n_hist) != 0) return -2;
+  return orc_replay_from(&s, r_table, seed, playout, max_steps, actions_out, len_out,
+                         terminal_out, ret0_out);
+}
+
+int orc_replay_batch(int game, int board_size, const int64_t* hist_flat, const int64_t* hist_off,
+                     int64_t n_roots, int rollouts, uint64_t seed, uint64_t first_playout,
+                     int max_steps, int32_t* len_out, int8_t* ret0_out, uint8_t* terminal_out,
+                     int16_t* actions_out, int actions_stride) {
+  int64_t acts[256];
+  for (int64_t i = 0; i < n_roots; ++i) {
+    orc_state root;
+    if (orc_from_history(&root, game, board_size, hist_flat + hist_off[i],
+                         (int)(hist_off[i + 1] - hist_off[i])) != 0)
+      return -2;
+    for (int j = 0; j < rollouts; ++j) {
+      int64_t p = i * rollouts + j;
+      orc_state s = root;
+      int len, term, ret0;
+      if (orc_replay_from(&s, 0, seed, first_playout + (uint64_t)p, max_steps, acts, &len, &term,
+                          &ret0) != 0)
+        return -1;
+      len_out[p] = len;
+      ret0_out[p] = (int8_t)ret0;
+      terminal_out[p] = (uint8_t)term;
+      if (actions_out)
+        for (int t = 0; t < len && t < actions_stride; ++t)
+          actions_out[p * actions_stride + t] = (int16_t)acts[t];
+    }
+  }
+  return 0;
+}
+
+int orc_state_dump(int game, int board_size, const int64_t* hist, int n_hist, int player,
+                   uint8_t* obs_out, int64_t* legal_out, int* n_legal, int* cur_player,
+                   int* terminal, int* returns_out) {
+  orc_state s;
+  int legal[128];
+  if (orc_from_history(&s, game, board_size, hist, n_hist) != 0) return -2;
+  *n_legal = orc_legal_actions(&s, legal);
+  if (legal_out) for (int i = 0; i < *n_legal; ++i) legal_out[i] = legal[i];
+  *cur_player = orc_current_player(&s);
+  *terminal = orc_is_terminal(&s);
+  orc_returns(&s, returns_out);
+  if (obs_out) orc_observation(&s, player, obs_out);
+  return 0;
+}
+
+/* Scalar timing loop for bench.py's cpu_baseline (kind "port"): playout p starts from root
+ * p mod n_roots and follows the replay contract with Philox draws. */
+int64_t orc_random_playouts(int game, int board_size, const int64_t* hist_flat,
+                            const int64_t* hist_off, int64_t n_roots, int64_t n_playouts,
+                            uint64_t seed, int64_t* sum_ret0_out) {
+  int64_t steps = 0, sum = 0;
+  for (int64_t p = 0; p < n_playouts; ++p) {
+    int64_t i = p % n_roots;
+    orc_state s;
+    int len, term, ret0;
+    if (orc_from_history(&s, game, board_size, hist_flat + hist_off[i],
+                         (int)(hist_off[i + 1] - hist_off[i])) != 0)
+      return -2;
+    if (orc_replay_from(&s, 0, seed, (uint64_t)p, 1 << 30, 0, &len, &term, &ret0) != 0) return -1;
+    steps += len;
+    sum += ret0;
+  }
+  *sum_ret0_out = sum;
+  return steps;
+}

@@ -1,0 +1,211 @@
+"""ctypes access to the CPU checkers (TEST INFRASTRUCTURE ONLY; never imported by the product).
+
+  Oracle    — oracle/_ref/libbsg_oracle.so, the plain-C restatement (oracle/bsg_oracle.c)
+  Reference — oracle/_ref/libspiel_ref.so, the unmodified reference C++ (oracle/ref_wrapper.cc);
+              only present where it was built (this container; it travels to the GPU box).
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(REPO, "oracle")
+GAME_IDS = {"tic_tac_toe": 0, "connect_four": 1, "breakthrough": 2, "hex": 3}
+OBS_SIZE = {"tic_tac_toe": 27, "connect_four": 126, "breakthrough": 192, "hex": 1089}
+vp = ctypes.c_void_p
+
+
+def _ptr(a):
+  return None if a is None else a.ctypes.data
+
+
+def build_oracle():
+  so = os.path.join(ORACLE_DIR, "_ref", "libbsg_oracle.so")
+  src = os.path.join(ORACLE_DIR, "bsg_oracle.c")
+  if not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+    subprocess.check_call(["make", "-C", ORACLE_DIR, "_ref/libbsg_oracle.so"],
+                          stdout=subprocess.DEVNULL)
+  return so
+
+
+def ragged(histories):
+  off = np.zeros(len(histories) + 1, np.int64)
+  for i, h in enumerate(histories):
+    off[i + 1] = off[i] + len(h)
+  flat = np.zeros(max(int(off[-1]), 1), np.int64)
+  for i, h in enumerate(histories):
+    flat[off[i]:off[i + 1]] = h
+  return flat, off
+
+
+class Oracle:
+  """The C restatement.  `game` is one of GAME_IDS; hex takes board_size (default 11)."""
+
+  def __init__(self):
+    self.lib = ctypes.CDLL(build_oracle())
+    L = self.lib
+    L.orc_replay.argtypes = [ctypes.c_int, ctypes.c_int, vp, ctypes.c_int, vp, ctypes.c_uint64,
+                             ctypes.c_uint64, ctypes.c_int, vp, vp, vp, vp]
+    L.orc_replay_batch.argtypes = [ctypes.c_int, ctypes.c_int, vp, vp, ctypes.c_int64,
+                                   ctypes.c_int, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int,
+                                   vp, vp, vp, vp, ctypes.c_int]
+    L.orc_state_dump.argtypes = [ctypes.c_int, ctypes.c_int, vp, ctypes.c_int, ctypes.c_int, vp,
+                                 vp, vp, vp, vp, vp]
+    L.orc_random_playouts.argtypes = [ctypes.c_int, ctypes.c_int, vp, vp, ctypes.c_int64,
+                                      ctypes.c_int64, ctypes.c_uint64, vp]
+    L.orc_random_playouts.restype = ctypes.c_int64
+    L.orc_draw.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint32]
+    L.orc_draw.restype = ctypes.c_uint32
+
+  def draw(self, seed, playout, t):
+    return self.lib.orc_draw(seed, playout, t)
+
+  def replay(self, game, hist, r_table=None, seed=0, playout=0, max_steps=1 << 20, board_size=11):
+    h = np.asarray(hist, np.int64)
+    acts = np.zeros(256, np.int64)
+    ln, term, ret = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    rt = None if r_table is None else np.asarray(r_table, np.uint32)
+    rc = self.lib.orc_replay(GAME_IDS[game], board_size, _ptr(h), len(h), _ptr(rt), seed, playout,
+                             max_steps, _ptr(acts), ctypes.byref(ln), ctypes.byref(term),
+                             ctypes.byref(ret))
+    if rc != 0:
+      raise RuntimeError("orc_replay failed rc=%d" % rc)
+    return acts[:ln.value].tolist(), term.value, ret.value
+
+  def replay_batch(self, game, histories, rollouts=1, seed=0, first_playout=0,
+                   max_steps=1 << 20, actions_stride=0, board_size=11):
+    flat, off = ragged(histories)
+    n = len(histories) * rollouts
+    lens = np.zeros(n, np.int32)
+    ret0 = np.zeros(n, np.int8)
+    term = np.zeros(n, np.uint8)
+    acts = np.full((n, actions_stride), -1, np.int16) if actions_stride else None
+    rc = self.lib.orc_replay_batch(GAME_IDS[game], board_size, _ptr(flat), _ptr(off),
+                                   len(histories), rollouts, seed, first_playout, max_steps,
+                                   _ptr(lens), _ptr(ret0), _ptr(term), _ptr(acts), actions_stride)
+    if rc != 0:
+      raise RuntimeError("orc_replay_batch failed rc=%d" % rc)
+    return lens, ret0, term, acts
+
+  def state_dump(self, game, hist, player=0, board_size=11):
+    h = np.asarray(hist, np.int64)
+    size = 9 * board_size * board_size if game == "hex" else OBS_SIZE[game]
+    obs = np.zeros(size, np.uint8)
+    legal = np.zeros(1024, np.int64)
+    nl, cp, tm = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    rets = np.zeros(2, np.int32)
+    rc = self.lib.orc_state_dump(GAME_IDS[game], board_size, _ptr(h), len(h), player, _ptr(obs),
+                                 _ptr(legal), ctypes.byref(nl), ctypes.byref(cp),
+                                 ctypes.byref(tm), _ptr(rets))
+    if rc != 0:
+      raise RuntimeError("orc_state_dump failed rc=%d (illegal history?)" % rc)
+    return {"obs": obs, "legal": legal[:nl.value].tolist(), "current_player": cp.value,
+            "terminal": bool(tm.value), "returns": rets.tolist()}
+
+  def random_playouts(self, game, histories, n_playouts, seed=0, board_size=11):
+    flat, off = ragged(histories)
+    s = ctypes.c_int64()
+    steps = self.lib.orc_random_playouts(GAME_IDS[game], board_size, _ptr(flat), _ptr(off),
+                                         len(histories), n_playouts, seed, ctypes.byref(s))
+    if steps < 0:
+      raise RuntimeError("orc_random_playouts failed")
+    return steps, s.value
+
+
+def reference_path():
+  return os.path.join(ORACLE_DIR, "_ref", "libspiel_ref.so")
+
+
+class Reference:
+  """The unmodified reference C++ behind oracle/ref_wrapper.cc."""
+
+  def __init__(self):
+    self.lib = ctypes.CDLL(reference_path())
+    L = self.lib
+    L.ref_replay.argtypes = [ctypes.c_char_p, vp, ctypes.c_int, vp, ctypes.c_uint64,
+                             ctypes.c_uint64, ctypes.c_int, vp, vp, vp, vp]
+    L.ref_replay_batch.argtypes = [ctypes.c_char_p, vp, vp, ctypes.c_int64, ctypes.c_int,
+                                   ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int, ctypes.c_int,
+                                   vp, vp, vp, vp, ctypes.c_int]
+    L.ref_state_dump.argtypes = [ctypes.c_char_p, vp, ctypes.c_int, ctypes.c_int, vp, vp, vp, vp,
+                                 vp, vp]
+    L.ref_random_playouts.argtypes = [ctypes.c_char_p, vp, vp, ctypes.c_int64, ctypes.c_int64,
+                                      ctypes.c_uint64, ctypes.c_int, ctypes.c_int, vp, vp]
+    L.ref_random_playouts.restype = ctypes.c_double
+    L.ref_mcts_selfplay.argtypes = [ctypes.c_char_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                    ctypes.c_double, ctypes.c_int, ctypes.c_uint64, ctypes.c_int,
+                                    vp, vp, vp]
+    L.ref_mcts_selfplay.restype = ctypes.c_double
+    L.ref_mcts_step.argtypes = [ctypes.c_char_p, vp, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                ctypes.c_double, ctypes.c_int, ctypes.c_int]
+    L.ref_mcts_step.restype = ctypes.c_int64
+
+  @staticmethod
+  def game_string(game, board_size=11):
+    return ("hex(board_size=%d)" % board_size if game == "hex" else game).encode()
+
+  def replay(self, game, hist, r_table=None, seed=0, playout=0, max_steps=1 << 20, board_size=11):
+    h = np.asarray(hist, np.int64)
+    acts = np.zeros(256, np.int64)
+    ln, term, ret = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    rt = None if r_table is None else np.asarray(r_table, np.uint32)
+    rc = self.lib.ref_replay(self.game_string(game, board_size), _ptr(h), len(h), _ptr(rt), seed,
+                             playout, max_steps, _ptr(acts), ctypes.byref(ln), ctypes.byref(term),
+                             ctypes.byref(ret))
+    if rc != 0:
+      raise RuntimeError("ref_replay failed")
+    return acts[:ln.value].tolist(), term.value, ret.value
+
+  def replay_batch(self, game, histories, rollouts=1, seed=0, first_playout=0,
+                   max_steps=1 << 20, actions_stride=0, threads=8, board_size=11):
+    flat, off = ragged(histories)
+    n = len(histories) * rollouts
+    lens = np.zeros(n, np.int32)
+    ret0 = np.zeros(n, np.int8)
+    term = np.zeros(n, np.uint8)
+    acts = np.full((n, actions_stride), -1, np.int16) if actions_stride else None
+    rc = self.lib.ref_replay_batch(self.game_string(game, board_size), _ptr(flat), _ptr(off),
+                                   len(histories), rollouts, seed, first_playout, max_steps,
+                                   threads, _ptr(lens), _ptr(ret0), _ptr(term), _ptr(acts),
+                                   actions_stride)
+    if rc != 0:
+      raise RuntimeError("ref_replay_batch failed")
+    return lens, ret0, term, acts
+
+  def state_dump(self, game, hist, player=0, board_size=11):
+    h = np.asarray(hist, np.int64)
+    size = 9 * board_size * board_size if game == "hex" else OBS_SIZE[game]
+    obs = np.zeros(size, np.float64)
+    legal = np.zeros(1024, np.int64)
+    nl, cp, tm = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    rets = np.zeros(2, np.float64)
+    self.lib.ref_state_dump(self.game_string(game, board_size), _ptr(h), len(h), player,
+                            _ptr(obs), _ptr(legal), ctypes.byref(nl), ctypes.byref(cp),
+                            ctypes.byref(tm), _ptr(rets))
+    return {"obs": obs.astype(np.uint8), "legal": legal[:nl.value].tolist(),
+            "current_player": cp.value, "terminal": bool(tm.value),
+            "returns": [int(rets[0]), int(rets[1])]}
+
+  def random_playouts(self, game, histories, n_playouts, seed=0, threads=1, with_obs=False,
+                      board_size=11):
+    flat, off = ragged(histories)
+    steps, s = ctypes.c_int64(), ctypes.c_int64()
+    secs = self.lib.ref_random_playouts(self.game_string(game, board_size), _ptr(flat), _ptr(off),
+                                        len(histories), n_playouts, seed, threads, int(with_obs),
+                                        ctypes.byref(steps), ctypes.byref(s))
+    return secs, steps.value, s.value
+
+  def mcts_selfplay(self, game, n_games, max_sims, n_rollouts, uct_c=2.0, solve=True, seed=1,
+                    threads=1):
+    mv, sims, s = ctypes.c_int64(), ctypes.c_int64(), ctypes.c_int64()
+    secs = self.lib.ref_mcts_selfplay(self.game_string(game), n_games, max_sims, n_rollouts,
+                                      uct_c, int(solve), seed, threads, ctypes.byref(mv),
+                                      ctypes.byref(sims), ctypes.byref(s))
+    return secs, mv.value, sims.value, s.value
+
+  def mcts_step(self, game, hist, max_sims, n_rollouts=1, uct_c=2.0, solve=True, seed=1):
+    h = np.asarray(hist, np.int64)
+    return self.lib.ref_mcts_step(self.game_string(game), _ptr(h), len(h), max_sims, n_rollouts,
+                                  uct_c, int(solve), seed)
