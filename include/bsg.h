@@ -1,0 +1,161 @@
+/* bsg.h — C ABI of the B200 batched game-simulation engine ("bsg").
+ *
+ * Drop-in boundary for OpenSpiel's rollout hot path.  The reference has no C ABI of its own
+ * (its FFI is the pybind11 module open_spiel/python/pybind11/pyspiel.cc); each entry point
+ * below names the reference interface it stands in for.  Plain pointers and sizes only; no
+ * C++/torch types.  Every function returns BSG_OK (0) or a negative error code and never
+ * throws or exits (the reference's SpielFatalError -> RuntimeError convention,
+ * pyspiel.cc:71-78,839-840, is reproduced by the Python wrapper).
+ *
+ * Ownership: the caller owns every buffer.  "dev" pointers are CUDA device pointers on the
+ * engine's device (e.g. torch tensor data_ptr()); "host" pointers are ordinary memory.
+ * `stream` is a cudaStream_t passed as void* (NULL = default stream); all device work is
+ * stream-ordered on it and the call returns without synchronising unless stated.
+ * Threading: one engine per (thread, GPU); calls on one engine must be serialised by the
+ * caller — the same contract as the reference evaluators, which own a mutable RNG
+ * (open_spiel/algorithms/mcts.h:105, python/algorithms/mcts.py:56).
+ *
+ * Replay contract (bit-exact parity with the reference):
+ *   r(seed, playout, t) = philox4x32_10(ctr = {playout_lo, playout_hi, t >> 2, 0},
+ *                                       key = {seed_lo, seed_hi})[t & 3]
+ *   action_t = State::LegalActions()[ r mod n ]        (ascending action ids)
+ * or, when io.r_table is given, r = r_table[playout_local * r_stride + t].
+ */
+#ifndef BSG_H_
+#define BSG_H_
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BSG_VERSION 1
+
+/* Game ids.  Strings accepted by bsg_game_id are the reference's game strings
+ * (open_spiel/spiel.h:792-803): "tic_tac_toe", "connect_four", "breakthrough",
+ * "breakthrough(rows=8,columns=8)", "hex", "hex(board_size=11)". */
+#define BSG_TIC_TAC_TOE 0
+#define BSG_CONNECT_FOUR 1
+#define BSG_BREAKTHROUGH 2
+#define BSG_HEX 3
+/* Host-helper-only id used to check the hex logic against the reference's 5x5 golden
+ * playthrough; no device kernels exist for it. */
+#define BSG_HEX5_HOST_ONLY 4
+
+#define BSG_OK 0
+#define BSG_ERR_BAD_GAME (-1)
+#define BSG_ERR_BAD_ARG (-2)
+#define BSG_ERR_ILLEGAL_ACTION (-3)
+#define BSG_ERR_CUDA (-4)
+#define BSG_ERR_NO_DEVICE (-5)
+#define BSG_ERR_STUCK_LANE (-6) /* a non-terminal state without legal actions was met */
+
+#define BSG_TERMINAL_PLAYER (-4) /* kTerminalPlayerId, open_spiel/spiel.h:48 */
+
+typedef struct bsg_engine bsg_engine;
+
+int bsg_version(void);
+const char* bsg_error_string(int code);
+
+/* ---- static game facts: Game::NumDistinctActions / MaxGameLength / ObservationTensorSize
+ *      (open_spiel/spiel.h:601-750), plus the packed-state size of this engine. */
+int bsg_game_id(const char* game_string);
+int bsg_num_distinct_actions(int game);
+int bsg_max_game_length(int game);
+int bsg_observation_size(int game);
+int bsg_observation_shape(int game, int shape_out[3]);
+int bsg_state_bytes(int game);
+
+/* ---- host helpers (pure CPU, usable without a GPU): moving reference states in and out.
+ * Packed states are plane-major structure-of-arrays buffers with a capacity `cap`:
+ * plane p of state i lives at base + plane_offset[p] * cap + i * plane_elem[p]
+ * (layouts per game in DESIGN.md).  A single state is the cap = 1 case. */
+
+/* Replays action histories (State::history(), pyspiel.cc:322) from the initial state into
+ * packed states; stands in for Game::NewInitialState + State::ApplyAction
+ * (open_spiel/spiel.h:205-210,622).  hist_off has n + 1 entries. */
+int bsg_pack_histories(int game, const int64_t* hist_flat, const int64_t* hist_off, int64_t n,
+                       void* packed_host, int64_t cap);
+/* State::CurrentPlayer / IsTerminal / Returns()[0] of packed state i. */
+int bsg_host_state_info(int game, const void* packed_host, int64_t cap, int64_t i,
+                        int* current_player, int* is_terminal, int* ret0);
+/* State::LegalActions (ascending).  Returns the count (>= 0) or an error. */
+int bsg_host_legal_actions(int game, const void* packed_host, int64_t cap, int64_t i,
+                           int64_t* actions_out, int capacity);
+/* State::ApplyAction on packed state i, in place. */
+int bsg_host_apply_action(int game, void* packed_host, int64_t cap, int64_t i, int64_t action);
+/* State::ObservationTensor(player) of one packed state as float 0/1, flat CHW. */
+int bsg_host_observation(int game, const void* packed_host, int64_t cap, int64_t i, int player,
+                         float* obs_out);
+/* Debug/test hook: applies LegalActions()[r mod n] to packed state i through the very step
+ * function the kernels run, so the selection logic can be checked on a CPU.  No product
+ * path calls it; playouts exist only as CUDA kernels. */
+int bsg_host_replay_step(int game, void* packed_host, int64_t cap, int64_t i, uint32_t r,
+                         int64_t* action_out);
+/* The t-th replay draw r(seed, playout, t). */
+uint32_t bsg_draw(uint64_t seed, uint64_t playout, uint32_t t);
+
+/* ---- device engine */
+int bsg_create(int game, int device, bsg_engine** out);
+void bsg_destroy(bsg_engine* e);
+const char* bsg_last_error(bsg_engine* e);
+int bsg_engine_game(const bsg_engine* e);
+int bsg_engine_device(const bsg_engine* e);
+int bsg_engine_sm_count(const bsg_engine* e);
+
+/* Optional inputs/outputs of one playout launch; all pointers are device pointers and may be
+ * NULL.  Playout p (0 <= p < n_roots * rollouts_per_root) starts from root p / rollouts. */
+typedef struct bsg_playout_io {
+  int32_t max_steps;            /* <= 0: play until terminal */
+  const uint8_t* step_limit;    /* per-playout step limit [n_playouts] (0 = no moves) */
+  const uint32_t* r_table;      /* pre-generated draws [n_playouts, r_stride] instead of Philox */
+  int32_t r_stride;
+  int8_t* ret0;                 /* per playout: (int)Returns()[0] at the stop state */
+  uint8_t* length;              /* per playout: moves played */
+  uint8_t* terminal;            /* per playout: IsTerminal() at the stop state */
+  int16_t* actions;             /* action log [n_playouts, actions_stride] */
+  int32_t actions_stride;
+  int32_t* root_sum_ret0;       /* per root: += sum of ret0 (caller zeroes) */
+  int32_t* root_sum_steps;      /* per root: += sum of moves played (caller zeroes) */
+  void* final_states;           /* packed SoA (capacity n_playouts) of the stop states */
+  int32_t final_before_terminal;/* != 0: a playout that ended writes its last non-terminal state */
+  uint64_t* totals;             /* u64[4] += {playouts, steps, sum ret0 (two's complement),
+                                   stuck lanes}; caller zeroes */
+} bsg_playout_io;
+
+/* The hot path.  Stands in for RandomRolloutEvaluator::Evaluate's playout loop
+ * (open_spiel/algorithms/mcts.cc:42-71; python/algorithms/mcts.py:58-74) and for the raw
+ * loop of examples/benchmark_game.cc:31-97, for n_roots * rollouts_per_root playouts at once.
+ * Draws of playout p use the global id first_playout + p. */
+int bsg_playouts(bsg_engine* e, const void* roots_dev, int64_t n_roots, int32_t rollouts_per_root,
+                 uint64_t seed, uint64_t first_playout, const bsg_playout_io* io, void* stream);
+
+/* Batched State::ObservationTensor (open_spiel/spiel.h:438-453; per-game writers cited in
+ * DESIGN.md): writes [n, C, H, W] float32 (0/1, reference element order) for n packed states.
+ * players_dev[i] is the observer of state i; NULL means the player to move.  When
+ * legal_mask_dev is non-NULL it also writes State::LegalActionsMask (spiel.h:244-252) as
+ * [n, NumDistinctActions] bytes. */
+int bsg_observations(bsg_engine* e, const void* states_dev, int64_t n, const uint8_t* players_dev,
+                     float* obs_dev, uint8_t* legal_mask_dev, void* stream);
+
+/* Host-buffer convenience wrappers (the reference-facing call with host memory: copies in,
+ * launches, copies out, synchronises).  roots_host is a packed SoA buffer of capacity n_roots.
+ * totals_out: {playouts, steps, sum ret0, stuck lanes}.  root_sum_* may be NULL. */
+int bsg_playouts_host(bsg_engine* e, const void* roots_host, int64_t n_roots,
+                      int32_t rollouts_per_root, uint64_t seed, uint64_t first_playout,
+                      int64_t totals_out[4], int32_t* root_sum_ret0_host,
+                      int32_t* root_sum_steps_host);
+int bsg_observations_host(bsg_engine* e, const void* states_host, int64_t n,
+                          const uint8_t* players_host, float* obs_host,
+                          uint8_t* legal_mask_host);
+
+/* Integer-issue microbenchmark used for the roofline denominator (bench.py): runs `iters`
+ * dependent-chain iterations of `ilp` independent 32-bit ops per thread on every SM and
+ * returns thread-instructions per second.  kind: 0 = LOP3/IADD3 mix (ALU pipe), 1 = IMAD
+ * (FMA pipe), 2 = alternating ALU/IMAD. */
+int bsg_int_peak(bsg_engine* e, int kind, int iters, double* thread_instr_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BSG_H_ */

@@ -1,0 +1,21 @@
+"""B200-native batched game-simulation engine for OpenSpiel's rollout hot path.
+
+Import as `open_spiel_1_b200` (the repo-root shim of that name loads this directory, whose
+on-disk name `open_spiel-1_b200` is not a Python identifier).
+
+  engine.Engine                  device side of the C ABI (include/bsg.h): playouts, observations
+  evaluator.GpuRolloutEvaluator  drop-in for mcts.RandomRolloutEvaluator (evaluate / prior)
+  spiel.load_game / Game / State host mirror of the pyspiel surface the path touches
+  mcts.MCTSBot / SearchNode      host tree with the reference's interface (+ batched leaves)
+  parallel.RootParallelMCTS      root-parallel search, one NCCL all-reduce per search step
+
+The CUDA extension (libbsg.so) is mandatory: importing this package without it raises.
+"""
+from . import _cabi  # noqa: F401  (raises ImportError when libbsg.so is missing)
+from .engine import Engine, game_id, pack_histories, draw
+from .evaluator import Evaluator, GpuRolloutEvaluator
+from .spiel import load_game, Game, State, GameType, PlayerId
+from .mcts import MCTSBot, SearchNode
+
+__all__ = ["Engine", "game_id", "pack_histories", "draw", "Evaluator", "GpuRolloutEvaluator",
+           "load_game", "Game", "State", "GameType", "PlayerId", "MCTSBot", "SearchNode"]

@@ -1,0 +1,98 @@
+"""ctypes binding of include/bsg.h (the C ABI of the engine).
+
+The library is built in-tree by `__graft_entry__.build()` (or `make -C csrc`) as
+`open_spiel-1_b200/libbsg.so`.  There is no Python/CPU stand-in: if the library is missing,
+importing this module raises, and every device entry point raises when no GPU is present.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libbsg.so")
+
+vp = ctypes.c_void_p
+i32, i64, u32, u64 = ctypes.c_int32, ctypes.c_int64, ctypes.c_uint32, ctypes.c_uint64
+
+OK = 0
+ERR_BAD_GAME, ERR_BAD_ARG, ERR_ILLEGAL_ACTION, ERR_CUDA, ERR_NO_DEVICE, ERR_STUCK_LANE = (
+    -1, -2, -3, -4, -5, -6)
+TERMINAL_PLAYER = -4
+
+TIC_TAC_TOE, CONNECT_FOUR, BREAKTHROUGH, HEX, HEX5_HOST_ONLY = 0, 1, 2, 3, 4
+
+
+class PlayoutIO(ctypes.Structure):
+  """struct bsg_playout_io (include/bsg.h)."""
+  _fields_ = [
+      ("max_steps", i32),
+      ("step_limit", vp),
+      ("r_table", vp),
+      ("r_stride", i32),
+      ("ret0", vp),
+      ("length", vp),
+      ("terminal", vp),
+      ("actions", vp),
+      ("actions_stride", i32),
+      ("root_sum_ret0", vp),
+      ("root_sum_steps", vp),
+      ("final_states", vp),
+      ("final_before_terminal", i32),
+      ("totals", vp),
+  ]
+
+
+def _load():
+  if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        "%s not found: build the CUDA extension first (python -c 'import __graft_entry__ as g; "
+        "g.build()' or make -C open_spiel-1_b200/csrc). There is no CPU fallback." % LIB_PATH)
+  lib = ctypes.CDLL(LIB_PATH)
+  sig = {
+      "bsg_version": (ctypes.c_int, []),
+      "bsg_error_string": (ctypes.c_char_p, [ctypes.c_int]),
+      "bsg_game_id": (ctypes.c_int, [ctypes.c_char_p]),
+      "bsg_num_distinct_actions": (ctypes.c_int, [ctypes.c_int]),
+      "bsg_max_game_length": (ctypes.c_int, [ctypes.c_int]),
+      "bsg_observation_size": (ctypes.c_int, [ctypes.c_int]),
+      "bsg_observation_shape": (ctypes.c_int, [ctypes.c_int, vp]),
+      "bsg_state_bytes": (ctypes.c_int, [ctypes.c_int]),
+      "bsg_pack_histories": (ctypes.c_int, [ctypes.c_int, vp, vp, i64, vp, i64]),
+      "bsg_host_state_info": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, vp, vp, vp]),
+      "bsg_host_legal_actions": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, vp, ctypes.c_int]),
+      "bsg_host_apply_action": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, i64]),
+      "bsg_host_observation": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, ctypes.c_int, vp]),
+      "bsg_host_replay_step": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, u32, vp]),
+      "bsg_draw": (u32, [u64, u64, u32]),
+      "bsg_create": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.POINTER(vp)]),
+      "bsg_destroy": (None, [vp]),
+      "bsg_last_error": (ctypes.c_char_p, [vp]),
+      "bsg_engine_game": (ctypes.c_int, [vp]),
+      "bsg_engine_device": (ctypes.c_int, [vp]),
+      "bsg_engine_sm_count": (ctypes.c_int, [vp]),
+      "bsg_playouts": (ctypes.c_int, [vp, vp, i64, i32, u64, u64, ctypes.POINTER(PlayoutIO), vp]),
+      "bsg_observations": (ctypes.c_int, [vp, vp, i64, vp, vp, vp, vp]),
+      "bsg_playouts_host": (ctypes.c_int, [vp, vp, i64, i32, u64, u64, vp, vp, vp]),
+      "bsg_observations_host": (ctypes.c_int, [vp, vp, i64, vp, vp, vp]),
+      "bsg_int_peak": (ctypes.c_int, [vp, ctypes.c_int, ctypes.c_int, vp]),
+  }
+  for name, (res, args) in sig.items():
+    fn = getattr(lib, name)
+    fn.restype = res
+    fn.argtypes = args
+  return lib, sorted(sig)
+
+
+lib, EXPORTS = _load()
+
+
+def check(rc, engine=None):
+  """Maps an error code to RuntimeError, the reference's error convention from Python
+  (SpielFatalError -> SpielException -> RuntimeError, pyspiel.cc:71-78,839-840)."""
+  if rc >= 0:
+    return rc
+  msg = lib.bsg_error_string(rc).decode()
+  if engine:
+    detail = lib.bsg_last_error(engine).decode()
+    if detail:
+      msg = "%s (%s)" % (msg, detail)
+  raise RuntimeError("bsg: " + msg)

@@ -1,0 +1,603 @@
+// Per-game bitboard state machines of the batched playout engine.
+//
+// Each game is a struct with the same static interface (used by the templated kernels in
+// bsg_kernels.cu and by the host helpers of the C-ABI):
+//   State                      registers-only state
+//   Tables / fill_tables       small lookup tables (shared memory on the device)
+//   init, load, store          initial position; packed SoA HBM layout <-> State
+//   terminal, outcome, mover   status
+//   n = step(s, r, tab, action) one playout step: a = legal[r mod n] in ascending action-id
+//                              order, apply it, update terminal/outcome.  Branch-free enough
+//                              to be run on finished lanes as a dead step (never traps).
+//   legal(s, out)              ascending legal action ids (host side: prior, pack, checks)
+//   apply(s, action)           apply one action id (host side; false if illegal)
+//   obs_bit(s, player, idx)    element idx of the flat CHW observation (reference order)
+//
+// Semantics follow the reference rules cited per function; the representation does not.
+#pragma once
+#include "bsg_common.cuh"
+
+namespace bsg {
+
+// =========================================================================================
+// tic_tac_toe — reference: open_spiel/games/tic_tac_toe.cc
+//   x = player 0 (moves first, tic_tac_toe.cc:55-65), o = player 1.  Two 9-bit masks.
+//   packed: one u32 = x | o << 9 | terminal << 18 | outcome << 19.
+// =========================================================================================
+struct TicTacToe {
+  static constexpr int kId = kGameTicTacToe;
+  static constexpr int kNumActions = 9, kMaxLen = 9, kObsSize = 27, kStateBytes = 4;
+  struct State { u32 x, o, term, outc; };
+  struct Tables { u32 modM[16]; };
+  static void fill_tables(Tables& t) { for (u32 n = 0; n < 16; ++n) t.modM[n] = modM_entry(n); }
+
+  BSG_HD static void init(State& s) { s.x = 0; s.o = 0; s.term = 0; s.outc = kOutcomeNone; }
+  BSG_HD static void load(State& s, const void* base, int64_t n, int64_t i) {
+    (void)n;
+    u32 w = ((const u32*)base)[i];
+    s.x = w & 0x1FF; s.o = (w >> 9) & 0x1FF; s.term = (w >> 18) & 1; s.outc = (w >> 19) & 3;
+  }
+  BSG_HD static void store(const State& s, void* base, int64_t n, int64_t i) {
+    (void)n;
+    ((u32*)base)[i] = s.x | (s.o << 9) | (s.term << 18) | (s.outc << 19);
+  }
+  BSG_HD static bool terminal(const State& s) { return s.term != 0; }
+  BSG_HD static int outcome(const State& s) { return (int)s.outc; }
+  BSG_HD static int mover(const State& s) { return (popc32(s.x) + popc32(s.o)) & 1; }
+
+  // tic_tac_toe.cc:108-118, the eight lines, as shifts over one 9-bit mask.
+  BSG_HD static bool has_line(u32 b) {
+    u32 rows = b & (b >> 1) & (b >> 2) & 0x49u;
+    u32 cols = b & (b >> 3) & (b >> 6) & 0x7u;
+    u32 diag = b & (b >> 4) & (b >> 8) & 0x1u;
+    u32 anti = (b >> 2) & (b >> 4) & (b >> 6) & 0x1u;
+    return (rows | cols | diag | anti) != 0;
+  }
+  // tic_tac_toe.cc:80-88 + :139-141 (win for the mover only; full board ends the game).
+  BSG_HD static void place(State& s, int cell) {
+    int m = mover(s);
+    u32 b = (m ? s.o : s.x) | (1u << cell);
+    if (m) s.o = b; else s.x = b;
+    bool win = has_line(b);
+    bool full = ((s.x | s.o) & 0x1FFu) == 0x1FFu;
+    s.term = (win || full) ? 1u : 0u;
+    s.outc = win ? (u32)m : (full ? (u32)kOutcomeDraw : (u32)kOutcomeNone);
+  }
+  BSG_HD static u32 step(State& s, u32 r, const Tables& tab, int& action) {
+    u32 empty = ~(s.x | s.o) & 0x1FFu;  // tic_tac_toe.cc:90-100, ascending cell order
+    u32 n = (u32)popc32(empty);
+    u32 k = fastmod(r, n, tab.modM[n & 15]);
+    int cell = select32(empty, (int)k) & 15;
+    action = cell;
+    place(s, cell);
+    return n;
+  }
+  BSG_HD static int legal(const State& s, int* out) {
+    if (terminal(s)) return 0;
+    int n = 0;
+    for (int c = 0; c < 9; ++c) if (!(((s.x | s.o) >> c) & 1)) out[n++] = c;
+    return n;
+  }
+  BSG_HD static bool apply(State& s, int a) {
+    if (terminal(s) || a < 0 || a >= 9 || (((s.x | s.o) >> a) & 1)) return false;
+    place(s, a);
+    return true;
+  }
+  BSG_HD static u32 legal_bit(const State& s, int a) {  // State::LegalActionsMask, spiel.h:244-252
+    return (!s.term && !(((s.x | s.o) >> a) & 1u)) ? 1u : 0u;
+  }
+  // tic_tac_toe.cc:165-175: plane = raw CellState (0 empty, 1 nought = player 1, 2 cross).
+  BSG_HD static u32 obs_bit(const State& s, int player, int idx) {
+    (void)player;
+    int plane = idx / 9, cell = idx - plane * 9;
+    u32 m = plane == 0 ? ~(s.x | s.o) : (plane == 1 ? s.o : s.x);
+    return (m >> cell) & 1u;
+  }
+};
+
+// =========================================================================================
+// connect_four — reference: open_spiel/games/connect_four.cc
+//   6 rows x 7 cols, row 0 at the bottom (connect_four.cc:77-83).  Bit = row * 8 + col: one
+//   guard column per row keeps horizontal/diagonal shifts from wrapping, and the top row
+//   (bits 40..46) gives the 7-bit "column not full" mask with one shift.
+//   packed: 16 B = { x stones (player 0), o stones | meta << 48 };
+//   meta = mover | terminal << 1 | outcome << 2.
+// =========================================================================================
+struct ConnectFour {
+  static constexpr int kId = kGameConnectFour;
+  static constexpr int kNumActions = 7, kMaxLen = 42, kObsSize = 126, kStateBytes = 16;
+  struct State {
+    u64 cur, opp;  // stones of the player to move / of the other player
+    u32 h;         // column heights, 4 bits per column
+    u32 stones, mv, term, outc;
+  };
+  // lut[L] for the 7-bit mask L of non-full columns: .x = modM[popc L],
+  // .y = k-th legal column (3 bits each, ascending) | popc(L) << 24.
+  struct Tables { u32 lut[128][2]; };
+  static void fill_tables(Tables& t) {
+    for (u32 L = 0; L < 128; ++L) {
+      u32 cols = 0, n = 0;
+      for (u32 c = 0; c < 7; ++c) if ((L >> c) & 1) { cols |= c << (3 * n); ++n; }
+      t.lut[L][0] = modM_entry(n);
+      t.lut[L][1] = cols | (n << 24);
+    }
+  }
+  BSG_HD static void init(State& s) {
+    s.cur = 0; s.opp = 0; s.h = 0; s.stones = 0; s.mv = 0; s.term = 0; s.outc = kOutcomeNone;
+  }
+  BSG_HD static void load(State& s, const void* base, int64_t n, int64_t i) {
+    (void)n;
+#if defined(__CUDA_ARCH__)
+    ulonglong2 w = ((const ulonglong2*)base)[i];
+    u64 x = w.x, o = w.y;
+#else
+    u64 x = ((const u64*)base)[2 * i], o = ((const u64*)base)[2 * i + 1];
+#endif
+    u32 meta = (u32)(o >> 48);
+    o &= 0xFFFFFFFFFFFFull;
+    s.mv = meta & 1; s.term = (meta >> 1) & 1; s.outc = (meta >> 2) & 3;
+    s.cur = s.mv ? o : x;
+    s.opp = s.mv ? x : o;
+    u64 occ = x | o;
+    s.stones = (u32)popc64(occ);
+    u32 h = 0;
+#pragma unroll
+    for (int c = 0; c < 7; ++c) h |= (u32)popc64((occ >> c) & 0x010101010101ull) << (4 * c);
+    s.h = h;
+  }
+  BSG_HD static void store(const State& s, void* base, int64_t n, int64_t i) {
+    (void)n;
+    u64 x = s.mv ? s.opp : s.cur, o = s.mv ? s.cur : s.opp;
+    u64 meta = (u64)(s.mv | (s.term << 1) | (s.outc << 2));
+    ((u64*)base)[2 * i] = x;
+    ((u64*)base)[2 * i + 1] = o | (meta << 48);
+  }
+  BSG_HD static bool terminal(const State& s) { return s.term != 0; }
+  BSG_HD static int outcome(const State& s) { return (int)s.outc; }
+  BSG_HD static int mover(const State& s) { return (int)s.mv; }
+
+  // Four-in-a-row anywhere on one player's board: the reference scans every cell in the four
+  // line directions (connect_four.cc:123-152); bit-parallel that is m = b & (b >> d),
+  // m & (m >> 2d) for d = 1 (row), 8 (column), 7 and 9 (diagonals).
+  BSG_HD static bool has_line(u64 b) {
+    u64 acc = 0, m;
+    m = b & (b >> 1); acc |= m & (m >> 2);
+    m = b & (b >> 8); acc |= m & (m >> 16);
+    m = b & (b >> 7); acc |= m & (m >> 14);
+    m = b & (b >> 9); acc |= m & (m >> 18);
+    return acc != 0;
+  }
+  // connect_four.cc:93-106: drop into `col`, win tested before draw, then the turn passes.
+  BSG_HD static void drop(State& s, int col) {
+    u32 row = (s.h >> (4 * col)) & 7u;
+    s.h += 1u << (4 * col);
+    u64 b = s.cur | (1ull << (row * 8 + col));
+    s.stones += 1;
+    bool win = has_line(b);
+    bool full = s.stones == 42;
+    s.term = (win || full) ? 1u : 0u;
+    s.outc = win ? s.mv : (full ? (u32)kOutcomeDraw : (u32)kOutcomeNone);
+    s.cur = s.opp;
+    s.opp = b;
+    s.mv ^= 1u;
+  }
+  BSG_HD static u32 open_columns(const State& s) {
+    return ~(u32)((s.cur | s.opp) >> 40) & 0x7Fu;  // connect_four.cc:108-116
+  }
+  BSG_HD static u32 step(State& s, u32 r, const Tables& tab, int& action) {
+    u32 L = open_columns(s);
+    u32 M = tab.lut[L][0], e = tab.lut[L][1];
+    u32 n = e >> 24;
+    u32 k = fastmod(r, n, M) & 7u;
+    int col = (int)((e >> (3 * k)) & 7u);
+    action = col;
+    drop(s, col);
+    return n;
+  }
+  BSG_HD static int legal(const State& s, int* out) {
+    if (terminal(s)) return 0;
+    u32 L = open_columns(s);
+    int n = 0;
+    for (int c = 0; c < 7; ++c) if ((L >> c) & 1) out[n++] = c;
+    return n;
+  }
+  BSG_HD static bool apply(State& s, int a) {
+    if (terminal(s) || a < 0 || a >= 7 || !((open_columns(s) >> a) & 1)) return false;
+    drop(s, a);
+    return true;
+  }
+  BSG_HD static u32 legal_bit(const State& s, int a) {
+    return (!s.term && ((open_columns(s) >> a) & 1u)) ? 1u : 0u;
+  }
+  // connect_four.cc:198-221: plane 0 = observer's opponent, 1 = observer's own, 2 = empty;
+  // element order plane * 42 + row * 7 + col.
+  BSG_HD static u32 obs_bit(const State& s, int player, int idx) {
+    int plane = idx / 42, cell = idx - plane * 42;
+    int row = cell / 7, col = cell - row * 7;
+    u64 mine = (player == (int)s.mv) ? s.cur : s.opp;
+    u64 theirs = (player == (int)s.mv) ? s.opp : s.cur;
+    u64 m = plane == 0 ? theirs : (plane == 1 ? mine : ~(mine | theirs));
+    return (u32)(m >> (row * 8 + col)) & 1u;
+  }
+};
+
+// =========================================================================================
+// breakthrough 8x8 — reference: open_spiel/games/breakthrough.cc
+//   cell = row * 8 + col; black = player 0 starts on rows 0-1 and moves to row + 1, white on
+//   rows 6-7 moves to row - 1 (breakthrough.cc:36-40,119-142).  Two u64 boards kept relative
+//   to the mover (own / opp) in ABSOLUTE orientation; the colour only changes shift amounts,
+//   expressed as 64-bit rotates so both colours run the same instructions.
+//   Action id = ((row*8 + col)*6 + dir)*2 + capture (spiel_utils.cc:45-58, bases {8,8,6,2}),
+//   dir = 3*colour + o, o = 0,1,2 <-> dcol = -1,0,+1.  Ascending id order = ascending source
+//   cell, then o: the k-th move is found by a weighted rank-select over two bit planes
+//   (low = L^F^R, high = maj(L,F,R) of the per-source legality masks L, F, R).
+//   packed: SoA plane 0 = 16 B {black, white}; plane 1 = u32 meta
+//   (mover | terminal << 1 | outcome << 2).
+// =========================================================================================
+struct Breakthrough {
+  static constexpr int kId = kGameBreakthrough;
+  static constexpr int kNumActions = 768, kMaxLen = 209, kObsSize = 192, kStateBytes = 20;
+  static constexpr u64 kCol0 = 0x0101010101010101ull, kCol7 = 0x8080808080808080ull;
+  struct State { u64 own, opp; u32 mv, term, outc; };
+  struct Tables { u32 modM[64]; };
+  static void fill_tables(Tables& t) { for (u32 n = 0; n < 64; ++n) t.modM[n] = modM_entry(n); }
+
+  BSG_HD static void init(State& s) {
+    s.own = 0x000000000000FFFFull; s.opp = 0xFFFF000000000000ull;
+    s.mv = 0; s.term = 0; s.outc = kOutcomeNone;
+  }
+  BSG_HD static void load(State& s, const void* base, int64_t n, int64_t i) {
+#if defined(__CUDA_ARCH__)
+    ulonglong2 w = ((const ulonglong2*)base)[i];
+    u64 b = w.x, wh = w.y;
+#else
+    u64 b = ((const u64*)base)[2 * i], wh = ((const u64*)base)[2 * i + 1];
+#endif
+    u32 meta = ((const u32*)((const char*)base + 16 * n))[i];
+    s.mv = meta & 1; s.term = (meta >> 1) & 1; s.outc = (meta >> 2) & 3;
+    s.own = s.mv ? wh : b;
+    s.opp = s.mv ? b : wh;
+  }
+  BSG_HD static void store(const State& s, void* base, int64_t n, int64_t i) {
+    ((u64*)base)[2 * i] = s.mv ? s.opp : s.own;
+    ((u64*)base)[2 * i + 1] = s.mv ? s.own : s.opp;
+    ((u32*)((char*)base + 16 * n))[i] = s.mv | (s.term << 1) | (s.outc << 2);
+  }
+  BSG_HD static bool terminal(const State& s) { return s.term != 0; }
+  BSG_HD static int outcome(const State& s) { return (int)s.outc; }
+  BSG_HD static int mover(const State& s) { return (int)s.mv; }
+
+  BSG_HD static u64 rotr64(u64 x, int sh) { return (x >> sh) | (x << ((64 - sh) & 63)); }
+
+  // Per-source legality masks (breakthrough.cc:217-256): forward needs an empty target,
+  // diagonals need a target that is not the mover's own piece (empty = move, enemy = capture).
+  // Target of source i is i + 8 - 1/0/+1 for black, i - 8 - 1/0/+1 for white; reading the
+  // target's occupancy at the source position is a rotate right by 7/8/9 resp. 55/56/57.
+  BSG_HD static void movegen(const State& s, u64& L, u64& F, u64& R) {
+    int base = s.mv ? 48 : 0;
+    u64 occ = s.own | s.opp;
+    F = s.own & ~rotr64(occ, base + 8);
+    L = s.own & ~kCol0 & ~rotr64(s.own, base + 7);
+    R = s.own & ~kCol7 & ~rotr64(s.own, base + 9);
+  }
+  // breakthrough.cc:152-192: move the piece, remove a captured piece, win on reaching the far
+  // row; :306-318: the game also ends when a side has no pieces left.
+  BSG_HD static int move(State& s, int src, int o) {
+    int dst = src + (s.mv ? -8 : 8) + (o - 1);
+    u64 sb = 1ull << src, db = 1ull << (dst & 63);
+    int cap = (int)((s.opp >> (dst & 63)) & 1ull);
+    u64 own = (s.own & ~sb) | db;
+    u64 opp = s.opp & ~db;
+    bool reach = s.mv ? (dst < 8) : (dst >= 56);
+    bool win = reach || opp == 0;
+    int action = ((src * 6) + (int)(3 * s.mv) + o) * 2 + cap;
+    s.term = win ? 1u : 0u;
+    s.outc = win ? s.mv : (u32)kOutcomeNone;
+    s.own = opp;
+    s.opp = own;
+    s.mv ^= 1u;
+    return action;
+  }
+  BSG_HD static u32 step(State& s, u32 r, const Tables& tab, int& action) {
+    u64 L, F, R;
+    movegen(s, L, F, R);
+    u64 lo = L ^ F ^ R, hi = (L & F) | (L & R) | (F & R);
+    u32 n = (u32)(popc64(lo) + 2 * popc64(hi));
+    int k = (int)fastmod(r, n, tab.modM[n & 63]);
+    // weighted rank-select: first source cell i whose inclusive prefix count exceeds k
+    u32 l32 = (u32)lo, h32 = (u32)hi;
+    int pos = 0;
+    int c = popc32(l32) + 2 * popc32(h32);
+    if (k >= c) { k -= c; pos = 32; l32 = (u32)(lo >> 32); h32 = (u32)(hi >> 32); }
+#pragma unroll
+    for (int w = 16; w >= 1; w >>= 1) {
+      u32 m = (1u << w) - 1u;
+      c = popc32(l32 & m) + 2 * popc32(h32 & m);
+      if (k >= c) { k -= c; pos += w; l32 >>= w; h32 >>= w; }
+    }
+    pos &= 63;
+    // k is now the index among this piece's own moves, in o = 0,1,2 order
+    u32 d = (u32)((L >> pos) & 1ull) | ((u32)((F >> pos) & 1ull) << 1) | ((u32)((R >> pos) & 1ull) << 2);
+    if (k >= 1) d &= d - 1;
+    if (k >= 2) d &= d - 1;
+    int o = (d & 1u) ? 0 : ((d & 2u) ? 1 : 2);
+    action = move(s, pos, o);
+    return n;
+  }
+  BSG_HD static int legal(const State& s, int* out) {
+    if (terminal(s)) return 0;
+    u64 L, F, R;
+    movegen(s, L, F, R);
+    int n = 0;
+    for (int i = 0; i < 64; ++i) {
+      for (int o = 0; o < 3; ++o) {
+        u64 m = o == 0 ? L : (o == 1 ? F : R);
+        if (!((m >> i) & 1ull)) continue;
+        int dst = i + (s.mv ? -8 : 8) + (o - 1);
+        int cap = (int)((s.opp >> dst) & 1ull);
+        out[n++] = ((i * 6) + (int)(3 * s.mv) + o) * 2 + cap;
+      }
+    }
+    return n;
+  }
+  BSG_HD static bool apply(State& s, int a) {
+    int list[64];
+    int n = legal(s, list);
+    bool ok = false;
+    for (int i = 0; i < n; ++i) ok |= (list[i] == a);
+    if (!ok) return false;
+    int dir = (a / 2) % 6, src = a / 12;
+    move(s, src, dir - 3 * (int)s.mv);
+    return true;
+  }
+  BSG_HD static u32 legal_bit(const State& s, int a) {
+    int cap = a & 1, dir = (a >> 1) % 6, src = a / 12;
+    int o = dir - 3 * (int)s.mv;
+    if (s.term || o < 0 || o > 2) return 0u;
+    u64 L, F, R;
+    movegen(s, L, F, R);
+    u64 m = o == 0 ? L : (o == 1 ? F : R);
+    int dst = (src + (s.mv ? -8 : 8) + (o - 1)) & 63;
+    return (((m >> src) & 1ull) && (int)((s.opp >> dst) & 1ull) == cap) ? 1u : 0u;
+  }
+  // breakthrough.cc:284-304,326-340: plane 0 black, 1 white, 2 empty, same for both observers.
+  BSG_HD static u32 obs_bit(const State& s, int player, int idx) {
+    (void)player;
+    int plane = idx >> 6, cell = idx & 63;
+    u64 black = s.mv ? s.opp : s.own, white = s.mv ? s.own : s.opp;
+    u64 m = plane == 0 ? black : (plane == 1 ? white : ~(black | white));
+    return (u32)(m >> cell) & 1u;
+  }
+};
+
+// =========================================================================================
+// hex N x N (N = 11 in the product; N = 5 only for the reference's golden playthrough) —
+// reference: open_spiel/games/hex.cc
+//   cell = row * N + col in a 128-bit mask (4 x u32).  Black = player 0 moves first and
+//   connects row 0 ("north") with row N-1; white connects col 0 ("west") with col N-1
+//   (hex.cc:55-121).  The reference keeps, per stone, whether its group touches one of its
+//   colour's edges (9 cell states, hex.h:51-61) and floods that label through adjacent PLAIN
+//   stones of the mover when an edge-connected stone is placed (hex.cc:149-184).  Here the same
+//   sets are bit masks per side — A (north / west), B (south / east), P (plain) — and the
+//   flood is a bit-parallel dilation: its first ring is one table look-up (neighbour mask of
+//   the new cell), further rings use six 128-bit shifts with column guards (hex.cc:206-222).
+//   A winning stone is a member of both A and B; no flood runs on the winning move.
+//   packed: SoA, 4 planes of 16 B: black, white, edgeA (north|west), edgeB (south|east).
+// =========================================================================================
+template <int N>
+struct HexT {
+  static constexpr int kId = kGameHex;
+  static constexpr int kCells = N * N;
+  static constexpr int kNumActions = N * N, kMaxLen = N * N, kObsSize = 9 * N * N;
+  static constexpr int kStateBytes = 64;
+  struct M128 { u32 w[4]; };
+  struct State {
+    u32 occ[4];                       // all stones; bits >= N*N are kept set (never legal)
+    u32 cA[4], cB[4], cP[4];          // mover's stones: edge A, edge B, plain
+    u32 oA[4], oB[4], oP[4];          // the other side's
+    u32 mv, term, outc;
+  };
+  // nb[cell]: neighbour mask; word 3 bits 28..31 carry the edge flags of the cell:
+  // bit 28 row 0, 29 row N-1, 30 col 0, 31 col N-1 (never board cells since N*N <= 124).
+  struct Tables {
+    u32 nb[128][4];
+    u32 modM[128];
+    u32 notColLast[4], notCol0[4];
+  };
+  static void fill_tables(Tables& t) {
+    for (u32 n = 0; n < 128; ++n) t.modM[n] = modM_entry(n);
+    for (int w = 0; w < 4; ++w) { t.notColLast[w] = 0xFFFFFFFFu; t.notCol0[w] = 0xFFFFFFFFu; }
+    for (int c = 0; c < 128; ++c) for (int w = 0; w < 4; ++w) t.nb[c][w] = 0;
+    for (int cell = 0; cell < kCells; ++cell) {
+      int row = cell / N, col = cell % N;
+      if (col == N - 1) t.notColLast[cell >> 5] &= ~(1u << (cell & 31));
+      if (col == 0) t.notCol0[cell >> 5] &= ~(1u << (cell & 31));
+      const int dr[6] = {-1, -1, 0, 0, 1, 1}, dc[6] = {0, 1, -1, 1, -1, 0};  // hex.cc:206-222
+      for (int k = 0; k < 6; ++k) {
+        int r2 = row + dr[k], c2 = col + dc[k];
+        if (r2 < 0 || r2 >= N || c2 < 0 || c2 >= N) continue;
+        int v = r2 * N + c2;
+        t.nb[cell][v >> 5] |= 1u << (v & 31);
+      }
+      if (row == 0) t.nb[cell][3] |= 1u << 28;
+      else if (row == N - 1) t.nb[cell][3] |= 1u << 29;   // "else if" as in hex.cc:70-74
+      if (col == 0) t.nb[cell][3] |= 1u << 30;
+      else if (col == N - 1) t.nb[cell][3] |= 1u << 31;   // hex.cc:95-99
+    }
+  }
+  BSG_HD static u32 pad_word(int w) {  // bits of word w that are not board cells
+    int lo = kCells - 32 * w;
+    return lo >= 32 ? 0u : (lo <= 0 ? 0xFFFFFFFFu : ~((1u << lo) - 1u));
+  }
+  BSG_HD static void init(State& s) {
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      s.occ[w] = pad_word(w);
+      s.cA[w] = s.cB[w] = s.cP[w] = s.oA[w] = s.oB[w] = s.oP[w] = 0;
+    }
+    s.mv = 0; s.term = 0; s.outc = kOutcomeNone;
+  }
+  BSG_HD static void load(State& s, const void* base, int64_t n, int64_t i) {
+    u32 bl[4], wh[4], ea[4], eb[4];
+#if defined(__CUDA_ARCH__)
+    const uint4* p = (const uint4*)base;
+    uint4 q0 = p[i], q1 = p[n + i], q2 = p[2 * n + i], q3 = p[3 * n + i];
+    bl[0] = q0.x; bl[1] = q0.y; bl[2] = q0.z; bl[3] = q0.w;
+    wh[0] = q1.x; wh[1] = q1.y; wh[2] = q1.z; wh[3] = q1.w;
+    ea[0] = q2.x; ea[1] = q2.y; ea[2] = q2.z; ea[3] = q2.w;
+    eb[0] = q3.x; eb[1] = q3.y; eb[2] = q3.z; eb[3] = q3.w;
+#else
+    const u32* p = (const u32*)base;
+    for (int w = 0; w < 4; ++w) {
+      bl[w] = p[4 * i + w]; wh[w] = p[4 * (n + i) + w];
+      ea[w] = p[4 * (2 * n + i) + w]; eb[w] = p[4 * (3 * n + i) + w];
+    }
+#endif
+    int nb = 0, nw = 0;
+    u32 winb = 0, winw = 0;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      nb += popc32(bl[w]); nw += popc32(wh[w]);
+      winb |= bl[w] & ea[w] & eb[w]; winw |= wh[w] & ea[w] & eb[w];
+    }
+    s.mv = nb > nw ? 1u : 0u;  // black moves first and turns alternate
+    s.term = (winb | winw) ? 1u : 0u;
+    s.outc = winb ? (u32)kOutcomeP0 : (winw ? (u32)kOutcomeP1 : (u32)kOutcomeNone);
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      s.occ[w] = bl[w] | wh[w] | pad_word(w);
+      u32 bA = bl[w] & ea[w], bB = bl[w] & eb[w], bP = bl[w] & ~(ea[w] | eb[w]);
+      u32 wA = wh[w] & ea[w], wB = wh[w] & eb[w], wP = wh[w] & ~(ea[w] | eb[w]);
+      s.cA[w] = s.mv ? wA : bA; s.cB[w] = s.mv ? wB : bB; s.cP[w] = s.mv ? wP : bP;
+      s.oA[w] = s.mv ? bA : wA; s.oB[w] = s.mv ? bB : wB; s.oP[w] = s.mv ? bP : wP;
+    }
+  }
+  BSG_HD static void store(const State& s, void* base, int64_t n, int64_t i) {
+    u32* p = (u32*)base;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      u32 cur = s.cA[w] | s.cB[w] | s.cP[w], oth = s.oA[w] | s.oB[w] | s.oP[w];
+      p[4 * i + w] = s.mv ? oth : cur;
+      p[4 * (n + i) + w] = s.mv ? cur : oth;
+      p[4 * (2 * n + i) + w] = s.cA[w] | s.oA[w];
+      p[4 * (3 * n + i) + w] = s.cB[w] | s.oB[w];
+    }
+  }
+  BSG_HD static bool terminal(const State& s) { return s.term != 0; }
+  BSG_HD static int outcome(const State& s) { return (int)s.outc; }
+  BSG_HD static int mover(const State& s) { return (int)s.mv; }
+
+  // One ring of neighbours of every cell in f (hex.cc:206-222 for a whole set at once).
+  BSG_HD static void dilate(const u32 f[4], const Tables& t, u32 out[4]) {
+    u32 a[4], b[4];
+#pragma unroll
+    for (int w = 0; w < 4; ++w) { a[w] = f[w] & t.notColLast[w]; b[w] = f[w] & t.notCol0[w]; }
+    // +1 and -(N-1) from a; -1 and +(N-1) from b; +N and -N from f
+    out[0] = (a[0] << 1) | fshr(a[0], a[1], N - 1) | fshr(b[0], b[1], 1) | (b[0] << (N - 1)) |
+             (f[0] << N) | fshr(f[0], f[1], N);
+    out[1] = fshl(a[0], a[1], 1) | fshr(a[1], a[2], N - 1) | fshr(b[1], b[2], 1) |
+             fshl(b[0], b[1], N - 1) | fshl(f[0], f[1], N) | fshr(f[1], f[2], N);
+    out[2] = fshl(a[1], a[2], 1) | fshr(a[2], a[3], N - 1) | fshr(b[2], b[3], 1) |
+             fshl(b[1], b[2], N - 1) | fshl(f[1], f[2], N) | fshr(f[2], f[3], N);
+    out[3] = fshl(a[2], a[3], 1) | (a[3] >> (N - 1)) | (b[3] >> 1) | fshl(b[2], b[3], N - 1) |
+             fshl(f[2], f[3], N) | (f[3] >> N);
+  }
+
+  // hex.cc:149-184 for the mover: label from edges + neighbours, win, or flood.
+  BSG_HD static void place(State& s, int cell, const Tables& t) {
+    int cw = cell >> 5;
+    u32 bit = 1u << (cell & 31);
+    u32 m[4], nb[4];
+#pragma unroll
+    for (int w = 0; w < 4; ++w) { m[w] = (w == cw) ? bit : 0u; nb[w] = t.nb[cell][w]; }
+    u32 flags = nb[3] >> (28 + 2 * s.mv);  // bit 0: on edge A, bit 1: on edge B
+    u32 hitA = 0, hitB = 0;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) { hitA |= nb[w] & s.cA[w]; hitB |= nb[w] & s.cB[w]; }
+    bool tA = (hitA != 0) || (flags & 1u), tB = (hitB != 0) || (flags & 2u);
+    bool win = tA && tB;
+    u32 add[4];
+#pragma unroll
+    for (int w = 0; w < 4; ++w) { s.occ[w] |= m[w]; add[w] = m[w]; }
+    if ((tA || tB) && !win) {
+      // first ring from the table, later rings by dilation, through plain stones only
+      u32 fr[4], any = 0;
+#pragma unroll
+      for (int w = 0; w < 4; ++w) { fr[w] = nb[w] & s.cP[w]; any |= fr[w]; }
+      while (any) {
+        u32 d[4];
+#pragma unroll
+        for (int w = 0; w < 4; ++w) { s.cP[w] &= ~fr[w]; add[w] |= fr[w]; }
+        dilate(fr, t, d);
+        any = 0;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) { fr[w] = d[w] & s.cP[w]; any |= fr[w]; }
+      }
+    }
+    u32 toA = tA ? 0xFFFFFFFFu : 0u, toB = tB ? 0xFFFFFFFFu : 0u;  // win: both
+    u32 toP = (tA || tB) ? 0u : 0xFFFFFFFFu;
+    u32 na[4], nbb[4], np[4];
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      na[w] = s.cA[w] | (add[w] & toA);
+      nbb[w] = s.cB[w] | (add[w] & toB);
+      np[w] = s.cP[w] | (add[w] & toP);
+      s.cA[w] = s.oA[w]; s.cB[w] = s.oB[w]; s.cP[w] = s.oP[w];
+      s.oA[w] = na[w]; s.oB[w] = nbb[w]; s.oP[w] = np[w];
+    }
+    s.term = win ? 1u : 0u;
+    s.outc = win ? s.mv : (u32)kOutcomeNone;
+    s.mv ^= 1u;
+  }
+  BSG_HD static u32 step(State& s, u32 r, const Tables& tab, int& action) {
+    u32 e0 = ~s.occ[0], e1 = ~s.occ[1], e2 = ~s.occ[2], e3 = ~s.occ[3];  // hex.cc:186-196
+    int c0 = popc32(e0), c1 = c0 + popc32(e1), c2 = c1 + popc32(e2), n = c2 + popc32(e3);
+    int k = (int)fastmod(r, (u32)n, tab.modM[n & 127]);
+    int w = (k >= c0) + (k >= c1) + (k >= c2);
+    u32 x = w == 0 ? e0 : (w == 1 ? e1 : (w == 2 ? e2 : e3));
+    int kk = k - (w == 0 ? 0 : (w == 1 ? c0 : (w == 2 ? c1 : c2)));
+    int cell = (32 * w + select32(x, kk)) & 127;
+    action = cell;
+    place(s, cell, tab);
+    return (u32)n;
+  }
+  BSG_HD static int legal(const State& s, int* out) {
+    if (terminal(s)) return 0;
+    int n = 0;
+    for (int c = 0; c < kCells; ++c) if (!((s.occ[c >> 5] >> (c & 31)) & 1u)) out[n++] = c;
+    return n;
+  }
+  BSG_HD static bool apply(State& s, int a, const Tables& t) {
+    if (terminal(s) || a < 0 || a >= kCells || ((s.occ[a >> 5] >> (a & 31)) & 1u)) return false;
+    place(s, a, t);
+    return true;
+  }
+  BSG_HD static u32 legal_bit(const State& s, int a) {
+    return (!s.term && !((s.occ[a >> 5] >> (a & 31)) & 1u)) ? 1u : 0u;
+  }
+  // hex.cc:266-277: plane = CellState + 4: 0 WhiteWin, 1 WhiteWest, 2 WhiteEast, 3 White,
+  // 4 Empty, 5 Black, 6 BlackSouth, 7 BlackNorth, 8 BlackWin; same for both observers.
+  BSG_HD static u32 obs_bit(const State& s, int player, int idx) {
+    (void)player;
+    int plane = idx / kCells, cell = idx - plane * kCells;
+    int w = cell >> 5, b = cell & 31;
+    u32 bA = (s.mv ? s.oA[w] : s.cA[w]) >> b & 1u, bB = (s.mv ? s.oB[w] : s.cB[w]) >> b & 1u;
+    u32 bP = (s.mv ? s.oP[w] : s.cP[w]) >> b & 1u;
+    u32 wA = (s.mv ? s.cA[w] : s.oA[w]) >> b & 1u, wB = (s.mv ? s.cB[w] : s.oB[w]) >> b & 1u;
+    u32 wP = (s.mv ? s.cP[w] : s.oP[w]) >> b & 1u;
+    switch (plane) {
+      case 0: return wA & wB;
+      case 1: return wA & ~wB & 1u;
+      case 2: return wB & ~wA & 1u;
+      case 3: return wP;
+      case 4: return (~s.occ[w] >> b) & 1u;
+      case 5: return bP;
+      case 6: return bB & ~bA & 1u;
+      case 7: return bA & ~bB & 1u;
+      default: return bA & bB;
+    }
+  }
+};
+typedef HexT<11> Hex;
+
+}  // namespace bsg

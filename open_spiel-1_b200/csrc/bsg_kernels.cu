@@ -1,0 +1,623 @@
+// CUDA kernels + C ABI of the batched playout engine.  sm_100a only; integer pipes only.
+//
+// Playout kernel design:
+//  * one playout per lane, whole game state in registers (per-game bitboards, bsg_games.cuh);
+//  * persistent CTAs: each CTA owns a contiguous slice of the launch's playouts and its lanes
+//    claim the next playout from a shared-memory counter when they finish (lane refill), so a
+//    warp keeps ~all lanes busy although game lengths differ;
+//  * steps run in groups of four: one Philox4x32-10 block (4 draws) per group, and lanes are
+//    refilled only at group boundaries, which keeps every lane's step index congruent to the
+//    group phase — the RNG and the refill code stay warp-convergent;
+//  * a step is unconditional straight-line code (finished lanes run dead steps on a dead
+//    state); only the bookkeeping is predicated.
+#include <cooperative_groups.h>
+#include <cuda_runtime.h>
+#include <stdio.h>
+
+#include <mutex>
+#include <new>
+#include <string>
+
+#include "bsg_host.cuh"
+
+namespace cg = cooperative_groups;
+namespace bsg {
+
+constexpr int kThreads = 256;
+
+struct PlayoutArgs {
+  const void* roots;
+  int64_t n_roots;
+  uint32_t n_playouts;
+  uint32_t rollouts;
+  uint64_t first_playout;
+  PhiloxKeys keys;
+  bsg_playout_io io;
+};
+
+template <class G, bool kFull>
+__global__ void __launch_bounds__(kThreads)
+playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab) {
+  __shared__ typename G::Tables tab;
+  __shared__ unsigned int s_next;
+  {
+    const u32* src = reinterpret_cast<const u32*>(gtab);
+    u32* dst = reinterpret_cast<u32*>(&tab);
+    for (int i = threadIdx.x; i < (int)(sizeof(typename G::Tables) / 4); i += kThreads) dst[i] = src[i];
+    if (threadIdx.x == 0) s_next = 0;
+  }
+  __syncthreads();
+
+  // contiguous slice of this CTA
+  const u32 per = (a.n_playouts + gridDim.x - 1) / gridDim.x;
+  const u32 begin = min(per * blockIdx.x, a.n_playouts);
+  const u32 count = min(per, a.n_playouts - begin);
+
+  typename G::State s;
+  G::init(s);
+  typename G::State prev;
+  if (kFull) G::init(prev);
+  bool active = false, have = false, exhausted = false;
+  u32 lid = 0, t = 0, limit = 0xFFFFFFFFu;
+  u32 fin_len = 0, fin_term = 0;
+  int fin_ret = 0;
+  unsigned long long my_steps = 0;
+  long long my_ret = 0;
+  u32 my_done = 0, my_stuck = 0;
+
+  for (;;) {
+    if (!active) {
+      if (have) {  // publish the finished playout
+        have = false;
+        if (a.io.ret0) a.io.ret0[lid] = (int8_t)fin_ret;
+        if (a.io.length) a.io.length[lid] = (uint8_t)fin_len;
+        if (a.io.terminal) a.io.terminal[lid] = (uint8_t)fin_term;
+        if (a.io.root_sum_ret0 || a.io.root_sum_steps) {
+          u32 root = a.rollouts == 1 ? lid : lid / a.rollouts;
+          if (a.io.root_sum_ret0 && fin_ret != 0) atomicAdd(a.io.root_sum_ret0 + root, fin_ret);
+          if (a.io.root_sum_steps) atomicAdd(a.io.root_sum_steps + root, (int)fin_len);
+        }
+        my_steps += fin_len;
+        my_ret += fin_ret;
+        my_done += 1;
+      }
+      if (!exhausted) {  // claim the next playout of this CTA's slice
+        cg::coalesced_group grp = cg::coalesced_threads();
+        u32 base = 0;
+        if (grp.thread_rank() == 0) base = atomicAdd(&s_next, grp.size());
+        u32 idx = grp.shfl(base, 0) + grp.thread_rank();
+        if (idx < count) {
+          lid = begin + idx;
+          u32 root = a.rollouts == 1 ? lid : lid / a.rollouts;
+          G::load(s, a.roots, a.n_roots, root);
+          t = 0;
+          have = true;
+          if (kFull) {
+            limit = a.io.max_steps > 0 ? (u32)a.io.max_steps : 0xFFFFFFFFu;
+            if (a.io.step_limit) limit = min(limit, (u32)a.io.step_limit[lid]);
+            prev = s;
+          }
+          active = !G::terminal(s) && (!kFull || limit > 0);
+          fin_len = 0;
+          fin_term = G::terminal(s) ? 1u : 0u;
+          fin_ret = outcome_ret0(G::outcome(s));
+          if (kFull && !active && a.io.final_states) G::store(s, a.io.final_states, a.n_playouts, lid);
+        } else {
+          exhausted = true;
+        }
+      }
+    }
+    if (!__any_sync(0xFFFFFFFFu, active)) {
+      if (!__any_sync(0xFFFFFFFFu, have)) break;
+      continue;
+    }
+
+    const unsigned long long pid = a.first_playout + lid;
+    u32 rr[4];
+    philox4x32_10((u32)pid, (u32)(pid >> 32), t >> 2, 0u, a.keys, rr);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      u32 r = rr[j];
+      if (kFull) {
+        if (a.io.r_table && active) r = a.io.r_table[(size_t)lid * a.io.r_stride + min(t, (u32)a.io.r_stride - 1)];
+        if (active) prev = s;
+      }
+      int action;
+      const u32 nlegal = G::step(s, r, tab, action);
+      if (active && nlegal == 0) {  // non-terminal state without a legal action
+        active = false;
+        my_stuck += 1;
+        fin_len = t;
+        fin_term = 0;
+        fin_ret = 0;
+        if (kFull && a.io.final_states) G::store(prev, a.io.final_states, a.n_playouts, lid);
+      }
+      if (active) {
+        if (kFull && a.io.actions && t < (u32)a.io.actions_stride)
+          a.io.actions[(size_t)lid * a.io.actions_stride + t] = (int16_t)action;
+        t += 1;
+        bool term = G::terminal(s);
+        if (term || (kFull && t >= limit)) {
+          active = false;
+          fin_len = t;
+          fin_term = term ? 1u : 0u;
+          fin_ret = outcome_ret0(G::outcome(s));
+          if (kFull && a.io.final_states) {
+            if (term && a.io.final_before_terminal) G::store(prev, a.io.final_states, a.n_playouts, lid);
+            else G::store(s, a.io.final_states, a.n_playouts, lid);
+          }
+        }
+      }
+    }
+  }
+
+  if (a.io.totals) {
+    unsigned long long st = my_steps;
+    long long rt = my_ret;
+    u32 dn = my_done, sk = my_stuck;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      st += __shfl_xor_sync(0xFFFFFFFFu, st, o);
+      rt += __shfl_xor_sync(0xFFFFFFFFu, rt, o);
+      dn += __shfl_xor_sync(0xFFFFFFFFu, dn, o);
+      sk += __shfl_xor_sync(0xFFFFFFFFu, sk, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+      atomicAdd((unsigned long long*)a.io.totals + 0, (unsigned long long)dn);
+      atomicAdd((unsigned long long*)a.io.totals + 1, st);
+      atomicAdd((unsigned long long*)a.io.totals + 2, (unsigned long long)rt);
+      if (sk) atomicAdd((unsigned long long*)a.io.totals + 3, (unsigned long long)sk);
+    }
+  }
+}
+
+
+// ---------------------------------------------------------------------------------------
+// Batched ObservationTensor / LegalActionsMask writer.  HBM-write bound: every thread emits
+// one 16-byte store (4 floats / 16 mask bytes) of the flat [n, size] output, so each warp
+// store instruction covers 512 contiguous bytes.  Packed states are re-read through L1/L2
+// (16-64 B per state against 108-4356 B written).
+// ---------------------------------------------------------------------------------------
+template <class G>
+__global__ void __launch_bounds__(kThreads)
+obs_kernel(const void* __restrict__ states, int64_t n, const uint8_t* __restrict__ players,
+           float* __restrict__ out) {
+  const int64_t total = n * G::kObsSize;
+  const int64_t total4 = (total + 3) >> 2;
+  const int64_t stride = (int64_t)gridDim.x * kThreads;
+  for (int64_t g = (int64_t)blockIdx.x * kThreads + threadIdx.x; g < total4; g += stride) {
+    int64_t e0 = g << 2;
+    int64_t st = e0 / G::kObsSize;
+    int idx = (int)(e0 - st * G::kObsSize);
+    typename G::State s;
+    G::load(s, states, n, st);
+    int player = players ? (int)players[st] : G::mover(s);
+    float v[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      if (idx == G::kObsSize) {
+        idx = 0;
+        st += 1;
+        if (st < n) {
+          G::load(s, states, n, st);
+          player = players ? (int)players[st] : G::mover(s);
+        }
+      }
+      v[q] = (st < n) ? (float)G::obs_bit(s, player, idx) : 0.f;
+      idx += 1;
+    }
+    if (e0 + 4 <= total) {
+      __stcs(reinterpret_cast<float4*>(out) + g, make_float4(v[0], v[1], v[2], v[3]));
+    } else {
+      for (int q = 0; q < 4 && e0 + q < total; ++q) out[e0 + q] = v[q];
+    }
+  }
+}
+
+template <class G>
+__global__ void __launch_bounds__(kThreads)
+legal_mask_kernel(const void* __restrict__ states, int64_t n, uint8_t* __restrict__ out) {
+  const int64_t total = n * G::kNumActions;
+  const int64_t total16 = (total + 15) >> 4;
+  const int64_t stride = (int64_t)gridDim.x * kThreads;
+  for (int64_t g = (int64_t)blockIdx.x * kThreads + threadIdx.x; g < total16; g += stride) {
+    int64_t e0 = g << 4;
+    int64_t st = e0 / G::kNumActions;
+    int idx = (int)(e0 - st * G::kNumActions);
+    typename G::State s;
+    G::load(s, states, n, st);
+    u32 w[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {
+      if (idx == G::kNumActions) {
+        idx = 0;
+        st += 1;
+        if (st < n) G::load(s, states, n, st);
+      }
+      u32 b = (st < n) ? G::legal_bit(s, idx) : 0u;
+      w[q >> 2] |= b << (8 * (q & 3));
+      idx += 1;
+    }
+    if (e0 + 16 <= total) {
+      __stcs(reinterpret_cast<uint4*>(out) + g, make_uint4(w[0], w[1], w[2], w[3]));
+    } else {
+      for (int q = 0; q < 16 && e0 + q < total; ++q) out[e0 + q] = (uint8_t)((w[q >> 2] >> (8 * (q & 3))) & 0xFF);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// Integer-issue microbenchmark (roofline denominator).  8 independent chains per thread.
+// ---------------------------------------------------------------------------------------
+template <int KIND>
+__global__ void __launch_bounds__(kThreads) int_peak_kernel(int iters, u32* sink) {
+  u32 x[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) x[i] = threadIdx.x * 2654435761u + i * 40503u + blockIdx.x;
+  u32 k = blockIdx.x | 1u;
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int rep = 0; rep < 8; ++rep) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        if (KIND == 0) x[i] = (x[i] ^ k) + (x[(i + 1) & 7] & 0x55555555u) ;          // LOP3 + IADD3
+        else if (KIND == 1) x[i] = x[i] * 0x9E3779B1u + k;                             // IMAD
+        else { x[i] = (x[i] ^ (x[(i + 3) & 7] >> 3)); x[i] = x[i] * 0x9E3779B1u + k; } // SHF/LOP + IMAD
+      }
+    }
+  }
+  u32 acc = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc ^= x[i];
+  if (acc == 0x12345678u) sink[0] = acc;
+}
+
+}  // namespace bsg
+
+// =========================================================================================
+// C ABI
+// =========================================================================================
+using namespace bsg;
+
+struct bsg_engine {
+  int game = -1;
+  int device = -1;
+  int sm_count = 0;
+  void* tables_dev = nullptr;
+  // scratch for the *_host wrappers
+  void* d_roots = nullptr; size_t d_roots_bytes = 0;
+  void* d_out = nullptr; size_t d_out_bytes = 0;
+  void* h_pinned = nullptr; size_t h_pinned_bytes = 0;
+  uint64_t* d_totals = nullptr;
+  cudaStream_t own_stream = nullptr;
+  std::string err;
+};
+
+namespace {
+int fail(bsg_engine* e, int code, const std::string& msg) {
+  if (e) e->err = msg;
+  return code;
+}
+int cuda_fail(bsg_engine* e, cudaError_t st, const char* what) {
+  return fail(e, BSG_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(st));
+}
+#define BSG_CUDA(e, call)                                   \
+  do {                                                      \
+    cudaError_t st__ = (call);                              \
+    if (st__ != cudaSuccess) return cuda_fail(e, st__, #call); \
+  } while (0)
+
+int ensure(bsg_engine* e, void** p, size_t* have, size_t need, bool pinned) {
+  if (*have >= need) return BSG_OK;
+  if (*p) { if (pinned) cudaFreeHost(*p); else cudaFree(*p); *p = nullptr; *have = 0; }
+  size_t cap = need + need / 4 + 256;
+  BSG_CUDA(e, pinned ? cudaMallocHost(p, cap) : cudaMalloc(p, cap));
+  *have = cap;
+  return BSG_OK;
+}
+
+struct FactOp {
+  int which;
+  template <class G> int operator()() const {
+    return which == 0 ? G::kNumActions : (which == 1 ? G::kMaxLen : (which == 2 ? G::kObsSize : G::kStateBytes));
+  }
+};
+
+struct CreateOp {
+  bsg_engine* e;
+  template <class G> int operator()() const {
+    typename G::Tables t;
+    G::fill_tables(t);
+    BSG_CUDA(e, cudaMalloc(&e->tables_dev, sizeof(t)));
+    BSG_CUDA(e, cudaMemcpy(e->tables_dev, &t, sizeof(t), cudaMemcpyHostToDevice));
+    return BSG_OK;
+  }
+};
+
+template <class G, bool kFull>
+int launch_playouts(bsg_engine* e, const PlayoutArgs& a, cudaStream_t st) {
+  static int blocks_per_sm = 0;
+  if (blocks_per_sm == 0) {
+    int b = 0;
+    BSG_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, playout_kernel<G, kFull>, kThreads, 0));
+    blocks_per_sm = b > 0 ? b : 1;
+  }
+  int64_t max_grid = (int64_t)e->sm_count * blocks_per_sm;
+  int64_t need = ((int64_t)a.n_playouts + kThreads - 1) / kThreads;
+  int grid = (int)(need < max_grid ? need : max_grid);
+  if (grid < 1) grid = 1;
+  playout_kernel<G, kFull><<<grid, kThreads, 0, st>>>(a, (const typename G::Tables*)e->tables_dev);
+  BSG_CUDA(e, cudaGetLastError());
+  return BSG_OK;
+}
+
+struct PlayoutOp {
+  bsg_engine* e; PlayoutArgs a; cudaStream_t st;
+  template <class G> int operator()() const {
+    const bsg_playout_io& io = a.io;
+    bool full = io.max_steps > 0 || io.step_limit || io.r_table || io.actions || io.final_states;
+    return full ? launch_playouts<G, true>(e, a, st) : launch_playouts<G, false>(e, a, st);
+  }
+};
+
+struct ObsOp2 {
+  bsg_engine* e; const void* states; int64_t n; const uint8_t* players; float* obs; uint8_t* mask;
+  cudaStream_t st;
+  template <class G> int operator()() const {
+    int64_t cap = (int64_t)e->sm_count * 8;
+    if (obs) {
+      int64_t total4 = (n * G::kObsSize + 3) / 4;
+      int64_t need = (total4 + kThreads - 1) / kThreads;
+      int grid = (int)(need < cap ? need : cap);
+      obs_kernel<G><<<grid < 1 ? 1 : grid, kThreads, 0, st>>>(states, n, players, obs);
+      BSG_CUDA(e, cudaGetLastError());
+    }
+    if (mask) {
+      int64_t total16 = (n * G::kNumActions + 15) / 16;
+      int64_t need = (total16 + kThreads - 1) / kThreads;
+      int grid = (int)(need < cap ? need : cap);
+      legal_mask_kernel<G><<<grid < 1 ? 1 : grid, kThreads, 0, st>>>(states, n, mask);
+      BSG_CUDA(e, cudaGetLastError());
+    }
+    return BSG_OK;
+  }
+};
+}  // namespace
+
+extern "C" {
+
+int bsg_version(void) { return BSG_VERSION; }
+
+const char* bsg_error_string(int code) {
+  switch (code) {
+    case BSG_OK: return "ok";
+    case BSG_ERR_BAD_GAME: return "unsupported game";
+    case BSG_ERR_BAD_ARG: return "bad argument";
+    case BSG_ERR_ILLEGAL_ACTION: return "illegal action";
+    case BSG_ERR_CUDA: return "CUDA error";
+    case BSG_ERR_NO_DEVICE: return "no CUDA device";
+    case BSG_ERR_STUCK_LANE: return "non-terminal state without legal actions";
+    default: return "unknown error";
+  }
+}
+
+int bsg_game_id(const char* g) {
+  if (!g) return BSG_ERR_BAD_GAME;
+  std::string s(g);
+  if (s == "tic_tac_toe" || s == "tic_tac_toe()") return BSG_TIC_TAC_TOE;
+  if (s == "connect_four" || s == "connect_four()") return BSG_CONNECT_FOUR;
+  if (s == "breakthrough" || s == "breakthrough()" || s == "breakthrough(rows=8,columns=8)" ||
+      s == "breakthrough(columns=8,rows=8)") return BSG_BREAKTHROUGH;
+  if (s == "hex" || s == "hex()" || s == "hex(board_size=11)") return BSG_HEX;
+  if (s == "hex(board_size=5)") return BSG_HEX5_HOST_ONLY;
+  return BSG_ERR_BAD_GAME;
+}
+
+int bsg_num_distinct_actions(int game) { return dispatch_game(game, FactOp{0}); }
+int bsg_max_game_length(int game) { return dispatch_game(game, FactOp{1}); }
+int bsg_observation_size(int game) { return dispatch_game(game, FactOp{2}); }
+int bsg_state_bytes(int game) { return dispatch_game(game, FactOp{3}); }
+
+int bsg_observation_shape(int game, int shape[3]) {
+  switch (game) {
+    case BSG_TIC_TAC_TOE: shape[0] = 3; shape[1] = 3; shape[2] = 3; return BSG_OK;   // tic_tac_toe.h:105-107
+    case BSG_CONNECT_FOUR: shape[0] = 3; shape[1] = 6; shape[2] = 7; return BSG_OK;  // connect_four.h:112-114
+    case BSG_BREAKTHROUGH: shape[0] = 3; shape[1] = 8; shape[2] = 8; return BSG_OK;  // breakthrough.h:107-109
+    case BSG_HEX: shape[0] = 9; shape[1] = 11; shape[2] = 11; return BSG_OK;         // hex.h:113-115
+    case BSG_HEX5_HOST_ONLY: shape[0] = 9; shape[1] = 5; shape[2] = 5; return BSG_OK;
+    default: return BSG_ERR_BAD_GAME;
+  }
+}
+
+int bsg_pack_histories(int game, const int64_t* flat, const int64_t* off, int64_t n, void* out, int64_t cap) {
+  if (!off || !out || n < 0 || cap < n) return BSG_ERR_BAD_ARG;
+  return dispatch_game(game, PackOp{flat, off, n, out, cap});
+}
+int bsg_host_state_info(int game, const void* p, int64_t cap, int64_t i, int* cur, int* term, int* ret0) {
+  if (!p || i < 0 || i >= cap) return BSG_ERR_BAD_ARG;
+  return dispatch_game(game, InfoOp{p, cap, i, cur, term, ret0});
+}
+int bsg_host_legal_actions(int game, const void* p, int64_t cap, int64_t i, int64_t* out, int capacity) {
+  if (!p || !out || i < 0 || i >= cap) return BSG_ERR_BAD_ARG;
+  return dispatch_game(game, LegalOp{p, cap, i, out, capacity});
+}
+int bsg_host_apply_action(int game, void* p, int64_t cap, int64_t i, int64_t a) {
+  if (!p || i < 0 || i >= cap) return BSG_ERR_BAD_ARG;
+  return dispatch_game(game, ApplyOp{p, cap, i, a});
+}
+int bsg_host_observation(int game, const void* p, int64_t cap, int64_t i, int player, float* out) {
+  if (!p || !out || i < 0 || i >= cap || player < 0 || player > 1) return BSG_ERR_BAD_ARG;
+  return dispatch_game(game, ObsOp{p, cap, i, player, out});
+}
+int bsg_host_replay_step(int game, void* p, int64_t cap, int64_t i, uint32_t r, int64_t* action) {
+  if (!p || i < 0 || i >= cap) return BSG_ERR_BAD_ARG;
+  return dispatch_game(game, StepOp{p, cap, i, r, action});
+}
+uint32_t bsg_draw(uint64_t seed, uint64_t playout, uint32_t t) {
+  PhiloxKeys ks;
+  philox_schedule(seed, ks);
+  u32 out[4];
+  philox4x32_10((u32)playout, (u32)(playout >> 32), t >> 2, 0u, ks, out);
+  return out[t & 3];
+}
+
+int bsg_create(int game, int device, bsg_engine** out) {
+  if (!out) return BSG_ERR_BAD_ARG;
+  *out = nullptr;
+  if (game < 0 || game > BSG_HEX) return BSG_ERR_BAD_GAME;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return BSG_ERR_NO_DEVICE;
+  if (device < 0 || device >= count) return BSG_ERR_BAD_ARG;
+  bsg_engine* e = new (std::nothrow) bsg_engine();
+  if (!e) return BSG_ERR_BAD_ARG;
+  e->game = game;
+  e->device = device;
+  *out = e;  // returned even on failure so bsg_last_error is readable; caller destroys it
+  BSG_CUDA(e, cudaSetDevice(device));
+  cudaDeviceProp prop;
+  BSG_CUDA(e, cudaGetDeviceProperties(&prop, device));
+  e->sm_count = prop.multiProcessorCount;
+  BSG_CUDA(e, cudaStreamCreateWithFlags(&e->own_stream, cudaStreamNonBlocking));
+  BSG_CUDA(e, cudaMalloc(&e->d_totals, 4 * sizeof(uint64_t)));
+  return dispatch_device_game(game, CreateOp{e});
+}
+
+void bsg_destroy(bsg_engine* e) {
+  if (!e) return;
+  if (e->device >= 0) cudaSetDevice(e->device);
+  if (e->tables_dev) cudaFree(e->tables_dev);
+  if (e->d_roots) cudaFree(e->d_roots);
+  if (e->d_out) cudaFree(e->d_out);
+  if (e->h_pinned) cudaFreeHost(e->h_pinned);
+  if (e->d_totals) cudaFree(e->d_totals);
+  if (e->own_stream) cudaStreamDestroy(e->own_stream);
+  delete e;
+}
+const char* bsg_last_error(bsg_engine* e) { return e ? e->err.c_str() : "null engine"; }
+int bsg_engine_game(const bsg_engine* e) { return e ? e->game : BSG_ERR_BAD_ARG; }
+int bsg_engine_device(const bsg_engine* e) { return e ? e->device : BSG_ERR_BAD_ARG; }
+int bsg_engine_sm_count(const bsg_engine* e) { return e ? e->sm_count : BSG_ERR_BAD_ARG; }
+
+int bsg_playouts(bsg_engine* e, const void* roots, int64_t n_roots, int32_t rollouts, uint64_t seed,
+                 uint64_t first_playout, const bsg_playout_io* io, void* stream) {
+  if (!e) return BSG_ERR_BAD_ARG;
+  if (!roots || n_roots < 0 || rollouts < 1) return fail(e, BSG_ERR_BAD_ARG, "bad roots/rollouts");
+  int64_t total = n_roots * (int64_t)rollouts;
+  if (total >= (int64_t)1 << 32) return fail(e, BSG_ERR_BAD_ARG, "more than 2^32-1 playouts in one launch");
+  if (total == 0) return BSG_OK;
+  PlayoutArgs a;
+  memset(&a, 0, sizeof(a));
+  a.roots = roots; a.n_roots = n_roots; a.n_playouts = (uint32_t)total; a.rollouts = (uint32_t)rollouts;
+  a.first_playout = first_playout;
+  philox_schedule(seed, a.keys);
+  if (io) a.io = *io;
+  if (a.io.r_table && a.io.r_stride < 1) return fail(e, BSG_ERR_BAD_ARG, "r_table needs r_stride >= 1");
+  if (a.io.actions && a.io.actions_stride < 1) return fail(e, BSG_ERR_BAD_ARG, "actions needs actions_stride >= 1");
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  return dispatch_device_game(e->game, PlayoutOp{e, a, (cudaStream_t)stream});
+}
+
+int bsg_observations(bsg_engine* e, const void* states, int64_t n, const uint8_t* players, float* obs,
+                     uint8_t* mask, void* stream) {
+  if (!e) return BSG_ERR_BAD_ARG;
+  if (!states || n < 0 || (!obs && !mask)) return fail(e, BSG_ERR_BAD_ARG, "bad observation arguments");
+  if (n == 0) return BSG_OK;
+  if (((uintptr_t)obs & 15) || ((uintptr_t)mask & 15)) return fail(e, BSG_ERR_BAD_ARG, "outputs must be 16-byte aligned");
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  return dispatch_device_game(e->game, ObsOp2{e, states, n, players, obs, mask, (cudaStream_t)stream});
+}
+
+int bsg_playouts_host(bsg_engine* e, const void* roots_host, int64_t n_roots, int32_t rollouts,
+                      uint64_t seed, uint64_t first_playout, int64_t totals_out[4],
+                      int32_t* root_ret_host, int32_t* root_steps_host) {
+  if (!e) return BSG_ERR_BAD_ARG;
+  if (!roots_host || n_roots < 1 || !totals_out) return fail(e, BSG_ERR_BAD_ARG, "bad host playout arguments");
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  size_t in_bytes = (size_t)n_roots * (size_t)bsg_state_bytes(e->game);
+  size_t out_elems = (root_ret_host ? n_roots : 0) + (root_steps_host ? n_roots : 0);
+  int rc;
+  if ((rc = ensure(e, &e->d_roots, &e->d_roots_bytes, in_bytes, false)) != BSG_OK) return rc;
+  if ((rc = ensure(e, &e->d_out, &e->d_out_bytes, out_elems * 4 + 16, false)) != BSG_OK) return rc;
+  if ((rc = ensure(e, &e->h_pinned, &e->h_pinned_bytes, in_bytes + out_elems * 4 + 64, true)) != BSG_OK) return rc;
+  cudaStream_t st = e->own_stream;
+  memcpy(e->h_pinned, roots_host, in_bytes);
+  BSG_CUDA(e, cudaMemcpyAsync(e->d_roots, e->h_pinned, in_bytes, cudaMemcpyHostToDevice, st));
+  BSG_CUDA(e, cudaMemsetAsync(e->d_totals, 0, 4 * sizeof(uint64_t), st));
+  if (out_elems) BSG_CUDA(e, cudaMemsetAsync(e->d_out, 0, out_elems * 4, st));
+  bsg_playout_io io;
+  memset(&io, 0, sizeof(io));
+  io.totals = e->d_totals;
+  int32_t* d_ret = root_ret_host ? (int32_t*)e->d_out : nullptr;
+  int32_t* d_steps = root_steps_host ? (int32_t*)e->d_out + (root_ret_host ? n_roots : 0) : nullptr;
+  io.root_sum_ret0 = d_ret;
+  io.root_sum_steps = d_steps;
+  if ((rc = bsg_playouts(e, e->d_roots, n_roots, rollouts, seed, first_playout, &io, st)) != BSG_OK) return rc;
+  char* hp = (char*)e->h_pinned + ((in_bytes + 15) & ~(size_t)15);
+  uint64_t* h_tot = (uint64_t*)hp;
+  BSG_CUDA(e, cudaMemcpyAsync(h_tot, e->d_totals, 32, cudaMemcpyDeviceToHost, st));
+  if (out_elems) BSG_CUDA(e, cudaMemcpyAsync(hp + 32, e->d_out, out_elems * 4, cudaMemcpyDeviceToHost, st));
+  BSG_CUDA(e, cudaStreamSynchronize(st));
+  for (int i = 0; i < 4; ++i) totals_out[i] = (int64_t)h_tot[i];
+  if (root_ret_host) memcpy(root_ret_host, hp + 32, (size_t)n_roots * 4);
+  if (root_steps_host) memcpy(root_steps_host, hp + 32 + (root_ret_host ? (size_t)n_roots * 4 : 0), (size_t)n_roots * 4);
+  if (totals_out[3] != 0) return fail(e, BSG_ERR_STUCK_LANE, "non-terminal state without legal actions");
+  return BSG_OK;
+}
+
+int bsg_observations_host(bsg_engine* e, const void* states_host, int64_t n, const uint8_t* players_host,
+                          float* obs_host, uint8_t* mask_host) {
+  if (!e) return BSG_ERR_BAD_ARG;
+  if (!states_host || n < 1 || (!obs_host && !mask_host)) return fail(e, BSG_ERR_BAD_ARG, "bad host observation arguments");
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  size_t sb = (size_t)n * (size_t)bsg_state_bytes(e->game);
+  size_t in_bytes = ((sb + 15) & ~(size_t)15) + (players_host ? (((size_t)n + 15) & ~(size_t)15) : 0);
+  size_t obs_bytes = obs_host ? (((size_t)n * bsg_observation_size(e->game) * 4 + 15) & ~(size_t)15) : 0;
+  size_t mask_bytes = mask_host ? (((size_t)n * bsg_num_distinct_actions(e->game) + 15) & ~(size_t)15) : 0;
+  int rc;
+  if ((rc = ensure(e, &e->d_roots, &e->d_roots_bytes, in_bytes, false)) != BSG_OK) return rc;
+  if ((rc = ensure(e, &e->d_out, &e->d_out_bytes, obs_bytes + mask_bytes, false)) != BSG_OK) return rc;
+  cudaStream_t st = e->own_stream;
+  BSG_CUDA(e, cudaMemcpyAsync(e->d_roots, states_host, sb, cudaMemcpyHostToDevice, st));
+  uint8_t* d_players = nullptr;
+  if (players_host) {
+    d_players = (uint8_t*)e->d_roots + ((sb + 15) & ~(size_t)15);
+    BSG_CUDA(e, cudaMemcpyAsync(d_players, players_host, (size_t)n, cudaMemcpyHostToDevice, st));
+  }
+  float* d_obs = obs_host ? (float*)e->d_out : nullptr;
+  uint8_t* d_mask = mask_host ? (uint8_t*)e->d_out + obs_bytes : nullptr;
+  if ((rc = bsg_observations(e, e->d_roots, n, d_players, d_obs, d_mask, st)) != BSG_OK) return rc;
+  if (obs_host) BSG_CUDA(e, cudaMemcpyAsync(obs_host, d_obs, (size_t)n * bsg_observation_size(e->game) * 4, cudaMemcpyDeviceToHost, st));
+  if (mask_host) BSG_CUDA(e, cudaMemcpyAsync(mask_host, d_mask, (size_t)n * bsg_num_distinct_actions(e->game), cudaMemcpyDeviceToHost, st));
+  BSG_CUDA(e, cudaStreamSynchronize(st));
+  return BSG_OK;
+}
+
+int bsg_int_peak(bsg_engine* e, int kind, int iters, double* out) {
+  if (!e || !out || iters < 1 || kind < 0 || kind > 2) return BSG_ERR_BAD_ARG;
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  int grid = e->sm_count * 8;
+  cudaEvent_t a, b;
+  BSG_CUDA(e, cudaEventCreate(&a));
+  BSG_CUDA(e, cudaEventCreate(&b));
+  u32* sink = (u32*)e->d_totals;
+  double best = 0;
+  for (int rep = 0; rep < 4; ++rep) {
+    cudaEventRecord(a, e->own_stream);
+    if (kind == 0) int_peak_kernel<0><<<grid, kThreads, 0, e->own_stream>>>(iters, sink);
+    else if (kind == 1) int_peak_kernel<1><<<grid, kThreads, 0, e->own_stream>>>(iters, sink);
+    else int_peak_kernel<2><<<grid, kThreads, 0, e->own_stream>>>(iters, sink);
+    cudaEventRecord(b, e->own_stream);
+    BSG_CUDA(e, cudaEventSynchronize(b));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, a, b);
+    double per_thread = (double)iters * 64.0 * (kind == 0 ? 2.0 : (kind == 1 ? 1.0 : 3.0));
+    double rate = per_thread * (double)grid * kThreads / (ms * 1e-3);
+    if (rep > 0 && rate > best) best = rate;
+  }
+  cudaEventDestroy(a);
+  cudaEventDestroy(b);
+  *out = best;
+  return BSG_OK;
+}
+
+}  // extern "C"

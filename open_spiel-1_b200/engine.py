@@ -1,0 +1,212 @@
+"""Engine: the device side of the C ABI, driven from Python.
+
+PyTorch is used only for device memory, streams and handing observation tensors to models;
+all game work happens in the CUDA kernels of libbsg.so.  Nothing here has a CPU fallback:
+constructing an Engine without a CUDA device raises RuntimeError.
+"""
+import ctypes
+
+import numpy as np
+
+from . import _cabi as C
+
+GAME_NAMES = ("tic_tac_toe", "connect_four", "breakthrough", "hex")
+
+
+def game_id(game):
+  """Accepts a game id, a reference game string ("hex(board_size=11)") or a Game-like object."""
+  if isinstance(game, int):
+    return game
+  if not isinstance(game, str):
+    game = str(game)
+  gid = C.lib.bsg_game_id(game.encode())
+  if gid < 0:
+    raise RuntimeError("bsg: unsupported game '%s' (supported: tic_tac_toe, connect_four, "
+                       "breakthrough 8x8, hex 11x11)" % game)
+  return gid
+
+
+def state_bytes(gid):
+  return C.check(C.lib.bsg_state_bytes(gid))
+
+
+def num_distinct_actions(gid):
+  return C.check(C.lib.bsg_num_distinct_actions(gid))
+
+
+def max_game_length(gid):
+  return C.check(C.lib.bsg_max_game_length(gid))
+
+
+def observation_shape(gid):
+  shape = (ctypes.c_int * 3)()
+  C.check(C.lib.bsg_observation_shape(gid, shape))
+  return [shape[0], shape[1], shape[2]]
+
+
+def observation_size(gid):
+  return C.check(C.lib.bsg_observation_size(gid))
+
+
+def pack_histories(game, histories):
+  """Action histories (State.history()) -> packed SoA states, a uint8 numpy buffer of
+  len(histories) * state_bytes.  Raises RuntimeError on an illegal action."""
+  gid = game_id(game)
+  n = len(histories)
+  off = np.zeros(n + 1, np.int64)
+  for i, h in enumerate(histories):
+    off[i + 1] = off[i] + len(h)
+  flat = np.zeros(max(int(off[-1]), 1), np.int64)
+  for i, h in enumerate(histories):
+    if len(h):
+      flat[off[i]:off[i + 1]] = h
+  out = np.zeros(max(n, 1) * state_bytes(gid), np.uint8)
+  C.check(C.lib.bsg_pack_histories(gid, flat.ctypes.data, off.ctypes.data, n, out.ctypes.data, n))
+  return out[:n * state_bytes(gid)]
+
+
+def draw(seed, playout, t):
+  """The t-th replay draw r(seed, playout, t) of the engine's Philox contract."""
+  return int(C.lib.bsg_draw(seed, playout, t))
+
+
+def _torch():
+  import torch  # local: only device paths need it
+  return torch
+
+
+class Engine:
+  """One engine per (thread, GPU) — the threading contract of the reference evaluators."""
+
+  def __init__(self, game, device=0):
+    self.gid = game_id(game)
+    if self.gid > C.HEX:
+      raise RuntimeError("bsg: game id %d has host helpers only" % self.gid)
+    torch = _torch()
+    if not torch.cuda.is_available():
+      raise RuntimeError("bsg: no CUDA device — the playout engine has no CPU fallback")
+    self.device = int(device)
+    self.torch_device = torch.device("cuda", self.device)
+    handle = C.vp()
+    rc = C.lib.bsg_create(self.gid, self.device, ctypes.byref(handle))
+    self._h = handle
+    if rc != C.OK:
+      try:
+        C.check(rc, handle if handle.value else None)
+      finally:
+        if handle.value:
+          C.lib.bsg_destroy(handle)
+        self._h = None
+    self.state_bytes = state_bytes(self.gid)
+    self.num_actions = num_distinct_actions(self.gid)
+    self.obs_shape = observation_shape(self.gid)
+    self.obs_size = observation_size(self.gid)
+    self.max_len = max_game_length(self.gid)
+    self.sm_count = C.lib.bsg_engine_sm_count(self._h)
+    self.launches = 0  # kernels launched through this engine (bench.py's gpu_launches)
+
+  def close(self):
+    if getattr(self, "_h", None):
+      C.lib.bsg_destroy(self._h)
+      self._h = None
+
+  def __del__(self):
+    try:
+      self.close()
+    except Exception:  # pragma: no cover
+      pass
+
+  # ---- helpers
+  def to_device(self, packed):
+    """Packed host buffer (numpy uint8) -> device tensor."""
+    torch = _torch()
+    t = torch.from_numpy(np.ascontiguousarray(packed))
+    return t.to(self.torch_device, non_blocking=False)
+
+  def _stream_ptr(self, stream):
+    torch = _torch()
+    if stream is None:
+      stream = torch.cuda.current_stream(self.torch_device)
+    return C.vp(stream.cuda_stream)
+
+  @staticmethod
+  def _p(t):
+    return None if t is None else C.vp(t.data_ptr())
+
+  # ---- the hot path
+  def playouts(self, roots, n_roots, rollouts=1, seed=0, first_playout=0, *, ret0=None,
+               length=None, terminal=None, actions=None, root_sum_ret0=None,
+               root_sum_steps=None, totals=None, max_steps=0, step_limit=None, r_table=None,
+               final_states=None, final_before_terminal=False, stream=None):
+    """Launches n_roots * rollouts random playouts (bsg_playouts).  All tensors are device
+    tensors owned by the caller; see include/bsg.h for their meaning.  Asynchronous."""
+    io = C.PlayoutIO()
+    io.max_steps = int(max_steps)
+    io.step_limit = self._p(step_limit)
+    io.r_table = self._p(r_table)
+    io.r_stride = int(r_table.shape[1]) if r_table is not None else 0
+    io.ret0 = self._p(ret0)
+    io.length = self._p(length)
+    io.terminal = self._p(terminal)
+    io.actions = self._p(actions)
+    io.actions_stride = int(actions.shape[1]) if actions is not None else 0
+    io.root_sum_ret0 = self._p(root_sum_ret0)
+    io.root_sum_steps = self._p(root_sum_steps)
+    io.final_states = self._p(final_states)
+    io.final_before_terminal = 1 if final_before_terminal else 0
+    io.totals = self._p(totals)
+    C.check(C.lib.bsg_playouts(self._h, self._p(roots), int(n_roots), int(rollouts),
+                               int(seed) & (2**64 - 1), int(first_playout), ctypes.byref(io),
+                               self._stream_ptr(stream)), self._h)
+    self.launches += 1
+
+  def observations(self, states, n, players=None, out=None, legal_mask=None, want_mask=False,
+                   stream=None):
+    """Batched ObservationTensor (+ LegalActionsMask) writer.  Returns (obs, mask) device
+    tensors of shape [n, C, H, W] float32 and [n, NumDistinctActions] uint8."""
+    torch = _torch()
+    if out is None:
+      out = torch.empty((n,) + tuple(self.obs_shape), dtype=torch.float32,
+                        device=self.torch_device)
+    if want_mask and legal_mask is None:
+      legal_mask = torch.empty((n, self.num_actions), dtype=torch.uint8,
+                               device=self.torch_device)
+    C.check(C.lib.bsg_observations(self._h, self._p(states), int(n), self._p(players),
+                                   self._p(out), self._p(legal_mask), self._stream_ptr(stream)),
+            self._h)
+    self.launches += 1 + (1 if legal_mask is not None else 0)
+    return out, legal_mask
+
+  # ---- host-buffer entry points (copies inside the call; synchronous)
+  def playouts_host(self, packed, n_roots, rollouts=1, seed=0, first_playout=0,
+                    want_root_sums=False):
+    """bsg_playouts_host: packed numpy roots in, totals {playouts, steps, sum_ret0, stuck} out."""
+    packed = np.ascontiguousarray(packed)
+    totals = np.zeros(4, np.int64)
+    rr = rs = None
+    if want_root_sums:
+      rr = np.zeros(n_roots, np.int32)
+      rs = np.zeros(n_roots, np.int32)
+    C.check(C.lib.bsg_playouts_host(self._h, packed.ctypes.data, int(n_roots), int(rollouts),
+                                    int(seed) & (2**64 - 1), int(first_playout),
+                                    totals.ctypes.data, None if rr is None else rr.ctypes.data,
+                                    None if rs is None else rs.ctypes.data), self._h)
+    self.launches += 1
+    return totals, rr, rs
+
+  def observations_host(self, packed, n, players=None, want_mask=False):
+    packed = np.ascontiguousarray(packed)
+    obs = np.empty((n,) + tuple(self.obs_shape), np.float32)
+    mask = np.empty((n, self.num_actions), np.uint8) if want_mask else None
+    pl = None if players is None else np.ascontiguousarray(players, np.uint8)
+    C.check(C.lib.bsg_observations_host(self._h, packed.ctypes.data, int(n),
+                                        None if pl is None else pl.ctypes.data, obs.ctypes.data,
+                                        None if mask is None else mask.ctypes.data), self._h)
+    self.launches += 1 + (1 if want_mask else 0)
+    return obs, mask
+
+  def int_peak(self, kind=2, iters=2000):
+    """Measured integer issue rate (thread-instructions/s) for the roofline denominator."""
+    out = ctypes.c_double()
+    C.check(C.lib.bsg_int_peak(self._h, kind, iters, ctypes.byref(out)), self._h)
+    return out.value

@@ -1,0 +1,123 @@
+"""GPU tests of the drop-in Evaluator behind MCTS (modelled on the reference's own tests:
+python/algorithms/mcts_test.py:70-153, alpha_zero/evaluator_test.py:35-104)."""
+import numpy as np
+import pytest
+
+from oracle_lib import Oracle
+
+pytestmark = pytest.mark.gpu
+UCT_C = 2.0
+
+
+@pytest.fixture(scope="module")
+def bsg():
+  import open_spiel_1_b200 as m
+  return m
+
+
+def test_evaluate_matches_oracle_rollouts(bsg):
+  """evaluate() = mean of the oracle's replays of the very playout ids it consumed."""
+  oracle = Oracle()
+  for game in ("tic_tac_toe", "connect_four", "breakthrough", "hex"):
+    ev = bsg.GpuRolloutEvaluator(game, n_rollouts=64, seed=123)
+    g = bsg.load_game(game)
+    state = g.new_initial_state()
+    rng = np.random.RandomState(1)
+    for _ in range(5):
+      la = state.legal_actions()
+      state.apply_action(la[rng.randint(len(la))])
+    before = state.history()
+    for call in range(3):
+      v = ev.evaluate(state)
+      assert state.history() == before               # evaluate must not mutate the state
+      assert len(v) == 2 and v[0] + v[1] == 0         # zero-sum (evaluator_test.py)
+      lo, hi = ev.last_playout_range
+      _, o_ret, _, _ = oracle.replay_batch(game, [before], rollouts=hi - lo, seed=123,
+                                           first_playout=lo)
+      assert v[0] == o_ret.astype(np.float64).mean()
+    pri = ev.prior(state)
+    assert isinstance(pri, list)
+    assert [a for a, _ in pri] == state.legal_actions()
+    assert abs(sum(p for _, p in pri) - 1.0) < 1e-12
+    ev.engine.close()
+
+
+def test_evaluate_batch_equals_single_calls(bsg):
+  g = bsg.load_game("connect_four")
+  states = []
+  rng = np.random.RandomState(3)
+  for i in range(17):
+    s = g.new_initial_state()
+    for _ in range(i % 9):
+      la = s.legal_actions()
+      s.apply_action(la[rng.randint(len(la))])
+    states.append(s)
+  ev_a = bsg.GpuRolloutEvaluator("connect_four", n_rollouts=32, seed=9)
+  ev_b = bsg.GpuRolloutEvaluator(ev_a.engine, n_rollouts=32, seed=9)
+  batch = ev_a.evaluate_batch(states)
+  single = np.stack([ev_b.evaluate(s) for s in states])
+  assert np.array_equal(batch, single)
+
+
+def test_mcts_plays_tic_tac_toe_games(bsg):
+  """mcts_test.py:70-81: two bots sharing one evaluator play a full game; returns sum to 0."""
+  game = bsg.load_game("tic_tac_toe")
+  rs = np.random.RandomState(42)
+  ev = bsg.GpuRolloutEvaluator("tic_tac_toe", n_rollouts=20, seed=42)
+  bots = [bsg.MCTSBot(game, UCT_C, 100, ev, random_state=rs),
+          bsg.MCTSBot(game, UCT_C, 100, ev, random_state=rs)]
+  state = game.new_initial_state()
+  while not state.is_terminal():
+    state.apply_action(bots[state.current_player()].step(state))
+  assert sum(state.returns()) == 0
+
+
+def _search(bsg, history, leaf_batch=1):
+  game = bsg.load_game("tic_tac_toe")
+  state = game.new_initial_state()
+  for a in history:
+    state.apply_action(a)
+  rs = np.random.RandomState(42)
+  ev = bsg.GpuRolloutEvaluator("tic_tac_toe", n_rollouts=20, seed=42)
+  bot = bsg.MCTSBot(game, UCT_C, 10000, ev, random_state=rs, leaf_batch=leaf_batch)
+  return bot.mcts_search(state), state
+
+
+@pytest.mark.parametrize("leaf_batch", [1, 8])
+def test_solver_known_answers(bsg, leaf_batch):
+  """mcts_test.py:115-153: draw / loss / win positions are proven by the solver."""
+  root, state = _search(bsg, [4, 0, 8], leaf_batch)          # x(1,1) o(0,0) x(2,2)
+  assert root.outcome[root.player] == 0
+  assert all(c.outcome[c.player] <= 0 for c in root.children)
+  best = root.best_child()
+  assert best.outcome[best.player] == 0 and best.action in (2, 6)
+  root, state = _search(bsg, [4, 0, 8, 1, 2], leaf_batch)    # all moves lose
+  assert root.outcome[root.player] == -1
+  assert all(c.outcome[c.player] == -1 for c in root.children)
+  root, state = _search(bsg, [1, 8], leaf_batch)             # x(0,1) o(2,2): x(0,2) wins
+  assert root.outcome[root.player] == 1
+  best = root.best_child()
+  assert best.outcome[best.player] == 1 and best.action == 2
+
+
+def test_best_child_ordering(bsg):
+  """mcts_test.py:155-216: proven win > unproven visits > proven loss; ties by count/reward."""
+  def node(count, reward, outcome):
+    n = bsg.SearchNode(0, 0, 1)
+    n.explore_count, n.total_reward = count, reward
+    n.outcome = None if outcome is None else [outcome, -outcome]
+    return n
+  def best(children):
+    root = bsg.SearchNode(None, 0, 1)
+    root.children = children
+    return root.best_child()
+  a, b = node(10, 5, 1), node(100, 90, None)
+  assert best([a, b]) is a                  # proven win beats a promising unproven move
+  a, b = node(10, 1, 0), node(20, 5, None)
+  assert best([a, b]) is b                  # more visits beat a proven draw with fewer
+  a, b = node(30, 1, 0), node(20, 5, None)
+  assert best([a, b]) is a
+  a, b = node(50, -40, -1), node(3, 0, None)
+  assert best([a, b]) is b                  # anything unproven beats a proven loss
+  a, b = node(10, 4, None), node(10, 5, None)
+  assert best([a, b]) is b                  # equal visits: higher reward

@@ -1,0 +1,243 @@
+"""GPU parity tests (run with -m gpu on the B200 box).  Everything goes through the C ABI.
+
+Checker: the unmodified reference (oracle/_ref/libspiel_ref.so) when it travelled with the
+repo, otherwise the C oracle.  Bar: bit-exact — action sequences, lengths, terminal flags,
+integer returns, observation planes, legal masks.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from oracle_lib import Oracle, Reference, reference_path
+
+pytestmark = pytest.mark.gpu
+
+GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex"]
+# replay-parity sizes: >= 1e5 playouts per game
+N_ROOTS = {"tic_tac_toe": 50000, "connect_four": 50000, "breakthrough": 25000, "hex": 12500}
+ROLLOUTS = {"tic_tac_toe": 2, "connect_four": 2, "breakthrough": 4, "hex": 8}
+
+
+@pytest.fixture(scope="module")
+def checker():
+  if os.path.exists(reference_path()):
+    return Reference()
+  return Oracle()
+
+
+@pytest.fixture(scope="module")
+def torch():
+  import torch as t
+  assert t.cuda.is_available()
+  return t
+
+
+def _engine(game):
+  import open_spiel_1_b200 as bsg
+  return bsg.Engine(game, 0)
+
+
+def _roots(eng, game, n, seed):
+  from open_spiel_1_b200.roots import make_roots, ROOT_DEPTHS
+  dmin, dmax = ROOT_DEPTHS[game]
+  return make_roots(eng, n, dmin, dmax, seed, want_histories=True)
+
+
+@pytest.mark.parametrize("game", GAMES)
+def test_replay_bit_exact(game, checker, torch):
+  """>= 1e5 playouts per game from synthetic mid-game roots: every action, length, terminal
+  flag and integer return equals the checker's under the same Philox draws."""
+  import open_spiel_1_b200 as bsg
+  eng = _engine(game)
+  n, R = N_ROOTS[game], ROLLOUTS[game]
+  states, hist = _roots(eng, game, n, seed=20240611)
+  # the device-made roots equal the host-packed roots of the same histories, byte for byte
+  assert np.array_equal(states.cpu().numpy(), bsg.pack_histories(game, hist))
+  dev = eng.torch_device
+  stride = eng.max_len if game != "breakthrough" else 209
+  ret0 = torch.zeros(n * R, dtype=torch.int8, device=dev)
+  length = torch.zeros(n * R, dtype=torch.uint8, device=dev)
+  term = torch.zeros(n * R, dtype=torch.uint8, device=dev)
+  acts = torch.full((n * R, stride), -1, dtype=torch.int16, device=dev)
+  totals = torch.zeros(4, dtype=torch.int64, device=dev)
+  rs = torch.zeros(n, dtype=torch.int32, device=dev)
+  rl = torch.zeros(n, dtype=torch.int32, device=dev)
+  eng.playouts(states, n, R, seed=77, first_playout=5, ret0=ret0, length=length, terminal=term,
+               actions=acts, totals=totals, root_sum_ret0=rs, root_sum_steps=rl)
+  torch.cuda.synchronize()
+  o_len, o_ret, o_term, o_acts = checker.replay_batch(game, hist, rollouts=R, seed=77,
+                                                      first_playout=5, actions_stride=stride)
+  assert np.array_equal(length.cpu().numpy().astype(np.int32), o_len)
+  assert np.array_equal(ret0.cpu().numpy(), o_ret)
+  assert np.array_equal(term.cpu().numpy(), o_term)
+  assert np.array_equal(acts.cpu().numpy(), o_acts)
+  t = totals.cpu().numpy()
+  assert t.tolist() == [n * R, int(o_len.sum()), int(o_ret.astype(np.int64).sum()), 0]
+  assert np.array_equal(rs.cpu().numpy(), o_ret.reshape(n, R).astype(np.int32).sum(1))
+  assert np.array_equal(rl.cpu().numpy(), o_len.reshape(n, R).sum(1))
+  # the fast kernel variant (no action log) gives the same per-playout results
+  ret0b = torch.zeros_like(ret0)
+  lengthb = torch.zeros_like(length)
+  eng.playouts(states, n, R, seed=77, first_playout=5, ret0=ret0b, length=lengthb)
+  torch.cuda.synchronize()
+  assert torch.equal(ret0, ret0b) and torch.equal(length, lengthb)
+  eng.close()
+
+
+@pytest.mark.parametrize("game", GAMES)
+def test_replay_with_explicit_r_table(game, checker, torch):
+  """Replay mode driven by pre-generated per-step integers (action = legal[r mod n])."""
+  eng = _engine(game)
+  n = 2000
+  states, hist = _roots(eng, game, n, seed=5)
+  dev = eng.torch_device
+  stride = 209 if game == "breakthrough" else eng.max_len
+  rng = np.random.RandomState(99)
+  table = rng.randint(0, 2**32, size=(n, stride), dtype=np.uint64).astype(np.uint32)
+  d_table = torch.from_numpy(table.view(np.int32)).to(dev)
+  ret0 = torch.zeros(n, dtype=torch.int8, device=dev)
+  length = torch.zeros(n, dtype=torch.uint8, device=dev)
+  acts = torch.full((n, stride), -1, dtype=torch.int16, device=dev)
+  eng.playouts(states, n, 1, seed=1, ret0=ret0, length=length, actions=acts, r_table=d_table)
+  torch.cuda.synchronize()
+  g_acts, g_len, g_ret = acts.cpu().numpy(), length.cpu().numpy(), ret0.cpu().numpy()
+  for i in range(0, n, 7):
+    a, term, r = checker.replay(game, hist[i], r_table=table[i])
+    assert g_len[i] == len(a) and g_ret[i] == r and term == 1
+    assert g_acts[i, :len(a)].tolist() == a
+  eng.close()
+
+
+@pytest.mark.parametrize("game", GAMES)
+def test_observations_and_masks_bit_exact(game, torch):
+  """ObservationTensor planes and LegalActionsMask of 1e5 states vs the oracle."""
+  oracle = Oracle()
+  eng = _engine(game)
+  n = 100000 if game != "hex" else 30000
+  states, hist = _roots(eng, game, n, seed=42)
+  dev = eng.torch_device
+  players = torch.from_numpy((np.arange(n) % 2).astype(np.uint8)).to(dev)
+  obs, mask = eng.observations(states, n, players, want_mask=True)
+  torch.cuda.synchronize()
+  obs = obs.cpu().numpy().reshape(n, -1)
+  mask = mask.cpu().numpy()
+  assert set(np.unique(obs).tolist()) <= {0.0, 1.0}
+  assert np.all(obs.sum(1) == eng.obs_size // eng.obs_shape[0])  # exactly one plane per cell
+  step = 1 if game in ("tic_tac_toe", "connect_four") else 3
+  for i in range(0, n, step * 10):
+    d = oracle.state_dump(game, hist[i], i % 2)
+    assert np.array_equal(obs[i].astype(np.uint8), d["obs"]), i
+    assert np.nonzero(mask[i])[0].tolist() == d["legal"], i
+  # host-buffer entry point gives the same bytes
+  k = 1000
+  import open_spiel_1_b200 as bsg
+  packed = bsg.pack_histories(game, hist[:k])
+  obs_h, mask_h = eng.observations_host(packed, k, (np.arange(k) % 2).astype(np.uint8), True)
+  assert np.array_equal(obs_h.reshape(k, -1), obs[:k]) and np.array_equal(mask_h, mask[:k])
+  # terminal states (the reference keeps *Win marks at terminal hex states)
+  term_hist = []
+  for p in range(300):
+    a, _, _ = oracle.replay(game, [], seed=9, playout=p)
+    term_hist.append(a)
+  packed = bsg.pack_histories(game, term_hist)
+  obs_t, mask_t = eng.observations_host(packed, len(term_hist), np.zeros(len(term_hist), np.uint8), True)
+  for i, h in enumerate(term_hist):
+    d = oracle.state_dump(game, h, 0)
+    assert np.array_equal(obs_t[i].ravel().astype(np.uint8), d["obs"])
+    assert mask_t[i].sum() == 0
+  eng.close()
+
+
+@pytest.mark.parametrize("game", GAMES)
+def test_native_rng_win_rates_within_binomial_ci(game, checker, torch):
+  """>= 1e6 playouts from the initial state: player-0 win / draw / loss rates within a
+  99.9 % binomial interval (z = 3.29) of the checker's rates under ITS OWN RNG stream
+  (std::mt19937 for the reference; distinct Philox seed for the oracle)."""
+  import open_spiel_1_b200 as bsg
+  eng = _engine(game)
+  dev = eng.torch_device
+  n_gpu = 1 << 20
+  root = eng.to_device(bsg.pack_histories(game, [[]]))
+  ret0 = torch.zeros(n_gpu, dtype=torch.int8, device=dev)
+  length = torch.zeros(n_gpu, dtype=torch.uint8, device=dev)
+  eng.playouts(root, 1, n_gpu, seed=20240611, ret0=ret0, length=length)
+  torch.cuda.synchronize()
+  r = ret0.cpu().numpy()
+  n_ref = {"tic_tac_toe": 400000, "connect_four": 200000, "breakthrough": 40000, "hex": 30000}[game]
+  if isinstance(checker, Reference):
+    # reference's own mt19937 stream; per-outcome counts via replay batch are Philox-tied, so
+    # use random_playouts for the mean and replay_batch (different seed) for the outcome split
+    _, _, sum_ret = checker.random_playouts(game, [[]], n_ref, seed=4242, threads=os.cpu_count() or 1)
+    mean_ref = sum_ret / n_ref
+  else:
+    _, sum_ret = checker.random_playouts(game, [[]], n_ref, seed=4242)
+    mean_ref = sum_ret / n_ref
+  mean_gpu = float(r.astype(np.float64).mean())
+  var = float(r.astype(np.float64).var()) + 1e-9
+  half = 3.29 * np.sqrt(var / n_gpu + var / n_ref)
+  assert abs(mean_gpu - mean_ref) <= half, (mean_gpu, mean_ref, half)
+  # outcome split against an independently seeded checker replay
+  o_len, o_ret, _, _ = checker.replay_batch(game, [[]], rollouts=n_ref, seed=987654321)
+  for outcome in (1, 0, -1):
+    p_gpu = float((r == outcome).mean())
+    p_ref = float((o_ret == outcome).mean())
+    p = (p_gpu * n_gpu + p_ref * n_ref) / (n_gpu + n_ref)
+    half = 3.29 * np.sqrt(p * (1 - p) * (1.0 / n_gpu + 1.0 / n_ref)) + 1e-12
+    assert abs(p_gpu - p_ref) <= half, (outcome, p_gpu, p_ref, half)
+  mean_len_gpu = float(length.cpu().numpy().astype(np.float64).mean())
+  assert abs(mean_len_gpu - float(o_len.mean())) < 0.05 * float(o_len.mean())
+  eng.close()
+
+
+def test_connect_four_full_size_properties(torch):
+  """BASELINE cfg2 size (16 Mi playouts): size-independent properties instead of an oracle run."""
+  from open_spiel_1_b200.roots import make_roots
+  eng = _engine("connect_four")
+  dev = eng.torch_device
+  n = 1 << 24
+  states, _ = make_roots(eng, n, 8, 20, seed=20240611 + 2)
+  ret0 = torch.zeros(n, dtype=torch.int8, device=dev)
+  length = torch.zeros(n, dtype=torch.uint8, device=dev)
+  term = torch.zeros(n, dtype=torch.uint8, device=dev)
+  totals = torch.zeros(4, dtype=torch.int64, device=dev)
+  eng.playouts(states, n, 1, seed=1, ret0=ret0, length=length, terminal=term, totals=totals)
+  torch.cuda.synchronize()
+  t = totals.cpu().numpy()
+  assert t[0] == n and t[3] == 0
+  assert int(length.to(torch.int64).sum()) == t[1]          # checksum of per-playout lengths
+  assert int(ret0.to(torch.int64).sum()) == t[2]
+  assert bool(term.all())                                    # every playout reached a terminal
+  assert int(length.max()) <= 42 - 8 and int(length.min()) >= 1
+  # idempotence / schedule independence: the same launch again, and a split launch with
+  # first_playout offsets, reproduce the same per-playout results
+  ret0b = torch.zeros_like(ret0)
+  lengthb = torch.zeros_like(length)
+  half = n // 2
+  sb = eng.state_bytes
+  eng.playouts(states[:half * sb], half, 1, seed=1, first_playout=0, ret0=ret0b[:half], length=lengthb[:half])
+  eng.playouts(states[half * sb:], half, 1, seed=1, first_playout=half, ret0=ret0b[half:], length=lengthb[half:])
+  torch.cuda.synchronize()
+  assert torch.equal(ret0, ret0b) and torch.equal(length, lengthb)
+  # sample of the full-size run against the oracle
+  oracle = Oracle()
+  import open_spiel_1_b200 as bsg
+  from open_spiel_1_b200 import _cabi as C
+  host = states.cpu().numpy()
+  idx = np.random.RandomState(0).randint(0, n, size=2000)
+  g_len, g_ret = length.cpu().numpy(), ret0.cpu().numpy()
+  for i in idx:
+    one = host[i * sb:(i + 1) * sb].copy()
+    # rebuild a history for the oracle is impossible from a board alone; replay the board through
+    # the host step hook instead and compare only lengths/returns with the kernel
+    acts = 0
+    import ctypes
+    while True:
+      cur, tm, r0 = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+      C.check(C.lib.bsg_host_state_info(1, one.ctypes.data, 1, 0, ctypes.byref(cur), ctypes.byref(tm), ctypes.byref(r0)))
+      if tm.value:
+        break
+      C.check(C.lib.bsg_host_replay_step(1, one.ctypes.data, 1, 0, bsg.draw(1, int(i), acts), None))
+      acts += 1
+    assert acts == g_len[i] and r0.value == g_ret[i]
+  eng.close()
