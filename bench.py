@@ -1,0 +1,423 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the rollout hot path (BASELINE.json configs[1]).
+
+Workload at every N: per GPU, 16 Mi independent uniform-random connect_four playouts, one per
+synthetic mid-game root (d ~ U{8..20} random moves from the empty board), i.e. weak scaling.
+A "step" is one pass of the playout kernel over that batch.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--game G] [--playouts P]
+
+For N > 1 launch under torchrun (one rank per GPU); rank 0 prints ONE JSON line.
+  value      game-steps/s, whole job, roots already resident in HBM (CUDA events, max over ranks)
+  e2e        same metric through the C-ABI host-buffer call bsg_playouts_host: pinned host
+             roots -> H2D -> kernel -> D2H totals, all inside the timed region
+  roofline   integer-issue roofline of the playout kernel (SURVEY.md §8d budget of 96
+             thread-instructions per connect_four step over the integer issue rate measured
+             live by bsg_int_peak), plus the HBM roofline of the observation writer
+  cpu_baseline  the unmodified reference C++ (oracle/_ref/libspiel_ref.so) on the box's cores,
+             on a bounded sample of the same kind of roots
+`--impl reference` times only that CPU reference arm (rank 0) and prints its own line.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REPO)
+sys.path.insert(0, os.path.join(REPO, "tests"))
+
+import numpy as np  # noqa: E402
+
+OPS_PER_STEP = {"tic_tac_toe": 48, "connect_four": 96, "breakthrough": 140, "hex": 200}
+ROOT_SEED = 20240611
+METRIC = "connect_four game-steps/s (uniform-random playouts from mid-game roots)"
+
+
+def parse_args():
+  ap = argparse.ArgumentParser()
+  ap.add_argument("--gpus", type=int, default=1)
+  ap.add_argument("--steps", type=int, default=10)
+  ap.add_argument("--warmup", type=int, default=3)
+  ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+  ap.add_argument("--game", default="connect_four")
+  ap.add_argument("--playouts", type=int, default=1 << 24, help="playouts per GPU per step")
+  ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline sample budget")
+  ap.add_argument("--no-cpu-baseline", action="store_true")
+  ap.add_argument("--no-extras", action="store_true", help="skip obs / other-game side numbers")
+  return ap.parse_args()
+
+
+class ClockSampler:
+  """Samples nvidia-smi clocks and throttle reasons during the timed region."""
+  QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+           "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+           "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+  def __init__(self, gpu_index):
+    self.gpu = gpu_index
+    self.proc = None
+    self.lines = []
+
+  def start(self):
+    try:
+      self.proc = subprocess.Popen(
+          ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.QUERY,
+           "--format=csv,noheader,nounits", "-lms", "100"],
+          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+      self.thread = threading.Thread(target=self._pump, daemon=True)
+      self.thread.start()
+    except Exception:
+      self.proc = None
+
+  def _pump(self):
+    for line in self.proc.stdout:
+      self.lines.append(line.strip())
+
+  def stop(self):
+    if not self.proc:
+      return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+    time.sleep(0.15)
+    self.proc.terminate()
+    try:
+      self.proc.wait(timeout=2)
+    except Exception:
+      self.proc.kill()
+    sm, mx, reasons = [], [], set()
+    names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    for line in self.lines:
+      f = [x.strip() for x in line.split(",")]
+      if len(f) < 9:
+        continue
+      try:
+        sm.append(float(f[1])); mx.append(float(f[2]))
+      except ValueError:
+        continue
+      for name, val in zip(names, f[5:9]):
+        if val.lower().startswith("active"):
+          reasons.add(name)
+    if not sm:
+      return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+    return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)),
+            "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_env():
+  rank = int(os.environ.get("RANK", "0"))
+  world = int(os.environ.get("WORLD_SIZE", "1"))
+  local = int(os.environ.get("LOCAL_RANK", "0"))
+  return rank, world, local
+
+
+def load_reference():
+  from oracle_lib import Oracle, Reference, reference_path
+  if os.path.exists(reference_path()):
+    return Reference(), "reference"
+  return Oracle(), "port"
+
+
+def sample_histories(game, n, seed):
+  """Bounded sample of synthetic roots WITH histories for the CPU arm, built by the oracle
+  under the same recipe as the GPU roots (d ~ U{dmin..dmax}; stop before a terminal move)."""
+  from oracle_lib import Oracle
+  from importlib import import_module
+  depths = {"tic_tac_toe": (0, 4), "connect_four": (8, 20), "breakthrough": (0, 40), "hex": (0, 60)}
+  dmin, dmax = depths[game]
+  orc = Oracle()
+  rng = np.random.RandomState(seed & 0x7FFFFFFF)
+  depth = rng.randint(dmin, dmax + 1, size=n)
+  hist = []
+  for i in range(n):
+    acts, term, _ = orc.replay(game, [], seed=seed, playout=i, max_steps=int(depth[i]))
+    hist.append(acts[:-1] if term else acts)
+  return hist
+
+
+def cpu_reference_run(game, hist, seconds, threads):
+  """Times the reference's own C++ playout loop (benchmark_game.cc shape) on `threads` cores
+  for about `seconds`; returns (steps/s, playouts/s, playouts run)."""
+  ref, kind = load_reference()
+  # calibrate on a small batch, then size the sample to the time budget
+  n0 = 2000 * max(threads, 1)
+  if kind == "reference":
+    secs, steps, _ = ref.random_playouts(game, hist, n0, seed=1, threads=threads)
+  else:
+    t0 = time.time(); steps, _ = ref.random_playouts(game, hist, n0, seed=1); secs = time.time() - t0
+    threads = 1
+  rate = n0 / max(secs, 1e-6)
+  n = int(max(n0, min(rate * seconds, 5e8)))
+  if kind == "reference":
+    secs, steps, _ = ref.random_playouts(game, hist, n, seed=2, threads=threads)
+  else:
+    t0 = time.time(); steps, _ = ref.random_playouts(game, hist, n, seed=2); secs = time.time() - t0
+  return steps / secs, n / secs, n, kind, threads, secs
+
+
+def run_reference_arm(args):
+  """--impl reference: the reference's own CPU implementation of the path, all host threads."""
+  rank, world, _ = dist_env()
+  if rank != 0:
+    return 0
+  threads = os.cpu_count() or 1
+  hist = sample_histories(args.game, 4096, ROOT_SEED + 2)
+  per_step_seconds = max(1.0, min(10.0, 60.0 / max(args.steps + args.warmup, 1)))
+  vals, last = [], None
+  for i in range(args.warmup + args.steps):
+    last = cpu_reference_run(args.game, hist, per_step_seconds, threads)
+    if i >= args.warmup:
+      vals.append(last)
+  steps_s = float(np.mean([v[0] for v in vals]))
+  playouts_s = float(np.mean([v[1] for v in vals]))
+  kind, used = last[3], last[4]
+  sample = "%d playouts/step from 4096 mid-game %s roots (d~U{8..20}), ~%.1f s/step" % (
+      last[2], args.game, per_step_seconds)
+  line = {
+      "impl": "reference", "metric": METRIC, "value": steps_s, "unit": "game-steps/s",
+      "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+      "ms_per_step": 1e3 * float(np.mean([v[5] for v in vals])), "higher_is_better": True,
+      "scaling": "weak", "vs_baseline": None, "dtype": "int64 actions / u8 cells (CPU)",
+      "data": "synthetic", "playouts_per_s": playouts_s,
+      "config": {"workload": "connect_four: 16Mi playouts from synthetic mid-game roots "
+                             "(bounded CPU sample)", "game": args.game,
+                 "root_depth": "U{8..20}", "rollouts_per_root": 1},
+      "cpu_baseline": {"value": steps_s, "unit": "game-steps/s", "cores": used, "kind": kind,
+                       "sample": sample},
+      "e2e": {"value": steps_s, "unit": "game-steps/s", "h2d_bytes_per_step": 0,
+              "d2h_bytes_per_step": 0},
+      "gpu_launches": 0,
+  }
+  print(json.dumps(line))
+  return 0
+
+
+def run_ours(args):
+  import torch
+  import open_spiel_1_b200 as bsg
+  from open_spiel_1_b200.roots import make_roots, ROOT_DEPTHS
+
+  rank, world, local = dist_env()
+  if world > 1:
+    import torch.distributed as dist
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+  else:
+    dist = None
+  torch.cuda.set_device(local)
+  dev = torch.device("cuda", local)
+  game = args.game
+  eng = bsg.Engine(game, local)
+  n = int(args.playouts)
+  dmin, dmax = ROOT_DEPTHS[game]
+  # distinct roots per rank (weak scaling): root seed offset by rank
+  states, _ = make_roots(eng, n, dmin, dmax, seed=ROOT_SEED + 2 + 1000 * rank)
+  ret0 = torch.zeros(n, dtype=torch.int8, device=dev)
+  length = torch.zeros(n, dtype=torch.uint8, device=dev)
+  totals = torch.zeros(4, dtype=torch.int64, device=dev)
+  first = rank * (1 << 40)  # disjoint Philox playout ids per rank
+
+  def barrier():
+    torch.cuda.synchronize(dev)
+    if dist is not None:
+      dist.barrier()
+    torch.cuda.synchronize(dev)
+
+  def one_step(i):
+    eng.playouts(states, n, 1, seed=ROOT_SEED, first_playout=first + i * n, ret0=ret0,
+                 length=length, totals=totals)
+
+  for i in range(args.warmup):
+    one_step(i)
+  barrier()
+  totals.zero_()
+  launches0 = eng.launches
+  sampler = ClockSampler(local)
+  if rank == 0:
+    sampler.start()
+  barrier()
+  ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+  ev0.record()
+  for i in range(args.steps):
+    one_step(args.warmup + i)
+  ev1.record()
+  barrier()
+  ms = ev0.elapsed_time(ev1)
+  clocks = sampler.stop() if rank == 0 else None
+  gpu_launches = eng.launches - launches0
+  tot = totals.cpu().numpy().astype(np.int64)
+  stats = torch.tensor([ms, float(tot[0]), float(tot[1])], dtype=torch.float64, device=dev)
+  if dist is not None:
+    mx = stats.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    sm = stats.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+    ms_max, playouts, steps = float(mx[0]), float(sm[1]), float(sm[2])
+  else:
+    ms_max, playouts, steps = ms, float(tot[0]), float(tot[1])
+  value = steps / (ms_max * 1e-3)
+
+  # ---- e2e through the host-buffer C-ABI call (pinned host roots, copies in the timed region)
+  host_roots = torch.empty(states.numel(), dtype=torch.uint8, pin_memory=True)
+  host_roots.copy_(states)
+  torch.cuda.synchronize(dev)
+  host_np = host_roots.numpy()
+  e2e_steps_n = max(2, min(args.steps, 5))
+  for i in range(2):
+    eng.playouts_host(host_np, n, 1, seed=ROOT_SEED, first_playout=first + i * n)
+  barrier()
+  t0 = time.perf_counter()
+  e2e_game_steps = 0
+  for i in range(e2e_steps_n):
+    t, _, _ = eng.playouts_host(host_np, n, 1, seed=ROOT_SEED, first_playout=first + (args.warmup + i) * n)
+    e2e_game_steps += int(t[1])
+  torch.cuda.synchronize(dev)
+  e2e_s = time.perf_counter() - t0
+  e2e_stats = torch.tensor([e2e_s, float(e2e_game_steps)], dtype=torch.float64, device=dev)
+  if dist is not None:
+    mx = e2e_stats.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    sm = e2e_stats.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+    e2e_value = float(sm[1]) / float(mx[0])
+  else:
+    e2e_value = e2e_game_steps / e2e_s
+
+  extras = {}
+  if rank == 0:
+    extras = rank0_extras(args, eng, torch, dev, value / world, ms_max / args.steps, n)
+  if dist is not None:
+    dist.barrier()
+    dist.destroy_process_group()
+  if rank != 0:
+    return 0
+  line = {
+      "metric": METRIC, "value": value, "unit": "game-steps/s", "n_gpus": world,
+      "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
+      "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+      "dtype": "u64 bitboards / u32 (integer)", "data": "synthetic",
+      "playouts_per_s": playouts / (ms_max * 1e-3),
+      "mean_steps_per_playout": steps / max(playouts, 1.0),
+      "config": {"workload": "connect_four: %d independent random playouts per GPU per step from "
+                             "synthetic mid-game roots, 1 playout/root" % n,
+                 "game": game, "playouts_per_gpu": n, "rollouts_per_root": 1,
+                 "root_depth": "U{%d..%d} random moves from the initial state" % (dmin, dmax),
+                 "root_seed": ROOT_SEED + 2, "playout_seed": ROOT_SEED,
+                 "rng": "philox4x32-10, counter=(playout id, step>>2), action=legal[r mod n]",
+                 "l2_policy": "inputs larger than L2 (%d MB of roots per step)" % (states.numel() >> 20),
+                 "parallelism": "playouts sharded by root across %d GPU(s), no data-path collective" % world},
+      "clocks": clocks,
+      "e2e": {"value": e2e_value, "unit": "game-steps/s",
+              "h2d_bytes_per_step": int(states.numel()), "d2h_bytes_per_step": 32,
+              "api": "bsg_playouts_host (C ABI, pinned host roots in, totals out)"},
+      "gpu_launches": gpu_launches,
+  }
+  line.update(extras)
+  print(json.dumps(line))
+  return 0
+
+
+def time_kernel(torch, dev, fn, reps=5, warm=2):
+  for _ in range(warm):
+    fn()
+  torch.cuda.synchronize(dev)
+  e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+  e0.record()
+  for _ in range(reps):
+    fn()
+  e1.record()
+  torch.cuda.synchronize(dev)
+  return e0.elapsed_time(e1) / reps
+
+
+def rank0_extras(args, eng, torch, dev, steps_per_s_per_gpu, kernel_ms, n):
+  """roofline, cpu_baseline and side numbers; rank 0 only, outside the headline timed region."""
+  import open_spiel_1_b200 as bsg
+  from open_spiel_1_b200.roots import make_roots, ROOT_DEPTHS
+  out = {}
+  peaks_path = os.path.join(REPO, "MEASURED_PEAKS.json")
+  hbm_peak, hbm_src = 6650.0, "fallback (B200_PROFILING.md)"
+  if os.path.exists(peaks_path):
+    with open(peaks_path) as f:
+      hbm_peak, hbm_src = float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+  # integer-issue peak measured live on this GPU: best of ALU-only, IMAD-only and mixed chains
+  kinds = {0: "LOP3+IADD3 (ALU pipe)", 1: "IMAD (FMA pipe)", 2: "SHF/LOP3 + IMAD mix"}
+  peaks = {k: eng.int_peak(k, 4000) for k in kinds}
+  peak_int = max(peaks.values())
+  ops = OPS_PER_STEP[args.game]
+  achieved = steps_per_s_per_gpu * ops
+  out["roofline"] = {
+      "bound": "int_issue", "kernel": "playout_kernel<ConnectFour,false>",
+      "achieved": achieved / 1e12, "peak": peak_int / 1e12, "unit": "T thread-instr/s",
+      "frac": achieved / peak_int, "traffic": None,
+      "algorithmic_ops_per_step": ops,
+      "peak_source": "bsg_int_peak microbenchmark, live: " + ", ".join(
+          "%s=%.2fT" % (kinds[k], peaks[k] / 1e12) for k in kinds),
+      "kernel_ms": kernel_ms,
+      "note": "the path is integer/branchy by design (north_star): the bound is the integer "
+              "issue rate, not HBM or tensor; HBM bytes are ~18 B/playout (<2 B/step)",
+      "hbm_achieved_gbs": n * 18 / (kernel_ms * 1e-3) / 1e9,
+  }
+  if not args.no_extras:
+    # observation writer: HBM-write bound (breakthrough, 784 algorithmic B/state)
+    side = {}
+    try:
+      e_bt = bsg.Engine("breakthrough", eng.device)
+      n_obs = 1 << 22
+      st, _ = make_roots(e_bt, n_obs, 0, 40, seed=ROOT_SEED + 3)
+      obs = torch.empty((n_obs, 3, 8, 8), dtype=torch.float32, device=dev)
+      ms = time_kernel(torch, dev, lambda: e_bt.observations(st, n_obs, None, out=obs))
+      gbs = n_obs * 784 / (ms * 1e-3) / 1e9
+      out["obs_roofline"] = {"bound": "hbm", "kernel": "obs_kernel<Breakthrough>",
+                             "achieved": gbs, "peak": hbm_peak, "unit": "GB/s",
+                             "frac": gbs / hbm_peak, "traffic": None, "peak_source": hbm_src,
+                             "states": n_obs, "obs_per_s": n_obs / (ms * 1e-3),
+                             "algorithmic_bytes_per_state": 784}
+      del obs, st
+      e_bt.close()
+      for g, npl in (("tic_tac_toe", 1 << 24), ("breakthrough", 1 << 22), ("hex", 1 << 20)):
+        e_g = bsg.Engine(g, eng.device)
+        dmin, dmax = ROOT_DEPTHS[g]
+        st, _ = make_roots(e_g, npl, dmin, dmax, seed=ROOT_SEED + 4)
+        tot = torch.zeros(4, dtype=torch.int64, device=dev)
+        ms = time_kernel(torch, dev, lambda: e_g.playouts(st, npl, 1, seed=7, totals=tot), reps=3, warm=1)
+        t = tot.cpu().numpy()
+        steps_per_launch = float(t[1]) / 4.0
+        side[g] = {"playouts": npl, "ms": ms, "game_steps_per_s": steps_per_launch / (ms * 1e-3),
+                   "playouts_per_s": npl / (ms * 1e-3),
+                   "int_roofline_frac": steps_per_launch / (ms * 1e-3) * OPS_PER_STEP[g] / peak_int}
+        e_g.close()
+    except Exception as ex:  # side numbers must never kill the headline line
+      side["error"] = repr(ex)
+    out["other_games"] = side
+  if not args.no_cpu_baseline:
+    threads = os.cpu_count() or 1
+    hist = sample_histories(args.game, 4096, ROOT_SEED + 2)
+    v_all = cpu_reference_run(args.game, hist, args.cpu_seconds, threads)
+    v_one = cpu_reference_run(args.game, hist, min(args.cpu_seconds, 4.0), 1)
+    out["cpu_baseline"] = {
+        "value": v_all[0], "unit": "game-steps/s", "cores": v_all[4], "kind": v_all[3],
+        "sample": "%d playouts from 4096 synthetic mid-game roots (d~U{8..20}), %.1f s, reference "
+                  "State::Clone/LegalActions/ApplyAction loop, one std::thread per core" % (v_all[2], v_all[5]),
+        "single_core_value": v_one[0], "playouts_per_s": v_all[1],
+        "cpu_model": cpu_model(),
+    }
+  return out
+
+
+def cpu_model():
+  try:
+    with open("/proc/cpuinfo") as f:
+      for line in f:
+        if line.startswith("model name"):
+          return line.split(":", 1)[1].strip()
+  except Exception:
+    pass
+  return "unknown"
+
+
+def main():
+  args = parse_args()
+  if args.impl == "reference":
+    return run_reference_arm(args)
+  return run_ours(args)
+
+
+if __name__ == "__main__":
+  sys.exit(main())

@@ -540,8 +540,15 @@ int bsg_playouts_host(bsg_engine* e, const void* roots_host, int64_t n_roots, in
   if ((rc = ensure(e, &e->d_out, &e->d_out_bytes, out_elems * 4 + 16, false)) != BSG_OK) return rc;
   if ((rc = ensure(e, &e->h_pinned, &e->h_pinned_bytes, in_bytes + out_elems * 4 + 64, true)) != BSG_OK) return rc;
   cudaStream_t st = e->own_stream;
-  memcpy(e->h_pinned, roots_host, in_bytes);
-  BSG_CUDA(e, cudaMemcpyAsync(e->d_roots, e->h_pinned, in_bytes, cudaMemcpyHostToDevice, st));
+  // Page-locked caller memory (e.g. a torch pin_memory() tensor) is copied from directly;
+  // pageable memory is staged through the engine's pinned buffer.
+  cudaPointerAttributes attr;
+  bool pinned_src = cudaPointerGetAttributes(&attr, roots_host) == cudaSuccess &&
+                    attr.type == cudaMemoryTypeHost;
+  cudaGetLastError();
+  const void* src = roots_host;
+  if (!pinned_src) { memcpy(e->h_pinned, roots_host, in_bytes); src = e->h_pinned; }
+  BSG_CUDA(e, cudaMemcpyAsync(e->d_roots, src, in_bytes, cudaMemcpyHostToDevice, st));
   BSG_CUDA(e, cudaMemsetAsync(e->d_totals, 0, 4 * sizeof(uint64_t), st));
   if (out_elems) BSG_CUDA(e, cudaMemsetAsync(e->d_out, 0, out_elems * 4, st));
   bsg_playout_io io;
