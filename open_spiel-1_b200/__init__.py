@@ -16,6 +16,8 @@ from .engine import Engine, game_id, pack_histories, draw
 from .evaluator import Evaluator, GpuRolloutEvaluator
 from .spiel import load_game, Game, State, GameType, PlayerId
 from .mcts import MCTSBot, SearchNode
+from .parallel import RootParallelMCTS, ShardedPlayouts, shard_range
 
 __all__ = ["Engine", "game_id", "pack_histories", "draw", "Evaluator", "GpuRolloutEvaluator",
-           "load_game", "Game", "State", "GameType", "PlayerId", "MCTSBot", "SearchNode"]
+           "load_game", "Game", "State", "GameType", "PlayerId", "MCTSBot", "SearchNode",
+           "RootParallelMCTS", "ShardedPlayouts", "shard_range"]

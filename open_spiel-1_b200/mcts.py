@@ -179,12 +179,21 @@ class MCTSBot(object):
         else:
           solved = False
 
-  def mcts_search(self, state):
-    """Runs max_simulations simulations from `state`; returns the root SearchNode."""
+  def expand_root(self, root, state):
+    """Creates the root's children without running a simulation (root-parallel merge)."""
+    if not root.children and not state.is_terminal():
+      self._expand(root, state, True)
+
+  def mcts_search(self, state, root=None, simulations=None):
+    """Runs max_simulations simulations from `state`; returns the root SearchNode.
+    `root` resumes an earlier search of the same state and `simulations` overrides the
+    budget of this call (both used by parallel.RootParallelMCTS between merges)."""
     root_player = state.current_player()
-    root = SearchNode(None, root_player, 1)
+    if root is None:
+      root = SearchNode(None, root_player, 1)
+    budget = self.max_simulations if simulations is None else int(simulations)
     done = 0
-    while done < self.max_simulations:
+    while done < budget:
       if self.leaf_batch == 1:
         path, leaf = self._apply_tree_policy(root, state)
         if leaf.is_terminal():
@@ -197,7 +206,7 @@ class MCTSBot(object):
         self._backup(path, returns, solved, root_player)
         done += 1
       else:
-        done += self._batched_round(root, state, root_player, self.max_simulations - done)
+        done += self._batched_round(root, state, root_player, budget - done)
       if root.outcome is not None:
         break
     return root

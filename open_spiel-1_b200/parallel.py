@@ -1,0 +1,199 @@
+"""Multi-GPU side of the rollout path: one process per GPU (torch.distributed).
+
+Two things shard:
+
+* Independent playouts (BASELINE configs 2-4).  `shard_range` gives rank r the contiguous
+  slice [r*N/W, (r+1)*N/W) of the playout index range.  The Philox counter of a playout is its
+  GLOBAL index, so per-playout results are identical for every GPU count; there is no
+  data-path collective, only an optional final all-reduce of the four int64 totals
+  (`ShardedPlayouts.run`).
+
+* Root-parallel MCTS (BASELINE config 5).  Every rank searches the same root with its own
+  tree, random stream and playout-id range; after every search step (a batch of simulations)
+  ONE all-reduce(sum) of a fixed int64 buffer merges the root children's statistics
+  (`explore_count`, `total_reward` — python/algorithms/mcts.py:116-122) into every rank's root,
+  and the final move is `best_child` over the merged statistics (mcts.py:144-162).  Rewards of
+  a rollout evaluator are multiples of 1/n_rollouts, so they travel as exact integers
+  (reward * n_rollouts): the merge is order-independent and bit-reproducible.  Solver-proven
+  outcomes (mcts.py:437) ride in the same buffer as per-value proof counts.
+
+Backend: "nccl" on GPUs (the buffer lives on the rank's device; 40 B per root child, so the
+collective is latency-bound and NVLink bandwidth is irrelevant), "gloo" in the CPU tests.
+"""
+import numpy as np
+
+from .mcts import MCTSBot, SearchNode
+
+
+def shard_range(n, rank, world):
+  """Contiguous slice [lo, hi) of range(n) owned by `rank` out of `world` (balanced to ±1)."""
+  if world < 1 or not 0 <= rank < world:
+    raise ValueError("bad rank/world %r/%r" % (rank, world))
+  return (n * rank) // world, (n * (rank + 1)) // world
+
+
+def _dist():
+  import torch.distributed as dist
+  return dist
+
+
+def _world(group=None):
+  dist = _dist()
+  if dist.is_available() and dist.is_initialized():
+    return dist.get_rank(group), dist.get_world_size(group)
+  return 0, 1
+
+
+def all_reduce_int64(values, device=None, group=None, op="sum"):
+  """One all-reduce of a small int64 vector; returns a numpy array.  World size 1 is a no-op
+  (never a CPU detour for the playouts themselves).  `device` = torch device of the buffer
+  (the rank's GPU under NCCL, None/cpu under gloo)."""
+  values = np.asarray(values, np.int64)
+  rank, world = _world(group)
+  if world == 1:
+    return values.copy()
+  import torch
+  dist = _dist()
+  t = torch.from_numpy(values.copy())
+  if device is not None:
+    t = t.to(device)
+  dist.all_reduce(t, op=dist.ReduceOp.SUM if op == "sum" else dist.ReduceOp.MAX, group=group)
+  return t.cpu().numpy()
+
+
+class ShardedPlayouts:
+  """Runs this rank's shard of `n_roots` roots through an `engine.Engine` and (optionally)
+  reduces the totals.  `roots_of(lo, hi)` must return the packed DEVICE states of roots
+  lo..hi-1 (capacity hi-lo), so each rank only ever materialises its own shard."""
+
+  def __init__(self, engine, group=None):
+    self.engine = engine
+    self.group = group
+    self.rank, self.world = _world(group)
+
+  def run(self, roots_of, n_roots, rollouts=1, seed=0, reduce=True):
+    import torch
+    lo, hi = shard_range(n_roots, self.rank, self.world)
+    totals = torch.zeros(4, dtype=torch.int64, device=self.engine.torch_device)
+    if hi > lo:
+      self.engine.playouts(roots_of(lo, hi), hi - lo, rollouts, seed=seed,
+                           first_playout=lo * rollouts, totals=totals)
+    if reduce and self.world > 1:
+      _dist().all_reduce(totals, group=self.group)  # int64 sum: order-independent
+    return totals.cpu().numpy()
+
+
+# Layout of the merge buffer, per root child (index = action id): visit delta, reward delta *
+# scale, then how many ranks hold a solver proof "mover loses / draws / wins" for that child.
+# Everything is summed, so ONE all-reduce carries statistics and proofs together.
+_F_VISITS, _F_REWARD, _F_PROVEN, _F_FIELDS = 0, 1, 2, 5
+
+
+class RootParallelMCTS:
+  """Root-parallel MCTS over `world` ranks with one all-reduce per search step.
+
+  Args:
+    game: pyspiel.Game / spiel.Game.
+    uct_c, evaluator, solve, child_selection_fn: as `MCTSBot` (mcts.py:199-262).
+    max_simulations: total simulations per move, summed over all ranks.
+    sims_per_step: simulations each rank runs between two all-reduces (the "search step").
+    seed: base seed; rank r shuffles priors with RandomState(seed + r) and — through
+      `evaluator.next_playout` when present — draws from its own playout-id range.
+    reward_scale: integer that makes every evaluator return an exact integer when multiplied
+      (n_rollouts for a rollout evaluator).
+    leaf_batch: leaves gathered per kernel launch inside a rank (mcts.MCTSBot.leaf_batch).
+    device: torch device of the collective buffer (None = CPU, for gloo).
+  """
+
+  def __init__(self, game, uct_c, max_simulations, evaluator, sims_per_step=None, solve=True,
+               seed=0, reward_scale=None, leaf_batch=1, child_selection_fn=SearchNode.uct_value,
+               device=None, group=None):
+    self.rank, self.world = _world(group)
+    self.group = group
+    self.device = device
+    self.total_simulations = int(max_simulations)
+    lo, hi = shard_range(self.total_simulations, self.rank, self.world)
+    self.local_simulations = hi - lo
+    # every rank must take the same number of steps (the all-reduce is collective)
+    per_rank_max = -(-self.total_simulations // self.world)
+    self.sims_per_step = int(sims_per_step or per_rank_max)
+    self.n_steps = max(1, -(-per_rank_max // self.sims_per_step))
+    if reward_scale is None:
+      reward_scale = getattr(evaluator, "n_rollouts", 1)
+    self.reward_scale = int(reward_scale)
+    self.num_actions = game.num_distinct_actions()
+    self.bot = MCTSBot(game, uct_c, self.local_simulations, evaluator, solve=solve,
+                       random_state=np.random.RandomState(seed + self.rank),
+                       child_selection_fn=child_selection_fn, leaf_batch=leaf_batch)
+    # disjoint playout-id ranges per rank keep the ranks' Philox streams independent
+    if hasattr(evaluator, "next_playout"):
+      evaluator.next_playout += self.rank << 40
+    self.all_reduces = 0
+    self.last_root = None
+
+  # ---- merge
+  def _pack(self, root, base):
+    """Deltas of this rank's root-child statistics since `base` + proven outcomes."""
+    buf = np.zeros((self.num_actions, _F_FIELDS), np.int64)
+    for ch in root.children:
+      b = base.get(ch.action, (0, 0))
+      scaled = int(round(ch.total_reward * self.reward_scale))
+      buf[ch.action, _F_VISITS] = ch.explore_count - b[0]
+      buf[ch.action, _F_REWARD] = scaled - b[1]
+      if ch.outcome is not None:  # proven value for the mover: -1 / 0 / +1 -> slot 0 / 1 / 2
+        buf[ch.action, _F_PROVEN + int(round(ch.outcome[ch.player])) + 1] = 1
+    return buf
+
+  def _merge(self, root, base):
+    """One all-reduce: sums the visit/reward deltas and proof counts of all ranks and installs
+    the global statistics into this rank's root children."""
+    mine = self._pack(root, base)
+    summed = all_reduce_int64(mine.reshape(-1), self.device, self.group)
+    summed = summed.reshape(self.num_actions, _F_FIELDS)
+    self.all_reduces += 1
+    new_base = {}
+    visits = 0
+    for ch in root.children:
+      b = base.get(ch.action, (0, 0))
+      n = b[0] + int(summed[ch.action, 0])
+      r = b[1] + int(summed[ch.action, 1])
+      ch.explore_count = n
+      ch.total_reward = r / self.reward_scale
+      new_base[ch.action] = (n, r)
+      visits += n
+      proofs = summed[ch.action, _F_PROVEN:_F_PROVEN + 3]
+      if ch.outcome is None and proofs.any():  # exact game values: ranks cannot disagree
+        v = float(int(np.argmax(proofs)) - 1)
+        ch.outcome = [v, -v] if ch.player == 0 else [-v, v]
+    if root.children:
+      root.explore_count = max(root.explore_count, visits)
+    return new_base
+
+  # ---- search
+  def mcts_search(self, state):
+    """Runs the sharded search; returns this rank's root with GLOBAL child statistics (equal
+    on every rank for visits/rewards)."""
+    root = None
+    base = {}
+    left = self.local_simulations
+    for _ in range(self.n_steps):
+      k = min(self.sims_per_step, left)
+      left -= k
+      root = self.bot.mcts_search(state, root=root, simulations=k)
+      if not root.children and not state.is_terminal():
+        self.bot.expand_root(root, state)  # a rank with 0 simulations still joins the merge
+      base = self._merge(root, base)
+    self.last_root = root
+    return root
+
+  def step_with_policy(self, state):
+    root = self.mcts_search(state)
+    # identical on every rank: ties in (proven, visits, reward) fall to the lowest action id
+    best = max(sorted(root.children, key=lambda c: c.action), key=SearchNode.sort_key)
+    action = best.action
+    policy = [(a, 1.0 if a == action else 0.0)
+              for a in state.legal_actions(state.current_player())]
+    return policy, action
+
+  def step(self, state):
+    return self.step_with_policy(state)[1]
