@@ -337,7 +337,8 @@ def rank0_extras(args, eng, torch, dev, steps_per_s_per_gpu, kernel_ms, n):
     with open(peaks_path) as f:
       hbm_peak, hbm_src = float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
   # integer-issue peak measured live on this GPU: best of ALU-only, IMAD-only and mixed chains
-  kinds = {0: "LOP3+IADD3 (ALU pipe)", 1: "IMAD (FMA pipe)", 2: "SHF/LOP3 + IMAD mix"}
+  kinds = {0: "LOP3+IADD3 (ALU pipe)", 1: "IMAD (FMA pipe)", 2: "SHF+LOP3+IMAD 2:1",
+           3: "LOP3+IMAD 1:1"}
   peaks = {k: eng.int_peak(k, 4000) for k in kinds}
   peak_int = max(peaks.values())
   ops = OPS_PER_STEP[args.game]
@@ -364,7 +365,7 @@ def rank0_extras(args, eng, torch, dev, steps_per_s_per_gpu, kernel_ms, n):
       obs = torch.empty((n_obs, 3, 8, 8), dtype=torch.float32, device=dev)
       ms = time_kernel(torch, dev, lambda: e_bt.observations(st, n_obs, None, out=obs))
       gbs = n_obs * 784 / (ms * 1e-3) / 1e9
-      out["obs_roofline"] = {"bound": "hbm", "kernel": "obs_kernel<Breakthrough>",
+      out["obs_roofline"] = {"bound": "hbm", "kernel": "expand_kernel<Breakthrough,false>",
                              "achieved": gbs, "peak": hbm_peak, "unit": "GB/s",
                              "frac": gbs / hbm_peak, "traffic": None, "peak_source": hbm_src,
                              "states": n_obs, "obs_per_s": n_obs / (ms * 1e-3),

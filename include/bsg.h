@@ -87,6 +87,9 @@ int bsg_host_apply_action(int game, void* packed_host, int64_t cap, int64_t i, i
 /* State::ObservationTensor(player) of one packed state as float 0/1, flat CHW. */
 int bsg_host_observation(int game, const void* packed_host, int64_t cap, int64_t i, int player,
                          float* obs_out);
+/* State::LegalActionsMask (spiel.h:244-252) of one packed state: NumDistinctActions bytes. */
+int bsg_host_legal_mask(int game, const void* packed_host, int64_t cap, int64_t i,
+                        uint8_t* mask_out);
 /* Debug/test hook: applies LegalActions()[r mod n] to packed state i through the very step
  * function the kernels run, so the selection logic can be checked on a CPU.  No product
  * path calls it; playouts exist only as CUDA kernels. */
@@ -152,7 +155,7 @@ int bsg_observations_host(bsg_engine* e, const void* states_host, int64_t n,
 /* Integer-issue microbenchmark used for the roofline denominator (bench.py): runs `iters`
  * dependent-chain iterations of `ilp` independent 32-bit ops per thread on every SM and
  * returns thread-instructions per second.  kind: 0 = LOP3/IADD3 mix (ALU pipe), 1 = IMAD
- * (FMA pipe), 2 = alternating ALU/IMAD. */
+ * (FMA pipe), 2 = SHF + LOP3 + IMAD (2 ALU : 1 FMA), 3 = LOP3 + IMAD (1 : 1, both pipes busy). */
 int bsg_int_peak(bsg_engine* e, int kind, int iters, double* thread_instr_per_s);
 
 #ifdef __cplusplus

@@ -61,6 +61,7 @@ def _load():
       "bsg_host_legal_actions": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, vp, ctypes.c_int]),
       "bsg_host_apply_action": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, i64]),
       "bsg_host_observation": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, ctypes.c_int, vp]),
+      "bsg_host_legal_mask": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, vp]),
       "bsg_host_replay_step": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, u32, vp]),
       "bsg_draw": (u32, [u64, u64, u32]),
       "bsg_create": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.POINTER(vp)]),

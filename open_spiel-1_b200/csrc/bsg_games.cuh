@@ -12,6 +12,9 @@
 //   legal(s, out)              ascending legal action ids (host side: prior, pack, checks)
 //   apply(s, action)           apply one action id (host side; false if illegal)
 //   obs_bit(s, player, idx)    element idx of the flat CHW observation (reference order)
+//   obs_words(s, player, out)  the whole flat observation as a bit string, kObsWords u32
+//                              (bit e of the string = element e); what the batched writer expands
+//   mask_words(s, out)         State::LegalActionsMask as a bit string, kMaskWords u32
 //
 // Semantics follow the reference rules cited per function; the representation does not.
 #pragma once
@@ -27,6 +30,9 @@ namespace bsg {
 struct TicTacToe {
   static constexpr int kId = kGameTicTacToe;
   static constexpr int kNumActions = 9, kMaxLen = 9, kObsSize = 27, kStateBytes = 4;
+  static constexpr int kObsWords = 1, kMaskWords = 1;
+  static constexpr int kPlanes = 1;   // packed SoA planes and their element sizes
+  BSG_HD static int plane_bytes(int p) { (void)p; return 4; }
   struct State { u32 x, o, term, outc; };
   struct Tables { u32 modM[16]; };
   static void fill_tables(Tables& t) { for (u32 n = 0; n < 16; ++n) t.modM[n] = modM_entry(n); }
@@ -93,6 +99,13 @@ struct TicTacToe {
     u32 m = plane == 0 ? ~(s.x | s.o) : (plane == 1 ? s.o : s.x);
     return (m >> cell) & 1u;
   }
+  BSG_HD static void obs_words(const State& s, int player, u32* out) {
+    (void)player;
+    out[0] = (~(s.x | s.o) & 0x1FFu) | (s.o << 9) | (s.x << 18);
+  }
+  BSG_HD static void mask_words(const State& s, u32* out) {
+    out[0] = s.term ? 0u : (~(s.x | s.o) & 0x1FFu);
+  }
 };
 
 // =========================================================================================
@@ -106,6 +119,9 @@ struct TicTacToe {
 struct ConnectFour {
   static constexpr int kId = kGameConnectFour;
   static constexpr int kNumActions = 7, kMaxLen = 42, kObsSize = 126, kStateBytes = 16;
+  static constexpr int kObsWords = 4, kMaskWords = 1;
+  static constexpr int kPlanes = 1;
+  BSG_HD static int plane_bytes(int p) { (void)p; return 16; }
   struct State {
     u64 cur, opp;  // stones of the player to move / of the other player
     u32 h;         // column heights, 4 bits per column
@@ -219,6 +235,24 @@ struct ConnectFour {
     u64 m = plane == 0 ? theirs : (plane == 1 ? mine : ~(mine | theirs));
     return (u32)(m >> (row * 8 + col)) & 1u;
   }
+  // Board with 8-bit rows -> the reference's 42-cell order (7-bit rows, cell = row * 7 + col).
+  BSG_HD static u64 squeeze(u64 b) {
+    u64 r = 0;
+#pragma unroll
+    for (int row = 0; row < 6; ++row) r |= ((b >> (8 * row)) & 0x7Full) << (7 * row);
+    return r;
+  }
+  BSG_HD static void obs_words(const State& s, int player, u32* out) {
+    u64 mine = squeeze((player == (int)s.mv) ? s.cur : s.opp);
+    u64 theirs = squeeze((player == (int)s.mv) ? s.opp : s.cur);
+    u64 empty = ~(mine | theirs) & 0x3FFFFFFFFFFull;
+    u64 lo = theirs | (mine << 42);               // plane 0 at bit 0, plane 1 at bit 42
+    u64 hi = (mine >> 22) | (empty << 20);        // plane 2 at bit 84
+    out[0] = (u32)lo; out[1] = (u32)(lo >> 32); out[2] = (u32)hi; out[3] = (u32)(hi >> 32);
+  }
+  BSG_HD static void mask_words(const State& s, u32* out) {
+    out[0] = s.term ? 0u : open_columns(s);
+  }
 };
 
 // =========================================================================================
@@ -237,6 +271,9 @@ struct ConnectFour {
 struct Breakthrough {
   static constexpr int kId = kGameBreakthrough;
   static constexpr int kNumActions = 768, kMaxLen = 209, kObsSize = 192, kStateBytes = 20;
+  static constexpr int kObsWords = 6, kMaskWords = 24;
+  static constexpr int kPlanes = 2;
+  BSG_HD static int plane_bytes(int p) { return p == 0 ? 16 : 4; }
   static constexpr u64 kCol0 = 0x0101010101010101ull, kCol7 = 0x8080808080808080ull;
   struct State { u64 own, opp; u32 mv, term, outc; };
   struct Tables { u32 modM[64]; };
@@ -368,6 +405,39 @@ struct Breakthrough {
     u64 m = plane == 0 ? black : (plane == 1 ? white : ~(black | white));
     return (u32)(m >> cell) & 1u;
   }
+  BSG_HD static void obs_words(const State& s, int player, u32* out) {
+    (void)player;
+    u64 black = s.mv ? s.opp : s.own, white = s.mv ? s.own : s.opp, empty = ~(black | white);
+    out[0] = (u32)black; out[1] = (u32)(black >> 32);
+    out[2] = (u32)white; out[3] = (u32)(white >> 32);
+    out[4] = (u32)empty; out[5] = (u32)(empty >> 32);
+  }
+  // 12 action bits per source cell: bit (3*mover + o)*2 + capture.  Built for mover 0 (six
+  // bits per cell at 12*cell), then the whole string moves up by 6 bits for mover 1.
+  BSG_HD static void mask_words(const State& s, u32* out) {
+    u64 L, F, R;
+    movegen(s, L, F, R);
+    if (s.term) { L = 0; F = 0; R = 0; }
+    int base = s.mv ? 48 : 0;
+    u64 CL = rotr64(s.opp, base + 7), CR = rotr64(s.opp, base + 9);  // enemy on the diagonal target
+    u64 a0 = L & ~CL, a1 = L & CL, a4 = R & ~CR, a5 = R & CR;
+#pragma unroll
+    for (int w = 0; w < kMaskWords; ++w) out[w] = 0;
+#pragma unroll
+    for (int i = 0; i < 64; ++i) {
+      u32 pat = (u32)((a0 >> i) & 1ull) | ((u32)((a1 >> i) & 1ull) << 1) |
+                ((u32)((F >> i) & 1ull) << 2) | ((u32)((a4 >> i) & 1ull) << 4) |
+                ((u32)((a5 >> i) & 1ull) << 5);
+      const int pos = 12 * i, w = pos >> 5, sh = pos & 31;
+      out[w] |= pat << sh;
+      if (sh > 26) out[w + 1] |= pat >> (32 - sh);
+    }
+    if (s.mv) {
+#pragma unroll
+      for (int w = kMaskWords - 1; w >= 1; --w) out[w] = (out[w] << 6) | (out[w - 1] >> 26);
+      out[0] <<= 6;
+    }
+  }
 };
 
 // =========================================================================================
@@ -390,6 +460,9 @@ struct HexT {
   static constexpr int kCells = N * N;
   static constexpr int kNumActions = N * N, kMaxLen = N * N, kObsSize = 9 * N * N;
   static constexpr int kStateBytes = 64;
+  static constexpr int kObsWords = (9 * N * N + 31) / 32, kMaskWords = 4;
+  static constexpr int kPlanes = 4;
+  BSG_HD static int plane_bytes(int p) { (void)p; return 16; }
   struct M128 { u32 w[4]; };
   struct State {
     u32 occ[4];                       // all stones; bits >= N*N are kept set (never legal)
@@ -596,6 +669,33 @@ struct HexT {
       case 7: return bA & ~bB & 1u;
       default: return bA & bB;
     }
+  }
+  BSG_HD static void obs_words(const State& s, int player, u32* out) {
+    (void)player;
+    u32 m[9][4];
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      u32 bA = s.mv ? s.oA[w] : s.cA[w], bB = s.mv ? s.oB[w] : s.cB[w], bP = s.mv ? s.oP[w] : s.cP[w];
+      u32 wA = s.mv ? s.cA[w] : s.oA[w], wB = s.mv ? s.cB[w] : s.oB[w], wP = s.mv ? s.cP[w] : s.oP[w];
+      m[0][w] = wA & wB; m[1][w] = wA & ~wB; m[2][w] = wB & ~wA; m[3][w] = wP;
+      m[4][w] = ~s.occ[w];
+      m[5][w] = bP; m[6][w] = bB & ~bA; m[7][w] = bA & ~bB; m[8][w] = bA & bB;
+    }
+#pragma unroll
+    for (int w = 0; w < kObsWords; ++w) out[w] = 0;
+#pragma unroll
+    for (int p = 0; p < 9; ++p) {
+      const int off = p * kCells, wi = off >> 5, sh = off & 31;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (wi + j < kObsWords) out[wi + j] |= m[p][j] << sh;
+        if (sh != 0 && wi + j + 1 < kObsWords) out[wi + j + 1] |= m[p][j] >> ((32 - sh) & 31);
+      }
+    }
+  }
+  BSG_HD static void mask_words(const State& s, u32* out) {
+#pragma unroll
+    for (int w = 0; w < 4; ++w) out[w] = s.term ? 0u : ~s.occ[w];
   }
 };
 typedef HexT<11> Hex;

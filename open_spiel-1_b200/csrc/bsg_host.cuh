@@ -122,7 +122,29 @@ struct ObsOp {
   template <class G> int operator()() const {
     typename G::State s;
     G::load(s, p, cap, i);
-    for (int k = 0; k < G::kObsSize; ++k) out[k] = (float)G::obs_bit(s, player, k);
+    // through the bit string the batched device writer expands, cross-checked per element
+    u32 words[G::kObsWords];
+    G::obs_words(s, player, words);
+    for (int k = 0; k < G::kObsSize; ++k) {
+      u32 b = (words[k >> 5] >> (k & 31)) & 1u;
+      if (b != G::obs_bit(s, player, k)) return BSG_ERR_BAD_ARG;  // internal inconsistency
+      out[k] = (float)b;
+    }
+    return BSG_OK;
+  }
+};
+struct MaskOp {
+  const void* p; int64_t cap, i; uint8_t* out;
+  template <class G> int operator()() const {
+    typename G::State s;
+    G::load(s, p, cap, i);
+    u32 words[G::kMaskWords];
+    G::mask_words(s, words);
+    for (int a = 0; a < G::kNumActions; ++a) {
+      u32 b = (words[a >> 5] >> (a & 31)) & 1u;
+      if (b != G::legal_bit(s, a)) return BSG_ERR_BAD_ARG;  // internal inconsistency
+      out[a] = (uint8_t)b;
+    }
     return BSG_OK;
   }
 };

@@ -27,7 +27,8 @@ constexpr int kThreads = 256;
 
 struct PlayoutArgs {
   const void* roots;
-  int64_t n_roots;
+  int64_t n_roots;   // capacity of the packed SoA root buffer
+  int64_t root0;     // first root of this launch (chunked host path); playout p uses root0 + p / rollouts
   uint32_t n_playouts;
   uint32_t rollouts;
   uint64_t first_playout;
@@ -89,7 +90,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         if (idx < count) {
           lid = begin + idx;
           u32 root = a.rollouts == 1 ? lid : lid / a.rollouts;
-          G::load(s, a.roots, a.n_roots, root);
+          G::load(s, a.roots, a.n_roots, a.root0 + root);
           t = 0;
           have = true;
           if (kFull) {
@@ -173,76 +174,102 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
 
 
 // ---------------------------------------------------------------------------------------
-// Batched ObservationTensor / LegalActionsMask writer.  HBM-write bound: every thread emits
-// one 16-byte store (4 floats / 16 mask bytes) of the flat [n, size] output, so each warp
-// store instruction covers 512 contiguous bytes.  Packed states are re-read through L1/L2
-// (16-64 B per state against 108-4356 B written).
+// Batched ObservationTensor / LegalActionsMask writer.  HBM-write bound.
+//
+// Both outputs are 0/1 expansions of a per-state bit string (G::obs_words: kObsSize bits in
+// the reference's flat CHW element order; G::mask_words: NumDistinctActions bits).  A CTA
+// works on chunks of kChunk consecutive states:
+//   phase 1  one thread per state: load the packed state (coalesced SoA read), build its bit
+//            string in registers, park it in shared memory (row stride odd: no bank conflicts);
+//   phase 2  the chunk's output is one contiguous, 16-byte aligned range of the [n, size]
+//            array; thread j emits the j-th 16-byte store of it — 4 floats from 4 bits, or 16
+//            mask bytes from 16 bits — so every warp store instruction covers 512 contiguous
+//            bytes.  Bits come from shared memory with one funnel shift; a store that spans
+//            two (or, for 7/9-action masks, more) states gathers across rows.
+// Algorithmic HBM bytes per state = output + packed state; nothing is re-read from HBM.
 // ---------------------------------------------------------------------------------------
-template <class G>
-__global__ void __launch_bounds__(kThreads)
-obs_kernel(const void* __restrict__ states, int64_t n, const uint8_t* __restrict__ players,
-           float* __restrict__ out) {
-  const int64_t total = n * G::kObsSize;
-  const int64_t total4 = (total + 3) >> 2;
-  const int64_t stride = (int64_t)gridDim.x * kThreads;
-  for (int64_t g = (int64_t)blockIdx.x * kThreads + threadIdx.x; g < total4; g += stride) {
-    int64_t e0 = g << 2;
-    int64_t st = e0 / G::kObsSize;
-    int idx = (int)(e0 - st * G::kObsSize);
-    typename G::State s;
-    G::load(s, states, n, st);
-    int player = players ? (int)players[st] : G::mover(s);
-    float v[4];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      if (idx == G::kObsSize) {
-        idx = 0;
-        st += 1;
-        if (st < n) {
-          G::load(s, states, n, st);
-          player = players ? (int)players[st] : G::mover(s);
-        }
-      }
-      v[q] = (st < n) ? (float)G::obs_bit(s, player, idx) : 0.f;
-      idx += 1;
-    }
-    if (e0 + 4 <= total) {
-      __stcs(reinterpret_cast<float4*>(out) + g, make_float4(v[0], v[1], v[2], v[3]));
-    } else {
-      for (int q = 0; q < 4 && e0 + q < total; ++q) out[e0 + q] = v[q];
-    }
+constexpr int kChunk = 256;  // states per CTA chunk (= threads); multiple of 32 keeps stores aligned
+
+template <int kBits, int kRow>
+__device__ __forceinline__ u32 gather_bits(const u32* __restrict__ sm, int st, int r, int want, int nst) {
+  // `want` (<= 16) bits starting at bit r of state st's string, continuing into later states
+  const u32* p = sm + st * kRow;
+  u32 x = __funnelshift_r(p[r >> 5], p[(r >> 5) + 1], r & 31);
+  int got = kBits - r;
+  if (got >= want) return x & ((1u << want) - 1u);
+  x &= (1u << got) - 1u;
+  for (st += 1; got < want && st < nst; ++st) {
+    x |= sm[st * kRow] << got;  // rows hold kBits >= 1 valid bits, the rest is zero
+    got += kBits;
   }
+  return x & ((1u << want) - 1u);
 }
 
-template <class G>
-__global__ void __launch_bounds__(kThreads)
-legal_mask_kernel(const void* __restrict__ states, int64_t n, uint8_t* __restrict__ out) {
-  const int64_t total = n * G::kNumActions;
-  const int64_t total16 = (total + 15) >> 4;
-  const int64_t stride = (int64_t)gridDim.x * kThreads;
-  for (int64_t g = (int64_t)blockIdx.x * kThreads + threadIdx.x; g < total16; g += stride) {
-    int64_t e0 = g << 4;
-    int64_t st = e0 / G::kNumActions;
-    int idx = (int)(e0 - st * G::kNumActions);
-    typename G::State s;
-    G::load(s, states, n, st);
-    u32 w[4] = {0, 0, 0, 0};
-#pragma unroll
-    for (int q = 0; q < 16; ++q) {
-      if (idx == G::kNumActions) {
-        idx = 0;
-        st += 1;
-        if (st < n) G::load(s, states, n, st);
+// kMask = false: float32 observation planes; true: uint8 legal-action mask.
+template <class G, bool kMask>
+__global__ void __launch_bounds__(kChunk)
+expand_kernel(const void* __restrict__ states, int64_t n, const uint8_t* __restrict__ players,
+              void* __restrict__ out_) {
+  constexpr int kBits = kMask ? G::kNumActions : G::kObsSize;
+  constexpr int kWords = kMask ? G::kMaskWords : G::kObsWords;
+  constexpr int kRow = (kWords + 1) | 1;            // + one zero word for the funnel read; odd
+  constexpr int kPer = kMask ? 16 : 4;              // output elements per 16-byte store
+  __shared__ u32 sm[kChunk * kRow];
+  const int64_t n_chunks = (n + kChunk - 1) / kChunk;
+  for (int64_t c = blockIdx.x; c < n_chunks; c += gridDim.x) {
+    const int64_t s0 = c * kChunk;
+    const int nst = (int)min((int64_t)kChunk, n - s0);
+    // ---- phase 1
+    if ((int)threadIdx.x < nst) {
+      typename G::State s;
+      G::load(s, states, n, s0 + threadIdx.x);
+      u32 w[kWords];
+      if (kMask) {
+        G::mask_words(s, w);
+      } else {
+        int player = players ? (int)players[s0 + threadIdx.x] : G::mover(s);
+        G::obs_words(s, player, w);
       }
-      u32 b = (st < n) ? G::legal_bit(s, idx) : 0u;
-      w[q >> 2] |= b << (8 * (q & 3));
-      idx += 1;
+      u32* row = sm + threadIdx.x * kRow;
+#pragma unroll
+      for (int i = 0; i < kWords; ++i) row[i] = w[i];
+#pragma unroll
+      for (int i = kWords; i < kRow; ++i) row[i] = 0u;
     }
-    if (e0 + 16 <= total) {
-      __stcs(reinterpret_cast<uint4*>(out) + g, make_uint4(w[0], w[1], w[2], w[3]));
-    } else {
-      for (int q = 0; q < 16 && e0 + q < total; ++q) out[e0 + q] = (uint8_t)((w[q >> 2] >> (8 * (q & 3))) & 0xFF);
+    __syncthreads();
+    // ---- phase 2
+    const int total = nst * kBits;                  // output elements of this chunk
+    const int n16 = total / kPer;
+    uint4* out16 = reinterpret_cast<uint4*>(reinterpret_cast<char*>(out_) +
+                                            s0 * (int64_t)kBits * (kMask ? 1 : 4));
+    for (int j = threadIdx.x; j < n16; j += kChunk) {
+      const int e0 = j * kPer;
+      const int st = e0 / kBits, r = e0 - st * kBits;
+      u32 x = gather_bits<kBits, kRow>(sm, st, r, kPer, nst);
+      uint4 v;
+      if (kMask) {  // 4 bits -> 4 bytes: (nibble * 0x00204081) & 0x01010101
+        v.x = ((x & 15u) * 0x00204081u) & 0x01010101u;
+        v.y = (((x >> 4) & 15u) * 0x00204081u) & 0x01010101u;
+        v.z = (((x >> 8) & 15u) * 0x00204081u) & 0x01010101u;
+        v.w = (((x >> 12) & 15u) * 0x00204081u) & 0x01010101u;
+      } else {      // bit -> 0.0f / 1.0f
+        v.x = (x & 1u) * 0x3F800000u;
+        v.y = ((x >> 1) & 1u) * 0x3F800000u;
+        v.z = ((x >> 2) & 1u) * 0x3F800000u;
+        v.w = ((x >> 3) & 1u) * 0x3F800000u;
+      }
+      __stcs(out16 + j, v);
     }
+    // tail of the very last chunk when its size is not a multiple of 16 bytes
+    const int rest = total - n16 * kPer;
+    if ((int)threadIdx.x < rest) {
+      const int e = n16 * kPer + threadIdx.x;
+      const int st = e / kBits, r = e - st * kBits;
+      u32 bit = (sm[st * kRow + (r >> 5)] >> (r & 31)) & 1u;
+      if (kMask) reinterpret_cast<uint8_t*>(out16)[e] = (uint8_t)bit;
+      else reinterpret_cast<float*>(out16)[e] = bit ? 1.f : 0.f;
+    }
+    __syncthreads();
   }
 }
 
@@ -262,7 +289,8 @@ __global__ void __launch_bounds__(kThreads) int_peak_kernel(int iters, u32* sink
       for (int i = 0; i < 8; ++i) {
         if (KIND == 0) x[i] = (x[i] ^ k) + (x[(i + 1) & 7] & 0x55555555u) ;          // LOP3 + IADD3
         else if (KIND == 1) x[i] = x[i] * 0x9E3779B1u + k;                             // IMAD
-        else { x[i] = (x[i] ^ (x[(i + 3) & 7] >> 3)); x[i] = x[i] * 0x9E3779B1u + k; } // SHF/LOP + IMAD
+        else if (KIND == 2) { x[i] = (x[i] ^ (x[(i + 3) & 7] >> 3)); x[i] = x[i] * 0x9E3779B1u + k; } // SHF/LOP + IMAD
+        else { x[i] = (x[i] ^ x[(i + 3) & 7]) * 0x9E3779B1u + k; }                      // LOP3 + IMAD, 1:1
       }
     }
   }
@@ -290,6 +318,8 @@ struct bsg_engine {
   void* h_pinned = nullptr; size_t h_pinned_bytes = 0;
   uint64_t* d_totals = nullptr;
   cudaStream_t own_stream = nullptr;
+  cudaStream_t aux_stream = nullptr;   // second lane of the chunked host path (copy/compute overlap)
+  cudaEvent_t ev_a = nullptr, ev_b = nullptr;
   std::string err;
 };
 
@@ -360,25 +390,36 @@ struct PlayoutOp {
   }
 };
 
+// Packed SoA plane table of a game: {count, element bytes...}.
+struct PlaneOp {
+  int* bytes;
+  template <class G> int operator()() const {
+    for (int p = 0; p < G::kPlanes; ++p) bytes[p] = G::plane_bytes(p);
+    return G::kPlanes;
+  }
+};
+
 struct ObsOp2 {
   bsg_engine* e; const void* states; int64_t n; const uint8_t* players; float* obs; uint8_t* mask;
   cudaStream_t st;
+  template <class G, bool kMask> int launch(void* out) const {
+    static int blocks_per_sm = 0;
+    if (blocks_per_sm == 0) {
+      int b = 0;
+      BSG_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, expand_kernel<G, kMask>, kChunk, 0));
+      blocks_per_sm = b > 0 ? b : 1;
+    }
+    int64_t cap = (int64_t)e->sm_count * blocks_per_sm;
+    int64_t need = (n + kChunk - 1) / kChunk;
+    int grid = (int)(need < cap ? need : cap);
+    expand_kernel<G, kMask><<<grid < 1 ? 1 : grid, kChunk, 0, st>>>(states, n, players, out);
+    BSG_CUDA(e, cudaGetLastError());
+    return BSG_OK;
+  }
   template <class G> int operator()() const {
-    int64_t cap = (int64_t)e->sm_count * 8;
-    if (obs) {
-      int64_t total4 = (n * G::kObsSize + 3) / 4;
-      int64_t need = (total4 + kThreads - 1) / kThreads;
-      int grid = (int)(need < cap ? need : cap);
-      obs_kernel<G><<<grid < 1 ? 1 : grid, kThreads, 0, st>>>(states, n, players, obs);
-      BSG_CUDA(e, cudaGetLastError());
-    }
-    if (mask) {
-      int64_t total16 = (n * G::kNumActions + 15) / 16;
-      int64_t need = (total16 + kThreads - 1) / kThreads;
-      int grid = (int)(need < cap ? need : cap);
-      legal_mask_kernel<G><<<grid < 1 ? 1 : grid, kThreads, 0, st>>>(states, n, mask);
-      BSG_CUDA(e, cudaGetLastError());
-    }
+    int rc = BSG_OK;
+    if (obs && (rc = launch<G, false>(obs)) != BSG_OK) return rc;
+    if (mask && (rc = launch<G, true>(mask)) != BSG_OK) return rc;
     return BSG_OK;
   }
 };
@@ -449,6 +490,10 @@ int bsg_host_observation(int game, const void* p, int64_t cap, int64_t i, int pl
   if (!p || !out || i < 0 || i >= cap || player < 0 || player > 1) return BSG_ERR_BAD_ARG;
   return dispatch_game(game, ObsOp{p, cap, i, player, out});
 }
+int bsg_host_legal_mask(int game, const void* p, int64_t cap, int64_t i, uint8_t* out) {
+  if (!p || !out || i < 0 || i >= cap) return BSG_ERR_BAD_ARG;
+  return dispatch_game(game, MaskOp{p, cap, i, out});
+}
 int bsg_host_replay_step(int game, void* p, int64_t cap, int64_t i, uint32_t r, int64_t* action) {
   if (!p || i < 0 || i >= cap) return BSG_ERR_BAD_ARG;
   return dispatch_game(game, StepOp{p, cap, i, r, action});
@@ -478,6 +523,9 @@ int bsg_create(int game, int device, bsg_engine** out) {
   BSG_CUDA(e, cudaGetDeviceProperties(&prop, device));
   e->sm_count = prop.multiProcessorCount;
   BSG_CUDA(e, cudaStreamCreateWithFlags(&e->own_stream, cudaStreamNonBlocking));
+  BSG_CUDA(e, cudaStreamCreateWithFlags(&e->aux_stream, cudaStreamNonBlocking));
+  BSG_CUDA(e, cudaEventCreateWithFlags(&e->ev_a, cudaEventDisableTiming));
+  BSG_CUDA(e, cudaEventCreateWithFlags(&e->ev_b, cudaEventDisableTiming));
   BSG_CUDA(e, cudaMalloc(&e->d_totals, 4 * sizeof(uint64_t)));
   return dispatch_device_game(game, CreateOp{e});
 }
@@ -491,6 +539,9 @@ void bsg_destroy(bsg_engine* e) {
   if (e->h_pinned) cudaFreeHost(e->h_pinned);
   if (e->d_totals) cudaFree(e->d_totals);
   if (e->own_stream) cudaStreamDestroy(e->own_stream);
+  if (e->aux_stream) cudaStreamDestroy(e->aux_stream);
+  if (e->ev_a) cudaEventDestroy(e->ev_a);
+  if (e->ev_b) cudaEventDestroy(e->ev_b);
   delete e;
 }
 const char* bsg_last_error(bsg_engine* e) { return e ? e->err.c_str() : "null engine"; }
@@ -527,46 +578,86 @@ int bsg_observations(bsg_engine* e, const void* states, int64_t n, const uint8_t
   return dispatch_device_game(e->game, ObsOp2{e, states, n, players, obs, mask, (cudaStream_t)stream});
 }
 
+// Host-buffer playouts.  The roots are cut into chunks that ping-pong between two streams, so
+// the H2D copy of chunk i+1 overlaps the playout kernel of chunk i (the copy is the longer
+// leg: 16 B/root over PCIe against < 0.1 ns/root of kernel time).  Totals and per-root sums
+// accumulate with integer atomics, so the result does not depend on the chunking.
 int bsg_playouts_host(bsg_engine* e, const void* roots_host, int64_t n_roots, int32_t rollouts,
                       uint64_t seed, uint64_t first_playout, int64_t totals_out[4],
                       int32_t* root_ret_host, int32_t* root_steps_host) {
   if (!e) return BSG_ERR_BAD_ARG;
-  if (!roots_host || n_roots < 1 || !totals_out) return fail(e, BSG_ERR_BAD_ARG, "bad host playout arguments");
+  if (!roots_host || n_roots < 1 || rollouts < 1 || !totals_out)
+    return fail(e, BSG_ERR_BAD_ARG, "bad host playout arguments");
+  if (n_roots * (int64_t)rollouts >= (int64_t)1 << 32)
+    return fail(e, BSG_ERR_BAD_ARG, "more than 2^32-1 playouts in one call");
   BSG_CUDA(e, cudaSetDevice(e->device));
+  int plane_bytes[8];
+  const int n_planes = dispatch_device_game(e->game, PlaneOp{plane_bytes});
+  if (n_planes < 1) return fail(e, BSG_ERR_BAD_GAME, "no device kernels for this game");
   size_t in_bytes = (size_t)n_roots * (size_t)bsg_state_bytes(e->game);
   size_t out_elems = (root_ret_host ? n_roots : 0) + (root_steps_host ? n_roots : 0);
   int rc;
   if ((rc = ensure(e, &e->d_roots, &e->d_roots_bytes, in_bytes, false)) != BSG_OK) return rc;
   if ((rc = ensure(e, &e->d_out, &e->d_out_bytes, out_elems * 4 + 16, false)) != BSG_OK) return rc;
-  if ((rc = ensure(e, &e->h_pinned, &e->h_pinned_bytes, in_bytes + out_elems * 4 + 64, true)) != BSG_OK) return rc;
-  cudaStream_t st = e->own_stream;
   // Page-locked caller memory (e.g. a torch pin_memory() tensor) is copied from directly;
   // pageable memory is staged through the engine's pinned buffer.
   cudaPointerAttributes attr;
   bool pinned_src = cudaPointerGetAttributes(&attr, roots_host) == cudaSuccess &&
                     attr.type == cudaMemoryTypeHost;
   cudaGetLastError();
-  const void* src = roots_host;
-  if (!pinned_src) { memcpy(e->h_pinned, roots_host, in_bytes); src = e->h_pinned; }
-  BSG_CUDA(e, cudaMemcpyAsync(e->d_roots, src, in_bytes, cudaMemcpyHostToDevice, st));
-  BSG_CUDA(e, cudaMemsetAsync(e->d_totals, 0, 4 * sizeof(uint64_t), st));
-  if (out_elems) BSG_CUDA(e, cudaMemsetAsync(e->d_out, 0, out_elems * 4, st));
-  bsg_playout_io io;
-  memset(&io, 0, sizeof(io));
-  io.totals = e->d_totals;
+  size_t pin_need = (pinned_src ? 0 : in_bytes) + out_elems * 4 + 128;
+  if ((rc = ensure(e, &e->h_pinned, &e->h_pinned_bytes, pin_need, true)) != BSG_OK) return rc;
+  char* h_res = (char*)e->h_pinned;                      // {totals[4], root sums...}
+  const char* src = (const char*)roots_host;
+  if (!pinned_src) {
+    char* stage = h_res + ((out_elems * 4 + 32 + 63) & ~(size_t)63);
+    memcpy(stage, roots_host, in_bytes);
+    src = stage;
+  }
+  cudaStream_t sa = e->own_stream, sb = e->aux_stream;
+  BSG_CUDA(e, cudaMemsetAsync(e->d_totals, 0, 4 * sizeof(uint64_t), sa));
+  if (out_elems) BSG_CUDA(e, cudaMemsetAsync(e->d_out, 0, out_elems * 4, sa));
+  BSG_CUDA(e, cudaEventRecord(e->ev_a, sa));
+  BSG_CUDA(e, cudaStreamWaitEvent(sb, e->ev_a, 0));
   int32_t* d_ret = root_ret_host ? (int32_t*)e->d_out : nullptr;
   int32_t* d_steps = root_steps_host ? (int32_t*)e->d_out + (root_ret_host ? n_roots : 0) : nullptr;
-  io.root_sum_ret0 = d_ret;
-  io.root_sum_steps = d_steps;
-  if ((rc = bsg_playouts(e, e->d_roots, n_roots, rollouts, seed, first_playout, &io, st)) != BSG_OK) return rc;
-  char* hp = (char*)e->h_pinned + ((in_bytes + 15) & ~(size_t)15);
-  uint64_t* h_tot = (uint64_t*)hp;
-  BSG_CUDA(e, cudaMemcpyAsync(h_tot, e->d_totals, 32, cudaMemcpyDeviceToHost, st));
-  if (out_elems) BSG_CUDA(e, cudaMemcpyAsync(hp + 32, e->d_out, out_elems * 4, cudaMemcpyDeviceToHost, st));
-  BSG_CUDA(e, cudaStreamSynchronize(st));
+  // chunks of >= 2 MiB of roots, at most 16; a small call stays one chunk
+  int64_t n_chunks = (int64_t)(in_bytes >> 21);
+  n_chunks = n_chunks < 1 ? 1 : (n_chunks > 16 ? 16 : n_chunks);
+  PhiloxKeys keys;
+  philox_schedule(seed, keys);
+  for (int64_t c = 0; c < n_chunks; ++c) {
+    const int64_t lo = n_roots * c / n_chunks, hi = n_roots * (c + 1) / n_chunks;
+    if (hi <= lo) continue;
+    cudaStream_t st = (c & 1) ? sb : sa;
+    size_t plane_off = 0;
+    for (int p = 0; p < n_planes; ++p) {
+      size_t pb = (size_t)plane_bytes[p];
+      BSG_CUDA(e, cudaMemcpyAsync((char*)e->d_roots + plane_off + (size_t)lo * pb,
+                                  src + plane_off + (size_t)lo * pb, (size_t)(hi - lo) * pb,
+                                  cudaMemcpyHostToDevice, st));
+      plane_off += (size_t)n_roots * pb;
+    }
+    PlayoutArgs a;
+    memset(&a, 0, sizeof(a));
+    a.roots = e->d_roots; a.n_roots = n_roots; a.root0 = lo;
+    a.n_playouts = (uint32_t)((hi - lo) * rollouts); a.rollouts = (uint32_t)rollouts;
+    a.first_playout = first_playout + (uint64_t)lo * (uint64_t)rollouts;
+    a.keys = keys;
+    a.io.totals = e->d_totals;
+    a.io.root_sum_ret0 = d_ret ? d_ret + lo : nullptr;
+    a.io.root_sum_steps = d_steps ? d_steps + lo : nullptr;
+    if ((rc = dispatch_device_game(e->game, PlayoutOp{e, a, st})) != BSG_OK) return rc;
+  }
+  BSG_CUDA(e, cudaEventRecord(e->ev_b, sb));
+  BSG_CUDA(e, cudaStreamWaitEvent(sa, e->ev_b, 0));
+  uint64_t* h_tot = (uint64_t*)h_res;
+  BSG_CUDA(e, cudaMemcpyAsync(h_tot, e->d_totals, 32, cudaMemcpyDeviceToHost, sa));
+  if (out_elems) BSG_CUDA(e, cudaMemcpyAsync(h_res + 32, e->d_out, out_elems * 4, cudaMemcpyDeviceToHost, sa));
+  BSG_CUDA(e, cudaStreamSynchronize(sa));
   for (int i = 0; i < 4; ++i) totals_out[i] = (int64_t)h_tot[i];
-  if (root_ret_host) memcpy(root_ret_host, hp + 32, (size_t)n_roots * 4);
-  if (root_steps_host) memcpy(root_steps_host, hp + 32 + (root_ret_host ? (size_t)n_roots * 4 : 0), (size_t)n_roots * 4);
+  if (root_ret_host) memcpy(root_ret_host, h_res + 32, (size_t)n_roots * 4);
+  if (root_steps_host) memcpy(root_steps_host, h_res + 32 + (root_ret_host ? (size_t)n_roots * 4 : 0), (size_t)n_roots * 4);
   if (totals_out[3] != 0) return fail(e, BSG_ERR_STUCK_LANE, "non-terminal state without legal actions");
   return BSG_OK;
 }
@@ -600,7 +691,7 @@ int bsg_observations_host(bsg_engine* e, const void* states_host, int64_t n, con
 }
 
 int bsg_int_peak(bsg_engine* e, int kind, int iters, double* out) {
-  if (!e || !out || iters < 1 || kind < 0 || kind > 2) return BSG_ERR_BAD_ARG;
+  if (!e || !out || iters < 1 || kind < 0 || kind > 3) return BSG_ERR_BAD_ARG;
   BSG_CUDA(e, cudaSetDevice(e->device));
   int grid = e->sm_count * 8;
   cudaEvent_t a, b;
@@ -612,12 +703,13 @@ int bsg_int_peak(bsg_engine* e, int kind, int iters, double* out) {
     cudaEventRecord(a, e->own_stream);
     if (kind == 0) int_peak_kernel<0><<<grid, kThreads, 0, e->own_stream>>>(iters, sink);
     else if (kind == 1) int_peak_kernel<1><<<grid, kThreads, 0, e->own_stream>>>(iters, sink);
-    else int_peak_kernel<2><<<grid, kThreads, 0, e->own_stream>>>(iters, sink);
+    else if (kind == 2) int_peak_kernel<2><<<grid, kThreads, 0, e->own_stream>>>(iters, sink);
+    else int_peak_kernel<3><<<grid, kThreads, 0, e->own_stream>>>(iters, sink);
     cudaEventRecord(b, e->own_stream);
     BSG_CUDA(e, cudaEventSynchronize(b));
     float ms = 0;
     cudaEventElapsedTime(&ms, a, b);
-    double per_thread = (double)iters * 64.0 * (kind == 0 ? 2.0 : (kind == 1 ? 1.0 : 3.0));
+    double per_thread = (double)iters * 64.0 * (kind == 0 ? 2.0 : (kind == 1 ? 1.0 : (kind == 2 ? 3.0 : 2.0)));
     double rate = per_thread * (double)grid * kThreads / (ms * 1e-3);
     if (rep > 0 && rate > best) best = rate;
   }

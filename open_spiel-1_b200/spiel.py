@@ -154,10 +154,13 @@ class State:
     return out[:n].tolist()
 
   def legal_actions_mask(self, player=None):
-    mask = [0] * self._game.num_distinct_actions()
-    for a in self.legal_actions(player):
-      mask[a] = 1
-    return mask
+    cur, term, _ = self._info()
+    n = self._game.num_distinct_actions()
+    if term or (player is not None and player != cur):
+      return [0] * n
+    out = np.zeros(n, np.uint8)
+    C.check(C.lib.bsg_host_legal_mask(self._gid, self._packed.ctypes.data, 1, 0, out.ctypes.data))
+    return out.tolist()
 
   def apply_action(self, action):
     C.check(C.lib.bsg_host_apply_action(self._gid, self._packed.ctypes.data, 1, 0, int(action)))

@@ -241,3 +241,35 @@ def test_connect_four_full_size_properties(torch):
       acts += 1
     assert acts == g_len[i] and r0.value == g_ret[i]
   eng.close()
+
+
+@pytest.mark.parametrize("game,n", [("connect_four", 400000), ("breakthrough", 330000),
+                                    ("hex", 110000), ("tic_tac_toe", 1100000)])
+def test_host_buffer_chunked_path_equals_device_path(game, n, torch):
+  """bsg_playouts_host cuts large inputs into chunks on two streams (H2D overlapping the
+  kernel); totals and per-root sums must equal one device-buffer launch over the same roots,
+  for pinned and for pageable host memory, and for every SoA plane layout."""
+  from open_spiel_1_b200.roots import make_roots, ROOT_DEPTHS
+  eng = _engine(game)
+  dev = eng.torch_device
+  dmin, dmax = ROOT_DEPTHS[game]
+  states, _ = make_roots(eng, n, dmin, dmax, seed=77)
+  assert states.numel() >= 4 << 20                       # several chunks
+  R = 2
+  totals = torch.zeros(4, dtype=torch.int64, device=dev)
+  rr = torch.zeros(n, dtype=torch.int32, device=dev)
+  rs = torch.zeros(n, dtype=torch.int32, device=dev)
+  eng.playouts(states, n, R, seed=5, first_playout=123, root_sum_ret0=rr, root_sum_steps=rs,
+               totals=totals)
+  torch.cuda.synchronize()
+  want_t, want_r, want_s = totals.cpu().numpy(), rr.cpu().numpy(), rs.cpu().numpy()
+  assert want_t[0] == n * R and want_t[3] == 0
+  pageable = states.cpu().numpy()
+  pinned = torch.empty(states.numel(), dtype=torch.uint8, pin_memory=True)
+  pinned.copy_(states)
+  torch.cuda.synchronize()
+  for host in (pageable, pinned.numpy()):
+    t, r, s = eng.playouts_host(host, n, R, seed=5, first_playout=123, want_root_sums=True)
+    assert np.array_equal(t, want_t)
+    assert np.array_equal(r, want_r) and np.array_equal(s, want_s)
+  eng.close()
