@@ -33,6 +33,7 @@ struct TicTacToe {
   static constexpr int kObsWords = 1, kMaskWords = 1;
   static constexpr int kPlanes = 1;   // packed SoA planes and their element sizes
   BSG_HD static int plane_bytes(int p) { (void)p; return 4; }
+  static constexpr bool kCanStick = false;  // a non-terminal state always has a legal action
   struct State { u32 x, o, term, outc; };
   struct Tables { u32 modM[16]; };
   static void fill_tables(Tables& t) { for (u32 n = 0; n < 16; ++n) t.modM[n] = modM_entry(n); }
@@ -122,10 +123,10 @@ struct ConnectFour {
   static constexpr int kObsWords = 4, kMaskWords = 1;
   static constexpr int kPlanes = 1;
   BSG_HD static int plane_bytes(int p) { (void)p; return 16; }
+  static constexpr bool kCanStick = false;
   struct State {
     u64 cur, opp;  // stones of the player to move / of the other player
-    u32 h;         // column heights, 4 bits per column
-    u32 stones, mv, term, outc;
+    u32 mv, term, outc;
   };
   // lut[L] for the 7-bit mask L of non-full columns: .x = modM[popc L],
   // .y = k-th legal column (3 bits each, ascending) | popc(L) << 24.
@@ -139,7 +140,7 @@ struct ConnectFour {
     }
   }
   BSG_HD static void init(State& s) {
-    s.cur = 0; s.opp = 0; s.h = 0; s.stones = 0; s.mv = 0; s.term = 0; s.outc = kOutcomeNone;
+    s.cur = 0; s.opp = 0; s.mv = 0; s.term = 0; s.outc = kOutcomeNone;
   }
   BSG_HD static void load(State& s, const void* base, int64_t n, int64_t i) {
     (void)n;
@@ -154,12 +155,6 @@ struct ConnectFour {
     s.mv = meta & 1; s.term = (meta >> 1) & 1; s.outc = (meta >> 2) & 3;
     s.cur = s.mv ? o : x;
     s.opp = s.mv ? x : o;
-    u64 occ = x | o;
-    s.stones = (u32)popc64(occ);
-    u32 h = 0;
-#pragma unroll
-    for (int c = 0; c < 7; ++c) h |= (u32)popc64((occ >> c) & 0x010101010101ull) << (4 * c);
-    s.h = h;
   }
   BSG_HD static void store(const State& s, void* base, int64_t n, int64_t i) {
     (void)n;
@@ -184,13 +179,16 @@ struct ConnectFour {
     return acc != 0;
   }
   // connect_four.cc:93-106: drop into `col`, win tested before draw, then the turn passes.
+  // The landing cell is the lowest empty cell of the column: isolate the column's empties and
+  // take the lowest set bit (no per-column height counters to carry around).  The board is
+  // full exactly when the top row (bits 40..46) is.
   BSG_HD static void drop(State& s, int col) {
-    u32 row = (s.h >> (4 * col)) & 7u;
-    s.h += 1u << (4 * col);
-    u64 b = s.cur | (1ull << (row * 8 + col));
-    s.stones += 1;
+    u64 occ = s.cur | s.opp;
+    u64 empties = ~occ & (0x0000010101010101ull << col);
+    u64 bit = empties & (0ull - empties);
+    u64 b = s.cur | bit;
     bool win = has_line(b);
-    bool full = s.stones == 42;
+    bool full = ((u32)((occ | bit) >> 40) & 0x7Fu) == 0x7Fu;
     s.term = (win || full) ? 1u : 0u;
     s.outc = win ? s.mv : (full ? (u32)kOutcomeDraw : (u32)kOutcomeNone);
     s.cur = s.opp;
@@ -274,6 +272,7 @@ struct Breakthrough {
   static constexpr int kObsWords = 6, kMaskWords = 24;
   static constexpr int kPlanes = 2;
   BSG_HD static int plane_bytes(int p) { return p == 0 ? 16 : 4; }
+  static constexpr bool kCanStick = true;   // all pieces blocked is possible
   static constexpr u64 kCol0 = 0x0101010101010101ull, kCol7 = 0x8080808080808080ull;
   struct State { u64 own, opp; u32 mv, term, outc; };
   struct Tables { u32 modM[64]; };
@@ -463,6 +462,7 @@ struct HexT {
   static constexpr int kObsWords = (9 * N * N + 31) / 32, kMaskWords = 4;
   static constexpr int kPlanes = 4;
   BSG_HD static int plane_bytes(int p) { (void)p; return 16; }
+  static constexpr bool kCanStick = false;
   struct M128 { u32 w[4]; };
   struct State {
     u32 occ[4];                       // all stones; bits >= N*N are kept set (never legal)

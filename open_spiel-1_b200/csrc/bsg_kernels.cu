@@ -2,15 +2,14 @@
 //
 // Playout kernel design:
 //  * one playout per lane, whole game state in registers (per-game bitboards, bsg_games.cuh);
-//  * persistent CTAs: each CTA owns a contiguous slice of the launch's playouts and its lanes
-//    claim the next playout from a shared-memory counter when they finish (lane refill), so a
-//    warp keeps ~all lanes busy although game lengths differ;
+//  * persistent warps: each warp owns a contiguous slice of the launch's playouts and its lanes
+//    claim the next playout from a warp-uniform cursor with one ballot when they finish (lane
+//    refill; no atomics), so a warp keeps ~all lanes busy although game lengths differ;
 //  * steps run in groups of four: one Philox4x32-10 block (4 draws) per group, and lanes are
 //    refilled only at group boundaries, which keeps every lane's step index congruent to the
 //    group phase — the RNG and the refill code stay warp-convergent;
 //  * a step is unconditional straight-line code (finished lanes run dead steps on a dead
 //    state); only the bookkeeping is predicated.
-#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <stdio.h>
 
@@ -20,7 +19,6 @@
 
 #include "bsg_host.cuh"
 
-namespace cg = cooperative_groups;
 namespace bsg {
 
 constexpr int kThreads = 256;
@@ -40,74 +38,71 @@ template <class G, bool kFull>
 __global__ void __launch_bounds__(kThreads)
 playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab) {
   __shared__ typename G::Tables tab;
-  __shared__ unsigned int s_next;
   {
     const u32* src = reinterpret_cast<const u32*>(gtab);
     u32* dst = reinterpret_cast<u32*>(&tab);
     for (int i = threadIdx.x; i < (int)(sizeof(typename G::Tables) / 4); i += kThreads) dst[i] = src[i];
-    if (threadIdx.x == 0) s_next = 0;
   }
   __syncthreads();
 
-  // contiguous slice of this CTA
-  const u32 per = (a.n_playouts + gridDim.x - 1) / gridDim.x;
-  const u32 begin = min(per * blockIdx.x, a.n_playouts);
+  // contiguous slice of this WARP; its lanes claim playouts from a warp-uniform cursor with
+  // one ballot (no atomics, no shared memory), so the claim itself is convergent code
+  const u32 n_warps = gridDim.x * (kThreads / 32);
+  const u32 warp_id = blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
+  const u32 per = (a.n_playouts + n_warps - 1) / n_warps;
+  const u32 begin = min(per * warp_id, a.n_playouts);
   const u32 count = min(per, a.n_playouts - begin);
+  const u32 lane_lt = (1u << (threadIdx.x & 31)) - 1u;
+  u32 cursor = 0;
 
   typename G::State s;
   G::init(s);
   typename G::State prev;
   if (kFull) G::init(prev);
-  bool active = false, have = false, exhausted = false;
+  bool active = false, have = false;
   u32 lid = 0, t = 0, limit = 0xFFFFFFFFu;
-  u32 fin_len = 0, fin_term = 0;
-  int fin_ret = 0;
-  unsigned long long my_steps = 0;
-  long long my_ret = 0;
-  u32 my_done = 0, my_stuck = 0;
+  u32 fin_term = 0, fin_outc = kOutcomeNone;
+  u32 my_steps = 0, my_done = 0, my_stuck = 0;
+  int my_ret = 0;
 
   for (;;) {
-    if (!active) {
-      if (have) {  // publish the finished playout
-        have = false;
-        if (a.io.ret0) a.io.ret0[lid] = (int8_t)fin_ret;
-        if (a.io.length) a.io.length[lid] = (uint8_t)fin_len;
+    const bool need = !active;
+    const u32 want = __ballot_sync(0xFFFFFFFFu, need);
+    if (need) {
+      if (have) {  // publish the finished playout (t froze at its length)
+        const int ret = outcome_ret0((int)fin_outc);
+        if (a.io.ret0) a.io.ret0[lid] = (int8_t)ret;
+        if (a.io.length) a.io.length[lid] = (uint8_t)t;
         if (a.io.terminal) a.io.terminal[lid] = (uint8_t)fin_term;
         if (a.io.root_sum_ret0 || a.io.root_sum_steps) {
           u32 root = a.rollouts == 1 ? lid : lid / a.rollouts;
-          if (a.io.root_sum_ret0 && fin_ret != 0) atomicAdd(a.io.root_sum_ret0 + root, fin_ret);
-          if (a.io.root_sum_steps) atomicAdd(a.io.root_sum_steps + root, (int)fin_len);
+          if (a.io.root_sum_ret0 && ret != 0) atomicAdd(a.io.root_sum_ret0 + root, ret);
+          if (a.io.root_sum_steps) atomicAdd(a.io.root_sum_steps + root, (int)t);
         }
-        my_steps += fin_len;
-        my_ret += fin_ret;
+        my_steps += t;
+        my_ret += ret;
         my_done += 1;
       }
-      if (!exhausted) {  // claim the next playout of this CTA's slice
-        cg::coalesced_group grp = cg::coalesced_threads();
-        u32 base = 0;
-        if (grp.thread_rank() == 0) base = atomicAdd(&s_next, grp.size());
-        u32 idx = grp.shfl(base, 0) + grp.thread_rank();
-        if (idx < count) {
-          lid = begin + idx;
-          u32 root = a.rollouts == 1 ? lid : lid / a.rollouts;
-          G::load(s, a.roots, a.n_roots, a.root0 + root);
-          t = 0;
-          have = true;
-          if (kFull) {
-            limit = a.io.max_steps > 0 ? (u32)a.io.max_steps : 0xFFFFFFFFu;
-            if (a.io.step_limit) limit = min(limit, (u32)a.io.step_limit[lid]);
-            prev = s;
-          }
-          active = !G::terminal(s) && (!kFull || limit > 0);
-          fin_len = 0;
-          fin_term = G::terminal(s) ? 1u : 0u;
-          fin_ret = outcome_ret0(G::outcome(s));
-          if (kFull && !active && a.io.final_states) G::store(s, a.io.final_states, a.n_playouts, lid);
-        } else {
-          exhausted = true;
+      const u32 idx = cursor + __popc(want & lane_lt);
+      have = idx < count;
+      if (have) {  // claim the next playout of the slice
+        lid = begin + idx;
+        u32 root = a.rollouts == 1 ? lid : lid / a.rollouts;
+        G::load(s, a.roots, a.n_roots, a.root0 + root);
+        t = 0;
+        if (kFull) {
+          limit = a.io.max_steps > 0 ? (u32)a.io.max_steps : 0xFFFFFFFFu;
+          if (a.io.step_limit) limit = min(limit, (u32)a.io.step_limit[lid]);
+          prev = s;
         }
+        const bool term = G::terminal(s);
+        active = !term && (!kFull || limit > 0);
+        fin_term = term ? 1u : 0u;
+        fin_outc = (u32)G::outcome(s);
+        if (kFull && !active && a.io.final_states) G::store(s, a.io.final_states, a.n_playouts, lid);
       }
     }
+    cursor += __popc(want);
     if (!__any_sync(0xFFFFFFFFu, active)) {
       if (!__any_sync(0xFFFFFFFFu, have)) break;
       continue;
@@ -125,37 +120,42 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
       }
       int action;
       const u32 nlegal = G::step(s, r, tab, action);
-      if (active && nlegal == 0) {  // non-terminal state without a legal action
+      if (G::kCanStick && active && nlegal == 0) {  // non-terminal state without a legal action
         active = false;
         my_stuck += 1;
-        fin_len = t;
         fin_term = 0;
-        fin_ret = 0;
+        fin_outc = kOutcomeNone;
         if (kFull && a.io.final_states) G::store(prev, a.io.final_states, a.n_playouts, lid);
       }
-      if (active) {
-        if (kFull && a.io.actions && t < (u32)a.io.actions_stride)
-          a.io.actions[(size_t)lid * a.io.actions_stride + t] = (int16_t)action;
-        t += 1;
-        bool term = G::terminal(s);
-        if (term || (kFull && t >= limit)) {
-          active = false;
-          fin_len = t;
-          fin_term = term ? 1u : 0u;
-          fin_ret = outcome_ret0(G::outcome(s));
-          if (kFull && a.io.final_states) {
-            if (term && a.io.final_before_terminal) G::store(prev, a.io.final_states, a.n_playouts, lid);
-            else G::store(s, a.io.final_states, a.n_playouts, lid);
+      if (kFull) {
+        if (active) {
+          if (a.io.actions && t < (u32)a.io.actions_stride)
+            a.io.actions[(size_t)lid * a.io.actions_stride + t] = (int16_t)action;
+          t += 1;
+          const bool term = G::terminal(s);
+          if (term || t >= limit) {
+            active = false;
+            fin_term = term ? 1u : 0u;
+            fin_outc = (u32)G::outcome(s);
+            if (a.io.final_states) {
+              if (term && a.io.final_before_terminal) G::store(prev, a.io.final_states, a.n_playouts, lid);
+              else G::store(s, a.io.final_states, a.n_playouts, lid);
+            }
           }
         }
+      } else {
+        // lean bookkeeping: t counts the moves of the live playout and freezes when it ends
+        const bool term = G::terminal(s);
+        t += active ? 1u : 0u;
+        if (active && term) { fin_term = 1u; fin_outc = (u32)G::outcome(s); }
+        active = active && !term;
       }
     }
   }
 
   if (a.io.totals) {
-    unsigned long long st = my_steps;
-    long long rt = my_ret;
-    u32 dn = my_done, sk = my_stuck;
+    u32 st = my_steps, dn = my_done, sk = my_stuck;
+    int rt = my_ret;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       st += __shfl_xor_sync(0xFFFFFFFFu, st, o);
@@ -165,8 +165,8 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
     }
     if ((threadIdx.x & 31) == 0) {
       atomicAdd((unsigned long long*)a.io.totals + 0, (unsigned long long)dn);
-      atomicAdd((unsigned long long*)a.io.totals + 1, st);
-      atomicAdd((unsigned long long*)a.io.totals + 2, (unsigned long long)rt);
+      atomicAdd((unsigned long long*)a.io.totals + 1, (unsigned long long)st);
+      atomicAdd((unsigned long long*)a.io.totals + 2, (unsigned long long)(long long)rt);
       if (sk) atomicAdd((unsigned long long*)a.io.totals + 3, (unsigned long long)sk);
     }
   }
