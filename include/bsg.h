@@ -155,7 +155,8 @@ int bsg_observations_host(bsg_engine* e, const void* states_host, int64_t n,
 /* Integer-issue microbenchmark used for the roofline denominator (bench.py): runs `iters`
  * dependent-chain iterations of `ilp` independent 32-bit ops per thread on every SM and
  * returns thread-instructions per second.  kind: 0 = LOP3/IADD3 mix (ALU pipe), 1 = IMAD
- * (FMA pipe), 2 = SHF + LOP3 + IMAD (2 ALU : 1 FMA), 3 = LOP3 + IMAD (1 : 1, both pipes busy). */
+ * (FMA pipe), 2 = SHF + LOP3 + IMAD (2 ALU : 1 FMA), 3 = LOP3 + IMAD (1 : 1, both pipes busy), 4 = IMAD.HI, 5 = IMAD.WIDE + LOP3,
+ * 6 = LOP3 + IMAD.HI (1 : 1). */
 int bsg_int_peak(bsg_engine* e, int kind, int iters, double* thread_instr_per_s);
 
 #ifdef __cplusplus

@@ -282,6 +282,7 @@ __global__ void __launch_bounds__(kThreads) int_peak_kernel(int iters, u32* sink
 #pragma unroll
   for (int i = 0; i < 8; ++i) x[i] = threadIdx.x * 2654435761u + i * 40503u + blockIdx.x;
   u32 k = blockIdx.x | 1u;
+  const u32 sh = 0x02000000u << (iters & 1);  // opaque to ptxas: keeps mul.hi an IMAD.HI
   for (int it = 0; it < iters; ++it) {
 #pragma unroll
     for (int rep = 0; rep < 8; ++rep) {
@@ -290,7 +291,17 @@ __global__ void __launch_bounds__(kThreads) int_peak_kernel(int iters, u32* sink
         if (KIND == 0) x[i] = (x[i] ^ k) + (x[(i + 1) & 7] & 0x55555555u) ;          // LOP3 + IADD3
         else if (KIND == 1) x[i] = x[i] * 0x9E3779B1u + k;                             // IMAD
         else if (KIND == 2) { x[i] = (x[i] ^ (x[(i + 3) & 7] >> 3)); x[i] = x[i] * 0x9E3779B1u + k; } // SHF/LOP + IMAD
-        else { x[i] = (x[i] ^ x[(i + 3) & 7]) * 0x9E3779B1u + k; }                      // LOP3 + IMAD, 1:1
+        else if (KIND == 3) { x[i] = (x[i] ^ x[(i + 3) & 7]) * 0x9E3779B1u + k; }       // LOP3 + IMAD, 1:1
+        else if (KIND == 4) { asm("mul.hi.u32 %0, %0, %1;" : "+r"(x[i]) : "r"(0x9E3779B1u)); x[i] |= 0x80000000u; }  // IMAD.HI (+1 LOP3 keeps the chain alive; counted)
+        else if (KIND == 5) {                                                            // IMAD.WIDE + LOP3
+          unsigned long long w;
+          asm("mul.wide.u32 %0, %1, %2;" : "=l"(w) : "r"(x[i]), "r"(0x9E3779B1u));
+          x[i] = (u32)w ^ (u32)(w >> 32) ^ k;
+        } else {                                                                         // LOP3 + IMAD.HI (power-of-two multiplier from a register = a right shift)
+          u32 y = x[i] ^ x[(i + 3) & 7] ^ k;
+          asm("mul.hi.u32 %0, %1, %2;" : "=r"(x[i]) : "r"(y), "r"(sh));
+          x[i] ^= y;
+        }
       }
     }
   }
@@ -691,7 +702,7 @@ int bsg_observations_host(bsg_engine* e, const void* states_host, int64_t n, con
 }
 
 int bsg_int_peak(bsg_engine* e, int kind, int iters, double* out) {
-  if (!e || !out || iters < 1 || kind < 0 || kind > 3) return BSG_ERR_BAD_ARG;
+  if (!e || !out || iters < 1 || kind < 0 || kind > 6) return BSG_ERR_BAD_ARG;
   BSG_CUDA(e, cudaSetDevice(e->device));
   int grid = e->sm_count * 8;
   cudaEvent_t a, b;
@@ -704,12 +715,15 @@ int bsg_int_peak(bsg_engine* e, int kind, int iters, double* out) {
     if (kind == 0) int_peak_kernel<0><<<grid, kThreads, 0, e->own_stream>>>(iters, sink);
     else if (kind == 1) int_peak_kernel<1><<<grid, kThreads, 0, e->own_stream>>>(iters, sink);
     else if (kind == 2) int_peak_kernel<2><<<grid, kThreads, 0, e->own_stream>>>(iters, sink);
-    else int_peak_kernel<3><<<grid, kThreads, 0, e->own_stream>>>(iters, sink);
+    else if (kind == 3) int_peak_kernel<3><<<grid, kThreads, 0, e->own_stream>>>(iters, sink);
+    else if (kind == 4) int_peak_kernel<4><<<grid, kThreads, 0, e->own_stream>>>(iters, sink);
+    else if (kind == 5) int_peak_kernel<5><<<grid, kThreads, 0, e->own_stream>>>(iters, sink);
+    else int_peak_kernel<6><<<grid, kThreads, 0, e->own_stream>>>(iters, sink);
     cudaEventRecord(b, e->own_stream);
     BSG_CUDA(e, cudaEventSynchronize(b));
     float ms = 0;
     cudaEventElapsedTime(&ms, a, b);
-    double per_thread = (double)iters * 64.0 * (kind == 0 ? 2.0 : (kind == 1 ? 1.0 : (kind == 2 ? 3.0 : 2.0)));
+    double per_thread = (double)iters * 64.0 * (kind == 0 ? 2.0 : (kind == 1 ? 1.0 : (kind == 2 ? 3.0 : (kind == 6 ? 4.0 : 2.0))));
     double rate = per_thread * (double)grid * kThreads / (ms * 1e-3);
     if (rep > 0 && rate > best) best = rate;
   }
