@@ -30,6 +30,13 @@ BSG_HD int popc64(u64 x) {
   return __builtin_popcountll(x);
 #endif
 }
+BSG_HD int ctz64(u64 x) {  // index of the lowest set bit; 64 for x = 0
+#if defined(__CUDA_ARCH__)
+  return x ? __ffsll((long long)x) - 1 : 64;
+#else
+  return x ? __builtin_ctzll(x) : 64;
+#endif
+}
 BSG_HD u32 umulhi32(u32 a, u32 b) {
 #if defined(__CUDA_ARCH__)
   return __umulhi(a, b);

@@ -5,7 +5,9 @@
 //   State                      registers-only state
 //   Tables / fill_tables       small lookup tables (shared memory on the device)
 //   init, load, store          initial position; packed SoA HBM layout <-> State
-//   terminal, outcome, mover   status
+//   terminal, outcome, mover   status; won(s) = the game ended with a win of the LAST mover (in all
+//                              four games a win is always the mover's: the kernels record only
+//                              this flag and the length, the winner follows from the parity)
 //   n = step(s, r, tab, action) one playout step: a = legal[r mod n] in ascending action-id
 //                              order, apply it, update terminal/outcome.  Branch-free enough
 //                              to be run on finished lanes as a dead step (never traps).
@@ -50,6 +52,7 @@ struct TicTacToe {
   }
   BSG_HD static bool terminal(const State& s) { return s.term != 0; }
   BSG_HD static int outcome(const State& s) { return (int)s.outc; }
+  BSG_HD static bool won(const State& s) { return s.outc < 2u; }  // the last mover won
   BSG_HD static int mover(const State& s) { return (popc32(s.x) + popc32(s.o)) & 1; }
 
   // tic_tac_toe.cc:108-118, the eight lines, as shifts over one 9-bit mask.
@@ -113,100 +116,123 @@ struct TicTacToe {
 // connect_four — reference: open_spiel/games/connect_four.cc
 //   6 rows x 7 cols, row 0 at the bottom (connect_four.cc:77-83).  Bit = row * 8 + col: one
 //   guard column per row keeps horizontal/diagonal shifts from wrapping, and the top row
-//   (bits 40..46) gives the 7-bit "column not full" mask with one shift.
-//   packed: 16 B = { x stones (player 0), o stones | meta << 48 };
-//   meta = mover | terminal << 1 | outcome << 2.
+//   (bits 40..46) gives the 7-bit "column not full" mask with one shift.  Rows 0-3 live in the
+//   low 32-bit word, rows 4-5 in the low half of the high word.
+//   packed: ONE u64 per state (8 B — the host->device copy of the roots is the end-to-end
+//   bound of this path, so the root format is as small as a position gets):
+//     bits 0..54   stones of the player to move | one marker bit per column at (height, col)
+//                  (everything below a marker is occupied, so the whole position decodes with
+//                  three shift-ors: smear the markers down, shift one row down = occupancy);
+//     bits 56..61  stones on the board (0..42; parity = player to move, x = player 0 first);
+//     bit  62      the last move made four in a row (terminal by win).
 // =========================================================================================
 struct ConnectFour {
   static constexpr int kId = kGameConnectFour;
-  static constexpr int kNumActions = 7, kMaxLen = 42, kObsSize = 126, kStateBytes = 16;
+  static constexpr int kNumActions = 7, kMaxLen = 42, kObsSize = 126, kStateBytes = 8;
   static constexpr int kObsWords = 4, kMaskWords = 1;
   static constexpr int kPlanes = 1;
-  BSG_HD static int plane_bytes(int p) { (void)p; return 16; }
+  BSG_HD static int plane_bytes(int p) { (void)p; return 8; }
   static constexpr bool kCanStick = false;
   struct State {
     u64 cur, opp;  // stones of the player to move / of the other player
-    u32 mv, term, outc;
+    u32 left;      // empty cells; 42 - left stones on the board, parity = player to move
+    u32 win;       // the last move completed a line
   };
-  // lut[L] for the 7-bit mask L of non-full columns: .x = modM[popc L],
-  // .y = k-th legal column (3 bits each, ascending) | popc(L) << 24.
-  struct Tables { u32 lut[128][2]; };
+  // One 72-byte row per 7-bit mask L of non-full columns (connect_four.cc:108-116):
+  //   word 0 = floor(2^32 / n), word 1 = -n (n = popc L: the fast-modulo constants),
+  //   words 2.. = for k < n the 64-bit cell mask of the k-th open column, ascending.
+  // 18 words per row: rows of different L start in different shared-memory banks.
+  static constexpr int kRowWords = 18;
+  struct Tables { u32 row[128][kRowWords]; };
+  static constexpr u64 kColumn = 0x0000010101010101ull;  // the six cells of column 0
   static void fill_tables(Tables& t) {
     for (u32 L = 0; L < 128; ++L) {
-      u32 cols = 0, n = 0;
-      for (u32 c = 0; c < 7; ++c) if ((L >> c) & 1) { cols |= c << (3 * n); ++n; }
-      t.lut[L][0] = modM_entry(n);
-      t.lut[L][1] = cols | (n << 24);
+      u32 n = 0;
+      for (int w = 0; w < kRowWords; ++w) t.row[L][w] = 0;
+      for (u32 c = 0; c < 7; ++c)
+        if ((L >> c) & 1) {
+          u64 m = kColumn << c;
+          t.row[L][2 + 2 * n] = (u32)m;
+          t.row[L][3 + 2 * n] = (u32)(m >> 32);
+          ++n;
+        }
+      // L = 0 only happens on finished lanes running dead steps: n = 1 keeps k = 0 and the
+      // empty column mask places nothing.
+      u32 nn = n ? n : 1;
+      t.row[L][0] = modM_entry(nn);
+      t.row[L][1] = 0u - nn;
     }
   }
-  BSG_HD static void init(State& s) {
-    s.cur = 0; s.opp = 0; s.mv = 0; s.term = 0; s.outc = kOutcomeNone;
-  }
+  BSG_HD static void init(State& s) { s.cur = 0; s.opp = 0; s.left = 42; s.win = 0; }
   BSG_HD static void load(State& s, const void* base, int64_t n, int64_t i) {
     (void)n;
-#if defined(__CUDA_ARCH__)
-    ulonglong2 w = ((const ulonglong2*)base)[i];
-    u64 x = w.x, o = w.y;
-#else
-    u64 x = ((const u64*)base)[2 * i], o = ((const u64*)base)[2 * i + 1];
-#endif
-    u32 meta = (u32)(o >> 48);
-    o &= 0xFFFFFFFFFFFFull;
-    s.mv = meta & 1; s.term = (meta >> 1) & 1; s.outc = (meta >> 2) & 3;
-    s.cur = s.mv ? o : x;
-    s.opp = s.mv ? x : o;
+    u64 w = ((const u64*)base)[i];
+    u32 meta = (u32)(w >> 56);
+    u64 key = w & 0x00FFFFFFFFFFFFFFull;
+    u64 sm = key;             // smear every marker (and stone) down its column
+    sm |= sm >> 8;
+    sm |= sm >> 16;
+    sm |= sm >> 32;
+    u64 occ = sm >> 8;        // strictly below the markers
+    s.cur = key & occ;
+    s.opp = occ & ~key;
+    s.left = 42u - (meta & 63u);
+    s.win = (meta >> 6) & 1u;
   }
   BSG_HD static void store(const State& s, void* base, int64_t n, int64_t i) {
     (void)n;
-    u64 x = s.mv ? s.opp : s.cur, o = s.mv ? s.cur : s.opp;
-    u64 meta = (u64)(s.mv | (s.term << 1) | (s.outc << 2));
-    ((u64*)base)[2 * i] = x;
-    ((u64*)base)[2 * i + 1] = o | (meta << 48);
+    u64 occ = s.cur | s.opp, markers = 0;
+    for (int c = 0; c < 7; ++c) {
+      u64 e = ~occ & (0x0001010101010101ull << c);   // 7 rows: a full column marks row 6
+      markers |= e & (0ull - e);
+    }
+    u64 meta = (u64)((42u - s.left) | (s.win << 6));
+    ((u64*)base)[i] = s.cur | markers | (meta << 56);
   }
-  BSG_HD static bool terminal(const State& s) { return s.term != 0; }
-  BSG_HD static int outcome(const State& s) { return (int)s.outc; }
-  BSG_HD static int mover(const State& s) { return (int)s.mv; }
+  BSG_HD static bool terminal(const State& s) { return (s.win != 0) || (s.left == 0); }
+  BSG_HD static bool won(const State& s) { return s.win != 0; }
+  BSG_HD static int mover(const State& s) { return (int)(s.left & 1u); }  // 42 is even
+  BSG_HD static int outcome(const State& s) {
+    return s.win ? (mover(s) ^ 1) : (s.left == 0 ? kOutcomeDraw : kOutcomeNone);
+  }
 
-  // Four-in-a-row anywhere on one player's board: the reference scans every cell in the four
-  // line directions (connect_four.cc:123-152); bit-parallel that is m = b & (b >> d),
-  // m & (m >> 2d) for d = 1 (row), 8 (column), 7 and 9 (diagonals).
+  // Four-in-a-row anywhere on one player's board.  The reference scans every cell in four
+  // directions (connect_four.cc:123-152); bit-parallel that is b & b>>d & b>>2d & b>>3d.
+  // Rows: d = 1, per 32-bit word (rows do not straddle words), with left shifts (they can run
+  // on the multiplier pipe).  Columns and diagonals (d = 8, 7, 9): the lowest cell of such a
+  // line is in rows 0..2, so only the LOW word of the product is needed — three funnel
+  // shifts of (hi:lo) and two ANDs per direction.
   BSG_HD static bool has_line(u64 b) {
-    u64 acc = 0, m;
-    m = b & (b >> 1); acc |= m & (m >> 2);
-    m = b & (b >> 8); acc |= m & (m >> 16);
-    m = b & (b >> 7); acc |= m & (m >> 14);
-    m = b & (b >> 9); acc |= m & (m >> 18);
+    u32 lo = (u32)b, hi = (u32)(b >> 32);
+    u32 ml = lo & (lo << 1), mh = hi & (hi << 1);
+    u32 acc = (ml & (ml << 2)) | (mh & (mh << 2));
+    acc |= lo & fshr(lo, hi, 8) & fshr(lo, hi, 16) & fshr(lo, hi, 24);
+    acc |= lo & fshr(lo, hi, 7) & fshr(lo, hi, 14) & fshr(lo, hi, 21);
+    acc |= lo & fshr(lo, hi, 9) & fshr(lo, hi, 18) & fshr(lo, hi, 27);
     return acc != 0;
   }
-  // connect_four.cc:93-106: drop into `col`, win tested before draw, then the turn passes.
-  // The landing cell is the lowest empty cell of the column: isolate the column's empties and
-  // take the lowest set bit (no per-column height counters to carry around).  The board is
-  // full exactly when the top row (bits 40..46) is.
-  BSG_HD static void drop(State& s, int col) {
-    u64 occ = s.cur | s.opp;
-    u64 empties = ~occ & (0x0000010101010101ull << col);
-    u64 bit = empties & (0ull - empties);
-    u64 b = s.cur | bit;
-    bool win = has_line(b);
-    bool full = ((u32)((occ | bit) >> 40) & 0x7Fu) == 0x7Fu;
-    s.term = (win || full) ? 1u : 0u;
-    s.outc = win ? s.mv : (full ? (u32)kOutcomeDraw : (u32)kOutcomeNone);
+  // connect_four.cc:93-106: the stone lands on the lowest empty cell of the column (lowest
+  // set bit of the column's empties), win tested before draw, then the turn passes.
+  BSG_HD static void drop_mask(State& s, u64 column) {
+    u64 e = column & ~(s.cur | s.opp);
+    u64 b = s.cur | (e & (0ull - e));
+    s.win = has_line(b) ? 1u : 0u;
     s.cur = s.opp;
     s.opp = b;
-    s.mv ^= 1u;
+    s.left -= 1u;
   }
   BSG_HD static u32 open_columns(const State& s) {
     return ~(u32)((s.cur | s.opp) >> 40) & 0x7Fu;  // connect_four.cc:108-116
   }
   BSG_HD static u32 step(State& s, u32 r, const Tables& tab, int& action) {
-    u32 L = open_columns(s);
-    u32 M = tab.lut[L][0], e = tab.lut[L][1];
-    u32 n = e >> 24;
-    u32 k = fastmod(r, n, M) & 7u;
-    int col = (int)((e >> (3 * k)) & 7u);
-    action = col;
-    drop(s, col);
-    return n;
+    const u32* row = tab.row[open_columns(s)];
+    u32 negn = row[1];
+    u32 rem = umulhi32(r, row[0]) * negn + r;       // r - floor-ish(r / n) * n, in [0, 2n)
+    u32 k = umin32(rem, rem + negn);                // r mod n
+    u64 column = (u64)row[2 + 2 * k] | ((u64)row[3 + 2 * k] << 32);
+    action = ctz64(column);                          // column index = lowest bit (row 0 cell)
+    drop_mask(s, column);
+    return 0u - negn;
   }
   BSG_HD static int legal(const State& s, int* out) {
     if (terminal(s)) return 0;
@@ -217,19 +243,19 @@ struct ConnectFour {
   }
   BSG_HD static bool apply(State& s, int a) {
     if (terminal(s) || a < 0 || a >= 7 || !((open_columns(s) >> a) & 1)) return false;
-    drop(s, a);
+    drop_mask(s, kColumn << a);
     return true;
   }
   BSG_HD static u32 legal_bit(const State& s, int a) {
-    return (!s.term && ((open_columns(s) >> a) & 1u)) ? 1u : 0u;
+    return (!terminal(s) && ((open_columns(s) >> a) & 1u)) ? 1u : 0u;
   }
   // connect_four.cc:198-221: plane 0 = observer's opponent, 1 = observer's own, 2 = empty;
   // element order plane * 42 + row * 7 + col.
   BSG_HD static u32 obs_bit(const State& s, int player, int idx) {
     int plane = idx / 42, cell = idx - plane * 42;
     int row = cell / 7, col = cell - row * 7;
-    u64 mine = (player == (int)s.mv) ? s.cur : s.opp;
-    u64 theirs = (player == (int)s.mv) ? s.opp : s.cur;
+    u64 mine = (player == mover(s)) ? s.cur : s.opp;
+    u64 theirs = (player == mover(s)) ? s.opp : s.cur;
     u64 m = plane == 0 ? theirs : (plane == 1 ? mine : ~(mine | theirs));
     return (u32)(m >> (row * 8 + col)) & 1u;
   }
@@ -241,15 +267,15 @@ struct ConnectFour {
     return r;
   }
   BSG_HD static void obs_words(const State& s, int player, u32* out) {
-    u64 mine = squeeze((player == (int)s.mv) ? s.cur : s.opp);
-    u64 theirs = squeeze((player == (int)s.mv) ? s.opp : s.cur);
+    u64 mine = squeeze((player == mover(s)) ? s.cur : s.opp);
+    u64 theirs = squeeze((player == mover(s)) ? s.opp : s.cur);
     u64 empty = ~(mine | theirs) & 0x3FFFFFFFFFFull;
     u64 lo = theirs | (mine << 42);               // plane 0 at bit 0, plane 1 at bit 42
     u64 hi = (mine >> 22) | (empty << 20);        // plane 2 at bit 84
     out[0] = (u32)lo; out[1] = (u32)(lo >> 32); out[2] = (u32)hi; out[3] = (u32)(hi >> 32);
   }
   BSG_HD static void mask_words(const State& s, u32* out) {
-    out[0] = s.term ? 0u : open_columns(s);
+    out[0] = terminal(s) ? 0u : open_columns(s);
   }
 };
 
@@ -301,6 +327,7 @@ struct Breakthrough {
   }
   BSG_HD static bool terminal(const State& s) { return s.term != 0; }
   BSG_HD static int outcome(const State& s) { return (int)s.outc; }
+  BSG_HD static bool won(const State& s) { return s.outc < 2u; }  // the last mover won
   BSG_HD static int mover(const State& s) { return (int)s.mv; }
 
   BSG_HD static u64 rotr64(u64 x, int sh) { return (x >> sh) | (x << ((64 - sh) & 63)); }
@@ -558,6 +585,7 @@ struct HexT {
   }
   BSG_HD static bool terminal(const State& s) { return s.term != 0; }
   BSG_HD static int outcome(const State& s) { return (int)s.outc; }
+  BSG_HD static bool won(const State& s) { return s.outc < 2u; }  // the last mover won
   BSG_HD static int mover(const State& s) { return (int)s.mv; }
 
   // One ring of neighbours of every cell in f (hex.cc:206-222 for a whole set at once).

@@ -37,7 +37,7 @@ struct PlayoutArgs {
 template <class G, bool kFull>
 __global__ void __launch_bounds__(kThreads)
 playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab) {
-  __shared__ typename G::Tables tab;
+  __shared__ __align__(16) typename G::Tables tab;
   {
     const u32* src = reinterpret_cast<const u32*>(gtab);
     u32* dst = reinterpret_cast<u32*>(&tab);
@@ -59,9 +59,11 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
   G::init(s);
   typename G::State prev;
   if (kFull) G::init(prev);
-  bool active = false, have = false;
-  u32 lid = 0, t = 0, limit = 0xFFFFFFFFu;
-  u32 fin_term = 0, fin_outc = kOutcomeNone;
+  // Per playout the kernel records only: its length t (frozen when it ends), whether it ended
+  // in a terminal state (fin_term) and whether that was a win (fin_win).  A win is always the
+  // last mover's, so the winner follows from the root's mover and the parity of t.
+  bool active = false, have = false, fin_term = false, fin_win = false;
+  u32 lid = 0, t = 0, limit = 0xFFFFFFFFu, root_mv = 0;
   u32 my_steps = 0, my_done = 0, my_stuck = 0;
   int my_ret = 0;
 
@@ -69,11 +71,11 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
     const bool need = !active;
     const u32 want = __ballot_sync(0xFFFFFFFFu, need);
     if (need) {
-      if (have) {  // publish the finished playout (t froze at its length)
-        const int ret = outcome_ret0((int)fin_outc);
+      if (have) {  // publish the finished playout
+        const int ret = (fin_term && fin_win) ? (((root_mv ^ t) & 1u) ? 1 : -1) : 0;
         if (a.io.ret0) a.io.ret0[lid] = (int8_t)ret;
         if (a.io.length) a.io.length[lid] = (uint8_t)t;
-        if (a.io.terminal) a.io.terminal[lid] = (uint8_t)fin_term;
+        if (a.io.terminal) a.io.terminal[lid] = (uint8_t)(fin_term ? 1 : 0);
         if (a.io.root_sum_ret0 || a.io.root_sum_steps) {
           u32 root = a.rollouts == 1 ? lid : lid / a.rollouts;
           if (a.io.root_sum_ret0 && ret != 0) atomicAdd(a.io.root_sum_ret0 + root, ret);
@@ -90,6 +92,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         u32 root = a.rollouts == 1 ? lid : lid / a.rollouts;
         G::load(s, a.roots, a.n_roots, a.root0 + root);
         t = 0;
+        root_mv = (u32)G::mover(s);
         if (kFull) {
           limit = a.io.max_steps > 0 ? (u32)a.io.max_steps : 0xFFFFFFFFu;
           if (a.io.step_limit) limit = min(limit, (u32)a.io.step_limit[lid]);
@@ -97,8 +100,8 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         }
         const bool term = G::terminal(s);
         active = !term && (!kFull || limit > 0);
-        fin_term = term ? 1u : 0u;
-        fin_outc = (u32)G::outcome(s);
+        fin_term = kFull ? term : true;   // a lean playout always runs to a terminal state
+        fin_win = G::won(s);
         if (kFull && !active && a.io.final_states) G::store(s, a.io.final_states, a.n_playouts, lid);
       }
     }
@@ -123,8 +126,8 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
       if (G::kCanStick && active && nlegal == 0) {  // non-terminal state without a legal action
         active = false;
         my_stuck += 1;
-        fin_term = 0;
-        fin_outc = kOutcomeNone;
+        fin_term = false;
+        fin_win = false;
         if (kFull && a.io.final_states) G::store(prev, a.io.final_states, a.n_playouts, lid);
       }
       if (kFull) {
@@ -135,8 +138,8 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
           const bool term = G::terminal(s);
           if (term || t >= limit) {
             active = false;
-            fin_term = term ? 1u : 0u;
-            fin_outc = (u32)G::outcome(s);
+            fin_term = term;
+            fin_win = term && G::won(s);
             if (a.io.final_states) {
               if (term && a.io.final_before_terminal) G::store(prev, a.io.final_states, a.n_playouts, lid);
               else G::store(s, a.io.final_states, a.n_playouts, lid);
@@ -146,8 +149,9 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
       } else {
         // lean bookkeeping: t counts the moves of the live playout and freezes when it ends
         const bool term = G::terminal(s);
+        const bool won = G::won(s);
+        fin_win = (active && term) ? won : fin_win;
         t += active ? 1u : 0u;
-        if (active && term) { fin_term = 1u; fin_outc = (u32)G::outcome(s); }
         active = active && !term;
       }
     }

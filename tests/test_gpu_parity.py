@@ -243,7 +243,7 @@ def test_connect_four_full_size_properties(torch):
   eng.close()
 
 
-@pytest.mark.parametrize("game,n", [("connect_four", 400000), ("breakthrough", 330000),
+@pytest.mark.parametrize("game,n", [("connect_four", 800000), ("breakthrough", 330000),
                                     ("hex", 110000), ("tic_tac_toe", 1100000)])
 def test_host_buffer_chunked_path_equals_device_path(game, n, torch):
   """bsg_playouts_host cuts large inputs into chunks on two streams (H2D overlapping the
