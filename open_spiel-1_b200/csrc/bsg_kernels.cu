@@ -22,6 +22,8 @@
 namespace bsg {
 
 constexpr int kThreads = 256;
+constexpr int kChunkPlayouts = 128;   // playouts per work-counter draw of a warp
+constexpr int kWorkSlots = 1024;      // launches that may be in flight at once, per engine
 
 struct PlayoutArgs {
   const void* roots;
@@ -32,7 +34,14 @@ struct PlayoutArgs {
   uint64_t first_playout;
   PhiloxKeys keys;
   bsg_playout_io io;
+  uint32_t* work_counter;  // zeroed before the launch; warps draw chunks of playouts from it
+  uint32_t out_flags;  // kOut* bits: which optional per-playout outputs of io are present
 };
+enum : uint32_t { kOutRet = 1, kOutLength = 2, kOutTerminal = 4, kOutRootSums = 8 };
+inline uint32_t out_flags_of(const bsg_playout_io& io) {
+  return (io.ret0 ? kOutRet : 0u) | (io.length ? kOutLength : 0u) | (io.terminal ? kOutTerminal : 0u) |
+         ((io.root_sum_ret0 || io.root_sum_steps) ? kOutRootSums : 0u);
+}
 
 template <class G, bool kFull>
 __global__ void __launch_bounds__(kThreads)
@@ -45,15 +54,14 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
   }
   __syncthreads();
 
-  // contiguous slice of this WARP; its lanes claim playouts from a warp-uniform cursor with
-  // one ballot (no atomics, no shared memory), so the claim itself is convergent code
-  const u32 n_warps = gridDim.x * (kThreads / 32);
-  const u32 warp_id = blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
-  const u32 per = (a.n_playouts + n_warps - 1) / n_warps;
-  const u32 begin = min(per * warp_id, a.n_playouts);
-  const u32 count = min(per, a.n_playouts - begin);
-  const u32 lane_lt = (1u << (threadIdx.x & 31)) - 1u;
-  u32 cursor = 0;
+  // Work distribution: every warp draws chunks of kChunkPlayouts consecutive playouts from one
+  // global counter (the hardware warp scheduler is not fair, so equal static slices finish at
+  // very different times and the SMs drain early); inside a chunk its lanes claim playouts
+  // from a warp-uniform cursor with one ballot, so the claim itself is convergent code.
+  const u32 lane = threadIdx.x & 31;
+  const u32 lane_lt = (1u << lane) - 1u;
+  u32 begin = 0, count = 0, cursor = 0;
+  bool drained = false;
 
   typename G::State s;
   G::init(s);
@@ -62,21 +70,33 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
   // Per playout the kernel records only: its length t (frozen when it ends), whether it ended
   // in a terminal state (fin_term) and whether that was a win (fin_win).  A win is always the
   // last mover's, so the winner follows from the root's mover and the parity of t.
-  bool active = false, have = false, fin_term = false, fin_win = false;
+  // Flags are 0/1 words (not bools) so they stay in plain registers.
+  u32 live = 0, have = 0, fin_term = 0, fin_win = 0;
   u32 lid = 0, t = 0, limit = 0xFFFFFFFFu, root_mv = 0;
   u32 my_steps = 0, my_done = 0, my_stuck = 0;
   int my_ret = 0;
+  const u32 out = a.out_flags;   // which optional outputs exist (uniform)
 
   for (;;) {
-    const bool need = !active;
-    const u32 want = __ballot_sync(0xFFFFFFFFu, need);
-    if (need) {
+    const u32 want = __ballot_sync(0xFFFFFFFFu, live == 0);
+    const u32 nwant = __popc(want);
+    u32 nbegin = 0, ncount = 0;
+    const bool grab = !drained && cursor + nwant > count;  // warp-uniform: the chunk runs out in this claim
+    if (grab) {
+      u32 nb = 0;
+      if (lane == 0) nb = atomicAdd(a.work_counter, kChunkPlayouts);
+      nb = __shfl_sync(0xFFFFFFFFu, nb, 0);
+      nbegin = min(nb, a.n_playouts);
+      ncount = min((u32)kChunkPlayouts, a.n_playouts - nbegin);
+      drained = ncount == 0;
+    }
+    if (live == 0) {
       if (have) {  // publish the finished playout
-        const int ret = (fin_term && fin_win) ? (((root_mv ^ t) & 1u) ? 1 : -1) : 0;
-        if (a.io.ret0) a.io.ret0[lid] = (int8_t)ret;
-        if (a.io.length) a.io.length[lid] = (uint8_t)t;
-        if (a.io.terminal) a.io.terminal[lid] = (uint8_t)(fin_term ? 1 : 0);
-        if (a.io.root_sum_ret0 || a.io.root_sum_steps) {
+        const int ret = (fin_term & fin_win) ? (int)(((root_mv ^ t) & 1u) << 1) - 1 : 0;
+        if (out & kOutRet) a.io.ret0[lid] = (int8_t)ret;
+        if (out & kOutLength) a.io.length[lid] = (uint8_t)t;
+        if (out & kOutTerminal) a.io.terminal[lid] = (uint8_t)fin_term;
+        if (out & kOutRootSums) {
           u32 root = a.rollouts == 1 ? lid : lid / a.rollouts;
           if (a.io.root_sum_ret0 && ret != 0) atomicAdd(a.io.root_sum_ret0 + root, ret);
           if (a.io.root_sum_steps) atomicAdd(a.io.root_sum_steps + root, (int)t);
@@ -85,10 +105,12 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         my_ret += ret;
         my_done += 1;
       }
-      const u32 idx = cursor + __popc(want & lane_lt);
-      have = idx < count;
-      if (have) {  // claim the next playout of the slice
-        lid = begin + idx;
+      u32 idx = cursor + __popc(want & lane_lt);
+      u32 base = begin, cnt = count;
+      if (idx >= count) { idx -= count; base = nbegin; cnt = ncount; }
+      have = idx < cnt ? 1u : 0u;
+      if (have) {  // claim the next playout
+        lid = base + idx;
         u32 root = a.rollouts == 1 ? lid : lid / a.rollouts;
         G::load(s, a.roots, a.n_roots, a.root0 + root);
         t = 0;
@@ -99,15 +121,16 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
           prev = s;
         }
         const bool term = G::terminal(s);
-        active = !term && (!kFull || limit > 0);
-        fin_term = kFull ? term : true;   // a lean playout always runs to a terminal state
-        fin_win = G::won(s);
-        if (kFull && !active && a.io.final_states) G::store(s, a.io.final_states, a.n_playouts, lid);
+        live = (!term && (!kFull || limit > 0)) ? 1u : 0u;
+        fin_term = (kFull && !term) ? 0u : 1u;   // a lean playout always runs to a terminal state
+        fin_win = G::won(s) ? 1u : 0u;
+        if (kFull && !live && a.io.final_states) G::store(s, a.io.final_states, a.n_playouts, lid);
       }
     }
-    cursor += __popc(want);
-    if (!__any_sync(0xFFFFFFFFu, active)) {
-      if (!__any_sync(0xFFFFFFFFu, have)) break;
+    cursor += nwant;
+    if (grab) { cursor = cursor > count ? cursor - count : 0u; begin = nbegin; count = ncount; }
+    if (!__any_sync(0xFFFFFFFFu, live != 0)) {
+      if (!__any_sync(0xFFFFFFFFu, have != 0)) break;
       continue;
     }
 
@@ -118,28 +141,28 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
     for (int j = 0; j < 4; ++j) {
       u32 r = rr[j];
       if (kFull) {
-        if (a.io.r_table && active) r = a.io.r_table[(size_t)lid * a.io.r_stride + min(t, (u32)a.io.r_stride - 1)];
-        if (active) prev = s;
+        if (a.io.r_table && live) r = a.io.r_table[(size_t)lid * a.io.r_stride + min(t, (u32)a.io.r_stride - 1)];
+        if (live) prev = s;
       }
       int action;
       const u32 nlegal = G::step(s, r, tab, action);
-      if (G::kCanStick && active && nlegal == 0) {  // non-terminal state without a legal action
-        active = false;
+      if (G::kCanStick && live && nlegal == 0) {  // non-terminal state without a legal action
+        live = 0;
         my_stuck += 1;
-        fin_term = false;
-        fin_win = false;
+        fin_term = 0;
+        fin_win = 0;
         if (kFull && a.io.final_states) G::store(prev, a.io.final_states, a.n_playouts, lid);
       }
       if (kFull) {
-        if (active) {
+        if (live) {
           if (a.io.actions && t < (u32)a.io.actions_stride)
             a.io.actions[(size_t)lid * a.io.actions_stride + t] = (int16_t)action;
           t += 1;
           const bool term = G::terminal(s);
           if (term || t >= limit) {
-            active = false;
-            fin_term = term;
-            fin_win = term && G::won(s);
+            live = 0;
+            fin_term = term ? 1u : 0u;
+            fin_win = (term && G::won(s)) ? 1u : 0u;
             if (a.io.final_states) {
               if (term && a.io.final_before_terminal) G::store(prev, a.io.final_states, a.n_playouts, lid);
               else G::store(s, a.io.final_states, a.n_playouts, lid);
@@ -147,12 +170,13 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
           }
         }
       } else {
-        // lean bookkeeping: t counts the moves of the live playout and freezes when it ends
-        const bool term = G::terminal(s);
-        const bool won = G::won(s);
-        fin_win = (active && term) ? won : fin_win;
-        t += active ? 1u : 0u;
-        active = active && !term;
+        // lean bookkeeping: t counts the moves of the live playout and freezes when it ends;
+        // fin_win was cleared at the claim and can only be set by the (single) ending move
+        const u32 term = G::terminal(s) ? 1u : 0u;
+        const u32 won = G::won(s) ? 1u : 0u;
+        fin_win |= live & won;
+        t += live;
+        live &= term ^ 1u;
       }
     }
   }
@@ -332,6 +356,8 @@ struct bsg_engine {
   void* d_out = nullptr; size_t d_out_bytes = 0;
   void* h_pinned = nullptr; size_t h_pinned_bytes = 0;
   uint64_t* d_totals = nullptr;
+  uint32_t* d_work = nullptr;          // ring of per-launch work counters (playout_kernel)
+  unsigned work_slot = 0;
   cudaStream_t own_stream = nullptr;
   cudaStream_t aux_stream = nullptr;   // second lane of the chunked host path (copy/compute overlap)
   cudaEvent_t ev_a = nullptr, ev_b = nullptr;
@@ -384,6 +410,9 @@ int launch_playouts(bsg_engine* e, const PlayoutArgs& a, cudaStream_t st) {
   static int blocks_per_sm = 0;
   if (blocks_per_sm == 0) {
     int b = 0;
+    // all of the L1/shared array as shared memory: the tables of every resident CTA must fit
+    BSG_CUDA(e, cudaFuncSetAttribute(playout_kernel<G, kFull>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                     cudaSharedmemCarveoutMaxShared));
     BSG_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, playout_kernel<G, kFull>, kThreads, 0));
     blocks_per_sm = b > 0 ? b : 1;
   }
@@ -391,7 +420,12 @@ int launch_playouts(bsg_engine* e, const PlayoutArgs& a, cudaStream_t st) {
   int64_t need = ((int64_t)a.n_playouts + kThreads - 1) / kThreads;
   int grid = (int)(need < max_grid ? need : max_grid);
   if (grid < 1) grid = 1;
-  playout_kernel<G, kFull><<<grid, kThreads, 0, st>>>(a, (const typename G::Tables*)e->tables_dev);
+  PlayoutArgs b = a;
+  b.out_flags = out_flags_of(a.io);
+  // work counter of this launch: next slot of the engine's ring, zeroed in stream order
+  b.work_counter = e->d_work + (e->work_slot++ % kWorkSlots);
+  BSG_CUDA(e, cudaMemsetAsync(b.work_counter, 0, sizeof(uint32_t), st));
+  playout_kernel<G, kFull><<<grid, kThreads, 0, st>>>(b, (const typename G::Tables*)e->tables_dev);
   BSG_CUDA(e, cudaGetLastError());
   return BSG_OK;
 }
@@ -542,6 +576,7 @@ int bsg_create(int game, int device, bsg_engine** out) {
   BSG_CUDA(e, cudaEventCreateWithFlags(&e->ev_a, cudaEventDisableTiming));
   BSG_CUDA(e, cudaEventCreateWithFlags(&e->ev_b, cudaEventDisableTiming));
   BSG_CUDA(e, cudaMalloc(&e->d_totals, 4 * sizeof(uint64_t)));
+  BSG_CUDA(e, cudaMalloc(&e->d_work, kWorkSlots * sizeof(uint32_t)));
   return dispatch_device_game(game, CreateOp{e});
 }
 
@@ -553,6 +588,7 @@ void bsg_destroy(bsg_engine* e) {
   if (e->d_out) cudaFree(e->d_out);
   if (e->h_pinned) cudaFreeHost(e->h_pinned);
   if (e->d_totals) cudaFree(e->d_totals);
+  if (e->d_work) cudaFree(e->d_work);
   if (e->own_stream) cudaStreamDestroy(e->own_stream);
   if (e->aux_stream) cudaStreamDestroy(e->aux_stream);
   if (e->ev_a) cudaEventDestroy(e->ev_a);
@@ -569,7 +605,7 @@ int bsg_playouts(bsg_engine* e, const void* roots, int64_t n_roots, int32_t roll
   if (!e) return BSG_ERR_BAD_ARG;
   if (!roots || n_roots < 0 || rollouts < 1) return fail(e, BSG_ERR_BAD_ARG, "bad roots/rollouts");
   int64_t total = n_roots * (int64_t)rollouts;
-  if (total >= (int64_t)1 << 32) return fail(e, BSG_ERR_BAD_ARG, "more than 2^32-1 playouts in one launch");
+  if (total >= ((int64_t)1 << 32) - (1 << 24)) return fail(e, BSG_ERR_BAD_ARG, "more than 2^32-2^24 playouts in one launch");
   if (total == 0) return BSG_OK;
   PlayoutArgs a;
   memset(&a, 0, sizeof(a));
@@ -603,8 +639,8 @@ int bsg_playouts_host(bsg_engine* e, const void* roots_host, int64_t n_roots, in
   if (!e) return BSG_ERR_BAD_ARG;
   if (!roots_host || n_roots < 1 || rollouts < 1 || !totals_out)
     return fail(e, BSG_ERR_BAD_ARG, "bad host playout arguments");
-  if (n_roots * (int64_t)rollouts >= (int64_t)1 << 32)
-    return fail(e, BSG_ERR_BAD_ARG, "more than 2^32-1 playouts in one call");
+  if (n_roots * (int64_t)rollouts >= ((int64_t)1 << 32) - (1 << 24))
+    return fail(e, BSG_ERR_BAD_ARG, "more than 2^32-2^24 playouts in one call");
   BSG_CUDA(e, cudaSetDevice(e->device));
   int plane_bytes[8];
   const int n_planes = dispatch_device_game(e->game, PlaneOp{plane_bytes});
