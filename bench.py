@@ -346,14 +346,16 @@ def rank0_extras(args, eng, torch, dev, steps_per_s_per_gpu, kernel_ms, n):
   out["roofline"] = {
       "bound": "int_issue", "kernel": "playout_kernel<ConnectFour,false>",
       "achieved": achieved / 1e12, "peak": peak_int / 1e12, "unit": "T thread-instr/s",
-      "frac": achieved / peak_int, "traffic": None,
+      "frac": achieved / peak_int, "traffic": ncu_traffic_bytes("playout_kernel<ConnectFour, 0>"),
       "algorithmic_ops_per_step": ops,
       "peak_source": "bsg_int_peak microbenchmark, live: " + ", ".join(
           "%s=%.2fT" % (kinds[k], peaks[k] / 1e12) for k in kinds),
       "kernel_ms": kernel_ms,
       "note": "the path is integer/branchy by design (north_star): the bound is the integer "
-              "issue rate, not HBM or tensor; HBM bytes are ~18 B/playout (<2 B/step)",
-      "hbm_achieved_gbs": n * 18 / (kernel_ms * 1e-3) / 1e9,
+              "issue rate, not HBM or tensor; algorithmic HBM bytes are 8 B root + 2 B results per "
+              "playout (~1 B/step); traffic = dram read+write bytes of one launch from the newest "
+              "ncu --set full capture under profiles/",
+      "hbm_achieved_gbs": n * (eng.state_bytes + 2) / (kernel_ms * 1e-3) / 1e9,
   }
   if not args.no_extras:
     # observation writer: HBM-write bound (breakthrough, 784 algorithmic B/state)
@@ -400,6 +402,27 @@ def rank0_extras(args, eng, torch, dev, steps_per_s_per_gpu, kernel_ms, n):
         "cpu_model": cpu_model(),
     }
   return out
+
+
+def ncu_traffic_bytes(kernel_substr):
+  """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the kernel, from the newest
+  committed ncu summary (profiles/r*_kernels.csv, written by profiles/summarize_ncu.py)."""
+  import csv
+  import glob
+  for path in sorted(glob.glob(os.path.join(REPO, "profiles", "r*_kernels.csv")), reverse=True):
+    try:
+      rows = list(csv.reader(open(path)))
+      hdr = rows[0]
+      rd = [i for i, h in enumerate(hdr) if h.startswith("dram__bytes_read.sum")][0]
+      wr = [i for i, h in enumerate(hdr) if h.startswith("dram__bytes_write.sum")][0]
+      scale = {"Mbyte": 1e6, "Kbyte": 1e3, "Gbyte": 1e9, "byte": 1.0}
+      for r in rows[1:]:
+        if kernel_substr in r[0]:
+          return (float(r[rd]) * scale[hdr[rd].split("[")[1].rstrip("]")] +
+                  float(r[wr]) * scale[hdr[wr].split("[")[1].rstrip("]")])
+    except Exception:
+      continue
+  return None
 
 
 def cpu_model():
