@@ -8,7 +8,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libbsg.so")
+LIB_PATH = os.environ.get("BSG_LIB") or os.path.join(_HERE, "libbsg.so")  # BSG_LIB: developer override (A/B builds)
 
 vp = ctypes.c_void_p
 i32, i64, u32, u64 = ctypes.c_int32, ctypes.c_int64, ctypes.c_uint32, ctypes.c_uint64

@@ -123,8 +123,8 @@ struct TicTacToe {
 //     bits 0..54   stones of the player to move | one marker bit per column at (height, col)
 //                  (everything below a marker is occupied, so the whole position decodes with
 //                  three shift-ors: smear the markers down, shift one row down = occupancy);
-//     bits 56..61  stones on the board (0..42; parity = player to move, x = player 0 first);
-//     bit  62      the last move made four in a row (terminal by win).
+//     bit  57      the last move made four in a row (terminal by win);
+//     bits 58..63  empty cells (42..0; parity = player to move, x = player 0 first).
 // =========================================================================================
 struct ConnectFour {
   static constexpr int kId = kGameConnectFour;
@@ -138,36 +138,30 @@ struct ConnectFour {
     u32 left;      // empty cells; 42 - left stones on the board, parity = player to move
     u32 win;       // the last move completed a line
   };
-  // One 72-byte row per 7-bit mask L of non-full columns (connect_four.cc:108-116):
-  //   word 0 = floor(2^32 / n), word 1 = -n (n = popc L: the fast-modulo constants),
-  //   words 2.. = for k < n the 64-bit cell mask of the k-th open column, ascending.
-  // 18 words per row: rows of different L start in different shared-memory banks.
-  static constexpr int kRowWords = 18;
-  struct Tables { u32 row[128][kRowWords]; };
+  // One 72-byte row (nine u64) per 7-bit mask L of non-full columns (connect_four.cc:108-116):
+  //   [0] = floor(2^32 / n) | (u64)(-n) << 32   (n = popc L: the fast-modulo constants),
+  //   [1 + k] = for k < n the 64-bit cell mask of the k-th open column, ascending.
+  // Nine words per row: rows of different L start in different shared-memory banks.
+  static constexpr int kRowWords = 9;
+  struct Tables { u64 row[128][kRowWords]; };
   static constexpr u64 kColumn = 0x0000010101010101ull;  // the six cells of column 0
   static void fill_tables(Tables& t) {
     for (u32 L = 0; L < 128; ++L) {
       u32 n = 0;
       for (int w = 0; w < kRowWords; ++w) t.row[L][w] = 0;
       for (u32 c = 0; c < 7; ++c)
-        if ((L >> c) & 1) {
-          u64 m = kColumn << c;
-          t.row[L][2 + 2 * n] = (u32)m;
-          t.row[L][3 + 2 * n] = (u32)(m >> 32);
-          ++n;
-        }
+        if ((L >> c) & 1) t.row[L][1 + n++] = kColumn << c;
       // L = 0 only happens on finished lanes running dead steps: n = 1 keeps k = 0 and the
       // empty column mask places nothing.
       u32 nn = n ? n : 1;
-      t.row[L][0] = modM_entry(nn);
-      t.row[L][1] = 0u - nn;
+      t.row[L][0] = (u64)modM_entry(nn) | ((u64)(0u - nn) << 32);
     }
   }
   BSG_HD static void init(State& s) { s.cur = 0; s.opp = 0; s.left = 42; s.win = 0; }
   BSG_HD static void load(State& s, const void* base, int64_t n, int64_t i) {
     (void)n;
     u64 w = ((const u64*)base)[i];
-    u32 meta = (u32)(w >> 56);
+    u32 top = (u32)(w >> 32);
     u64 key = w & 0x00FFFFFFFFFFFFFFull;
     u64 sm = key;             // smear every marker (and stone) down its column
     sm |= sm >> 8;
@@ -176,8 +170,8 @@ struct ConnectFour {
     u64 occ = sm >> 8;        // strictly below the markers
     s.cur = key & occ;
     s.opp = occ & ~key;
-    s.left = 42u - (meta & 63u);
-    s.win = (meta >> 6) & 1u;
+    s.left = top >> 26;
+    s.win = (top >> 25) & 1u;
   }
   BSG_HD static void store(const State& s, void* base, int64_t n, int64_t i) {
     (void)n;
@@ -186,7 +180,7 @@ struct ConnectFour {
       u64 e = ~occ & (0x0001010101010101ull << c);   // 7 rows: a full column marks row 6
       markers |= e & (0ull - e);
     }
-    u64 meta = (u64)((42u - s.left) | (s.win << 6));
+    u64 meta = (u64)((s.win << 1) | (s.left << 2));
     ((u64*)base)[i] = s.cur | markers | (meta << 56);
   }
   BSG_HD static bool terminal(const State& s) { return (s.win != 0) || (s.left == 0); }
@@ -201,7 +195,9 @@ struct ConnectFour {
   // Rows: d = 1, per 32-bit word (rows do not straddle words), with left shifts (they can run
   // on the multiplier pipe).  Columns and diagonals (d = 8, 7, 9): the lowest cell of such a
   // line is in rows 0..2, so only the LOW word of the product is needed — three funnel
-  // shifts of (hi:lo) and two ANDs per direction.
+  // shifts of (hi:lo) and two ANDs per direction.  (Measured and rejected: running some of
+  // the funnel shifts on the multiplier pipe as IMAD.HI + IMAD; IMAD.HI issues every 4 cycles
+  // and every variant was slower than the plain SHF form.)
   BSG_HD static bool has_line(u64 b) {
     u32 lo = (u32)b, hi = (u32)(b >> 32);
     u32 ml = lo & (lo << 1), mh = hi & (hi << 1);
@@ -225,11 +221,25 @@ struct ConnectFour {
     return ~(u32)((s.cur | s.opp) >> 40) & 0x7Fu;  // connect_four.cc:108-116
   }
   BSG_HD static u32 step(State& s, u32 r, const Tables& tab, int& action) {
-    const u32* row = tab.row[open_columns(s)];
-    u32 negn = row[1];
-    u32 rem = umulhi32(r, row[0]) * negn + r;       // r - floor-ish(r / n) * n, in [0, 2n)
+    // row L of the table straight from the top-row word (L << 8), without isolating L first
+    const u32 t = ~(u32)((s.cur | s.opp) >> 32) & 0x7F00u;
+#if defined(__CUDA_ARCH__)
+    // 32-bit shared-window addressing (generic pointers would cost 64-bit address arithmetic)
+    const u32 off = (u32)__cvta_generic_to_shared(&tab) + ((t * 9u) >> 5);   // + L * 72
+    u32 M, negn, c_lo, c_hi;
+    asm("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(M), "=r"(negn) : "r"(off));
+    u32 rem = umulhi32(r, M) * negn + r;            // r - floor-ish(r / n) * n, in [0, 2n)
     u32 k = umin32(rem, rem + negn);                // r mod n
-    u64 column = (u64)row[2 + 2 * k] | ((u64)row[3 + 2 * k] << 32);
+    asm("ld.shared.v2.u32 {%0, %1}, [%2+8];" : "=r"(c_lo), "=r"(c_hi) : "r"(off + k * 8u));
+    u64 column = (u64)c_lo | ((u64)c_hi << 32);
+#else
+    const u64* row = tab.row[t >> 8];
+    const u64 mc = row[0];
+    const u32 negn = (u32)(mc >> 32);
+    u32 rem = umulhi32(r, (u32)mc) * negn + r;
+    u32 k = umin32(rem, rem + negn);
+    u64 column = row[1 + k];
+#endif
     action = ctz64(column);                          // column index = lowest bit (row 0 cell)
     drop_mask(s, column);
     return 0u - negn;
