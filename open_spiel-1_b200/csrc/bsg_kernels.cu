@@ -8,6 +8,8 @@
 //  * steps run in groups of four: one Philox4x32-10 block (4 draws) per group, and lanes are
 //    refilled only at group boundaries, which keeps every lane's step index congruent to the
 //    group phase — the RNG and the refill code stay warp-convergent;
+//  * the refill code runs whenever a lane waits (measured and rejected: waiting until >= 4..16
+//    lanes are idle; it was slower for all four games);
 //  * a step is unconditional straight-line code (finished lanes run dead steps on a dead
 //    state); only the bookkeeping is predicated.
 #include <cuda_runtime.h>
