@@ -6,9 +6,11 @@
 #if defined(__CUDACC__)
 #define BSG_HD __host__ __device__ __forceinline__
 #define BSG_D __device__ __forceinline__
+#define BSG_HDC __host__ __device__ constexpr
 #else
 #define BSG_HD inline
 #define BSG_D inline
+#define BSG_HDC constexpr
 #endif
 
 namespace bsg {

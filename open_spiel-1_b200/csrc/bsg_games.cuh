@@ -36,6 +36,7 @@ struct TicTacToe {
   static constexpr int kPlanes = 1;   // packed SoA planes and their element sizes
   BSG_HD static int plane_bytes(int p) { (void)p; return 4; }
   static constexpr bool kCanStick = false;  // a non-terminal state always has a legal action
+  static constexpr bool kAsync = false;     // a step completes within the step (see HexT)
   struct State { u32 x, o, term, outc; };
   struct Tables { u32 modM[16]; };
   static void fill_tables(Tables& t) { for (u32 n = 0; n < 16; ++n) t.modM[n] = modM_entry(n); }
@@ -133,6 +134,7 @@ struct ConnectFour {
   static constexpr int kPlanes = 1;
   BSG_HD static int plane_bytes(int p) { (void)p; return 8; }
   static constexpr bool kCanStick = false;
+  static constexpr bool kAsync = false;
   struct State {
     u64 cur, opp;  // stones of the player to move / of the other player
     u32 left;      // empty cells; 42 - left stones on the board, parity = player to move
@@ -309,6 +311,7 @@ struct Breakthrough {
   static constexpr int kPlanes = 2;
   BSG_HD static int plane_bytes(int p) { return p == 0 ? 16 : 4; }
   static constexpr bool kCanStick = true;   // all pieces blocked is possible
+  static constexpr bool kAsync = false;
   static constexpr u64 kCol0 = 0x0101010101010101ull, kCol7 = 0x8080808080808080ull;
   struct State { u64 own, opp; u32 mv, term, outc; };
   struct Tables { u32 modM[64]; };
@@ -484,9 +487,16 @@ struct Breakthrough {
 //   (hex.cc:55-121).  The reference keeps, per stone, whether its group touches one of its
 //   colour's edges (9 cell states, hex.h:51-61) and floods that label through adjacent PLAIN
 //   stones of the mover when an edge-connected stone is placed (hex.cc:149-184).  Here the same
-//   sets are bit masks per side — A (north / west), B (south / east), P (plain) — and the
-//   flood is a bit-parallel dilation: its first ring is one table look-up (neighbour mask of
-//   the new cell), further rings use six 128-bit shifts with column guards (hex.cc:206-222).
+//   sets are bit masks per side — O (all stones), A (north / west connected), B (south / east
+//   connected); plain = O & ~A & ~B — and the flood is a bit-parallel dilation.
+//
+//   The flood is ASYNCHRONOUS on the device (kAsync): placing a stone only records the first
+//   frontier (the plain neighbours of the new stone, one table look-up); every later kernel
+//   iteration runs ONE dilation ring for every lane (straight-line code) and a lane makes its
+//   next move only when its frontier is empty.  Flood depth has a fat tail in random play
+//   (11 % of the moves flood, 1.4 % need >= 3 rings, some 15+); a per-move flood loop made the
+//   whole warp wait for its deepest lane (measured: 58 % of the kernel's instructions ran in
+//   that loop with 2.3 of 32 lanes active).  Host helpers flood synchronously (`finish`).
 //   A winning stone is a member of both A and B; no flood runs on the winning move.
 //   packed: SoA, 4 planes of 16 B: black, white, edgeA (north|west), edgeB (south|east).
 // =========================================================================================
@@ -500,28 +510,37 @@ struct HexT {
   static constexpr int kPlanes = 4;
   BSG_HD static int plane_bytes(int p) { (void)p; return 16; }
   static constexpr bool kCanStick = false;
-  struct M128 { u32 w[4]; };
+  static constexpr bool kAsync = true;
   struct State {
-    u32 occ[4];                       // all stones; bits >= N*N are kept set (never legal)
-    u32 cA[4], cB[4], cP[4];          // mover's stones: edge A, edge B, plain
-    u32 oA[4], oB[4], oP[4];          // the other side's
-    u32 mv, term, outc;
+    u32 cO[4], cA[4], cB[4];   // side to move: all stones / edge-A connected / edge-B connected
+    u32 oO[4], oA[4], oB[4];   // the side that moved last
+    u32 F[4];                  // pending flood frontier: plain stones of the o side that are
+                               // adjacent to newly labelled ones and not labelled yet
+    u32 fA;                    // ~0: the pending flood spreads label A; 0: label B
+    u32 left;                  // empty cells
+    u32 mv;                    // player to move (0 black, 1 white)
+    u32 win;                   // the last move connected both edges
   };
   // nb[cell]: neighbour mask; word 3 bits 28..31 carry the edge flags of the cell:
   // bit 28 row 0, 29 row N-1, 30 col 0, 31 col N-1 (never board cells since N*N <= 124).
+  // one[cell]: one-hot mask.  sel8[b][k]: position of the k-th set bit of byte b.
   struct Tables {
     u32 nb[128][4];
+    u32 one[128][4];
     u32 modM[128];
-    u32 notColLast[4], notCol0[4];
+    unsigned char sel8[256][8];
   };
   static void fill_tables(Tables& t) {
     for (u32 n = 0; n < 128; ++n) t.modM[n] = modM_entry(n);
-    for (int w = 0; w < 4; ++w) { t.notColLast[w] = 0xFFFFFFFFu; t.notCol0[w] = 0xFFFFFFFFu; }
-    for (int c = 0; c < 128; ++c) for (int w = 0; w < 4; ++w) t.nb[c][w] = 0;
+    for (int c = 0; c < 128; ++c)
+      for (int w = 0; w < 4; ++w) { t.nb[c][w] = 0; t.one[c][w] = (w == (c >> 5)) ? 1u << (c & 31) : 0u; }
+    for (int b = 0; b < 256; ++b) {
+      int k = 0;
+      for (int i = 0; i < 8; ++i) t.sel8[b][i] = 0;
+      for (int i = 0; i < 8; ++i) if ((b >> i) & 1) t.sel8[b][k++] = (unsigned char)i;
+    }
     for (int cell = 0; cell < kCells; ++cell) {
       int row = cell / N, col = cell % N;
-      if (col == N - 1) t.notColLast[cell >> 5] &= ~(1u << (cell & 31));
-      if (col == 0) t.notCol0[cell >> 5] &= ~(1u << (cell & 31));
       const int dr[6] = {-1, -1, 0, 0, 1, 1}, dc[6] = {0, 1, -1, 1, -1, 0};  // hex.cc:206-222
       for (int k = 0; k < 6; ++k) {
         int r2 = row + dr[k], c2 = col + dc[k];
@@ -535,17 +554,38 @@ struct HexT {
       else if (col == N - 1) t.nb[cell][3] |= 1u << 31;   // hex.cc:95-99
     }
   }
-  BSG_HD static u32 pad_word(int w) {  // bits of word w that are not board cells
-    int lo = kCells - 32 * w;
-    return lo >= 32 ? 0u : (lo <= 0 ? 0xFFFFFFFFu : ~((1u << lo) - 1u));
+  // Compile-time masks of word w: board cells, cells not in column 0, cells not in column N-1.
+  BSG_HDC static u32 word_mask(int w, int kind) {
+    u32 m = 0;
+    for (int b = 0; b < 32; ++b) {
+      int cell = 32 * w + b;
+      if (cell >= kCells) break;
+      int col = cell % N;
+      bool in = kind == 0 ? true : (kind == 1 ? col != 0 : col != N - 1);
+      if (in) m |= 1u << b;
+    }
+    return m;
   }
+  BSG_HD static u32 board_word(int w) {
+    constexpr u32 m[4] = {word_mask(0, 0), word_mask(1, 0), word_mask(2, 0), word_mask(3, 0)};
+    return m[w];
+  }
+  BSG_HD static u32 not_col0(int w) {
+    constexpr u32 m[4] = {word_mask(0, 1), word_mask(1, 1), word_mask(2, 1), word_mask(3, 1)};
+    return m[w];
+  }
+  BSG_HD static u32 not_col_last(int w) {
+    constexpr u32 m[4] = {word_mask(0, 2), word_mask(1, 2), word_mask(2, 2), word_mask(3, 2)};
+    return m[w];
+  }
+
   BSG_HD static void init(State& s) {
 #pragma unroll
     for (int w = 0; w < 4; ++w) {
-      s.occ[w] = pad_word(w);
-      s.cA[w] = s.cB[w] = s.cP[w] = s.oA[w] = s.oB[w] = s.oP[w] = 0;
+      s.cO[w] = s.cA[w] = s.cB[w] = s.oO[w] = s.oA[w] = s.oB[w] = 0;
+      s.F[w] = 0;
     }
-    s.mv = 0; s.term = 0; s.outc = kOutcomeNone;
+    s.fA = 0; s.left = kCells; s.mv = 0; s.win = 0;
   }
   BSG_HD static void load(State& s, const void* base, int64_t n, int64_t i) {
     u32 bl[4], wh[4], ea[4], eb[4];
@@ -564,161 +604,179 @@ struct HexT {
     }
 #endif
     int nb = 0, nw = 0;
-    u32 winb = 0, winw = 0;
+    u32 won = 0;
 #pragma unroll
     for (int w = 0; w < 4; ++w) {
       nb += popc32(bl[w]); nw += popc32(wh[w]);
-      winb |= bl[w] & ea[w] & eb[w]; winw |= wh[w] & ea[w] & eb[w];
+      won |= (bl[w] | wh[w]) & ea[w] & eb[w];
     }
     s.mv = nb > nw ? 1u : 0u;  // black moves first and turns alternate
-    s.term = (winb | winw) ? 1u : 0u;
-    s.outc = winb ? (u32)kOutcomeP0 : (winw ? (u32)kOutcomeP1 : (u32)kOutcomeNone);
+    s.win = won ? 1u : 0u;
+    s.left = (u32)(kCells - nb - nw);
+    s.fA = 0;
 #pragma unroll
     for (int w = 0; w < 4; ++w) {
-      s.occ[w] = bl[w] | wh[w] | pad_word(w);
-      u32 bA = bl[w] & ea[w], bB = bl[w] & eb[w], bP = bl[w] & ~(ea[w] | eb[w]);
-      u32 wA = wh[w] & ea[w], wB = wh[w] & eb[w], wP = wh[w] & ~(ea[w] | eb[w]);
-      s.cA[w] = s.mv ? wA : bA; s.cB[w] = s.mv ? wB : bB; s.cP[w] = s.mv ? wP : bP;
-      s.oA[w] = s.mv ? bA : wA; s.oB[w] = s.mv ? bB : wB; s.oP[w] = s.mv ? bP : wP;
+      u32 mine = s.mv ? wh[w] : bl[w], theirs = s.mv ? bl[w] : wh[w];
+      s.cO[w] = mine; s.cA[w] = mine & ea[w]; s.cB[w] = mine & eb[w];
+      s.oO[w] = theirs; s.oA[w] = theirs & ea[w]; s.oB[w] = theirs & eb[w];
+      s.F[w] = 0;
     }
   }
-  BSG_HD static void store(const State& s, void* base, int64_t n, int64_t i) {
+  BSG_HD static void store(const State& s0, void* base, int64_t n, int64_t i) {
+    State s = s0;
+    finish(s);   // a packed state always carries complete edge-connected sets
     u32* p = (u32*)base;
 #pragma unroll
     for (int w = 0; w < 4; ++w) {
-      u32 cur = s.cA[w] | s.cB[w] | s.cP[w], oth = s.oA[w] | s.oB[w] | s.oP[w];
-      p[4 * i + w] = s.mv ? oth : cur;
-      p[4 * (n + i) + w] = s.mv ? cur : oth;
+      p[4 * i + w] = s.mv ? s.oO[w] : s.cO[w];
+      p[4 * (n + i) + w] = s.mv ? s.cO[w] : s.oO[w];
       p[4 * (2 * n + i) + w] = s.cA[w] | s.oA[w];
       p[4 * (3 * n + i) + w] = s.cB[w] | s.oB[w];
     }
   }
-  BSG_HD static bool terminal(const State& s) { return s.term != 0; }
-  BSG_HD static int outcome(const State& s) { return (int)s.outc; }
-  BSG_HD static bool won(const State& s) { return s.outc < 2u; }  // the last mover won
+  BSG_HD static bool terminal(const State& s) { return s.win != 0; }
+  BSG_HD static bool won(const State& s) { return s.win != 0; }
   BSG_HD static int mover(const State& s) { return (int)s.mv; }
+  BSG_HD static int outcome(const State& s) { return s.win ? (int)(s.mv ^ 1u) : kOutcomeNone; }
 
-  // One ring of neighbours of every cell in f (hex.cc:206-222 for a whole set at once).
-  BSG_HD static void dilate(const u32 f[4], const Tables& t, u32 out[4]) {
-    u32 a[4], b[4];
+  // One ring of neighbours of every cell in f (hex.cc:206-222 for a whole set at once),
+  // restricted to `within`.  East/west neighbours are 128-bit shifts by one with the column
+  // wrap masked; the two northern neighbours (r-1,c), (r-1,c+1) are (f | east) shifted one row
+  // down in index, the two southern ones (f | west) shifted one row up.
+  BSG_HD static void dilate_within(const u32 f[4], const u32 within[4], u32 out[4]) {
+    u32 E[4], W[4], fe[4], fw[4];
+    E[0] = f[0] << 1; E[1] = fshl(f[0], f[1], 1); E[2] = fshl(f[1], f[2], 1); E[3] = fshl(f[2], f[3], 1);
+    W[0] = fshr(f[0], f[1], 1); W[1] = fshr(f[1], f[2], 1); W[2] = fshr(f[2], f[3], 1); W[3] = f[3] >> 1;
 #pragma unroll
-    for (int w = 0; w < 4; ++w) { a[w] = f[w] & t.notColLast[w]; b[w] = f[w] & t.notCol0[w]; }
-    // +1 and -(N-1) from a; -1 and +(N-1) from b; +N and -N from f
-    out[0] = (a[0] << 1) | fshr(a[0], a[1], N - 1) | fshr(b[0], b[1], 1) | (b[0] << (N - 1)) |
-             (f[0] << N) | fshr(f[0], f[1], N);
-    out[1] = fshl(a[0], a[1], 1) | fshr(a[1], a[2], N - 1) | fshr(b[1], b[2], 1) |
-             fshl(b[0], b[1], N - 1) | fshl(f[0], f[1], N) | fshr(f[1], f[2], N);
-    out[2] = fshl(a[1], a[2], 1) | fshr(a[2], a[3], N - 1) | fshr(b[2], b[3], 1) |
-             fshl(b[1], b[2], N - 1) | fshl(f[1], f[2], N) | fshr(f[2], f[3], N);
-    out[3] = fshl(a[2], a[3], 1) | (a[3] >> (N - 1)) | (b[3] >> 1) | fshl(b[2], b[3], N - 1) |
-             fshl(f[2], f[3], N) | (f[3] >> N);
+    for (int w = 0; w < 4; ++w) {
+      E[w] &= not_col0(w);          // a stone in the last column has no east neighbour
+      W[w] &= not_col_last(w);      // a stone in column 0 has no west neighbour
+      fe[w] = f[w] | E[w];
+      fw[w] = f[w] | W[w];
+    }
+    u32 nn[4], ss[4];
+    nn[0] = fshr(fe[0], fe[1], N); nn[1] = fshr(fe[1], fe[2], N); nn[2] = fshr(fe[2], fe[3], N); nn[3] = fe[3] >> N;
+    ss[0] = fw[0] << N; ss[1] = fshl(fw[0], fw[1], N); ss[2] = fshl(fw[1], fw[2], N); ss[3] = fshl(fw[2], fw[3], N);
+#pragma unroll
+    for (int w = 0; w < 4; ++w) out[w] = (E[w] | W[w] | nn[w] | ss[w]) & within[w];
   }
-
-  // hex.cc:149-184 for the mover: label from edges + neighbours, win, or flood.
-  BSG_HD static void place(State& s, int cell, const Tables& t) {
-    int cw = cell >> 5;
-    u32 bit = 1u << (cell & 31);
-    u32 m[4], nb[4];
+  // The pending flood (hex.cc:158-182, one ring per call): label the frontier, then the next
+  // frontier is its ring of neighbours among the stones that are still plain.
+  BSG_HD static void ring(State& s) {
+    u32 P[4];
 #pragma unroll
-    for (int w = 0; w < 4; ++w) { m[w] = (w == cw) ? bit : 0u; nb[w] = t.nb[cell][w]; }
+    for (int w = 0; w < 4; ++w) {
+      s.oA[w] |= s.F[w] & s.fA;
+      s.oB[w] |= s.F[w] & ~s.fA;
+      P[w] = s.oO[w] & ~(s.oA[w] | s.oB[w]);
+    }
+    u32 d[4];
+    dilate_within(s.F, P, d);
+#pragma unroll
+    for (int w = 0; w < 4; ++w) s.F[w] = d[w];
+  }
+  BSG_HD static bool pending(const State& s) { return (s.F[0] | s.F[1] | s.F[2] | s.F[3]) != 0; }
+  BSG_HD static void finish(State& s) { while (pending(s)) ring(s); }
+
+  // hex.cc:149-184 for the mover: label from edges + neighbours, win, or start the flood.
+  BSG_HD static void place(State& s, int cell, const Tables& t) {
+    u32 nb[4], m[4];
+#pragma unroll
+    for (int w = 0; w < 4; ++w) { nb[w] = t.nb[cell][w]; m[w] = t.one[cell][w]; }
     u32 flags = nb[3] >> (28 + 2 * s.mv);  // bit 0: on edge A, bit 1: on edge B
     u32 hitA = 0, hitB = 0;
 #pragma unroll
     for (int w = 0; w < 4; ++w) { hitA |= nb[w] & s.cA[w]; hitB |= nb[w] & s.cB[w]; }
     bool tA = (hitA != 0) || (flags & 1u), tB = (hitB != 0) || (flags & 2u);
-    bool win = tA && tB;
-    u32 add[4];
-#pragma unroll
-    for (int w = 0; w < 4; ++w) { s.occ[w] |= m[w]; add[w] = m[w]; }
-    if ((tA || tB) && !win) {
-      // first ring from the table, later rings by dilation, through plain stones only
-      u32 fr[4], any = 0;
-#pragma unroll
-      for (int w = 0; w < 4; ++w) { fr[w] = nb[w] & s.cP[w]; any |= fr[w]; }
-      while (any) {
-        u32 d[4];
-#pragma unroll
-        for (int w = 0; w < 4; ++w) { s.cP[w] &= ~fr[w]; add[w] |= fr[w]; }
-        dilate(fr, t, d);
-        any = 0;
-#pragma unroll
-        for (int w = 0; w < 4; ++w) { fr[w] = d[w] & s.cP[w]; any |= fr[w]; }
-      }
-    }
-    u32 toA = tA ? 0xFFFFFFFFu : 0u, toB = tB ? 0xFFFFFFFFu : 0u;  // win: both
-    u32 toP = (tA || tB) ? 0u : 0xFFFFFFFFu;
-    u32 na[4], nbb[4], np[4];
+    u32 toA = tA ? 0xFFFFFFFFu : 0u, toB = tB ? 0xFFFFFFFFu : 0u;
+    u32 go = (tA != tB) ? 0xFFFFFFFFu : 0u;   // exactly one label: it spreads through plain stones
+    u32 nO[4], nA[4], nB[4];
 #pragma unroll
     for (int w = 0; w < 4; ++w) {
-      na[w] = s.cA[w] | (add[w] & toA);
-      nbb[w] = s.cB[w] | (add[w] & toB);
-      np[w] = s.cP[w] | (add[w] & toP);
-      s.cA[w] = s.oA[w]; s.cB[w] = s.oB[w]; s.cP[w] = s.oP[w];
-      s.oA[w] = na[w]; s.oB[w] = nbb[w]; s.oP[w] = np[w];
+      nO[w] = s.cO[w] | m[w];
+      nA[w] = s.cA[w] | (m[w] & toA);
+      nB[w] = s.cB[w] | (m[w] & toB);
+      u32 plain = nO[w] & ~(nA[w] | nB[w]);
+      u32 f = nb[w] & plain & go;
+      // pass the turn: the mover's sets become the o side
+      s.cO[w] = s.oO[w]; s.cA[w] = s.oA[w]; s.cB[w] = s.oB[w];
+      s.oO[w] = nO[w]; s.oA[w] = nA[w]; s.oB[w] = nB[w];
+      s.F[w] = f;
     }
-    s.term = win ? 1u : 0u;
-    s.outc = win ? s.mv : (u32)kOutcomeNone;
+    s.fA = toA;
+    s.win = (tA && tB) ? 1u : 0u;
     s.mv ^= 1u;
+    s.left -= 1u;
+  }
+  BSG_HD static u32 empty_word(const State& s, int w) { return ~(s.cO[w] | s.oO[w]) & board_word(w); }
+  // k-th (ascending) empty cell, k < left.  Word by prefix popcounts, then halves of the word,
+  // then a byte table.
+  BSG_HD static int select_empty(const State& s, u32 k, const Tables& tab) {
+    u32 e0 = empty_word(s, 0), e1 = empty_word(s, 1), e2 = empty_word(s, 2), e3 = empty_word(s, 3);
+    u32 c0 = (u32)popc32(e0), c1 = c0 + (u32)popc32(e1), c2 = c1 + (u32)popc32(e2);
+    bool g0 = k >= c0, g1 = k >= c1, g2 = k >= c2;
+    u32 x = g2 ? e3 : (g1 ? e2 : (g0 ? e1 : e0));
+    u32 below = g2 ? c2 : (g1 ? c1 : (g0 ? c0 : 0u));
+    u32 pos = g2 ? 96u : (g1 ? 64u : (g0 ? 32u : 0u));
+    u32 kk = k - below;
+    u32 h = (u32)popc32(x & 0xFFFFu);
+    if (kk >= h) { kk -= h; x >>= 16; pos += 16; }
+    h = (u32)popc32(x & 0xFFu);
+    if (kk >= h) { kk -= h; x >>= 8; pos += 8; }
+    return (int)((pos + tab.sel8[x & 0xFFu][kk & 7u]) & 127u);
   }
   BSG_HD static u32 step(State& s, u32 r, const Tables& tab, int& action) {
-    u32 e0 = ~s.occ[0], e1 = ~s.occ[1], e2 = ~s.occ[2], e3 = ~s.occ[3];  // hex.cc:186-196
-    int c0 = popc32(e0), c1 = c0 + popc32(e1), c2 = c1 + popc32(e2), n = c2 + popc32(e3);
-    int k = (int)fastmod(r, (u32)n, tab.modM[n & 127]);
-    int w = (k >= c0) + (k >= c1) + (k >= c2);
-    u32 x = w == 0 ? e0 : (w == 1 ? e1 : (w == 2 ? e2 : e3));
-    int kk = k - (w == 0 ? 0 : (w == 1 ? c0 : (w == 2 ? c1 : c2)));
-    int cell = (32 * w + select32(x, kk)) & 127;
+    u32 n = s.left;                                        // hex.cc:186-196: every empty cell
+    u32 k = fastmod(r, n, tab.modM[n & 127]);
+    int cell = select_empty(s, k, tab);
     action = cell;
     place(s, cell, tab);
-    return (u32)n;
+    return n;
   }
   BSG_HD static int legal(const State& s, int* out) {
     if (terminal(s)) return 0;
     int n = 0;
-    for (int c = 0; c < kCells; ++c) if (!((s.occ[c >> 5] >> (c & 31)) & 1u)) out[n++] = c;
+    for (int c = 0; c < kCells; ++c) if ((empty_word(s, c >> 5) >> (c & 31)) & 1u) out[n++] = c;
     return n;
   }
   BSG_HD static bool apply(State& s, int a, const Tables& t) {
-    if (terminal(s) || a < 0 || a >= kCells || ((s.occ[a >> 5] >> (a & 31)) & 1u)) return false;
+    if (terminal(s) || a < 0 || a >= kCells || !((empty_word(s, a >> 5) >> (a & 31)) & 1u)) return false;
     place(s, a, t);
+    finish(s);      // host helpers flood synchronously
     return true;
   }
   BSG_HD static u32 legal_bit(const State& s, int a) {
-    return (!s.term && !((s.occ[a >> 5] >> (a & 31)) & 1u)) ? 1u : 0u;
+    return (!s.win && ((empty_word(s, a >> 5) >> (a & 31)) & 1u)) ? 1u : 0u;
+  }
+  // Per-word absolute sets for the observation: black/white x {A only, B only, plain, both}.
+  BSG_HD static void abs_sets(const State& s, int w, u32& bA, u32& bB, u32& bO, u32& wA, u32& wB, u32& wO) {
+    bA = s.mv ? s.oA[w] : s.cA[w]; bB = s.mv ? s.oB[w] : s.cB[w]; bO = s.mv ? s.oO[w] : s.cO[w];
+    wA = s.mv ? s.cA[w] : s.oA[w]; wB = s.mv ? s.cB[w] : s.oB[w]; wO = s.mv ? s.cO[w] : s.oO[w];
   }
   // hex.cc:266-277: plane = CellState + 4: 0 WhiteWin, 1 WhiteWest, 2 WhiteEast, 3 White,
   // 4 Empty, 5 Black, 6 BlackSouth, 7 BlackNorth, 8 BlackWin; same for both observers.
-  BSG_HD static u32 obs_bit(const State& s, int player, int idx) {
-    (void)player;
-    int plane = idx / kCells, cell = idx - plane * kCells;
-    int w = cell >> 5, b = cell & 31;
-    u32 bA = (s.mv ? s.oA[w] : s.cA[w]) >> b & 1u, bB = (s.mv ? s.oB[w] : s.cB[w]) >> b & 1u;
-    u32 bP = (s.mv ? s.oP[w] : s.cP[w]) >> b & 1u;
-    u32 wA = (s.mv ? s.cA[w] : s.oA[w]) >> b & 1u, wB = (s.mv ? s.cB[w] : s.oB[w]) >> b & 1u;
-    u32 wP = (s.mv ? s.cP[w] : s.oP[w]) >> b & 1u;
+  BSG_HD static u32 plane_word(const State& s, int plane, int w) {
+    u32 bA, bB, bO, wA, wB, wO;
+    abs_sets(s, w, bA, bB, bO, wA, wB, wO);
     switch (plane) {
       case 0: return wA & wB;
-      case 1: return wA & ~wB & 1u;
-      case 2: return wB & ~wA & 1u;
-      case 3: return wP;
-      case 4: return (~s.occ[w] >> b) & 1u;
-      case 5: return bP;
-      case 6: return bB & ~bA & 1u;
-      case 7: return bA & ~bB & 1u;
+      case 1: return wA & ~wB;
+      case 2: return wB & ~wA;
+      case 3: return wO & ~(wA | wB);
+      case 4: return empty_word(s, w);
+      case 5: return bO & ~(bA | bB);
+      case 6: return bB & ~bA;
+      case 7: return bA & ~bB;
       default: return bA & bB;
     }
   }
+  BSG_HD static u32 obs_bit(const State& s, int player, int idx) {
+    (void)player;
+    int plane = idx / kCells, cell = idx - plane * kCells;
+    return (plane_word(s, plane, cell >> 5) >> (cell & 31)) & 1u;
+  }
   BSG_HD static void obs_words(const State& s, int player, u32* out) {
     (void)player;
-    u32 m[9][4];
-#pragma unroll
-    for (int w = 0; w < 4; ++w) {
-      u32 bA = s.mv ? s.oA[w] : s.cA[w], bB = s.mv ? s.oB[w] : s.cB[w], bP = s.mv ? s.oP[w] : s.cP[w];
-      u32 wA = s.mv ? s.cA[w] : s.oA[w], wB = s.mv ? s.cB[w] : s.oB[w], wP = s.mv ? s.cP[w] : s.oP[w];
-      m[0][w] = wA & wB; m[1][w] = wA & ~wB; m[2][w] = wB & ~wA; m[3][w] = wP;
-      m[4][w] = ~s.occ[w];
-      m[5][w] = bP; m[6][w] = bB & ~bA; m[7][w] = bA & ~bB; m[8][w] = bA & bB;
-    }
 #pragma unroll
     for (int w = 0; w < kObsWords; ++w) out[w] = 0;
 #pragma unroll
@@ -726,14 +784,15 @@ struct HexT {
       const int off = p * kCells, wi = off >> 5, sh = off & 31;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        if (wi + j < kObsWords) out[wi + j] |= m[p][j] << sh;
-        if (sh != 0 && wi + j + 1 < kObsWords) out[wi + j + 1] |= m[p][j] >> ((32 - sh) & 31);
+        u32 m = plane_word(s, p, j);
+        if (wi + j < kObsWords) out[wi + j] |= m << sh;
+        if (sh != 0 && wi + j + 1 < kObsWords) out[wi + j + 1] |= m >> ((32 - sh) & 31);
       }
     }
   }
   BSG_HD static void mask_words(const State& s, u32* out) {
 #pragma unroll
-    for (int w = 0; w < 4; ++w) out[w] = s.term ? 0u : ~s.occ[w];
+    for (int w = 0; w < 4; ++w) out[w] = s.win ? 0u : empty_word(s, w);
   }
 };
 typedef HexT<11> Hex;

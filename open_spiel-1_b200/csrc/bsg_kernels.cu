@@ -77,6 +77,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
   u32 lid = 0, t = 0, limit = 0xFFFFFFFFu, root_mv = 0;
   u32 my_steps = 0, my_done = 0, my_stuck = 0;
   int my_ret = 0;
+  u32 rnew[4] = {0, 0, 0, 0}, rold[4] = {0, 0, 0, 0}, nblk = 0xFFFFFFFFu;   // kAsync draws (below)
   const u32 out = a.out_flags;   // which optional outputs exist (uniform)
 
   for (;;) {
@@ -116,6 +117,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         u32 root = a.rollouts == 1 ? lid : lid / a.rollouts;
         G::load(s, a.roots, a.n_roots, a.root0 + root);
         t = 0;
+        nblk = 0xFFFFFFFFu;
         root_mv = (u32)G::mover(s);
         if (kFull) {
           limit = a.io.max_steps > 0 ? (u32)a.io.max_steps : 0xFFFFFFFFu;
@@ -138,25 +140,56 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
 
     const unsigned long long pid = a.first_playout + lid;
     u32 rr[4];
-    philox4x32_10((u32)pid, (u32)(pid >> 32), t >> 2, 0u, a.keys, rr);
+    if constexpr (!G::kAsync) {
+      philox4x32_10((u32)pid, (u32)(pid >> 32), t >> 2, 0u, a.keys, rr);
+    } else {
+      // A lane of an asynchronous game does not move in every iteration, so the lanes of a warp
+      // are at different phases of their Philox blocks.  The block computation stays convergent
+      // by running every four iterations for ALL lanes on the block a lane will need next,
+      // ceil(t / 4); the block it may still be inside, floor(t / 4), is kept beside it.  In the
+      // next four iterations a lane draws at most t .. t + 3: always one of the two.
+      if ((t >> 2) == nblk) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) rold[i] = rnew[i];
+      }
+      nblk = (t + 3u) >> 2;
+      philox4x32_10((u32)pid, (u32)(pid >> 32), nblk, 0u, a.keys, rnew);
+    }
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      u32 r = rr[j];
-      if (kFull) {
-        if (a.io.r_table && live) r = a.io.r_table[(size_t)lid * a.io.r_stride + min(t, (u32)a.io.r_stride - 1)];
-        if (live) prev = s;
+      u32 r, can = live;   // can: this lane makes a move in this iteration
+      if constexpr (!G::kAsync) {
+        r = rr[j];
+      } else {
+        G::ring(s);
+        can = G::pending(s) ? 0u : live;
+        const bool in_new = (t >> 2) == nblk;
+        const u32 d0 = in_new ? rnew[0] : rold[0], d1 = in_new ? rnew[1] : rold[1];
+        const u32 d2 = in_new ? rnew[2] : rold[2], d3 = in_new ? rnew[3] : rold[3];
+        const u32 lo2 = (t & 1u) ? d1 : d0, hi2 = (t & 1u) ? d3 : d2;
+        r = (t & 2u) ? hi2 : lo2;
       }
-      int action;
-      const u32 nlegal = G::step(s, r, tab, action);
-      if (G::kCanStick && live && nlegal == 0) {  // non-terminal state without a legal action
+      if (kFull) {
+        if (a.io.r_table && can) r = a.io.r_table[(size_t)lid * a.io.r_stride + min(t, (u32)a.io.r_stride - 1)];
+        if (can) prev = s;
+      }
+      int action = 0;
+      u32 nlegal = 1;
+      if constexpr (!G::kAsync) {
+        nlegal = G::step(s, r, tab, action);   // finished lanes run dead steps: no divergence
+      } else {
+        if (can) nlegal = G::step(s, r, tab, action);
+      }
+      if (G::kCanStick && can && nlegal == 0) {  // non-terminal state without a legal action
         live = 0;
+        can = 0;
         my_stuck += 1;
         fin_term = 0;
         fin_win = 0;
         if (kFull && a.io.final_states) G::store(prev, a.io.final_states, a.n_playouts, lid);
       }
       if (kFull) {
-        if (live) {
+        if (can) {
           if (a.io.actions && t < (u32)a.io.actions_stride)
             a.io.actions[(size_t)lid * a.io.actions_stride + t] = (int16_t)action;
           t += 1;
@@ -176,9 +209,9 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         // fin_win was cleared at the claim and can only be set by the (single) ending move
         const u32 term = G::terminal(s) ? 1u : 0u;
         const u32 won = G::won(s) ? 1u : 0u;
-        fin_win |= live & won;
-        t += live;
-        live &= term ^ 1u;
+        fin_win |= can & won;
+        t += can;
+        live &= (can & term) ^ 1u;
       }
     }
   }
