@@ -9,7 +9,8 @@ behind the search loop the reference calls it from (a
           * reference C++ MCTSBot + RandomRolloutEvaluator (algorithms/mcts.cc), one bot per
             host thread (oracle/_ref/libspiel_ref.so);
           * this repo: MCTSBot mirror + GpuRolloutEvaluator, one leaf per kernel launch
-            (leaf_batch = 1, exactly the reference's call pattern) and with batched leaves.
+            (leaf_batch = 1, exactly the reference's call pattern) and with batched leaves;
+          * this repo: the native host tree (NativeMCTSBot, csrc/bsg_mcts.cuh), same search.
   cfg5  connect_four, 256 rollouts/leaf, root-parallel over the ranks of the job with ONE
         int64 all-reduce per search step (parallel.RootParallelMCTS): simulations/s and
         playouts/s of one move search from the empty board, whole job.
@@ -75,6 +76,12 @@ def run_cfg1(args, bsg, local):
     selfplay(bsg, "tic_tac_toe", bot_of, 1)  # warm-up
     mv, sims, secs = selfplay(bsg, "tic_tac_toe", bot_of, args.games)
     out["ours_python_tree_leaf_batch_%d" % lb] = sims / secs
+  for lb in (1, args.leaf_batch):
+    bot_of = lambda game: bsg.NativeMCTSBot(game, 2.0, args.sims, eng, n_rollouts=1, solve=True,
+                                            seed=7, shuffle_seed=3, leaf_batch=lb)
+    selfplay(bsg, "tic_tac_toe", bot_of, 1)
+    mv, sims, secs = selfplay(bsg, "tic_tac_toe", bot_of, max(args.games, 20))
+    out["ours_native_tree_leaf_batch_%d" % lb] = sims / secs
   eng.close()
   return out
 
@@ -93,20 +100,22 @@ def run_cfg5(args, bsg, local, rank, world):
   total_sims = args.sims5 * world                      # weak scaling: fixed sims per rank
   ev = bsg.GpuRolloutEvaluator(eng, n_rollouts=n_roll, seed=11)
   rp = bsg.RootParallelMCTS(game, 2.0, total_sims, ev, sims_per_step=args.sims_per_step,
-                            solve=True, seed=5, leaf_batch=args.leaf_batch, device=dev)
+                            solve=True, seed=5, leaf_batch=args.leaf_batch, device=dev,
+                            native=args.native)
   state = game.new_initial_state()
   rp.mcts_search(state)                                # warm-up search
   torch.cuda.synchronize(dev)
   if dist is not None:
     dist.barrier()
-  steps0, ar0 = ev.total_steps, rp.all_reduces
+  steps0, ar0 = (rp.bot.total_steps if args.native else ev.total_steps), rp.all_reduces
   t0 = time.perf_counter()
   root = rp.mcts_search(state)
   torch.cuda.synchronize(dev)
   secs = time.perf_counter() - t0
   stats = np.array([[c.action, c.explore_count, int(round(c.total_reward * n_roll))]
                     for c in sorted(root.children, key=lambda c: c.action)], np.int64)
-  t = torch.tensor([secs, float(ev.total_steps - steps0)], dtype=torch.float64, device=dev)
+  steps_now = rp.bot.total_steps if args.native else ev.total_steps
+  t = torch.tensor([secs, float(steps_now - steps0)], dtype=torch.float64, device=dev)
   same = True
   if dist is not None:
     mx = t.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
@@ -124,6 +133,7 @@ def run_cfg5(args, bsg, local, rank, world):
   out = {"config": "cfg5: connect_four root-parallel MCTS from the empty board, %d rollouts/leaf, "
                    "%d simulations/move/rank x %d rank(s), %d sims per all-reduce step, leaf_batch %d"
                    % (n_roll, args.sims5, world, args.sims_per_step, args.leaf_batch),
+         "tree": "native (csrc/bsg_mcts.cuh)" if args.native else "python mirror",
          "n_gpus": world, "simulations": visits, "seconds": secs,
          "simulations_per_s": visits / secs, "playouts_per_s": visits * n_roll / secs,
          "game_steps_per_s": game_steps / secs, "all_reduces": rp.all_reduces - ar0,
@@ -136,8 +146,8 @@ def run_cfg5(args, bsg, local, rank, world):
       threads = os.cpu_count() or 1
       r = Reference()
       # one search of the same shape per thread (the reference has no root-parallel mode)
-      secs_r, mv, sims, _ = r.mcts_selfplay("connect_four", 1, max(64, args.sims5 // 16), n_roll,
-                                            threads=threads)
+      # bounded sample: one self-play game of 256 simulations/move per thread (a few seconds)
+      secs_r, mv, sims, _ = r.mcts_selfplay("connect_four", 1, 256, n_roll, threads=threads)
       out["reference_cpp_all_threads_simulations_per_s"] = sims / secs_r
       out["host_threads"] = threads
   eng.close()
@@ -152,6 +162,7 @@ def main():
   ap.add_argument("--sims5", type=int, default=16384, help="cfg5 simulations per move per rank")
   ap.add_argument("--sims-per-step", type=int, default=4096)
   ap.add_argument("--leaf-batch", type=int, default=256)
+  ap.add_argument("--native", type=int, default=1, help="cfg5: 1 = native host tree, 0 = Python mirror")
   args = ap.parse_args()
   rank, world, local = dist_env()
   import torch

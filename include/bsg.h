@@ -152,6 +152,41 @@ int bsg_observations_host(bsg_engine* e, const void* states_host, int64_t n,
                           const uint8_t* players_host, float* obs_host,
                           uint8_t* legal_mask_host);
 
+/* ---- native MCTS tree with batched leaf evaluation.
+ * Stands in for MCTSBot::MCTSearch (open_spiel/algorithms/mcts.cc:255-428;
+ * python/algorithms/mcts.py:347-443) when the evaluator is the rollout evaluator of this
+ * engine: UCT descent (SearchNode::UCTValue, mcts.cc:95-105), uniform shuffled priors,
+ * MCTS-Solver backups — on the host, as in the reference — with up to `leaf_batch` leaves
+ * gathered by virtual visits and evaluated by ONE launch of the playout kernel
+ * (`n_rollouts` playouts per leaf).  leaf_batch = 1 is the reference's one-leaf-per-call
+ * order.  Playout ids advance exactly as in the Python GpuRolloutEvaluator (next_playout),
+ * priors are shuffled by Fisher-Yates over bsg_draw(shuffle_seed, counter, 0): with the same
+ * seeds the Python mirror (mcts.MCTSBot + PhiloxShuffle) builds the identical tree. */
+typedef struct bsg_mcts bsg_mcts;
+int bsg_mcts_create(bsg_engine* e, double uct_c, int solve, int n_rollouts, int leaf_batch,
+                    uint64_t eval_seed, uint64_t shuffle_seed, bsg_mcts** out);
+void bsg_mcts_destroy(bsg_mcts* m);
+const char* bsg_mcts_last_error(bsg_mcts* m);
+/* Runs `simulations` simulations from the packed root state (capacity-1 packed state on the
+ * host).  resume != 0 continues the tree of the previous call (same root). */
+int bsg_mcts_search(bsg_mcts* m, const void* root_packed_host, int64_t simulations, int resume);
+/* Creates the root's children without a simulation (root-parallel merge on a rank with no budget). */
+int bsg_mcts_expand_root(bsg_mcts* m, const void* root_packed_host);
+/* Root statistics after a search: returns the number of root children (in the tree's shuffled
+ * order) and fills up to `capacity` entries.  outcome[i] is the proven value for the root
+ * mover (-1, 0, +1) or 2 when not proven. */
+int bsg_mcts_root_children(bsg_mcts* m, int capacity, int64_t* actions, int64_t* visits,
+                           double* total_reward, int32_t* outcome);
+/* info_out: {root explore_count, root proven (0/1), root proven value for player 0, nodes,
+ * game steps played by the evaluator, kernel launches, next playout id, root mover}. */
+int bsg_mcts_info(bsg_mcts* m, double info_out[8]);
+/* Overwrites the statistics of the root child with this action (root-parallel merge,
+ * SURVEY.md section 8e); outcome as above.  root_explore < 0 leaves the root count alone. */
+int bsg_mcts_set_root_child(bsg_mcts* m, int64_t action, int64_t visits, double total_reward,
+                            int32_t outcome);
+int bsg_mcts_set_root_explore(bsg_mcts* m, int64_t root_explore);
+int bsg_mcts_set_next_playout(bsg_mcts* m, uint64_t next_playout);
+
 /* Integer-issue microbenchmark used for the roofline denominator (bench.py): runs `iters`
  * dependent-chain iterations of `ilp` independent 32-bit ops per thread on every SM and
  * returns thread-instructions per second.  kind: 0 = LOP3/IADD3 mix (ALU pipe), 1 = IMAD

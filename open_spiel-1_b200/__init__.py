@@ -15,9 +15,9 @@ from . import _cabi  # noqa: F401  (raises ImportError when libbsg.so is missing
 from .engine import Engine, game_id, pack_histories, draw
 from .evaluator import Evaluator, GpuRolloutEvaluator
 from .spiel import load_game, Game, State, GameType, PlayerId
-from .mcts import MCTSBot, SearchNode
+from .mcts import MCTSBot, SearchNode, NativeMCTSBot, PhiloxShuffle
 from .parallel import RootParallelMCTS, ShardedPlayouts, shard_range
 
 __all__ = ["Engine", "game_id", "pack_histories", "draw", "Evaluator", "GpuRolloutEvaluator",
-           "load_game", "Game", "State", "GameType", "PlayerId", "MCTSBot", "SearchNode",
+           "load_game", "Game", "State", "GameType", "PlayerId", "MCTSBot", "SearchNode", "NativeMCTSBot", "PhiloxShuffle",
            "RootParallelMCTS", "ShardedPlayouts", "shard_range"]

@@ -75,6 +75,17 @@ def _load():
       "bsg_playouts_host": (ctypes.c_int, [vp, vp, i64, i32, u64, u64, vp, vp, vp]),
       "bsg_observations_host": (ctypes.c_int, [vp, vp, i64, vp, vp, vp]),
       "bsg_int_peak": (ctypes.c_int, [vp, ctypes.c_int, ctypes.c_int, vp]),
+      "bsg_mcts_create": (ctypes.c_int, [vp, ctypes.c_double, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                          u64, u64, ctypes.POINTER(vp)]),
+      "bsg_mcts_destroy": (None, [vp]),
+      "bsg_mcts_last_error": (ctypes.c_char_p, [vp]),
+      "bsg_mcts_search": (ctypes.c_int, [vp, vp, i64, ctypes.c_int]),
+      "bsg_mcts_expand_root": (ctypes.c_int, [vp, vp]),
+      "bsg_mcts_root_children": (ctypes.c_int, [vp, ctypes.c_int, vp, vp, vp, vp]),
+      "bsg_mcts_info": (ctypes.c_int, [vp, vp]),
+      "bsg_mcts_set_root_child": (ctypes.c_int, [vp, i64, i64, ctypes.c_double, i32]),
+      "bsg_mcts_set_root_explore": (ctypes.c_int, [vp, i64]),
+      "bsg_mcts_set_next_playout": (ctypes.c_int, [vp, u64]),
   }
   for name, (res, args) in sig.items():
     fn = getattr(lib, name)

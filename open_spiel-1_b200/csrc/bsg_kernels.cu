@@ -20,6 +20,7 @@
 #include <string>
 
 #include "bsg_host.cuh"
+#include "bsg_mcts.cuh"
 
 namespace bsg {
 
@@ -773,6 +774,86 @@ int bsg_observations_host(bsg_engine* e, const void* states_host, int64_t n, con
   if (obs_host) BSG_CUDA(e, cudaMemcpyAsync(obs_host, d_obs, (size_t)n * bsg_observation_size(e->game) * 4, cudaMemcpyDeviceToHost, st));
   if (mask_host) BSG_CUDA(e, cudaMemcpyAsync(mask_host, d_mask, (size_t)n * bsg_num_distinct_actions(e->game), cudaMemcpyDeviceToHost, st));
   BSG_CUDA(e, cudaStreamSynchronize(st));
+  return BSG_OK;
+}
+
+// ---- native MCTS tree (bsg_mcts.cuh)
+struct bsg_mcts { bsg::MctsBase* t = nullptr; };
+
+int bsg_mcts_create(bsg_engine* e, double uct_c, int solve, int n_rollouts, int leaf_batch,
+                    uint64_t eval_seed, uint64_t shuffle_seed, bsg_mcts** out) {
+  if (!e || !out || n_rollouts < 1 || leaf_batch < 1) return BSG_ERR_BAD_ARG;
+  *out = nullptr;
+  bsg::MctsBase* t = nullptr;
+  int rc = dispatch_device_game(e->game, MctsCreateOp{&t});
+  if (rc != BSG_OK) return rc;
+  t->engine = e; t->uct_c = uct_c; t->solve = solve; t->n_rollouts = n_rollouts;
+  t->leaf_batch = leaf_batch; t->eval_seed = eval_seed; t->shuffle_seed = shuffle_seed;
+  bsg_mcts* m = new (std::nothrow) bsg_mcts();
+  if (!m) { delete t; return BSG_ERR_BAD_ARG; }
+  m->t = t;
+  *out = m;
+  return BSG_OK;
+}
+void bsg_mcts_destroy(bsg_mcts* m) {
+  if (!m) return;
+  delete m->t;
+  delete m;
+}
+const char* bsg_mcts_last_error(bsg_mcts* m) {
+  return (m && m->t) ? (m->t->err.empty() ? bsg_last_error(m->t->engine) : m->t->err.c_str()) : "null tree";
+}
+int bsg_mcts_search(bsg_mcts* m, const void* root, int64_t simulations, int resume) {
+  if (!m || !m->t || !root || simulations < 0) return BSG_ERR_BAD_ARG;
+  return m->t->search(root, simulations, resume);
+}
+int bsg_mcts_expand_root(bsg_mcts* m, const void* root) {
+  if (!m || !m->t || !root) return BSG_ERR_BAD_ARG;
+  return m->t->expand_root(root);
+}
+int bsg_mcts_root_children(bsg_mcts* m, int capacity, int64_t* actions, int64_t* visits,
+                           double* reward, int32_t* outcome) {
+  if (!m || !m->t || m->t->nodes.empty()) return BSG_ERR_BAD_ARG;
+  const bsg::MctsNode& root = m->t->nodes[0];
+  for (int i = 0; i < root.n_children && i < capacity; ++i) {
+    const bsg::MctsNode& c = m->t->nodes[root.first_child + i];
+    if (actions) actions[i] = c.action;
+    if (visits) visits[i] = c.explore;
+    if (reward) reward[i] = c.reward;
+    if (outcome) outcome[i] = c.has_outcome ? (int32_t)(c.player == 0 ? c.out0 : -c.out0) : 2;
+  }
+  return root.n_children;
+}
+int bsg_mcts_info(bsg_mcts* m, double info[8]) {
+  if (!m || !m->t || !info || m->t->nodes.empty()) return BSG_ERR_BAD_ARG;
+  const bsg::MctsNode& root = m->t->nodes[0];
+  info[0] = (double)root.explore; info[1] = root.has_outcome; info[2] = root.out0;
+  info[3] = (double)m->t->nodes.size(); info[4] = (double)m->t->total_game_steps;
+  info[5] = (double)m->t->kernel_launches; info[6] = (double)m->t->next_playout;
+  info[7] = (double)m->t->root_player;
+  return BSG_OK;
+}
+int bsg_mcts_set_root_child(bsg_mcts* m, int64_t action, int64_t visits, double reward, int32_t outcome) {
+  if (!m || !m->t || m->t->nodes.empty()) return BSG_ERR_BAD_ARG;
+  const bsg::MctsNode& root = m->t->nodes[0];
+  for (int i = 0; i < root.n_children; ++i) {
+    bsg::MctsNode& c = m->t->nodes[root.first_child + i];
+    if (c.action != action) continue;
+    c.explore = visits;
+    c.reward = reward;
+    if (outcome != 2) { c.has_outcome = 1; c.out0 = c.player == 0 ? (double)outcome : -(double)outcome; }
+    return BSG_OK;
+  }
+  return BSG_ERR_ILLEGAL_ACTION;
+}
+int bsg_mcts_set_root_explore(bsg_mcts* m, int64_t n) {
+  if (!m || !m->t || m->t->nodes.empty() || n < 0) return BSG_ERR_BAD_ARG;
+  m->t->nodes[0].explore = n;
+  return BSG_OK;
+}
+int bsg_mcts_set_next_playout(bsg_mcts* m, uint64_t next) {
+  if (!m || !m->t) return BSG_ERR_BAD_ARG;
+  m->t->next_playout = next;
   return BSG_OK;
 }
 

@@ -75,6 +75,26 @@ class SearchNode(object):
     return self.to_str(None)
 
 
+class PhiloxShuffle(object):
+  """`random_state` for MCTSBot whose shuffle() is the Fisher-Yates of the native tree
+  (csrc/bsg_mcts.cuh): j = bsg_draw(seed, counter, 0) mod (i + 1) for i = n-1 .. 1.  With it the
+  Python mirror and `NativeMCTSBot` build identical trees (the mirror is the specification)."""
+
+  def __init__(self, seed):
+    self.seed = int(seed)
+    self.counter = 0
+
+  def shuffle(self, items):
+    from .engine import draw
+    for i in range(len(items) - 1, 0, -1):
+      j = draw(self.seed, self.counter, 0) % (i + 1)
+      self.counter += 1
+      items[i], items[j] = items[j], items[i]
+
+  def dirichlet(self, alpha):
+    raise NotImplementedError("PhiloxShuffle has no Dirichlet noise")
+
+
 class MCTSBot(object):
   """UCT / PUCT search with MCTS-Solver backups (mcts.py:199-443)."""
 
@@ -237,3 +257,148 @@ class MCTSBot(object):
         self._backup(path, values[vi], False, root_player)
         vi += 1
     return len(pending)
+
+
+class NativeMCTSBot(object):
+  """MCTSBot whose tree lives in the C-ABI library (csrc/bsg_mcts.cuh): same search as
+  `MCTSBot(game, uct_c, max_simulations, GpuRolloutEvaluator(engine, n_rollouts, seed),
+  solve, random_state=PhiloxShuffle(shuffle_seed), leaf_batch=leaf_batch)` — identical tree,
+  visit for visit — without the Python interpreter between two leaves.  The evaluator is the
+  engine's rollout evaluator by construction (its rollouts run on the GPU, up to `leaf_batch`
+  leaves per kernel launch); child selection is UCT (mcts.py:124-133).
+
+  mcts_search returns a `SearchNode` root whose children carry the tree's statistics; a root
+  passed back in (`root=`, as parallel.RootParallelMCTS does after merging) has its children's
+  statistics written into the native tree before the search resumes."""
+
+  def __init__(self, game, uct_c, max_simulations, engine, n_rollouts=1, solve=True, seed=0,
+               shuffle_seed=0, leaf_batch=1, verbose=False):
+    import ctypes
+    from . import _cabi as C
+    self._C, self._ct = C, ctypes
+    self._game = game
+    self.engine = engine
+    self.uct_c = float(uct_c)
+    self.max_simulations = int(max_simulations)
+    self.n_rollouts = int(n_rollouts)
+    self.solve = bool(solve)
+    self.leaf_batch = max(1, int(leaf_batch))
+    self.verbose = verbose
+    h = ctypes.c_void_p()
+    C.check(C.lib.bsg_mcts_create(engine._h, self.uct_c, int(self.solve), self.n_rollouts,
+                                  self.leaf_batch, int(seed), int(shuffle_seed), ctypes.byref(h)),
+            engine._h)
+    self._h = h
+    self._cap = game.num_distinct_actions()
+    self._last_root = None
+
+  def close(self):
+    if getattr(self, "_h", None):
+      self._C.lib.bsg_mcts_destroy(self._h)
+      self._h = None
+
+  def __del__(self):
+    try:
+      self.close()
+    except Exception:
+      pass
+
+  # evaluator-compatible bookkeeping (parallel.RootParallelMCTS offsets the playout ids per rank)
+  @property
+  def next_playout(self):
+    return int(self.info()[6])
+
+  @next_playout.setter
+  def next_playout(self, value):
+    self._C.check(self._C.lib.bsg_mcts_set_next_playout(self._h, int(value)))
+
+  @property
+  def total_steps(self):
+    return int(self.info()[4])
+
+  def info(self):
+    out = np.zeros(8, np.float64)
+    self._C.check(self._C.lib.bsg_mcts_info(self._h, out.ctypes.data))
+    return out
+
+  def restart_at(self, state):
+    pass
+
+  def _packed(self, state):
+    from .evaluator import _packed_of
+    return np.ascontiguousarray(_packed_of(self.engine.gid, state))
+
+  def _read_root(self, state):
+    C = self._C
+    n = self._cap
+    actions, visits = np.zeros(n, np.int64), np.zeros(n, np.int64)
+    reward, outcome = np.zeros(n, np.float64), np.zeros(n, np.int32)
+    k = C.check(C.lib.bsg_mcts_root_children(self._h, n, actions.ctypes.data, visits.ctypes.data,
+                                              reward.ctypes.data, outcome.ctypes.data))
+    info = self.info()
+    player = int(info[7])
+    root = SearchNode(None, player, 1)
+    root.explore_count = int(info[0])
+    if info[1]:
+      root.outcome = [float(info[2]), -float(info[2])]
+    for i in range(k):
+      ch = SearchNode(int(actions[i]), player, 1.0 / k)
+      ch.explore_count = int(visits[i])
+      ch.total_reward = float(reward[i])
+      if outcome[i] != 2:
+        v = float(outcome[i])
+        ch.outcome = [v, -v] if player == 0 else [-v, v]
+      root.children.append(ch)
+    root.total_reward = float(sum(c.total_reward for c in root.children))
+    return root
+
+  def _write_root(self, root):
+    C = self._C
+    for ch in root.children:
+      oc = 2 if ch.outcome is None else int(round(ch.outcome[ch.player]))
+      C.check(C.lib.bsg_mcts_set_root_child(self._h, int(ch.action), int(ch.explore_count),
+                                            float(ch.total_reward), oc))
+    C.check(C.lib.bsg_mcts_set_root_explore(self._h, int(root.explore_count)))
+
+  def expand_root(self, root, state):
+    if not root.children and not state.is_terminal():
+      packed = self._packed(state)
+      self._C.check(self._C.lib.bsg_mcts_expand_root(self._h, packed.ctypes.data), self.engine._h)
+      fresh = self._read_root(state)
+      root.children = fresh.children
+
+  def mcts_search(self, state, root=None, simulations=None):
+    C = self._C
+    budget = self.max_simulations if simulations is None else int(simulations)
+    packed = self._packed(state)
+    resume = 0
+    if root is not None and root is self._last_root:
+      self._write_root(root)
+      resume = 1
+    rc = C.lib.bsg_mcts_search(self._h, packed.ctypes.data, budget, resume)
+    if rc < 0:
+      raise RuntimeError("bsg: " + C.lib.bsg_mcts_last_error(self._h).decode())
+    new_root = self._read_root(state)
+    if root is not None and resume:
+      # keep the caller's object alive: copy the fresh statistics into it
+      root.explore_count, root.total_reward = new_root.explore_count, new_root.total_reward
+      root.outcome, root.children = new_root.outcome, new_root.children
+      new_root = root
+    self._last_root = new_root
+    return new_root
+
+  def step_with_policy(self, state):
+    t0 = time.time()
+    root = self.mcts_search(state)
+    best = root.best_child()
+    if self.verbose:
+      secs = max(time.time() - t0, 1e-9)
+      print("Finished {} sims in {:.3f} secs, {:.1f} sims/s".format(
+          root.explore_count, secs, root.explore_count / secs))
+    action = best.action
+    policy = [(a, 1.0 if a == action else 0.0)
+              for a in state.legal_actions(state.current_player())]
+    return policy, action
+
+  def step(self, state):
+    return self.step_with_policy(state)[1]

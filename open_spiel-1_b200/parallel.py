@@ -22,7 +22,7 @@ collective is latency-bound and NVLink bandwidth is irrelevant), "gloo" in the C
 """
 import numpy as np
 
-from .mcts import MCTSBot, SearchNode
+from .mcts import MCTSBot, NativeMCTSBot, SearchNode
 
 
 def shard_range(n, rank, world):
@@ -103,11 +103,13 @@ class RootParallelMCTS:
       (n_rollouts for a rollout evaluator).
     leaf_batch: leaves gathered per kernel launch inside a rank (mcts.MCTSBot.leaf_batch).
     device: torch device of the collective buffer (None = CPU, for gloo).
+    native: run each rank's tree in the C-ABI library (mcts.NativeMCTSBot) instead of the
+      Python mirror; `evaluator` must then be a GpuRolloutEvaluator.
   """
 
   def __init__(self, game, uct_c, max_simulations, evaluator, sims_per_step=None, solve=True,
                seed=0, reward_scale=None, leaf_batch=1, child_selection_fn=SearchNode.uct_value,
-               device=None, group=None):
+               device=None, group=None, native=False):
     self.rank, self.world = _world(group)
     self.group = group
     self.device = device
@@ -122,12 +124,20 @@ class RootParallelMCTS:
       reward_scale = getattr(evaluator, "n_rollouts", 1)
     self.reward_scale = int(reward_scale)
     self.num_actions = game.num_distinct_actions()
-    self.bot = MCTSBot(game, uct_c, self.local_simulations, evaluator, solve=solve,
-                       random_state=np.random.RandomState(seed + self.rank),
-                       child_selection_fn=child_selection_fn, leaf_batch=leaf_batch)
-    # disjoint playout-id ranges per rank keep the ranks' Philox streams independent
-    if hasattr(evaluator, "next_playout"):
-      evaluator.next_playout += self.rank << 40
+    if native:
+      # the tree in the C-ABI library (csrc/bsg_mcts.cuh); `evaluator` supplies engine,
+      # n_rollouts and seed, its rollouts run inside the native search
+      self.bot = NativeMCTSBot(game, uct_c, self.local_simulations, evaluator.engine,
+                               n_rollouts=evaluator.n_rollouts, solve=solve, seed=evaluator.seed,
+                               shuffle_seed=seed + self.rank, leaf_batch=leaf_batch)
+      self.bot.next_playout = evaluator.next_playout + (self.rank << 40)
+    else:
+      self.bot = MCTSBot(game, uct_c, self.local_simulations, evaluator, solve=solve,
+                         random_state=np.random.RandomState(seed + self.rank),
+                         child_selection_fn=child_selection_fn, leaf_batch=leaf_batch)
+      # disjoint playout-id ranges per rank keep the ranks' Philox streams independent
+      if hasattr(evaluator, "next_playout"):
+        evaluator.next_playout += self.rank << 40
     self.all_reduces = 0
     self.last_root = None
 

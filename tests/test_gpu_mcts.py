@@ -121,3 +121,67 @@ def test_best_child_ordering(bsg):
   assert best([a, b]) is b                  # anything unproven beats a proven loss
   a, b = node(10, 4, None), node(10, 5, None)
   assert best([a, b]) is b                  # equal visits: higher reward
+
+
+def _root_stats(root):
+  return sorted((c.action, c.explore_count, c.total_reward,
+                 None if c.outcome is None else tuple(c.outcome)) for c in root.children)
+
+
+@pytest.mark.parametrize("game,moves,leaf_batch", [
+    ("tic_tac_toe", 0, 1), ("tic_tac_toe", 2, 8), ("connect_four", 6, 1), ("connect_four", 9, 16),
+    ("breakthrough", 10, 8), ("hex", 30, 4)])
+def test_native_tree_equals_python_mirror(bsg, game, moves, leaf_batch):
+  """The native host tree (csrc/bsg_mcts.cuh) builds the same tree as the Python mirror — the
+  specification, itself a restatement of mcts.py:199-443 — visit for visit: same shuffles
+  (PhiloxShuffle), same playout ids, same UCT arithmetic, same solver backups; also when a
+  search is resumed."""
+  g = bsg.load_game(game)
+  state = g.new_initial_state()
+  rng = np.random.RandomState(5)
+  for _ in range(moves):
+    la = state.legal_actions()
+    state.apply_action(la[rng.randint(len(la))])
+  sims, n_roll = 300, 8
+  eng = bsg.Engine(game, 0)
+  ev = bsg.GpuRolloutEvaluator(eng, n_rollouts=n_roll, seed=77)
+  py = bsg.MCTSBot(g, UCT_C, sims, ev, solve=True, random_state=bsg.PhiloxShuffle(13),
+                   leaf_batch=leaf_batch)
+  nat = bsg.NativeMCTSBot(g, UCT_C, sims, eng, n_rollouts=n_roll, solve=True, seed=77,
+                          shuffle_seed=13, leaf_batch=leaf_batch)
+  r_py = py.mcts_search(state)
+  r_nat = nat.mcts_search(state)
+  assert r_nat.explore_count == r_py.explore_count
+  assert _root_stats(r_nat) == _root_stats(r_py)
+  assert nat.next_playout == ev.next_playout
+  assert [c.action for c in r_nat.children] == [c.action for c in r_py.children]   # same shuffle
+  assert r_nat.best_child().action == r_py.best_child().action
+  # resume both with 100 more simulations
+  r_py = py.mcts_search(state, root=r_py, simulations=100)
+  r_nat = nat.mcts_search(state, root=r_nat, simulations=100)
+  assert _root_stats(r_nat) == _root_stats(r_py)
+  nat.close()
+  eng.close()
+
+
+def test_native_tree_solver_known_answers(bsg):
+  """mcts_test.py:115-153 on the native tree: proven win, proven loss, proven draw."""
+  g = bsg.load_game("tic_tac_toe")
+  eng = bsg.Engine("tic_tac_toe", 0)
+  # x to move after x(4) o(1) x(0) o(8): x wins (e.g. 6 or 3 threatens twice); solver proves +1
+  state = g.new_initial_state()
+  for a in [4, 1, 0, 8]:
+    state.apply_action(a)
+  nat = bsg.NativeMCTSBot(g, UCT_C, 5000, eng, n_rollouts=1, solve=True, seed=1, shuffle_seed=2,
+                          leaf_batch=4)
+  root = nat.mcts_search(state)
+  assert root.outcome is not None and root.outcome[state.current_player()] == 1.0
+  best = root.best_child()
+  assert best.outcome is not None and best.outcome[best.player] == 1.0
+  # the python mirror agrees on the proven value
+  ev = bsg.GpuRolloutEvaluator(eng, n_rollouts=1, seed=1)
+  py = bsg.MCTSBot(g, UCT_C, 5000, ev, solve=True, random_state=bsg.PhiloxShuffle(2), leaf_batch=4)
+  r_py = py.mcts_search(state)
+  assert r_py.outcome == root.outcome
+  nat.close()
+  eng.close()
