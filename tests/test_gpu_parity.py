@@ -190,13 +190,21 @@ def test_native_rng_win_rates_within_binomial_ci(game, checker, torch):
   eng.close()
 
 
-def test_connect_four_full_size_properties(torch):
-  """BASELINE cfg2 size (16 Mi playouts): size-independent properties instead of an oracle run."""
-  from open_spiel_1_b200.roots import make_roots
-  eng = _engine("connect_four")
+@pytest.mark.parametrize("game,n,max_len,min_len", [
+    ("connect_four", 1 << 24, 42, 1),     # BASELINE cfg2: 16 Mi playouts
+    ("breakthrough", 1 << 22, 209, 1),    # cfg3: 4 Mi playouts per GPU
+    ("hex", 1 << 20, 121, 1),             # cfg4: 1 Mi playouts per GPU
+])
+def test_full_size_properties(game, n, max_len, min_len, torch):
+  """BASELINE configuration sizes: size-independent properties instead of an oracle run —
+  checksum of checksums (totals vs per-playout outputs), every playout terminal, length
+  bounds, idempotence, invariance under splitting the launch, and a 2000-playout sample
+  re-played through the host step hook."""
+  from open_spiel_1_b200.roots import make_roots, ROOT_DEPTHS
+  eng = _engine(game)
   dev = eng.torch_device
-  n = 1 << 24
-  states, _ = make_roots(eng, n, 8, 20, seed=20240611 + 2)
+  dmin, dmax = ROOT_DEPTHS[game]
+  states, _ = make_roots(eng, n, dmin, dmax, seed=20240611 + 2)
   ret0 = torch.zeros(n, dtype=torch.int8, device=dev)
   length = torch.zeros(n, dtype=torch.uint8, device=dev)
   term = torch.zeros(n, dtype=torch.uint8, device=dev)
@@ -208,36 +216,50 @@ def test_connect_four_full_size_properties(torch):
   assert int(length.to(torch.int64).sum()) == t[1]          # checksum of per-playout lengths
   assert int(ret0.to(torch.int64).sum()) == t[2]
   assert bool(term.all())                                    # every playout reached a terminal
-  assert int(length.max()) <= 42 and int(length.min()) >= 1
-  # idempotence / schedule independence: the same launch again, and a split launch with
-  # first_playout offsets, reproduce the same per-playout results
+  assert int(length.max()) <= max_len and int(length.min()) >= min_len
+  if game != "connect_four":
+    assert bool((ret0 != 0).all())                           # no draws in breakthrough / hex
+  # idempotence / schedule independence: a split launch with first_playout offsets reproduces
+  # the same per-playout results (every SoA plane must be sliced for the second half)
   ret0b = torch.zeros_like(ret0)
   lengthb = torch.zeros_like(length)
   half = n // 2
-  sb = eng.state_bytes
-  eng.playouts(states[:half * sb], half, 1, seed=1, first_playout=0, ret0=ret0b[:half], length=lengthb[:half])
-  eng.playouts(states[half * sb:], half, 1, seed=1, first_playout=half, ret0=ret0b[half:], length=lengthb[half:])
-  torch.cuda.synchronize()
-  assert torch.equal(ret0, ret0b) and torch.equal(length, lengthb)
-  # sample of the full-size run against the oracle
-  oracle = Oracle()
   import open_spiel_1_b200 as bsg
   from open_spiel_1_b200 import _cabi as C
   host = states.cpu().numpy()
-  idx = np.random.RandomState(0).randint(0, n, size=2000)
+  sb = eng.state_bytes
+  planes = {"connect_four": [8], "breakthrough": [16, 4], "hex": [16, 16, 16, 16]}[game]
+  assert sum(planes) == sb
+
+  def take(lo, hi):
+    parts, off = [], 0
+    for pb in planes:
+      parts.append(host[off + lo * pb: off + hi * pb])
+      off += n * pb
+    return np.concatenate(parts)
+
+  lo_half = eng.to_device(take(0, half))
+  hi_half = eng.to_device(take(half, n))
+  eng.playouts(lo_half, half, 1, seed=1, first_playout=0, ret0=ret0b[:half], length=lengthb[:half])
+  eng.playouts(hi_half, n - half, 1, seed=1, first_playout=half, ret0=ret0b[half:], length=lengthb[half:])
+  torch.cuda.synchronize()
+  assert torch.equal(ret0, ret0b) and torch.equal(length, lengthb)
+  # sample of the full-size run re-played on the host through the very step function the
+  # kernels run (a board alone has no history for the oracle; the step hook itself is checked
+  # against the oracle in tests/test_host_logic.py)
+  import ctypes
+  gid = eng.gid
+  idx = np.random.RandomState(0).randint(0, n, size=2000 if game == "connect_four" else 300)
   g_len, g_ret = length.cpu().numpy(), ret0.cpu().numpy()
   for i in idx:
-    one = host[i * sb:(i + 1) * sb].copy()
-    # rebuild a history for the oracle is impossible from a board alone; replay the board through
-    # the host step hook instead and compare only lengths/returns with the kernel
+    one = take(int(i), int(i) + 1).copy()
     acts = 0
-    import ctypes
     while True:
       cur, tm, r0 = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
-      C.check(C.lib.bsg_host_state_info(1, one.ctypes.data, 1, 0, ctypes.byref(cur), ctypes.byref(tm), ctypes.byref(r0)))
+      C.check(C.lib.bsg_host_state_info(gid, one.ctypes.data, 1, 0, ctypes.byref(cur), ctypes.byref(tm), ctypes.byref(r0)))
       if tm.value:
         break
-      C.check(C.lib.bsg_host_replay_step(1, one.ctypes.data, 1, 0, bsg.draw(1, int(i), acts), None))
+      C.check(C.lib.bsg_host_replay_step(gid, one.ctypes.data, 1, 0, bsg.draw(1, int(i), acts), None))
       acts += 1
     assert acts == g_len[i] and r0.value == g_ret[i]
   eng.close()
