@@ -26,7 +26,8 @@ namespace bsg {
 
 // =========================================================================================
 // tic_tac_toe — reference: open_spiel/games/tic_tac_toe.cc
-//   x = player 0 (moves first, tic_tac_toe.cc:55-65), o = player 1.  Two 9-bit masks.
+//   x = player 0 (moves first, tic_tac_toe.cc:55-65), o = player 1.  Two 9-bit masks, kept
+//   relative to the mover; move selection, cell and line test come from shared-memory tables.
 //   packed: one u32 = x | o << 9 | terminal << 18 | outcome << 19.
 // =========================================================================================
 struct TicTacToe {
@@ -37,26 +38,60 @@ struct TicTacToe {
   BSG_HD static int plane_bytes(int p) { (void)p; return 4; }
   static constexpr bool kCanStick = false;  // a non-terminal state always has a legal action
   static constexpr bool kAsync = false;     // a step completes within the step (see HexT)
-  struct State { u32 x, o, term, outc; };
-  struct Tables { u32 modM[16]; };
-  static void fill_tables(Tables& t) { for (u32 n = 0; n < 16; ++n) t.modM[n] = modM_entry(n); }
+  struct State {
+    u32 cur, opp;   // marks of the player to move / of the other player (9-bit masks)
+    u32 left;       // empty cells; parity = player to move (x = player 0 first, 9 cells)
+    u32 win;        // the last move completed a line
+  };
+  // One 24-byte row per 9-bit mask e of empty cells (tic_tac_toe.cc:90-100):
+  //   word 0 = floor(2^32 / n), word 1 = -n (n = popc e), bytes 8..16 = the k-th empty cell,
+  //   ascending.  line[b] = 1 when the 9-bit mask b contains one of the eight lines
+  //   (tic_tac_toe.cc:108-118).  A step is then three shared-memory loads and ~8 ALU
+  //   instructions (no popcount, no rank-select, no shifts over the eight lines).
+  struct Tables {
+    u32 row[512][6];
+    unsigned char line[512];
+  };
+  static void fill_tables(Tables& t) {
+    for (u32 e = 0; e < 512; ++e) {
+      unsigned char* cells = (unsigned char*)&t.row[e][2];
+      for (int i = 0; i < 16; ++i) cells[i] = 0;
+      u32 n = 0;
+      for (u32 c = 0; c < 9; ++c) if ((e >> c) & 1) cells[n++] = (unsigned char)c;
+      u32 nn = n ? n : 1;   // e = 0 only on finished lanes running dead steps
+      t.row[e][0] = modM_entry(nn);
+      t.row[e][1] = 0u - nn;
+      t.line[e] = has_line(e) ? 1 : 0;
+    }
+  }
 
-  BSG_HD static void init(State& s) { s.x = 0; s.o = 0; s.term = 0; s.outc = kOutcomeNone; }
+  BSG_HD static void init(State& s) { s.cur = 0; s.opp = 0; s.left = 9; s.win = 0; }
   BSG_HD static void load(State& s, const void* base, int64_t n, int64_t i) {
     (void)n;
     u32 w = ((const u32*)base)[i];
-    s.x = w & 0x1FF; s.o = (w >> 9) & 0x1FF; s.term = (w >> 18) & 1; s.outc = (w >> 19) & 3;
+    u32 x = w & 0x1FF, o = (w >> 9) & 0x1FF;
+    u32 stones = (u32)(popc32(x) + popc32(o));
+    u32 mv = stones & 1u;
+    s.cur = mv ? o : x;
+    s.opp = mv ? x : o;
+    s.left = 9u - stones;
+    s.win = (((w >> 18) & 1u) && ((w >> 19) & 3u) < 2u) ? 1u : 0u;
   }
   BSG_HD static void store(const State& s, void* base, int64_t n, int64_t i) {
     (void)n;
-    ((u32*)base)[i] = s.x | (s.o << 9) | (s.term << 18) | (s.outc << 19);
+    u32 mv = (u32)mover(s);
+    u32 x = mv ? s.opp : s.cur, o = mv ? s.cur : s.opp;
+    ((u32*)base)[i] = x | (o << 9) | ((terminal(s) ? 1u : 0u) << 18) | ((u32)outcome(s) << 19);
   }
-  BSG_HD static bool terminal(const State& s) { return s.term != 0; }
-  BSG_HD static int outcome(const State& s) { return (int)s.outc; }
-  BSG_HD static bool won(const State& s) { return s.outc < 2u; }  // the last mover won
-  BSG_HD static int mover(const State& s) { return (popc32(s.x) + popc32(s.o)) & 1; }
+  BSG_HD static bool terminal(const State& s) { return (s.win != 0) || (s.left == 0); }
+  BSG_HD static bool won(const State& s) { return s.win != 0; }  // the last mover won
+  BSG_HD static int mover(const State& s) { return (int)((s.left & 1u) ^ 1u); }  // 9 is odd
+  BSG_HD static int outcome(const State& s) {
+    return s.win ? (mover(s) ^ 1) : (s.left == 0 ? kOutcomeDraw : kOutcomeNone);
+  }
 
-  // tic_tac_toe.cc:108-118, the eight lines, as shifts over one 9-bit mask.
+  // tic_tac_toe.cc:108-118, the eight lines, as shifts over one 9-bit mask (table builder and
+  // host helpers; the kernels read Tables::line).
   BSG_HD static bool has_line(u32 b) {
     u32 rows = b & (b >> 1) & (b >> 2) & 0x49u;
     u32 cols = b & (b >> 3) & (b >> 6) & 0x7u;
@@ -65,51 +100,67 @@ struct TicTacToe {
     return (rows | cols | diag | anti) != 0;
   }
   // tic_tac_toe.cc:80-88 + :139-141 (win for the mover only; full board ends the game).
-  BSG_HD static void place(State& s, int cell) {
-    int m = mover(s);
-    u32 b = (m ? s.o : s.x) | (1u << cell);
-    if (m) s.o = b; else s.x = b;
-    bool win = has_line(b);
-    bool full = ((s.x | s.o) & 0x1FFu) == 0x1FFu;
-    s.term = (win || full) ? 1u : 0u;
-    s.outc = win ? (u32)m : (full ? (u32)kOutcomeDraw : (u32)kOutcomeNone);
+  BSG_HD static void place(State& s, u32 bit, u32 win) {
+    u32 b = s.cur | bit;
+    s.win = win;
+    s.cur = s.opp;
+    s.opp = b;
+    s.left -= 1u;
   }
   BSG_HD static u32 step(State& s, u32 r, const Tables& tab, int& action) {
-    u32 empty = ~(s.x | s.o) & 0x1FFu;  // tic_tac_toe.cc:90-100, ascending cell order
-    u32 n = (u32)popc32(empty);
-    u32 k = fastmod(r, n, tab.modM[n & 15]);
-    int cell = select32(empty, (int)k) & 15;
-    action = cell;
-    place(s, cell);
-    return n;
+    const u32 e = ~(s.cur | s.opp) & 0x1FFu;  // tic_tac_toe.cc:90-100, ascending cell order
+#if defined(__CUDA_ARCH__)
+    const u32 base = (u32)__cvta_generic_to_shared(&tab);
+    const u32 off = base + e * 24u;
+    u32 M, negn, cell, win;
+    asm("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(M), "=r"(negn) : "r"(off));
+    u32 rem = umulhi32(r, M) * negn + r;
+    u32 k = umin32(rem, rem + negn);                 // r mod n
+    asm("ld.shared.u8 %0, [%1+8];" : "=r"(cell) : "r"(off + k));
+    const u32 bit = 1u << cell;
+    asm("ld.shared.u8 %0, [%1+%2];" : "=r"(win) : "r"(base + (s.cur | bit)), "n"(512 * 24));
+#else
+    const u32* row = tab.row[e];
+    const u32 negn = row[1];
+    u32 rem = umulhi32(r, row[0]) * negn + r;
+    u32 k = umin32(rem, rem + negn);
+    const u32 cell = ((const unsigned char*)&row[2])[k];
+    const u32 bit = 1u << cell;
+    const u32 win = tab.line[s.cur | bit];
+#endif
+    action = (int)cell;
+    place(s, bit, win);
+    return 0u - negn;
   }
   BSG_HD static int legal(const State& s, int* out) {
     if (terminal(s)) return 0;
     int n = 0;
-    for (int c = 0; c < 9; ++c) if (!(((s.x | s.o) >> c) & 1)) out[n++] = c;
+    for (int c = 0; c < 9; ++c) if (!(((s.cur | s.opp) >> c) & 1)) out[n++] = c;
     return n;
   }
   BSG_HD static bool apply(State& s, int a) {
-    if (terminal(s) || a < 0 || a >= 9 || (((s.x | s.o) >> a) & 1)) return false;
-    place(s, a);
+    if (terminal(s) || a < 0 || a >= 9 || (((s.cur | s.opp) >> a) & 1)) return false;
+    place(s, 1u << a, has_line(s.cur | (1u << a)) ? 1u : 0u);
     return true;
   }
   BSG_HD static u32 legal_bit(const State& s, int a) {  // State::LegalActionsMask, spiel.h:244-252
-    return (!s.term && !(((s.x | s.o) >> a) & 1u)) ? 1u : 0u;
+    return (!terminal(s) && !(((s.cur | s.opp) >> a) & 1u)) ? 1u : 0u;
   }
   // tic_tac_toe.cc:165-175: plane = raw CellState (0 empty, 1 nought = player 1, 2 cross).
   BSG_HD static u32 obs_bit(const State& s, int player, int idx) {
     (void)player;
     int plane = idx / 9, cell = idx - plane * 9;
-    u32 m = plane == 0 ? ~(s.x | s.o) : (plane == 1 ? s.o : s.x);
+    u32 x = mover(s) ? s.opp : s.cur, o = mover(s) ? s.cur : s.opp;
+    u32 m = plane == 0 ? ~(x | o) : (plane == 1 ? o : x);
     return (m >> cell) & 1u;
   }
   BSG_HD static void obs_words(const State& s, int player, u32* out) {
     (void)player;
-    out[0] = (~(s.x | s.o) & 0x1FFu) | (s.o << 9) | (s.x << 18);
+    u32 x = mover(s) ? s.opp : s.cur, o = mover(s) ? s.cur : s.opp;
+    out[0] = (~(x | o) & 0x1FFu) | (o << 9) | (x << 18);
   }
   BSG_HD static void mask_words(const State& s, u32* out) {
-    out[0] = s.term ? 0u : (~(s.x | s.o) & 0x1FFu);
+    out[0] = terminal(s) ? 0u : (~(s.cur | s.opp) & 0x1FFu);
   }
 };
 
