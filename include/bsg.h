@@ -124,6 +124,15 @@ typedef struct bsg_playout_io {
   int32_t final_before_terminal;/* != 0: a playout that ended writes its last non-terminal state */
   uint64_t* totals;             /* u64[4] += {playouts, steps, sum ret0 (two's complement),
                                    stuck lanes}; caller zeroes */
+  /* Trajectory log (the AlphaZero actor's record of every decision point, alpha_zero.py:196-228):
+   * the state BEFORE move t of playout p is written as packed state number
+   * state_log_off[p] + t of a packed SoA buffer with capacity state_log_cap.  Offsets are the
+   * exclusive prefix sum of the lengths of an earlier identical launch (playouts are
+   * deterministic), so the log is dense; bsg_observations turns it into observation planes
+   * and legal masks. */
+  void* state_log;
+  int64_t state_log_cap;
+  const int64_t* state_log_off;
 } bsg_playout_io;
 
 /* The hot path.  Stands in for RandomRolloutEvaluator::Evaluate's playout loop

@@ -13,11 +13,11 @@ The CUDA extension (libbsg.so) is mandatory: importing this package without it r
 """
 from . import _cabi  # noqa: F401  (raises ImportError when libbsg.so is missing)
 from .engine import Engine, game_id, pack_histories, draw
-from .evaluator import Evaluator, GpuRolloutEvaluator
+from .evaluator import Evaluator, GpuRolloutEvaluator, AlphaZeroEvaluator
 from .spiel import load_game, Game, State, GameType, PlayerId
 from .mcts import MCTSBot, SearchNode, NativeMCTSBot, PhiloxShuffle
 from .parallel import RootParallelMCTS, ShardedPlayouts, shard_range
 
-__all__ = ["Engine", "game_id", "pack_histories", "draw", "Evaluator", "GpuRolloutEvaluator",
+__all__ = ["Engine", "game_id", "pack_histories", "draw", "Evaluator", "GpuRolloutEvaluator", "AlphaZeroEvaluator",
            "load_game", "Game", "State", "GameType", "PlayerId", "MCTSBot", "SearchNode", "NativeMCTSBot", "PhiloxShuffle",
            "RootParallelMCTS", "ShardedPlayouts", "shard_range"]

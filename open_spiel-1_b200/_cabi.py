@@ -38,6 +38,9 @@ class PlayoutIO(ctypes.Structure):
       ("final_states", vp),
       ("final_before_terminal", i32),
       ("totals", vp),
+      ("state_log", vp),
+      ("state_log_cap", i64),
+      ("state_log_off", vp),
   ]
 
 

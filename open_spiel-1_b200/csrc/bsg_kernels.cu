@@ -172,7 +172,10 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
       }
       if (kFull) {
         if (a.io.r_table && can) r = a.io.r_table[(size_t)lid * a.io.r_stride + min(t, (u32)a.io.r_stride - 1)];
-        if (can) prev = s;
+        if (can) {
+          prev = s;
+          if (a.io.state_log) G::store(s, a.io.state_log, a.io.state_log_cap, a.io.state_log_off[lid] + t);
+        }
       }
       int action = 0;
       u32 nlegal = 1;
@@ -470,7 +473,7 @@ struct PlayoutOp {
   bsg_engine* e; PlayoutArgs a; cudaStream_t st;
   template <class G> int operator()() const {
     const bsg_playout_io& io = a.io;
-    bool full = io.max_steps > 0 || io.step_limit || io.r_table || io.actions || io.final_states;
+    bool full = io.max_steps > 0 || io.step_limit || io.r_table || io.actions || io.final_states || io.state_log;
     return full ? launch_playouts<G, true>(e, a, st) : launch_playouts<G, false>(e, a, st);
   }
 };
@@ -651,6 +654,8 @@ int bsg_playouts(bsg_engine* e, const void* roots, int64_t n_roots, int32_t roll
   if (io) a.io = *io;
   if (a.io.r_table && a.io.r_stride < 1) return fail(e, BSG_ERR_BAD_ARG, "r_table needs r_stride >= 1");
   if (a.io.actions && a.io.actions_stride < 1) return fail(e, BSG_ERR_BAD_ARG, "actions needs actions_stride >= 1");
+  if (a.io.state_log && (!a.io.state_log_off || a.io.state_log_cap < 1))
+    return fail(e, BSG_ERR_BAD_ARG, "state_log needs state_log_off and state_log_cap >= 1");
   BSG_CUDA(e, cudaSetDevice(e->device));
   return dispatch_device_game(e->game, PlayoutOp{e, a, (cudaStream_t)stream});
 }

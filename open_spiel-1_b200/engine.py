@@ -30,6 +30,11 @@ def state_bytes(gid):
   return C.check(C.lib.bsg_state_bytes(gid))
 
 
+def plane_bytes(gid):
+  """Element sizes of the packed SoA planes of a game."""
+  return {0: [4], 1: [8], 2: [16, 4], 3: [16, 16, 16, 16], 4: [16, 16, 16, 16]}[gid]
+
+
 def num_distinct_actions(gid):
   return C.check(C.lib.bsg_num_distinct_actions(gid))
 
@@ -137,7 +142,8 @@ class Engine:
   def playouts(self, roots, n_roots, rollouts=1, seed=0, first_playout=0, *, ret0=None,
                length=None, terminal=None, actions=None, root_sum_ret0=None,
                root_sum_steps=None, totals=None, max_steps=0, step_limit=None, r_table=None,
-               final_states=None, final_before_terminal=False, stream=None):
+               final_states=None, final_before_terminal=False, state_log=None,
+               state_log_off=None, stream=None):
     """Launches n_roots * rollouts random playouts (bsg_playouts).  All tensors are device
     tensors owned by the caller; see include/bsg.h for their meaning.  Asynchronous."""
     io = C.PlayoutIO()
@@ -155,6 +161,9 @@ class Engine:
     io.final_states = self._p(final_states)
     io.final_before_terminal = 1 if final_before_terminal else 0
     io.totals = self._p(totals)
+    io.state_log = self._p(state_log)
+    io.state_log_cap = int(state_log.numel() // self.state_bytes) if state_log is not None else 0
+    io.state_log_off = self._p(state_log_off)
     C.check(C.lib.bsg_playouts(self._h, self._p(roots), int(n_roots), int(rollouts),
                                int(seed) & (2**64 - 1), int(first_playout), ctypes.byref(io),
                                self._stream_ptr(stream)), self._h)
@@ -176,6 +185,41 @@ class Engine:
             self._h)
     self.launches += 1 + (1 if legal_mask is not None else 0)
     return out, legal_mask
+
+  def trajectories(self, roots, n_roots, rollouts=1, seed=0, first_playout=0, want_mask=True,
+                   want_actions=True):
+    """Self-play records of every decision point of n_roots * rollouts random playouts, as
+    the AlphaZero actor keeps them (python/algorithms/alpha_zero/alpha_zero.py:196-228):
+    observation of the player to move, legal-action mask, the action taken and the final
+    return for player 0.  Everything stays on the device: launch 1 plays the playouts and
+    returns their lengths, an exclusive prefix sum gives dense offsets, launch 2 replays them
+    (playouts are deterministic functions of (seed, playout id, root)) writing the packed
+    state before every move, and the batched writer expands the log.
+
+    Returns a dict of device tensors: obs [T, C, H, W] f32, mask [T, A] u8 (or None),
+    actions [T] int64 (or None), playout [T] / step [T] int64 (owner and move number of each
+    record), ret0 [n] int8, length [n] int64, offsets [n] int64, states (packed log, capacity T)."""
+    torch = _torch()
+    dev = self.torch_device
+    n = int(n_roots) * int(rollouts)
+    ret0 = torch.zeros(n, dtype=torch.int8, device=dev)
+    length8 = torch.zeros(n, dtype=torch.uint8, device=dev)
+    self.playouts(roots, n_roots, rollouts, seed, first_playout, ret0=ret0, length=length8)
+    length = length8.to(torch.int64)
+    offsets = torch.cumsum(length, 0) - length
+    total = int(length.sum().item())
+    states = torch.zeros(max(total, 1) * self.state_bytes, dtype=torch.uint8, device=dev)
+    acts = None
+    if want_actions:
+      acts = torch.full((n, max(int(length8.max().item()), 1)), -1, dtype=torch.int16, device=dev)
+    self.playouts(roots, n_roots, rollouts, seed, first_playout, state_log=states,
+                  state_log_off=offsets, actions=acts)
+    owner = torch.repeat_interleave(torch.arange(n, device=dev), length)
+    step = torch.arange(total, device=dev) - offsets[owner]
+    obs, mask = self.observations(states, total, None, want_mask=want_mask) if total else (None, None)
+    actions = acts[owner, step].to(torch.int64) if want_actions and total else None
+    return {"obs": obs, "mask": mask, "actions": actions, "playout": owner, "step": step,
+            "ret0": ret0, "length": length, "offsets": offsets, "states": states, "total": total}
 
   # ---- host-buffer entry points (copies inside the call; synchronous)
   def playouts_host(self, packed, n_roots, rollouts=1, seed=0, first_playout=0,

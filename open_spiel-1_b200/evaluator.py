@@ -94,3 +94,92 @@ class GpuRolloutEvaluator(Evaluator):
     """Equal probability for every legal action, in ascending action order (mcts.py:76-82)."""
     legal_actions = state.legal_actions(state.current_player())
     return [(action, 1.0 / len(legal_actions)) for action in legal_actions]
+
+
+class AlphaZeroEvaluator(Evaluator):
+  """`AlphaZeroEvaluator(game, model, cache_size)` of the reference
+  (python/algorithms/alpha_zero/evaluator.py:38-83) over the batched GPU observation writer.
+
+  The reference builds `state.observation_tensor()` and `state.legal_actions_mask()` as Python
+  lists on the host, stacks a singleton batch and calls `model.inference(obs, mask)` which
+  returns `(value [B, 1], policy [B, NumDistinctActions])` (alpha_zero/model.py).  Here the
+  state crosses as its packed bitboards, the observation planes and the legal mask are written
+  on the device by `bsg_observations` and handed to the model as DEVICE torch tensors
+  `obs [B, C, H, W] float32`, `mask [B, A] bool` — no host copy of the planes.  `model` is any
+  object with that `inference` method (returning torch tensors or numpy arrays).  Results are
+  cached per packed state like the reference's LRU cache (evaluator.py:56-75).
+
+  evaluate() returns `[value, -value]` exactly as the reference does (evaluator.py:77-80);
+  prior() returns `[(action, policy[action])]` over the legal actions (evaluator.py:82-85).
+  """
+
+  def __init__(self, game, model, cache_size=2**16, device=0, engine=None):
+    import collections
+    if game.num_players() != 2:
+      raise ValueError("Game must be for two players.")
+    self.engine = engine if engine is not None else _engine.Engine(game, device)
+    self._model = model
+    self._cache = collections.OrderedDict()
+    self._cache_size = int(cache_size)
+    self.hits = self.misses = 0
+
+  def clear_cache(self):
+    self._cache.clear()
+
+  def cache_info(self):
+    return {"size": len(self._cache), "max_size": self._cache_size, "hits": self.hits,
+            "misses": self.misses}
+
+  def inference_batch(self, states):
+    """(values [n], policies [n, A]) float64 for a list of states, one model call for all
+    states that are not cached."""
+    import torch
+    gid = self.engine.gid
+    packs = [np.ascontiguousarray(_packed_of(gid, s)) for s in states]
+    keys = [p.tobytes() for p in packs]
+    todo = [i for i, k in enumerate(keys) if k not in self._cache]
+    uniq = {}
+    for i in todo:
+      uniq.setdefault(keys[i], i)
+    idx = list(uniq.values())
+    if idx:
+      n = len(idx)
+      sb = self.engine.state_bytes
+      # packed SoA with capacity n: interleave the per-state planes
+      planes = _engine.plane_bytes(gid)
+      buf = np.zeros(n * sb, np.uint8)
+      off_dst = 0
+      off_src = 0
+      for pb in planes:
+        for j, i in enumerate(idx):
+          buf[off_dst + j * pb: off_dst + (j + 1) * pb] = packs[i][off_src: off_src + pb]
+        off_dst += n * pb
+        off_src += pb
+      d_states = self.engine.to_device(buf)
+      obs, mask = self.engine.observations(d_states, n, None, want_mask=True)
+      value, policy = self._model.inference(obs, mask.to(torch.bool))
+      value = torch.as_tensor(value).detach().to("cpu", torch.float64).reshape(n).numpy()
+      policy = torch.as_tensor(policy).detach().to("cpu", torch.float64).reshape(n, -1).numpy()
+      for j, i in enumerate(idx):
+        self._cache[keys[i]] = (float(value[j]), policy[j])
+        if len(self._cache) > self._cache_size:
+          self._cache.popitem(last=False)
+    self.misses += len(idx)
+    self.hits += len(states) - len(idx)
+    vals = np.array([self._cache[k][0] for k in keys], np.float64)
+    pols = np.stack([self._cache[k][1] for k in keys]) if keys else np.zeros((0, 0))
+    for k in keys:
+      self._cache.move_to_end(k)
+    return vals, pols
+
+  def evaluate(self, state):
+    v, _ = self.inference_batch([state])
+    return np.array([v[0], -v[0]])
+
+  def evaluate_batch(self, states):
+    v, _ = self.inference_batch(states)
+    return np.stack([v, -v], axis=1) if len(states) else np.zeros((0, 2))
+
+  def prior(self, state):
+    _, p = self.inference_batch([state])
+    return [(action, p[0][action]) for action in state.legal_actions()]

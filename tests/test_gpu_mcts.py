@@ -185,3 +185,69 @@ def test_native_tree_solver_known_answers(bsg):
   assert r_py.outcome == root.outcome
   nat.close()
   eng.close()
+
+
+class _TinyModel(object):
+  """Deterministic stand-in for alpha_zero/model.py: value = tanh(w_v . obs), policy = softmax
+  of W_p obs over the legal actions; float64 so host and device agree to rounding."""
+
+  def __init__(self, obs_size, num_actions, device):
+    import torch
+    g = torch.Generator().manual_seed(4)
+    self.wv = (torch.randint(-3, 4, (obs_size,), generator=g).double() / 16).to(device)
+    self.wp = (torch.randint(-3, 4, (num_actions, obs_size), generator=g).double() / 16).to(device)
+    self.calls = 0
+
+  def inference(self, obs, mask):
+    import torch
+    self.calls += 1
+    x = obs.reshape(obs.shape[0], -1).double().to(self.wv.device)
+    mask = torch.as_tensor(mask).to(self.wv.device).bool()
+    value = torch.tanh(x @ self.wv).reshape(-1, 1)
+    logits = (x @ self.wp.T).masked_fill(~mask, -1e30)
+    return value, torch.softmax(logits, dim=1)
+
+
+@pytest.mark.parametrize("game", ["tic_tac_toe", "connect_four", "breakthrough", "hex"])
+def test_alpha_zero_evaluator_matches_host_observations(bsg, game):
+  """AlphaZeroEvaluator (evaluator.py:38-83 of the reference) over the GPU observation writer:
+  same value / prior as feeding the model the host mirror's observation_tensor() and
+  legal_actions_mask(), zero-sum evaluate, priors over the legal actions only, cache hits."""
+  import torch
+  g = bsg.load_game(game)
+  dev = torch.device("cuda", 0)
+  model = _TinyModel(g.observation_tensor_size(), g.num_distinct_actions(), dev)
+  host_model = _TinyModel(g.observation_tensor_size(), g.num_distinct_actions(), torch.device("cpu"))
+  ev = bsg.AlphaZeroEvaluator(g, model)
+  rng = np.random.RandomState(2)
+  states = []
+  for i in range(9):
+    s = g.new_initial_state()
+    for _ in range(2 * i):
+      if s.is_terminal():
+        break
+      la = s.legal_actions()
+      s.apply_action(la[rng.randint(len(la))])
+    if not s.is_terminal():
+      states.append(s)
+  batch = ev.evaluate_batch(states)
+  for i, s in enumerate(states):
+    obs = torch.tensor(np.asarray(s.observation_tensor(), np.float64)).reshape(1, -1)
+    mask = torch.tensor(np.asarray(s.legal_actions_mask(), np.bool_)).reshape(1, -1)
+    v, p = host_model.inference(obs, mask)
+    e = ev.evaluate(s)
+    assert abs(e[0] - float(v[0, 0])) < 1e-9 and e[0] + e[1] == 0
+    assert np.array_equal(batch[i], e)
+    pri = ev.prior(s)
+    assert [a for a, _ in pri] == s.legal_actions()
+    assert abs(sum(x for _, x in pri) - 1.0) < 1e-9
+    for a, x in pri:
+      assert abs(x - float(p[0, a])) < 1e-9
+  info = ev.cache_info()
+  assert model.calls == 1 and info["hits"] > 0     # one batched model call, the rest cached
+  # drives the Python MCTS like the reference's AlphaZero actor (alpha_zero.py:196-228)
+  bot = bsg.MCTSBot(g, 1.5, 30, ev, solve=False, random_state=np.random.RandomState(0),
+                    child_selection_fn=bsg.SearchNode.puct_value)
+  action = bot.step(g.new_initial_state())
+  assert action in g.new_initial_state().legal_actions()
+  ev.engine.close()

@@ -295,3 +295,41 @@ def test_host_buffer_chunked_path_equals_device_path(game, n, torch):
     assert np.array_equal(t, want_t)
     assert np.array_equal(r, want_r) and np.array_equal(s, want_s)
   eng.close()
+
+
+@pytest.mark.parametrize("game", GAMES)
+def test_trajectory_records_match_oracle(game, torch):
+  """Engine.trajectories: every decision point of every playout — observation of the player to
+  move, legal mask, action taken — equals the oracle's replay of the same playout ids
+  (the AlphaZero actor's record, alpha_zero.py:196-228)."""
+  import open_spiel_1_b200 as bsg
+  oracle = Oracle()
+  eng = _engine(game)
+  roots = []
+  for p in range(12):
+    acts, _, _ = oracle.replay(game, [], seed=5, playout=p, max_steps=(3 * p) % 11)
+    roots.append(acts if not oracle.state_dump(game, acts)["terminal"] else acts[:-1])
+  R = 3
+  d_roots = eng.to_device(bsg.pack_histories(game, roots))
+  tr = eng.trajectories(d_roots, len(roots), R, seed=21, first_playout=500)
+  torch.cuda.synchronize()
+  o_len, o_ret, o_term, o_acts = oracle.replay_batch(game, roots, rollouts=R, seed=21,
+                                                     first_playout=500, actions_stride=256)
+  assert np.array_equal(tr["length"].cpu().numpy(), o_len)
+  assert np.array_equal(tr["ret0"].cpu().numpy(), o_ret)
+  assert tr["total"] == int(o_len.sum())
+  obs = tr["obs"].cpu().numpy().reshape(tr["total"], -1).astype(np.uint8)
+  mask = tr["mask"].cpu().numpy()
+  actions = tr["actions"].cpu().numpy()
+  owner, step = tr["playout"].cpu().numpy(), tr["step"].cpu().numpy()
+  rng = np.random.RandomState(1)
+  picks = rng.choice(tr["total"], size=min(tr["total"], 150), replace=False)
+  for i in picks:
+    p, t = int(owner[i]), int(step[i])
+    hist = list(roots[p // R]) + [int(a) for a in o_acts[p, :t]]
+    assert actions[i] == o_acts[p, t]
+    d = oracle.state_dump(game, hist)
+    dd = oracle.state_dump(game, hist, d["current_player"])
+    assert np.array_equal(obs[i], dd["obs"]), (game, p, t)
+    assert np.nonzero(mask[i])[0].tolist() == dd["legal"], (game, p, t)
+  eng.close()
