@@ -374,6 +374,27 @@ def rank0_extras(args, eng, torch, dev, steps_per_s_per_gpu, kernel_ms, n):
                              "algorithmic_bytes_per_state": 784}
       del obs, st
       e_bt.close()
+      # BASELINE cfg3: breakthrough playouts + ObservationTensor / legal-mask write-out of every
+      # visited state (the AlphaZero actor's records), all on the device
+      e_bt = bsg.Engine("breakthrough", eng.device)
+      n_tr = 1 << 18
+      st, _ = make_roots(e_bt, n_tr, 0, 40, seed=ROOT_SEED + 5)
+      rec = {}
+
+      def run_traj():
+        rec["t"] = e_bt.trajectories(st, n_tr, 1, seed=9, want_actions=True)
+      ms = time_kernel(torch, dev, run_traj, reps=2, warm=1)
+      total = rec["t"]["total"]
+      out["trajectory_cfg3"] = {
+          "workload": "breakthrough: %d playouts, observation [3,8,8] f32 + legal mask [768] u8 + "
+                      "action of every decision point" % n_tr,
+          "records": total, "ms": ms, "records_per_s": total / (ms * 1e-3),
+          "bytes_written_per_record": 768 + 768 + 20,
+          "output_gb_per_s": total * (768 + 768 + 20) / (ms * 1e-3) / 1e9}
+      rec.clear()
+      del st
+      e_bt.close()
+      torch.cuda.empty_cache()
       for g, npl in (("tic_tac_toe", 1 << 24), ("breakthrough", 1 << 22), ("hex", 1 << 20)):
         e_g = bsg.Engine(g, eng.device)
         dmin, dmax = ROOT_DEPTHS[g]

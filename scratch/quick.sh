@@ -7,6 +7,6 @@ for l in sys.stdin:
   if l.startswith('{'):
     d = json.loads(l); print('value %.4g  ms %.4f  e2e %.4g  frac %.3f' % (d['value'], d['ms_per_step'], d['e2e']['value'], d['roofline']['frac']))
     for g, v in (d.get('other_games') or {}).items(): print(' ', g, v if isinstance(v, str) else '%.4g steps/s  %.3f ms  frac %.3f' % (v['game_steps_per_s'], v['ms'], v['int_roofline_frac']))
-    if 'obs_roofline' in d: print('  obs frac %.3f' % d['obs_roofline']['frac'])
+    if 'obs_roofline' in d: print('  obs frac %.3f' % d['obs_roofline']['frac'], d.get('trajectory_cfg3'))
   else: print(l[:300])
 "
