@@ -94,16 +94,16 @@ struct MctsTree : MctsBase {
     nodes[node].n_children = n;
   }
   // SearchNode.uct_value (mcts.py:124-133) with the virtual-visit rule of the batched mirror.
-  double value_of(const MctsNode& ch, int64_t parent_n, bool batched) const {
+  // log_pn = log(parent visits) (log(max(parent, 2)) for a child with virtual visits) is the
+  // same for every child of a node, so the caller computes both once per node visit.
+  double value_of(const MctsNode& ch, double log_pn, double log_pn2, bool batched) const {
     if (batched && ch.virt && !ch.has_outcome) {
       double n = (double)(ch.explore + ch.virt);
-      int64_t pn = parent_n > 2 ? parent_n : 2;
-      return (ch.reward - ch.virt) / n + uct_c * sqrt(log((double)pn) / n);
+      return (ch.reward - ch.virt) / n + uct_c * sqrt(log_pn2 / n);
     }
-    if (batched && parent_n < 1) parent_n = 1;
     if (ch.has_outcome) return ret_of(ch.out0, ch.player);
     if (ch.explore == 0) return std::numeric_limits<double>::infinity();
-    return ch.reward / (double)ch.explore + uct_c * sqrt(log((double)parent_n) / (double)ch.explore);
+    return ch.reward / (double)ch.explore + uct_c * sqrt(log_pn / (double)ch.explore);
   }
   // mcts.py:292-345: descend to a leaf; `working` ends as the leaf's state.
   void tree_policy(std::vector<int32_t>& path, State& working) {
@@ -116,10 +116,13 @@ struct MctsTree : MctsBase {
       if (nodes[node].n_children == 0 && nodes[node].first_child < 0) expand(node, working);
       const MctsNode& nd = nodes[node];
       int64_t parent_n = nd.explore + nd.virt;
+      const double log_pn = log((double)parent_n);
+      const double log_pn2 = parent_n > 2 ? log_pn : log(2.0);
       int32_t best = -1;
       double best_v = -std::numeric_limits<double>::infinity();
+      const MctsNode* ch = &nodes[nd.first_child];
       for (int i = 0; i < nd.n_children; ++i) {
-        double v = value_of(nodes[nd.first_child + i], parent_n, batched);
+        double v = value_of(ch[i], log_pn, log_pn2, batched);
         if (best < 0 || v > best_v) { best = nd.first_child + i; best_v = v; }
       }
       if (best < 0) break;  // no legal action in a non-terminal state (blocked breakthrough)
