@@ -90,6 +90,22 @@ int bsg_host_observation(int game, const void* packed_host, int64_t cap, int64_t
 /* State::LegalActionsMask (spiel.h:244-252) of one packed state: NumDistinctActions bytes. */
 int bsg_host_legal_mask(int game, const void* packed_host, int64_t cap, int64_t i,
                         uint8_t* mask_out);
+/* State::ToString (open_spiel/spiel.h:228; per game tic_tac_toe.cc:126-137, connect_four.cc:166-175,
+ * breakthrough.cc:262-282, hex.cc:229-246) of packed state i into buf (NUL-terminated).
+ * Returns the length, or BSG_ERR_BAD_ARG when `capacity` is too small. */
+int bsg_host_to_string(int game, const void* packed_host, int64_t cap, int64_t i, char* buf,
+                       int capacity);
+/* State::Serialize for the games whose serialisation is the board (connect_four.cc:227 =
+ * ToString(); breakthrough.cc:389-397 = 64 cell characters).  tic_tac_toe and hex serialise
+ * as their action history (spiel.cc:375-384), which a packed state does not carry:
+ * BSG_ERR_BAD_ARG (the Python mirror writes those from State.history()). */
+int bsg_host_serialize(int game, const void* packed_host, int64_t cap, int64_t i, char* buf,
+                       int capacity);
+/* Game::DeserializeState for the board formats (connect_four.cc:229-279: side to move from the
+ * stone counts, outcome from the lines; breakthrough.cc:399-435: side to move stays black, no
+ * winner is set — the reference's own quirk, reproduced).  Histories deserialise through
+ * bsg_pack_histories. */
+int bsg_host_deserialize(int game, const char* str, void* packed_host, int64_t cap, int64_t i);
 /* Debug/test hook: applies LegalActions()[r mod n] to packed state i through the very step
  * function the kernels run, so the selection logic can be checked on a CPU.  No product
  * path calls it; playouts exist only as CUDA kernels. */

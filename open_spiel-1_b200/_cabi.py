@@ -66,6 +66,9 @@ def _load():
       "bsg_host_observation": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, ctypes.c_int, vp]),
       "bsg_host_legal_mask": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, vp]),
       "bsg_host_replay_step": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, u32, vp]),
+      "bsg_host_to_string": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, vp, ctypes.c_int]),
+      "bsg_host_serialize": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, vp, ctypes.c_int]),
+      "bsg_host_deserialize": (ctypes.c_int, [ctypes.c_int, ctypes.c_char_p, vp, i64, i64]),
       "bsg_draw": (u32, [u64, u64, u32]),
       "bsg_create": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.POINTER(vp)]),
       "bsg_destroy": (None, [vp]),

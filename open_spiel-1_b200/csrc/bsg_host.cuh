@@ -5,6 +5,8 @@
 #pragma once
 #include <string.h>
 
+#include <string>
+
 #include "../../include/bsg.h"
 #include "bsg_games.cuh"
 
@@ -145,6 +147,168 @@ struct MaskOp {
       if (b != G::legal_bit(s, a)) return BSG_ERR_BAD_ARG;  // internal inconsistency
       out[a] = (uint8_t)b;
     }
+    return BSG_OK;
+  }
+};
+
+// ---------------------------------------------------------------------------------------
+// Text formats of the reference: State::ToString and the board-string serialisation
+// (State::Serialize / Game::DeserializeState).  tic_tac_toe and hex serialise as their action
+// history (spiel.cc:375-384), which a packed state does not carry — the Python mirror keeps
+// the history and handles those two itself; connect_four and breakthrough serialise the board.
+// ---------------------------------------------------------------------------------------
+template <class G> struct Text {
+  static std::string to_string(const typename G::State&) { return std::string(); }
+  static bool has_board_format() { return false; }
+  static std::string serialize(const typename G::State&) { return std::string(); }
+  static int deserialize(typename G::State&, const char*) { return BSG_ERR_BAD_ARG; }
+};
+template <> struct Text<TicTacToe> {   // tic_tac_toe.cc:126-137
+  static std::string to_string(const TicTacToe::State& s) {
+    u32 x = TicTacToe::mover(s) ? s.opp : s.cur, o = TicTacToe::mover(s) ? s.cur : s.opp;
+    std::string str;
+    for (int r = 0; r < 3; ++r) {
+      for (int c = 0; c < 3; ++c) str += ((x >> (3 * r + c)) & 1) ? 'x' : (((o >> (3 * r + c)) & 1) ? 'o' : '.');
+      if (r < 2) str += '\n';
+    }
+    return str;
+  }
+  static bool has_board_format() { return false; }
+  static std::string serialize(const TicTacToe::State&) { return std::string(); }
+  static int deserialize(TicTacToe::State&, const char*) { return BSG_ERR_BAD_ARG; }
+};
+template <> struct Text<ConnectFour> {  // connect_four.cc:166-175 (rows top-down), :227-279
+  static std::string to_string(const ConnectFour::State& s) {
+    u64 x = ConnectFour::mover(s) ? s.opp : s.cur, o = ConnectFour::mover(s) ? s.cur : s.opp;
+    std::string str;
+    for (int row = 5; row >= 0; --row) {
+      for (int col = 0; col < 7; ++col) {
+        int b = row * 8 + col;
+        str += ((x >> b) & 1) ? 'x' : (((o >> b) & 1) ? 'o' : '.');
+      }
+      str += '\n';
+    }
+    return str;
+  }
+  static bool has_board_format() { return true; }
+  static std::string serialize(const ConnectFour::State& s) { return to_string(s); }
+  static int deserialize(ConnectFour::State& s, const char* str) {
+    u64 x = 0, o = 0;
+    int xs = 0, os = 0, r = 5, c = 0;
+    for (const char* p = str; *p; ++p) {
+      char ch = *p;
+      if (ch != '.' && ch != 'x' && ch != 'o') continue;
+      if (r < 0) return BSG_ERR_BAD_ARG;
+      if (ch == 'x') { x |= 1ull << (r * 8 + c); ++xs; }
+      if (ch == 'o') { o |= 1ull << (r * 8 + c); ++os; }
+      if (++c >= 7) { --r; c = 0; }
+    }
+    if (!(xs == os || xs == os + 1) || r != -1 || c != 0) return BSG_ERR_BAD_ARG;
+    int mv = (xs == os) ? 0 : 1;                    // connect_four.cc:270
+    bool line_x = ConnectFour::has_line(x), line_o = ConnectFour::has_line(o);
+    // a win is always the last mover's in a reachable position; the reference would also
+    // accept boards where the side to move already has a line — no playout can start there
+    if ((line_x && mv == 0) || (line_o && mv == 1) || (line_x && line_o)) return BSG_ERR_BAD_ARG;
+    s.cur = mv ? o : x;
+    s.opp = mv ? x : o;
+    s.left = (u32)(42 - xs - os);
+    s.win = (line_x || line_o) ? 1u : 0u;
+    return BSG_OK;
+  }
+};
+template <> struct Text<Breakthrough> {  // breakthrough.cc:262-282, :389-435
+  static void boards(const Breakthrough::State& s, u64& black, u64& white) {
+    black = s.mv ? s.opp : s.own; white = s.mv ? s.own : s.opp;
+  }
+  static std::string to_string(const Breakthrough::State& s) {
+    u64 b, w;
+    boards(s, b, w);
+    std::string str;
+    for (int r = 0; r < 8; ++r) {
+      str += (char)('1' + (7 - r));
+      for (int c = 0; c < 8; ++c) str += ((b >> (8 * r + c)) & 1) ? 'b' : (((w >> (8 * r + c)) & 1) ? 'w' : '.');
+      str += '\n';
+    }
+    str += ' ';
+    for (int c = 0; c < 8; ++c) str += (char)('a' + c);
+    str += '\n';
+    return str;
+  }
+  static bool has_board_format() { return true; }
+  static std::string serialize(const Breakthrough::State& s) {
+    u64 b, w;
+    boards(s, b, w);
+    std::string str;
+    for (int i = 0; i < 64; ++i) str += ((b >> i) & 1) ? 'b' : (((w >> i) & 1) ? 'w' : '.');
+    return str;
+  }
+  // The reference keeps the side to move of a fresh state (black) and sets no winner
+  // (breakthrough.cc:399-434): the state is terminal only when a side has no pieces left.
+  static int deserialize(Breakthrough::State& s, const char* str) {
+    if (strlen(str) != 64) return BSG_ERR_BAD_ARG;
+    u64 b = 0, w = 0;
+    for (int i = 0; i < 64; ++i) {
+      if (str[i] == 'b') b |= 1ull << i;
+      else if (str[i] == 'w') w |= 1ull << i;
+      else if (str[i] != '.') return BSG_ERR_BAD_ARG;
+    }
+    // A piece on its goal row means the game is over (breakthrough.cc:187-191).  The reference's
+    // reader never restores winner_ (breakthrough.cc:399-435), so it reports such a board as
+    // unfinished with that piece immobile; here the winner is restored instead — the move
+    // generator relies on "no mover piece on the goal row in an unfinished game".
+    bool b_home = (b >> 56) != 0, w_home = (w & 0xFFull) != 0;
+    if (b_home && w_home) return BSG_ERR_BAD_ARG;
+    s.own = b; s.opp = w; s.mv = 0;
+    bool p0 = w == 0 || b_home, p1 = b == 0 || w_home;
+    if (p0 && p1) return BSG_ERR_BAD_ARG;
+    s.term = (p0 || p1) ? 1u : 0u;
+    s.outc = p0 ? (u32)kOutcomeP0 : (p1 ? (u32)kOutcomeP1 : (u32)kOutcomeNone);
+    return BSG_OK;
+  }
+};
+template <int N> struct Text<HexT<N>> {  // hex.cc:229-246, cell characters hex.cc:123-146
+  typedef HexT<N> H;
+  static std::string to_string(const typename H::State& s0) {
+    typename H::State s = s0;
+    H::finish(s);
+    const char names[9] = {'O', 'p', 'q', 'o', '.', 'x', 'z', 'y', 'X'};  // plane order of the observation
+    std::string str;
+    int line = 0;
+    for (int cell = 0; cell < N * N; ++cell) {
+      if (cell && !(cell % N)) { str += '\n'; ++line; str += std::string(line, ' '); }
+      char ch = '?';
+      for (int p = 0; p < 9; ++p)
+        if ((H::plane_word(s, p, cell >> 5) >> (cell & 31)) & 1u) ch = names[p];
+      str += ch;
+      str += ' ';
+    }
+    return str;
+  }
+  static bool has_board_format() { return false; }
+  static std::string serialize(const typename H::State&) { return std::string(); }
+  static int deserialize(typename H::State&, const char*) { return BSG_ERR_BAD_ARG; }
+};
+
+struct ToStringOp {
+  const void* p; int64_t cap, i; int serialize; char* buf; int capacity;
+  template <class G> int operator()() const {
+    typename G::State s;
+    G::load(s, p, cap, i);
+    if (serialize && !Text<G>::has_board_format()) return BSG_ERR_BAD_ARG;
+    std::string str = serialize ? Text<G>::serialize(s) : Text<G>::to_string(s);
+    if ((int)str.size() + 1 > capacity) return BSG_ERR_BAD_ARG;
+    memcpy(buf, str.c_str(), str.size() + 1);
+    return (int)str.size();
+  }
+};
+struct DeserializeOp {
+  const char* str; void* p; int64_t cap, i;
+  template <class G> int operator()() const {
+    typename G::State s;
+    G::init(s);
+    int rc = Text<G>::deserialize(s, str);
+    if (rc != BSG_OK) return rc;
+    G::store(s, p, cap, i);
     return BSG_OK;
   }
 };

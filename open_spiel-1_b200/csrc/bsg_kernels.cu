@@ -586,6 +586,18 @@ int bsg_host_replay_step(int game, void* p, int64_t cap, int64_t i, uint32_t r, 
   if (!p || i < 0 || i >= cap) return BSG_ERR_BAD_ARG;
   return dispatch_game(game, StepOp{p, cap, i, r, action});
 }
+int bsg_host_to_string(int game, const void* p, int64_t cap, int64_t i, char* buf, int capacity) {
+  if (!p || !buf || i < 0 || i >= cap || capacity < 1) return BSG_ERR_BAD_ARG;
+  return dispatch_game(game, ToStringOp{p, cap, i, 0, buf, capacity});
+}
+int bsg_host_serialize(int game, const void* p, int64_t cap, int64_t i, char* buf, int capacity) {
+  if (!p || !buf || i < 0 || i >= cap || capacity < 1) return BSG_ERR_BAD_ARG;
+  return dispatch_game(game, ToStringOp{p, cap, i, 1, buf, capacity});
+}
+int bsg_host_deserialize(int game, const char* str, void* p, int64_t cap, int64_t i) {
+  if (!p || !str || i < 0 || i >= cap) return BSG_ERR_BAD_ARG;
+  return dispatch_game(game, DeserializeOp{str, p, cap, i});
+}
 uint32_t bsg_draw(uint64_t seed, uint64_t playout, uint32_t t) {
   PhiloxKeys ks;
   philox_schedule(seed, ks);

@@ -56,10 +56,20 @@ class Game:
   """Mirror of pyspiel.Game for the four supported games (load with `load_game`)."""
 
   def __init__(self, game_string):
+    game_string = str(game_string).strip()
     self.gid = _engine.game_id(game_string)
     self._type = GameType(_SHORT[self.gid])
+    # Game::ToString (spiel.cc:565-569) echoes the parameters the game was loaded with,
+    # sorted by key
+    name, _, rest = game_string.partition("(")
+    params = sorted(p.strip() for p in rest.rstrip(")").split(",") if p.strip())
+    self._string = "%s(%s)" % (name, ",".join(params))
 
   def __str__(self):
+    return self._string
+
+  def canonical_string(self):
+    """The game string with every parameter spelled out."""
     return _CANONICAL[self.gid]
 
   def get_type(self):
@@ -92,6 +102,20 @@ class Game:
   def utility_sum(self):
     return 0.0
 
+  def deserialize_state(self, text):
+    """Game::DeserializeState: board strings for connect_four (connect_four.cc:229-279) and
+    breakthrough (breakthrough.cc:399-435, side to move stays black as in the reference), one
+    action per line for tic_tac_toe and hex (spiel.cc:396-426)."""
+    if self.gid in (C.CONNECT_FOUR, C.BREAKTHROUGH):
+      packed = np.zeros(_engine.state_bytes(self.gid), np.uint8)
+      C.check(C.lib.bsg_host_deserialize(self.gid, text.encode(), packed.ctypes.data, 1, 0))
+      return State(self, packed, _history=None, _history_known=False)
+    state = self.new_initial_state()
+    for line in text.split("\n"):
+      if line.strip():
+        state.apply_action(int(line))
+    return state
+
 
 def load_game(game_string):
   """pyspiel.load_game for the supported game strings; RuntimeError otherwise
@@ -102,13 +126,15 @@ def load_game(game_string):
 class State:
   """Mirror of pyspiel.State over one packed bitboard state (host memory)."""
 
-  def __init__(self, game, _packed=None, _history=None):
+  def __init__(self, game, _packed=None, _history=None, _history_known=True):
     self._game = game
     self._gid = game.gid
     if _packed is None:
       _packed = _engine.pack_histories(self._gid, [[]])
     self._packed = _packed
     self._history = list(_history) if _history is not None else []
+    # a state deserialised from a board string has no history, exactly as in the reference
+    self._history_known = _history_known
 
   # -- plumbing
   def get_game(self):
@@ -119,7 +145,7 @@ class State:
     return self._packed
 
   def clone(self):
-    return State(self._game, self._packed.copy(), self._history)
+    return State(self._game, self._packed.copy(), self._history, self._history_known)
 
   def history(self):
     return list(self._history)
@@ -184,5 +210,44 @@ class State:
   def action_to_string(self, player, action):
     return str(action)
 
+  def _text(self, fn):
+    buf = ctypes.create_string_buffer(1024)
+    n = C.check(fn(self._gid, self._packed.ctypes.data, 1, 0, buf, 1024))
+    return buf.raw[:n].decode()
+
+  def to_string(self):
+    """State::ToString in the reference's format (e.g. connect_four.cc:166-175)."""
+    return self._text(C.lib.bsg_host_to_string)
+
   def __str__(self):
-    return "%s history=%s" % (self._game, self._history)
+    return self.to_string()
+
+  def serialize(self):
+    """State::Serialize: the board for connect_four / breakthrough, the action history (one
+    action per line, spiel.cc:375-384) for tic_tac_toe / hex."""
+    if self._gid in (C.CONNECT_FOUR, C.BREAKTHROUGH):
+      return self._text(C.lib.bsg_host_serialize)
+    return "".join("%d\n" % a for a in self._history) if self._history else "\n"
+
+
+def serialize_game_and_state(game, state):
+  """SerializeGameAndState (spiel.cc:428-447)."""
+  return ("# Automatically generated by OpenSpiel SerializeGameAndState\n[Meta]\nVersion: 1\n\n"
+          "[Game]\n%s\n[State]\n%s\n" % (game, state.serialize()))
+
+
+def deserialize_game_and_state(text):
+  """DeserializeGameAndState (spiel.cc:449-495): (game, state) from the three sections."""
+  sections = {"[Meta]": [], "[Game]": [], "[State]": []}
+  cur = None
+  for line in text.split("\n"):
+    if not line or line.startswith("#"):
+      continue
+    if line in sections:
+      cur = line
+    elif cur is None:
+      raise RuntimeError("bsg: text before the first section")
+    else:
+      sections[cur].append(line)
+  game = load_game("\n".join(sections["[Game]"]))
+  return game, game.deserialize_state("\n".join(sections["[State]"]))

@@ -248,6 +248,55 @@ double ref_mcts_selfplay(const char* game, int n_games, int max_sims, int n_roll
   return secs;
 }
 
+// Text formats: State::ToString / State::Serialize of the state reached by `hist`
+// (spiel.h:228, spiel.cc:375-384 and the per-game overrides).  Returns the length written.
+int ref_to_string(const char* game, const int64_t* hist, int n_hist, int serialize, char* buf,
+                  int capacity) {
+  auto g = GetGame(game);
+  auto s = FromHistory(*g, hist, n_hist);
+  std::string str = serialize ? s->Serialize() : s->ToString();
+  if (static_cast<int>(str.size()) + 1 > capacity) return -1;
+  std::memcpy(buf, str.c_str(), str.size() + 1);
+  return static_cast<int>(str.size());
+}
+
+// Game::DeserializeState(str) followed by the same dump as ref_state_dump, plus the
+// deserialised state's own ToString().
+int ref_deserialize_dump(const char* game, const char* str, int player, double* obs_out,
+                         int64_t* legal_out, int* n_legal, int* cur_player, int* terminal,
+                         double* returns_out, char* text_out, int text_capacity) {
+  auto g = GetGame(game);
+  std::unique_ptr<open_spiel::State> s = g->DeserializeState(str);
+  std::vector<open_spiel::Action> legal = s->LegalActions();
+  *n_legal = static_cast<int>(legal.size());
+  if (legal_out) std::copy(legal.begin(), legal.end(), legal_out);
+  *cur_player = s->CurrentPlayer();
+  *terminal = s->IsTerminal() ? 1 : 0;
+  std::vector<double> ret = s->Returns();
+  returns_out[0] = ret[0];
+  returns_out[1] = ret[1];
+  if (obs_out && player >= 0) {
+    std::vector<double> obs;
+    s->ObservationTensor(player, &obs);
+    std::copy(obs.begin(), obs.end(), obs_out);
+  }
+  std::string text = s->ToString();
+  if (text_out && static_cast<int>(text.size()) + 1 <= text_capacity)
+    std::memcpy(text_out, text.c_str(), text.size() + 1);
+  return 0;
+}
+
+// SerializeGameAndState (spiel.cc:428-447) of the state reached by `hist`.
+int ref_serialize_game_and_state(const char* game, const int64_t* hist, int n_hist, char* buf,
+                                 int capacity) {
+  auto g = GetGame(game);
+  auto s = FromHistory(*g, hist, n_hist);
+  std::string str = open_spiel::SerializeGameAndState(*g, *s);
+  if (static_cast<int>(str.size()) + 1 > capacity) return -1;
+  std::memcpy(buf, str.c_str(), str.size() + 1);
+  return static_cast<int>(str.size());
+}
+
 // One MCTS search from a history: returns the chosen action (for solver known-answer tests).
 int64_t ref_mcts_step(const char* game, const int64_t* hist, int n_hist, int max_sims,
                       int n_rollouts, double uct_c, int solve, int seed) {

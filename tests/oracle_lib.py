@@ -141,6 +141,12 @@ class Reference:
     L.ref_mcts_step.argtypes = [ctypes.c_char_p, vp, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                 ctypes.c_double, ctypes.c_int, ctypes.c_int]
     L.ref_mcts_step.restype = ctypes.c_int64
+    L.ref_to_string.argtypes = [ctypes.c_char_p, vp, ctypes.c_int, ctypes.c_int, ctypes.c_char_p,
+                                ctypes.c_int]
+    L.ref_serialize_game_and_state.argtypes = [ctypes.c_char_p, vp, ctypes.c_int, ctypes.c_char_p,
+                                               ctypes.c_int]
+    L.ref_deserialize_dump.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_int, vp, vp, vp,
+                                       vp, vp, vp, ctypes.c_char_p, ctypes.c_int]
 
   @staticmethod
   def game_string(game, board_size=11):
@@ -204,6 +210,37 @@ class Reference:
                                       uct_c, int(solve), seed, threads, ctypes.byref(mv),
                                       ctypes.byref(sims), ctypes.byref(s))
     return secs, mv.value, sims.value, s.value
+
+  def to_string(self, game, hist, serialize=False, board_size=11):
+    h = np.asarray(hist, np.int64)
+    buf = ctypes.create_string_buffer(4096)
+    n = self.lib.ref_to_string(self.game_string(game, board_size), _ptr(h), len(h),
+                               int(serialize), buf, 4096)
+    assert n >= 0
+    return buf.raw[:n].decode()
+
+  def serialize_game_and_state(self, game, hist, board_size=11):
+    h = np.asarray(hist, np.int64)
+    buf = ctypes.create_string_buffer(8192)
+    n = self.lib.ref_serialize_game_and_state(self.game_string(game, board_size), _ptr(h), len(h),
+                                              buf, 8192)
+    assert n >= 0
+    return buf.raw[:n].decode()
+
+  def deserialize_dump(self, game, text, player=None, board_size=11):
+    size = 9 * board_size * board_size if game == "hex" else OBS_SIZE[game]
+    obs = np.zeros(size, np.float64)
+    legal = np.zeros(1024, np.int64)
+    nl, cp, tm = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    rets = np.zeros(2, np.float64)
+    out = ctypes.create_string_buffer(4096)
+    self.lib.ref_deserialize_dump(self.game_string(game, board_size), text.encode(),
+                                  -1 if player is None else player, _ptr(obs), _ptr(legal),
+                                  ctypes.byref(nl), ctypes.byref(cp), ctypes.byref(tm), _ptr(rets),
+                                  out, 4096)
+    return {"obs": obs.astype(np.uint8), "legal": legal[:nl.value].tolist(),
+            "current_player": cp.value, "terminal": bool(tm.value),
+            "returns": [int(rets[0]), int(rets[1])], "text": out.value.decode()}
 
   def mcts_step(self, game, hist, max_sims, n_rollouts=1, uct_c=2.0, solve=True, seed=1):
     h = np.asarray(hist, np.int64)
