@@ -97,24 +97,24 @@ def run_cfg5(args, bsg, local, rank, world):
   game = bsg.load_game("connect_four")
   eng = bsg.Engine("connect_four", local)
   n_roll = 256
-  total_sims = args.sims5 * world                      # weak scaling: fixed sims per rank
+  total_sims = args.sims5 * world * args.trees         # weak scaling: fixed sims per tree
   ev = bsg.GpuRolloutEvaluator(eng, n_rollouts=n_roll, seed=11)
   rp = bsg.RootParallelMCTS(game, 2.0, total_sims, ev, sims_per_step=args.sims_per_step,
                             solve=True, seed=5, leaf_batch=args.leaf_batch, device=dev,
-                            native=args.native)
+                            native=args.native, trees_per_rank=args.trees)
   state = game.new_initial_state()
   rp.mcts_search(state)                                # warm-up search
   torch.cuda.synchronize(dev)
   if dist is not None:
     dist.barrier()
-  steps0, ar0 = (rp.bot.total_steps if args.native else ev.total_steps), rp.all_reduces
+  steps0, ar0 = (rp.total_steps if args.native else ev.total_steps), rp.all_reduces
   t0 = time.perf_counter()
   root = rp.mcts_search(state)
   torch.cuda.synchronize(dev)
   secs = time.perf_counter() - t0
   stats = np.array([[c.action, c.explore_count, int(round(c.total_reward * n_roll))]
                     for c in sorted(root.children, key=lambda c: c.action)], np.int64)
-  steps_now = rp.bot.total_steps if args.native else ev.total_steps
+  steps_now = rp.total_steps if args.native else ev.total_steps
   t = torch.tensor([secs, float(steps_now - steps0)], dtype=torch.float64, device=dev)
   same = True
   if dist is not None:
@@ -131,10 +131,11 @@ def run_cfg5(args, bsg, local, rank, world):
   assert same, "ranks disagree on the merged root statistics"
   visits = int(stats[:, 1].sum())
   out = {"config": "cfg5: connect_four root-parallel MCTS from the empty board, %d rollouts/leaf, "
-                   "%d simulations/move/rank x %d rank(s), %d sims per all-reduce step, leaf_batch %d"
-                   % (n_roll, args.sims5, world, args.sims_per_step, args.leaf_batch),
+                   "%d simulations/move/tree x %d tree(s)/rank x %d rank(s), %d sims per tree per "
+                   "all-reduce step, leaf_batch %d"
+                   % (n_roll, args.sims5, args.trees, world, args.sims_per_step, args.leaf_batch),
          "tree": "native (csrc/bsg_mcts.cuh)" if args.native else "python mirror",
-         "n_gpus": world, "simulations": visits, "seconds": secs,
+         "n_gpus": world, "trees_per_rank": args.trees, "simulations": visits, "seconds": secs,
          "simulations_per_s": visits / secs, "playouts_per_s": visits * n_roll / secs,
          "game_steps_per_s": game_steps / secs, "all_reduces": rp.all_reduces - ar0,
          "merged_root_identical_on_all_ranks": same,
@@ -159,9 +160,11 @@ def main():
   ap.add_argument("--cfg", default="all")
   ap.add_argument("--sims", type=int, default=1000, help="cfg1 simulations per move")
   ap.add_argument("--games", type=int, default=3, help="cfg1 self-play games (ours)")
-  ap.add_argument("--sims5", type=int, default=16384, help="cfg5 simulations per move per rank")
+  ap.add_argument("--sims5", type=int, default=16384, help="cfg5 simulations per move per tree")
   ap.add_argument("--sims-per-step", type=int, default=4096)
   ap.add_argument("--leaf-batch", type=int, default=256)
+  ap.add_argument("--trees", type=int, default=1,
+                  help="cfg5: independent trees (host threads + engines) per rank, native only")
   ap.add_argument("--native", type=int, default=1, help="cfg5: 1 = native host tree, 0 = Python mirror")
   args = ap.parse_args()
   rank, world, local = dist_env()

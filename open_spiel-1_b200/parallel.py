@@ -105,19 +105,33 @@ class RootParallelMCTS:
     device: torch device of the collective buffer (None = CPU, for gloo).
     native: run each rank's tree in the C-ABI library (mcts.NativeMCTSBot) instead of the
       Python mirror; `evaluator` must then be a GpuRolloutEvaluator.
+    trees_per_rank: (native only) K independent trees per rank, each walked by its own host
+      thread with its own engine (streams, staging buffers) on the rank's GPU.  One host thread
+      walking one tree keeps a B200 ~1 % busy, so this is how a rank
+      fills its GPU.  Tree j of rank r is "virtual rank" r*K + j: it gets the seeds, playout-id
+      range and simulation share that rank r*K + j would get in a job of world*K ranks with one
+      tree each, and the per-step merge sums over all of them — so the merged root statistics
+      depend only on world*K, not on how the trees are spread over processes.
+    threads: walk the K trees concurrently (default) or one after the other (same result).
   """
 
   def __init__(self, game, uct_c, max_simulations, evaluator, sims_per_step=None, solve=True,
                seed=0, reward_scale=None, leaf_batch=1, child_selection_fn=SearchNode.uct_value,
-               device=None, group=None, native=False):
+               device=None, group=None, native=False, trees_per_rank=1, threads=True):
     self.rank, self.world = _world(group)
     self.group = group
     self.device = device
     self.total_simulations = int(max_simulations)
-    lo, hi = shard_range(self.total_simulations, self.rank, self.world)
-    self.local_simulations = hi - lo
+    self.trees = int(trees_per_rank)
+    if self.trees < 1 or (self.trees > 1 and not native):
+      raise ValueError("trees_per_rank > 1 needs native=True")
+    vworld = self.world * self.trees
+    vranks = [self.rank * self.trees + j for j in range(self.trees)]
+    shares = [shard_range(self.total_simulations, v, vworld) for v in vranks]
+    self.tree_simulations = [hi - lo for lo, hi in shares]
+    self.local_simulations = sum(self.tree_simulations)
     # every rank must take the same number of steps (the all-reduce is collective)
-    per_rank_max = -(-self.total_simulations // self.world)
+    per_rank_max = -(-self.total_simulations // vworld)
     self.sims_per_step = int(sims_per_step or per_rank_max)
     self.n_steps = max(1, -(-per_rank_max // self.sims_per_step))
     if reward_scale is None:
@@ -127,19 +141,34 @@ class RootParallelMCTS:
     if native:
       # the tree in the C-ABI library (csrc/bsg_mcts.cuh); `evaluator` supplies engine,
       # n_rollouts and seed, its rollouts run inside the native search
-      self.bot = NativeMCTSBot(game, uct_c, self.local_simulations, evaluator.engine,
-                               n_rollouts=evaluator.n_rollouts, solve=solve, seed=evaluator.seed,
-                               shuffle_seed=seed + self.rank, leaf_batch=leaf_batch)
-      self.bot.next_playout = evaluator.next_playout + (self.rank << 40)
+      from .engine import Engine
+      self.bots = []
+      for j, v in enumerate(vranks):
+        eng = evaluator.engine if j == 0 else Engine(evaluator.engine.gid, evaluator.engine.device)
+        bot = NativeMCTSBot(game, uct_c, self.tree_simulations[j], eng,
+                            n_rollouts=evaluator.n_rollouts, solve=solve, seed=evaluator.seed,
+                            shuffle_seed=seed + v, leaf_batch=leaf_batch)
+        bot.next_playout = evaluator.next_playout + (v << 40)
+        self.bots.append(bot)
     else:
-      self.bot = MCTSBot(game, uct_c, self.local_simulations, evaluator, solve=solve,
-                         random_state=np.random.RandomState(seed + self.rank),
-                         child_selection_fn=child_selection_fn, leaf_batch=leaf_batch)
+      self.bots = [MCTSBot(game, uct_c, self.local_simulations, evaluator, solve=solve,
+                           random_state=np.random.RandomState(seed + self.rank),
+                           child_selection_fn=child_selection_fn, leaf_batch=leaf_batch)]
       # disjoint playout-id ranges per rank keep the ranks' Philox streams independent
       if hasattr(evaluator, "next_playout"):
         evaluator.next_playout += self.rank << 40
+    self.bot = self.bots[0]
+    self._pool = None
+    if self.trees > 1 and threads:
+      from concurrent.futures import ThreadPoolExecutor
+      self._pool = ThreadPoolExecutor(max_workers=self.trees)   # ctypes calls drop the GIL
     self.all_reduces = 0
     self.last_root = None
+
+  @property
+  def total_steps(self):
+    """Game steps played by this rank's rollouts (native trees)."""
+    return sum(b.total_steps for b in self.bots)
 
   # ---- merge
   def _pack(self, root, base):
@@ -154,47 +183,61 @@ class RootParallelMCTS:
         buf[ch.action, _F_PROVEN + int(round(ch.outcome[ch.player])) + 1] = 1
     return buf
 
-  def _merge(self, root, base):
-    """One all-reduce: sums the visit/reward deltas and proof counts of all ranks and installs
-    the global statistics into this rank's root children."""
-    mine = self._pack(root, base)
+  def _merge(self, roots, base):
+    """One all-reduce: sums the visit/reward deltas and proof counts of all trees of all ranks
+    and installs the global statistics into the root children of every local tree."""
+    mine = self._pack(roots[0], base)
+    for root in roots[1:]:
+      mine += self._pack(root, base)
     summed = all_reduce_int64(mine.reshape(-1), self.device, self.group)
     summed = summed.reshape(self.num_actions, _F_FIELDS)
     self.all_reduces += 1
     new_base = {}
-    visits = 0
-    for ch in root.children:
-      b = base.get(ch.action, (0, 0))
-      n = b[0] + int(summed[ch.action, 0])
-      r = b[1] + int(summed[ch.action, 1])
-      ch.explore_count = n
-      ch.total_reward = r / self.reward_scale
-      new_base[ch.action] = (n, r)
-      visits += n
-      proofs = summed[ch.action, _F_PROVEN:_F_PROVEN + 3]
-      if ch.outcome is None and proofs.any():  # exact game values: ranks cannot disagree
-        v = float(int(np.argmax(proofs)) - 1)
-        ch.outcome = [v, -v] if ch.player == 0 else [-v, v]
-    if root.children:
-      root.explore_count = max(root.explore_count, visits)
+    for root in roots:
+      visits = 0
+      for ch in root.children:
+        b = base.get(ch.action, (0, 0))
+        n = b[0] + int(summed[ch.action, 0])
+        r = b[1] + int(summed[ch.action, 1])
+        ch.explore_count = n
+        ch.total_reward = r / self.reward_scale
+        new_base[ch.action] = (n, r)
+        visits += n
+        proofs = summed[ch.action, _F_PROVEN:_F_PROVEN + 3]
+        if ch.outcome is None and proofs.any():  # exact game values: trees cannot disagree
+          v = float(int(np.argmax(proofs)) - 1)
+          ch.outcome = [v, -v] if ch.player == 0 else [-v, v]
+      if root.children:
+        root.explore_count = max(root.explore_count, visits)
     return new_base
 
   # ---- search
+  def _search_tree(self, j, state, root, k):
+    bot = self.bots[j]
+    root = bot.mcts_search(state, root=root, simulations=k)
+    if not root.children and not state.is_terminal():
+      bot.expand_root(root, state)  # a tree with 0 simulations still joins the merge
+    return root
+
   def mcts_search(self, state):
     """Runs the sharded search; returns this rank's root with GLOBAL child statistics (equal
     on every rank for visits/rewards)."""
-    root = None
+    n_trees = len(self.bots)
+    roots = [None] * n_trees
     base = {}
-    left = self.local_simulations
+    left = list(self.tree_simulations) if n_trees > 1 else [self.local_simulations]
     for _ in range(self.n_steps):
-      k = min(self.sims_per_step, left)
-      left -= k
-      root = self.bot.mcts_search(state, root=root, simulations=k)
-      if not root.children and not state.is_terminal():
-        self.bot.expand_root(root, state)  # a rank with 0 simulations still joins the merge
-      base = self._merge(root, base)
-    self.last_root = root
-    return root
+      ks = [min(self.sims_per_step, l) for l in left]
+      left = [l - k for l, k in zip(left, ks)]
+      if self._pool is not None:
+        futs = [self._pool.submit(self._search_tree, j, state, roots[j], ks[j])
+                for j in range(n_trees)]
+        roots = [f.result() for f in futs]
+      else:
+        roots = [self._search_tree(j, state, roots[j], ks[j]) for j in range(n_trees)]
+      base = self._merge(roots, base)
+    self.last_root = roots[0]
+    return roots[0]
 
   def step_with_policy(self, state):
     root = self.mcts_search(state)

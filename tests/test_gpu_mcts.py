@@ -251,3 +251,48 @@ def test_alpha_zero_evaluator_matches_host_observations(bsg, game):
   action = bot.step(g.new_initial_state())
   assert action in g.new_initial_state().legal_actions()
   ev.engine.close()
+
+
+def _root_table(root):
+  return sorted((c.action, c.explore_count, round(c.total_reward * 64)) for c in root.children)
+
+
+def test_trees_per_rank_is_deterministic_and_equals_virtual_ranks(bsg):
+  """K trees per rank (one host thread + one engine each): the merged root statistics are the
+  same whether the trees run concurrently or one after the other, and — for a single merge
+  step — equal the sum of the K single-tree searches that virtual ranks 0..K-1 would run
+  alone (same shuffle seeds, playout-id ranges and simulation shares)."""
+  from open_spiel_1_b200.parallel import RootParallelMCTS, shard_range
+  game = bsg.load_game("connect_four")
+  state = game.new_initial_state()
+  for a in (3, 3, 2):
+    state.apply_action(a)
+  K, sims, n_roll = 3, 3000, 64
+
+  def run(threads, sims_per_step):
+    ev = bsg.GpuRolloutEvaluator("connect_four", n_rollouts=n_roll, seed=21)
+    rp = RootParallelMCTS(game, UCT_C, sims, ev, sims_per_step=sims_per_step, solve=True, seed=9,
+                          leaf_batch=32, native=True, trees_per_rank=K, threads=threads)
+    root = rp.mcts_search(state)
+    return _root_table(root), rp
+
+  multi_step, rp = run(True, 256)
+  assert rp.n_steps == 4 and len(rp.bots) == K
+  assert multi_step == run(False, 256)[0] == run(True, 256)[0]
+  assert sum(v for _, v, _ in multi_step) == sims
+
+  one_step, _ = run(True, None)
+  total = {}
+  for v in range(K):
+    lo, hi = shard_range(sims, v, K)
+    eng = bsg.Engine("connect_four", 0)
+    bot = bsg.NativeMCTSBot(game, UCT_C, hi - lo, eng, n_rollouts=n_roll, solve=True, seed=21,
+                            shuffle_seed=9 + v, leaf_batch=32)
+    bot.next_playout = v << 40
+    for a, n, r in _root_table(bot.mcts_search(state)):
+      t = total.setdefault(a, [0, 0])
+      t[0] += n
+      t[1] += r
+    bot.close()
+    eng.close()
+  assert one_step == sorted((a, n, r) for a, (n, r) in total.items())
