@@ -68,6 +68,17 @@ class Game:
   def __str__(self):
     return self._string
 
+  def __eq__(self, other):
+    # pyspiel.Game.__eq__ compares the game strings (pyspiel.cc:383-386)
+    return isinstance(other, Game) and str(self) == str(other)
+
+  def __hash__(self):
+    return hash(self._string)
+
+  def __reduce__(self):
+    # pickle support as pyspiel.cc:387-396: the game string, reloaded with load_game
+    return (load_game, (self._string,))
+
   def canonical_string(self):
     """The game string with every parameter spelled out."""
     return _CANONICAL[self.gid]
@@ -146,6 +157,10 @@ class State:
 
   def clone(self):
     return State(self._game, self._packed.copy(), self._history, self._history_known)
+
+  def __reduce__(self):
+    # pickle support as pyspiel.cc:352-360: the state travels as SerializeGameAndState text
+    return (_state_from_text, (serialize_game_and_state(self._game, self),))
 
   def history(self):
     return list(self._history)
@@ -234,6 +249,10 @@ def serialize_game_and_state(game, state):
   """SerializeGameAndState (spiel.cc:428-447)."""
   return ("# Automatically generated by OpenSpiel SerializeGameAndState\n[Meta]\nVersion: 1\n\n"
           "[Game]\n%s\n[State]\n%s\n" % (game, state.serialize()))
+
+
+def _state_from_text(text):
+  return deserialize_game_and_state(text)[1]
 
 
 def deserialize_game_and_state(text):

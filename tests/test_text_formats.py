@@ -100,3 +100,27 @@ def test_connect_four_board_string_fixture(ref):
   assert got.legal_actions() == want["legal"] and str(got) == want["text"] == board
   with pytest.raises(RuntimeError):
     g.deserialize_state("xxxx...\n" * 6)       # malformed: too many x
+
+
+@pytest.mark.parametrize("game", GAMES)
+def test_pickle_round_trip(ref, game):
+  """pickle of State / Game as pyspiel does it (pyspiel.cc:352-360,387-396): the state travels
+  as SerializeGameAndState text, the game as its string (python/tests/pyspiel_test.py pickling
+  tests have the same shape)."""
+  import pickle
+  import open_spiel_1_b200 as bsg
+  rng = np.random.RandomState(3)
+  for _ in range(10):
+    g, s = random_history(bsg, game, rng, 30)
+    s2 = pickle.loads(pickle.dumps(s))
+    assert str(s2) == str(s)
+    if game == "breakthrough" and len(s.history()) % 2:
+      # the reference's board reader always leaves black to move (breakthrough.cc:399-435):
+      # a pickled white-to-move state comes back black-to-move there too
+      assert s2.current_player() == 0 or s2.is_terminal()
+      continue
+    assert s2.current_player() == s.current_player()
+    assert s2.legal_actions() == s.legal_actions() and s2.returns() == s.returns()
+    assert np.array_equal(s2.packed(), s.packed())
+    g2 = pickle.loads(pickle.dumps(g))
+    assert g2 == g and str(g2) == str(g) == str(s2.get_game())
