@@ -365,8 +365,31 @@ struct Breakthrough {
   static constexpr bool kAsync = false;
   static constexpr u64 kCol0 = 0x0101010101010101ull, kCol7 = 0x8080808080808080ull;
   struct State { u64 own, opp; u32 mv, term, outc; };
-  struct Tables { u32 modM[64]; };
-  static void fill_tables(Tables& t) { for (u32 n = 0; n < 64; ++n) t.modM[n] = modM_entry(n); }
+  // sel4: the last two levels of the weighted rank-select as one look-up.  Index = h4 << 8 |
+  // l4 << 4 | k, where cell i of a group of four has l_i + 2 h_i moves and k < 12 is the rank
+  // inside the group; value = cell | (rank inside the cell) << 3.
+  // selo: direction of a piece's rank-th move; index = rank << 3 | R << 2 | F << 1 | L.
+  struct Tables { u32 modM[64]; unsigned char sel4[4096]; unsigned char selo[32]; };
+  static void fill_tables(Tables& t) {
+    for (u32 n = 0; n < 64; ++n) t.modM[n] = modM_entry(n);
+    for (u32 h = 0; h < 16; ++h)
+      for (u32 l = 0; l < 16; ++l)
+        for (u32 k = 0; k < 16; ++k) {
+          u32 rest = k, cell = 0, v = 0;
+          for (; cell < 4; ++cell) {
+            u32 c = ((l >> cell) & 1u) + 2u * ((h >> cell) & 1u);
+            if (rest < c) { v = cell | (rest << 3); break; }
+            rest -= c;
+          }
+          t.sel4[(h << 8) | (l << 4) | k] = (unsigned char)v;
+        }
+    for (u32 i = 0; i < 32; ++i) {
+      u32 d = i & 7u, rank = i >> 3, o = 0;
+      for (u32 b = 0, seen = 0; b < 3; ++b)
+        if ((d >> b) & 1u) { if (seen == rank) o = b; ++seen; }
+      t.selo[i] = (unsigned char)o;
+    }
+  }
 
   BSG_HD static void init(State& s) {
     s.own = 0x000000000000FFFFull; s.opp = 0xFFFF000000000000ull;
@@ -401,11 +424,27 @@ struct Breakthrough {
   // Target of source i is i + 8 - 1/0/+1 for black, i - 8 - 1/0/+1 for white; reading the
   // target's occupancy at the source position is a rotate right by 7/8/9 resp. 55/56/57.
   BSG_HD static void movegen(const State& s, u64& L, u64& F, u64& R) {
-    int base = s.mv ? 48 : 0;
     u64 occ = s.own | s.opp;
+#if defined(__CUDA_ARCH__)
+    // A variable 64-bit rotate costs the compiler four shifts and two merges.  By hand: white's
+    // 55/56/57 = 32 + 23/24/25, so swap the words for white (one select each) and rotate by
+    // 7/8/9 + 16 * mover < 32 with two funnel shifts.
+    const bool w = s.mv != 0;
+    const u32 ol = (u32)s.own, oh = (u32)(s.own >> 32), cl = (u32)occ, ch = (u32)(occ >> 32);
+    const u32 al = w ? oh : ol, ah = w ? ol : oh, bl = w ? ch : cl, bh = w ? cl : ch;
+    const u32 sh = s.mv * 16u + 7u;
+    const u32 r7l = __funnelshift_r(al, ah, sh), r7h = __funnelshift_r(ah, al, sh);
+    const u32 r8l = __funnelshift_r(bl, bh, sh + 1u), r8h = __funnelshift_r(bh, bl, sh + 1u);
+    const u32 r9l = __funnelshift_r(al, ah, sh + 2u), r9h = __funnelshift_r(ah, al, sh + 2u);
+    F = (u64)(ol & ~r8l) | ((u64)(oh & ~r8h) << 32);
+    L = (u64)(ol & 0xFEFEFEFEu & ~r7l) | ((u64)(oh & 0xFEFEFEFEu & ~r7h) << 32);
+    R = (u64)(ol & 0x7F7F7F7Fu & ~r9l) | ((u64)(oh & 0x7F7F7F7Fu & ~r9h) << 32);
+#else
+    int base = s.mv ? 48 : 0;
     F = s.own & ~rotr64(occ, base + 8);
     L = s.own & ~kCol0 & ~rotr64(s.own, base + 7);
     R = s.own & ~kCol7 & ~rotr64(s.own, base + 9);
+#endif
   }
   // breakthrough.cc:152-192: move the piece, remove a captured piece, win on reaching the far
   // row; :306-318: the game also ends when a side has no pieces left.
@@ -437,17 +476,16 @@ struct Breakthrough {
     int c = popc32(l32) + 2 * popc32(h32);
     if (k >= c) { k -= c; pos = 32; l32 = (u32)(lo >> 32); h32 = (u32)(hi >> 32); }
 #pragma unroll
-    for (int w = 16; w >= 1; w >>= 1) {
-      u32 m = (1u << w) - 1u;
-      c = popc32(l32 & m) + 2 * popc32(h32 & m);
+    for (int w = 16; w >= 4; w >>= 1) {
+      // low w bits counted through a left shift (a multiply-pipe instruction) instead of a mask
+      c = popc32(l32 << (32 - w)) + 2 * popc32(h32 << (32 - w));
       if (k >= c) { k -= c; pos += w; l32 >>= w; h32 >>= w; }
     }
-    pos &= 63;
-    // k is now the index among this piece's own moves, in o = 0,1,2 order
-    u32 d = (u32)((L >> pos) & 1ull) | ((u32)((F >> pos) & 1ull) << 1) | ((u32)((R >> pos) & 1ull) << 2);
-    if (k >= 1) d &= d - 1;
-    if (k >= 2) d &= d - 1;
-    int o = (d & 1u) ? 0 : ((d & 2u) ? 1 : 2);
+    const u32 v = tab.sel4[((h32 << 8) & 0xF00u) | ((l32 << 4) & 0xF0u) | ((u32)k & 0xFu)];
+    pos = (pos + (int)(v & 3u)) & 63;
+    // the piece's moves in o = 0,1,2 order; v >> 3 is the rank among them
+    const u32 d = (u32)((L >> pos) & 1ull) | ((u32)((F >> pos) & 1ull) << 1) | ((u32)((R >> pos) & 1ull) << 2);
+    const int o = (int)tab.selo[(v & 0x18u) | d];
     action = move(s, pos, o);
     return n;
   }
