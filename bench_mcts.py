@@ -69,6 +69,29 @@ def run_cfg1(args, bsg, local):
     out["reference_cpp_all_threads"] = sims / secs
     out["host_threads"] = threads
   eng = bsg.Engine("tic_tac_toe", local)
+  from oracle_lib import reference_python
+  mods = reference_python()
+  if mods is not None:
+    # the reference's own python/algorithms/mcts.py (unmodified bytecode, oracle/_ref) over its
+    # own compiled game: (a) exactly as python/examples/mcts.py runs it, with its CPU
+    # RandomRolloutEvaluator; (b) with this repo's GPU evaluator dropped into `evaluator`
+    pyspiel, ref_mcts = mods
+    rgame = pyspiel.load_game("tic_tac_toe")
+    for key, ev in (("reference_python_mcts_py_cpu_evaluator",
+                     ref_mcts.RandomRolloutEvaluator(1, np.random.RandomState(7))),
+                    ("reference_python_mcts_py_gpu_evaluator",
+                     bsg.GpuRolloutEvaluator(eng, n_rollouts=1, seed=7))):
+      sims = 0
+      t0 = time.perf_counter()
+      for g in range(args.games):
+        bot = ref_mcts.MCTSBot(rgame, 2.0, args.sims, ev, solve=True,
+                               random_state=np.random.RandomState(3 + g))
+        state = rgame.new_initial_state()
+        while not state.is_terminal():
+          root = bot.mcts_search(state)
+          sims += root.explore_count
+          state.apply_action(root.best_child().action)
+      out[key] = sims / (time.perf_counter() - t0)
   for lb in (1, args.leaf_batch):
     ev = bsg.GpuRolloutEvaluator(eng, n_rollouts=1, seed=7)
     bot_of = lambda game: bsg.MCTSBot(game, 2.0, args.sims, ev, solve=True,

@@ -246,3 +246,28 @@ class Reference:
     h = np.asarray(hist, np.int64)
     return self.lib.ref_mcts_step(self.game_string(game), _ptr(h), len(h), max_sims, n_rollouts,
                                   uct_c, int(solve), seed)
+
+
+def reference_python():
+  """(pyspiel, mcts) — the reduced `pyspiel` module over the unmodified reference C++
+  (oracle/pyspiel_min.cc) and the reference's python/algorithms/mcts.py byte-compiled from
+  where it lies, both built by oracle/Makefile into oracle/_ref/.  None when not built."""
+  import glob
+  import importlib.machinery
+  import importlib.util
+  import sys
+  ref_dir = os.path.dirname(reference_path())
+  pyc = os.path.join(ref_dir, "ref_mcts.pyc")
+  if not glob.glob(os.path.join(ref_dir, "pyspiel*.so")) or not os.path.exists(pyc):
+    return None
+  if "ref_mcts" in sys.modules:
+    return sys.modules["pyspiel"], sys.modules["ref_mcts"]
+  if ref_dir not in sys.path:
+    sys.path.insert(0, ref_dir)
+  import pyspiel
+  loader = importlib.machinery.SourcelessFileLoader("ref_mcts", pyc)
+  spec = importlib.util.spec_from_loader("ref_mcts", loader)
+  module = importlib.util.module_from_spec(spec)
+  loader.exec_module(module)
+  sys.modules["ref_mcts"] = module
+  return pyspiel, module
