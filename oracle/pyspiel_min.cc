@@ -2,7 +2,7 @@
 // reference C++ (spiel.cc + the four games), compiled where the sources lie under
 // /root/reference by oracle/Makefile into oracle/_ref/.  It exposes exactly the surface the
 // reference's python/algorithms/mcts.py touches (last row) so that file —
-// byte-compiled from its own location into oracle/_ref/ref_mcts.pyc — runs unmodified:
+// byte-compiled from its own location into oracle/_ref/ref_mcts.bytecode — runs unmodified:
 //   * on top of the reference's own states with THIS repo's GpuRolloutEvaluator plugged into
 //     its `evaluator` argument: the drop-in test proper (tests/test_gpu_dropin.py);
 //   * with its own RandomRolloutEvaluator as the Python CPU baseline of BASELINE config 1.

@@ -257,7 +257,7 @@ def reference_python():
   import importlib.util
   import sys
   ref_dir = os.path.dirname(reference_path())
-  pyc = os.path.join(ref_dir, "ref_mcts.pyc")
+  pyc = os.path.join(ref_dir, "ref_mcts.bytecode")
   if not glob.glob(os.path.join(ref_dir, "pyspiel*.so")) or not os.path.exists(pyc):
     return None
   if "ref_mcts" in sys.modules:

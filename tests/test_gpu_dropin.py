@@ -17,7 +17,7 @@ GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex(board_size=11)"]
 def refpy():
   mods = reference_python()
   if mods is None:
-    pytest.skip("oracle/_ref/pyspiel*.so or ref_mcts.pyc not built")
+    pytest.skip("oracle/_ref/pyspiel*.so or ref_mcts.bytecode not built")
   return mods
 
 
