@@ -361,7 +361,13 @@ struct Breakthrough {
   static constexpr int kObsWords = 6, kMaskWords = 24;
   static constexpr int kPlanes = 2;
   BSG_HD static int plane_bytes(int p) { return p == 0 ? 16 : 4; }
-  static constexpr bool kCanStick = true;   // all pieces blocked is possible
+  // A non-terminal state without a legal action cannot arise in play: take
+  // the mover's most advanced piece; it is not on the goal row (the game would be over), no own
+  // piece stands on the row ahead of it, and at least one of its two diagonal targets is on the
+  // board — empty (a move) or enemy (a capture).  Moves keep that invariant, so only a ROOT
+  // handed in from outside can be stuck; the kernel tests roots once (has_move) and the
+  // per-step test is gone.
+  static constexpr bool kCanStick = true;
   static constexpr bool kAsync = false;
   static constexpr u64 kCol0 = 0x0101010101010101ull, kCol7 = 0x8080808080808080ull;
   struct State { u64 own, opp; u32 mv, term, outc; };
@@ -445,6 +451,11 @@ struct Breakthrough {
     L = s.own & ~kCol0 & ~rotr64(s.own, base + 7);
     R = s.own & ~kCol7 & ~rotr64(s.own, base + 9);
 #endif
+  }
+  BSG_HD static bool has_move(const State& s) {
+    u64 L, F, R;
+    movegen(s, L, F, R);
+    return (L | F | R) != 0;
   }
   // breakthrough.cc:152-192: move the piece, remove a captured piece, win on reaching the far
   // row; :306-318: the game also ends when a side has no pieces left.

@@ -129,6 +129,10 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         live = (!term && (!kFull || limit > 0)) ? 1u : 0u;
         fin_term = (kFull && !term) ? 0u : 1u;   // a lean playout always runs to a terminal state
         fin_win = G::won(s) ? 1u : 0u;
+        if constexpr (G::kCanStick) {
+          // non-terminal root without a legal action: only a root can be (see the game's note)
+          if (!term && !G::has_move(s)) { live = 0; fin_term = 0; fin_win = 0; my_stuck += 1; }
+        }
         if (kFull && !live && a.io.final_states) G::store(s, a.io.final_states, a.n_playouts, lid);
       }
     }
@@ -183,14 +187,6 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         nlegal = G::step(s, r, tab, action);   // finished lanes run dead steps: no divergence
       } else {
         if (can) nlegal = G::step(s, r, tab, action);
-      }
-      if (G::kCanStick && can && nlegal == 0) {  // non-terminal state without a legal action
-        live = 0;
-        can = 0;
-        my_stuck += 1;
-        fin_term = 0;
-        fin_win = 0;
-        if (kFull && a.io.final_states) G::store(prev, a.io.final_states, a.n_playouts, lid);
       }
       if (kFull) {
         if (can) {
