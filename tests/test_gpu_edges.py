@@ -150,12 +150,18 @@ def test_step_limits_stop_playouts_early(game, bsg, torch):
                step_limit=limit, actions=actions, final_states=final)
   torch.cuda.synchronize()
   lim, ln, acts = limit.cpu().numpy(), length.cpu().numpy(), actions.cpu().numpy()
-  assert np.array_equal(ln, lim) and not term.cpu().numpy().any() and not ret0.cpu().numpy().any()
+  tm, rt = term.cpu().numpy(), ret0.cpu().numpy()
   hists = [[int(a) for a in acts[i, :ln[i]]] for i in range(n)]
-  assert np.array_equal(final.cpu().numpy(), bsg.pack_histories(game, hists))   # legal, and the state matches
-  for i in range(0, n, 37):                               # and they are the oracle's actions
-    o_acts, _, _ = oracle.replay(game, [], seed=12, playout=i, max_steps=int(lim[i]))
-    assert hists[i] == list(o_acts)
+  stopped = 0
+  for i in range(n):                                       # the oracle under the same limit
+    o_acts, o_term, o_ret = oracle.replay(game, [], seed=12, playout=i, max_steps=int(lim[i]))
+    assert hists[i] == list(o_acts) and tm[i] == o_term and rt[i] == o_ret
+    if not o_term:
+      assert ln[i] == lim[i] and rt[i] == 0
+      stopped += 1
+  assert stopped > n // 2
+  # the states they stopped in: legal histories, and exactly those positions
+  assert np.array_equal(final.cpu().numpy(), bsg.pack_histories(game, hists))
   eng.close()
 
 
