@@ -5,6 +5,8 @@
  *       (open_spiel/games/tic_tac_toe.h:44-48, connect_four.h:54-58)
  *   breakthrough: 0 empty, 1 black (player 0), 2 white (player 1)  (breakthrough.h:45-49)
  *   hex: the signed 9-value enum of hex.h:51-61 (-4..4)
+ *   pentago: 0 empty, 1 player 0, 2 player 1 (pentago.h:44-49 orders kPlayer1, kPlayer2, kPlayerNone;
+ *       only the observation plane order depends on it and that is player-relative)
  */
 #include "bsg_oracle.h"
 
@@ -30,6 +32,7 @@ int orc_num_distinct_actions(int game, int n) {
     case ORC_TTT: return 9;
     case ORC_C4: return 7;
     case ORC_BT: return 8 * 8 * 6 * 2;
+    case ORC_PENTAGO: return 36 * 8; /* pentago.h:40-42 */
     default: return n * n;
   }
 }
@@ -38,6 +41,7 @@ int orc_max_game_length(int game, int n) {
     case ORC_TTT: return 9;
     case ORC_C4: return 42;
     case ORC_BT: return 2 * (2 * 8 - 3) * 8 + 1; /* breakthrough.h:116-118 */
+    case ORC_PENTAGO: return 36; /* pentago.h:109-113 */
     default: return n * n;
   }
 }
@@ -46,6 +50,7 @@ int orc_obs_size(int game, int n) {
     case ORC_TTT: return 27;
     case ORC_C4: return 126;
     case ORC_BT: return 192;
+    case ORC_PENTAGO: return 3 * 36; /* pentago.h:106-108 */
     default: return 9 * n * n;
   }
 }
@@ -245,6 +250,63 @@ static int hex_apply(orc_state* s, int a) {
   return 0;
 }
 
+/* ---------------------------------------------------------------- pentago (6x6) */
+#define PG_N 6
+/* pentago.cc:52-75: action = ((y*6 + x) * 8) + r; quadrant = r >> 1 numbered clockwise from
+ * the top-left (0 TL, 1 TR, 2 BR, 3 BL: the bit order table pentago.cc:78-85), direction =
+ * r & 1 (0 counter-clockwise, 1 clockwise: pentago.cc:132-141 move ring bit i to i-2 / i+2 and
+ * every quadrant's ring is numbered clockwise). */
+static void pg_rotate(int* cells, int quadrant, int clockwise) {
+  int ox = (quadrant == 1 || quadrant == 2) ? 3 : 0, oy = quadrant >= 2 ? 3 : 0;
+  int old[3][3];
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 3; ++c) old[r][c] = cells[(oy + r) * PG_N + ox + c];
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 3; ++c) {
+      /* clockwise (y grows downwards): the cell at row r, column c moves to row c, column 2-r */
+      int nr = clockwise ? c : 2 - c, nc = clockwise ? 2 - r : r;
+      cells[(oy + nr) * PG_N + ox + nc] = old[r][c];
+    }
+}
+/* pentago.cc:104-125 win_mask: every horizontal, vertical and diagonal run of five. */
+static int pg_has_five(const int* cells, int code) {
+  static const int D[4][2] = {{1, 0}, {0, 1}, {1, 1}, {1, -1}};
+  for (int y = 0; y < PG_N; ++y)
+    for (int x = 0; x < PG_N; ++x)
+      for (int d = 0; d < 4; ++d) {
+        int ex = x + 4 * D[d][0], ey = y + 4 * D[d][1], i;
+        if (ex < 0 || ex >= PG_N || ey < 0 || ey >= PG_N) continue;
+        for (i = 0; i < 5; ++i)
+          if (cells[(y + i * D[d][1]) * PG_N + x + i * D[d][0]] != code) break;
+        if (i == 5) return 1;
+      }
+  return 0;
+}
+/* pentago.cc:147-160 */
+static int pg_legal(const orc_state* s, int* out) {
+  int n = 0;
+  for (int y = 0; y < PG_N; ++y)
+    for (int x = 0; x < PG_N; ++x)
+      if (s->cells[y * PG_N + x] == 0)
+        for (int r = 0; r < 8; ++r) out[n++] = (y * PG_N + x) * 8 + r;
+  return n;
+}
+/* pentago.cc:274-312: place, rotate both colours, then both players' lines: a rotation can
+ * complete the opponent's line (they win) or both (draw); a full board is a draw. */
+static int pg_apply(orc_state* s, int a) {
+  if (a < 0 || a >= 288 || s->cells[a / 8] != 0) return -1;
+  s->cells[a / 8] = s->cur_player + 1;
+  pg_rotate(s->cells, (a % 8) >> 1, (a % 8) & 1);
+  s->num_moves += 1;
+  int w0 = pg_has_five(s->cells, 1), w1 = pg_has_five(s->cells, 2);
+  if (w0 && w1) s->outcome = 2;
+  else if (w0) s->outcome = 0;
+  else if (w1) s->outcome = 1;
+  else if (s->num_moves == 36) s->outcome = 2;
+  s->cur_player = 1 - s->cur_player;
+  return 0;
+}
+
 /* ---------------------------------------------------------------- generic API */
 void orc_init(orc_state* s, int game, int board_size) {
   memset(s, 0, sizeof(*s));
@@ -265,6 +327,7 @@ int orc_is_terminal(const orc_state* s) {
     case ORC_TTT: return s->outcome != -1 || s->num_moves == 9;     /* tic_tac_toe.cc:139-141 */
     case ORC_C4: return s->outcome != -1;                           /* connect_four.cc:176-178 */
     case ORC_BT: return s->outcome >= 0 || s->pieces[0] == 0 || s->pieces[1] == 0; /* :306-308 */
+    case ORC_PENTAGO: return s->outcome != -1;                      /* pentago.h:62 */
     default: return s->outcome != -1;                               /* hex.cc:248 */
   }
 }
@@ -285,6 +348,8 @@ int orc_legal_actions(const orc_state* s, int* out) {
       return n;
     case ORC_BT:
       return bt_legal(s, out);
+    case ORC_PENTAGO:
+      return pg_legal(s, out);
     default: /* hex.cc:186-196 */
       for (int c = 0; c < s->board_size * s->board_size; ++c)
         if (s->cells[c] == HX_EMPTY) out[n++] = c;
@@ -298,6 +363,7 @@ int orc_apply(orc_state* s, int a) {
     case ORC_TTT: return ttt_apply(s, a);
     case ORC_C4: return c4_apply(s, a);
     case ORC_BT: return bt_apply(s, a);
+    case ORC_PENTAGO: return pg_apply(s, a);
     default: return hex_apply(s, a);
   }
 }
@@ -338,6 +404,14 @@ void orc_observation(const orc_state* s, int player, uint8_t* out) {
         out[plane * 64 + c] = 1;
       }
       return;
+    case ORC_PENTAGO: /* pentago.cc:246-272: plane 0 the observer's stones, 1 the other's, 2 empty */
+      memset(out, 0, 108);
+      for (int c = 0; c < 36; ++c) {
+        int v = s->cells[c];
+        plane = v == 0 ? 2 : ((v - 1) == player ? 0 : 1);
+        out[plane * 36 + c] = 1;
+      }
+      return;
     default: /* hex.cc:266-277: plane = state - kMinValueCellState(-4) */
       ncell = s->board_size * s->board_size;
       memset(out, 0, 9 * ncell);
@@ -356,7 +430,7 @@ static int orc_from_history(orc_state* s, int game, int board_size, const int64_
 static int orc_replay_from(orc_state* s, const uint32_t* r_table, uint64_t seed, uint64_t playout,
                            int max_steps, int64_t* actions_out, int* len_out, int* terminal_out,
                            int* ret0_out) {
-  int legal[128], t = 0, ret[2];
+  int legal[ORC_MAX_LEGAL], t = 0, ret[2];
   while (!orc_is_terminal(s) && t < max_steps) {
     int n = orc_legal_actions(s, legal);
     if (n == 0) return -1;
@@ -414,7 +488,7 @@ int orc_state_dump(int game, int board_size, const int64_t* hist, int n_hist, in
                    uint8_t* obs_out, int64_t* legal_out, int* n_legal, int* cur_player,
                    int* terminal, int* returns_out) {
   orc_state s;
-  int legal[128];
+  int legal[ORC_MAX_LEGAL];
   if (orc_from_history(&s, game, board_size, hist, n_hist) != 0) return -2;
   *n_legal = orc_legal_actions(&s, legal);
   if (legal_out) for (int i = 0; i < *n_legal; ++i) legal_out[i] = legal[i];

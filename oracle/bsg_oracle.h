@@ -18,7 +18,8 @@
 extern "C" {
 #endif
 
-enum { ORC_TTT = 0, ORC_C4 = 1, ORC_BT = 2, ORC_HEX = 3 };
+enum { ORC_TTT = 0, ORC_C4 = 1, ORC_BT = 2, ORC_HEX = 3, ORC_PENTAGO = 5 };
+#define ORC_MAX_LEGAL 320 /* pentago: 36 cells x 8 rotations = 288 */
 #define ORC_MAX_CELLS 121
 #define ORC_TERMINAL_PLAYER (-4) /* kTerminalPlayerId, open_spiel/spiel.h:48 */
 
@@ -39,7 +40,7 @@ int orc_obs_size(int game, int board_size);
 void orc_init(orc_state* s, int game, int board_size);
 int orc_is_terminal(const orc_state* s);
 int orc_current_player(const orc_state* s);
-/* Writes legal actions ascending into out (capacity >= 128); returns the count. */
+/* Writes legal actions ascending into out (capacity >= ORC_MAX_LEGAL); returns the count. */
 int orc_legal_actions(const orc_state* s, int* out);
 /* Returns 0, or -1 when the action is illegal. */
 int orc_apply(orc_state* s, int action);
