@@ -33,7 +33,7 @@ extern "C" {
 
 /* Game ids.  Strings accepted by bsg_game_id are the reference's game strings
  * (open_spiel/spiel.h:792-803): "tic_tac_toe", "connect_four", "breakthrough",
- * "breakthrough(rows=8,columns=8)", "hex", "hex(board_size=11)". */
+ * "breakthrough(rows=8,columns=8)", "hex", "hex(board_size=11)", "pentago". */
 #define BSG_TIC_TAC_TOE 0
 #define BSG_CONNECT_FOUR 1
 #define BSG_BREAKTHROUGH 2
@@ -41,6 +41,9 @@ extern "C" {
 /* Host-helper-only id used to check the hex logic against the reference's 5x5 golden
  * playthrough; no device kernels exist for it. */
 #define BSG_HEX5_HOST_ONLY 4
+/* open_spiel/games/pentago.cc — the first game of SURVEY.md section 8f row 4 (more
+ * perfect-information board games on the same kernels). */
+#define BSG_PENTAGO 5
 
 #define BSG_OK 0
 #define BSG_ERR_BAD_GAME (-1)

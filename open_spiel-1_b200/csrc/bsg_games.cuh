@@ -38,6 +38,7 @@ struct TicTacToe {
   BSG_HD static int plane_bytes(int p) { (void)p; return 4; }
   static constexpr bool kCanStick = false;  // a non-terminal state always has a legal action
   static constexpr bool kAsync = false;     // a step completes within the step (see HexT)
+  static constexpr bool kMoverCanLose = false;  // a move never ends the game in the mover's disfavour (see Pentago)
   struct State {
     u32 cur, opp;   // marks of the player to move / of the other player (9-bit masks)
     u32 left;       // empty cells; parity = player to move (x = player 0 first, 9 cells)
@@ -186,6 +187,7 @@ struct ConnectFour {
   BSG_HD static int plane_bytes(int p) { (void)p; return 8; }
   static constexpr bool kCanStick = false;
   static constexpr bool kAsync = false;
+  static constexpr bool kMoverCanLose = false;
   struct State {
     u64 cur, opp;  // stones of the player to move / of the other player
     u32 left;      // empty cells; 42 - left stones on the board, parity = player to move
@@ -369,6 +371,7 @@ struct Breakthrough {
   // per-step test is gone.
   static constexpr bool kCanStick = true;
   static constexpr bool kAsync = false;
+  static constexpr bool kMoverCanLose = false;
   static constexpr u64 kCol0 = 0x0101010101010101ull, kCol7 = 0x8080808080808080ull;
   struct State { u64 own, opp; u32 mv, term, outc; };
   // sel4: the last two levels of the weighted rank-select as one look-up.  Index = h4 << 8 |
@@ -611,6 +614,7 @@ struct HexT {
   BSG_HD static int plane_bytes(int p) { (void)p; return 16; }
   static constexpr bool kCanStick = false;
   static constexpr bool kAsync = true;
+  static constexpr bool kMoverCanLose = false;
   struct State {
     u32 cO[4], cA[4], cB[4];   // side to move: all stones / edge-A connected / edge-B connected
     u32 oO[4], oA[4], oB[4];   // the side that moved last
@@ -896,5 +900,186 @@ struct HexT {
   }
 };
 typedef HexT<11> Hex;
+
+// =========================================================================================
+// pentago — reference: open_spiel/games/pentago.cc   (one more
+//   perfect-information board game on the same kernel framework)
+//   6 x 6 board, a move places a stone on an empty cell and then turns one 3 x 3 quadrant a
+//   quarter turn: action = (y * 6 + x) * 8 + r, quadrant = r >> 1 numbered clockwise from the
+//   top-left (0 TL, 1 TR, 2 BR, 3 BL), r & 1 = 0 counter-clockwise / 1 clockwise
+//   (pentago.cc:52-75,78-85,132-141).  Five in a row wins — and because the turn comes after
+//   the stone, a move can complete the OPPONENT's line (they win) or both (draw): the one game
+//   here where the mover can lose by moving (kMoverCanLose; pentago.cc:290-308).
+//   Bit = y * 8 + x in one u64 per colour (two guard columns keep shifts from wrapping), which
+//   is also the reference's ascending action order, so the k-th legal action is the (k >> 3)-th
+//   empty cell with rotation k & 7.  The quadrant turn is a 512-entry look-up on the nine
+//   cells; the 32 win lines are four bit-parallel run-of-five tests.
+//   packed: one 16-byte element = {player 0's stones | outcome code << 48, player 1's stones}.
+// =========================================================================================
+struct Pentago {
+  static constexpr int kId = kGamePentago;
+  static constexpr int kNumActions = 288, kMaxLen = 36, kObsSize = 108, kStateBytes = 16;
+  static constexpr int kObsWords = 4, kMaskWords = 9;
+  static constexpr int kPlanes = 1;
+  BSG_HD static int plane_bytes(int p) { (void)p; return 16; }
+  static constexpr bool kCanStick = false;
+  static constexpr bool kAsync = false;
+  static constexpr bool kMoverCanLose = true;
+  static constexpr u64 kBoard = 0x00003F3F3F3F3F3Full;
+  struct State {
+    u64 cur, opp;   // stones of the player to move / of the player who moved last
+    u32 left;       // empty cells (36..0); parity = player to move (player 0 first, 36 is even)
+    u32 res;        // bit 0: the last mover has five in a row; bit 1: the player to move has
+  };
+  // rot[d][m]: the nine cells m (bit 3 * row + col) of a quadrant after a quarter turn, d = 0
+  // counter-clockwise / 1 clockwise, already spread to board rows (bits 0-2, 8-10, 16-18).
+  struct Tables { u32 modM[64]; u32 rot[2][512]; };
+  static void fill_tables(Tables& t) {
+    for (u32 e = 0; e < 64; ++e) t.modM[e] = modM_entry(e * 8u);   // n = 8 * empty cells
+    for (u32 d = 0; d < 2; ++d)
+      for (u32 m = 0; m < 512; ++m) {
+        u32 out = 0;
+        for (u32 r = 0; r < 3; ++r)
+          for (u32 c = 0; c < 3; ++c)
+            if ((m >> (3 * r + c)) & 1u) {
+              // clockwise, y growing downwards: (row r, col c) -> (row c, col 2 - r)
+              u32 nr = d ? c : 2 - c, nc = d ? 2 - r : r;
+              out |= 1u << (8 * nr + nc);
+            }
+        t.rot[d][m] = out;
+      }
+  }
+  BSG_HD static void init(State& s) { s.cur = 0; s.opp = 0; s.left = 36; s.res = 0; }
+  BSG_HD static int mover(const State& s) { return (int)(s.left & 1u); }
+  BSG_HD static bool terminal(const State& s) { return s.res != 0 || s.left == 0; }
+  BSG_HD static bool won(const State& s) { return s.res == 1u; }    // the last mover won
+  BSG_HD static bool lost(const State& s) { return s.res == 2u; }   // ... lost by moving
+  BSG_HD static int outcome(const State& s) {
+    if (s.res == 1u) return mover(s) ^ 1;
+    if (s.res == 2u) return mover(s);
+    return (s.res == 3u || s.left == 0) ? kOutcomeDraw : kOutcomeNone;
+  }
+  BSG_HD static void load(State& s, const void* base, int64_t n, int64_t i) {
+    (void)n;
+#if defined(__CUDA_ARCH__)
+    ulonglong2 w = ((const ulonglong2*)base)[i];
+    u64 w0 = w.x, p1 = w.y;
+#else
+    u64 w0 = ((const u64*)base)[2 * i], p1 = ((const u64*)base)[2 * i + 1];
+#endif
+    u64 p0 = w0 & kBoard;
+    u32 outc = (u32)(w0 >> 48) & 3u;
+    s.left = 36u - (u32)(popc64(p0) + popc64(p1));
+    u32 mv = s.left & 1u;
+    s.cur = mv ? p1 : p0;
+    s.opp = mv ? p0 : p1;
+    // outcome code -> who has a line, relative to the last mover (1 - mv)
+    s.res = outc == (u32)kOutcomeNone ? 0u : (outc == (u32)kOutcomeDraw ? 3u : (outc == (mv ^ 1u) ? 1u : 2u));
+  }
+  BSG_HD static void store(const State& s, void* base, int64_t n, int64_t i) {
+    (void)n;
+    u32 mv = (u32)mover(s);
+    u64 p0 = mv ? s.opp : s.cur, p1 = mv ? s.cur : s.opp;
+    ((u64*)base)[2 * i] = p0 | ((u64)(u32)outcome(s) << 48);
+    ((u64*)base)[2 * i + 1] = p1;
+  }
+  // pentago.cc:104-125: the 32 runs of five, as four bit-parallel directions.
+  BSG_HD static bool has_five(u64 b) {
+    u64 acc = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int d = i == 0 ? 1 : (i == 1 ? 8 : (i == 2 ? 9 : 7));
+      u64 t = b & (b >> d);
+      u64 u = t & (t >> (2 * d));
+      acc |= u & (b >> (4 * d));
+    }
+    return acc != 0;
+  }
+  // Bit offset of the quadrant's top-left cell: TL 0, TR 3, BR 27, BL 24.
+  BSG_HD static u32 quadrant_shift(u32 q) { return (0x181B0300u >> (8u * q)) & 0xFFu; }
+  BSG_HD static u64 turn(u64 b, u32 sh, u32 dir, const Tables& tab) {
+    u32 w = (u32)(b >> sh);
+    u32 m = (w & 7u) | ((w >> 5) & 0x38u) | ((w >> 10) & 0x1C0u);
+    return (b & ~(0x070707ull << sh)) | ((u64)tab.rot[dir][m] << sh);
+  }
+  // pentago.cc:274-312 from the placed stone on: turn both colours, test both players' lines.
+  BSG_HD static void play(State& s, int pos, u32 r, const Tables& tab) {
+    const u32 sh = quadrant_shift(r >> 1), dir = r & 1u;
+    u64 mine = turn(s.cur | (1ull << pos), sh, dir, tab);
+    u64 theirs = turn(s.opp, sh, dir, tab);
+    s.res = (has_five(mine) ? 1u : 0u) | (has_five(theirs) ? 2u : 0u);
+    s.cur = theirs;
+    s.opp = mine;
+    s.left -= 1u;
+  }
+  BSG_HD static int cell_of(int pos) { return (pos >> 3) * 6 + (pos & 7); }
+  BSG_HD static int pos_of(int cell) { return (cell / 6) * 8 + cell % 6; }
+  BSG_HD static u32 step(State& s, u32 r, const Tables& tab, int& action) {
+    const u64 e = ~(s.cur | s.opp) & kBoard;               // pentago.cc:147-160
+    const u32 n = s.left * 8u;
+    const u32 k = fastmod(r, n, tab.modM[s.left & 63u]);   // dead lanes: left wraps, index stays in range
+    u32 j = k >> 3;                                        // the j-th empty cell, ascending
+    u32 w = (u32)e;
+    int pos = 0;
+    const u32 c = (u32)popc32(w);
+    if (j >= c) { j -= c; pos = 32; w = (u32)(e >> 32); }
+    pos += select32(w, (int)j);
+    pos &= 63;
+    action = cell_of(pos) * 8 + (int)(k & 7u);
+    play(s, pos, k & 7u, tab);
+    return n;
+  }
+  BSG_HD static int legal(const State& s, int* out) {
+    if (terminal(s)) return 0;
+    int n = 0;
+    for (int cell = 0; cell < 36; ++cell)
+      if (!(((s.cur | s.opp) >> pos_of(cell)) & 1ull))
+        for (int r = 0; r < 8; ++r) out[n++] = cell * 8 + r;
+    return n;
+  }
+  BSG_HD static bool apply(State& s, int a, const Tables& tab) {
+    if (terminal(s) || a < 0 || a >= kNumActions) return false;
+    const int pos = pos_of(a >> 3);
+    if (((s.cur | s.opp) >> pos) & 1ull) return false;
+    play(s, pos, (u32)a & 7u, tab);
+    return true;
+  }
+  BSG_HD static u32 legal_bit(const State& s, int a) {
+    return (!terminal(s) && !(((s.cur | s.opp) >> pos_of(a >> 3)) & 1ull)) ? 1u : 0u;
+  }
+  // Rows of 8 bits -> rows of 6 bits (cell order of the observation planes).
+  BSG_HD static u64 compact(u64 b) {
+    u64 out = 0;
+#pragma unroll
+    for (int y = 0; y < 6; ++y) out |= ((b >> (8 * y)) & 0x3Full) << (6 * y);
+    return out;
+  }
+  // pentago.cc:246-272: plane 0 the observer's stones, 1 the other player's, 2 empty.
+  BSG_HD static u32 obs_bit(const State& s, int player, int idx) {
+    int plane = idx / 36, pos = pos_of(idx - plane * 36);
+    u64 own = (mover(s) == player) ? s.cur : s.opp, other = (mover(s) == player) ? s.opp : s.cur;
+    u64 m = plane == 0 ? own : (plane == 1 ? other : ~(own | other));
+    return (u32)(m >> pos) & 1u;
+  }
+  BSG_HD static void obs_words(const State& s, int player, u32* out) {
+    u64 own = (mover(s) == player) ? s.cur : s.opp, other = (mover(s) == player) ? s.opp : s.cur;
+    u64 a = compact(own), b = compact(other), e = compact(~(own | other) & kBoard);
+    out[0] = (u32)a;                                         // bits 0..35 own, 36..71 other, 72..107 empty
+    out[1] = (u32)(a >> 32) | (u32)(b << 4);
+    out[2] = (u32)(b >> 28) | (u32)(e << 8);
+    out[3] = (u32)(e >> 24);
+  }
+  // eight action bits per empty cell: byte `cell` of the 288-bit string
+  BSG_HD static void mask_words(const State& s, u32* out) {
+    u64 e = terminal(s) ? 0ull : compact(~(s.cur | s.opp) & kBoard);
+#pragma unroll
+    for (int w = 0; w < kMaskWords; ++w) {
+      u32 nib = (u32)(e >> (4 * w)) & 0xFu;
+      out[w] = ((nib & 1u) ? 0xFFu : 0u) | ((nib & 2u) ? 0xFF00u : 0u) |
+               ((nib & 4u) ? 0xFF0000u : 0u) | ((nib & 8u) ? 0xFF000000u : 0u);
+    }
+  }
+};
+
 
 }  // namespace bsg

@@ -13,6 +13,7 @@
 namespace bsg {
 
 typedef HexT<5> Hex5;
+constexpr int kMaxLegal = 320;   // pentago: 36 cells x 8 rotations
 
 template <class G> struct TablesOf {
   static const typename G::Tables& get() {
@@ -29,6 +30,7 @@ template <class G> struct TablesOf {
 template <class G> inline bool apply_any(typename G::State& s, int a) { return G::apply(s, a); }
 template <> inline bool apply_any<Hex>(Hex::State& s, int a) { return Hex::apply(s, a, TablesOf<Hex>::get()); }
 template <> inline bool apply_any<Hex5>(Hex5::State& s, int a) { return Hex5::apply(s, a, TablesOf<Hex5>::get()); }
+template <> inline bool apply_any<Pentago>(Pentago::State& s, int a) { return Pentago::apply(s, a, TablesOf<Pentago>::get()); }
 
 // Calls f.template operator()<G>() for the game id; returns BSG_ERR_BAD_GAME otherwise.
 template <class F> inline int dispatch_game(int game, F&& f) {
@@ -38,17 +40,19 @@ template <class F> inline int dispatch_game(int game, F&& f) {
     case BSG_BREAKTHROUGH: return f.template operator()<Breakthrough>();
     case BSG_HEX: return f.template operator()<Hex>();
     case BSG_HEX5_HOST_ONLY: return f.template operator()<Hex5>();
+    case BSG_PENTAGO: return f.template operator()<Pentago>();
     default: break;
   }
   return BSG_ERR_BAD_GAME;
 }
-// The four games that have device kernels.
+// The games that have device kernels.
 template <class F> inline int dispatch_device_game(int game, F&& f) {
   switch (game) {
     case BSG_TIC_TAC_TOE: return f.template operator()<TicTacToe>();
     case BSG_CONNECT_FOUR: return f.template operator()<ConnectFour>();
     case BSG_BREAKTHROUGH: return f.template operator()<Breakthrough>();
     case BSG_HEX: return f.template operator()<Hex>();
+    case BSG_PENTAGO: return f.template operator()<Pentago>();
     default: break;
   }
   return BSG_ERR_BAD_GAME;
@@ -84,7 +88,7 @@ struct LegalOp {
   template <class G> int operator()() const {
     typename G::State s;
     G::load(s, p, cap, i);
-    int tmp[128];
+    int tmp[kMaxLegal];
     int n = G::legal(s, tmp);
     if (n > capacity) return BSG_ERR_BAD_ARG;
     for (int k = 0; k < n; ++k) out[k] = tmp[k];
@@ -110,7 +114,7 @@ struct StepOp {
     typename G::State s;
     G::load(s, p, cap, i);
     if (G::terminal(s)) return BSG_ERR_ILLEGAL_ACTION;
-    int tmp[128];
+    int tmp[kMaxLegal];
     if (G::legal(s, tmp) == 0) return BSG_ERR_STUCK_LANE;
     int a = -1;
     G::step(s, r, TablesOf<G>::get(), a);
@@ -287,6 +291,33 @@ template <int N> struct Text<HexT<N>> {  // hex.cc:229-246, cell characters hex.
   static bool has_board_format() { return false; }
   static std::string serialize(const typename H::State&) { return std::string(); }
   static int deserialize(typename H::State&, const char*) { return BSG_ERR_BAD_ARG; }
+};
+
+template <> struct Text<Pentago> {  // pentago.cc:168-217 (plain output, no ANSI colours)
+  static std::string to_string(const Pentago::State& s) {
+    const u64 p0 = Pentago::mover(s) ? s.opp : s.cur, p1 = Pentago::mover(s) ? s.cur : s.opp;
+    const char* left[6] = {"v", "s", " ", " ", "z", "^"};
+    const char* right[6] = {"v", "v", " ", " ", "w", "^"};
+    std::string out = "    > t     u <\n    a b c d e f\n";
+    for (int y = 0; y < 6; ++y) {
+      out += left[y];
+      out += ' ';
+      out += (char)('1' + y);
+      out += ' ';
+      for (int x = 0; x < 6; ++x) {
+        const int pos = y * 8 + x;
+        out += ((p0 >> pos) & 1ull) ? 'O' : (((p1 >> pos) & 1ull) ? '@' : '.');
+        out += ' ';
+      }
+      out += right[y];
+      out += '\n';
+    }
+    out += "    > y     x <\n";
+    return out;
+  }
+  static bool has_board_format() { return false; }
+  static std::string serialize(const Pentago::State&) { return std::string(); }
+  static int deserialize(Pentago::State&, const char*) { return BSG_ERR_BAD_ARG; }
 };
 
 struct ToStringOp {

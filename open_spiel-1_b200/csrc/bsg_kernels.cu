@@ -74,7 +74,8 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
   // in a terminal state (fin_term) and whether that was a win (fin_win).  A win is always the
   // last mover's, so the winner follows from the root's mover and the parity of t.
   // Flags are 0/1 words (not bools) so they stay in plain registers.
-  u32 live = 0, have = 0, fin_term = 0, fin_win = 0;
+  // (fin_lose: only in a game whose mover can lose by moving — pentago.)
+  u32 live = 0, have = 0, fin_term = 0, fin_win = 0, fin_lose = 0;
   u32 lid = 0, t = 0, limit = 0xFFFFFFFFu, root_mv = 0;
   u32 my_steps = 0, my_done = 0, my_stuck = 0;
   int my_ret = 0;
@@ -96,7 +97,10 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
     }
     if (live == 0) {
       if (have) {  // publish the finished playout
-        const int ret = (fin_term & fin_win) ? (int)(((root_mv ^ t) & 1u) << 1) - 1 : 0;
+        int ret = (fin_term & fin_win) ? (int)(((root_mv ^ t) & 1u) << 1) - 1 : 0;
+        if constexpr (G::kMoverCanLose) {
+          if (fin_term & fin_lose) ret = 1 - (int)(((root_mv ^ t) & 1u) << 1);
+        }
         if (out & kOutRet) a.io.ret0[lid] = (int8_t)ret;
         if (out & kOutLength) a.io.length[lid] = (uint8_t)t;
         if (out & kOutTerminal) a.io.terminal[lid] = (uint8_t)fin_term;
@@ -129,6 +133,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         live = (!term && (!kFull || limit > 0)) ? 1u : 0u;
         fin_term = (kFull && !term) ? 0u : 1u;   // a lean playout always runs to a terminal state
         fin_win = G::won(s) ? 1u : 0u;
+        if constexpr (G::kMoverCanLose) fin_lose = G::lost(s) ? 1u : 0u;
         if constexpr (G::kCanStick) {
           // non-terminal root without a legal action: only a root can be (see the game's note)
           if (!term && !G::has_move(s)) { live = 0; fin_term = 0; fin_win = 0; my_stuck += 1; }
@@ -198,6 +203,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
             live = 0;
             fin_term = term ? 1u : 0u;
             fin_win = (term && G::won(s)) ? 1u : 0u;
+            if constexpr (G::kMoverCanLose) fin_lose = (term && G::lost(s)) ? 1u : 0u;
             if (a.io.final_states) {
               if (term && a.io.final_before_terminal) G::store(prev, a.io.final_states, a.n_playouts, lid);
               else G::store(s, a.io.final_states, a.n_playouts, lid);
@@ -210,6 +216,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         const u32 term = G::terminal(s) ? 1u : 0u;
         const u32 won = G::won(s) ? 1u : 0u;
         fin_win |= can & won;
+        if constexpr (G::kMoverCanLose) fin_lose |= can & (G::lost(s) ? 1u : 0u);
         t += can;
         live &= (can & term) ^ 1u;
       }
@@ -535,6 +542,8 @@ int bsg_game_id(const char* g) {
       s == "breakthrough(columns=8,rows=8)") return BSG_BREAKTHROUGH;
   if (s == "hex" || s == "hex()" || s == "hex(board_size=11)") return BSG_HEX;
   if (s == "hex(board_size=5)") return BSG_HEX5_HOST_ONLY;
+  if (s == "pentago" || s == "pentago()" || s == "pentago(ansi_color_output=False)" ||
+      s == "pentago(ansi_color_output=false)") return BSG_PENTAGO;
   return BSG_ERR_BAD_GAME;
 }
 
@@ -550,6 +559,7 @@ int bsg_observation_shape(int game, int shape[3]) {
     case BSG_BREAKTHROUGH: shape[0] = 3; shape[1] = 8; shape[2] = 8; return BSG_OK;  // breakthrough.h:107-109
     case BSG_HEX: shape[0] = 9; shape[1] = 11; shape[2] = 11; return BSG_OK;         // hex.h:113-115
     case BSG_HEX5_HOST_ONLY: shape[0] = 9; shape[1] = 5; shape[2] = 5; return BSG_OK;
+    case BSG_PENTAGO: shape[0] = 3; shape[1] = 6; shape[2] = 6; return BSG_OK;       // pentago.h:106-108
     default: return BSG_ERR_BAD_GAME;
   }
 }
@@ -605,7 +615,7 @@ uint32_t bsg_draw(uint64_t seed, uint64_t playout, uint32_t t) {
 int bsg_create(int game, int device, bsg_engine** out) {
   if (!out) return BSG_ERR_BAD_ARG;
   *out = nullptr;
-  if (game < 0 || game > BSG_HEX) return BSG_ERR_BAD_GAME;
+  if (game < 0 || game == BSG_HEX5_HOST_ONLY || game > BSG_PENTAGO) return BSG_ERR_BAD_GAME;
   int count = 0;
   if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return BSG_ERR_NO_DEVICE;
   if (device < 0 || device >= count) return BSG_ERR_BAD_ARG;

@@ -78,7 +78,7 @@ struct MctsTree : MctsBase {
   }
   // mcts.py:308-324: children from the evaluator's prior (uniform, legal order), shuffled.
   void expand(int32_t node, const State& st) {
-    int legal[128 * 6 + 8];
+    int legal[kMaxLegal > 128 * 6 + 8 ? kMaxLegal : 128 * 6 + 8];
     int n = G::legal(st, legal);
     std::vector<int> acts(legal, legal + n);
     shuffle(acts);

@@ -14,6 +14,7 @@ ROOT_DEPTHS = {  # cfg2 U{8..20}, cfg3 U{0..40}, cfg4 U{0..60}
     "connect_four": (8, 20),
     "breakthrough": (0, 40),
     "hex": (0, 60),
+    "pentago": (0, 20),
 }
 
 

@@ -47,9 +47,10 @@ class GameType:
 
 _CANONICAL = {C.TIC_TAC_TOE: "tic_tac_toe()", C.CONNECT_FOUR: "connect_four()",
               C.BREAKTHROUGH: "breakthrough(columns=8,rows=8)", C.HEX: "hex(board_size=11)",
-              C.HEX5_HOST_ONLY: "hex(board_size=5)"}
+              C.HEX5_HOST_ONLY: "hex(board_size=5)", C.PENTAGO: "pentago(ansi_color_output=False)"}
 _SHORT = {C.TIC_TAC_TOE: "tic_tac_toe", C.CONNECT_FOUR: "connect_four",
-          C.BREAKTHROUGH: "breakthrough", C.HEX: "hex", C.HEX5_HOST_ONLY: "hex"}
+          C.BREAKTHROUGH: "breakthrough", C.HEX: "hex", C.HEX5_HOST_ONLY: "hex",
+          C.PENTAGO: "pentago"}
 
 
 class Game:
@@ -189,9 +190,9 @@ class State:
     cur, term, _ = self._info()
     if term or (player is not None and player != cur):
       return []  # empty for the non-mover, as the reference (basic_tests.cc:84-106)
-    out = np.zeros(128, np.int64)
+    out = np.zeros(320, np.int64)
     n = C.check(C.lib.bsg_host_legal_actions(self._gid, self._packed.ctypes.data, 1, 0,
-                                             out.ctypes.data, 128))
+                                             out.ctypes.data, 320))
     return out[:n].tolist()
 
   def legal_actions_mask(self, player=None):

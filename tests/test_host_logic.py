@@ -18,7 +18,8 @@ from oracle_lib import Oracle
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 GAMES = [("tic_tac_toe", "tic_tac_toe", 11), ("connect_four", "connect_four", 11),
-         ("breakthrough", "breakthrough", 11), ("hex", "hex", 11), ("hex(board_size=5)", "hex", 5)]
+         ("breakthrough", "breakthrough", 11), ("hex", "hex", 11), ("hex(board_size=5)", "hex", 5),
+         ("pentago", "pentago", 11)]
 
 
 @pytest.fixture(scope="module")
@@ -41,7 +42,8 @@ def check_state(oracle, st, oname, bs, hist):
 @pytest.mark.parametrize("fixture,name", [("tic_tac_toe", "tic_tac_toe"),
                                           ("connect_four", "connect_four"),
                                           ("breakthrough", "breakthrough"),
-                                          ("hex5", "hex(board_size=5)")])
+                                          ("hex5", "hex(board_size=5)"),
+                                          ("pentago", "pentago")])
 def test_golden_playthroughs(fixture, name):
   with open(os.path.join(GOLD, "playthrough_%s.json" % fixture)) as f:
     data = json.load(f)
