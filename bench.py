@@ -32,7 +32,11 @@ sys.path.insert(0, os.path.join(REPO, "tests"))
 
 import numpy as np  # noqa: E402
 
-OPS_PER_STEP = {"tic_tac_toe": 48, "connect_four": 96, "breakthrough": 140, "hex": 200}
+OPS_PER_STEP = {"tic_tac_toe": 48, "connect_four": 96, "breakthrough": 140, "hex": 200,
+                # pentago (not in SURVEY 8d; same counting rules): legal 4, rng 25, mod 4, 64-bit
+                # rank-select 24, place 2, two quadrant turns 24, two 4-direction run-of-five
+                # tests on 64-bit boards 96, outcome/loop 6
+                "pentago": 185}
 ROOT_SEED = 20240611
 METRIC = "connect_four game-steps/s (uniform-random playouts from mid-game roots)"
 
@@ -124,7 +128,8 @@ def sample_histories(game, n, seed):
   under the same recipe as the GPU roots (d ~ U{dmin..dmax}; stop before a terminal move)."""
   from oracle_lib import Oracle
   from importlib import import_module
-  depths = {"tic_tac_toe": (0, 4), "connect_four": (8, 20), "breakthrough": (0, 40), "hex": (0, 60)}
+  depths = {"tic_tac_toe": (0, 4), "connect_four": (8, 20), "breakthrough": (0, 40), "hex": (0, 60),
+            "pentago": (0, 20)}
   dmin, dmax = depths[game]
   orc = Oracle()
   rng = np.random.RandomState(seed & 0x7FFFFFFF)
@@ -395,7 +400,8 @@ def rank0_extras(args, eng, torch, dev, steps_per_s_per_gpu, kernel_ms, n):
       del st
       e_bt.close()
       torch.cuda.empty_cache()
-      for g, npl in (("tic_tac_toe", 1 << 24), ("breakthrough", 1 << 22), ("hex", 1 << 20)):
+      for g, npl in (("tic_tac_toe", 1 << 24), ("breakthrough", 1 << 22), ("hex", 1 << 20),
+                     ("pentago", 1 << 22)):
         e_g = bsg.Engine(g, eng.device)
         dmin, dmax = ROOT_DEPTHS[g]
         st, _ = make_roots(e_g, npl, dmin, dmax, seed=ROOT_SEED + 4)

@@ -933,9 +933,17 @@ struct Pentago {
   };
   // rot[d][m]: the nine cells m (bit 3 * row + col) of a quadrant after a quarter turn, d = 0
   // counter-clockwise / 1 clockwise, already spread to board rows (bits 0-2, 8-10, 16-18).
-  struct Tables { u32 modM[64]; u32 rot[2][512]; };
+  // sel6[row << 3 | k]: column of the k-th empty cell of a board row (6-bit mask).
+  struct Tables { u32 modM[64]; u32 rot[2][512]; unsigned char sel6[512]; };
   static void fill_tables(Tables& t) {
     for (u32 e = 0; e < 64; ++e) t.modM[e] = modM_entry(e * 8u);   // n = 8 * empty cells
+    for (u32 row = 0; row < 64; ++row)
+      for (u32 k = 0; k < 8; ++k) {
+        u32 seen = 0, col = 0;
+        for (u32 c = 0; c < 6; ++c)
+          if ((row >> c) & 1u) { if (seen == k) col = c; ++seen; }
+        t.sel6[(row << 3) | k] = (unsigned char)col;
+      }
     for (u32 d = 0; d < 2; ++d)
       for (u32 m = 0; m < 512; ++m) {
         u32 out = 0;
@@ -983,20 +991,28 @@ struct Pentago {
     ((u64*)base)[2 * i] = p0 | ((u64)(u32)outcome(s) << 48);
     ((u64*)base)[2 * i + 1] = p1;
   }
-  // pentago.cc:104-125: the 32 runs of five, as four bit-parallel directions.
+  // pentago.cc:104-125: the 32 runs of five, as four bit-parallel directions, on the two
+  // 32-bit words (rows 0-3 / rows 4-5).  Rows: inside each word, with left shifts (they can
+  // run on the multiplier pipe).  Columns and diagonals: the top cell of such a run is in row
+  // 0 or 1, so only the LOW word of the product matters — pairs, then pairs of pairs (both
+  // inside rows 0-3 of the low word), then the fifth cell four rows further down, which is
+  // the high word shifted into place.
   BSG_HD static bool has_five(u64 b) {
-    u64 acc = 0;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int d = i == 0 ? 1 : (i == 1 ? 8 : (i == 2 ? 9 : 7));
-      u64 t = b & (b >> d);
-      u64 u = t & (t >> (2 * d));
-      acc |= u & (b >> (4 * d));
-    }
+    const u32 lo = (u32)b, hi = (u32)(b >> 32);
+    u32 tl = lo & (lo << 1), th = hi & (hi << 1);
+    u32 acc = (tl & (tl << 2) & (lo << 4)) | (th & (th << 2) & (hi << 4));
+    u32 t = lo & fshr(lo, hi, 8);                 // columns: rows r, r+1
+    acc |= t & (t >> 16) & hi;                    //   r..r+3, then row r+4 = bit + 32
+    t = lo & fshr(lo, hi, 9);                     // diagonals down-right
+    acc |= t & (t >> 18) & (hi >> 4);             //   fifth cell at bit + 36
+    t = lo & fshr(lo, hi, 7);                     // diagonals down-left
+    acc |= t & (t >> 14) & fshr(lo, hi, 28);      //   fifth cell at bit + 28
     return acc != 0;
   }
   // Bit offset of the quadrant's top-left cell: TL 0, TR 3, BR 27, BL 24.
   BSG_HD static u32 quadrant_shift(u32 q) { return (0x181B0300u >> (8u * q)) & 0xFFu; }
+  // Quarter turn: the nine cells of the quadrant through the look-up.  (A word-level variant
+  // — funnel the half to one word, bit-select it back — compiled to more instructions.)
   BSG_HD static u64 turn(u64 b, u32 sh, u32 dir, const Tables& tab) {
     u32 w = (u32)(b >> sh);
     u32 m = (w & 7u) | ((w >> 5) & 0x38u) | ((w >> 10) & 0x1C0u);
@@ -1021,9 +1037,11 @@ struct Pentago {
     u32 j = k >> 3;                                        // the j-th empty cell, ascending
     u32 w = (u32)e;
     int pos = 0;
-    const u32 c = (u32)popc32(w);
+    u32 c = (u32)popc32(w);
     if (j >= c) { j -= c; pos = 32; w = (u32)(e >> 32); }
-    pos += select32(w, (int)j);
+    c = (u32)popc32(w << 16); if (j >= c) { j -= c; pos += 16; w >>= 16; }   // two rows
+    c = (u32)popc32(w << 24); if (j >= c) { j -= c; pos += 8; w >>= 8; }     // the row
+    pos += (int)tab.sel6[((w << 3) & 0x1F8u) | (j & 7u)];                    // the column
     pos &= 63;
     action = cell_of(pos) * 8 + (int)(k & 7u);
     play(s, pos, k & 7u, tab);
