@@ -8,6 +8,7 @@ on-disk name `open_spiel-1_b200` is not a Python identifier).
   spiel.load_game / Game / State host mirror of the pyspiel surface the path touches
   mcts.MCTSBot / SearchNode      host tree with the reference's interface (+ batched leaves)
   parallel.RootParallelMCTS      root-parallel search, one NCCL all-reduce per search step
+  evaluate_bots.evaluate_bots    the reference's bot-vs-bot loop (+ play_match over many roots)
 
 The CUDA extension (libbsg.so) is mandatory: importing this package without it raises.
 """
@@ -17,7 +18,8 @@ from .evaluator import Evaluator, GpuRolloutEvaluator, AlphaZeroEvaluator
 from .spiel import load_game, Game, State, GameType, PlayerId
 from .mcts import MCTSBot, SearchNode, NativeMCTSBot, PhiloxShuffle
 from .parallel import RootParallelMCTS, ShardedPlayouts, shard_range
+from .evaluate_bots import evaluate_bots, play_match, UniformRandomBot
 
 __all__ = ["Engine", "game_id", "pack_histories", "draw", "Evaluator", "GpuRolloutEvaluator", "AlphaZeroEvaluator",
            "load_game", "Game", "State", "GameType", "PlayerId", "MCTSBot", "SearchNode", "NativeMCTSBot", "PhiloxShuffle",
-           "RootParallelMCTS", "ShardedPlayouts", "shard_range"]
+           "RootParallelMCTS", "ShardedPlayouts", "shard_range", "evaluate_bots", "play_match", "UniformRandomBot"]

@@ -121,6 +121,9 @@ class MCTSBot(object):
   def restart_at(self, state):
     pass
 
+  def inform_action(self, state, player_id, action):
+    pass  # pyspiel.Bot's default: the search keeps no state between moves
+
   def step_with_policy(self, state):
     t0 = time.time()
     root = self.mcts_search(state)
@@ -322,6 +325,9 @@ class NativeMCTSBot(object):
     return out
 
   def restart_at(self, state):
+    pass
+
+  def inform_action(self, state, player_id, action):
     pass
 
   def _packed(self, state):

@@ -296,3 +296,31 @@ def test_trees_per_rank_is_deterministic_and_equals_virtual_ranks(bsg):
     bot.close()
     eng.close()
   assert one_step == sorted((a, n, r) for a, (n, r) in total.items())
+
+
+def test_tournament_from_gpu_roots(bsg):
+  """evaluate_bots / play_match (algorithms/evaluate_bots.cc:24-62) with GPU-evaluated search
+  bots, from roots the playout kernel generated: a native-tree MCTS bot beats uniform-random
+  play at connect_four from both seats."""
+  from open_spiel_1_b200.roots import make_roots
+  game = bsg.load_game("connect_four")
+  eng = bsg.Engine("connect_four", 0)
+  _, hists = make_roots(eng, 24, 0, 4, seed=5, want_histories=True)
+  score = 0.0
+  for seat in (0, 1):
+    mcts_bot = bsg.NativeMCTSBot(game, UCT_C, 300, eng, n_rollouts=16, seed=3, shuffle_seed=seat,
+                                 leaf_batch=8)
+    rnd = bsg.UniformRandomBot(1 - seat, np.random.RandomState(seat))
+    bots = [mcts_bot, rnd] if seat == 0 else [rnd, mcts_bot]
+    roots = []
+    for h in hists:
+      s = game.new_initial_state()
+      for a in h:
+        s.apply_action(a)
+      roots.append(s)
+    mean, results = bsg.play_match(roots, bots)
+    assert all(r.is_terminal() for r in roots) and (results.sum(axis=1) == 0).all()
+    score += mean[seat]
+    mcts_bot.close()
+  assert score > 1.2          # wins the large majority from either seat
+  eng.close()

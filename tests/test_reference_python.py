@@ -132,3 +132,40 @@ def test_mirror_states_answer_like_pyspiel_states(refpy):
         rs.apply_action(0)
       with pytest.raises(RuntimeError):
         ms.apply_action(0)
+
+
+def test_evaluate_bots_mirror_plays_like_the_reference_loop(refpy):
+  """evaluate_bots (python/algorithms/evaluate_bots.py:24-50): with equal bot seeds the mirror
+  loop over mirror states and the same loop over pyspiel states play the same games (the
+  reference's own file imports the full pyspiel, so its sequential branch is restated here)."""
+  pyspiel, ref_mcts = refpy
+  import open_spiel_1_b200 as bsg
+
+  def reference_loop(state, bots):
+    for bot in bots:
+      bot.restart_at(state)
+    while not state.is_terminal():
+      current_player = state.current_player()
+      action = bots[current_player].step(state)
+      state.apply_action(action)
+    return state.returns()
+
+  for game in ("tic_tac_toe", "connect_four", "pentago"):
+    rg, mg = pyspiel.load_game(game), bsg.load_game(game)
+    total = np.zeros(2)
+    for g in range(15):
+      bots_m = [bsg.UniformRandomBot(0, np.random.RandomState(g)), bsg.UniformRandomBot(1, np.random.RandomState(100 + g))]
+      bots_r = [bsg.UniformRandomBot(0, np.random.RandomState(g)), bsg.UniformRandomBot(1, np.random.RandomState(100 + g))]
+      ms, rs = mg.new_initial_state(), rg.new_initial_state()
+      got = bsg.evaluate_bots(ms, bots_m, np.random)
+      want = reference_loop(rs, bots_r)
+      assert got == want and ms.history() == rs.history() and ms.is_terminal()
+      total += got
+    assert total.sum() == 0
+  # an MCTS bot (reference evaluator on the CPU) against a random bot through play_match
+  mg = bsg.load_game("tic_tac_toe")
+  ev = ref_mcts.RandomRolloutEvaluator(2, np.random.RandomState(1))
+  bots = [bsg.MCTSBot(mg, UCT_C, 200, ev, random_state=np.random.RandomState(2)),
+          bsg.UniformRandomBot(1, np.random.RandomState(3))]
+  mean, results = bsg.play_match([mg.new_initial_state() for _ in range(10)], bots)
+  assert results.shape == (10, 2) and mean[0] + mean[1] == 0 and mean[0] > 0   # x never loses to random play here
