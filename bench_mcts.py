@@ -122,22 +122,27 @@ def run_cfg5(args, bsg, local, rank, world):
   n_roll = 256
   total_sims = args.sims5 * world * args.trees         # weak scaling: fixed sims per tree
   ev = bsg.GpuRolloutEvaluator(eng, n_rollouts=n_roll, seed=11)
-  rp = bsg.RootParallelMCTS(game, 2.0, total_sims, ev, sims_per_step=args.sims_per_step,
-                            solve=True, seed=5, leaf_batch=args.leaf_batch, device=dev,
-                            native=args.native, trees_per_rank=args.trees)
+  if args.forest:
+    from open_spiel_1_b200.forest import ForestMCTS
+    rp = ForestMCTS(game, 2.0, total_sims, ev, args.trees, sims_per_step=args.sims_per_step,
+                    solve=True, seed=5, leaf_batch=args.leaf_batch, device=dev)
+  else:
+    rp = bsg.RootParallelMCTS(game, 2.0, total_sims, ev, sims_per_step=args.sims_per_step,
+                              solve=True, seed=5, leaf_batch=args.leaf_batch, device=dev,
+                              native=args.native, trees_per_rank=args.trees)
   state = game.new_initial_state()
   rp.mcts_search(state)                                # warm-up search
   torch.cuda.synchronize(dev)
   if dist is not None:
     dist.barrier()
-  steps0, ar0 = (rp.total_steps if args.native else ev.total_steps), rp.all_reduces
+  steps0, ar0 = (rp.total_steps if (args.native or args.forest) else ev.total_steps), rp.all_reduces
   t0 = time.perf_counter()
   root = rp.mcts_search(state)
   torch.cuda.synchronize(dev)
   secs = time.perf_counter() - t0
   stats = np.array([[c.action, c.explore_count, int(round(c.total_reward * n_roll))]
                     for c in sorted(root.children, key=lambda c: c.action)], np.int64)
-  steps_now = rp.total_steps if args.native else ev.total_steps
+  steps_now = rp.total_steps if (args.native or args.forest) else ev.total_steps
   t = torch.tensor([secs, float(steps_now - steps0)], dtype=torch.float64, device=dev)
   same = True
   if dist is not None:
@@ -157,7 +162,8 @@ def run_cfg5(args, bsg, local, rank, world):
                    "%d simulations/move/tree x %d tree(s)/rank x %d rank(s), %d sims per tree per "
                    "all-reduce step, leaf_batch %d"
                    % (n_roll, args.sims5, args.trees, world, args.sims_per_step, args.leaf_batch),
-         "tree": "native (csrc/bsg_mcts.cuh)" if args.native else "python mirror",
+         "tree": ("GPU-resident forest (csrc/bsg_forest.cuh)" if args.forest else
+                  ("native (csrc/bsg_mcts.cuh)" if args.native else "python mirror")),
          "n_gpus": world, "trees_per_rank": args.trees, "simulations": visits, "seconds": secs,
          "simulations_per_s": visits / secs, "playouts_per_s": visits * n_roll / secs,
          "game_steps_per_s": game_steps / secs, "all_reduces": rp.all_reduces - ar0,
@@ -188,6 +194,8 @@ def main():
   ap.add_argument("--leaf-batch", type=int, default=256)
   ap.add_argument("--trees", type=int, default=1,
                   help="cfg5: independent trees (host threads + engines) per rank, native only")
+  ap.add_argument("--forest", type=int, default=0,
+                  help="cfg5: 1 = the --trees trees of a rank live on the GPU (forest.ForestMCTS)")
   ap.add_argument("--native", type=int, default=1, help="cfg5: 1 = native host tree, 0 = Python mirror")
   args = ap.parse_args()
   rank, world, local = dist_env()

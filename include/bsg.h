@@ -152,6 +152,11 @@ typedef struct bsg_playout_io {
   void* state_log;
   int64_t state_log_cap;
   const int64_t* state_log_off;
+  /* Per-root playout ids: when non-NULL, rollout j of root i draws with the global id
+   * root_playout_base[i] + j instead of first_playout + i * rollouts + j, and a base of
+   * UINT64_MAX skips the root (no playout; nothing is added to its sums).  Lets many search
+   * trees, each with its own id range, share one launch (bsg_forest_*). */
+  const uint64_t* root_playout_base;
 } bsg_playout_io;
 
 /* The hot path.  Stands in for RandomRolloutEvaluator::Evaluate's playout loop
@@ -214,6 +219,48 @@ int bsg_mcts_set_root_child(bsg_mcts* m, int64_t action, int64_t visits, double 
                             int32_t outcome);
 int bsg_mcts_set_root_explore(bsg_mcts* m, int64_t root_explore);
 int bsg_mcts_set_next_playout(bsg_mcts* m, uint64_t next_playout);
+
+/* ---- GPU-resident search forest ("then a GPU-resident tree").
+ * n_trees independent MCTS trees in device memory, searched together: per round one kernel
+ * descends every tree (up to leaf_batch leaves each), one launch of the playout kernel
+ * evaluates all leaves of all trees, one kernel backs the results up.  Tree v runs exactly the
+ * search of bsg_mcts_create(.., shuffle_seed0 + v) with playout ids from first_playout +
+ * (v << 40): the algorithm of MCTSBot::MCTSearch (algorithms/mcts.cc:255-428,
+ * python/algorithms/mcts.py:292-443), visit for visit.  node_capacity bounds the nodes per
+ * tree, max_visits the visit count any node can reach (after root merges: the total of all
+ * trees of all ranks). */
+typedef struct bsg_forest bsg_forest;
+int bsg_forest_create(bsg_engine* e, int32_t n_trees, int32_t node_capacity, int64_t max_visits,
+                      double uct_c, int solve, int n_rollouts, int leaf_batch, uint64_t eval_seed,
+                      uint64_t shuffle_seed0, uint64_t first_playout, bsg_forest** out);
+void bsg_forest_destroy(bsg_forest* f);
+const char* bsg_forest_last_error(bsg_forest* f);
+/* Runs simulations_per_tree (or per_tree_host[v]) simulations in every tree from the packed
+ * host root; resume != 0 continues the trees of the previous call.  A tree left without
+ * children gets its root expanded (so that it joins a merge). */
+int bsg_forest_search(bsg_forest* f, const void* root_host, int64_t simulations_per_tree,
+                      const int64_t* per_tree_host, int resume);
+/* Root merge of root-parallel search, dense per action id (device buffers of the caller):
+ * base_dev int64[NumDistinctActions][2] = {visits, reward * n_rollouts} after the last merge;
+ * pack adds into out_dev int64[NumDistinctActions][5] (caller zeroes) the sum over the trees of
+ * {visit delta, scaled reward delta, proofs "mover loses / draws / wins"}; install writes
+ * base + summed into every tree's root children (summed = out_dev after the caller's
+ * all-reduce over ranks). */
+int bsg_forest_pack_root(bsg_forest* f, const int64_t* base_dev, int64_t* out_dev);
+int bsg_forest_install_root(bsg_forest* f, const int64_t* base_dev, const int64_t* summed_dev);
+/* Root children of one tree (as bsg_mcts_root_children); info = {root visits, root solved,
+ * root returns[0], nodes used}.  Returns the number of children. */
+int bsg_forest_tree_root(bsg_forest* f, int32_t tree, int capacity, int64_t* actions, int64_t* visits,
+                         double* reward, int32_t* outcome, double info[4]);
+/* info = {game steps played, kernel launches, rounds, trees}. */
+int bsg_forest_info(bsg_forest* f, double info[4]);
+/* Test hook, no GPU needed and not used by any product path: runs the forest's per-tree code
+ * on host memory next to the host tree of bsg_mcts_*, both fed stand-in leaf values hashed from
+ * the playout ids, for `sims` simulations and a resumed search of `sims_resume` more, from the
+ * state reached by `history`.  0 = every tree identical node for node; k > 0 = tree k - 1
+ * differs; < 0 = error. */
+int bsg_forest_selftest(int game, int n_trees, int sims, int sims_resume, int leaf_batch, int n_rollouts,
+                        int solve, uint64_t seed, const int64_t* history, int n_history);
 
 /* Integer-issue microbenchmark used for the roofline denominator (bench.py): runs `iters`
  * dependent-chain iterations of `ilp` independent 32-bit ops per thread on every SM and

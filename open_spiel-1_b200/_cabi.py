@@ -42,6 +42,7 @@ class PlayoutIO(ctypes.Structure):
       ("state_log", vp),
       ("state_log_cap", i64),
       ("state_log_off", vp),
+      ("root_playout_base", vp),
   ]
 
 
@@ -93,6 +94,17 @@ def _load():
       "bsg_mcts_set_root_child": (ctypes.c_int, [vp, i64, i64, ctypes.c_double, i32]),
       "bsg_mcts_set_root_explore": (ctypes.c_int, [vp, i64]),
       "bsg_mcts_set_next_playout": (ctypes.c_int, [vp, u64]),
+      "bsg_forest_create": (ctypes.c_int, [vp, i32, i32, i64, ctypes.c_double, ctypes.c_int, ctypes.c_int,
+                                           ctypes.c_int, u64, u64, u64, ctypes.POINTER(vp)]),
+      "bsg_forest_destroy": (None, [vp]),
+      "bsg_forest_last_error": (ctypes.c_char_p, [vp]),
+      "bsg_forest_search": (ctypes.c_int, [vp, vp, i64, vp, ctypes.c_int]),
+      "bsg_forest_pack_root": (ctypes.c_int, [vp, vp, vp]),
+      "bsg_forest_install_root": (ctypes.c_int, [vp, vp, vp]),
+      "bsg_forest_tree_root": (ctypes.c_int, [vp, i32, ctypes.c_int, vp, vp, vp, vp, vp]),
+      "bsg_forest_info": (ctypes.c_int, [vp, vp]),
+      "bsg_forest_selftest": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                             ctypes.c_int, ctypes.c_int, ctypes.c_int, u64, vp, ctypes.c_int]),
   }
   for name, (res, args) in sig.items():
     fn = getattr(lib, name)

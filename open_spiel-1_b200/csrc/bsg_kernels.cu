@@ -18,9 +18,11 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <vector>
 
 #include "bsg_host.cuh"
 #include "bsg_mcts.cuh"
+#include "bsg_forest.cuh"
 
 namespace bsg {
 
@@ -77,6 +79,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
   // (fin_lose: only in a game whose mover can lose by moving — pentago.)
   u32 live = 0, have = 0, fin_term = 0, fin_win = 0, fin_lose = 0;
   u32 lid = 0, t = 0, limit = 0xFFFFFFFFu, root_mv = 0;
+  unsigned long long pid0 = a.first_playout;   // playout id = pid0 + lid (per root with root_playout_base)
   u32 my_steps = 0, my_done = 0, my_stuck = 0;
   int my_ret = 0;
   u32 rnew[4] = {0, 0, 0, 0}, rold[4] = {0, 0, 0, 0}, nblk = 0xFFFFFFFFu;   // kAsync draws (below)
@@ -121,6 +124,12 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         lid = base + idx;
         u32 root = a.rollouts == 1 ? lid : lid / a.rollouts;
         G::load(s, a.roots, a.n_roots, a.root0 + root);
+        bool skip = false;
+        if (kFull && a.io.root_playout_base) {
+          const unsigned long long rb = a.io.root_playout_base[a.root0 + root];
+          skip = rb == 0xFFFFFFFFFFFFFFFFull;
+          pid0 = rb - (unsigned long long)root * a.rollouts;
+        }
         t = 0;
         nblk = 0xFFFFFFFFu;
         root_mv = (u32)G::mover(s);
@@ -129,11 +138,12 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
           if (a.io.step_limit) limit = min(limit, (u32)a.io.step_limit[lid]);
           prev = s;
         }
-        const bool term = G::terminal(s);
+        const bool term = G::terminal(s) || (kFull && skip);
         live = (!term && (!kFull || limit > 0)) ? 1u : 0u;
         fin_term = (kFull && !term) ? 0u : 1u;   // a lean playout always runs to a terminal state
         fin_win = G::won(s) ? 1u : 0u;
         if constexpr (G::kMoverCanLose) fin_lose = G::lost(s) ? 1u : 0u;
+        if (kFull && skip) { fin_win = 0; fin_lose = 0; }   // a skipped slot holds no state
         if constexpr (G::kCanStick) {
           // non-terminal root without a legal action: only a root can be (see the game's note)
           if (!term && !G::has_move(s)) { live = 0; fin_term = 0; fin_win = 0; my_stuck += 1; }
@@ -148,7 +158,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
       continue;
     }
 
-    const unsigned long long pid = a.first_playout + lid;
+    const unsigned long long pid = (kFull ? pid0 : a.first_playout) + lid;
     u32 rr[4];
     if constexpr (!G::kAsync) {
       philox4x32_10((u32)pid, (u32)(pid >> 32), t >> 2, 0u, a.keys, rr);
@@ -447,6 +457,44 @@ struct CreateOp {
   }
 };
 
+
+// ---- GPU-resident search forest (bsg_forest.cuh): one thread per tree ---------------------
+constexpr int kForestThreads = 64;
+template <class G>
+__global__ void forest_reset_kernel(ForestView F) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v < F.n_trees) ForestTree<G>::reset(F, v);
+}
+template <class G>
+__global__ void forest_descend_kernel(ForestView F, const typename G::Tables* __restrict__ tab) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= F.n_trees) return;
+  if (F.sims_left[v] > 0) atomicAdd(F.active, 1u);
+  ForestTree<G>::descend(F, v, *tab);
+}
+template <class G>
+__global__ void forest_finish_kernel(ForestView F) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v < F.n_trees) ForestTree<G>::finish_round(F, v);
+}
+template <class G>
+__global__ void forest_expand_root_kernel(ForestView F) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v < F.n_trees) ForestTree<G>::expand_root(F, v);
+}
+__global__ void forest_fill_kernel(int64_t* dst, int64_t value, const int64_t* per_tree, int n) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v < n) dst[v] = per_tree ? per_tree[v] : value;
+}
+__global__ void forest_pack_kernel(ForestView F, const int64_t* base, unsigned long long* out) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v < F.n_trees) forest_pack_root(F, v, base, out);
+}
+__global__ void forest_install_kernel(ForestView F, const int64_t* base, const int64_t* summed) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v < F.n_trees) forest_install_root(F, v, base, summed);
+}
+
 template <class G, bool kFull>
 int launch_playouts(bsg_engine* e, const PlayoutArgs& a, cudaStream_t st) {
   static int blocks_per_sm = 0;
@@ -476,7 +524,8 @@ struct PlayoutOp {
   bsg_engine* e; PlayoutArgs a; cudaStream_t st;
   template <class G> int operator()() const {
     const bsg_playout_io& io = a.io;
-    bool full = io.max_steps > 0 || io.step_limit || io.r_table || io.actions || io.final_states || io.state_log;
+    bool full = io.max_steps > 0 || io.step_limit || io.r_table || io.actions || io.final_states || io.state_log ||
+                io.root_playout_base;
     return full ? launch_playouts<G, true>(e, a, st) : launch_playouts<G, false>(e, a, st);
   }
 };
@@ -877,6 +926,314 @@ int bsg_mcts_set_root_explore(bsg_mcts* m, int64_t n) {
 int bsg_mcts_set_next_playout(bsg_mcts* m, uint64_t next) {
   if (!m || !m->t) return BSG_ERR_BAD_ARG;
   m->t->next_playout = next;
+  return BSG_OK;
+}
+
+
+// ---- GPU-resident search forest -------------------------------------------------------------
+}  // extern "C"
+
+struct bsg_forest {
+  bsg_engine* e = nullptr;
+  bsg::ForestView F;
+  std::vector<void*> allocs;
+  void* d_root = nullptr;
+  int64_t* d_per_tree = nullptr;
+  uint64_t* d_totals = nullptr;
+  uint64_t eval_seed = 0;
+  int64_t rounds = 0, launches = 0, game_steps = 0;
+  std::string err;
+  ~bsg_forest() { for (void* p : allocs) cudaFree(p); }
+};
+
+namespace {
+struct ForestGeomOp {
+  int* depth;
+  template <class G> int operator()() const { *depth = G::kMaxLen + 2; return BSG_OK; }
+};
+template <class T> int forest_alloc(bsg_forest* f, T** p, size_t count) {
+  void* q = nullptr;
+  cudaError_t st = cudaMalloc(&q, count * sizeof(T) + 16);
+  if (st != cudaSuccess) { f->err = std::string("cudaMalloc: ") + cudaGetErrorString(st); return BSG_ERR_CUDA; }
+  cudaMemset(q, 0, count * sizeof(T) + 16);
+  f->allocs.push_back(q);
+  *p = (T*)q;
+  return BSG_OK;
+}
+int forest_grid(const bsg_forest* f) { return (f->F.n_trees + kForestThreads - 1) / kForestThreads; }
+
+// Test hook: the forest's per-tree code on host memory against the host tree, both with the
+// stand-in leaf values of MctsBase::fake_eval.  Returns 0 when every tree is identical node for
+// node, 1 + the first differing tree otherwise.
+struct ForestSelfTestOp {
+  int n_trees, sims, sims2, leaf_batch, n_rollouts, solve; uint64_t seed; const int64_t* hist; int n_hist;
+  template <class G> int operator()() const {
+    typedef typename G::State State;
+    State root;
+    G::init(root);
+    for (int i = 0; i < n_hist; ++i)
+      if (!apply_any<G>(root, (int)hist[i])) return BSG_ERR_ILLEGAL_ACTION;
+    std::vector<unsigned char> rootbuf((size_t)G::kStateBytes + 64, 0);
+    G::store(root, rootbuf.data(), 1, 0);
+    const size_t T = (size_t)n_trees, B = (size_t)leaf_batch;
+    const int cap = (sims + sims2 + 2) * (G::kNumActions < 64 ? G::kNumActions : 64) + 2 * G::kNumActions + 8;
+    const int depth = G::kMaxLen + 2;
+    std::vector<bsg::MctsNode> nodes(T * (size_t)cap);
+    std::vector<int32_t> n_nodes(T), paths(T * B * (size_t)depth), path_len(T * B), leaf_kind(T * B), n_pending(T), leaf_ret(T * B);
+    std::vector<uint64_t> shuffle_ctr(T, 0), next_playout(T), leaf_base(T * B);
+    std::vector<int64_t> sims_left(T);
+    std::vector<double> leaf_out0(T * B), logtab((size_t)(sims + sims2 + leaf_batch + 4));
+    std::vector<unsigned char> leaf_states(T * B * (size_t)G::kStateBytes + 64);
+    int32_t error = 0; uint32_t active = 0;
+    for (size_t i = 1; i < logtab.size(); ++i) logtab[i] = log((double)i);
+    bsg::ForestView F;
+    memset(&F, 0, sizeof(F));
+    F.nodes = nodes.data(); F.n_nodes = n_nodes.data(); F.shuffle_ctr = shuffle_ctr.data();
+    F.next_playout = next_playout.data(); F.sims_left = sims_left.data(); F.paths = paths.data();
+    F.path_len = path_len.data(); F.leaf_kind = leaf_kind.data(); F.leaf_out0 = leaf_out0.data();
+    F.n_pending = n_pending.data(); F.leaf_states = leaf_states.data(); F.leaf_base = leaf_base.data();
+    F.leaf_ret = leaf_ret.data(); F.logtab = logtab.data(); F.error = &error; F.active = &active;
+    F.root = rootbuf.data(); F.shuffle_seed0 = seed + 1000; F.n_trees = n_trees; F.cap = cap;
+    F.batch = leaf_batch; F.depth = depth; F.n_rollouts = n_rollouts; F.solve = solve;
+    F.logtab_n = (int32_t)logtab.size(); F.uct_c = 2.0;
+    const uint64_t first = 12345;
+    const typename G::Tables& tab = TablesOf<G>::get();
+    for (int v = 0; v < n_trees; ++v) { next_playout[(size_t)v] = first + ((uint64_t)v << 40); bsg::ForestTree<G>::reset(F, v); }
+    std::vector<bsg::MctsTree<G>> ref((size_t)n_trees);
+    for (int v = 0; v < n_trees; ++v) {
+      bsg::MctsTree<G>& t = ref[(size_t)v];
+      t.fake_eval = true; t.uct_c = 2.0; t.solve = solve; t.n_rollouts = n_rollouts; t.leaf_batch = leaf_batch;
+      t.eval_seed = seed; t.shuffle_seed = seed + 1000 + (uint64_t)v; t.next_playout = first + ((uint64_t)v << 40);
+    }
+    for (int phase = 0; phase < 2; ++phase) {
+      const int budget = phase == 0 ? sims : sims2;
+      if (phase == 1 && budget == 0) break;
+      for (int v = 0; v < n_trees; ++v) sims_left[(size_t)v] = budget + (phase == 0 ? v % 3 : 0);   // uneven shares
+      for (;;) {
+        active = 0;
+        for (int v = 0; v < n_trees; ++v) {
+          if (sims_left[(size_t)v] > 0) ++active;
+          bsg::ForestTree<G>::descend(F, v, tab);
+        }
+        if (error) return BSG_ERR_BAD_ARG;
+        if (!active) break;
+        for (size_t sl = 0; sl < T * B; ++sl)
+          leaf_ret[sl] = leaf_base[sl] == bsg::kSkipRoot ? 0 : bsg::fake_leaf_value(seed, leaf_base[sl], n_rollouts);
+        for (int v = 0; v < n_trees; ++v) bsg::ForestTree<G>::finish_round(F, v);
+      }
+      for (int v = 0; v < n_trees; ++v) bsg::ForestTree<G>::expand_root(F, v);
+      for (int v = 0; v < n_trees; ++v) {
+        bsg::MctsTree<G>& t = ref[(size_t)v];
+        int rc = t.search(rootbuf.data(), budget + (phase == 0 ? v % 3 : 0), phase);
+        if (rc != BSG_OK) return rc;
+        t.expand_root(rootbuf.data());
+        if ((int)t.nodes.size() != n_nodes[(size_t)v]) return 1 + v;
+        if (t.next_playout != next_playout[(size_t)v] || t.shuffle_ctr != shuffle_ctr[(size_t)v]) return 1 + v;
+        for (size_t i = 0; i < t.nodes.size(); ++i) {
+          const bsg::MctsNode& a = t.nodes[i];
+          const bsg::MctsNode& b = nodes[(size_t)v * (size_t)cap + i];
+          if (a.action != b.action || a.player != b.player || a.explore != b.explore || a.reward != b.reward ||
+              a.virt != b.virt || a.has_outcome != b.has_outcome || a.out0 != b.out0 ||
+              a.first_child != b.first_child || a.n_children != b.n_children)
+            return 1 + v;
+        }
+      }
+    }
+    return 0;
+  }
+};
+
+struct ForestSearchOp {
+  bsg_forest* f; int resume;
+  template <class G> int operator()() const {
+    bsg_engine* e = f->e;
+    cudaStream_t st = e->own_stream;
+    const bsg::ForestView& F = f->F;
+    const int grid = forest_grid(f);
+    if (!resume) forest_reset_kernel<G><<<grid, kForestThreads, 0, st>>>(F);
+    BSG_CUDA(e, cudaMemsetAsync(f->d_totals, 0, 4 * sizeof(uint64_t), st));
+    const int64_t slots = (int64_t)F.n_trees * F.batch;
+    for (;;) {
+      BSG_CUDA(e, cudaMemsetAsync(F.active, 0, sizeof(uint32_t), st));
+      BSG_CUDA(e, cudaMemsetAsync(F.leaf_ret, 0, (size_t)slots * sizeof(int32_t), st));
+      forest_descend_kernel<G><<<grid, kForestThreads, 0, st>>>(F, (const typename G::Tables*)e->tables_dev);
+      uint32_t hdr[2] = {0, 0};   // {active trees, error}
+      BSG_CUDA(e, cudaMemcpyAsync(&hdr[0], F.active, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+      BSG_CUDA(e, cudaMemcpyAsync(&hdr[1], F.error, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+      BSG_CUDA(e, cudaStreamSynchronize(st));
+      if (hdr[1]) {
+        f->err = hdr[1] == 1 ? "forest: node pool exhausted (raise node_capacity)"
+               : (hdr[1] == 2 ? "forest: log table exhausted (raise max_visits)" : "forest: path deeper than the game allows");
+        return BSG_ERR_BAD_ARG;
+      }
+      if (hdr[0] == 0) break;
+      PlayoutArgs a;
+      memset(&a, 0, sizeof(a));
+      a.roots = F.leaf_states; a.n_roots = slots; a.root0 = 0;
+      a.n_playouts = (uint32_t)(slots * F.n_rollouts); a.rollouts = (uint32_t)F.n_rollouts;
+      a.first_playout = 0;
+      bsg::philox_schedule(f->eval_seed, a.keys);
+      a.io.root_sum_ret0 = F.leaf_ret;
+      a.io.totals = f->d_totals;
+      a.io.root_playout_base = F.leaf_base;
+      int rc = launch_playouts<G, true>(e, a, st);
+      if (rc != BSG_OK) return rc;
+      forest_finish_kernel<G><<<grid, kForestThreads, 0, st>>>(F);
+      f->rounds += 1;
+      f->launches += 3;
+    }
+    forest_expand_root_kernel<G><<<grid, kForestThreads, 0, st>>>(F);
+    uint64_t tot[4];
+    BSG_CUDA(e, cudaMemcpyAsync(tot, f->d_totals, sizeof(tot), cudaMemcpyDeviceToHost, st));
+    BSG_CUDA(e, cudaStreamSynchronize(st));
+    BSG_CUDA(e, cudaGetLastError());
+    f->game_steps += (int64_t)tot[1];
+    if (tot[3] != 0) { f->err = "forest: non-terminal state without legal actions"; return BSG_ERR_STUCK_LANE; }
+    return BSG_OK;
+  }
+};
+}  // namespace
+
+extern "C" {
+
+int bsg_forest_create(bsg_engine* e, int32_t n_trees, int32_t node_capacity, int64_t max_visits,
+                      double uct_c, int solve, int n_rollouts, int leaf_batch, uint64_t eval_seed,
+                      uint64_t shuffle_seed0, uint64_t first_playout, bsg_forest** out) {
+  if (!e || !out || n_trees < 1 || node_capacity < 2 || max_visits < 4 || n_rollouts < 1 || leaf_batch < 1)
+    return BSG_ERR_BAD_ARG;
+  *out = nullptr;
+  if ((int64_t)n_trees * leaf_batch * n_rollouts >= ((int64_t)1 << 32) - (1 << 24))
+    return fail(e, BSG_ERR_BAD_ARG, "forest: trees * leaf_batch * rollouts exceeds one launch");
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  int depth = 0;
+  int rc = dispatch_device_game(e->game, ForestGeomOp{&depth});
+  if (rc != BSG_OK) return rc;
+  bsg_forest* f = new (std::nothrow) bsg_forest();
+  if (!f) return BSG_ERR_BAD_ARG;
+  f->e = e;
+  f->eval_seed = eval_seed;
+  bsg::ForestView& F = f->F;
+  memset(&F, 0, sizeof(F));
+  F.n_trees = n_trees; F.cap = node_capacity; F.batch = leaf_batch; F.depth = depth;
+  F.n_rollouts = n_rollouts; F.solve = solve; F.uct_c = uct_c; F.shuffle_seed0 = shuffle_seed0;
+  F.logtab_n = (int32_t)(max_visits + leaf_batch + 2);
+  const size_t T = (size_t)n_trees, B = (size_t)leaf_batch;
+  double* logtab = nullptr;
+  rc = forest_alloc(f, &F.nodes, T * (size_t)node_capacity);
+  if (rc == BSG_OK) rc = forest_alloc(f, &F.n_nodes, T);
+  if (rc == BSG_OK) rc = forest_alloc(f, &F.shuffle_ctr, T);
+  if (rc == BSG_OK) rc = forest_alloc(f, &F.next_playout, T);
+  if (rc == BSG_OK) rc = forest_alloc(f, &F.sims_left, T);
+  if (rc == BSG_OK) rc = forest_alloc(f, &F.paths, T * B * (size_t)depth);
+  if (rc == BSG_OK) rc = forest_alloc(f, &F.path_len, T * B);
+  if (rc == BSG_OK) rc = forest_alloc(f, &F.leaf_kind, T * B);
+  if (rc == BSG_OK) rc = forest_alloc(f, &F.leaf_out0, T * B);
+  if (rc == BSG_OK) rc = forest_alloc(f, &F.n_pending, T);
+  unsigned char* leaf_states = nullptr;
+  if (rc == BSG_OK) rc = forest_alloc(f, &leaf_states, T * B * (size_t)bsg_state_bytes(e->game));
+  if (rc == BSG_OK) rc = forest_alloc(f, &F.leaf_base, T * B);
+  if (rc == BSG_OK) rc = forest_alloc(f, &F.leaf_ret, T * B);
+  if (rc == BSG_OK) rc = forest_alloc(f, &logtab, (size_t)F.logtab_n);
+  if (rc == BSG_OK) rc = forest_alloc(f, &F.error, 4);
+  if (rc == BSG_OK) rc = forest_alloc(f, &F.active, 4);
+  unsigned char* d_root = nullptr;
+  if (rc == BSG_OK) rc = forest_alloc(f, &d_root, (size_t)bsg_state_bytes(e->game) + 64);
+  if (rc == BSG_OK) rc = forest_alloc(f, &f->d_per_tree, T);
+  if (rc == BSG_OK) rc = forest_alloc(f, &f->d_totals, 4);
+  if (rc != BSG_OK) { e->err = f->err; delete f; return rc; }
+  F.leaf_states = leaf_states;
+  F.root = d_root;
+  f->d_root = d_root;
+  {  // log(n) from the host's libm — the table the host tree's log() calls amount to
+    std::vector<double> h((size_t)F.logtab_n);
+    h[0] = 0.0;
+    for (int32_t i = 1; i < F.logtab_n; ++i) h[(size_t)i] = log((double)i);
+    cudaMemcpy(logtab, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice);
+    F.logtab = logtab;
+    std::vector<uint64_t> np(T);
+    for (size_t v = 0; v < T; ++v) np[v] = first_playout + ((uint64_t)v << 40);
+    cudaMemcpy(F.next_playout, np.data(), T * sizeof(uint64_t), cudaMemcpyHostToDevice);
+  }
+  BSG_CUDA(e, cudaGetLastError());
+  *out = f;
+  return BSG_OK;
+}
+void bsg_forest_destroy(bsg_forest* f) {
+  if (!f) return;
+  if (f->e && f->e->device >= 0) cudaSetDevice(f->e->device);
+  delete f;
+}
+const char* bsg_forest_last_error(bsg_forest* f) {
+  return f ? (f->err.empty() ? bsg_last_error(f->e) : f->err.c_str()) : "null forest";
+}
+int bsg_forest_search(bsg_forest* f, const void* root_host, int64_t simulations_per_tree,
+                      const int64_t* per_tree_host, int resume) {
+  if (!f || !root_host || simulations_per_tree < 0) return BSG_ERR_BAD_ARG;
+  bsg_engine* e = f->e;
+  f->err.clear();
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  cudaStream_t st = e->own_stream;
+  BSG_CUDA(e, cudaMemcpyAsync(f->d_root, root_host, (size_t)bsg_state_bytes(e->game), cudaMemcpyHostToDevice, st));
+  if (per_tree_host)
+    BSG_CUDA(e, cudaMemcpyAsync(f->d_per_tree, per_tree_host, (size_t)f->F.n_trees * sizeof(int64_t),
+                                cudaMemcpyHostToDevice, st));
+  forest_fill_kernel<<<forest_grid(f), kForestThreads, 0, st>>>(
+      f->F.sims_left, simulations_per_tree, per_tree_host ? f->d_per_tree : nullptr, f->F.n_trees);
+  return dispatch_device_game(e->game, ForestSearchOp{f, resume});
+}
+int bsg_forest_pack_root(bsg_forest* f, const int64_t* base_dev, int64_t* out_dev) {
+  if (!f || !base_dev || !out_dev) return BSG_ERR_BAD_ARG;
+  bsg_engine* e = f->e;
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  forest_pack_kernel<<<forest_grid(f), kForestThreads, 0, e->own_stream>>>(
+      f->F, base_dev, (unsigned long long*)out_dev);
+  BSG_CUDA(e, cudaStreamSynchronize(e->own_stream));
+  return BSG_OK;
+}
+int bsg_forest_install_root(bsg_forest* f, const int64_t* base_dev, const int64_t* summed_dev) {
+  if (!f || !base_dev || !summed_dev) return BSG_ERR_BAD_ARG;
+  bsg_engine* e = f->e;
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  forest_install_kernel<<<forest_grid(f), kForestThreads, 0, e->own_stream>>>(f->F, base_dev, summed_dev);
+  BSG_CUDA(e, cudaStreamSynchronize(e->own_stream));
+  return BSG_OK;
+}
+int bsg_forest_tree_root(bsg_forest* f, int32_t tree, int capacity, int64_t* actions, int64_t* visits,
+                         double* reward, int32_t* outcome, double info[4]) {
+  if (!f || tree < 0 || tree >= f->F.n_trees) return BSG_ERR_BAD_ARG;
+  bsg_engine* e = f->e;
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  bsg::MctsNode root;
+  const bsg::MctsNode* nodes = f->F.nodes + (size_t)tree * f->F.cap;
+  BSG_CUDA(e, cudaMemcpy(&root, nodes, sizeof(root), cudaMemcpyDeviceToHost));
+  std::vector<bsg::MctsNode> ch((size_t)(root.n_children > 0 ? root.n_children : 0));
+  if (!ch.empty())
+    BSG_CUDA(e, cudaMemcpy(ch.data(), nodes + root.first_child, ch.size() * sizeof(bsg::MctsNode), cudaMemcpyDeviceToHost));
+  for (int i = 0; i < root.n_children && i < capacity; ++i) {
+    const bsg::MctsNode& c = ch[(size_t)i];
+    if (actions) actions[i] = c.action;
+    if (visits) visits[i] = c.explore;
+    if (reward) reward[i] = c.reward;
+    if (outcome) outcome[i] = c.has_outcome ? (int32_t)(c.player == 0 ? c.out0 : -c.out0) : 2;
+  }
+  if (info) {
+    int32_t n_nodes = 0;
+    BSG_CUDA(e, cudaMemcpy(&n_nodes, f->F.n_nodes + tree, sizeof(n_nodes), cudaMemcpyDeviceToHost));
+    info[0] = (double)root.explore; info[1] = root.has_outcome; info[2] = root.out0; info[3] = (double)n_nodes;
+  }
+  return root.n_children;
+}
+int bsg_forest_selftest(int game, int n_trees, int sims, int sims_resume, int leaf_batch, int n_rollouts,
+                        int solve, uint64_t seed, const int64_t* history, int n_history) {
+  if (n_trees < 1 || sims < 0 || sims_resume < 0 || leaf_batch < 1 || n_rollouts < 1 || (n_history > 0 && !history))
+    return BSG_ERR_BAD_ARG;
+  return dispatch_device_game(game, ForestSelfTestOp{n_trees, sims, sims_resume, leaf_batch, n_rollouts, solve,
+                                                     seed, history, n_history});
+}
+int bsg_forest_info(bsg_forest* f, double info[4]) {
+  if (!f || !info) return BSG_ERR_BAD_ARG;
+  info[0] = (double)f->game_steps; info[1] = (double)f->launches; info[2] = (double)f->rounds;
+  info[3] = (double)f->F.n_trees;
   return BSG_OK;
 }
 

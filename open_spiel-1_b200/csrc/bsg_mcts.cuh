@@ -52,8 +52,20 @@ struct MctsBase {
   uint64_t eval_seed = 0, shuffle_seed = 0, shuffle_ctr = 0, next_playout = 0;
   int64_t total_game_steps = 0, kernel_launches = 0;
   int root_player = 0;
+  // Test hook (bsg_forest_selftest): leaf values from a hash of the playout-id base instead of
+  // rollouts, so tree logic can be compared on a machine without a GPU.
+  bool fake_eval = false;
   std::string err;
 };
+
+// The stand-in leaf value of the test hook: an integer in [-n_rollouts, n_rollouts].
+inline int32_t fake_leaf_value(uint64_t seed, uint64_t playout_base, int n_rollouts) {
+  PhiloxKeys ks;
+  philox_schedule(seed ^ 0x9E3779B97F4A7C15ull, ks);
+  u32 out[4];
+  philox4x32_10((u32)playout_base, (u32)(playout_base >> 32), 7u, 0u, ks, out);
+  return (int32_t)(out[0] % (uint32_t)(2 * n_rollouts + 1)) - n_rollouts;
+}
 
 template <class G>
 struct MctsTree : MctsBase {
@@ -162,6 +174,12 @@ struct MctsTree : MctsBase {
     for (size_t i = 0; i < leaf_states.size(); ++i)
       if (!leaf_terminal[i]) G::store(leaf_states[i], packed.data(), n_leaves, li++);
     root_ret.assign(n_leaves, 0);
+    if (fake_eval) {
+      for (int i = 0; i < n_leaves; ++i)
+        root_ret[i] = fake_leaf_value(eval_seed, next_playout + (uint64_t)i * (uint64_t)n_rollouts, n_rollouts);
+      next_playout += (uint64_t)n_leaves * (uint64_t)n_rollouts;
+      return BSG_OK;
+    }
     int64_t totals[4];
     int rc = bsg_playouts_host(engine, packed.data(), n_leaves, n_rollouts, eval_seed, next_playout,
                                totals, root_ret.data(), nullptr);

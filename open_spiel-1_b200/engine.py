@@ -143,7 +143,7 @@ class Engine:
                length=None, terminal=None, actions=None, root_sum_ret0=None,
                root_sum_steps=None, totals=None, max_steps=0, step_limit=None, r_table=None,
                final_states=None, final_before_terminal=False, state_log=None,
-               state_log_off=None, stream=None):
+               state_log_off=None, root_playout_base=None, stream=None):
     """Launches n_roots * rollouts random playouts (bsg_playouts).  All tensors are device
     tensors owned by the caller; see include/bsg.h for their meaning.  Asynchronous."""
     io = C.PlayoutIO()
@@ -164,6 +164,7 @@ class Engine:
     io.state_log = self._p(state_log)
     io.state_log_cap = int(state_log.numel() // self.state_bytes) if state_log is not None else 0
     io.state_log_off = self._p(state_log_off)
+    io.root_playout_base = self._p(root_playout_base)
     C.check(C.lib.bsg_playouts(self._h, self._p(roots), int(n_roots), int(rollouts),
                                int(seed) & (2**64 - 1), int(first_playout), ctypes.byref(io),
                                self._stream_ptr(stream)), self._h)
