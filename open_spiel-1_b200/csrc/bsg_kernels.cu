@@ -48,7 +48,7 @@ inline uint32_t out_flags_of(const bsg_playout_io& io) {
          ((io.root_sum_ret0 || io.root_sum_steps) ? kOutRootSums : 0u);
 }
 
-template <class G, bool kFull>
+template <class G, bool kFull, bool kBase>
 __global__ void __launch_bounds__(kThreads)
 playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab) {
   __shared__ __align__(16) typename G::Tables tab;
@@ -125,7 +125,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         u32 root = a.rollouts == 1 ? lid : lid / a.rollouts;
         G::load(s, a.roots, a.n_roots, a.root0 + root);
         bool skip = false;
-        if (kFull && a.io.root_playout_base) {
+        if (kBase) {
           const unsigned long long rb = a.io.root_playout_base[a.root0 + root];
           skip = rb == 0xFFFFFFFFFFFFFFFFull;
           pid0 = rb - (unsigned long long)root * a.rollouts;
@@ -138,12 +138,12 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
           if (a.io.step_limit) limit = min(limit, (u32)a.io.step_limit[lid]);
           prev = s;
         }
-        const bool term = G::terminal(s) || (kFull && skip);
+        const bool term = G::terminal(s) || (kBase && skip);
         live = (!term && (!kFull || limit > 0)) ? 1u : 0u;
         fin_term = (kFull && !term) ? 0u : 1u;   // a lean playout always runs to a terminal state
         fin_win = G::won(s) ? 1u : 0u;
         if constexpr (G::kMoverCanLose) fin_lose = G::lost(s) ? 1u : 0u;
-        if (kFull && skip) { fin_win = 0; fin_lose = 0; }   // a skipped slot holds no state
+        if (kBase && skip) { fin_win = 0; fin_lose = 0; }   // a skipped slot holds no state
         if constexpr (G::kCanStick) {
           // non-terminal root without a legal action: only a root can be (see the game's note)
           if (!term && !G::has_move(s)) { live = 0; fin_term = 0; fin_win = 0; my_stuck += 1; }
@@ -158,7 +158,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
       continue;
     }
 
-    const unsigned long long pid = (kFull ? pid0 : a.first_playout) + lid;
+    const unsigned long long pid = (kBase ? pid0 : a.first_playout) + lid;
     u32 rr[4];
     if constexpr (!G::kAsync) {
       philox4x32_10((u32)pid, (u32)(pid >> 32), t >> 2, 0u, a.keys, rr);
@@ -495,15 +495,15 @@ __global__ void forest_install_kernel(ForestView F, const int64_t* base, const i
   if (v < F.n_trees) forest_install_root(F, v, base, summed);
 }
 
-template <class G, bool kFull>
+template <class G, bool kFull, bool kBase = false>
 int launch_playouts(bsg_engine* e, const PlayoutArgs& a, cudaStream_t st) {
   static int blocks_per_sm = 0;
   if (blocks_per_sm == 0) {
     int b = 0;
     // all of the L1/shared array as shared memory: the tables of every resident CTA must fit
-    BSG_CUDA(e, cudaFuncSetAttribute(playout_kernel<G, kFull>, cudaFuncAttributePreferredSharedMemoryCarveout,
+    BSG_CUDA(e, cudaFuncSetAttribute(playout_kernel<G, kFull, kBase>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                      cudaSharedmemCarveoutMaxShared));
-    BSG_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, playout_kernel<G, kFull>, kThreads, 0));
+    BSG_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, playout_kernel<G, kFull, kBase>, kThreads, 0));
     blocks_per_sm = b > 0 ? b : 1;
   }
   int64_t max_grid = (int64_t)e->sm_count * blocks_per_sm;
@@ -515,7 +515,7 @@ int launch_playouts(bsg_engine* e, const PlayoutArgs& a, cudaStream_t st) {
   // work counter of this launch: next slot of the engine's ring, zeroed in stream order
   b.work_counter = e->d_work + (e->work_slot++ % kWorkSlots);
   BSG_CUDA(e, cudaMemsetAsync(b.work_counter, 0, sizeof(uint32_t), st));
-  playout_kernel<G, kFull><<<grid, kThreads, 0, st>>>(b, (const typename G::Tables*)e->tables_dev);
+  playout_kernel<G, kFull, kBase><<<grid, kThreads, 0, st>>>(b, (const typename G::Tables*)e->tables_dev);
   BSG_CUDA(e, cudaGetLastError());
   return BSG_OK;
 }
@@ -524,8 +524,9 @@ struct PlayoutOp {
   bsg_engine* e; PlayoutArgs a; cudaStream_t st;
   template <class G> int operator()() const {
     const bsg_playout_io& io = a.io;
-    bool full = io.max_steps > 0 || io.step_limit || io.r_table || io.actions || io.final_states || io.state_log ||
-                io.root_playout_base;
+    bool full = io.max_steps > 0 || io.step_limit || io.r_table || io.actions || io.final_states || io.state_log;
+    if (io.root_playout_base)
+      return full ? launch_playouts<G, true, true>(e, a, st) : launch_playouts<G, false, true>(e, a, st);
     return full ? launch_playouts<G, true>(e, a, st) : launch_playouts<G, false>(e, a, st);
   }
 };
@@ -1076,7 +1077,7 @@ struct ForestSearchOp {
       a.io.root_sum_ret0 = F.leaf_ret;
       a.io.totals = f->d_totals;
       a.io.root_playout_base = F.leaf_base;
-      int rc = launch_playouts<G, true>(e, a, st);
+      int rc = launch_playouts<G, false, true>(e, a, st);
       if (rc != BSG_OK) return rc;
       forest_finish_kernel<G><<<grid, kForestThreads, 0, st>>>(F);
       f->rounds += 1;

@@ -1,6 +1,6 @@
 #!/bin/bash
 # cfg5 with the GPU-resident forest: sweep trees / sims per tree / leaf batch
-for cfg in "4096 1024 32 256" "8192 512 32 256" "16384 256 32 256" "8192 512 64 512" "16384 256 64 256" "32768 128 32 128"; do
+for cfg in "4096 1024 32 256" "16384 256 32 256" "32768 128 32 128" "65536 64 32 64"; do
   set -- $cfg
   python bench_mcts.py --cfg 5 --forest 1 --trees $1 --sims5 $2 --leaf-batch $3 --sims-per-step $4 2>&1 | tail -1 | tee -a gpurun_out/mcts_forest.jsonl | python -c "
 import sys,json
