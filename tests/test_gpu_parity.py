@@ -337,3 +337,43 @@ def test_trajectory_records_match_oracle(game, torch):
     assert np.array_equal(obs[i], dd["obs"]), (game, p, t)
     assert np.nonzero(mask[i])[0].tolist() == dd["legal"], (game, p, t)
   eng.close()
+
+
+def test_device_replay_buffer_takes_trajectories(torch):
+  """trajectory records go straight into a device replay buffer with the
+  semantics of the reference's Buffer (alpha_zero.py:83-104: keeps the newest, counts what
+  passed through, samples without replacement) and TrainInput fields (model.py:80-91)."""
+  import open_spiel_1_b200 as bsg
+  oracle = Oracle()
+  game = "connect_four"
+  eng = _engine(game)
+  roots = eng.to_device(bsg.pack_histories(game, [[3, 3], [0, 1, 2]]))
+  rec = eng.trajectories(roots, 2, rollouts=64, seed=5)
+  total = rec["total"]
+  buf = bsg.DeviceReplayBuffer(total + 100, eng.obs_size, eng.num_actions, eng.torch_device)
+  buf.extend_from_trajectories(rec)
+  assert len(buf) == total == buf.total_seen
+  got = buf.newest(total)
+  assert got.observation.is_cuda and got.observation.shape == (total, eng.obs_size)
+  assert torch.equal(got.observation, rec["obs"].reshape(total, -1))
+  assert torch.equal(got.legals_mask, rec["mask"].to(torch.bool))
+  # policy = uniform over the legal actions; value = the playout's return for player 0
+  n_legal = got.legals_mask.sum(dim=1, keepdim=True).to(torch.float32)
+  assert torch.equal(got.policy, got.legals_mask.to(torch.float32) / n_legal)
+  o_len, o_ret, _, _ = oracle.replay_batch(game, [[3, 3], [0, 1, 2]], rollouts=64, seed=5)
+  want_value = np.repeat(o_ret.astype(np.float32), o_len)
+  assert np.array_equal(got.value.cpu().numpy().ravel(), want_value)
+  batch = buf.sample(256, generator=torch.Generator(device=eng.torch_device).manual_seed(1))
+  assert batch.value.shape == (256, 1) and batch.policy.shape == (256, eng.num_actions)
+  assert torch.allclose(batch.policy.sum(dim=1), torch.ones(256, device=eng.torch_device))
+  # the oldest fall out, exactly like data[:-max_size] = [] in the reference
+  small = bsg.DeviceReplayBuffer(100, eng.obs_size, eng.num_actions, eng.torch_device)
+  small.extend_from_trajectories(rec)
+  small.extend(got.observation[:30], got.legals_mask[:30], got.policy[:30], got.value[:30])
+  assert len(small) == 100 and small.total_seen == total + 30
+  tail = small.newest(100)
+  want_obs = torch.cat([got.observation[total - 70:], got.observation[:30]])
+  assert torch.equal(tail.observation, want_obs)
+  with pytest.raises(ValueError):
+    small.sample(101)
+  eng.close()
