@@ -5,6 +5,7 @@
  *       (open_spiel/games/tic_tac_toe.h:44-48, connect_four.h:54-58)
  *   breakthrough: 0 empty, 1 black (player 0), 2 white (player 1)  (breakthrough.h:45-49)
  *   hex: the signed 9-value enum of hex.h:51-61 (-4..4)
+ *   othello: 0 empty, 1 black (player 0), 2 white (player 1)  (othello.h:40-44)
  *   pentago: 0 empty, 1 player 0, 2 player 1 (pentago.h:44-49 orders kPlayer1, kPlayer2, kPlayerNone;
  *       only the observation plane order depends on it and that is player-relative)
  */
@@ -33,6 +34,7 @@ int orc_num_distinct_actions(int game, int n) {
     case ORC_C4: return 7;
     case ORC_BT: return 8 * 8 * 6 * 2;
     case ORC_PENTAGO: return 36 * 8; /* pentago.h:40-42 */
+    case ORC_OTHELLO: return 65;     /* othello.h:128: 64 cells + pass */
     default: return n * n;
   }
 }
@@ -42,6 +44,7 @@ int orc_max_game_length(int game, int n) {
     case ORC_C4: return 42;
     case ORC_BT: return 2 * (2 * 8 - 3) * 8 + 1; /* breakthrough.h:116-118 */
     case ORC_PENTAGO: return 36; /* pentago.h:109-113 */
+    case ORC_OTHELLO: return 64; /* othello.h:142 */
     default: return n * n;
   }
 }
@@ -51,6 +54,7 @@ int orc_obs_size(int game, int n) {
     case ORC_C4: return 126;
     case ORC_BT: return 192;
     case ORC_PENTAGO: return 3 * 36; /* pentago.h:106-108 */
+    case ORC_OTHELLO: return 3 * 64; /* othello.h:139-141 */
     default: return 9 * n * n;
   }
 }
@@ -307,12 +311,88 @@ static int pg_apply(orc_state* s, int a) {
   return 0;
 }
 
+/* ---------------------------------------------------------------- othello (8x8) */
+#define OT_N 8
+#define OT_PASS 64
+/* othello.h:46-57 + othello.cc:97-120: the eight directions as (drow, dcol). */
+static const int kOtDir[8][2] = {{-1, 0}, {1, 0}, {0, -1}, {0, 1}, {-1, -1}, {-1, 1}, {1, -1}, {1, 1}};
+static int ot_on(int r, int c) { return r >= 0 && r < OT_N && c >= 0 && c < OT_N; }
+/* othello.cc:126-146: opponent discs from `move` in direction d that end on a disc of `player`. */
+static int ot_count_steps(const orc_state* s, int player, int move, int d) {
+  int r = move / OT_N + kOtDir[d][0], c = move % OT_N + kOtDir[d][1], count = 0;
+  int mine = player + 1;
+  while (ot_on(r, c)) {
+    int v = s->cells[r * OT_N + c];
+    if (v == mine) return count;
+    if (v == 0) return 0;
+    ++count;
+    r += kOtDir[d][0];
+    c += kOtDir[d][1];
+  }
+  return 0;
+}
+/* othello.cc:148-158, 196-198 */
+static int ot_valid(const orc_state* s, int player, int move) {
+  if (s->cells[move] != 0) return 0;
+  for (int d = 0; d < 8; ++d)
+    if (ot_count_steps(s, player, move, d) != 0) return 1;
+  return 0;
+}
+static int ot_regular(const orc_state* s, int player, int* out) {   /* othello.cc:231-239 */
+  int n = 0;
+  for (int cell = 0; cell < OT_N * OT_N; ++cell)
+    if (ot_valid(s, player, cell)) { if (out) out[n] = cell; ++n; }
+  return n;
+}
+/* othello.cc:241-246: a player without a regular move must pass. */
+static int ot_legal(const orc_state* s, int* out) {
+  int n = ot_regular(s, s->cur_player, out);
+  if (n == 0) out[n++] = OT_PASS;
+  return n;
+}
+/* othello.cc:200-229: pass flips the turn; a placement captures in every direction, then the
+ * game ends when neither side has a regular move (disc majority wins, equal = tie). */
+static int ot_apply(orc_state* s, int a) {
+  if (a == OT_PASS) {
+    if (ot_regular(s, s->cur_player, 0) != 0) return -1;   /* the oracle also rejects illegal passes */
+    s->cur_player = 1 - s->cur_player;
+    s->num_moves += 1;
+    return 0;
+  }
+  if (a < 0 || a >= OT_N * OT_N || !ot_valid(s, s->cur_player, a)) return -1;
+  int mine = s->cur_player + 1;
+  int steps[8];
+  for (int d = 0; d < 8; ++d) steps[d] = ot_count_steps(s, s->cur_player, a, d);
+  s->cells[a] = mine;
+  for (int d = 0; d < 8; ++d) {
+    int r = a / OT_N, c = a % OT_N;
+    for (int k = 0; k < steps[d]; ++k) {
+      r += kOtDir[d][0];
+      c += kOtDir[d][1];
+      s->cells[r * OT_N + c] = mine;
+    }
+  }
+  s->num_moves += 1;
+  if (ot_regular(s, 0, 0) == 0 && ot_regular(s, 1, 0) == 0) {
+    int c0 = 0, c1 = 0;
+    for (int i = 0; i < OT_N * OT_N; ++i) { c0 += s->cells[i] == 1; c1 += s->cells[i] == 2; }
+    s->outcome = c0 > c1 ? 0 : (c0 < c1 ? 1 : 2);
+  }
+  s->cur_player = 1 - s->cur_player;
+  return 0;
+}
+
 /* ---------------------------------------------------------------- generic API */
 void orc_init(orc_state* s, int game, int board_size) {
   memset(s, 0, sizeof(*s));
   s->game = game;
   s->outcome = -1;
   s->board_size = game == ORC_HEX ? (board_size > 0 ? board_size : 11) : 0;
+  if (game == ORC_OTHELLO) {
+    /* othello.cc:263-269: white on d4/e5, black on e4/d5; black (player 0) moves first */
+    s->cells[3 * OT_N + 3] = 2; s->cells[3 * OT_N + 4] = 1;
+    s->cells[4 * OT_N + 3] = 1; s->cells[4 * OT_N + 4] = 2;
+  }
   if (game == ORC_BT) {
     /* breakthrough.cc:119-142: black on rows 0-1, white on rows 6-7, black (player 0) first. */
     for (int r = 0; r < BT_N; ++r)
@@ -328,6 +408,7 @@ int orc_is_terminal(const orc_state* s) {
     case ORC_C4: return s->outcome != -1;                           /* connect_four.cc:176-178 */
     case ORC_BT: return s->outcome >= 0 || s->pieces[0] == 0 || s->pieces[1] == 0; /* :306-308 */
     case ORC_PENTAGO: return s->outcome != -1;                      /* pentago.h:62 */
+    case ORC_OTHELLO: return s->outcome != -1;                      /* othello.cc:284-286 */
     default: return s->outcome != -1;                               /* hex.cc:248 */
   }
 }
@@ -350,6 +431,8 @@ int orc_legal_actions(const orc_state* s, int* out) {
       return bt_legal(s, out);
     case ORC_PENTAGO:
       return pg_legal(s, out);
+    case ORC_OTHELLO:
+      return ot_legal(s, out);
     default: /* hex.cc:186-196 */
       for (int c = 0; c < s->board_size * s->board_size; ++c)
         if (s->cells[c] == HX_EMPTY) out[n++] = c;
@@ -364,6 +447,7 @@ int orc_apply(orc_state* s, int a) {
     case ORC_C4: return c4_apply(s, a);
     case ORC_BT: return bt_apply(s, a);
     case ORC_PENTAGO: return pg_apply(s, a);
+    case ORC_OTHELLO: return ot_apply(s, a);
     default: return hex_apply(s, a);
   }
 }
@@ -401,6 +485,14 @@ void orc_observation(const orc_state* s, int player, uint8_t* out) {
       for (int c = 0; c < 64; ++c) {
         int v = s->cells[c];
         plane = v == BT_B ? 0 : (v == BT_W ? 1 : 2);
+        out[plane * 64 + c] = 1;
+      }
+      return;
+    case ORC_OTHELLO: /* othello.cc:310-329: plane 0 empty, 1 the observer's discs, 2 the opponent's */
+      memset(out, 0, 192);
+      for (int c = 0; c < 64; ++c) {
+        int v = s->cells[c];
+        plane = v == 0 ? 0 : ((v - 1) == player ? 1 : 2);
         out[plane * 64 + c] = 1;
       }
       return;

@@ -18,7 +18,7 @@
 extern "C" {
 #endif
 
-enum { ORC_TTT = 0, ORC_C4 = 1, ORC_BT = 2, ORC_HEX = 3, ORC_PENTAGO = 5 };
+enum { ORC_TTT = 0, ORC_C4 = 1, ORC_BT = 2, ORC_HEX = 3, ORC_PENTAGO = 5, ORC_OTHELLO = 6 };
 #define ORC_MAX_LEGAL 320 /* pentago: 36 cells x 8 rotations = 288 */
 #define ORC_MAX_CELLS 121
 #define ORC_TERMINAL_PLAYER (-4) /* kTerminalPlayerId, open_spiel/spiel.h:48 */

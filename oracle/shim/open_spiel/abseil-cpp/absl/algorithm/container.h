@@ -10,5 +10,11 @@ template <typename C, typename P>
 auto c_find_if(C& c, P p) -> decltype(c.begin()) { return std::find_if(c.begin(), c.end(), p); }
 template <typename C, typename F>
 void c_for_each(C&& c, F f) { std::for_each(c.begin(), c.end(), f); }
+template <typename C, typename T>
+auto c_count(const C& c, const T& v) -> decltype(std::count(c.begin(), c.end(), v)) {
+  return std::count(c.begin(), c.end(), v);
+}
+template <typename C, typename T>
+void c_fill(C& c, const T& v) { std::fill(c.begin(), c.end(), v); }
 }  // namespace absl
 #endif

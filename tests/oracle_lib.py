@@ -12,8 +12,8 @@ import numpy as np
 
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(REPO, "oracle")
-GAME_IDS = {"tic_tac_toe": 0, "connect_four": 1, "breakthrough": 2, "hex": 3, "pentago": 5}
-OBS_SIZE = {"tic_tac_toe": 27, "connect_four": 126, "breakthrough": 192, "hex": 1089, "pentago": 108}
+GAME_IDS = {"tic_tac_toe": 0, "connect_four": 1, "breakthrough": 2, "hex": 3, "pentago": 5, "othello": 6}
+OBS_SIZE = {"tic_tac_toe": 27, "connect_four": 126, "breakthrough": 192, "hex": 1089, "pentago": 108, "othello": 192}
 vp = ctypes.c_void_p
 
 
