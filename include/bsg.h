@@ -33,7 +33,7 @@ extern "C" {
 
 /* Game ids.  Strings accepted by bsg_game_id are the reference's game strings
  * (open_spiel/spiel.h:792-803): "tic_tac_toe", "connect_four", "breakthrough",
- * "breakthrough(rows=8,columns=8)", "hex", "hex(board_size=11)", "pentago". */
+ * "breakthrough(rows=8,columns=8)", "hex", "hex(board_size=11)", "pentago", "othello". */
 #define BSG_TIC_TAC_TOE 0
 #define BSG_CONNECT_FOUR 1
 #define BSG_BREAKTHROUGH 2
@@ -44,6 +44,7 @@ extern "C" {
 /* open_spiel/games/pentago.cc — the first game of SURVEY.md section 8f row 4 (more
  * perfect-information board games on the same kernels). */
 #define BSG_PENTAGO 5
+#define BSG_OTHELLO 6 /* open_spiel/games/othello.cc, same row */
 
 #define BSG_OK 0
 #define BSG_ERR_BAD_GAME (-1)

@@ -32,7 +32,7 @@ namespace bsg {
 // =========================================================================================
 struct TicTacToe {
   static constexpr int kId = kGameTicTacToe;
-  static constexpr int kNumActions = 9, kMaxLen = 9, kObsSize = 27, kStateBytes = 4;
+  static constexpr int kNumActions = 9, kMaxLen = 9, kMaxDepth = kMaxLen, kObsSize = 27, kStateBytes = 4;
   static constexpr int kObsWords = 1, kMaskWords = 1;
   static constexpr int kPlanes = 1;   // packed SoA planes and their element sizes
   BSG_HD static int plane_bytes(int p) { (void)p; return 4; }
@@ -181,7 +181,7 @@ struct TicTacToe {
 // =========================================================================================
 struct ConnectFour {
   static constexpr int kId = kGameConnectFour;
-  static constexpr int kNumActions = 7, kMaxLen = 42, kObsSize = 126, kStateBytes = 8;
+  static constexpr int kNumActions = 7, kMaxLen = 42, kMaxDepth = kMaxLen, kObsSize = 126, kStateBytes = 8;
   static constexpr int kObsWords = 4, kMaskWords = 1;
   static constexpr int kPlanes = 1;
   BSG_HD static int plane_bytes(int p) { (void)p; return 8; }
@@ -359,7 +359,7 @@ struct ConnectFour {
 // =========================================================================================
 struct Breakthrough {
   static constexpr int kId = kGameBreakthrough;
-  static constexpr int kNumActions = 768, kMaxLen = 209, kObsSize = 192, kStateBytes = 20;
+  static constexpr int kNumActions = 768, kMaxLen = 209, kMaxDepth = kMaxLen, kObsSize = 192, kStateBytes = 20;
   static constexpr int kObsWords = 6, kMaskWords = 24;
   static constexpr int kPlanes = 2;
   BSG_HD static int plane_bytes(int p) { return p == 0 ? 16 : 4; }
@@ -607,7 +607,7 @@ template <int N>
 struct HexT {
   static constexpr int kId = kGameHex;
   static constexpr int kCells = N * N;
-  static constexpr int kNumActions = N * N, kMaxLen = N * N, kObsSize = 9 * N * N;
+  static constexpr int kNumActions = N * N, kMaxLen = N * N, kMaxDepth = kMaxLen, kObsSize = 9 * N * N;
   static constexpr int kStateBytes = 64;
   static constexpr int kObsWords = (9 * N * N + 31) / 32, kMaskWords = 4;
   static constexpr int kPlanes = 4;
@@ -902,6 +902,189 @@ struct HexT {
 typedef HexT<11> Hex;
 
 // =========================================================================================
+// othello — reference: open_spiel/games/othello.cc   
+//   8 x 8, cell = row * 8 + col, black = player 0 moves first (othello.cc:263-269).  A move
+//   places a disc that brackets opponent discs in at least one of eight directions and flips
+//   them (othello.cc:126-158,200-229); a player without such a move must PASS (action 64,
+//   othello.cc:241-246) and the game ends right after a placement that leaves neither side a
+//   move — disc majority wins, equal counts tie (othello.cc:214-226).  The winner is decided
+//   by counting, so the last mover can win or lose (kMoverCanLose).
+//   Bit = cell in one u64 per colour.  Legal moves: the parallel-prefix bracket scan in four
+//   axis pairs; flips: eight directional fills from the new disc.  The mover's move set is
+//   carried in the state (the terminal test needs the next mover's moves anyway), so a step
+//   runs one move generation, or a second one in the rare case that the next mover has none.
+//   The reference reports MaxGameLength() = 64 (othello.h:142); with passes a game can take up
+//   to 60 placements + 59 passes, which is what kMaxDepth bounds.
+//   packed: plane 0: 16 B {black, white}; plane 1: u32 = mover | terminal << 1 | outcome << 2.
+// =========================================================================================
+struct Othello {
+  static constexpr int kId = kGameOthello;
+  static constexpr int kNumActions = 65, kMaxLen = 64, kMaxDepth = 120, kObsSize = 192, kStateBytes = 20;
+  static constexpr int kObsWords = 6, kMaskWords = 3;
+  static constexpr int kPlanes = 2;
+  BSG_HD static int plane_bytes(int p) { return p == 0 ? 16 : 4; }
+  static constexpr bool kCanStick = false;    // a player without a placement passes
+  static constexpr bool kAsync = false;
+  static constexpr bool kMoverCanLose = true;
+  static constexpr int kPass = 64;
+  static constexpr u64 kInner = 0x7E7E7E7E7E7E7E7Eull;   // columns 1..6: no wrap for +-1, +-7, +-9
+  struct State {
+    u64 own, opp;   // discs of the player to move / of the other player
+    u64 moves;      // placements open to the player to move (0: must pass)
+    u32 mv;         // player to move
+    u32 term;       // neither side can move
+    u32 res;        // at the end: 1 = the last mover has more discs, 2 = fewer, 0 = equal
+  };
+  struct Tables { u32 modM[64]; };
+  static void fill_tables(Tables& t) { for (u32 n = 0; n < 64; ++n) t.modM[n] = modM_entry(n); }
+
+  // Cells where `p` may place: empty cells at the far end of a run of `o` discs that starts
+  // next to a `p` disc (othello.cc:126-158 for every cell at once).  One axis = two directions.
+  BSG_HD static u64 axis_moves(u64 p, u64 mask, int d) {
+    u64 fl = mask & (p << d), fr = mask & (p >> d);
+    fl |= mask & (fl << d);   fr |= mask & (fr >> d);
+    const u64 ml = mask & (mask << d), mr = mask & (mask >> d);
+    fl |= ml & (fl << (2 * d)); fr |= mr & (fr >> (2 * d));
+    fl |= ml & (fl << (2 * d)); fr |= mr & (fr >> (2 * d));
+    return (fl << d) | (fr >> d);
+  }
+  BSG_HD static u64 get_moves(u64 p, u64 o) {
+    const u64 inner = o & kInner;
+    const u64 m = axis_moves(p, inner, 1) | axis_moves(p, o, 8) | axis_moves(p, inner, 7) | axis_moves(p, inner, 9);
+    return m & ~(p | o);
+  }
+  // Discs flipped by a disc of `p` on bit x: per direction the run of `o` discs from x, kept
+  // when a `p` disc ends it (othello.cc:126-146,160-177).
+  BSG_HD static u64 get_flips(u64 x, u64 p, u64 o) {
+    const u64 inner = o & kInner;
+    u64 flips = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int d = i == 0 ? 1 : (i == 1 ? 8 : (i == 2 ? 7 : 9));
+      const u64 mask = i == 1 ? o : inner;
+      u64 fl = mask & (x << d), fr = mask & (x >> d);
+#pragma unroll
+      for (int k = 0; k < 5; ++k) { fl |= mask & (fl << d); fr |= mask & (fr >> d); }
+      if (p & (fl << d)) flips |= fl;
+      if (p & (fr >> d)) flips |= fr;
+    }
+    return flips;
+  }
+
+  BSG_HD static void init(State& s) {
+    s.own = (1ull << 28) | (1ull << 35);   // black e4, d5
+    s.opp = (1ull << 27) | (1ull << 36);   // white d4, e5
+    s.mv = 0; s.term = 0; s.res = 0;
+    s.moves = get_moves(s.own, s.opp);
+  }
+  BSG_HD static void load(State& s, const void* base, int64_t n, int64_t i) {
+#if defined(__CUDA_ARCH__)
+    ulonglong2 w = ((const ulonglong2*)base)[i];
+    u64 b = w.x, wh = w.y;
+#else
+    u64 b = ((const u64*)base)[2 * i], wh = ((const u64*)base)[2 * i + 1];
+#endif
+    u32 meta = ((const u32*)((const char*)base + 16 * n))[i];
+    s.mv = meta & 1u; s.term = (meta >> 1) & 1u;
+    const u32 outc = (meta >> 2) & 3u;
+    s.own = s.mv ? wh : b;
+    s.opp = s.mv ? b : wh;
+    s.moves = s.term ? 0ull : get_moves(s.own, s.opp);
+    s.res = (!s.term || outc >= 2u) ? 0u : (outc == (s.mv ^ 1u) ? 1u : 2u);
+  }
+  BSG_HD static void store(const State& s, void* base, int64_t n, int64_t i) {
+    ((u64*)base)[2 * i] = s.mv ? s.opp : s.own;
+    ((u64*)base)[2 * i + 1] = s.mv ? s.own : s.opp;
+    ((u32*)((char*)base + 16 * n))[i] = s.mv | (s.term << 1) | ((u32)outcome(s) << 2);
+  }
+  BSG_HD static bool terminal(const State& s) { return s.term != 0; }
+  BSG_HD static bool won(const State& s) { return s.term && s.res == 1u; }
+  BSG_HD static bool lost(const State& s) { return s.term && s.res == 2u; }
+  BSG_HD static int mover(const State& s) { return (int)s.mv; }
+  BSG_HD static int outcome(const State& s) {
+    if (!s.term) return kOutcomeNone;
+    return s.res == 1u ? (int)(s.mv ^ 1u) : (s.res == 2u ? (int)s.mv : kOutcomeDraw);
+  }
+
+  // othello.cc:200-229.  pos = 64 is the pass.
+  BSG_HD static void play(State& s, int pos) {
+    if (pos == kPass) {
+      const u64 t = s.own; s.own = s.opp; s.opp = t;
+      s.mv ^= 1u;
+      s.moves = get_moves(s.own, s.opp);
+      return;
+    }
+    const u64 x = 1ull << pos;
+    const u64 flips = get_flips(x, s.own, s.opp);
+    const u64 mine = s.own | x | flips, theirs = s.opp & ~flips;
+    u64 next = get_moves(theirs, mine);           // the other player's placements
+    if (next == 0 && get_moves(mine, theirs) == 0) {
+      const int a = popc64(mine), b = popc64(theirs);
+      s.term = 1u;
+      s.res = a > b ? 1u : (a < b ? 2u : 0u);
+    }
+    s.own = theirs;
+    s.opp = mine;
+    s.moves = next;
+    s.mv ^= 1u;
+  }
+  BSG_HD static u32 step(State& s, u32 r, const Tables& tab, int& action) {
+    const u64 m = s.moves;
+    const u32 n = (u32)popc64(m);
+    int pos = kPass;
+    if (n != 0) {
+      u32 k = fastmod(r, n, tab.modM[n & 63u]);
+      u32 w = (u32)m;
+      pos = 0;
+      const u32 c = (u32)popc32(w);
+      if (k >= c) { k -= c; pos = 32; w = (u32)(m >> 32); }
+      pos += select32(w, (int)k);
+    }
+    action = pos;
+    play(s, pos);
+    return n ? n : 1u;
+  }
+  BSG_HD static int legal(const State& s, int* out) {
+    if (s.term) return 0;
+    int n = 0;
+    for (int c = 0; c < 64; ++c) if ((s.moves >> c) & 1ull) out[n++] = c;
+    if (n == 0) out[n++] = kPass;
+    return n;
+  }
+  BSG_HD static bool apply(State& s, int a) {
+    if (s.term || a < 0 || a > kPass) return false;
+    if (a == kPass) { if (s.moves != 0) return false; }   // (the reference lets any pass through)
+    else if (!((s.moves >> a) & 1ull)) return false;
+    play(s, a);
+    return true;
+  }
+  BSG_HD static u32 legal_bit(const State& s, int a) {
+    if (s.term) return 0u;
+    return a == kPass ? (s.moves == 0 ? 1u : 0u) : (u32)((s.moves >> a) & 1ull);
+  }
+  // othello.cc:310-329: plane 0 empty, 1 the observer's discs, 2 the opponent's.
+  BSG_HD static u32 obs_bit(const State& s, int player, int idx) {
+    const int plane = idx >> 6, cell = idx & 63;
+    const u64 mine = ((int)s.mv == player) ? s.own : s.opp, theirs = ((int)s.mv == player) ? s.opp : s.own;
+    const u64 m = plane == 0 ? ~(mine | theirs) : (plane == 1 ? mine : theirs);
+    return (u32)(m >> cell) & 1u;
+  }
+  BSG_HD static void obs_words(const State& s, int player, u32* out) {
+    const u64 mine = ((int)s.mv == player) ? s.own : s.opp, theirs = ((int)s.mv == player) ? s.opp : s.own;
+    const u64 e = ~(mine | theirs);
+    out[0] = (u32)e; out[1] = (u32)(e >> 32);
+    out[2] = (u32)mine; out[3] = (u32)(mine >> 32);
+    out[4] = (u32)theirs; out[5] = (u32)(theirs >> 32);
+  }
+  BSG_HD static void mask_words(const State& s, u32* out) {
+    const u64 m = s.term ? 0ull : s.moves;
+    out[0] = (u32)m; out[1] = (u32)(m >> 32);
+    out[2] = (!s.term && m == 0) ? 1u : 0u;
+  }
+};
+
+
+// =========================================================================================
 // pentago — reference: open_spiel/games/pentago.cc   (one more
 //   perfect-information board game on the same kernel framework)
 //   6 x 6 board, a move places a stone on an empty cell and then turns one 3 x 3 quadrant a
@@ -918,7 +1101,7 @@ typedef HexT<11> Hex;
 // =========================================================================================
 struct Pentago {
   static constexpr int kId = kGamePentago;
-  static constexpr int kNumActions = 288, kMaxLen = 36, kObsSize = 108, kStateBytes = 16;
+  static constexpr int kNumActions = 288, kMaxLen = 36, kMaxDepth = kMaxLen, kObsSize = 108, kStateBytes = 16;
   static constexpr int kObsWords = 4, kMaskWords = 9;
   static constexpr int kPlanes = 1;
   BSG_HD static int plane_bytes(int p) { (void)p; return 16; }

@@ -41,6 +41,7 @@ template <class F> inline int dispatch_game(int game, F&& f) {
     case BSG_HEX: return f.template operator()<Hex>();
     case BSG_HEX5_HOST_ONLY: return f.template operator()<Hex5>();
     case BSG_PENTAGO: return f.template operator()<Pentago>();
+    case BSG_OTHELLO: return f.template operator()<Othello>();
     default: break;
   }
   return BSG_ERR_BAD_GAME;
@@ -53,6 +54,7 @@ template <class F> inline int dispatch_device_game(int game, F&& f) {
     case BSG_BREAKTHROUGH: return f.template operator()<Breakthrough>();
     case BSG_HEX: return f.template operator()<Hex>();
     case BSG_PENTAGO: return f.template operator()<Pentago>();
+    case BSG_OTHELLO: return f.template operator()<Othello>();
     default: break;
   }
   return BSG_ERR_BAD_GAME;
@@ -318,6 +320,31 @@ template <> struct Text<Pentago> {  // pentago.cc:168-217 (plain output, no ANSI
   static bool has_board_format() { return false; }
   static std::string serialize(const Pentago::State&) { return std::string(); }
   static int deserialize(Pentago::State&, const char*) { return BSG_ERR_BAD_ARG; }
+};
+
+template <> struct Text<Othello> {  // othello.cc:271-282; labels :68-92
+  static std::string to_string(const Othello::State& s) {
+    const u64 black = s.mv ? s.opp : s.own, white = s.mv ? s.own : s.opp;
+    // CurrentPlayer() is kTerminalPlayerId (-4) at the end, printed as a number (othello.cc:82-92)
+    std::string str = s.term ? "-4" : (s.mv ? "White (o)" : "Black (x)");
+    str += " to play:\n  a b c d e f g h  \n";
+    for (int r = 0; r < 8; ++r) {
+      str += (char)('1' + r);
+      str += ' ';
+      for (int c = 0; c < 8; ++c) {
+        const int cell = r * 8 + c;
+        str += ((black >> cell) & 1ull) ? 'x' : (((white >> cell) & 1ull) ? 'o' : '-');
+        str += ' ';
+      }
+      str += (char)('1' + r);
+      str += '\n';
+    }
+    str += "  a b c d e f g h  ";
+    return str;
+  }
+  static bool has_board_format() { return false; }
+  static std::string serialize(const Othello::State&) { return std::string(); }
+  static int deserialize(Othello::State&, const char*) { return BSG_ERR_BAD_ARG; }
 };
 
 struct ToStringOp {

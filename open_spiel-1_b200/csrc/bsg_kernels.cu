@@ -594,6 +594,7 @@ int bsg_game_id(const char* g) {
   if (s == "hex(board_size=5)") return BSG_HEX5_HOST_ONLY;
   if (s == "pentago" || s == "pentago()" || s == "pentago(ansi_color_output=False)" ||
       s == "pentago(ansi_color_output=false)") return BSG_PENTAGO;
+  if (s == "othello" || s == "othello()") return BSG_OTHELLO;
   return BSG_ERR_BAD_GAME;
 }
 
@@ -610,6 +611,7 @@ int bsg_observation_shape(int game, int shape[3]) {
     case BSG_HEX: shape[0] = 9; shape[1] = 11; shape[2] = 11; return BSG_OK;         // hex.h:113-115
     case BSG_HEX5_HOST_ONLY: shape[0] = 9; shape[1] = 5; shape[2] = 5; return BSG_OK;
     case BSG_PENTAGO: shape[0] = 3; shape[1] = 6; shape[2] = 6; return BSG_OK;       // pentago.h:106-108
+    case BSG_OTHELLO: shape[0] = 3; shape[1] = 8; shape[2] = 8; return BSG_OK;       // othello.h:139-141
     default: return BSG_ERR_BAD_GAME;
   }
 }
@@ -665,7 +667,7 @@ uint32_t bsg_draw(uint64_t seed, uint64_t playout, uint32_t t) {
 int bsg_create(int game, int device, bsg_engine** out) {
   if (!out) return BSG_ERR_BAD_ARG;
   *out = nullptr;
-  if (game < 0 || game == BSG_HEX5_HOST_ONLY || game > BSG_PENTAGO) return BSG_ERR_BAD_GAME;
+  if (game < 0 || game == BSG_HEX5_HOST_ONLY || game > BSG_OTHELLO) return BSG_ERR_BAD_GAME;
   int count = 0;
   if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return BSG_ERR_NO_DEVICE;
   if (device < 0 || device >= count) return BSG_ERR_BAD_ARG;
@@ -950,7 +952,7 @@ struct bsg_forest {
 namespace {
 struct ForestGeomOp {
   int* depth;
-  template <class G> int operator()() const { *depth = G::kMaxLen + 2; return BSG_OK; }
+  template <class G> int operator()() const { *depth = G::kMaxDepth + 2; return BSG_OK; }
 };
 template <class T> int forest_alloc(bsg_forest* f, T** p, size_t count) {
   void* q = nullptr;
@@ -978,7 +980,7 @@ struct ForestSelfTestOp {
     G::store(root, rootbuf.data(), 1, 0);
     const size_t T = (size_t)n_trees, B = (size_t)leaf_batch;
     const int cap = (sims + sims2 + 2) * (G::kNumActions < 64 ? G::kNumActions : 64) + 2 * G::kNumActions + 8;
-    const int depth = G::kMaxLen + 2;
+    const int depth = G::kMaxDepth + 2;
     std::vector<bsg::MctsNode> nodes(T * (size_t)cap);
     std::vector<int32_t> n_nodes(T), paths(T * B * (size_t)depth), path_len(T * B), leaf_kind(T * B), n_pending(T), leaf_ret(T * B);
     std::vector<uint64_t> shuffle_ctr(T, 0), next_playout(T), leaf_base(T * B);

@@ -47,10 +47,10 @@ class GameType:
 
 _CANONICAL = {C.TIC_TAC_TOE: "tic_tac_toe()", C.CONNECT_FOUR: "connect_four()",
               C.BREAKTHROUGH: "breakthrough(columns=8,rows=8)", C.HEX: "hex(board_size=11)",
-              C.HEX5_HOST_ONLY: "hex(board_size=5)", C.PENTAGO: "pentago(ansi_color_output=False)"}
+              C.HEX5_HOST_ONLY: "hex(board_size=5)", C.PENTAGO: "pentago(ansi_color_output=False)", C.OTHELLO: "othello()"}
 _SHORT = {C.TIC_TAC_TOE: "tic_tac_toe", C.CONNECT_FOUR: "connect_four",
           C.BREAKTHROUGH: "breakthrough", C.HEX: "hex", C.HEX5_HOST_ONLY: "hex",
-          C.PENTAGO: "pentago"}
+          C.PENTAGO: "pentago", C.OTHELLO: "othello"}
 
 
 class Game:

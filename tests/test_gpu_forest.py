@@ -26,7 +26,8 @@ def table(root, scale):
     ("tic_tac_toe", [4, 0], 5, 4000, 200, 8),        # solver proofs travel through the merge
     ("pentago", [112, 3], 3, 600, 64, 8),
     ("hex", [60, 48], 3, 450, 50, 4),
-    ("breakthrough", [], 3, 450, 75, 8)])
+    ("breakthrough", [], 3, 450, 75, 8),
+    ("othello", [19, 18], 3, 450, 75, 8)])
 def test_forest_equals_host_tree_root_parallel(bsg, game, history, trees, sims, step, batch):
   from open_spiel_1_b200.forest import ForestMCTS
   from open_spiel_1_b200.parallel import RootParallelMCTS

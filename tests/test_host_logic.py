@@ -19,7 +19,7 @@ from oracle_lib import Oracle
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 GAMES = [("tic_tac_toe", "tic_tac_toe", 11), ("connect_four", "connect_four", 11),
          ("breakthrough", "breakthrough", 11), ("hex", "hex", 11), ("hex(board_size=5)", "hex", 5),
-         ("pentago", "pentago", 11)]
+         ("pentago", "pentago", 11), ("othello", "othello", 11)]
 
 
 @pytest.fixture(scope="module")
@@ -43,7 +43,7 @@ def check_state(oracle, st, oname, bs, hist):
                                           ("connect_four", "connect_four"),
                                           ("breakthrough", "breakthrough"),
                                           ("hex5", "hex(board_size=5)"),
-                                          ("pentago", "pentago")])
+                                          ("pentago", "pentago"), ("othello", "othello")])
 def test_golden_playthroughs(fixture, name):
   with open(os.path.join(GOLD, "playthrough_%s.json" % fixture)) as f:
     data = json.load(f)

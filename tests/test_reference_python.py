@@ -12,7 +12,7 @@ import pytest
 from oracle_lib import reference_python
 
 UCT_C = 2.0
-GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex(board_size=11)", "pentago"]
+GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex(board_size=11)", "pentago", "othello"]
 
 
 @pytest.fixture(scope="module")
