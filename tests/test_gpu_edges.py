@@ -124,7 +124,7 @@ def test_empty_input_and_bad_arguments(bsg, torch):
   assert msg                                              # the message of the last failure
   assert C.lib.bsg_playouts(None, None, 1, 1, 0, 0, None, None) == C.ERR_BAD_ARG
   with pytest.raises(RuntimeError):
-    bsg.Engine("othello", 0)                              # unsupported game string
+    bsg.Engine("chess", 0)                                # unsupported game string
   with pytest.raises(RuntimeError):
     bsg.pack_histories("connect_four", [[3, 3, 3, 3, 3, 3, 3]])   # seventh stone in a column
   # the engine is still usable after the failures
