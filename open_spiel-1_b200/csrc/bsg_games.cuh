@@ -39,6 +39,7 @@ struct TicTacToe {
   static constexpr bool kCanStick = false;  // a non-terminal state always has a legal action
   static constexpr bool kAsync = false;     // a step completes within the step (see HexT)
   static constexpr bool kMoverCanLose = false;  // a move never ends the game in the mover's disfavour (see Pentago)
+  static constexpr bool kLazyEnd = false;       // the lean kernel sees a terminal state in the step that reaches it (see Othello)
   struct State {
     u32 cur, opp;   // marks of the player to move / of the other player (9-bit masks)
     u32 left;       // empty cells; parity = player to move (x = player 0 first, 9 cells)
@@ -188,6 +189,7 @@ struct ConnectFour {
   static constexpr bool kCanStick = false;
   static constexpr bool kAsync = false;
   static constexpr bool kMoverCanLose = false;
+  static constexpr bool kLazyEnd = false;       // the lean kernel sees a terminal state in the step that reaches it (see Othello)
   struct State {
     u64 cur, opp;  // stones of the player to move / of the other player
     u32 left;      // empty cells; 42 - left stones on the board, parity = player to move
@@ -372,6 +374,7 @@ struct Breakthrough {
   static constexpr bool kCanStick = true;
   static constexpr bool kAsync = false;
   static constexpr bool kMoverCanLose = false;
+  static constexpr bool kLazyEnd = false;       // the lean kernel sees a terminal state in the step that reaches it (see Othello)
   static constexpr u64 kCol0 = 0x0101010101010101ull, kCol7 = 0x8080808080808080ull;
   struct State { u64 own, opp; u32 mv, term, outc; };
   // sel4: the last two levels of the weighted rank-select as one look-up.  Index = h4 << 8 |
@@ -615,6 +618,7 @@ struct HexT {
   static constexpr bool kCanStick = false;
   static constexpr bool kAsync = true;
   static constexpr bool kMoverCanLose = false;
+  static constexpr bool kLazyEnd = false;       // the lean kernel sees a terminal state in the step that reaches it (see Othello)
   struct State {
     u32 cO[4], cA[4], cB[4];   // side to move: all stones / edge-A connected / edge-B connected
     u32 oO[4], oA[4], oB[4];   // the side that moved last
@@ -912,7 +916,8 @@ typedef HexT<11> Hex;
 //   Bit = cell in one u64 per colour.  Legal moves: the parallel-prefix bracket scan in four
 //   axis pairs; flips: eight directional fills from the new disc.  The mover's move set is
 //   carried in the state (the terminal test needs the next mover's moves anyway), so a step
-//   runs one move generation, or a second one in the rare case that the next mover has none.
+//   runs one move generation, or a second one in the rare case that the next mover has none
+//   (the lean kernel defers that second one to an iteration of its own: step_lazy).
 //   The reference reports MaxGameLength() = 64 (othello.h:142); with passes a game can take up
 //   to 60 placements + 59 passes, which is what kMaxDepth bounds.
 //   packed: plane 0: 16 B {black, white}; plane 1: u32 = mover | terminal << 1 | outcome << 2.
@@ -926,6 +931,10 @@ struct Othello {
   static constexpr bool kCanStick = false;    // a player without a placement passes
   static constexpr bool kAsync = false;
   static constexpr bool kMoverCanLose = true;
+  // The lean kernel learns that a playout is over one iteration late (step_lazy below): the
+  // "neither side can move" test after a placement needs a second move generation that only
+  // ~1 step in 40 uses but, as a branch, most warp-steps would pay for.
+  static constexpr bool kLazyEnd = true;
   static constexpr int kPass = 64;
   static constexpr u64 kInner = 0x7E7E7E7E7E7E7E7Eull;   // columns 1..6: no wrap for +-1, +-7, +-9
   struct State {
@@ -997,6 +1006,10 @@ struct Othello {
     ((u64*)base)[2 * i + 1] = s.mv ? s.own : s.opp;
     ((u32*)((char*)base + 16 * n))[i] = s.mv | (s.term << 1) | ((u32)outcome(s) << 2);
   }
+  BSG_HD static bool same_state(const State& a, const State& b) {
+    return a.own == b.own && a.opp == b.opp && a.moves == b.moves && a.mv == b.mv && a.term == b.term &&
+           (!a.term || a.res == b.res);
+  }
   BSG_HD static bool terminal(const State& s) { return s.term != 0; }
   BSG_HD static bool won(const State& s) { return s.term && s.res == 1u; }
   BSG_HD static bool lost(const State& s) { return s.term && s.res == 2u; }
@@ -1027,6 +1040,62 @@ struct Othello {
     s.opp = mine;
     s.moves = next;
     s.mv ^= 1u;
+  }
+  // Flips for the device step: the same eight directional runs, filled by doubling (a run is
+  // at most six discs: 1 + 1 + 2 + 2) like the move generator, three fill steps instead of six.
+  BSG_HD static u64 get_flips_fast(u64 x, u64 p, u64 o) {
+    const u64 inner = o & kInner;
+    u64 flips = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int d = i == 0 ? 1 : (i == 1 ? 8 : (i == 2 ? 7 : 9));
+      const u64 mask = i == 1 ? o : inner;
+      u64 fl = mask & (x << d), fr = mask & (x >> d);
+      fl |= mask & (fl << d);   fr |= mask & (fr >> d);
+      const u64 ml = mask & (mask << d), mr = mask & (mask >> d);
+      fl |= ml & (fl << (2 * d)); fr |= mr & (fr >> (2 * d));
+      fl |= ml & (fl << (2 * d)); fr |= mr & (fr >> (2 * d));
+      flips |= (p & (fl << d)) ? fl : 0ull;
+      flips |= (p & (fr >> d)) ? fr : 0ull;
+    }
+    return flips;
+  }
+  // One iteration of the lean kernel, straight-line for every lane.  A state with an empty
+  // move set that is not marked terminal is UNRESOLVED: either the player to move must pass or
+  // the game is over (othello.cc:214-229,241-246).  With g = the moves of the other side after
+  // this iteration's placement (or, without a placement, of the other side as it stands):
+  //   moves != 0           place a disc; the other side is to move with g (g may be empty)
+  //   moves == 0, g != 0   the pass: the other side is to move with g
+  //   moves == 0, g == 0   nobody can move: the game ended with the previous placement; no
+  //                        action is made (made = 0) and the state becomes terminal
+  // Every path is the same flips + one move generation; the result equals play()'s.
+  BSG_HD static u32 step_lazy(State& s, u32 r, const Tables& tab, int& action, u32& made) {
+    const u64 m = s.moves;
+    const u32 n = (u32)popc64(m);
+    u32 k = fastmod(r, n, tab.modM[n & 63u]);
+    u32 w = (u32)m;
+    int pos = 0;
+    const u32 c = (u32)popc32(w);
+    if (k >= c) { k -= c; pos = 32; w = (u32)(m >> 32); }
+    pos += select32(w, (int)k);
+    const u64 x = n ? (1ull << (pos & 63)) : 0ull;
+    const u64 flips = get_flips_fast(x, s.own, s.opp);
+    const u64 mine = s.own | x | flips, theirs = s.opp & ~flips;
+    const u64 g = get_moves(theirs, mine);
+    const bool over = (n == 0) & (g == 0);
+    if (over) {   // the last mover's discs are s.opp
+      const int a = popc64(s.opp), b = popc64(s.own);
+      s.term = 1u;
+      s.res = a > b ? 1u : (a < b ? 2u : 0u);
+    } else {
+      s.own = theirs;
+      s.opp = mine;
+      s.mv ^= 1u;
+    }
+    s.moves = g;
+    made = over ? 0u : 1u;
+    action = n ? pos : kPass;
+    return n ? n : 1u;
   }
   BSG_HD static u32 step(State& s, u32 r, const Tables& tab, int& action) {
     const u64 m = s.moves;
@@ -1108,6 +1177,7 @@ struct Pentago {
   static constexpr bool kCanStick = false;
   static constexpr bool kAsync = false;
   static constexpr bool kMoverCanLose = true;
+  static constexpr bool kLazyEnd = false;       // the lean kernel sees a terminal state in the step that reaches it (see Othello)
   static constexpr u64 kBoard = 0x00003F3F3F3F3F3Full;
   struct State {
     u64 cur, opp;   // stones of the player to move / of the player who moved last

@@ -119,7 +119,22 @@ struct StepOp {
     int tmp[kMaxLegal];
     if (G::legal(s, tmp) == 0) return BSG_ERR_STUCK_LANE;
     int a = -1;
-    G::step(s, r, TablesOf<G>::get(), a);
+    if constexpr (G::kLazyEnd) {
+      // the lean kernel's step_lazy must arrive where step() does: the same action and state,
+      // a terminal state one action-less iteration later
+      typename G::State z = s;
+      int az = -1; u32 made = 0;
+      G::step_lazy(z, r, TablesOf<G>::get(), az, made);
+      G::step(s, r, TablesOf<G>::get(), a);
+      if (made != 1u || az != a || G::terminal(z)) return BSG_ERR_BAD_ARG;  // internal inconsistency
+      if (G::terminal(s)) {
+        G::step_lazy(z, r ^ 0x9E3779B9u, TablesOf<G>::get(), az, made);
+        if (made != 0u || !G::terminal(z)) return BSG_ERR_BAD_ARG;
+      }
+      if (!G::same_state(s, z)) return BSG_ERR_BAD_ARG;
+    } else {
+      G::step(s, r, TablesOf<G>::get(), a);
+    }
     if (action) *action = a;
     G::store(s, p, cap, i);
     return BSG_OK;

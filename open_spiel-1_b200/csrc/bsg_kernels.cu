@@ -198,7 +198,10 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
       }
       int action = 0;
       u32 nlegal = 1;
-      if constexpr (!G::kAsync) {
+      u32 made = 1;   // kLazyEnd: 0 in the iteration that only finds the game over
+      if constexpr (G::kLazyEnd && !kFull) {
+        nlegal = G::step_lazy(s, r, tab, action, made);
+      } else if constexpr (!G::kAsync) {
         nlegal = G::step(s, r, tab, action);   // finished lanes run dead steps: no divergence
       } else {
         if (can) nlegal = G::step(s, r, tab, action);
@@ -227,7 +230,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         const u32 won = G::won(s) ? 1u : 0u;
         fin_win |= can & won;
         if constexpr (G::kMoverCanLose) fin_lose |= can & (G::lost(s) ? 1u : 0u);
-        t += can;
+        if constexpr (G::kLazyEnd) t += can & made; else t += can;
         live &= (can & term) ^ 1u;
       }
     }
