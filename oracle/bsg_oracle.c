@@ -6,6 +6,8 @@
  *   breakthrough: 0 empty, 1 black (player 0), 2 white (player 1)  (breakthrough.h:45-49)
  *   hex: the signed 9-value enum of hex.h:51-61 (-4..4)
  *   othello: 0 empty, 1 black (player 0), 2 white (player 1)  (othello.h:40-44)
+ *   y: 0 player 0 (kPlayer1), 1 player 1 (kPlayer2), 2 empty (kPlayerNone), 3 off the board
+ *       (kPlayerInvalid)  (y.h:43-48)
  *   pentago: 0 empty, 1 player 0, 2 player 1 (pentago.h:44-49 orders kPlayer1, kPlayer2, kPlayerNone;
  *       only the observation plane order depends on it and that is player-relative)
  */
@@ -35,6 +37,7 @@ int orc_num_distinct_actions(int game, int n) {
     case ORC_BT: return 8 * 8 * 6 * 2;
     case ORC_PENTAGO: return 36 * 8; /* pentago.h:40-42 */
     case ORC_OTHELLO: return 65;     /* othello.h:128: 64 cells + pass */
+    case ORC_Y: return n * n;        /* y.h:174-178: the cut-off corner is never legal */
     default: return n * n;
   }
 }
@@ -45,6 +48,7 @@ int orc_max_game_length(int game, int n) {
     case ORC_BT: return 2 * (2 * 8 - 3) * 8 + 1; /* breakthrough.h:116-118 */
     case ORC_PENTAGO: return 36; /* pentago.h:109-113 */
     case ORC_OTHELLO: return 64; /* othello.h:142 */
+    case ORC_Y: return n * (n + 1) / 2; /* y.h:192-197 */
     default: return n * n;
   }
 }
@@ -55,6 +59,7 @@ int orc_obs_size(int game, int n) {
     case ORC_BT: return 192;
     case ORC_PENTAGO: return 3 * 36; /* pentago.h:106-108 */
     case ORC_OTHELLO: return 3 * 64; /* othello.h:139-141 */
+    case ORC_Y: return 3 * n * n;    /* y.h:189-191 */
     default: return 9 * n * n;
   }
 }
@@ -382,12 +387,78 @@ static int ot_apply(orc_state* s, int a) {
   return 0;
 }
 
+/* ---------------------------------------------------------------- y (N x N grid, the triangle x + y < N) */
+enum { Y_P0 = 0, Y_P1 = 1, Y_NONE = 2, Y_INVALID = 3 };   /* y.h:43-48 */
+/* y.h:56-63 */
+static int y_xy(int x, int y, int n) {
+  return (x >= 0 && y >= 0 && x < n && y < n && x + y < n) ? x + y * n : -1;
+}
+/* y.cc:106-111: bit 0 the x = 0 edge, bit 1 the y = 0 edge, bit 2 the x + y = N - 1 edge */
+static int y_edge(int x, int y, int n) {
+  if (y_xy(x, y, n) < 0) return 0;
+  return (x == 0 ? 1 : 0) | (y == 0 ? 2 : 0) | (x + y == n - 1 ? 4 : 0);
+}
+/* y.cc:67-71: neighbour offsets, clockwise */
+static const int kYNb[6][2] = {{0, -1}, {1, -1}, {1, 0}, {0, 1}, {-1, 1}, {-1, 0}};
+/* y.cc:120-132 */
+static void y_init(orc_state* s) {
+  int n = s->board_size;
+  for (int i = 0; i < n * n; ++i) {
+    int x = i % n, y = i / n;
+    s->cells[i] = y_xy(x, y, n) >= 0 ? Y_NONE : Y_INVALID;
+    s->parent[i] = (int16_t)i;
+    s->size[i] = 1;
+    s->edge[i] = (uint8_t)y_edge(x, y, n);
+  }
+}
+/* y.cc:293-304: follow the parents to the leader, compress this cell's path only */
+static int y_find(orc_state* s, int cell) {
+  int parent = s->parent[cell];
+  if (parent != cell) {
+    do {
+      parent = s->parent[parent];
+    } while (parent != s->parent[parent]);
+    s->parent[cell] = (int16_t)parent;
+  }
+  return parent;
+}
+/* y.cc:306-325: the smaller group joins the larger one (ties: b joins a) */
+static void y_join(orc_state* s, int a, int b) {
+  int la = y_find(s, a), lb = y_find(s, b);
+  if (la == lb) return;
+  if (s->size[la] < s->size[lb]) { int t = la; la = lb; lb = t; }
+  s->parent[lb] = (int16_t)la;
+  s->size[la] = (int16_t)(s->size[la] + s->size[lb]);
+  s->edge[la] |= s->edge[lb];
+}
+/* y.cc:269-291 */
+static int y_apply(orc_state* s, int a) {
+  int n = s->board_size;
+  if (a < 0 || a >= n * n || s->cells[a] != Y_NONE) return -1;
+  int x = a % n, y = a / n;
+  s->cells[a] = s->cur_player;
+  s->num_moves += 1;
+  for (int d = 0; d < 6; ++d) {
+    int m = y_xy(x + kYNb[d][0], y + kYNb[d][1], n);
+    if (m >= 0 && s->cells[m] == s->cur_player) y_join(s, a, m);
+  }
+  if (s->edge[y_find(s, a)] == 7) s->outcome = s->cur_player;
+  s->cur_player = 1 - s->cur_player;
+  return 0;
+}
+
 /* ---------------------------------------------------------------- generic API */
 void orc_init(orc_state* s, int game, int board_size) {
   memset(s, 0, sizeof(*s));
   s->game = game;
   s->outcome = -1;
   s->board_size = game == ORC_HEX ? (board_size > 0 ? board_size : 11) : 0;
+  if (game == ORC_Y) {
+    /* y.h:38: 19 by default; the reference's playthrough uses 9.  A hex-style default of 11
+     * passed by a caller that does not care about the size means "the default". */
+    s->board_size = (board_size > 0 && board_size != 11) ? board_size : 19;
+    y_init(s);
+  }
   if (game == ORC_OTHELLO) {
     /* othello.cc:263-269: white on d4/e5, black on e4/d5; black (player 0) moves first */
     s->cells[3 * OT_N + 3] = 2; s->cells[3 * OT_N + 4] = 1;
@@ -409,6 +480,7 @@ int orc_is_terminal(const orc_state* s) {
     case ORC_BT: return s->outcome >= 0 || s->pieces[0] == 0 || s->pieces[1] == 0; /* :306-308 */
     case ORC_PENTAGO: return s->outcome != -1;                      /* pentago.h:62 */
     case ORC_OTHELLO: return s->outcome != -1;                      /* othello.cc:284-286 */
+    case ORC_Y: return s->outcome != -1;                            /* y.h:129 */
     default: return s->outcome != -1;                               /* hex.cc:248 */
   }
 }
@@ -433,6 +505,10 @@ int orc_legal_actions(const orc_state* s, int* out) {
       return pg_legal(s, out);
     case ORC_OTHELLO:
       return ot_legal(s, out);
+    case ORC_Y: /* y.cc:138-149 */
+      for (int c = 0; c < s->board_size * s->board_size; ++c)
+        if (s->cells[c] == Y_NONE) out[n++] = c;
+      return n;
     default: /* hex.cc:186-196 */
       for (int c = 0; c < s->board_size * s->board_size; ++c)
         if (s->cells[c] == HX_EMPTY) out[n++] = c;
@@ -448,6 +524,7 @@ int orc_apply(orc_state* s, int a) {
     case ORC_BT: return bt_apply(s, a);
     case ORC_PENTAGO: return pg_apply(s, a);
     case ORC_OTHELLO: return ot_apply(s, a);
+    case ORC_Y: return y_apply(s, a);
     default: return hex_apply(s, a);
   }
 }
@@ -494,6 +571,17 @@ void orc_observation(const orc_state* s, int player, uint8_t* out) {
         int v = s->cells[c];
         plane = v == 0 ? 0 : ((v - 1) == player ? 1 : 2);
         out[plane * 64 + c] = 1;
+      }
+      return;
+    case ORC_Y: /* y.cc:239-267: plane 0 the observer's stones, 1 the other's, 2 empty; cells
+                 * off the board stay zero in every plane */
+      ncell = s->board_size * s->board_size;
+      memset(out, 0, 3 * ncell);
+      for (int c = 0; c < ncell; ++c) {
+        int v = s->cells[c];
+        if (v == Y_INVALID) continue;
+        plane = v == Y_NONE ? 2 : (v == player ? 0 : 1);
+        out[plane * ncell + c] = 1;
       }
       return;
     case ORC_PENTAGO: /* pentago.cc:246-272: plane 0 the observer's stones, 1 the other's, 2 empty */

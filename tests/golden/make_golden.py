@@ -3,7 +3,7 @@
 
 Sources (all under /root/reference, read in place, never copied verbatim):
   * open_spiel/integration_tests/playthroughs/{tic_tac_toe,connect_four,breakthrough,
-    hex(board_size=5),pentago,othello}.txt — the reference's own golden playthroughs; per state we keep the
+    hex(board_size=5),pentago,othello,y(board_size=9)}.txt — the reference's own golden playthroughs; per state we keep the
     action history, LegalActions(), CurrentPlayer(), IsTerminal(), Returns() and both
     players' ObservationTensor planes (as flat 0/1 lists in CHW order).
   * open_spiel/games/connect_four_test.cc:33-80 — FastLoss / DeserializeDraw known answers.
@@ -33,6 +33,7 @@ GAMES = {
     "hex5": ("hex(board_size=5).txt", (9, 5, 5)),
     "pentago": ("pentago.txt", (3, 6, 6)),
     "othello": ("othello.txt", (3, 8, 8)),
+    "y9": ("y(board_size=9).txt", (3, 9, 9)),
 }
 
 
@@ -128,8 +129,8 @@ def reference_vectors(lib):
   lib.ref_state_dump.argtypes = [ctypes.c_char_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
                                  ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                  ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
-  sizes = {"tic_tac_toe": 27, "connect_four": 126, "breakthrough": 192, "hex": 1089, "pentago": 108, "othello": 192}
-  for game in ["tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello"]:
+  sizes = {"tic_tac_toe": 27, "connect_four": 126, "breakthrough": 192, "hex": 1089, "pentago": 108, "othello": 192, "y": 1083}
+  for game in ["tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y"]:
     recs = []
     for playout in range(12):
       # root = first `d` moves of another replay (seed 7), then replay with seed 20240611.

@@ -12,9 +12,18 @@ import numpy as np
 
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(REPO, "oracle")
-GAME_IDS = {"tic_tac_toe": 0, "connect_four": 1, "breakthrough": 2, "hex": 3, "pentago": 5, "othello": 6}
-OBS_SIZE = {"tic_tac_toe": 27, "connect_four": 126, "breakthrough": 192, "hex": 1089, "pentago": 108, "othello": 192}
+GAME_IDS = {"tic_tac_toe": 0, "connect_four": 1, "breakthrough": 2, "hex": 3, "pentago": 5, "othello": 6, "y": 7}
+OBS_SIZE = {"tic_tac_toe": 27, "connect_four": 126, "breakthrough": 192, "hex": 1089, "pentago": 108, "othello": 192, "y": 1083}
 vp = ctypes.c_void_p
+
+
+def obs_size(game, board_size=11):
+  if game == "hex":
+    return 9 * board_size * board_size
+  if game == "y":
+    n = 19 if board_size == 11 else board_size
+    return 3 * n * n
+  return OBS_SIZE[game]
 
 
 def _ptr(a):
@@ -91,7 +100,7 @@ class Oracle:
 
   def state_dump(self, game, hist, player=0, board_size=11):
     h = np.asarray(hist, np.int64)
-    size = 9 * board_size * board_size if game == "hex" else OBS_SIZE[game]
+    size = obs_size(game, board_size)
     obs = np.zeros(size, np.uint8)
     legal = np.zeros(1024, np.int64)
     nl, cp, tm = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
@@ -150,6 +159,8 @@ class Reference:
 
   @staticmethod
   def game_string(game, board_size=11):
+    if game == "y":   # default 19 (y.h:38); callers that pass the hex default mean "default"
+      return ("y(board_size=%d)" % (19 if board_size == 11 else board_size)).encode()
     return ("hex(board_size=%d)" % board_size if game == "hex" else game).encode()
 
   def replay(self, game, hist, r_table=None, seed=0, playout=0, max_steps=1 << 20, board_size=11):
@@ -182,7 +193,7 @@ class Reference:
 
   def state_dump(self, game, hist, player=0, board_size=11):
     h = np.asarray(hist, np.int64)
-    size = 9 * board_size * board_size if game == "hex" else OBS_SIZE[game]
+    size = obs_size(game, board_size)
     obs = np.zeros(size, np.float64)
     legal = np.zeros(1024, np.int64)
     nl, cp, tm = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
@@ -228,7 +239,7 @@ class Reference:
     return buf.raw[:n].decode()
 
   def deserialize_dump(self, game, text, player=None, board_size=11):
-    size = 9 * board_size * board_size if game == "hex" else OBS_SIZE[game]
+    size = obs_size(game, board_size)
     obs = np.zeros(size, np.float64)
     legal = np.zeros(1024, np.int64)
     nl, cp, tm = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()

@@ -13,7 +13,8 @@ pytestmark = pytest.mark.skipif(not os.path.exists(reference_path()),
                                 reason="reference library not built")
 
 CASES = [("tic_tac_toe", 11, 400), ("connect_four", 11, 400), ("breakthrough", 11, 150),
-         ("hex", 11, 60), ("hex", 5, 200), ("pentago", 11, 300), ("othello", 11, 150)]
+         ("hex", 11, 60), ("hex", 5, 200), ("pentago", 11, 300), ("othello", 11, 150),
+         ("y", 11, 60), ("y", 9, 200)]   # y: 11 stands for the default size 19
 
 
 @pytest.fixture(scope="module")
