@@ -40,7 +40,12 @@ OPS_PER_STEP = {"tic_tac_toe": 48, "connect_four": 96, "breakthrough": 140, "hex
                 # othello: parallel-prefix move generation 4 axes x 22 64-bit ops = 176, popc 2,
                 # rng 25, mod 4, 64-bit rank-select 24, flips 8 directions x 19 64-bit ops = 304,
                 # update 8, terminal test 6, loop 6
-                "othello": 555}
+                "othello": 555,
+                # y 19 (11-word sets over the 19 x 19 grid): legal 11, popc 11, rng 25, mod 4,
+                # 11-word rank-select 50, place (one-hot 22, neighbour labels 44, set updates 55)
+                # 121, amortised flood ~1.0 ring x 198 (11 words x (label 3 + within 5 + ring 10)),
+                # loop 4
+                "y": 424}
 ROOT_SEED = 20240611
 METRIC = "connect_four game-steps/s (uniform-random playouts from mid-game roots)"
 
@@ -133,7 +138,7 @@ def sample_histories(game, n, seed):
   from oracle_lib import Oracle
   from importlib import import_module
   depths = {"tic_tac_toe": (0, 4), "connect_four": (8, 20), "breakthrough": (0, 40), "hex": (0, 60),
-            "pentago": (0, 20), "othello": (0, 40)}
+            "pentago": (0, 20), "othello": (0, 40), "y": (0, 80)}
   dmin, dmax = depths[game]
   orc = Oracle()
   rng = np.random.RandomState(seed & 0x7FFFFFFF)
@@ -405,7 +410,7 @@ def rank0_extras(args, eng, torch, dev, steps_per_s_per_gpu, kernel_ms, n):
       e_bt.close()
       torch.cuda.empty_cache()
       for g, npl in (("tic_tac_toe", 1 << 24), ("breakthrough", 1 << 22), ("hex", 1 << 20),
-                     ("pentago", 1 << 22), ("othello", 1 << 21)):
+                     ("pentago", 1 << 22), ("othello", 1 << 21), ("y", 1 << 19)):
         e_g = bsg.Engine(g, eng.device)
         dmin, dmax = ROOT_DEPTHS[g]
         st, _ = make_roots(e_g, npl, dmin, dmax, seed=ROOT_SEED + 4)

@@ -33,7 +33,8 @@ extern "C" {
 
 /* Game ids.  Strings accepted by bsg_game_id are the reference's game strings
  * (open_spiel/spiel.h:792-803): "tic_tac_toe", "connect_four", "breakthrough",
- * "breakthrough(rows=8,columns=8)", "hex", "hex(board_size=11)", "pentago", "othello". */
+ * "breakthrough(rows=8,columns=8)", "hex", "hex(board_size=11)", "pentago", "othello", "y",
+ * "y(board_size=19)". */
 #define BSG_TIC_TAC_TOE 0
 #define BSG_CONNECT_FOUR 1
 #define BSG_BREAKTHROUGH 2
@@ -45,6 +46,9 @@ extern "C" {
  * perfect-information board games on the same kernels). */
 #define BSG_PENTAGO 5
 #define BSG_OTHELLO 6 /* open_spiel/games/othello.cc, same row */
+#define BSG_Y 7       /* open_spiel/games/y.cc, board_size = 19 (the reference's default), same row */
+/* Host-helper-only id for the reference's y(board_size=9) golden playthrough; no kernels. */
+#define BSG_Y9_HOST_ONLY 8
 
 #define BSG_OK 0
 #define BSG_ERR_BAD_GAME (-1)

@@ -1353,4 +1353,331 @@ struct Pentago {
 };
 
 
+// =========================================================================================
+// y N (N = 19, the reference's default, in the product; N = 9 only for the reference's golden
+// playthrough) — reference: open_spiel/games/y.cc   
+//   The board is the triangle x + y < N of an N x N grid, cell = x + y * N (y.h:56-63), so
+//   NumDistinctActions = N * N with the cut-off corner never legal (y.h:174-178).  Player 0
+//   ("kPlayer1", drawn O) moves first.  A player wins when ONE group of their stones touches
+//   all three edges x = 0, y = 0, x + y = N - 1 (y.cc:106-111,285-287); corners touch two.  The
+//   board cannot fill up without a winner, so there is no draw.  The six neighbours
+//   (y.cc:67-71) are the offsets -N, -N+1, +1, +N, +N-1, -1: the hex neighbourhood, so one
+//   ring of a set is the same four shifts as in HexT, on W = ceil((N*(N-1)+1)/32) words.
+//
+//   The reference keeps groups in a union-find with an edge bit-set per leader
+//   (y.cc:293-325).  Here every stone carries its group's edge set as three bit planes
+//   E0, E1, E2 over the grid (both colours in one plane: a cell has one owner): a new stone
+//   takes the union L of its own edges and its neighbours' groups' edge sets, wins when L is
+//   all three, and otherwise L floods through the mover's stones that lack a label of L — the
+//   union of the merged groups.  The flood is the asynchronous one of HexT (kAsync): placing
+//   a stone records the first frontier, every kernel iteration runs one ring for every lane,
+//   a lane moves only when its frontier is empty; host helpers flood synchronously.
+//   Stones are kept as A (all stones) and P (player 1's), so the mover's stones are one LOP3
+//   and nothing is swapped when the turn passes.
+//   packed: SoA, 5 planes of 4*PW bytes (PW = W rounded up to 4 words): player 0's stones,
+//   player 1's stones, E0, E1, E2; plane 5: u32 = last move + 1 (0: none; y.cc:160-207 draws
+//   it in brackets).
+// =========================================================================================
+template <int N>
+struct YT {
+  static constexpr int kId = kGameY;
+  static constexpr int kGrid = N * N;
+  static constexpr int kCells = N * (N + 1) / 2;
+  static constexpr int kBits = N * (N - 1) + 1;          // highest on-board cell index + 1
+  static constexpr int W = (kBits + 31) / 32;            // words that can hold a stone
+  static constexpr int PW = (W + 3) / 4 * 4;             // words per packed plane (16-byte multiples)
+  static_assert(PW <= 12 && N <= 19, "mask tables below are written out for at most 12 words");
+  static constexpr int kNumActions = kGrid, kMaxLen = kCells, kMaxDepth = kMaxLen, kObsSize = 3 * kGrid;
+  static constexpr int kStateBytes = 5 * 4 * PW + 4;
+  static constexpr int kObsWords = (3 * kGrid + 31) / 32, kMaskWords = (kGrid + 31) / 32;
+  static constexpr int kPlanes = 6;
+  BSG_HD static int plane_bytes(int p) { return p < 5 ? 4 * PW : 4; }
+  static constexpr bool kCanStick = false;
+  static constexpr bool kAsync = true;
+  static constexpr bool kMoverCanLose = false;
+  static constexpr bool kLazyEnd = false;
+  struct State {
+    u32 A[W], P[W];            // all stones / player 1's stones
+    u32 E0[W], E1[W], E2[W];   // stones whose group touches edge x = 0 / y = 0 / x + y = N - 1
+    u32 F[W];                  // pending flood frontier: stones of the flood's owner next to
+                               // newly labelled ones that still lack a label being spread
+    u32 m0, m1, m2;            // ~0: the pending flood spreads that label
+    u32 fq;                    // ~0: the flood's owner is player 1
+    u32 left;                  // empty cells
+    u32 mv;                    // player to move
+    u32 win;                   // the last move connected all three edges
+    u32 last;                  // last move + 1 (0: none)
+  };
+  // nb[cell]: neighbour mask in words 0..W-1; word PW-1... the cell's own edge set sits in
+  // edge[cell] (bit 0 x = 0, bit 1 y = 0, bit 2 x + y = N - 1).  sel8[b][k]: k-th set bit of b.
+  struct Tables {
+    u32 nb[kGrid][PW];
+    u32 modM[256];
+    unsigned char edge[(kGrid + 3) / 4 * 4];
+    unsigned char sel8[256][8];
+  };
+  BSG_HDC static bool on_board(int x, int y) { return x >= 0 && y >= 0 && x < N && y < N && x + y < N; }
+  static void fill_tables(Tables& t) {
+    for (u32 n = 0; n < 256; ++n) t.modM[n] = modM_entry(n);
+    for (int b = 0; b < 256; ++b) {
+      int k = 0;
+      for (int i = 0; i < 8; ++i) t.sel8[b][i] = 0;
+      for (int i = 0; i < 8; ++i) if ((b >> i) & 1) t.sel8[b][k++] = (unsigned char)i;
+    }
+    for (int i = 0; i < (int)sizeof(t.edge); ++i) t.edge[i] = 0;
+    const int dx[6] = {0, 1, 1, 0, -1, -1}, dy[6] = {-1, -1, 0, 1, 1, 0};   // y.cc:67-71
+    for (int cell = 0; cell < kGrid; ++cell) {
+      for (int w = 0; w < PW; ++w) t.nb[cell][w] = 0;
+      const int x = cell % N, y = cell / N;
+      if (!on_board(x, y)) continue;
+      for (int k = 0; k < 6; ++k) {
+        const int x2 = x + dx[k], y2 = y + dy[k];
+        if (!on_board(x2, y2)) continue;
+        const int v = x2 + y2 * N;
+        t.nb[cell][v >> 5] |= 1u << (v & 31);
+      }
+      t.edge[cell] = (unsigned char)((x == 0 ? 1 : 0) | (y == 0 ? 2 : 0) | (x + y == N - 1 ? 4 : 0));
+    }
+  }
+  // Compile-time masks of word w: board cells, cells with x != 0, cells with x != N - 1.
+  BSG_HDC static u32 word_mask(int w, int kind) {
+    u32 m = 0;
+    for (int b = 0; b < 32; ++b) {
+      const int cell = 32 * w + b;
+      if (cell >= kGrid) break;
+      const int x = cell % N, y = cell / N;
+      const bool in = kind == 0 ? on_board(x, y) : (kind == 1 ? x != 0 : x != N - 1);
+      if (in) m |= 1u << b;
+    }
+    return m;
+  }
+#define BSG_Y_MASKS(kind)                                                                        \
+  {word_mask(0, kind), word_mask(1, kind), word_mask(2, kind),  word_mask(3, kind),              \
+   word_mask(4, kind), word_mask(5, kind), word_mask(6, kind),  word_mask(7, kind),              \
+   word_mask(8, kind), word_mask(9, kind), word_mask(10, kind), word_mask(11, kind)}
+  BSG_HD static u32 board_word(int w) { constexpr u32 m[12] = BSG_Y_MASKS(0); return m[w]; }
+  BSG_HD static u32 not_col0(int w) { constexpr u32 m[12] = BSG_Y_MASKS(1); return m[w]; }
+  BSG_HD static u32 not_col_last(int w) { constexpr u32 m[12] = BSG_Y_MASKS(2); return m[w]; }
+#undef BSG_Y_MASKS
+
+  BSG_HD static void init(State& s) {
+#pragma unroll
+    for (int w = 0; w < W; ++w) s.A[w] = s.P[w] = s.E0[w] = s.E1[w] = s.E2[w] = s.F[w] = 0;
+    s.m0 = s.m1 = s.m2 = 0; s.fq = 0;
+    s.left = kCells; s.mv = 0; s.win = 0; s.last = 0;
+  }
+  BSG_HD static void load(State& s, const void* base, int64_t n, int64_t i) {
+    u32 pl[5][PW];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+    for (int p = 0; p < 5; ++p) {
+      const uint4* q = (const uint4*)((const char*)base + (int64_t)p * 4 * PW * n) + i * (PW / 4);
+#pragma unroll
+      for (int j = 0; j < PW / 4; ++j) {
+        const uint4 v = q[j];
+        pl[p][4 * j] = v.x; pl[p][4 * j + 1] = v.y; pl[p][4 * j + 2] = v.z; pl[p][4 * j + 3] = v.w;
+      }
+    }
+#else
+    for (int p = 0; p < 5; ++p) {
+      const u32* q = (const u32*)((const char*)base + (int64_t)p * 4 * PW * n) + i * PW;
+      for (int j = 0; j < PW; ++j) pl[p][j] = q[j];
+    }
+#endif
+    s.last = ((const u32*)((const char*)base + (int64_t)5 * 4 * PW * n))[i];
+    int n0 = 0, n1 = 0;
+    u32 won = 0;
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+      n0 += popc32(pl[0][w]); n1 += popc32(pl[1][w]);
+      s.A[w] = pl[0][w] | pl[1][w]; s.P[w] = pl[1][w];
+      s.E0[w] = pl[2][w]; s.E1[w] = pl[3][w]; s.E2[w] = pl[4][w];
+      s.F[w] = 0;
+      won |= pl[2][w] & pl[3][w] & pl[4][w];
+    }
+    s.mv = n0 > n1 ? 1u : 0u;   // player 0 moves first and turns alternate
+    s.win = won ? 1u : 0u;
+    s.left = (u32)(kCells - n0 - n1);
+    s.m0 = s.m1 = s.m2 = 0; s.fq = 0;
+  }
+  BSG_HD static void store(const State& s0, void* base, int64_t n, int64_t i) {
+    State s = s0;
+    finish(s);   // a packed state always carries complete edge sets
+#pragma unroll
+    for (int p = 0; p < 5; ++p) {
+      u32* q = (u32*)((char*)base + (int64_t)p * 4 * PW * n) + i * PW;
+#pragma unroll
+      for (int w = 0; w < PW; ++w) {
+        u32 v = 0;
+        if (w < W) v = p == 0 ? (s.A[w] & ~s.P[w]) : (p == 1 ? s.P[w] : (p == 2 ? s.E0[w] : (p == 3 ? s.E1[w] : s.E2[w])));
+        q[w] = v;
+      }
+    }
+    ((u32*)((char*)base + (int64_t)5 * 4 * PW * n))[i] = s.last;
+  }
+  BSG_HD static bool terminal(const State& s) { return s.win != 0; }
+  BSG_HD static bool won(const State& s) { return s.win != 0; }
+  BSG_HD static int mover(const State& s) { return (int)s.mv; }
+  BSG_HD static int outcome(const State& s) { return s.win ? (int)(s.mv ^ 1u) : kOutcomeNone; }
+
+  // One ring of neighbours of every cell of f, restricted to `within` (which lies on the
+  // board).  x+1 / x-1 are shifts by one with the row wrap masked; (x, y-1) and (x+1, y-1) are
+  // (f | east) shifted down by N, (x, y+1) and (x-1, y+1) are (f | west) shifted up by N.
+  BSG_HD static void dilate_within(const u32 f[W], const u32 within[W], u32 out[W]) {
+    u32 fe[W], fw[W], ew[W];
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+      const u32 e = (w == 0 ? f[0] << 1 : fshl(f[w - 1], f[w], 1)) & not_col0(w);
+      const u32 x = (w == W - 1 ? f[w] >> 1 : fshr(f[w], f[w + 1], 1)) & not_col_last(w);
+      fe[w] = f[w] | e;
+      fw[w] = f[w] | x;
+      ew[w] = e | x;
+    }
+    constexpr int q = N >> 5, r = N & 31;   // N < 32 here: q = 0
+    static_assert(q == 0 && r != 0, "row shifts are written for N < 32");
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+      const u32 nn = w == W - 1 ? fe[w] >> r : fshr(fe[w], fe[w + 1], r);
+      const u32 ss = w == 0 ? fw[0] << r : fshl(fw[w - 1], fw[w], r);
+      out[w] = (ew[w] | nn | ss) & within[w];
+    }
+  }
+  // The pending flood, one ring per call: the frontier takes the labels being spread, the next
+  // frontier is its ring among the owner's stones that still lack one of them.
+  BSG_HD static void ring(State& s) {
+    u32 within[W], d[W];
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+      s.E0[w] |= s.F[w] & s.m0;
+      s.E1[w] |= s.F[w] & s.m1;
+      s.E2[w] |= s.F[w] & s.m2;
+      const u32 own = s.A[w] & ~(s.P[w] ^ s.fq);
+      const u32 full = (s.E0[w] | ~s.m0) & (s.E1[w] | ~s.m1) & (s.E2[w] | ~s.m2);
+      within[w] = own & ~full;
+    }
+    dilate_within(s.F, within, d);
+#pragma unroll
+    for (int w = 0; w < W; ++w) s.F[w] = d[w];
+  }
+  BSG_HD static bool pending(const State& s) {
+    u32 any = 0;
+#pragma unroll
+    for (int w = 0; w < W; ++w) any |= s.F[w];
+    return any != 0;
+  }
+  BSG_HD static void finish(State& s) { while (pending(s)) ring(s); }
+
+  // y.cc:269-291 for the mover.  The new stone's group has the edges of the stone itself and
+  // of every neighbouring group of the mover (y.cc:279-283: JoinGroups ORs the edge sets).
+  BSG_HD static void place(State& s, int cell, const Tables& t) {
+    const u32 q = s.mv ? 0xFFFFFFFFu : 0u;
+    const u32 edges = t.edge[cell];
+    const u32 cw = (u32)cell >> 5, cb = 1u << (cell & 31);
+    u32 nb[W], mine[W];
+    u32 h0 = 0, h1 = 0, h2 = 0;
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+      nb[w] = t.nb[cell][w];
+      mine[w] = s.A[w] & ~(s.P[w] ^ q);
+      const u32 x = nb[w] & mine[w];
+      h0 |= x & s.E0[w]; h1 |= x & s.E1[w]; h2 |= x & s.E2[w];
+    }
+    const bool t0 = h0 != 0 || (edges & 1u), t1 = h1 != 0 || (edges & 2u), t2 = h2 != 0 || (edges & 4u);
+    const u32 l0 = t0 ? 0xFFFFFFFFu : 0u, l1 = t1 ? 0xFFFFFFFFu : 0u, l2 = t2 ? 0xFFFFFFFFu : 0u;
+    const bool win = t0 && t1 && t2;
+    const u32 go = win ? 0u : 0xFFFFFFFFu;   // no flood runs on the winning move
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+      const u32 m = (u32)w == cw ? cb : 0u;
+      s.A[w] |= m;
+      s.P[w] |= m & q;
+      s.E0[w] |= m & l0; s.E1[w] |= m & l1; s.E2[w] |= m & l2;
+      const u32 full = (s.E0[w] | ~l0) & (s.E1[w] | ~l1) & (s.E2[w] | ~l2);
+      s.F[w] = nb[w] & mine[w] & ~full & go;
+    }
+    s.m0 = l0; s.m1 = l1; s.m2 = l2; s.fq = q;
+    s.win = win ? 1u : 0u;
+    s.mv ^= 1u;
+    s.left -= 1u;
+    s.last = (u32)cell + 1u;
+  }
+  BSG_HD static u32 empty_word(const State& s, int w) { return ~s.A[w] & board_word(w); }
+  // k-th (ascending) empty cell, k < left: the word by running popcounts, then halves of the
+  // word, then a byte table.
+  BSG_HD static int select_empty(const State& s, u32 k, const Tables& tab) {
+    u32 x = empty_word(s, 0), below = 0, pos = 0, cum = 0;
+#pragma unroll
+    for (int w = 0; w + 1 < W; ++w) {
+      cum += (u32)popc32(empty_word(s, w));
+      const bool g = k >= cum;
+      x = g ? empty_word(s, w + 1) : x;
+      below = g ? cum : below;
+      pos = g ? 32u * (u32)(w + 1) : pos;
+    }
+    u32 kk = k - below;
+    u32 h = (u32)popc32(x & 0xFFFFu);
+    if (kk >= h) { kk -= h; x >>= 16; pos += 16; }
+    h = (u32)popc32(x & 0xFFu);
+    if (kk >= h) { kk -= h; x >>= 8; pos += 8; }
+    const u32 cell = pos + tab.sel8[x & 0xFFu][kk & 7u];
+    return (int)(cell < (u32)kGrid ? cell : 0u);   // a dead lane's garbage stays inside the tables
+  }
+  BSG_HD static u32 step(State& s, u32 r, const Tables& tab, int& action) {
+    const u32 n = s.left;                                  // y.cc:138-149: every empty cell
+    const u32 k = fastmod(r, n, tab.modM[n & 255u]);
+    const int cell = select_empty(s, k, tab);
+    action = cell;
+    place(s, cell, tab);
+    return n;
+  }
+  BSG_HD static int legal(const State& s, int* out) {
+    if (terminal(s)) return 0;
+    int n = 0;
+    for (int c = 0; c < kBits; ++c) if ((empty_word(s, c >> 5) >> (c & 31)) & 1u) out[n++] = c;
+    return n;
+  }
+  BSG_HD static u32 legal_bit(const State& s, int a) {
+    return (!s.win && a >= 0 && a < kBits && ((empty_word(s, a >> 5) >> (a & 31)) & 1u)) ? 1u : 0u;
+  }
+  BSG_HD static bool apply(State& s, int a, const Tables& t) {
+    if (!legal_bit(s, a)) return false;
+    place(s, a, t);
+    finish(s);      // host helpers flood synchronously
+    return true;
+  }
+  // y.cc:239-267: plane 0 the observer's stones, 1 the other player's, 2 empty board cells;
+  // grid cells off the board are zero in every plane.
+  BSG_HD static u32 plane_word(const State& s, int player, int plane, int w) {
+    const u32 q = player ? 0xFFFFFFFFu : 0u;
+    if (plane == 0) return s.A[w] & ~(s.P[w] ^ q);
+    if (plane == 1) return s.A[w] & (s.P[w] ^ q);
+    return empty_word(s, w);
+  }
+  BSG_HD static u32 obs_bit(const State& s, int player, int idx) {
+    const int plane = idx / kGrid, cell = idx - plane * kGrid;
+    if (cell >= kBits) return 0u;
+    return (plane_word(s, player, plane, cell >> 5) >> (cell & 31)) & 1u;
+  }
+  BSG_HD static void obs_words(const State& s, int player, u32* out) {
+#pragma unroll
+    for (int w = 0; w < kObsWords; ++w) out[w] = 0;
+#pragma unroll
+    for (int p = 0; p < 3; ++p) {
+      const int off = p * kGrid, wi = off >> 5, sh = off & 31;
+#pragma unroll
+      for (int j = 0; j < W; ++j) {
+        const u32 m = plane_word(s, player, p, j);
+        if (wi + j < kObsWords) out[wi + j] |= m << sh;
+        if (sh != 0 && wi + j + 1 < kObsWords) out[wi + j + 1] |= m >> ((32 - sh) & 31);
+      }
+    }
+  }
+  BSG_HD static void mask_words(const State& s, u32* out) {
+#pragma unroll
+    for (int w = 0; w < kMaskWords; ++w) out[w] = (w < W && !s.win) ? empty_word(s, w < W ? w : 0) : 0u;
+  }
+};
+typedef YT<19> Y;
+
+
 }  // namespace bsg

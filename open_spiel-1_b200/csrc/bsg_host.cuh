@@ -13,6 +13,7 @@
 namespace bsg {
 
 typedef HexT<5> Hex5;
+typedef YT<9> Y9;
 constexpr int kMaxLegal = 320;   // pentago: 36 cells x 8 rotations
 
 template <class G> struct TablesOf {
@@ -31,6 +32,8 @@ template <class G> inline bool apply_any(typename G::State& s, int a) { return G
 template <> inline bool apply_any<Hex>(Hex::State& s, int a) { return Hex::apply(s, a, TablesOf<Hex>::get()); }
 template <> inline bool apply_any<Hex5>(Hex5::State& s, int a) { return Hex5::apply(s, a, TablesOf<Hex5>::get()); }
 template <> inline bool apply_any<Pentago>(Pentago::State& s, int a) { return Pentago::apply(s, a, TablesOf<Pentago>::get()); }
+template <> inline bool apply_any<Y>(Y::State& s, int a) { return Y::apply(s, a, TablesOf<Y>::get()); }
+template <> inline bool apply_any<Y9>(Y9::State& s, int a) { return Y9::apply(s, a, TablesOf<Y9>::get()); }
 
 // Calls f.template operator()<G>() for the game id; returns BSG_ERR_BAD_GAME otherwise.
 template <class F> inline int dispatch_game(int game, F&& f) {
@@ -42,6 +45,8 @@ template <class F> inline int dispatch_game(int game, F&& f) {
     case BSG_HEX5_HOST_ONLY: return f.template operator()<Hex5>();
     case BSG_PENTAGO: return f.template operator()<Pentago>();
     case BSG_OTHELLO: return f.template operator()<Othello>();
+    case BSG_Y: return f.template operator()<Y>();
+    case BSG_Y9_HOST_ONLY: return f.template operator()<Y9>();
     default: break;
   }
   return BSG_ERR_BAD_GAME;
@@ -55,6 +60,7 @@ template <class F> inline int dispatch_device_game(int game, F&& f) {
     case BSG_HEX: return f.template operator()<Hex>();
     case BSG_PENTAGO: return f.template operator()<Pentago>();
     case BSG_OTHELLO: return f.template operator()<Othello>();
+    case BSG_Y: return f.template operator()<Y>();
     default: break;
   }
   return BSG_ERR_BAD_GAME;
@@ -360,6 +366,36 @@ template <> struct Text<Othello> {  // othello.cc:271-282; labels :68-92
   static bool has_board_format() { return false; }
   static std::string serialize(const Othello::State&) { return std::string(); }
   static int deserialize(Othello::State&, const char*) { return BSG_ERR_BAD_ARG; }
+};
+
+template <int N> struct Text<YT<N>> {  // y.cc:155-225 (plain output: ansi_color_output = false)
+  typedef YT<N> G;
+  static std::string to_string(const typename G::State& s) {
+    std::string out = " ";
+    for (int x = 0; x < N; ++x) { out += ' '; out += (char)('a' + x); }
+    out += '\n';
+    const int last = (int)s.last - 1;
+    for (int y = 0; y < N; ++y) {
+      out += std::string(y + ((y + 1) < 10 ? 1 : 0), ' ');   // leading space
+      out += std::to_string(y + 1);
+      bool found_last = false;
+      for (int x = 0; x < N - y; ++x) {
+        const int cell = x + y * N;
+        // spacing and last-move highlight
+        if (found_last) { out += ']'; found_last = false; }
+        else if (cell == last) { out += '['; found_last = true; }
+        else out += ' ';
+        const bool stone = (s.A[cell >> 5] >> (cell & 31)) & 1u, p1 = (s.P[cell >> 5] >> (cell & 31)) & 1u;
+        out += !stone ? '.' : (p1 ? '@' : 'O');
+      }
+      if (found_last) out += ']';
+      out += '\n';
+    }
+    return out;
+  }
+  static bool has_board_format() { return false; }
+  static std::string serialize(const typename G::State&) { return std::string(); }
+  static int deserialize(typename G::State&, const char*) { return BSG_ERR_BAD_ARG; }
 };
 
 struct ToStringOp {

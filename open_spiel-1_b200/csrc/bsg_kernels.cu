@@ -598,6 +598,10 @@ int bsg_game_id(const char* g) {
   if (s == "pentago" || s == "pentago()" || s == "pentago(ansi_color_output=False)" ||
       s == "pentago(ansi_color_output=false)") return BSG_PENTAGO;
   if (s == "othello" || s == "othello()") return BSG_OTHELLO;
+  if (s == "y" || s == "y()" || s == "y(board_size=19)" || s == "y(ansi_color_output=False,board_size=19)" ||
+      s == "y(ansi_color_output=false,board_size=19)") return BSG_Y;
+  if (s == "y(board_size=9)" || s == "y(ansi_color_output=False,board_size=9)" ||
+      s == "y(ansi_color_output=false,board_size=9)") return BSG_Y9_HOST_ONLY;
   return BSG_ERR_BAD_GAME;
 }
 
@@ -615,6 +619,8 @@ int bsg_observation_shape(int game, int shape[3]) {
     case BSG_HEX5_HOST_ONLY: shape[0] = 9; shape[1] = 5; shape[2] = 5; return BSG_OK;
     case BSG_PENTAGO: shape[0] = 3; shape[1] = 6; shape[2] = 6; return BSG_OK;       // pentago.h:106-108
     case BSG_OTHELLO: shape[0] = 3; shape[1] = 8; shape[2] = 8; return BSG_OK;       // othello.h:139-141
+    case BSG_Y: shape[0] = 3; shape[1] = 19; shape[2] = 19; return BSG_OK;           // y.h:189-191
+    case BSG_Y9_HOST_ONLY: shape[0] = 3; shape[1] = 9; shape[2] = 9; return BSG_OK;
     default: return BSG_ERR_BAD_GAME;
   }
 }
@@ -670,7 +676,7 @@ uint32_t bsg_draw(uint64_t seed, uint64_t playout, uint32_t t) {
 int bsg_create(int game, int device, bsg_engine** out) {
   if (!out) return BSG_ERR_BAD_ARG;
   *out = nullptr;
-  if (game < 0 || game == BSG_HEX5_HOST_ONLY || game > BSG_OTHELLO) return BSG_ERR_BAD_GAME;
+  if (game < 0 || game == BSG_HEX5_HOST_ONLY || game > BSG_Y) return BSG_ERR_BAD_GAME;
   int count = 0;
   if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return BSG_ERR_NO_DEVICE;
   if (device < 0 || device >= count) return BSG_ERR_BAD_ARG;

@@ -10,7 +10,7 @@ import numpy as np
 
 from . import _cabi as C
 
-GAME_NAMES = ("tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello")
+GAME_NAMES = ("tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y")
 
 
 def game_id(game):
@@ -22,7 +22,7 @@ def game_id(game):
   gid = C.lib.bsg_game_id(game.encode())
   if gid < 0:
     raise RuntimeError("bsg: unsupported game '%s' (supported: tic_tac_toe, connect_four, "
-                       "breakthrough 8x8, hex 11x11, pentago, othello)" % game)
+                       "breakthrough 8x8, hex 11x11, pentago, othello, y 19)" % game)
   return gid
 
 
@@ -32,7 +32,8 @@ def state_bytes(gid):
 
 def plane_bytes(gid):
   """Element sizes of the packed SoA planes of a game."""
-  return {0: [4], 1: [8], 2: [16, 4], 3: [16, 16, 16, 16], 4: [16, 16, 16, 16], 5: [16], 6: [16, 4]}[gid]
+  return {0: [4], 1: [8], 2: [16, 4], 3: [16, 16, 16, 16], 4: [16, 16, 16, 16], 5: [16], 6: [16, 4],
+          7: [48, 48, 48, 48, 48, 4], 8: [16, 16, 16, 16, 16, 4]}[gid]
 
 
 def num_distinct_actions(gid):

@@ -16,6 +16,7 @@ ROOT_DEPTHS = {  # cfg2 U{8..20}, cfg3 U{0..40}, cfg4 U{0..60}
     "hex": (0, 60),
     "pentago": (0, 20),
     "othello": (0, 40),
+    "y": (0, 80),
 }
 
 

@@ -47,10 +47,11 @@ class GameType:
 
 _CANONICAL = {C.TIC_TAC_TOE: "tic_tac_toe()", C.CONNECT_FOUR: "connect_four()",
               C.BREAKTHROUGH: "breakthrough(columns=8,rows=8)", C.HEX: "hex(board_size=11)",
-              C.HEX5_HOST_ONLY: "hex(board_size=5)", C.PENTAGO: "pentago(ansi_color_output=False)", C.OTHELLO: "othello()"}
+              C.HEX5_HOST_ONLY: "hex(board_size=5)", C.PENTAGO: "pentago(ansi_color_output=False)", C.OTHELLO: "othello()",
+              C.Y: "y(ansi_color_output=False,board_size=19)", C.Y9_HOST_ONLY: "y(ansi_color_output=False,board_size=9)"}
 _SHORT = {C.TIC_TAC_TOE: "tic_tac_toe", C.CONNECT_FOUR: "connect_four",
           C.BREAKTHROUGH: "breakthrough", C.HEX: "hex", C.HEX5_HOST_ONLY: "hex",
-          C.PENTAGO: "pentago", C.OTHELLO: "othello"}
+          C.PENTAGO: "pentago", C.OTHELLO: "othello", C.Y: "y", C.Y9_HOST_ONLY: "y"}
 
 
 class Game:
@@ -227,8 +228,8 @@ class State:
     return str(action)
 
   def _text(self, fn):
-    buf = ctypes.create_string_buffer(1024)
-    n = C.check(fn(self._gid, self._packed.ctypes.data, 1, 0, buf, 1024))
+    buf = ctypes.create_string_buffer(4096)
+    n = C.check(fn(self._gid, self._packed.ctypes.data, 1, 0, buf, 4096))
     return buf.raw[:n].decode()
 
   def to_string(self):

@@ -31,7 +31,8 @@ def test_static_facts_match_reference_constants():
   import open_spiel_1_b200 as bsg
   facts = {"tic_tac_toe": (9, 9, 27, [3, 3, 3]), "connect_four": (7, 42, 126, [3, 6, 7]),
            "breakthrough": (768, 209, 192, [3, 8, 8]), "hex": (121, 121, 1089, [9, 11, 11]),
-           "pentago": (288, 36, 108, [3, 6, 6]), "othello": (65, 64, 192, [3, 8, 8])}
+           "pentago": (288, 36, 108, [3, 6, 6]), "othello": (65, 64, 192, [3, 8, 8]),
+           "y": (361, 190, 1083, [3, 19, 19]), "y(board_size=9)": (81, 45, 243, [3, 9, 9])}
   for name, (na, ml, osz, shape) in facts.items():
     g = bsg.load_game(name)
     assert g.num_distinct_actions() == na

@@ -13,11 +13,11 @@ from oracle_lib import Oracle, Reference, reference_path
 
 pytestmark = pytest.mark.gpu
 
-GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello"]
+GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y"]
 # replay-parity sizes: >= 1e5 playouts per game
 N_ROOTS = {"tic_tac_toe": 50000, "connect_four": 50000, "breakthrough": 25000, "hex": 12500,
-           "pentago": 50000, "othello": 25000}
-ROLLOUTS = {"tic_tac_toe": 2, "connect_four": 2, "breakthrough": 4, "hex": 8, "pentago": 2, "othello": 4}
+           "pentago": 50000, "othello": 25000, "y": 6250}
+ROLLOUTS = {"tic_tac_toe": 2, "connect_four": 2, "breakthrough": 4, "hex": 8, "pentago": 2, "othello": 4, "y": 16}
 
 
 @pytest.fixture(scope="module")
@@ -166,7 +166,7 @@ def test_native_rng_win_rates_within_binomial_ci(game, checker, torch):
   torch.cuda.synchronize()
   r = ret0.cpu().numpy()
   n_ref = {"tic_tac_toe": 400000, "connect_four": 200000, "breakthrough": 40000, "hex": 30000,
-           "pentago": 100000, "othello": 40000}[game]
+           "pentago": 100000, "othello": 40000, "y": 20000}[game]
   if isinstance(checker, Reference):
     # reference's own mt19937 stream; per-outcome counts via replay batch are Philox-tied, so
     # use random_playouts for the mean and replay_batch (different seed) for the outcome split
@@ -198,6 +198,7 @@ def test_native_rng_win_rates_within_binomial_ci(game, checker, torch):
     ("hex", 1 << 20, 121, 1),             # cfg4: 1 Mi playouts per GPU
     ("pentago", 1 << 22, 36, 1),
     ("othello", 1 << 22, 120, 1),
+    ("y", 1 << 20, 190, 1),
 ])
 def test_full_size_properties(game, n, max_len, min_len, torch):
   """BASELINE configuration sizes: size-independent properties instead of an oracle run —
@@ -221,7 +222,7 @@ def test_full_size_properties(game, n, max_len, min_len, torch):
   assert int(ret0.to(torch.int64).sum()) == t[2]
   assert bool(term.all())                                    # every playout reached a terminal
   assert int(length.max()) <= max_len and int(length.min()) >= min_len
-  if game in ("breakthrough", "hex"):
+  if game in ("breakthrough", "hex", "y"):
     assert bool((ret0 != 0).all())                           # no draws in breakthrough / hex
   # idempotence / schedule independence: a split launch with first_playout offsets reproduces
   # the same per-playout results (every SoA plane must be sliced for the second half)
@@ -232,7 +233,8 @@ def test_full_size_properties(game, n, max_len, min_len, torch):
   from open_spiel_1_b200 import _cabi as C
   host = states.cpu().numpy()
   sb = eng.state_bytes
-  planes = {"connect_four": [8], "breakthrough": [16, 4], "hex": [16, 16, 16, 16], "pentago": [16], "othello": [16, 4]}[game]
+  planes = {"connect_four": [8], "breakthrough": [16, 4], "hex": [16, 16, 16, 16], "pentago": [16], "othello": [16, 4],
+            "y": [48, 48, 48, 48, 48, 4]}[game]
   assert sum(planes) == sb
 
   def take(lo, hi):
@@ -271,7 +273,7 @@ def test_full_size_properties(game, n, max_len, min_len, torch):
 
 @pytest.mark.parametrize("game,n", [("connect_four", 800000), ("breakthrough", 330000),
                                     ("hex", 110000), ("tic_tac_toe", 1100000),
-                                    ("pentago", 300000), ("othello", 330000)])
+                                    ("pentago", 300000), ("othello", 330000), ("y", 60000)])
 def test_host_buffer_chunked_path_equals_device_path(game, n, torch):
   """bsg_playouts_host cuts large inputs into chunks on two streams (H2D overlapping the
   kernel); totals and per-root sums must equal one device-buffer launch over the same roots,

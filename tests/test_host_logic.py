@@ -19,7 +19,8 @@ from oracle_lib import Oracle
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 GAMES = [("tic_tac_toe", "tic_tac_toe", 11), ("connect_four", "connect_four", 11),
          ("breakthrough", "breakthrough", 11), ("hex", "hex", 11), ("hex(board_size=5)", "hex", 5),
-         ("pentago", "pentago", 11), ("othello", "othello", 11)]
+         ("pentago", "pentago", 11), ("othello", "othello", 11),
+         ("y", "y", 11), ("y(board_size=9)", "y", 9)]   # oracle: 11 = the default size, 19
 
 
 @pytest.fixture(scope="module")
@@ -43,7 +44,8 @@ def check_state(oracle, st, oname, bs, hist):
                                           ("connect_four", "connect_four"),
                                           ("breakthrough", "breakthrough"),
                                           ("hex5", "hex(board_size=5)"),
-                                          ("pentago", "pentago"), ("othello", "othello")])
+                                          ("pentago", "pentago"), ("othello", "othello"),
+                                          ("y9", "y(board_size=9)")])
 def test_golden_playthroughs(fixture, name):
   with open(os.path.join(GOLD, "playthrough_%s.json" % fixture)) as f:
     data = json.load(f)
@@ -90,7 +92,7 @@ def test_kernel_step_path_matches_oracle_replay(oracle, name, oname, bs):
   """Drives bsg_host_replay_step (the kernels' step()) with the Philox draws and compares the
   whole action sequence, length, terminal flag and return with the oracle's replay."""
   gid = bsg.game_id(name)
-  n = 25 if bs == 11 and oname in ("hex", "breakthrough") else 150
+  n = 25 if bs == 11 and oname in ("hex", "breakthrough", "y") else 150
   for playout in range(n):
     seed = 20240611
     packed = bsg.pack_histories(name, [[]]).copy()
