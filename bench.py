@@ -360,7 +360,7 @@ def rank0_extras(args, eng, torch, dev, steps_per_s_per_gpu, kernel_ms, n):
   out["roofline"] = {
       "bound": "int_issue", "kernel": "playout_kernel<ConnectFour,false>",
       "achieved": achieved / 1e12, "peak": peak_int / 1e12, "unit": "T thread-instr/s",
-      "frac": achieved / peak_int, "traffic": ncu_traffic_bytes("playout_kernel<ConnectFour, 0>"),
+      "frac": achieved / peak_int, "traffic": ncu_traffic_bytes("playout_kernel<ConnectFour, 0"),
       "algorithmic_ops_per_step": ops,
       "peak_source": "bsg_int_peak microbenchmark, live: " + ", ".join(
           "%s=%.2fT" % (kinds[k], peaks[k] / 1e12) for k in kinds),
@@ -383,7 +383,8 @@ def rank0_extras(args, eng, torch, dev, steps_per_s_per_gpu, kernel_ms, n):
       gbs = n_obs * 784 / (ms * 1e-3) / 1e9
       out["obs_roofline"] = {"bound": "hbm", "kernel": "expand_kernel<Breakthrough,false>",
                              "achieved": gbs, "peak": hbm_peak, "unit": "GB/s",
-                             "frac": gbs / hbm_peak, "traffic": None, "peak_source": hbm_src,
+                             "frac": gbs / hbm_peak, "traffic": ncu_traffic_bytes("expand_kernel<Breakthrough, 0"),
+                             "peak_source": hbm_src,
                              "states": n_obs, "obs_per_s": n_obs / (ms * 1e-3),
                              "algorithmic_bytes_per_state": 784}
       del obs, st

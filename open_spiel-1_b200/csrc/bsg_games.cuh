@@ -1394,6 +1394,7 @@ struct YT {
   BSG_HD static int plane_bytes(int p) { return p < 5 ? 4 * PW : 4; }
   static constexpr bool kCanStick = false;
   static constexpr bool kAsync = true;
+  static constexpr int kMinBlocks = 2;        // lean kernel: register cap (128) for two CTAs per SM
   static constexpr bool kMoverCanLose = false;
   static constexpr bool kLazyEnd = false;
   struct State {
@@ -1585,15 +1586,16 @@ struct YT {
     const bool t0 = h0 != 0 || (edges & 1u), t1 = h1 != 0 || (edges & 2u), t2 = h2 != 0 || (edges & 4u);
     const u32 l0 = t0 ? 0xFFFFFFFFu : 0u, l1 = t1 ? 0xFFFFFFFFu : 0u, l2 = t2 ? 0xFFFFFFFFu : 0u;
     const bool win = t0 && t1 && t2;
-    const u32 go = win ? 0u : 0xFFFFFFFFu;   // no flood runs on the winning move
+    const u32 go = win ? 0u : 0xFFFFFFFFu;   // the kernel stops at a win; store() completes the labels
 #pragma unroll
     for (int w = 0; w < W; ++w) {
       const u32 m = (u32)w == cw ? cb : 0u;
       s.A[w] |= m;
       s.P[w] |= m & q;
-      s.E0[w] |= m & l0; s.E1[w] |= m & l1; s.E2[w] |= m & l2;
+      // the new stone rides in the frontier: the next ring (run before any lane moves again,
+      // and by store()) gives it the labels L, together with its neighbours that lack one
       const u32 full = (s.E0[w] | ~l0) & (s.E1[w] | ~l1) & (s.E2[w] | ~l2);
-      s.F[w] = nb[w] & mine[w] & ~full & go;
+      s.F[w] = (nb[w] & mine[w] & ~full & go) | m;
     }
     s.m0 = l0; s.m1 = l1; s.m2 = l2; s.fq = q;
     s.win = win ? 1u : 0u;

@@ -12,6 +12,7 @@
 //    lanes are idle; it was slower for all four games);
 //  * a step is unconditional straight-line code (finished lanes run dead steps on a dead
 //    state); only the bookkeeping is predicated.
+#include <type_traits>
 #include <cuda_runtime.h>
 #include <stdio.h>
 
@@ -48,8 +49,12 @@ inline uint32_t out_flags_of(const bsg_playout_io& io) {
          ((io.root_sum_ret0 || io.root_sum_steps) ? kOutRootSums : 0u);
 }
 
+// Resident CTAs per SM the lean kernel is compiled for (register cap); 1 = no cap.
+template <class G, class = void> struct min_blocks : std::integral_constant<int, 1> {};
+template <class G> struct min_blocks<G, std::enable_if_t<(G::kMinBlocks > 1)>> : std::integral_constant<int, G::kMinBlocks> {};
+
 template <class G, bool kFull, bool kBase>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, kFull ? 1 : min_blocks<G>::value)
 playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab) {
   __shared__ __align__(16) typename G::Tables tab;
   {

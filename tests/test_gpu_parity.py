@@ -124,7 +124,8 @@ def test_observations_and_masks_bit_exact(game, torch):
   obs = obs.cpu().numpy().reshape(n, -1)
   mask = mask.cpu().numpy()
   assert set(np.unique(obs).tolist()) <= {0.0, 1.0}
-  assert np.all(obs.sum(1) == eng.obs_size // eng.obs_shape[0])  # exactly one plane per cell
+  cells = 190 if game == "y" else eng.obs_size // eng.obs_shape[0]   # y: the triangle of the 19 x 19 grid
+  assert np.all(obs.sum(1) == cells)  # exactly one plane per board cell
   step = 1 if game in ("tic_tac_toe", "connect_four") else 3
   for i in range(0, n, step * 10):
     d = oracle.state_dump(game, hist[i], i % 2)
