@@ -1528,8 +1528,12 @@ struct YT {
     u32 fe[W], fw[W], ew[W];
 #pragma unroll
     for (int w = 0; w < W; ++w) {
-      const u32 e = (w == 0 ? f[0] << 1 : fshl(f[w - 1], f[w], 1)) & not_col0(w);
-      const u32 x = (w == W - 1 ? f[w] >> 1 : fshr(f[w], f[w + 1], 1)) & not_col_last(w);
+      // f lies on the board, so the only shifts by one that wrap onto a board cell are
+      // (N-1, 0) -> (0, 1) and back: bits N and N - 1 of word 0; every other stray bit lands
+      // off the board and is dropped by `within`
+      u32 e = w == 0 ? f[0] << 1 : fshl(f[w - 1], f[w], 1);
+      u32 x = w == W - 1 ? f[w] >> 1 : fshr(f[w], f[w + 1], 1);
+      if (w == 0) { e &= ~(1u << N); x &= ~(1u << (N - 1)); }
       fe[w] = f[w] | e;
       fw[w] = f[w] | x;
       ew[w] = e | x;
