@@ -411,7 +411,7 @@ def rank0_extras(args, eng, torch, dev, steps_per_s_per_gpu, kernel_ms, n):
       e_bt.close()
       torch.cuda.empty_cache()
       for g, npl in (("tic_tac_toe", 1 << 24), ("breakthrough", 1 << 22), ("hex", 1 << 20),
-                     ("pentago", 1 << 22), ("othello", 1 << 21), ("y", 1 << 19)):
+                     ("pentago", 1 << 22), ("othello", 1 << 21), ("y", 1 << 21)):
         e_g = bsg.Engine(g, eng.device)
         dmin, dmax = ROOT_DEPTHS[g]
         st, _ = make_roots(e_g, npl, dmin, dmax, seed=ROOT_SEED + 4)
