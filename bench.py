@@ -422,6 +422,15 @@ def rank0_extras(args, eng, torch, dev, steps_per_s_per_gpu, kernel_ms, n):
         side[g] = {"playouts": npl, "ms": ms, "game_steps_per_s": steps_per_launch / (ms * 1e-3),
                    "playouts_per_s": npl / (ms * 1e-3),
                    "int_roofline_frac": steps_per_launch / (ms * 1e-3) * OPS_PER_STEP[g] / peak_int}
+        if g in ("hex", "y"):
+          # value-only launch (bsg_playout_io.value_only): same returns, plain stones to a full
+          # board + one reading of the winner; what an Evaluator needs
+          tot.zero_()
+          ms_v = time_kernel(torch, dev, lambda: e_g.playouts(st, npl, 1, seed=7, totals=tot, value_only=True),
+                             reps=3, warm=1)
+          side[g]["value_only"] = {"ms": ms_v, "playouts_per_s": npl / (ms_v * 1e-3),
+                                   "speedup_in_playouts": ms / ms_v,
+                                   "sum_ret0_equal": bool(int(tot.cpu().numpy()[2]) == int(t[2]))}
         e_g.close()
     except Exception as ex:  # side numbers must never kill the headline line
       side["error"] = repr(ex)

@@ -119,6 +119,12 @@ int bsg_host_deserialize(int game, const char* str, void* packed_host, int64_t c
  * path calls it; playouts exist only as CUDA kernels. */
 int bsg_host_replay_step(int game, void* packed_host, int64_t cap, int64_t i, uint32_t r,
                          int64_t* action_out);
+/* Debug/test hook for value-only playouts (bsg_playout_io.value_only): plays packed state i on
+ * with the draws r(seed, playout, t), t = 0, 1, ..., through the kernels' step_fill until the
+ * board is full and reads the winner off it with the kernels' fill_winner.  *ret0_out is the
+ * return to player 0, *moves_out the moves played.  hex / y only.  No product path calls it. */
+int bsg_host_fill_playout(int game, const void* packed_host, int64_t cap, int64_t i, uint64_t seed,
+                          uint64_t playout, int* ret0_out, int* moves_out);
 /* The t-th replay draw r(seed, playout, t). */
 uint32_t bsg_draw(uint64_t seed, uint64_t playout, uint32_t t);
 
@@ -129,6 +135,11 @@ const char* bsg_last_error(bsg_engine* e);
 int bsg_engine_game(const bsg_engine* e);
 int bsg_engine_device(const bsg_engine* e);
 int bsg_engine_sm_count(const bsg_engine* e);
+/* on != 0: the host-buffer playouts of this engine (bsg_playouts_host) run value-only (see
+ * bsg_playout_io.value_only below): same returns, fewer instructions per move, move counts to
+ * the full board.  hex / y only (BSG_ERR_BAD_ARG otherwise).  Value-only launches of one engine
+ * share one scratch buffer: keep them stream-ordered. */
+int bsg_engine_set_value_only(bsg_engine* e, int on);
 
 /* Optional inputs/outputs of one playout launch; all pointers are device pointers and may be
  * NULL.  Playout p (0 <= p < n_roots * rollouts_per_root) starts from root p / rollouts. */
@@ -162,6 +173,16 @@ typedef struct bsg_playout_io {
    * UINT64_MAX skips the root (no playout; nothing is added to its sums).  Lets many search
    * trees, each with its own id range, share one launch (bsg_forest_*). */
   const uint64_t* root_playout_base;
+  /* Value-only playouts, for the games whose full board has exactly one winner and whose stones
+   * never leave the board (hex, y; BSG_ERR_BAD_ARG otherwise): the same draws and the same
+   * moves are played on until the board is full — no connectivity bookkeeping per move — and a
+   * second kernel reads the winner off the full board.  ret0, root_sum_ret0 and totals[2] are
+   * identical to an exact launch (the side that connects first is the side connected at the
+   * end); length, root_sum_steps and totals[1] count the moves to the full board instead of to
+   * the win.  What RandomRolloutEvaluator::Evaluate (mcts.cc:42-71) needs is only the returns.
+   * Excludes max_steps / step_limit / r_table / actions / final_states / state_log /
+   * root_playout_base. */
+  int32_t value_only;
 } bsg_playout_io;
 
 /* The hot path.  Stands in for RandomRolloutEvaluator::Evaluate's playout loop

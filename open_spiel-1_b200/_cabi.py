@@ -43,6 +43,7 @@ class PlayoutIO(ctypes.Structure):
       ("state_log_cap", i64),
       ("state_log_off", vp),
       ("root_playout_base", vp),
+      ("value_only", i32),
   ]
 
 
@@ -68,6 +69,7 @@ def _load():
       "bsg_host_observation": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, ctypes.c_int, vp]),
       "bsg_host_legal_mask": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, vp]),
       "bsg_host_replay_step": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, u32, vp]),
+      "bsg_host_fill_playout": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, ctypes.c_uint64, ctypes.c_uint64, vp, vp]),
       "bsg_host_to_string": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, vp, ctypes.c_int]),
       "bsg_host_serialize": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, vp, ctypes.c_int]),
       "bsg_host_deserialize": (ctypes.c_int, [ctypes.c_int, ctypes.c_char_p, vp, i64, i64]),
@@ -78,6 +80,7 @@ def _load():
       "bsg_engine_game": (ctypes.c_int, [vp]),
       "bsg_engine_device": (ctypes.c_int, [vp]),
       "bsg_engine_sm_count": (ctypes.c_int, [vp]),
+      "bsg_engine_set_value_only": (ctypes.c_int, [vp, ctypes.c_int]),
       "bsg_playouts": (ctypes.c_int, [vp, vp, i64, i32, u64, u64, ctypes.POINTER(PlayoutIO), vp]),
       "bsg_observations": (ctypes.c_int, [vp, vp, i64, vp, vp, vp, vp]),
       "bsg_playouts_host": (ctypes.c_int, [vp, vp, i64, i32, u64, u64, vp, vp, vp]),

@@ -902,6 +902,71 @@ struct HexT {
 #pragma unroll
     for (int w = 0; w < 4; ++w) out[w] = s.win ? 0u : empty_word(s, w);
   }
+
+  // ---- value-only playouts (bsg_playout_io.value_only).  Stones never leave a hex board and
+  // a full board has exactly one winner, so the side that connects first is the side that is
+  // connected when the same move sequence is played on until the board is full: the playout
+  // needs no labels and no flood per move, only one flood of the full board afterwards
+  // (fill_winner, run by a second kernel with every lane busy).  Same draws, same moves, same
+  // winner as the exact playout; only the move count differs.
+  static constexpr bool kFillable = true;
+  static constexpr int kFillWords = 4;
+  BSG_HD static u32 step_fill(State& s, u32 r, const Tables& tab, int& action) {
+    const u32 n = s.left;
+    const u32 k = fastmod(r, n, tab.modM[n & 127]);
+    const int cell = select_empty(s, k, tab);
+    action = cell;
+    // a lane whose board is full runs dead steps until its warp's group ends: they must not
+    // touch the board, which IS the result here
+    const u32 live = n ? 0xFFFFFFFFu : 0u;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const u32 mine = s.cO[w] | (tab.one[cell][w] & live);
+      s.cO[w] = s.oO[w];
+      s.oO[w] = mine;
+    }
+    s.mv ^= 1u;
+    s.left -= live & 1u;
+    return n;
+  }
+  BSG_HD static bool fill_done(const State& s) { return s.left == 0 || s.win != 0; }
+  // what the second kernel needs: black's stones (on a full board the rest is white's)
+  BSG_HD static void fill_store(const State& s, u32* out) {
+#pragma unroll
+    for (int w = 0; w < 4; ++w) out[w] = s.mv ? s.oO[w] : s.cO[w];
+  }
+  // 0: black connects row 0 to row N-1 through black stones; 1: it does not (white wins a
+  // full or finished board)
+  BSG_HD static int fill_winner(const u32* black) {
+    u32 reach[4], f[4], rest[4];
+    constexpr int last = N * (N - 1);
+    u32 any = 0;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      u32 row0 = 0;
+      if (32 * w < N) row0 = (N - 32 * w >= 32) ? 0xFFFFFFFFu : ((1u << (N - 32 * w)) - 1u);
+      f[w] = black[w] & row0;
+      reach[w] = f[w];
+      any |= f[w];
+    }
+    while (any) {
+      u32 d[4];
+#pragma unroll
+      for (int w = 0; w < 4; ++w) rest[w] = black[w] & ~reach[w];
+      dilate_within(f, rest, d);
+      any = 0;
+#pragma unroll
+      for (int w = 0; w < 4; ++w) { f[w] = d[w]; reach[w] |= d[w]; any |= d[w]; }
+    }
+    u32 hit = 0;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      u32 m = 0;   // cells last .. N*N-1 of word w
+      for (int b = 0; b < 32; ++b) { const int c = 32 * w + b; if (c >= last && c < N * N) m |= 1u << b; }
+      hit |= reach[w] & m;
+    }
+    return hit ? 0 : 1;
+  }
 };
 typedef HexT<11> Hex;
 
@@ -1447,7 +1512,8 @@ struct YT {
       const int cell = 32 * w + b;
       if (cell >= kGrid) break;
       const int x = cell % N, y = cell / N;
-      const bool in = kind == 0 ? on_board(x, y) : (kind == 1 ? x != 0 : x != N - 1);
+      const bool in = kind == 0 ? on_board(x, y) : (kind == 1 ? x != 0 : (kind == 2 ? x != N - 1 :
+                      (on_board(x, y) && (kind == 3 ? x == 0 : (kind == 4 ? y == 0 : x + y == N - 1)))));
       if (in) m |= 1u << b;
     }
     return m;
@@ -1459,6 +1525,12 @@ struct YT {
   BSG_HD static u32 board_word(int w) { constexpr u32 m[12] = BSG_Y_MASKS(0); return m[w]; }
   BSG_HD static u32 not_col0(int w) { constexpr u32 m[12] = BSG_Y_MASKS(1); return m[w]; }
   BSG_HD static u32 not_col_last(int w) { constexpr u32 m[12] = BSG_Y_MASKS(2); return m[w]; }
+  BSG_HD static u32 edge_word(int e, int w) {   // board cells on edge e (0: x = 0, 1: y = 0, 2: x + y = N - 1)
+    constexpr u32 m0[12] = BSG_Y_MASKS(3);
+    constexpr u32 m1[12] = BSG_Y_MASKS(4);
+    constexpr u32 m2[12] = BSG_Y_MASKS(5);
+    return e == 0 ? m0[w] : (e == 1 ? m1[w] : m2[w]);
+  }
 #undef BSG_Y_MASKS
 
   BSG_HD static void init(State& s) {
@@ -1681,6 +1753,66 @@ struct YT {
   BSG_HD static void mask_words(const State& s, u32* out) {
 #pragma unroll
     for (int w = 0; w < kMaskWords; ++w) out[w] = (w < W && !s.win) ? empty_word(s, w < W ? w : 0) : 0u;
+  }
+
+  // ---- value-only playouts (see HexT): a full y board has exactly one winner and stones
+  // never leave the board, so the first player to join the three edges is the one whose
+  // stones join them on the full board.
+  static constexpr bool kFillable = true;
+  static constexpr int kFillWords = PW;
+  BSG_HD static u32 step_fill(State& s, u32 r, const Tables& tab, int& action) {
+    const u32 n = s.left;
+    const u32 k = fastmod(r, n, tab.modM[n & 255u]);
+    const int cell = select_empty(s, k, tab);
+    action = cell;
+    const u32 q = s.mv ? 0xFFFFFFFFu : 0u;
+    // (n = 0: a dead step of a lane whose board is full must not touch the board)
+    const u32 cw = (u32)cell >> 5, cb = n ? 1u << (cell & 31) : 0u;
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+      const u32 m = (u32)w == cw ? cb : 0u;
+      s.A[w] |= m;
+      s.P[w] |= m & q;
+    }
+    s.mv ^= 1u;
+    s.left -= n ? 1u : 0u;
+    return n;
+  }
+  BSG_HD static bool fill_done(const State& s) { return s.left == 0 || s.win != 0; }
+  BSG_HD static void fill_store(const State& s, u32* out) {   // player 0's stones
+#pragma unroll
+    for (int w = 0; w < PW; ++w) out[w] = w < W ? (s.A[w] & ~s.P[w]) : 0u;
+  }
+  // stones of `set` connected to `seed` (seed within set)
+  BSG_HD static void flood(const u32* set, u32* seed_reach) {
+    u32 f[W], rest[W], d[W];
+    u32 any = 0;
+#pragma unroll
+    for (int w = 0; w < W; ++w) { f[w] = seed_reach[w]; any |= f[w]; }
+    while (any) {
+#pragma unroll
+      for (int w = 0; w < W; ++w) rest[w] = set[w] & ~seed_reach[w];
+      dilate_within(f, rest, d);
+      any = 0;
+#pragma unroll
+      for (int w = 0; w < W; ++w) { f[w] = d[w]; seed_reach[w] |= d[w]; any |= d[w]; }
+    }
+  }
+  // 0: a group of player 0 touches all three edges; 1: none does (player 1 wins a full or
+  // finished board).  Groups touching edge 0, of those the groups touching edge 1, of those
+  // any stone on edge 2.
+  BSG_HD static int fill_winner(const u32* p0) {
+    u32 r0[W], r01[W];
+#pragma unroll
+    for (int w = 0; w < W; ++w) r0[w] = p0[w] & edge_word(0, w);
+    flood(p0, r0);
+#pragma unroll
+    for (int w = 0; w < W; ++w) r01[w] = r0[w] & edge_word(1, w);
+    flood(r0, r01);
+    u32 hit = 0;
+#pragma unroll
+    for (int w = 0; w < W; ++w) hit |= r01[w] & edge_word(2, w);
+    return hit ? 0 : 1;
   }
 };
 typedef YT<19> Y;

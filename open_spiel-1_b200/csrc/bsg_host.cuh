@@ -6,6 +6,7 @@
 #include <string.h>
 
 #include <string>
+#include <type_traits>
 
 #include "../../include/bsg.h"
 #include "bsg_games.cuh"
@@ -144,6 +145,34 @@ struct StepOp {
     if (action) *action = a;
     G::store(s, p, cap, i);
     return BSG_OK;
+  }
+};
+template <class G, class = void> struct host_fillable : std::false_type {};
+template <class G> struct host_fillable<G, std::enable_if_t<G::kFillable>> : std::true_type {};
+struct FillOp {
+  const void* p; int64_t cap, i; uint64_t seed, playout; int* ret0; int* moves;
+  template <class G> int operator()() const {
+    if constexpr (host_fillable<G>::value) {
+      typename G::State s;
+      G::load(s, p, cap, i);
+      PhiloxKeys ks;
+      philox_schedule(seed, ks);
+      int t = 0;
+      while (!G::fill_done(s)) {
+        u32 rr[4];
+        philox4x32_10((u32)playout, (u32)(playout >> 32), (u32)t >> 2, 0u, ks, rr);
+        int a = -1;
+        G::step_fill(s, rr[t & 3], TablesOf<G>::get(), a);
+        ++t;
+      }
+      u32 board[G::kFillWords];
+      G::fill_store(s, board);
+      if (ret0) *ret0 = G::fill_winner(board) == 0 ? 1 : -1;
+      if (moves) *moves = t;
+      return BSG_OK;
+    } else {
+      return BSG_ERR_BAD_ARG;
+    }
   }
 };
 struct ObsOp {

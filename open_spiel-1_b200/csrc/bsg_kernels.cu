@@ -42,6 +42,8 @@ struct PlayoutArgs {
   bsg_playout_io io;
   uint32_t* work_counter;  // zeroed before the launch; warps draw chunks of playouts from it
   uint32_t out_flags;  // kOut* bits: which optional per-playout outputs of io are present
+  uint32_t* fill_boards;  // value-only launches: kFillWords words per playout for fill_resolve_kernel
+  uint64_t fill_base;     // host path: this launch parks its boards from playout slot fill_base on
 };
 enum : uint32_t { kOutRet = 1, kOutLength = 2, kOutTerminal = 4, kOutRootSums = 8 };
 inline uint32_t out_flags_of(const bsg_playout_io& io) {
@@ -53,9 +55,32 @@ inline uint32_t out_flags_of(const bsg_playout_io& io) {
 template <class G, class = void> struct min_blocks : std::integral_constant<int, 1> {};
 template <class G> struct min_blocks<G, std::enable_if_t<(G::kMinBlocks > 1)>> : std::integral_constant<int, G::kMinBlocks> {};
 
-template <class G, bool kFull, bool kBase>
-__global__ void __launch_bounds__(kThreads, kFull ? 1 : min_blocks<G>::value)
+// Indirection so that the kernel body only names the fill functions of a game that has them.
+template <class G, bool kOn> struct fill_words : std::integral_constant<int, 4> {};
+template <class G> struct fill_words<G, true> : std::integral_constant<int, G::kFillWords> {};
+template <class G, bool kOn> struct fill_ops {
+  BSG_HD static bool done(const typename G::State&) { return true; }
+  BSG_HD static void store(const typename G::State&, u32*) {}
+  BSG_HD static u32 step(typename G::State&, u32, const typename G::Tables&, int&) { return 1u; }
+};
+template <class G> struct fill_ops<G, true> {
+  BSG_HD static bool done(const typename G::State& s) { return G::fill_done(s); }
+  BSG_HD static void store(const typename G::State& s, u32* out) { G::fill_store(s, out); }
+  BSG_HD static u32 step(typename G::State& s, u32 r, const typename G::Tables& t, int& a) { return G::step_fill(s, r, t, a); }
+};
+
+// Games with value-only playouts (bsg_playout_io.value_only; see HexT).
+template <class G, class = void> struct fillable : std::false_type {};
+template <class G> struct fillable<G, std::enable_if_t<G::kFillable>> : std::true_type {};
+
+// kFill: value-only launch of a fillable game — the lanes play plain stones until the board is
+// full (no labels, no flood, no waiting) and park the board for fill_resolve_kernel, which
+// reads the winner off it and publishes ret0 / per-root sums / totals[2].
+template <class G, bool kFull, bool kBase, bool kFill = false>
+__global__ void __launch_bounds__(kThreads, kFull ? 1 : (kFill ? 4 : min_blocks<G>::value))
 playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab) {
+  static_assert(!kFill || (!kFull && !kBase), "value-only playouts are a lean launch");
+  constexpr bool kAsync = G::kAsync && !kFill;
   __shared__ __align__(16) typename G::Tables tab;
   {
     const u32* src = reinterpret_cast<const u32*>(gtab);
@@ -105,16 +130,25 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
     }
     if (live == 0) {
       if (have) {  // publish the finished playout
+        if constexpr (kFill) {   // park the board; the winner is read off it by the next kernel
+          u32 bw[fill_words<G, kFill>::value];
+          fill_ops<G, kFill>::store(s, bw);
+          uint4* dst = reinterpret_cast<uint4*>(a.fill_boards) + (size_t)lid * (fill_words<G, kFill>::value / 4);
+#pragma unroll
+          for (int q4 = 0; q4 < fill_words<G, kFill>::value / 4; ++q4)
+            dst[q4] = make_uint4(bw[4 * q4], bw[4 * q4 + 1], bw[4 * q4 + 2], bw[4 * q4 + 3]);
+        }
         int ret = (fin_term & fin_win) ? (int)(((root_mv ^ t) & 1u) << 1) - 1 : 0;
+        if constexpr (kFill) ret = 0;
         if constexpr (G::kMoverCanLose) {
           if (fin_term & fin_lose) ret = 1 - (int)(((root_mv ^ t) & 1u) << 1);
         }
-        if (out & kOutRet) a.io.ret0[lid] = (int8_t)ret;
+        if (!kFill && (out & kOutRet)) a.io.ret0[lid] = (int8_t)ret;
         if (out & kOutLength) a.io.length[lid] = (uint8_t)t;
         if (out & kOutTerminal) a.io.terminal[lid] = (uint8_t)fin_term;
         if (out & kOutRootSums) {
           u32 root = a.rollouts == 1 ? lid : lid / a.rollouts;
-          if (a.io.root_sum_ret0 && ret != 0) atomicAdd(a.io.root_sum_ret0 + root, ret);
+          if (!kFill && a.io.root_sum_ret0 && ret != 0) atomicAdd(a.io.root_sum_ret0 + root, ret);
           if (a.io.root_sum_steps) atomicAdd(a.io.root_sum_steps + root, (int)t);
         }
         my_steps += t;
@@ -143,7 +177,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
           if (a.io.step_limit) limit = min(limit, (u32)a.io.step_limit[lid]);
           prev = s;
         }
-        const bool term = G::terminal(s) || (kBase && skip);
+        const bool term = (kFill ? fill_ops<G, kFill>::done(s) : G::terminal(s)) || (kBase && skip);
         live = (!term && (!kFull || limit > 0)) ? 1u : 0u;
         fin_term = (kFull && !term) ? 0u : 1u;   // a lean playout always runs to a terminal state
         fin_win = G::won(s) ? 1u : 0u;
@@ -165,7 +199,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
 
     const unsigned long long pid = (kBase ? pid0 : a.first_playout) + lid;
     u32 rr[4];
-    if constexpr (!G::kAsync) {
+    if constexpr (!kAsync) {
       philox4x32_10((u32)pid, (u32)(pid >> 32), t >> 2, 0u, a.keys, rr);
     } else {
       // A lane of an asynchronous game does not move in every iteration, so the lanes of a warp
@@ -183,7 +217,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       u32 r, can = live;   // can: this lane makes a move in this iteration
-      if constexpr (!G::kAsync) {
+      if constexpr (!kAsync) {
         r = rr[j];
       } else {
         G::ring(s);
@@ -204,9 +238,11 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
       int action = 0;
       u32 nlegal = 1;
       u32 made = 1;   // kLazyEnd: 0 in the iteration that only finds the game over
-      if constexpr (G::kLazyEnd && !kFull) {
+      if constexpr (kFill) {
+        nlegal = fill_ops<G, kFill>::step(s, r, tab, action);
+      } else if constexpr (G::kLazyEnd && !kFull) {
         nlegal = G::step_lazy(s, r, tab, action, made);
-      } else if constexpr (!G::kAsync) {
+      } else if constexpr (!kAsync) {
         nlegal = G::step(s, r, tab, action);   // finished lanes run dead steps: no divergence
       } else {
         if (can) nlegal = G::step(s, r, tab, action);
@@ -231,8 +267,8 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
       } else {
         // lean bookkeeping: t counts the moves of the live playout and freezes when it ends;
         // fin_win was cleared at the claim and can only be set by the (single) ending move
-        const u32 term = G::terminal(s) ? 1u : 0u;
-        const u32 won = G::won(s) ? 1u : 0u;
+        const u32 term = (kFill ? fill_ops<G, kFill>::done(s) : G::terminal(s)) ? 1u : 0u;
+        const u32 won = (!kFill && G::won(s)) ? 1u : 0u;
         fin_win |= can & won;
         if constexpr (G::kMoverCanLose) fin_lose |= can & (G::lost(s) ? 1u : 0u);
         if constexpr (G::kLazyEnd) t += can & made; else t += can;
@@ -257,6 +293,35 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
       atomicAdd((unsigned long long*)a.io.totals + 2, (unsigned long long)(long long)rt);
       if (sk) atomicAdd((unsigned long long*)a.io.totals + 3, (unsigned long long)sk);
     }
+  }
+}
+
+
+// Second kernel of a value-only launch: one thread per parked board reads the winner off it
+// (G::fill_winner: one or two floods, every lane busy from the first ring) and publishes what
+// playout_kernel<.., kFill> could not: ret0, the per-root return sums and totals[2].
+template <class G>
+__global__ void __launch_bounds__(kThreads)
+fill_resolve_kernel(const PlayoutArgs a) {
+  int my_ret = 0;
+  for (u32 p = blockIdx.x * kThreads + threadIdx.x; p < a.n_playouts; p += gridDim.x * kThreads) {
+    u32 bw[G::kFillWords];
+    const uint4* src = reinterpret_cast<const uint4*>(a.fill_boards) + (size_t)p * (G::kFillWords / 4);
+#pragma unroll
+    for (int q4 = 0; q4 < G::kFillWords / 4; ++q4) {
+      const uint4 v = src[q4];
+      bw[4 * q4] = v.x; bw[4 * q4 + 1] = v.y; bw[4 * q4 + 2] = v.z; bw[4 * q4 + 3] = v.w;
+    }
+    const int ret = G::fill_winner(bw) == 0 ? 1 : -1;
+    if (a.io.ret0) a.io.ret0[p] = (int8_t)ret;
+    if (a.io.root_sum_ret0) atomicAdd(a.io.root_sum_ret0 + (a.rollouts == 1 ? p : p / a.rollouts), ret);
+    my_ret += ret;
+  }
+  if (a.io.totals) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) my_ret += __shfl_xor_sync(0xFFFFFFFFu, my_ret, o);
+    if ((threadIdx.x & 31) == 0 && my_ret != 0)
+      atomicAdd((unsigned long long*)a.io.totals + 2, (unsigned long long)(long long)my_ret);
   }
 }
 
@@ -414,6 +479,8 @@ struct bsg_engine {
   // scratch for the *_host wrappers
   void* d_roots = nullptr; size_t d_roots_bytes = 0;
   void* d_out = nullptr; size_t d_out_bytes = 0;
+  void* d_fill = nullptr; size_t d_fill_bytes = 0;   // parked boards of value-only launches
+  int value_only = 0;                                // bsg_engine_set_value_only: the *_host playouts
   void* h_pinned = nullptr; size_t h_pinned_bytes = 0;
   uint64_t* d_totals = nullptr;
   uint32_t* d_work = nullptr;          // ring of per-launch work counters (playout_kernel)
@@ -446,6 +513,12 @@ int ensure(bsg_engine* e, void** p, size_t* have, size_t need, bool pinned) {
   *have = cap;
   return BSG_OK;
 }
+
+struct FillWordsOp {
+  template <class G> int operator()() const {
+    if constexpr (fillable<G>::value) return G::kFillWords; else return 0;
+  }
+};
 
 struct FactOp {
   int which;
@@ -503,15 +576,15 @@ __global__ void forest_install_kernel(ForestView F, const int64_t* base, const i
   if (v < F.n_trees) forest_install_root(F, v, base, summed);
 }
 
-template <class G, bool kFull, bool kBase = false>
+template <class G, bool kFull, bool kBase = false, bool kFill = false>
 int launch_playouts(bsg_engine* e, const PlayoutArgs& a, cudaStream_t st) {
   static int blocks_per_sm = 0;
   if (blocks_per_sm == 0) {
     int b = 0;
     // all of the L1/shared array as shared memory: the tables of every resident CTA must fit
-    BSG_CUDA(e, cudaFuncSetAttribute(playout_kernel<G, kFull, kBase>, cudaFuncAttributePreferredSharedMemoryCarveout,
+    BSG_CUDA(e, cudaFuncSetAttribute(playout_kernel<G, kFull, kBase, kFill>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                      cudaSharedmemCarveoutMaxShared));
-    BSG_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, playout_kernel<G, kFull, kBase>, kThreads, 0));
+    BSG_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, playout_kernel<G, kFull, kBase, kFill>, kThreads, 0));
     blocks_per_sm = b > 0 ? b : 1;
   }
   int64_t max_grid = (int64_t)e->sm_count * blocks_per_sm;
@@ -523,9 +596,32 @@ int launch_playouts(bsg_engine* e, const PlayoutArgs& a, cudaStream_t st) {
   // work counter of this launch: next slot of the engine's ring, zeroed in stream order
   b.work_counter = e->d_work + (e->work_slot++ % kWorkSlots);
   BSG_CUDA(e, cudaMemsetAsync(b.work_counter, 0, sizeof(uint32_t), st));
-  playout_kernel<G, kFull, kBase><<<grid, kThreads, 0, st>>>(b, (const typename G::Tables*)e->tables_dev);
+  if constexpr (kFill) {
+    // (the chunked host path sized the buffer for the whole call, so this does not reallocate
+    // under a chunk that is still running)
+    int rc = ensure(e, &e->d_fill, &e->d_fill_bytes, (size_t)(a.fill_base + a.n_playouts) * G::kFillWords * 4, false);
+    if (rc != BSG_OK) return rc;
+    b.fill_boards = (uint32_t*)e->d_fill + (size_t)a.fill_base * G::kFillWords;
+  }
+  playout_kernel<G, kFull, kBase, kFill><<<grid, kThreads, 0, st>>>(b, (const typename G::Tables*)e->tables_dev);
   BSG_CUDA(e, cudaGetLastError());
+  if constexpr (kFill) {
+    int rgrid = (int)(need < (int64_t)e->sm_count * 8 ? need : (int64_t)e->sm_count * 8);
+    fill_resolve_kernel<G><<<rgrid < 1 ? 1 : rgrid, kThreads, 0, st>>>(b);
+    BSG_CUDA(e, cudaGetLastError());
+  }
   return BSG_OK;
+}
+
+template <class G>
+int launch_value_only(bsg_engine* e, const PlayoutArgs& a, cudaStream_t st, bool full) {
+  if constexpr (fillable<G>::value) {
+    if (full || a.io.root_playout_base)
+      return fail(e, BSG_ERR_BAD_ARG, "value_only excludes step limits, r_table, action / state logs, final states and root_playout_base");
+    return launch_playouts<G, false, false, true>(e, a, st);
+  } else {
+    return fail(e, BSG_ERR_BAD_ARG, "value_only needs a game whose full board has exactly one winner (hex, y)");
+  }
 }
 
 struct PlayoutOp {
@@ -533,6 +629,7 @@ struct PlayoutOp {
   template <class G> int operator()() const {
     const bsg_playout_io& io = a.io;
     bool full = io.max_steps > 0 || io.step_limit || io.r_table || io.actions || io.final_states || io.state_log;
+    if (io.value_only) return launch_value_only<G>(e, a, st, full);
     if (io.root_playout_base)
       return full ? launch_playouts<G, true, true>(e, a, st) : launch_playouts<G, false, true>(e, a, st);
     return full ? launch_playouts<G, true>(e, a, st) : launch_playouts<G, false>(e, a, st);
@@ -658,6 +755,11 @@ int bsg_host_replay_step(int game, void* p, int64_t cap, int64_t i, uint32_t r, 
   if (!p || i < 0 || i >= cap) return BSG_ERR_BAD_ARG;
   return dispatch_game(game, StepOp{p, cap, i, r, action});
 }
+int bsg_host_fill_playout(int game, const void* p, int64_t cap, int64_t i, uint64_t seed, uint64_t playout,
+                          int* ret0_out, int* moves_out) {
+  if (!p || i < 0 || i >= cap) return BSG_ERR_BAD_ARG;
+  return dispatch_game(game, FillOp{p, cap, i, seed, playout, ret0_out, moves_out});
+}
 int bsg_host_to_string(int game, const void* p, int64_t cap, int64_t i, char* buf, int capacity) {
   if (!p || !buf || i < 0 || i >= cap || capacity < 1) return BSG_ERR_BAD_ARG;
   return dispatch_game(game, ToStringOp{p, cap, i, 0, buf, capacity});
@@ -709,6 +811,7 @@ void bsg_destroy(bsg_engine* e) {
   if (e->tables_dev) cudaFree(e->tables_dev);
   if (e->d_roots) cudaFree(e->d_roots);
   if (e->d_out) cudaFree(e->d_out);
+  if (e->d_fill) cudaFree(e->d_fill);
   if (e->h_pinned) cudaFreeHost(e->h_pinned);
   if (e->d_totals) cudaFree(e->d_totals);
   if (e->d_work) cudaFree(e->d_work);
@@ -722,6 +825,13 @@ const char* bsg_last_error(bsg_engine* e) { return e ? e->err.c_str() : "null en
 int bsg_engine_game(const bsg_engine* e) { return e ? e->game : BSG_ERR_BAD_ARG; }
 int bsg_engine_device(const bsg_engine* e) { return e ? e->device : BSG_ERR_BAD_ARG; }
 int bsg_engine_sm_count(const bsg_engine* e) { return e ? e->sm_count : BSG_ERR_BAD_ARG; }
+int bsg_engine_set_value_only(bsg_engine* e, int on) {
+  if (!e) return BSG_ERR_BAD_ARG;
+  if (on && dispatch_device_game(e->game, FillWordsOp{}) <= 0)
+    return fail(e, BSG_ERR_BAD_ARG, "value_only needs a game whose full board has exactly one winner (hex, y)");
+  e->value_only = on ? 1 : 0;
+  return BSG_OK;
+}
 
 int bsg_playouts(bsg_engine* e, const void* roots, int64_t n_roots, int32_t rollouts, uint64_t seed,
                  uint64_t first_playout, const bsg_playout_io* io, void* stream) {
@@ -802,6 +912,10 @@ int bsg_playouts_host(bsg_engine* e, const void* roots_host, int64_t n_roots, in
   n_chunks = n_chunks < 1 ? 1 : (n_chunks > 16 ? 16 : n_chunks);
   PhiloxKeys keys;
   philox_schedule(seed, keys);
+  if (e->value_only) {
+    const int words = dispatch_device_game(e->game, FillWordsOp{});
+    if ((rc = ensure(e, &e->d_fill, &e->d_fill_bytes, (size_t)n_roots * rollouts * words * 4, false)) != BSG_OK) return rc;
+  }
   for (int64_t c = 0; c < n_chunks; ++c) {
     const int64_t lo = n_roots * c / n_chunks, hi = n_roots * (c + 1) / n_chunks;
     if (hi <= lo) continue;
@@ -823,6 +937,8 @@ int bsg_playouts_host(bsg_engine* e, const void* roots_host, int64_t n_roots, in
     a.io.totals = e->d_totals;
     a.io.root_sum_ret0 = d_ret ? d_ret + lo : nullptr;
     a.io.root_sum_steps = d_steps ? d_steps + lo : nullptr;
+    a.io.value_only = e->value_only;
+    a.fill_base = (uint64_t)lo * (uint64_t)rollouts;
     if ((rc = dispatch_device_game(e->game, PlayoutOp{e, a, st})) != BSG_OK) return rc;
   }
   BSG_CUDA(e, cudaEventRecord(e->ev_b, sb));

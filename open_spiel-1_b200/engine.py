@@ -139,12 +139,17 @@ class Engine:
   def _p(t):
     return None if t is None else C.vp(t.data_ptr())
 
+  def set_value_only(self, on=True):
+    """hex / y: the host-buffer playouts (playouts_host, hence GpuRolloutEvaluator) fill the
+    board and read the winner off it — same returns, about a third of the instructions."""
+    C.check(C.lib.bsg_engine_set_value_only(self._h, 1 if on else 0), self._h)
+
   # ---- the hot path
   def playouts(self, roots, n_roots, rollouts=1, seed=0, first_playout=0, *, ret0=None,
                length=None, terminal=None, actions=None, root_sum_ret0=None,
                root_sum_steps=None, totals=None, max_steps=0, step_limit=None, r_table=None,
                final_states=None, final_before_terminal=False, state_log=None,
-               state_log_off=None, root_playout_base=None, stream=None):
+               state_log_off=None, root_playout_base=None, value_only=False, stream=None):
     """Launches n_roots * rollouts random playouts (bsg_playouts).  All tensors are device
     tensors owned by the caller; see include/bsg.h for their meaning.  Asynchronous."""
     io = C.PlayoutIO()
@@ -166,6 +171,7 @@ class Engine:
     io.state_log_cap = int(state_log.numel() // self.state_bytes) if state_log is not None else 0
     io.state_log_off = self._p(state_log_off)
     io.root_playout_base = self._p(root_playout_base)
+    io.value_only = 1 if value_only else 0   # hex / y: fill the board, read the winner off it
     C.check(C.lib.bsg_playouts(self._h, self._p(roots), int(n_roots), int(rollouts),
                                int(seed) & (2**64 - 1), int(first_playout), ctypes.byref(io),
                                self._stream_ptr(stream)), self._h)

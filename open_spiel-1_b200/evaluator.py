@@ -44,13 +44,18 @@ class GpuRolloutEvaluator(Evaluator):
     seed: Philox key.  Playout ids advance with every call, so results are reproducible for a
       given (seed, call sequence) and every playout is replayable by the oracle.
     device: CUDA device index.
+    value_only: hex / y only — play plain stones until the board is full and read the winner
+      off it (include/bsg.h, bsg_playout_io.value_only): evaluate() returns exactly the same
+      values from the same playout ids; only `total_steps` counts moves to the full board.
   """
 
-  def __init__(self, game, n_rollouts=1, seed=0, device=0):
+  def __init__(self, game, n_rollouts=1, seed=0, device=0, value_only=False):
     if isinstance(game, _engine.Engine):
       self.engine = game
     else:
       self.engine = _engine.Engine(game, device)
+    if value_only:
+      self.engine.set_value_only(True)
     self.n_rollouts = int(n_rollouts)
     if self.n_rollouts < 1:
       raise ValueError("n_rollouts must be >= 1")

@@ -324,3 +324,34 @@ def test_tournament_from_gpu_roots(bsg):
     mcts_bot.close()
   assert score > 1.2          # wins the large majority from either seat
   eng.close()
+
+
+@pytest.mark.parametrize("game", ["hex", "y"])
+def test_value_only_evaluator_returns_the_same_values(bsg, game):
+  """GpuRolloutEvaluator(value_only=True): evaluate / evaluate_batch give exactly the values of
+  the exact evaluator for the same playout ids (chunked host path included); games without the
+  property refuse."""
+  g = bsg.load_game(game)
+  rng = np.random.RandomState(4)
+  states = []
+  for i in range(40):
+    s = g.new_initial_state()
+    for _ in range(3 * i):
+      if s.is_terminal():
+        break
+      la = s.legal_actions()
+      s.apply_action(la[rng.randint(len(la))])
+    if not s.is_terminal():
+      states.append(s)
+  ev_a = bsg.GpuRolloutEvaluator(game, n_rollouts=64, seed=5)
+  ev_b = bsg.GpuRolloutEvaluator(game, n_rollouts=64, seed=5, value_only=True)
+  for s in states[:6]:
+    assert np.array_equal(ev_a.evaluate(s), ev_b.evaluate(s))
+  assert np.array_equal(ev_a.evaluate_batch(states), ev_b.evaluate_batch(states))
+  big = states * 3000                       # > 2 MiB of roots: several chunks on two streams
+  ev_a.n_rollouts = ev_b.n_rollouts = 1
+  assert np.array_equal(ev_a.evaluate_batch(big), ev_b.evaluate_batch(big))
+  assert ev_b.total_steps >= ev_a.total_steps
+  ev_a.engine.close(); ev_b.engine.close()
+  with pytest.raises(RuntimeError):
+    bsg.GpuRolloutEvaluator("breakthrough", n_rollouts=4, value_only=True)

@@ -381,3 +381,57 @@ def test_device_replay_buffer_takes_trajectories(torch):
   with pytest.raises(ValueError):
     small.sample(101)
   eng.close()
+
+
+@pytest.mark.parametrize("game,n,R", [("hex", 12500, 8), ("y", 6250, 16)])
+def test_value_only_playouts_return_the_exact_results(game, n, R, torch):
+  """bsg_playout_io.value_only (hex, y): plain stones to a full board and one reading of the
+  winner give, playout for playout, the ret0 / per-root sums / totals[2] of the exact launch
+  (which the tests above tie to the oracle); the moves are the empty cells of the root.
+  Terminal roots are in the batch; other games refuse the flag."""
+  import open_spiel_1_b200 as bsg
+  eng = _engine(game)
+  dev = eng.torch_device
+  states, hist = _roots(eng, game, n, seed=99)
+  # make the last roots terminal ones
+  oracle = Oracle()
+  k = 64
+  for i in range(k):
+    a, _, _ = oracle.replay(game, [], seed=8, playout=i)
+    hist[n - 1 - i] = a
+  states = eng.to_device(bsg.pack_histories(game, hist))
+  outs = []
+  for vo in (False, True):
+    ret0 = torch.zeros(n * R, dtype=torch.int8, device=dev)
+    length = torch.zeros(n * R, dtype=torch.uint8, device=dev)
+    term = torch.zeros(n * R, dtype=torch.uint8, device=dev)
+    totals = torch.zeros(4, dtype=torch.int64, device=dev)
+    rs = torch.zeros(n, dtype=torch.int32, device=dev)
+    rl = torch.zeros(n, dtype=torch.int32, device=dev)
+    eng.playouts(states, n, R, seed=31, first_playout=1 << 33, ret0=ret0, length=length, terminal=term,
+                 totals=totals, root_sum_ret0=rs, root_sum_steps=rl, value_only=vo)
+    torch.cuda.synchronize()
+    outs.append((ret0, length, term, totals.cpu().numpy(), rs, rl))
+  (r_a, l_a, t_a, tot_a, rs_a, rl_a), (r_b, l_b, t_b, tot_b, rs_b, rl_b) = outs
+  assert torch.equal(r_a, r_b) and torch.equal(rs_a, rs_b)
+  assert bool((r_b != 0).all()) and bool(t_b.all())
+  assert tot_a[0] == tot_b[0] == n * R and tot_a[2] == tot_b[2] and tot_b[3] == 0
+  cells = {"hex": 121, "y": 190}[game]
+  empties = np.array([0 if i >= n - k else cells - len(h) for i, h in enumerate(hist)], np.int64)
+  assert np.array_equal(l_b.cpu().numpy().reshape(n, R).astype(np.int64), np.repeat(empties[:, None], R, 1))
+  assert np.array_equal(rl_b.cpu().numpy().astype(np.int64), empties * R) and tot_b[1] == int(empties.sum()) * R
+  assert bool((l_a.to(torch.int64) <= l_b.to(torch.int64)).all())
+  # totals-only launch (what the evaluator asks for)
+  totals = torch.zeros(4, dtype=torch.int64, device=dev)
+  eng.playouts(states, n, R, seed=31, first_playout=1 << 33, totals=totals, value_only=True)
+  torch.cuda.synchronize()
+  assert np.array_equal(totals.cpu().numpy(), tot_b)
+  eng.close()
+  e2 = _engine("connect_four")
+  root = e2.to_device(bsg.pack_histories("connect_four", [[]]))
+  with pytest.raises(RuntimeError):
+    e2.playouts(root, 1, 4, totals=torch.zeros(4, dtype=torch.int64, device=dev), value_only=True)
+  with pytest.raises(RuntimeError):
+    eng2 = _engine(game)
+    eng2.playouts(states, n, 1, totals=torch.zeros(4, dtype=torch.int64, device=dev), max_steps=3, value_only=True)
+  e2.close()

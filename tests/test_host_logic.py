@@ -148,3 +148,31 @@ def test_connect_four_known_answers():
   assert not s.is_terminal()
   s.apply_action(k["connect_four_fast_loss"]["history"][-1])
   assert s.is_terminal() and s.returns() == [1.0, -1.0] and s.current_player() == -4
+
+
+@pytest.mark.parametrize("name,oname,bs,n", [("hex", "hex", 11, 120), ("hex(board_size=5)", "hex", 5, 300),
+                                             ("y", "y", 11, 60), ("y(board_size=9)", "y", 9, 300)])
+def test_value_only_fill_gives_the_exact_playouts_winner(oracle, name, oname, bs, n):
+  """bsg_playout_io.value_only: the kernels' step_fill + fill_winner (plain stones to a full
+  board, then one reading of the winner) against the oracle's exact replay of the same playout
+  id from the same mid-game root: same winner; the moves are the empty cells of the root."""
+  gid = bsg.game_id(name)
+  cells = {"hex": bs * bs, "y": (19 if bs == 11 else bs) * ((19 if bs == 11 else bs) + 1) // 2}[oname]
+  for playout in range(n):
+    root, _, _ = oracle.replay(oname, [], seed=5, playout=playout, max_steps=playout % 40, board_size=bs)
+    if oracle.state_dump(oname, root, board_size=bs)["terminal"]:
+      root = root[:-1]
+    packed = bsg.pack_histories(name, [root])
+    ret0, moves = ctypes.c_int(), ctypes.c_int()
+    C.check(C.lib.bsg_host_fill_playout(gid, packed.ctypes.data, 1, 0, 77, playout,
+                                        ctypes.byref(ret0), ctypes.byref(moves)))
+    _, o_term, o_ret = oracle.replay(oname, root, seed=77, playout=playout, board_size=bs)
+    assert o_term == 1 and ret0.value == o_ret, (name, playout)
+    assert moves.value == cells - len(root)
+  # a finished root: no move is made, the winner is the root's
+  full, _, o_ret = oracle.replay(oname, [], seed=3, playout=1, board_size=bs)
+  packed = bsg.pack_histories(name, [full])
+  C.check(C.lib.bsg_host_fill_playout(gid, packed.ctypes.data, 1, 0, 1, 1, ctypes.byref(ret0), ctypes.byref(moves)))
+  assert ret0.value == o_ret and moves.value == 0
+  with pytest.raises(RuntimeError):
+    C.check(C.lib.bsg_host_fill_playout(bsg.game_id("connect_four"), packed.ctypes.data, 1, 0, 1, 1, None, None))
