@@ -180,8 +180,7 @@ typedef struct bsg_playout_io {
    * identical to an exact launch (the side that connects first is the side connected at the
    * end); length, root_sum_steps and totals[1] count the moves to the full board instead of to
    * the win.  What RandomRolloutEvaluator::Evaluate (mcts.cc:42-71) needs is only the returns.
-   * Excludes max_steps / step_limit / r_table / actions / final_states / state_log /
-   * root_playout_base. */
+   * Excludes max_steps / step_limit / r_table / actions / final_states / state_log. */
   int32_t value_only;
 } bsg_playout_io;
 

@@ -79,7 +79,7 @@ template <class G> struct fillable<G, std::enable_if_t<G::kFillable>> : std::tru
 template <class G, bool kFull, bool kBase, bool kFill = false>
 __global__ void __launch_bounds__(kThreads, kFull ? 1 : (kFill ? 4 : min_blocks<G>::value))
 playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab) {
-  static_assert(!kFill || (!kFull && !kBase), "value-only playouts are a lean launch");
+  static_assert(!kFill || !kFull, "value-only playouts are a lean launch");
   constexpr bool kAsync = G::kAsync && !kFill;
   __shared__ __align__(16) typename G::Tables tab;
   {
@@ -312,9 +312,12 @@ fill_resolve_kernel(const PlayoutArgs a) {
       const uint4 v = src[q4];
       bw[4 * q4] = v.x; bw[4 * q4 + 1] = v.y; bw[4 * q4 + 2] = v.z; bw[4 * q4 + 3] = v.w;
     }
+    const u32 root = a.rollouts == 1 ? p : p / a.rollouts;
+    // a skipped root (root_playout_base = UINT64_MAX) parked nothing
+    if (a.io.root_playout_base && a.io.root_playout_base[a.root0 + root] == 0xFFFFFFFFFFFFFFFFull) continue;
     const int ret = G::fill_winner(bw) == 0 ? 1 : -1;
     if (a.io.ret0) a.io.ret0[p] = (int8_t)ret;
-    if (a.io.root_sum_ret0) atomicAdd(a.io.root_sum_ret0 + (a.rollouts == 1 ? p : p / a.rollouts), ret);
+    if (a.io.root_sum_ret0) atomicAdd(a.io.root_sum_ret0 + root, ret);
     my_ret += ret;
   }
   if (a.io.totals) {
@@ -616,9 +619,10 @@ int launch_playouts(bsg_engine* e, const PlayoutArgs& a, cudaStream_t st) {
 template <class G>
 int launch_value_only(bsg_engine* e, const PlayoutArgs& a, cudaStream_t st, bool full) {
   if constexpr (fillable<G>::value) {
-    if (full || a.io.root_playout_base)
-      return fail(e, BSG_ERR_BAD_ARG, "value_only excludes step limits, r_table, action / state logs, final states and root_playout_base");
-    return launch_playouts<G, false, false, true>(e, a, st);
+    if (full)
+      return fail(e, BSG_ERR_BAD_ARG, "value_only excludes step limits, r_table, action / state logs and final states");
+    return a.io.root_playout_base ? launch_playouts<G, false, true, true>(e, a, st)
+                                  : launch_playouts<G, false, false, true>(e, a, st);
   } else {
     return fail(e, BSG_ERR_BAD_ARG, "value_only needs a game whose full board has exactly one winner (hex, y)");
   }
@@ -1209,11 +1213,17 @@ struct ForestSearchOp {
       a.io.root_sum_ret0 = F.leaf_ret;
       a.io.totals = f->d_totals;
       a.io.root_playout_base = F.leaf_base;
-      int rc = launch_playouts<G, false, true>(e, a, st);
+      int rc;
+      if constexpr (fillable<G>::value) {   // bsg_engine_set_value_only: same leaf values, fewer instructions
+        a.io.value_only = e->value_only;
+        rc = e->value_only ? launch_playouts<G, false, true, true>(e, a, st) : launch_playouts<G, false, true>(e, a, st);
+      } else {
+        rc = launch_playouts<G, false, true>(e, a, st);
+      }
       if (rc != BSG_OK) return rc;
       forest_finish_kernel<G><<<grid, kForestThreads, 0, st>>>(F);
       f->rounds += 1;
-      f->launches += 3;
+      f->launches += 3 + (a.io.value_only ? 1 : 0);   // + fill_resolve_kernel
     }
     forest_expand_root_kernel<G><<<grid, kForestThreads, 0, st>>>(F);
     uint64_t tot[4];

@@ -98,3 +98,26 @@ def test_large_forest_accounts_for_every_simulation(bsg):
     assert table(forest.tree_root(v, 0), 32) == t0
   forest.close()
   eng.close()
+
+
+@pytest.mark.parametrize("game,history", [("hex", [60, 48]), ("y", [40, 41])])
+def test_forest_with_value_only_leaves_builds_the_same_trees(bsg, game, history):
+  """GpuRolloutEvaluator(value_only=True) behind the forest: the leaves are evaluated by the
+  value-only kernels (root_playout_base + value_only in one launch, skipped slots included) and
+  every root statistic equals the exact forest's."""
+  from open_spiel_1_b200.forest import ForestMCTS
+  g = bsg.load_game(game)
+  state = g.new_initial_state()
+  for a in history:
+    state.apply_action(a)
+  roots = []
+  for vo in (False, True):
+    eng = bsg.Engine(game, 0)
+    ev = bsg.GpuRolloutEvaluator(eng, n_rollouts=16, seed=21, value_only=vo)
+    forest = ForestMCTS(g, UCT_C, 600, ev, 4, sims_per_step=50, solve=True, seed=9, leaf_batch=4)
+    roots.append(table(forest.mcts_search(state), 16))
+    info = forest.info()
+    assert info["launches"] == (4 if vo else 3) * info["rounds"]
+    forest.close()
+    eng.close()
+  assert roots[0] == roots[1]
