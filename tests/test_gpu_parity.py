@@ -14,10 +14,10 @@ from oracle_lib import Oracle, Reference, reference_path
 pytestmark = pytest.mark.gpu
 
 GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y"]
-# replay-parity sizes: >= 1e5 playouts per game
-N_ROOTS = {"tic_tac_toe": 50000, "connect_four": 50000, "breakthrough": 25000, "hex": 12500,
-           "pentago": 50000, "othello": 25000, "y": 6250}
-ROLLOUTS = {"tic_tac_toe": 2, "connect_four": 2, "breakthrough": 4, "hex": 8, "pentago": 2, "othello": 4, "y": 16}
+# replay-parity sizes: >= 1e5 ROOTS per game, two rollouts per root where
+# the checker is cheap so that the rollouts > 1 indexing is in the same comparison
+N_ROOTS = {g: 100000 for g in GAMES}
+ROLLOUTS = {"tic_tac_toe": 2, "connect_four": 2, "breakthrough": 1, "hex": 1, "pentago": 2, "othello": 1, "y": 1}
 
 
 @pytest.fixture(scope="module")
@@ -115,7 +115,7 @@ def test_observations_and_masks_bit_exact(game, torch):
   """ObservationTensor planes and LegalActionsMask of 1e5 states vs the oracle."""
   oracle = Oracle()
   eng = _engine(game)
-  n = 100000 if game != "hex" else 30000
+  n = 100000
   states, hist = _roots(eng, game, n, seed=42)
   dev = eng.torch_device
   players = torch.from_numpy((np.arange(n) % 2).astype(np.uint8)).to(dev)
@@ -126,8 +126,7 @@ def test_observations_and_masks_bit_exact(game, torch):
   assert set(np.unique(obs).tolist()) <= {0.0, 1.0}
   cells = 190 if game == "y" else eng.obs_size // eng.obs_shape[0]   # y: the triangle of the 19 x 19 grid
   assert np.all(obs.sum(1) == cells)  # exactly one plane per board cell
-  step = 1 if game in ("tic_tac_toe", "connect_four") else 3
-  for i in range(0, n, step * 10):
+  for i in range(n):                      # every one of the 1e5 states against the oracle
     d = oracle.state_dump(game, hist[i], i % 2)
     assert np.array_equal(obs[i].astype(np.uint8), d["obs"]), i
     assert np.nonzero(mask[i])[0].tolist() == d["legal"], i
