@@ -1505,15 +1505,15 @@ struct YT {
       t.edge[cell] = (unsigned char)((x == 0 ? 1 : 0) | (y == 0 ? 2 : 0) | (x + y == N - 1 ? 4 : 0));
     }
   }
-  // Compile-time masks of word w: board cells, cells with x != 0, cells with x != N - 1.
+  // Compile-time masks of word w: board cells (kind 0), board cells on edge 0 / 1 / 2 (kinds 3 / 4 / 5).
   BSG_HDC static u32 word_mask(int w, int kind) {
     u32 m = 0;
     for (int b = 0; b < 32; ++b) {
       const int cell = 32 * w + b;
       if (cell >= kGrid) break;
       const int x = cell % N, y = cell / N;
-      const bool in = kind == 0 ? on_board(x, y) : (kind == 1 ? x != 0 : (kind == 2 ? x != N - 1 :
-                      (on_board(x, y) && (kind == 3 ? x == 0 : (kind == 4 ? y == 0 : x + y == N - 1)))));
+      const bool in = on_board(x, y) &&
+                      (kind == 0 || (kind == 3 ? x == 0 : (kind == 4 ? y == 0 : x + y == N - 1)));
       if (in) m |= 1u << b;
     }
     return m;
@@ -1523,8 +1523,6 @@ struct YT {
    word_mask(4, kind), word_mask(5, kind), word_mask(6, kind),  word_mask(7, kind),              \
    word_mask(8, kind), word_mask(9, kind), word_mask(10, kind), word_mask(11, kind)}
   BSG_HD static u32 board_word(int w) { constexpr u32 m[12] = BSG_Y_MASKS(0); return m[w]; }
-  BSG_HD static u32 not_col0(int w) { constexpr u32 m[12] = BSG_Y_MASKS(1); return m[w]; }
-  BSG_HD static u32 not_col_last(int w) { constexpr u32 m[12] = BSG_Y_MASKS(2); return m[w]; }
   BSG_HD static u32 edge_word(int e, int w) {   // board cells on edge e (0: x = 0, 1: y = 0, 2: x + y = N - 1)
     constexpr u32 m0[12] = BSG_Y_MASKS(3);
     constexpr u32 m1[12] = BSG_Y_MASKS(4);
