@@ -1474,8 +1474,8 @@ struct YT {
     u32 win;                   // the last move connected all three edges
     u32 last;                  // last move + 1 (0: none)
   };
-  // nb[cell]: neighbour mask in words 0..W-1; word PW-1... the cell's own edge set sits in
-  // edge[cell] (bit 0 x = 0, bit 1 y = 0, bit 2 x + y = N - 1).  sel8[b][k]: k-th set bit of b.
+  // nb[cell]: neighbour mask (words 0..W-1).  edge[cell]: the cell's own edge set (bit 0 x = 0,
+  // bit 1 y = 0, bit 2 x + y = N - 1).  sel8[b][k]: position of the k-th set bit of byte b.
   struct Tables {
     u32 nb[kGrid][PW];
     u32 modM[256];
