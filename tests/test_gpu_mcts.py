@@ -355,3 +355,22 @@ def test_value_only_evaluator_returns_the_same_values(bsg, game):
   ev_a.engine.close(); ev_b.engine.close()
   with pytest.raises(RuntimeError):
     bsg.GpuRolloutEvaluator("breakthrough", n_rollouts=4, value_only=True)
+
+
+def test_native_tree_over_a_value_only_engine_builds_the_same_tree(bsg):
+  """bsg_mcts_* evaluates its leaves through bsg_playouts_host, which honours
+  bsg_engine_set_value_only: same tree, visit for visit."""
+  g = bsg.load_game("hex")
+  state = g.new_initial_state()
+  for a in (60, 48, 61):
+    state.apply_action(a)
+  roots = []
+  for vo in (False, True):
+    eng = bsg.Engine("hex", 0)
+    if vo:
+      eng.set_value_only(True)
+    bot = bsg.NativeMCTSBot(g, UCT_C, 400, eng, n_rollouts=8, solve=True, seed=77, shuffle_seed=13, leaf_batch=8)
+    roots.append(_root_stats(bot.mcts_search(state)))
+    bot.close()
+    eng.close()
+  assert roots[0] == roots[1]
