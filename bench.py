@@ -192,7 +192,7 @@ def run_reference_arm(args):
       "impl": "reference", "metric": METRIC, "value": steps_s, "unit": "game-steps/s",
       "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
       "ms_per_step": 1e3 * float(np.mean([v[5] for v in vals])), "higher_is_better": True,
-      "scaling": "weak", "vs_baseline": None, "dtype": "int64 actions / u8 cells (CPU)",
+      "scaling": "weak", "vs_baseline": None, "dtype": "int64", "dtype_note": "int64 actions over enum cell arrays (the reference C++ State classes)",
       "data": "synthetic", "playouts_per_s": playouts_s,
       "config": {"workload": "connect_four: 16Mi playouts from synthetic mid-game roots "
                              "(bounded CPU sample)", "game": args.game,
@@ -305,7 +305,7 @@ def run_ours(args):
       "metric": METRIC, "value": value, "unit": "game-steps/s", "n_gpus": world,
       "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
       "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-      "dtype": "u64 bitboards / u32 (integer)", "data": "synthetic",
+      "dtype": "u64", "dtype_note": "u64 bitboards handled as u32 word pairs; integer only", "data": "synthetic",
       "playouts_per_s": playouts / (ms_max * 1e-3),
       "mean_steps_per_playout": steps / max(playouts, 1.0),
       "config": {"workload": "connect_four: %d independent random playouts per GPU per step from "
