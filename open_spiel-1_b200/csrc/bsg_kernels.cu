@@ -344,6 +344,12 @@ fill_resolve_kernel(const PlayoutArgs a) {
 //            two (or, for 7/9-action masks, more) states gathers across rows.
 // Algorithmic HBM bytes per state = output + packed state; nothing is re-read from HBM.
 // ---------------------------------------------------------------------------------------
+#ifndef BSG_OBS_TMA
+#define BSG_OBS_TMA 1
+#endif
+#ifndef BSG_OBS_TILE
+#define BSG_OBS_TILE 512   // uint4 per staged tile (8 KB); a multiple of kChunk
+#endif
 constexpr int kChunk = 256;  // states per CTA chunk (= threads); multiple of 32 keeps stores aligned
 
 template <int kBits, int kRow>
@@ -371,6 +377,17 @@ expand_kernel(const void* __restrict__ states, int64_t n, const uint8_t* __restr
   constexpr int kRow = (kWords + 1) | 1;            // + one zero word for the funnel read; odd
   constexpr int kPer = kMask ? 16 : 4;              // output elements per 16-byte store
   __shared__ u32 sm[kChunk * kRow];
+#if BSG_OBS_TMA
+  // Output staging for bulk (TMA) stores: three 8 KB tiles in a ring.  A tile is written with
+  // STS.128, made visible to the async proxy, and one thread hands it to the copy engine; the
+  // ring of three needs one barrier per tile (see the wait_group.read below).
+  constexpr int kTileVec = BSG_OBS_TILE;
+  constexpr bool kTma = kChunk * kRow * 4 + 3 * kTileVec * 16 <= 48 * 1024;
+  __shared__ __align__(128) uint4 stage[kTma ? 3 * kTileVec : 1];
+  int tsel = 0;
+#else
+  constexpr bool kTma = false;
+#endif
   const int64_t n_chunks = (n + kChunk - 1) / kChunk;
   for (int64_t c = blockIdx.x; c < n_chunks; c += gridDim.x) {
     const int64_t s0 = c * kChunk;
@@ -398,6 +415,48 @@ expand_kernel(const void* __restrict__ states, int64_t n, const uint8_t* __restr
     const int n16 = total / kPer;
     uint4* out16 = reinterpret_cast<uint4*>(reinterpret_cast<char*>(out_) +
                                             s0 * (int64_t)kBits * (kMask ? 1 : 4));
+#if BSG_OBS_TMA
+    if constexpr (kTma) {
+      const int ntiles = (n16 + kTileVec - 1) / kTileVec;
+      for (int t = 0; t < ntiles; ++t) {
+        uint4* sbuf = stage + tsel * kTileVec;
+#pragma unroll
+        for (int q = 0; q < kTileVec / kChunk; ++q) {
+          const int j = t * kTileVec + q * kChunk + threadIdx.x;
+          if (j < n16) {
+            const int e0 = j * kPer;
+            const int st = e0 / kBits, r = e0 - st * kBits;
+            u32 x = gather_bits<kBits, kRow>(sm, st, r, kPer, nst);
+            uint4 v;
+            if (kMask) {
+              v.x = ((x & 15u) * 0x00204081u) & 0x01010101u;
+              v.y = (((x >> 4) & 15u) * 0x00204081u) & 0x01010101u;
+              v.z = (((x >> 8) & 15u) * 0x00204081u) & 0x01010101u;
+              v.w = (((x >> 12) & 15u) * 0x00204081u) & 0x01010101u;
+            } else {
+              v.x = (x & 1u) * 0x3F800000u;
+              v.y = ((x >> 1) & 1u) * 0x3F800000u;
+              v.z = ((x >> 2) & 1u) * 0x3F800000u;
+              v.w = ((x >> 3) & 1u) * 0x3F800000u;
+            }
+            sbuf[q * kChunk + threadIdx.x] = v;
+          }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        if (threadIdx.x == 0) {
+          const int vecs = min(kTileVec, n16 - t * kTileVec);
+          asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                       :: "l"(out16 + (size_t)t * kTileVec), "r"((u32)__cvta_generic_to_shared(sbuf)), "r"(vecs * 16) : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          // the store issued one tile ago has been read out of shared memory: its buffer is
+          // the one the tile after next will write, two barriers from here
+          asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        }
+        tsel = tsel == 2 ? 0 : tsel + 1;
+      }
+    } else
+#endif
     for (int j = threadIdx.x; j < n16; j += kChunk) {
       const int e0 = j * kPer;
       const int st = e0 / kBits, r = e0 - st * kBits;
@@ -427,6 +486,9 @@ expand_kernel(const void* __restrict__ states, int64_t n, const uint8_t* __restr
     }
     __syncthreads();
   }
+#if BSG_OBS_TMA
+  if (kTma && threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+#endif
 }
 
 // ---------------------------------------------------------------------------------------
