@@ -367,6 +367,17 @@ __device__ __forceinline__ u32 gather_bits(const u32* __restrict__ sm, int st, i
   return x & ((1u << want) - 1u);
 }
 
+// Dynamic shared memory of expand_kernel: the staging ring + one bit-string row per state.
+template <class G, bool kMask> constexpr size_t expand_smem_bytes() {
+  constexpr int kWords = kMask ? G::kMaskWords : G::kObsWords;
+  constexpr int kRow = (kWords + 1) | 1;
+#if BSG_OBS_TMA
+  return (size_t)3 * BSG_OBS_TILE * 16 + (size_t)kChunk * kRow * 4;
+#else
+  return 0;
+#endif
+}
+
 // kMask = false: float32 observation planes; true: uint8 legal-action mask.
 template <class G, bool kMask>
 __global__ void __launch_bounds__(kChunk)
@@ -376,14 +387,21 @@ expand_kernel(const void* __restrict__ states, int64_t n, const uint8_t* __restr
   constexpr int kWords = kMask ? G::kMaskWords : G::kObsWords;
   constexpr int kRow = (kWords + 1) | 1;            // + one zero word for the funnel read; odd
   constexpr int kPer = kMask ? 16 : 4;              // output elements per 16-byte store
-  __shared__ u32 sm[kChunk * kRow];
 #if BSG_OBS_TMA
-  // Output staging for bulk (TMA) stores: three 8 KB tiles in a ring.  A tile is written with
+  // dynamic shared memory: [three staging tiles][kChunk rows]  (expand_smem_bytes below)
+  extern __shared__ __align__(128) unsigned char expand_smem[];
+  u32* const sm = reinterpret_cast<u32*>(expand_smem + 3 * BSG_OBS_TILE * 16);
+#else
+  __shared__ u32 sm[kChunk * kRow];
+#endif
+#if BSG_OBS_TMA
+  // Output staging for bulk (TMA) stores: three 8 KB tiles in a ring (dynamic shared memory, so
+  // that the writers with long rows — hex / y planes, breakthrough's 768-action mask — fit too).  A tile is written with
   // STS.128, made visible to the async proxy, and one thread hands it to the copy engine; the
   // ring of three needs one barrier per tile (see the wait_group.read below).
   constexpr int kTileVec = BSG_OBS_TILE;
-  constexpr bool kTma = kChunk * kRow * 4 + 3 * kTileVec * 16 <= 48 * 1024;
-  __shared__ __align__(128) uint4 stage[kTma ? 3 * kTileVec : 1];
+  constexpr bool kTma = true;
+  uint4* const stage = reinterpret_cast<uint4*>(expand_smem);
   int tsel = 0;
 #else
   constexpr bool kTma = false;
@@ -455,8 +473,9 @@ expand_kernel(const void* __restrict__ states, int64_t n, const uint8_t* __restr
         }
         tsel = tsel == 2 ? 0 : tsel + 1;
       }
-    } else
+    }
 #endif
+    if constexpr (!kTma) {
     for (int j = threadIdx.x; j < n16; j += kChunk) {
       const int e0 = j * kPer;
       const int st = e0 / kBits, r = e0 - st * kBits;
@@ -474,6 +493,7 @@ expand_kernel(const void* __restrict__ states, int64_t n, const uint8_t* __restr
         v.w = ((x >> 3) & 1u) * 0x3F800000u;
       }
       __stcs(out16 + j, v);
+    }
     }
     // tail of the very last chunk when its size is not a multiple of 16 bytes
     const int rest = total - n16 * kPer;
@@ -718,13 +738,16 @@ struct ObsOp2 {
     static int blocks_per_sm = 0;
     if (blocks_per_sm == 0) {
       int b = 0;
-      BSG_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, expand_kernel<G, kMask>, kChunk, 0));
+      BSG_CUDA(e, cudaFuncSetAttribute(expand_kernel<G, kMask>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)expand_smem_bytes<G, kMask>()));
+      BSG_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, expand_kernel<G, kMask>, kChunk,
+                                                                expand_smem_bytes<G, kMask>()));
       blocks_per_sm = b > 0 ? b : 1;
     }
     int64_t cap = (int64_t)e->sm_count * blocks_per_sm;
     int64_t need = (n + kChunk - 1) / kChunk;
     int grid = (int)(need < cap ? need : cap);
-    expand_kernel<G, kMask><<<grid < 1 ? 1 : grid, kChunk, 0, st>>>(states, n, players, out);
+    expand_kernel<G, kMask><<<grid < 1 ? 1 : grid, kChunk, expand_smem_bytes<G, kMask>(), st>>>(states, n, players, out);
     BSG_CUDA(e, cudaGetLastError());
     return BSG_OK;
   }
