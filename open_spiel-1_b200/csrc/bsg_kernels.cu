@@ -461,15 +461,16 @@ expand_kernel(const void* __restrict__ states, int64_t n, const uint8_t* __restr
           }
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        // Before anyone passes this barrier and writes the NEXT tile, the store that last used
+        // the next tile's buffer (issued two tiles ago) must have been read out of shared memory:
+        // all committed groups but the newest one.
+        if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
         __syncthreads();
         if (threadIdx.x == 0) {
           const int vecs = min(kTileVec, n16 - t * kTileVec);
           asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
                        :: "l"(out16 + (size_t)t * kTileVec), "r"((u32)__cvta_generic_to_shared(sbuf)), "r"(vecs * 16) : "memory");
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-          // the store issued one tile ago has been read out of shared memory: its buffer is
-          // the one the tile after next will write, two barriers from here
-          asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
         }
         tsel = tsel == 2 ? 0 : tsel + 1;
       }
