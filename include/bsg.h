@@ -73,6 +73,10 @@ int bsg_max_game_length(int game);
 int bsg_observation_size(int game);
 int bsg_observation_shape(int game, int shape_out[3]);
 int bsg_state_bytes(int game);
+/* Element sizes of the packed structure-of-arrays planes of a game (their sum is
+ * bsg_state_bytes): fills bytes_out[0..count) and returns the count, or BSG_ERR_BAD_ARG when
+ * `capacity` is too small.  What a caller needs to slice or interleave packed buffers. */
+int bsg_plane_bytes(int game, int* bytes_out, int capacity);
 
 /* ---- host helpers (pure CPU, usable without a GPU): moving reference states in and out.
  * Packed states are plane-major structure-of-arrays buffers with a capacity `cap`:

@@ -62,6 +62,7 @@ def _load():
       "bsg_observation_size": (ctypes.c_int, [ctypes.c_int]),
       "bsg_observation_shape": (ctypes.c_int, [ctypes.c_int, vp]),
       "bsg_state_bytes": (ctypes.c_int, [ctypes.c_int]),
+      "bsg_plane_bytes": (ctypes.c_int, [ctypes.c_int, vp, ctypes.c_int]),
       "bsg_pack_histories": (ctypes.c_int, [ctypes.c_int, vp, vp, i64, vp, i64]),
       "bsg_host_state_info": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, vp, vp, vp]),
       "bsg_host_legal_actions": (ctypes.c_int, [ctypes.c_int, vp, i64, i64, vp, ctypes.c_int]),

@@ -260,6 +260,10 @@ template <> struct Text<ConnectFour> {  // connect_four.cc:166-175 (rows top-dow
       if (++c >= 7) { --r; c = 0; }
     }
     if (!(xs == os || xs == os + 1) || r != -1 || c != 0) return BSG_ERR_BAD_ARG;
+    // gravity: an empty cell below a stone cannot be packed (the marker encoding keeps only the
+    // height of a column); the reference keeps such a board as written, no playout starts there
+    const u64 occ = x | o;
+    if ((occ >> 8) & ~occ & 0x00007F7F7F7F7F7Full) return BSG_ERR_BAD_ARG;
     int mv = (xs == os) ? 0 : 1;                    // connect_four.cc:270
     bool line_x = ConnectFour::has_line(x), line_o = ConnectFour::has_line(o);
     // a win is always the last mover's in a reachable position; the reference would also

@@ -2,9 +2,10 @@
 //
 // Playout kernel design:
 //  * one playout per lane, whole game state in registers (per-game bitboards, bsg_games.cuh);
-//  * persistent warps: each warp owns a contiguous slice of the launch's playouts and its lanes
-//    claim the next playout from a warp-uniform cursor with one ballot when they finish (lane
-//    refill; no atomics), so a warp keeps ~all lanes busy although game lengths differ;
+//  * persistent warps: every warp draws chunks of kChunkPlayouts consecutive playouts from one
+//    global work counter (one atomicAdd per chunk) and its lanes claim the next playout of the
+//    chunk from a warp-uniform cursor with one ballot when they finish (lane refill; no
+//    per-playout atomics), so a warp keeps ~all lanes busy although game lengths differ;
 //  * steps run in groups of four: one Philox4x32-10 block (4 draws) per group, and lanes are
 //    refilled only at group boundaries, which keeps every lane's step index congruent to the
 //    group phase — the RNG and the refill code stay warp-convergent;
@@ -30,6 +31,7 @@ namespace bsg {
 constexpr int kThreads = 256;
 constexpr int kChunkPlayouts = 128;   // playouts per work-counter draw of a warp
 constexpr int kWorkSlots = 1024;      // launches that may be in flight at once, per engine
+constexpr int kMaxDevices = 64;       // per-device caches of function attributes
 
 struct PlayoutArgs {
   const void* roots;
@@ -664,14 +666,23 @@ __global__ void forest_install_kernel(ForestView F, const int64_t* base, const i
 
 template <class G, bool kFull, bool kBase = false, bool kFill = false>
 int launch_playouts(bsg_engine* e, const PlayoutArgs& a, cudaStream_t st) {
-  static int blocks_per_sm = 0;
-  if (blocks_per_sm == 0) {
-    int b = 0;
-    // all of the L1/shared array as shared memory: the tables of every resident CTA must fit
-    BSG_CUDA(e, cudaFuncSetAttribute(playout_kernel<G, kFull, kBase, kFill>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                     cudaSharedmemCarveoutMaxShared));
-    BSG_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, playout_kernel<G, kFull, kBase, kFill>, kThreads, 0));
-    blocks_per_sm = b > 0 ? b : 1;
+  // function attributes belong to the current device: one cached answer per device, set under a
+  // lock (RootParallelMCTS walks several engines of one process from a thread pool)
+  static int per_device[kMaxDevices] = {};
+  static std::mutex mu;
+  int blocks_per_sm;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    int& slot = per_device[e->device % kMaxDevices];
+    if (slot == 0) {
+      int b = 0;
+      // all of the L1/shared array as shared memory: the tables of every resident CTA must fit
+      BSG_CUDA(e, cudaFuncSetAttribute(playout_kernel<G, kFull, kBase, kFill>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                       cudaSharedmemCarveoutMaxShared));
+      BSG_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, playout_kernel<G, kFull, kBase, kFill>, kThreads, 0));
+      slot = b > 0 ? b : 1;
+    }
+    blocks_per_sm = slot;
   }
   int64_t max_grid = (int64_t)e->sm_count * blocks_per_sm;
   int64_t need = ((int64_t)a.n_playouts + kThreads - 1) / kThreads;
@@ -736,14 +747,21 @@ struct ObsOp2 {
   bsg_engine* e; const void* states; int64_t n; const uint8_t* players; float* obs; uint8_t* mask;
   cudaStream_t st;
   template <class G, bool kMask> int launch(void* out) const {
-    static int blocks_per_sm = 0;
-    if (blocks_per_sm == 0) {
-      int b = 0;
-      BSG_CUDA(e, cudaFuncSetAttribute(expand_kernel<G, kMask>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)expand_smem_bytes<G, kMask>()));
-      BSG_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, expand_kernel<G, kMask>, kChunk,
-                                                                expand_smem_bytes<G, kMask>()));
-      blocks_per_sm = b > 0 ? b : 1;
+    static int per_device[kMaxDevices] = {};
+    static std::mutex mu;
+    int blocks_per_sm;
+    {
+      std::lock_guard<std::mutex> lock(mu);
+      int& slot = per_device[e->device % kMaxDevices];
+      if (slot == 0) {
+        int b = 0;
+        BSG_CUDA(e, cudaFuncSetAttribute(expand_kernel<G, kMask>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)expand_smem_bytes<G, kMask>()));
+        BSG_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, expand_kernel<G, kMask>, kChunk,
+                                                                  expand_smem_bytes<G, kMask>()));
+        slot = b > 0 ? b : 1;
+      }
+      blocks_per_sm = slot;
     }
     int64_t cap = (int64_t)e->sm_count * blocks_per_sm;
     int64_t need = (n + kChunk - 1) / kChunk;
@@ -801,6 +819,14 @@ int bsg_num_distinct_actions(int game) { return dispatch_game(game, FactOp{0}); 
 int bsg_max_game_length(int game) { return dispatch_game(game, FactOp{1}); }
 int bsg_observation_size(int game) { return dispatch_game(game, FactOp{2}); }
 int bsg_state_bytes(int game) { return dispatch_game(game, FactOp{3}); }
+int bsg_plane_bytes(int game, int* bytes_out, int capacity) {
+  int tmp[16];
+  const int n = dispatch_game(game, PlaneOp{tmp});
+  if (n < 0) return n;
+  if (!bytes_out || capacity < n) return BSG_ERR_BAD_ARG;
+  for (int p = 0; p < n; ++p) bytes_out[p] = tmp[p];
+  return n;
+}
 
 int bsg_observation_shape(int game, int shape[3]) {
   switch (game) {

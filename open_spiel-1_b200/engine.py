@@ -30,10 +30,28 @@ def state_bytes(gid):
   return C.check(C.lib.bsg_state_bytes(gid))
 
 
+_PLANES = {}
+
+
 def plane_bytes(gid):
-  """Element sizes of the packed SoA planes of a game."""
-  return {0: [4], 1: [8], 2: [16, 4], 3: [16, 16, 16, 16], 4: [16, 16, 16, 16], 5: [16], 6: [16, 4],
-          7: [48, 48, 48, 48, 48, 4], 8: [16, 16, 16, 16, 16, 4]}[gid]
+  """Element sizes of the packed SoA planes of a game (bsg_plane_bytes)."""
+  if gid not in _PLANES:
+    out = (ctypes.c_int * 16)()
+    n = C.check(C.lib.bsg_plane_bytes(gid, out, 16))
+    _PLANES[gid] = [int(out[i]) for i in range(n)]
+  return _PLANES[gid]
+
+
+def interleave_packed(gid, packs):
+  """Single packed states (capacity 1 each) -> one packed SoA buffer of capacity len(packs)."""
+  n = len(packs)
+  sb = state_bytes(gid)
+  rows = np.stack([np.ascontiguousarray(p, np.uint8).reshape(sb) for p in packs]) if n else np.zeros((0, sb), np.uint8)
+  parts, off = [], 0
+  for pb in plane_bytes(gid):
+    parts.append(rows[:, off:off + pb].reshape(-1))
+    off += pb
+  return np.concatenate(parts) if parts else np.zeros(0, np.uint8)
 
 
 def num_distinct_actions(gid):

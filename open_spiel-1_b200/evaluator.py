@@ -28,10 +28,28 @@ class Evaluator(object):
 
 
 def _packed_of(gid, state):
+  """Packed bitboards of one state.  The host mirror carries them (`packed()`), also when it
+  was deserialised from a board string and has no history; a `pyspiel.State` crosses as its
+  action history (pyspiel.cc:322) — except connect_four, whose Serialize() is the board itself
+  (connect_four.cc:227) and therefore also right for a state the reference deserialised from
+  a board string, where history() only holds the moves made since."""
   packed = getattr(state, "packed", None)
   if callable(packed):
     return packed()
+  if gid == _engine.C.CONNECT_FOUR and callable(getattr(state, "serialize", None)):
+    out = np.zeros(_engine.state_bytes(gid), np.uint8)
+    _engine.C.check(_engine.C.lib.bsg_host_deserialize(gid, state.serialize().encode(),
+                                                       out.ctypes.data, 1, 0))
+    return out
   return _engine.pack_histories(gid, [list(state.history())])
+
+
+def pack_states(gid, states):
+  """Packed SoA buffer (capacity len(states)) of a list of states: one C call over the
+  histories when no state carries its bitboards, the per-state planes interleaved otherwise."""
+  if not any(callable(getattr(s, "packed", None)) for s in states) and gid != _engine.C.CONNECT_FOUR:
+    return _engine.pack_histories(gid, [list(s.history()) for s in states])
+  return _engine.interleave_packed(gid, [_packed_of(gid, s) for s in states])
 
 
 class GpuRolloutEvaluator(Evaluator):
@@ -81,11 +99,7 @@ class GpuRolloutEvaluator(Evaluator):
     n = len(states)
     if n == 0:
       return np.zeros((0, 2))
-    gid = self.engine.gid
-    if all(callable(getattr(s, "packed", None)) for s in states) and n == 1:
-      packed = states[0].packed()
-    else:
-      packed = _engine.pack_histories(gid, [list(s.history()) for s in states])
+    packed = pack_states(self.engine.gid, states)
     first = self.next_playout
     totals, root_ret, _ = self.engine.playouts_host(packed, n, self.n_rollouts, self.seed, first,
                                                     want_root_sums=True)
@@ -142,39 +156,33 @@ class AlphaZeroEvaluator(Evaluator):
     gid = self.engine.gid
     packs = [np.ascontiguousarray(_packed_of(gid, s)) for s in states]
     keys = [p.tobytes() for p in packs]
-    todo = [i for i, k in enumerate(keys) if k not in self._cache]
+    # this batch's answers are collected here first: inserting the misses may evict entries
+    # (also this batch's own hits, or its own misses when the batch exceeds the cache)
+    got = {}
+    for k in keys:
+      if k in self._cache and k not in got:
+        got[k] = self._cache[k]
+        self._cache.move_to_end(k)
     uniq = {}
-    for i in todo:
-      uniq.setdefault(keys[i], i)
+    for i, k in enumerate(keys):
+      if k not in got:
+        uniq.setdefault(k, i)
     idx = list(uniq.values())
     if idx:
       n = len(idx)
-      sb = self.engine.state_bytes
-      # packed SoA with capacity n: interleave the per-state planes
-      planes = _engine.plane_bytes(gid)
-      buf = np.zeros(n * sb, np.uint8)
-      off_dst = 0
-      off_src = 0
-      for pb in planes:
-        for j, i in enumerate(idx):
-          buf[off_dst + j * pb: off_dst + (j + 1) * pb] = packs[i][off_src: off_src + pb]
-        off_dst += n * pb
-        off_src += pb
-      d_states = self.engine.to_device(buf)
+      d_states = self.engine.to_device(_engine.interleave_packed(gid, [packs[i] for i in idx]))
       obs, mask = self.engine.observations(d_states, n, None, want_mask=True)
       value, policy = self._model.inference(obs, mask.to(torch.bool))
       value = torch.as_tensor(value).detach().to("cpu", torch.float64).reshape(n).numpy()
       policy = torch.as_tensor(policy).detach().to("cpu", torch.float64).reshape(n, -1).numpy()
       for j, i in enumerate(idx):
-        self._cache[keys[i]] = (float(value[j]), policy[j])
-        if len(self._cache) > self._cache_size:
-          self._cache.popitem(last=False)
+        got[keys[i]] = self._cache[keys[i]] = (float(value[j]), policy[j])
+      while len(self._cache) > self._cache_size:
+        self._cache.popitem(last=False)
     self.misses += len(idx)
     self.hits += len(states) - len(idx)
-    vals = np.array([self._cache[k][0] for k in keys], np.float64)
-    pols = np.stack([self._cache[k][1] for k in keys]) if keys else np.zeros((0, 0))
-    for k in keys:
-      self._cache.move_to_end(k)
+    vals = np.array([got[k][0] for k in keys], np.float64)
+    pols = np.stack([got[k][1] for k in keys]) if keys else np.zeros((0, 0))
     return vals, pols
 
   def evaluate(self, state):

@@ -374,3 +374,25 @@ def test_native_tree_over_a_value_only_engine_builds_the_same_tree(bsg):
     bot.close()
     eng.close()
   assert roots[0] == roots[1]
+
+
+def test_batched_search_from_a_deserialized_root(bsg):
+  """A connect_four root read from a board string has no history (as in the reference,
+  connect_four.cc:229-279); the leaves of a batched search below it must still be evaluated at
+  THEIR positions: the search equals the one from the same position reached by its history."""
+  game = bsg.load_game("connect_four")
+  played = game.new_initial_state()
+  for a in (3, 3, 2, 4, 1, 5, 3, 2):
+    played.apply_action(a)
+  loaded = game.deserialize_state(played.serialize())
+  assert loaded.history() == [] and np.array_equal(loaded.packed(), played.packed())
+  roots = []
+  for root_state, lb in ((played, 1), (played, 8), (loaded, 8), (loaded, 1)):
+    ev = bsg.GpuRolloutEvaluator("connect_four", n_rollouts=16, seed=5)
+    bot = bsg.MCTSBot(game, UCT_C, 200, ev, solve=True, random_state=bsg.PhiloxShuffle(11),
+                      leaf_batch=lb)
+    root = bot.mcts_search(root_state)
+    roots.append((lb, sorted((c.action, c.explore_count, c.total_reward) for c in root.children)))
+    ev.engine.close()
+  assert roots[0][1] == roots[3][1]      # leaf_batch 1: history vs board string
+  assert roots[1][1] == roots[2][1]      # leaf_batch 8: history vs board string

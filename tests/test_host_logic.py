@@ -176,3 +176,97 @@ def test_value_only_fill_gives_the_exact_playouts_winner(oracle, name, oname, bs
   assert ret0.value == o_ret and moves.value == 0
   with pytest.raises(RuntimeError):
     C.check(C.lib.bsg_host_fill_playout(bsg.game_id("connect_four"), packed.ctypes.data, 1, 0, 1, 1, None, None))
+
+
+def test_plane_table_comes_from_the_abi():
+  """bsg_plane_bytes: the packed SoA plane sizes sum to the state size for every game id."""
+  from open_spiel_1_b200 import engine as E
+  for gid in range(9):
+    planes = E.plane_bytes(gid)
+    assert planes and sum(planes) == E.state_bytes(gid)
+  assert E.plane_bytes(C.CONNECT_FOUR) == [8] and E.plane_bytes(C.BREAKTHROUGH) == [16, 4]
+
+
+@pytest.mark.parametrize("name", ["connect_four", "breakthrough", "hex", "othello", "y"])
+def test_pack_states_interleaves_mirror_states_like_pack_histories(name):
+  """evaluator.pack_states: a batch of mirror states travels as their own bitboards (also
+  when a state has no history: a connect_four / breakthrough root deserialised from a board
+  string), and equals the batch packed from the histories."""
+  from open_spiel_1_b200.evaluator import pack_states
+  game = bsg.load_game(name)
+  rng = np.random.RandomState(3)
+  states = []
+  for i in range(7):
+    s = game.new_initial_state()
+    for _ in range(3 * i):
+      la = s.legal_actions()
+      if not la:
+        break
+      s.apply_action(la[rng.randint(len(la))])
+    states.append(s)
+  want = bsg.pack_histories(name, [s.history() for s in states])
+  assert np.array_equal(pack_states(game.gid, states), want)
+  if name == "connect_four":
+    # the same positions through the board-string reader: no history, same bitboards; moves
+    # made after the deserialisation are the only history such a state has
+    des = [game.deserialize_state(s.serialize()) for s in states if not s.is_terminal()]
+    live = [s for s in states if not s.is_terminal()]
+    assert all(d.history() == [] for d in des)
+    assert np.array_equal(pack_states(game.gid, des), pack_states(game.gid, live))
+    for d, s in zip(des, live):
+      a = s.legal_actions()[0]
+      d.apply_action(a); s.apply_action(a)
+    assert np.array_equal(pack_states(game.gid, des), pack_states(game.gid, live))
+
+
+def test_connect_four_reader_rejects_floating_stones():
+  game = bsg.load_game("connect_four")
+  ok = ".......\n.......\n.......\n.......\n...o...\n...x...\n"
+  assert game.deserialize_state(ok).legal_actions() == list(range(7))
+  floating = ".......\n.......\n.......\n...o...\n.......\n...x...\n"
+  with pytest.raises(RuntimeError):
+    game.deserialize_state(floating)
+
+
+def test_alpha_zero_cache_survives_eviction_inside_a_batch():
+  """AlphaZeroEvaluator.inference_batch with a cache smaller than the batch, and with a hit at
+  the LRU end while misses are inserted (evaluator.py:56-75 of the reference is an LRU too)."""
+  from open_spiel_1_b200 import evaluator as ev_mod
+
+  class FakeEngine:
+    gid = C.TIC_TAC_TOE
+    state_bytes = 4
+
+    def to_device(self, buf):
+      return np.asarray(buf).copy()
+
+    def observations(self, d_states, n, players, want_mask=False):
+      import torch
+      w = torch.from_numpy(d_states.view(np.uint32).astype(np.int64))
+      return w.reshape(n, 1).double(), torch.ones((n, 9), dtype=torch.uint8)
+
+  class Model:
+    calls = 0
+
+    def inference(self, obs, mask):
+      import torch
+      Model.calls += 1
+      return obs / 1e6, torch.full((obs.shape[0], 9), 1.0 / 9, dtype=torch.float64)
+
+  game = bsg.load_game("tic_tac_toe")
+  ev = ev_mod.AlphaZeroEvaluator(game, Model(), cache_size=3, engine=FakeEngine())
+  states = []
+  for a in range(9):
+    s = game.new_initial_state()
+    s.apply_action(a)
+    states.append(s)
+  want = np.array([float(s.packed().view(np.uint32)[0]) / 1e6 for s in states])
+  v, p = ev.inference_batch(states)                       # 9 misses through a cache of 3
+  assert np.allclose(v, want) and p.shape == (9, 9)
+  assert ev.cache_info()["size"] == 3
+  # states[6] is now the LRU entry: a batch that hits it and brings three misses must not lose it
+  v, _ = ev.inference_batch([states[0], states[6], states[1], states[2]])
+  assert np.allclose(v, want[[0, 6, 1, 2]])
+  assert ev.cache_info()["size"] == 3
+  v, _ = ev.inference_batch([states[2], states[2]])       # duplicate keys, one hit each
+  assert np.allclose(v, want[[2, 2]])
