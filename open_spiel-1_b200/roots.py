@@ -20,9 +20,12 @@ ROOT_DEPTHS = {  # cfg2 U{8..20}, cfg3 U{0..40}, cfg4 U{0..60}
 }
 
 
-def make_roots(engine, n, dmin, dmax, seed, want_histories=False, chunk=1 << 22):
+def make_roots(engine, n, dmin, dmax, seed, want_histories=False, chunk=1 << 22, want_log=False):
   """Returns (states, histories): `states` is a device uint8 tensor holding n packed states
-  (SoA, capacity n); `histories` is a list of action lists or None."""
+  (SoA, capacity n); `histories` is a list of action lists or None.  With `want_log` the
+  histories come back as a dense action log instead of Python lists — (actions int16
+  [n, max(dmax, 1)] numpy, root_len int32 [n] numpy): row i holds the root_len[i] moves that
+  lead to root i — which is how BASELINE-size batches (16 Mi roots) reach a CPU checker."""
   import torch
   dev = engine.torch_device
   sb = engine.state_bytes
@@ -34,14 +37,17 @@ def make_roots(engine, n, dmin, dmax, seed, want_histories=False, chunk=1 << 22)
   length = torch.empty(n, dtype=torch.uint8, device=dev)
   term = torch.empty(n, dtype=torch.uint8, device=dev)
   acts = None
-  if want_histories:
+  if want_histories or want_log:
     acts = torch.full((n, max(int(dmax), 1)), -1, dtype=torch.int16, device=dev)
   # one root (the initial position), n rollouts: playout i is root i of the result
   engine.playouts(init, 1, n, seed=seed, first_playout=0, step_limit=d_depth, length=length,
                   terminal=term, actions=acts, final_states=states, final_before_terminal=True)
   torch.cuda.synchronize(dev)
   histories = None
-  if want_histories:
+  if want_log:
+    ln = length.cpu().numpy().astype(np.int32)
+    histories = (acts.cpu().numpy(), ln - (term.cpu().numpy() != 0).astype(np.int32))
+  elif want_histories:
     a = acts.cpu().numpy()
     ln = length.cpu().numpy().astype(np.int64)
     tm = term.cpu().numpy()

@@ -150,6 +150,97 @@ int ref_replay_batch(const char* game, const int64_t* hist_flat, const int64_t* 
   return bad.load() ? -1 : 0;
 }
 
+// The same replay for roots given as a dense int16 action log (row i holds the root_len[i]
+// moves that lead to root i) — what the device root generator returns — so that BASELINE-size
+// batches (16 Mi roots) cross without a ragged int64 copy.  Per playout: moves played,
+// (int)Returns()[0], IsTerminal().  One std::thread per requested core, playouts handed out in
+// blocks.
+int ref_replay_log(const char* game, const int16_t* log, int log_stride, const int32_t* root_len,
+                   int64_t n_roots, int rollouts, uint64_t seed, uint64_t first_playout,
+                   int threads, int32_t* len_out, int8_t* ret0_out, uint8_t* terminal_out) {
+  auto g = GetGame(game);
+  if (threads < 1) threads = 1;
+  std::atomic<int64_t> next{0};
+  std::atomic<int> bad{0};
+  const int64_t kBlock = 256;
+  auto work = [&]() {
+    for (;;) {
+      const int64_t lo = next.fetch_add(kBlock);
+      if (lo >= n_roots) break;
+      const int64_t hi = std::min(lo + kBlock, n_roots);
+      for (int64_t i = lo; i < hi; ++i) {
+        auto root = g->NewInitialState();
+        const int16_t* h = log + i * log_stride;
+        for (int k = 0; k < root_len[i]; ++k) root->ApplyAction(h[k]);
+        for (int j = 0; j < rollouts; ++j) {
+          const int64_t p = i * rollouts + j;
+          std::unique_ptr<open_spiel::State> s = rollouts == 1 ? std::move(root) : root->Clone();
+          int t = 0;
+          while (!s->IsTerminal()) {
+            std::vector<open_spiel::Action> legal = s->LegalActions();
+            if (legal.empty()) { bad.store(1); break; }
+            const uint32_t r = oracle_draw(seed, first_playout + (uint64_t)p, (uint32_t)t);
+            s->ApplyAction(legal[r % legal.size()]);
+            ++t;
+          }
+          len_out[p] = t;
+          ret0_out[p] = static_cast<int8_t>(s->Returns()[0]);
+          terminal_out[p] = s->IsTerminal() ? 1 : 0;
+        }
+      }
+    }
+  };
+  std::vector<std::thread> pool;
+  for (int k = 0; k < threads; ++k) pool.emplace_back(work);
+  for (auto& th : pool) th.join();
+  return bad.load() ? -1 : 0;
+}
+
+// State dumps of many states given as a dense int16 action log: ObservationTensor(players[i])
+// as bytes (the reference's doubles are 0.0 / 1.0), LegalActionsMask as bytes, CurrentPlayer,
+// IsTerminal.  Any out pointer may be NULL.
+int ref_state_dump_log(const char* game, const int16_t* log, int log_stride, const int32_t* hist_len,
+                       int64_t n, const uint8_t* players, int threads, uint8_t* obs_out,
+                       uint8_t* mask_out, int32_t* cur_player_out, uint8_t* terminal_out) {
+  auto g = GetGame(game);
+  const int obs_size = g->ObservationTensorSize();
+  const int n_actions = g->NumDistinctActions();
+  if (threads < 1) threads = 1;
+  std::atomic<int64_t> next{0};
+  std::atomic<int> bad{0};
+  auto work = [&]() {
+    std::vector<double> obs;
+    for (;;) {
+      const int64_t lo = next.fetch_add(64);
+      if (lo >= n) break;
+      const int64_t hi = std::min(lo + (int64_t)64, n);
+      for (int64_t i = lo; i < hi; ++i) {
+        auto s = g->NewInitialState();
+        const int16_t* h = log + i * log_stride;
+        for (int k = 0; k < hist_len[i]; ++k) s->ApplyAction(h[k]);
+        if (obs_out) {
+          s->ObservationTensor(players ? players[i] : 0, &obs);
+          for (int e = 0; e < obs_size; ++e) {
+            if (obs[e] != 0.0 && obs[e] != 1.0) bad.store(1);
+            obs_out[i * obs_size + e] = obs[e] != 0.0 ? 1 : 0;
+          }
+        }
+        if (mask_out) {
+          std::memset(mask_out + i * n_actions, 0, n_actions);
+          if (!s->IsTerminal())
+            for (open_spiel::Action a : s->LegalActions()) mask_out[i * n_actions + a] = 1;
+        }
+        if (cur_player_out) cur_player_out[i] = s->CurrentPlayer();
+        if (terminal_out) terminal_out[i] = s->IsTerminal() ? 1 : 0;
+      }
+    }
+  };
+  std::vector<std::thread> pool;
+  for (int k = 0; k < threads; ++k) pool.emplace_back(work);
+  for (auto& th : pool) th.join();
+  return bad.load() ? -1 : 0;
+}
+
 // CPU baseline, shaped like open_spiel/examples/benchmark_game.cc:31-97: from each root
 // (history), Clone-free replay of LegalActions -> uniform pick -> ApplyAction until terminal,
 // optionally filling ObservationTensor(CurrentPlayer()) every step (benchmark_game.cc:46-47).

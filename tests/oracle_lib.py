@@ -39,7 +39,21 @@ def build_oracle():
   return so
 
 
+def ragged_from_log(log, lens):
+  """Dense action log (int16 [n, stride], lens [n]) -> (flat int64, off int64) without loops."""
+  lens = np.asarray(lens, np.int64)
+  off = np.zeros(len(lens) + 1, np.int64)
+  np.cumsum(lens, out=off[1:])
+  keep = np.arange(log.shape[1])[None, :] < lens[:, None]
+  flat = log[keep].astype(np.int64)
+  if flat.size == 0:
+    flat = np.zeros(1, np.int64)
+  return flat, off
+
+
 def ragged(histories):
+  if isinstance(histories, tuple):      # already (flat, off)
+    return histories
   off = np.zeros(len(histories) + 1, np.int64)
   for i, h in enumerate(histories):
     off[i + 1] = off[i] + len(h)
@@ -86,13 +100,14 @@ class Oracle:
   def replay_batch(self, game, histories, rollouts=1, seed=0, first_playout=0,
                    max_steps=1 << 20, actions_stride=0, board_size=11):
     flat, off = ragged(histories)
-    n = len(histories) * rollouts
+    n_roots = len(off) - 1
+    n = n_roots * rollouts
     lens = np.zeros(n, np.int32)
     ret0 = np.zeros(n, np.int8)
     term = np.zeros(n, np.uint8)
     acts = np.full((n, actions_stride), -1, np.int16) if actions_stride else None
     rc = self.lib.orc_replay_batch(GAME_IDS[game], board_size, _ptr(flat), _ptr(off),
-                                   len(histories), rollouts, seed, first_playout, max_steps,
+                                   n_roots, rollouts, seed, first_playout, max_steps,
                                    _ptr(lens), _ptr(ret0), _ptr(term), _ptr(acts), actions_stride)
     if rc != 0:
       raise RuntimeError("orc_replay_batch failed rc=%d" % rc)
@@ -140,6 +155,11 @@ class Reference:
                                    vp, vp, vp, vp, ctypes.c_int]
     L.ref_state_dump.argtypes = [ctypes.c_char_p, vp, ctypes.c_int, ctypes.c_int, vp, vp, vp, vp,
                                  vp, vp]
+    L.ref_replay_log.argtypes = [ctypes.c_char_p, vp, ctypes.c_int, vp, ctypes.c_int64, ctypes.c_int,
+                                 ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int, vp, vp, vp]
+    L.ref_state_dump_log.argtypes = [ctypes.c_char_p, vp, ctypes.c_int, vp, ctypes.c_int64, vp,
+                                     ctypes.c_int, vp, vp, vp, vp]
+    L.ref_game_info.argtypes = [ctypes.c_char_p, vp, vp, vp]
     L.ref_random_playouts.argtypes = [ctypes.c_char_p, vp, vp, ctypes.c_int64, ctypes.c_int64,
                                       ctypes.c_uint64, ctypes.c_int, ctypes.c_int, vp, vp]
     L.ref_random_playouts.restype = ctypes.c_double
@@ -178,18 +198,51 @@ class Reference:
   def replay_batch(self, game, histories, rollouts=1, seed=0, first_playout=0,
                    max_steps=1 << 20, actions_stride=0, threads=8, board_size=11):
     flat, off = ragged(histories)
-    n = len(histories) * rollouts
+    n_roots = len(off) - 1
+    n = n_roots * rollouts
     lens = np.zeros(n, np.int32)
     ret0 = np.zeros(n, np.int8)
     term = np.zeros(n, np.uint8)
     acts = np.full((n, actions_stride), -1, np.int16) if actions_stride else None
     rc = self.lib.ref_replay_batch(self.game_string(game, board_size), _ptr(flat), _ptr(off),
-                                   len(histories), rollouts, seed, first_playout, max_steps,
+                                   n_roots, rollouts, seed, first_playout, max_steps,
                                    threads, _ptr(lens), _ptr(ret0), _ptr(term), _ptr(acts),
                                    actions_stride)
     if rc != 0:
       raise RuntimeError("ref_replay_batch failed")
     return lens, ret0, term, acts
+
+  def replay_log(self, game, log, root_len, rollouts=1, seed=0, first_playout=0, threads=8):
+    """ref_replay_log: replay from roots given as a dense int16 action log (roots.make_roots
+    want_log).  Returns (lens int32, ret0 int8, terminal uint8) per playout."""
+    log = np.ascontiguousarray(log, np.int16)
+    root_len = np.ascontiguousarray(root_len, np.int32)
+    n = len(root_len) * rollouts
+    lens, ret0, term = np.zeros(n, np.int32), np.zeros(n, np.int8), np.zeros(n, np.uint8)
+    rc = self.lib.ref_replay_log(self.game_string(game), _ptr(log), log.shape[1], _ptr(root_len),
+                                 len(root_len), rollouts, seed, first_playout, threads, _ptr(lens),
+                                 _ptr(ret0), _ptr(term))
+    if rc != 0:
+      raise RuntimeError("ref_replay_log failed")
+    return lens, ret0, term
+
+  def state_dump_log(self, game, log, hist_len, players=None, threads=8, want_obs=True, want_mask=True):
+    """ref_state_dump_log: ObservationTensor(players[i]) and LegalActionsMask as bytes, current
+    player and terminal flag of the states reached by the rows of a dense int16 action log."""
+    log = np.ascontiguousarray(log, np.int16)
+    hist_len = np.ascontiguousarray(hist_len, np.int32)
+    n = len(hist_len)
+    na, ml, osz = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    self.lib.ref_game_info(self.game_string(game), ctypes.byref(na), ctypes.byref(ml), ctypes.byref(osz))
+    obs = np.zeros((n, osz.value), np.uint8) if want_obs else None
+    mask = np.zeros((n, na.value), np.uint8) if want_mask else None
+    cur, term = np.zeros(n, np.int32), np.zeros(n, np.uint8)
+    pl = None if players is None else np.ascontiguousarray(players, np.uint8)
+    rc = self.lib.ref_state_dump_log(self.game_string(game), _ptr(log), log.shape[1], _ptr(hist_len),
+                                     n, _ptr(pl), threads, _ptr(obs), _ptr(mask), _ptr(cur), _ptr(term))
+    if rc != 0:
+      raise RuntimeError("ref_state_dump_log failed")
+    return {"obs": obs, "mask": mask, "current_player": cur, "terminal": term}
 
   def state_dump(self, game, hist, player=0, board_size=11):
     h = np.asarray(hist, np.int64)

@@ -111,14 +111,21 @@ def test_replay_with_explicit_r_table(game, checker, torch):
 
 
 @pytest.mark.parametrize("game", GAMES)
-def test_observations_and_masks_bit_exact(game, torch):
-  """ObservationTensor planes and LegalActionsMask of 1e5 states vs the oracle."""
+def test_observations_and_masks_bit_exact(game, checker, torch):
+  """ObservationTensor planes and LegalActionsMask of 1e5 states per game, every one of them
+  against the COMPILED REFERENCE's State::ObservationTensor / LegalActions in the same process
+  (ref_state_dump_log; hex edge-label planes hex.cc:55-121,149-184,266-277), then 1e4 of them
+  also against the C restatement, then terminal states (the reference keeps the *Win marks)."""
+  import open_spiel_1_b200 as bsg
+  from open_spiel_1_b200.roots import make_roots, ROOT_DEPTHS
   oracle = Oracle()
   eng = _engine(game)
   n = 100000
-  states, hist = _roots(eng, game, n, seed=42)
+  dmin, dmax = ROOT_DEPTHS[game]
+  states, (log, lens) = make_roots(eng, n, dmin, dmax, seed=42, want_log=True)
   dev = eng.torch_device
-  players = torch.from_numpy((np.arange(n) % 2).astype(np.uint8)).to(dev)
+  pl = (np.arange(n) % 2).astype(np.uint8)
+  players = torch.from_numpy(pl).to(dev)
   obs, mask = eng.observations(states, n, players, want_mask=True)
   torch.cuda.synchronize()
   obs = obs.cpu().numpy().reshape(n, -1)
@@ -126,27 +133,47 @@ def test_observations_and_masks_bit_exact(game, torch):
   assert set(np.unique(obs).tolist()) <= {0.0, 1.0}
   cells = 190 if game == "y" else eng.obs_size // eng.obs_shape[0]   # y: the triangle of the 19 x 19 grid
   assert np.all(obs.sum(1) == cells)  # exactly one plane per board cell
-  for i in range(n):                      # every one of the 1e5 states against the oracle
+  obs8 = obs.astype(np.uint8)
+  if isinstance(checker, Reference):
+    d = checker.state_dump_log(game, log, lens, pl, threads=os.cpu_count() or 1)
+    assert np.array_equal(obs8, d["obs"])
+    assert np.array_equal(mask, d["mask"])
+    assert not d["terminal"].any()
+  hist = [log[i, :lens[i]].astype(np.int64).tolist() for i in range(n)]
+  step = 1 if not isinstance(checker, Reference) else 10
+  for i in range(0, n, step):             # the C restatement
     d = oracle.state_dump(game, hist[i], i % 2)
-    assert np.array_equal(obs[i].astype(np.uint8), d["obs"]), i
+    assert np.array_equal(obs8[i], d["obs"]), i
     assert np.nonzero(mask[i])[0].tolist() == d["legal"], i
   # host-buffer entry point gives the same bytes
   k = 1000
-  import open_spiel_1_b200 as bsg
   packed = bsg.pack_histories(game, hist[:k])
-  obs_h, mask_h = eng.observations_host(packed, k, (np.arange(k) % 2).astype(np.uint8), True)
+  obs_h, mask_h = eng.observations_host(packed, k, pl[:k], True)
   assert np.array_equal(obs_h.reshape(k, -1), obs[:k]) and np.array_equal(mask_h, mask[:k])
-  # terminal states (the reference keeps *Win marks at terminal hex states)
+  # terminal states: 3000 finished games (hex / y: the winning cell carries both edge labels)
   term_hist = []
   for p in range(300):
     a, _, _ = oracle.replay(game, [], seed=9, playout=p)
     term_hist.append(a)
+  _, _, _, t_acts = oracle.replay_batch(game, [[]], rollouts=3000, seed=10, actions_stride=256)
+  t_lens = (t_acts >= 0).sum(1).astype(np.int32)
+  term_hist += [t_acts[i, :t_lens[i]].astype(np.int64).tolist() for i in range(3000)]
+  nt = len(term_hist)
   packed = bsg.pack_histories(game, term_hist)
-  obs_t, mask_t = eng.observations_host(packed, len(term_hist), np.zeros(len(term_hist), np.uint8), True)
-  for i, h in enumerate(term_hist):
-    d = oracle.state_dump(game, h, 0)
-    assert np.array_equal(obs_t[i].ravel().astype(np.uint8), d["obs"])
-    assert mask_t[i].sum() == 0
+  tp = (np.arange(nt) % 2).astype(np.uint8)
+  obs_t, mask_t = eng.observations_host(packed, nt, tp, True)
+  obs_t = obs_t.reshape(nt, -1).astype(np.uint8)
+  assert mask_t.sum() == 0
+  if isinstance(checker, Reference):
+    t_log = np.full((nt, 256), -1, np.int16)
+    for i, h in enumerate(term_hist):
+      t_log[i, :len(h)] = h
+    d = checker.state_dump_log(game, t_log, np.array([len(h) for h in term_hist], np.int32), tp,
+                               threads=os.cpu_count() or 1)
+    assert d["terminal"].all() and np.array_equal(obs_t, d["obs"]) and d["mask"].sum() == 0
+  for i in range(300):
+    d = oracle.state_dump(game, term_hist[i], int(tp[i]))
+    assert np.array_equal(obs_t[i], d["obs"])
   eng.close()
 
 
@@ -165,8 +192,10 @@ def test_native_rng_win_rates_within_binomial_ci(game, checker, torch):
   eng.playouts(root, 1, n_gpu, seed=20240611, ret0=ret0, length=length)
   torch.cuda.synchronize()
   r = ret0.cpu().numpy()
-  n_ref = {"tic_tac_toe": 400000, "connect_four": 200000, "breakthrough": 40000, "hex": 30000,
-           "pentago": 100000, "othello": 40000, "y": 20000}[game]
+  # >= 1e6 reference playouts per game where the reference plays them in
+  # seconds (all host cores); breakthrough / hex / y at what ~5 s of the reference buys
+  n_ref = {"tic_tac_toe": 1 << 20, "connect_four": 1 << 20, "breakthrough": 200000, "hex": 100000,
+           "pentago": 400000, "othello": 40000, "y": 60000}[game]
   if isinstance(checker, Reference):
     # reference's own mt19937 stream; per-outcome counts via replay batch are Philox-tied, so
     # use random_playouts for the mean and replay_batch (different seed) for the outcome split
@@ -180,7 +209,11 @@ def test_native_rng_win_rates_within_binomial_ci(game, checker, torch):
   half = 3.29 * np.sqrt(var / n_gpu + var / n_ref)
   assert abs(mean_gpu - mean_ref) <= half, (mean_gpu, mean_ref, half)
   # outcome split against an independently seeded checker replay
-  o_len, o_ret, _, _ = checker.replay_batch(game, [[]], rollouts=n_ref, seed=987654321)
+  if isinstance(checker, Reference):
+    o_len, o_ret, _, _ = checker.replay_batch(game, [[]], rollouts=n_ref, seed=987654321,
+                                              threads=os.cpu_count() or 1)
+  else:
+    o_len, o_ret, _, _ = checker.replay_batch(game, [[]], rollouts=n_ref, seed=987654321)
   for outcome in (1, 0, -1):
     p_gpu = float((r == outcome).mean())
     p_ref = float((o_ret == outcome).mean())
@@ -192,24 +225,27 @@ def test_native_rng_win_rates_within_binomial_ci(game, checker, torch):
   eng.close()
 
 
-@pytest.mark.parametrize("game,n,max_len,min_len", [
-    ("connect_four", 1 << 24, 42, 1),     # BASELINE cfg2: 16 Mi playouts
-    ("breakthrough", 1 << 22, 209, 1),    # cfg3: 4 Mi playouts per GPU
-    ("hex", 1 << 20, 121, 1),             # cfg4: 1 Mi playouts per GPU
-    ("pentago", 1 << 22, 36, 1),
-    ("othello", 1 << 22, 120, 1),
-    ("y", 1 << 20, 190, 1),
+@pytest.mark.parametrize("game,n,max_len,min_len,n_check", [
+    ("connect_four", 1 << 24, 42, 1, 1 << 24),     # BASELINE cfg2: 16 Mi playouts, ALL replayed
+    ("breakthrough", 1 << 22, 209, 1, 1 << 21),    # cfg3: 4 Mi playouts per GPU, 2 Mi replayed
+    ("hex", 1 << 20, 121, 1, 1 << 20),             # cfg4: 1 Mi playouts per GPU, all replayed
+    ("pentago", 1 << 22, 36, 1, 1 << 20),
+    ("othello", 1 << 22, 120, 1, 1 << 16),
+    ("y", 1 << 20, 190, 1, 1 << 18),
 ])
-def test_full_size_properties(game, n, max_len, min_len, torch):
-  """BASELINE configuration sizes: size-independent properties instead of an oracle run —
-  checksum of checksums (totals vs per-playout outputs), every playout terminal, length
-  bounds, idempotence, invariance under splitting the launch, and a 2000-playout sample
-  re-played through the host step hook."""
+def test_full_size_properties(game, n, max_len, min_len, n_check, checker, torch):
+  """BASELINE configuration sizes.  (1) The lean kernel's per-playout results (length, return)
+  against the COMPILED REFERENCE replaying the same playouts from the same roots — all 16 Mi of
+  cfg2, 2 Mi of cfg3, all 1 Mi of cfg4 (ref_replay_log, all host cores; the roots reach it as
+  the dense action log of the root generator).  (2) Size-independent properties: checksum of
+  checksums (totals vs per-playout outputs), every playout terminal, length bounds,
+  idempotence, invariance under splitting the launch."""
   from open_spiel_1_b200.roots import make_roots, ROOT_DEPTHS
+  from oracle_lib import ragged_from_log
   eng = _engine(game)
   dev = eng.torch_device
   dmin, dmax = ROOT_DEPTHS[game]
-  states, _ = make_roots(eng, n, dmin, dmax, seed=20240611 + 2)
+  states, (log, root_len) = make_roots(eng, n, dmin, dmax, seed=20240611 + 2, want_log=True)
   ret0 = torch.zeros(n, dtype=torch.int8, device=dev)
   length = torch.zeros(n, dtype=torch.uint8, device=dev)
   term = torch.zeros(n, dtype=torch.uint8, device=dev)
@@ -233,8 +269,7 @@ def test_full_size_properties(game, n, max_len, min_len, torch):
   from open_spiel_1_b200 import _cabi as C
   host = states.cpu().numpy()
   sb = eng.state_bytes
-  planes = {"connect_four": [8], "breakthrough": [16, 4], "hex": [16, 16, 16, 16], "pentago": [16], "othello": [16, 4],
-            "y": [48, 48, 48, 48, 48, 4]}[game]
+  planes = bsg.engine.plane_bytes(eng.gid)
   assert sum(planes) == sb
 
   def take(lo, hi):
@@ -250,24 +285,18 @@ def test_full_size_properties(game, n, max_len, min_len, torch):
   eng.playouts(hi_half, n - half, 1, seed=1, first_playout=half, ret0=ret0b[half:], length=lengthb[half:])
   torch.cuda.synchronize()
   assert torch.equal(ret0, ret0b) and torch.equal(length, lengthb)
-  # sample of the full-size run re-played on the host through the very step function the
-  # kernels run (a board alone has no history for the oracle; the step hook itself is checked
-  # against the oracle in tests/test_host_logic.py)
-  import ctypes
-  gid = eng.gid
-  idx = np.random.RandomState(0).randint(0, n, size=2000 if game == "connect_four" else 300)
+  # (1) the compiled reference replays the playouts themselves
   g_len, g_ret = length.cpu().numpy(), ret0.cpu().numpy()
-  for i in idx:
-    one = take(int(i), int(i) + 1).copy()
-    acts = 0
-    while True:
-      cur, tm, r0 = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
-      C.check(C.lib.bsg_host_state_info(gid, one.ctypes.data, 1, 0, ctypes.byref(cur), ctypes.byref(tm), ctypes.byref(r0)))
-      if tm.value:
-        break
-      C.check(C.lib.bsg_host_replay_step(gid, one.ctypes.data, 1, 0, bsg.draw(1, int(i), acts), None))
-      acts += 1
-    assert acts == g_len[i] and r0.value == g_ret[i]
+  if isinstance(checker, Reference):
+    o_len, o_ret, o_term = checker.replay_log(game, log[:n_check], root_len[:n_check], seed=1,
+                                              first_playout=0, threads=os.cpu_count() or 1)
+  else:   # no reference library on this box: the C restatement on a smaller prefix
+    n_check = min(n_check, 1 << 17)
+    o_len, o_ret, o_term, _ = checker.replay_batch(game, ragged_from_log(log[:n_check], root_len[:n_check]),
+                                                   seed=1, first_playout=0)
+  assert np.array_equal(g_len[:n_check].astype(np.int32), o_len)
+  assert np.array_equal(g_ret[:n_check], o_ret)
+  assert o_term.all()
   eng.close()
 
 

@@ -58,3 +58,42 @@ def test_batch_matches(libs):
     r = ref.replay_batch(game, roots, rollouts=3, seed=11, actions_stride=64, threads=4)
     for x, y in zip(o, r):
       assert np.array_equal(x, y)
+
+
+def _log_of(histories, stride):
+  log = np.full((len(histories), stride), -1, np.int16)
+  lens = np.zeros(len(histories), np.int32)
+  for i, h in enumerate(histories):
+    log[i, :len(h)] = h
+    lens[i] = len(h)
+  return log, lens
+
+
+@pytest.mark.parametrize("game", ["tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y"])
+def test_dense_log_entry_points_equal_the_per_state_ones(libs, game):
+  """ref_replay_log / ref_state_dump_log (the BASELINE-size checker calls of the GPU tests) =
+  ref_replay_batch / ref_state_dump on the same roots, terminal states included, and the oracle
+  taking the same roots through ragged_from_log."""
+  from oracle_lib import ragged_from_log
+  orc, ref = libs
+  roots = []
+  for p in range(120):
+    acts, _, _ = orc.replay(game, [], seed=6, playout=p, max_steps=(5 * p) % 37)
+    roots.append(acts)                       # some of them are terminal (short games)
+  full, _, _ = orc.replay(game, [], seed=6, playout=999)
+  roots.append(full)                         # one certainly terminal root
+  log, lens = _log_of(roots, 256)
+  for R in (1, 3):
+    a = ref.replay_log(game, log, lens, rollouts=R, seed=17, first_playout=40, threads=3)
+    b = ref.replay_batch(game, roots, rollouts=R, seed=17, first_playout=40, threads=2)
+    c = orc.replay_batch(game, ragged_from_log(log, lens), rollouts=R, seed=17, first_playout=40)
+    for x, y, z in zip(a, b[:3], c[:3]):
+      assert np.array_equal(x, y) and np.array_equal(x, z)
+  players = (np.arange(len(roots)) % 2).astype(np.uint8)
+  d = ref.state_dump_log(game, log, lens, players, threads=3)
+  for i, h in enumerate(roots):
+    one = ref.state_dump(game, h, int(players[i]))
+    assert np.array_equal(d["obs"][i], one["obs"])
+    assert np.nonzero(d["mask"][i])[0].tolist() == one["legal"]
+    assert d["current_player"][i] == one["current_player"] and bool(d["terminal"][i]) == one["terminal"]
+  assert d["terminal"][-1] == 1 and d["mask"][-1].sum() == 0
