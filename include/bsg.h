@@ -291,6 +291,25 @@ int bsg_forest_info(bsg_forest* f, double info[4]);
 int bsg_forest_selftest(int game, int n_trees, int sims, int sims_resume, int leaf_batch, int n_rollouts,
                         int solve, uint64_t seed, const int64_t* history, int n_history);
 
+/* Value-only playouts (bsg_playout_io.value_only above: hex, y) that ALLOCATE NOTHING.  No
+ * counterpart in the reference; added for callers that
+ * cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The launch's scratch — its work counter and one parked board per playout (16 B hex, 48 B y) —
+ * lives in a file-scope `static __device__` array of 16 MiB (+ 256 B) that every GPU loading the
+ * library holds until exit, so one call runs at most bsg_noalloc_max_playouts(game) playouts
+ * (hex 1 048 576, y 349 525); more is refused with BSG_ERR_BAD_ARG and a message in
+ * bsg_last_error.  Same results as bsg_playouts with io.value_only = 1: ret0_dev [n_playouts],
+ * length_dev [n_playouts] (moves to the full board), root_sum_*_dev [n_roots] (+=, caller
+ * zeroes), totals_dev u64[4] (+=, caller zeroes); each may be NULL.  Calls no cudaMalloc /
+ * cudaFree / allocating library routine; stream-ordered on `stream`, no synchronisation.  Every
+ * call shares the one array: calls that overlap on the GPU (two streams, two engines of one
+ * device) race — keep them stream-ordered. */
+int bsg_noalloc_max_playouts(int game);
+int bsg_playouts_value_only_noalloc(bsg_engine* e, const void* roots_dev, int64_t n_roots,
+                                    int32_t rollouts_per_root, uint64_t seed, uint64_t first_playout,
+                                    int8_t* ret0_dev, uint8_t* length_dev, int32_t* root_sum_ret0_dev,
+                                    int32_t* root_sum_steps_dev, uint64_t* totals_dev, void* stream);
+
 /* Integer-issue microbenchmark used for the roofline denominator (bench.py): runs `iters`
  * dependent-chain iterations of `ilp` independent 32-bit ops per thread on every SM and
  * returns thread-instructions per second.  kind: 0 = LOP3/IADD3 mix (ALU pipe), 1 = IMAD

@@ -1492,6 +1492,117 @@ int bsg_forest_info(bsg_forest* f, double info[4]) {
   return BSG_OK;
 }
 
+// ---- value-only playouts without any allocation (
+// no counterpart in the reference).  The scratch of a value-only launch — the launch's work
+// counter and one parked board per playout — lives in a file-scope device array of a fixed,
+// modest size instead of the engine's cudaMalloc'ed buffers.  Every GPU that loads the library
+// holds the array until exit; every call shares it, so calls that overlap on the GPU race.
+}  // extern "C"
+
+namespace bsg {
+constexpr size_t kStaticScratchHeader = 256;                  // work counter (first word), padded
+constexpr size_t kStaticBoardBytes = (size_t)16 << 20;        // 16 MiB of parked boards
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchHeader + kStaticBoardBytes];
+}  // namespace bsg
+
+namespace {
+// Per device, once, with that device current: the device address of the array (its name is only
+// a host-side stand-in in host code) and the launch geometry of the two kernels.
+struct StaticScratchSetup {
+  unsigned char* ptr = nullptr;
+  int blocks_per_sm = 0;
+};
+template <class G>
+int static_scratch_setup(bsg_engine* e, StaticScratchSetup* out) {
+  static StaticScratchSetup per_device[kMaxDevices];
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lock(mu);
+  if (e->device < 0 || e->device >= kMaxDevices) return fail(e, BSG_ERR_BAD_ARG, "device index beyond the per-device table");
+  StaticScratchSetup& slot = per_device[e->device];
+  if (!slot.ptr) {
+    void* p = nullptr;
+    BSG_CUDA(e, cudaGetSymbolAddress(&p, g_static_scratch));
+    int b = 0;
+    BSG_CUDA(e, cudaFuncSetAttribute(playout_kernel<G, false, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                     cudaSharedmemCarveoutMaxShared));
+    BSG_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, playout_kernel<G, false, false, true>, kThreads, 0));
+    slot.blocks_per_sm = b > 0 ? b : 1;
+    slot.ptr = (unsigned char*)p;
+  }
+  *out = slot;
+  return BSG_OK;
+}
+
+struct NoAllocMaxOp {
+  template <class G> int operator()() const {
+    if constexpr (fillable<G>::value) return (int)(kStaticBoardBytes / ((size_t)G::kFillWords * 4));
+    else return 0;
+  }
+};
+
+struct NoAllocPlayoutOp {
+  bsg_engine* e; PlayoutArgs a; cudaStream_t st;
+  template <class G> int operator()() const {
+    if constexpr (fillable<G>::value) {
+      const size_t need = (size_t)a.n_playouts * G::kFillWords * 4;
+      if (need > kStaticBoardBytes)
+        return fail(e, BSG_ERR_BAD_ARG, "bsg_playouts_value_only_noalloc: " + std::to_string(a.n_playouts) +
+                    " playouts exceed the static scratch (" + std::to_string(kStaticBoardBytes / ((size_t)G::kFillWords * 4)) +
+                    " playouts of this game; bsg_noalloc_max_playouts)");
+      StaticScratchSetup su;
+      int rc = static_scratch_setup<G>(e, &su);
+      if (rc != BSG_OK) return rc;
+      PlayoutArgs b = a;
+      b.out_flags = out_flags_of(a.io);
+      // the array keeps the last call's contents: the work counter must start at zero (stream
+      // order); every playout of this launch overwrites its own board before it is read
+      b.work_counter = reinterpret_cast<uint32_t*>(su.ptr);
+      b.fill_boards = reinterpret_cast<uint32_t*>(su.ptr + kStaticScratchHeader);
+      b.fill_base = 0;
+      BSG_CUDA(e, cudaMemsetAsync(b.work_counter, 0, sizeof(uint32_t), st));
+      const int64_t need_blocks = ((int64_t)a.n_playouts + kThreads - 1) / kThreads;
+      const int64_t max_grid = (int64_t)e->sm_count * su.blocks_per_sm;
+      int grid = (int)(need_blocks < max_grid ? need_blocks : max_grid);
+      playout_kernel<G, false, false, true><<<grid < 1 ? 1 : grid, kThreads, 0, st>>>(b, (const typename G::Tables*)e->tables_dev);
+      BSG_CUDA(e, cudaGetLastError());
+      const int rgrid = (int)(need_blocks < (int64_t)e->sm_count * 8 ? need_blocks : (int64_t)e->sm_count * 8);
+      fill_resolve_kernel<G><<<rgrid < 1 ? 1 : rgrid, kThreads, 0, st>>>(b);
+      BSG_CUDA(e, cudaGetLastError());
+      return BSG_OK;
+    } else {
+      return fail(e, BSG_ERR_BAD_ARG, "value_only needs a game whose full board has exactly one winner (hex, y)");
+    }
+  }
+};
+}  // namespace
+
+extern "C" {
+
+int bsg_noalloc_max_playouts(int game) {
+  const int n = dispatch_device_game(game, NoAllocMaxOp{});
+  return n;
+}
+
+int bsg_playouts_value_only_noalloc(bsg_engine* e, const void* roots, int64_t n_roots, int32_t rollouts,
+                                    uint64_t seed, uint64_t first_playout, int8_t* ret0, uint8_t* length,
+                                    int32_t* root_sum_ret0, int32_t* root_sum_steps, uint64_t* totals,
+                                    void* stream) {
+  if (!e) return BSG_ERR_BAD_ARG;
+  if (!roots || n_roots < 0 || rollouts < 1) return fail(e, BSG_ERR_BAD_ARG, "bad roots/rollouts");
+  const int64_t total = n_roots * (int64_t)rollouts;
+  if (total >= ((int64_t)1 << 32) - (1 << 24)) return fail(e, BSG_ERR_BAD_ARG, "more than 2^32-2^24 playouts in one launch");
+  if (total == 0) return BSG_OK;
+  PlayoutArgs a;
+  memset(&a, 0, sizeof(a));
+  a.roots = roots; a.n_roots = n_roots; a.n_playouts = (uint32_t)total; a.rollouts = (uint32_t)rollouts;
+  a.first_playout = first_playout;
+  philox_schedule(seed, a.keys);
+  a.io.ret0 = ret0; a.io.length = length; a.io.root_sum_ret0 = root_sum_ret0;
+  a.io.root_sum_steps = root_sum_steps; a.io.totals = totals; a.io.value_only = 1;
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  return dispatch_device_game(e->game, NoAllocPlayoutOp{e, a, (cudaStream_t)stream});
+}
+
 int bsg_int_peak(bsg_engine* e, int kind, int iters, double* out) {
   if (!e || !out || iters < 1 || kind < 0 || kind > 6) return BSG_ERR_BAD_ARG;
   BSG_CUDA(e, cudaSetDevice(e->device));

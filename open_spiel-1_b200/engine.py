@@ -195,6 +195,23 @@ class Engine:
                                self._stream_ptr(stream)), self._h)
     self.launches += 1
 
+  def noalloc_max_playouts(self):
+    """Playouts one playouts_value_only_noalloc call can run (the static scratch's capacity)."""
+    return C.check(C.lib.bsg_noalloc_max_playouts(self.gid))
+
+  def playouts_value_only_noalloc(self, roots, n_roots, rollouts=1, seed=0, first_playout=0, *,
+                                  ret0=None, length=None, root_sum_ret0=None, root_sum_steps=None,
+                                  totals=None, stream=None):
+    """bsg_playouts_value_only_noalloc: value-only playouts (hex, y) whose scratch is a static
+    device array of the library — the call allocates nothing.  Same outputs as
+    playouts(..., value_only=True); at most noalloc_max_playouts() playouts per call; calls
+    that overlap on the GPU race on the shared array (include/bsg.h)."""
+    C.check(C.lib.bsg_playouts_value_only_noalloc(
+        self._h, self._p(roots), int(n_roots), int(rollouts), int(seed) & (2**64 - 1),
+        int(first_playout), self._p(ret0), self._p(length), self._p(root_sum_ret0),
+        self._p(root_sum_steps), self._p(totals), self._stream_ptr(stream)), self._h)
+    self.launches += 2
+
   def observations(self, states, n, players=None, out=None, legal_mask=None, want_mask=False,
                    stream=None):
     """Batched ObservationTensor (+ LegalActionsMask) writer.  Returns (obs, mask) device
