@@ -207,20 +207,222 @@ def run_reference_arm(args):
   return 0
 
 
+CFG5_TOTAL_SIMS = 1 << 20      # BASELINE cfg5: 1 Mi simulations per move, summed over all GPUs
+CFG5_ROLLOUTS = 256            # rollouts per leaf
+CFG5_SIMS_PER_TREE = 256       # => 4096 trees in the job, 4096 / N per GPU
+CFG5_SIMS_PER_STEP = 64        # simulations per tree between two all-reduces => 4 per move
+CFG5_LEAF_BATCH = 8
+
+
+def cfg5_roots(bsg):
+  """The empty board and 16 fixed mid-game connect_four roots (d ~ U{8..20} random legal moves,
+  host PRNG seeded with ROOT_SEED + 5, terminal states rejected) as mirror states; the same on
+  every rank."""
+  game = bsg.load_game("connect_four")
+  rng = np.random.RandomState(ROOT_SEED + 5)
+  roots = [game.new_initial_state()]
+  while len(roots) < 17:
+    s = game.new_initial_state()
+    for _ in range(int(rng.randint(8, 21))):
+      la = s.legal_actions()
+      if not la:
+        break
+      s.apply_action(la[int(rng.randint(len(la)))])
+    if not s.is_terminal():
+      roots.append(s)
+  return game, roots
+
+
+def best_of(bsg, root):
+  """(best action, its Q for the mover, visits) by the reference's final-move rule
+  (mcts.py:144-162 sort_key; ties to the lowest action id)."""
+  best = max(sorted(root.children, key=lambda c: c.action), key=bsg.SearchNode.sort_key)
+  q = best.total_reward / best.explore_count if best.explore_count else 0.0
+  return int(best.action), float(q), int(best.explore_count)
+
+
+def cfg5_single_tree_reference(bsg, local):
+  """Quality yardstick of cfg5, rank 0 only: ONE native tree (csrc/bsg_mcts.cuh = the
+  reference's MCTSBot search) with the whole 1 Mi-simulation budget on each of the 16 mid-game
+  roots, 256 rollouts per leaf."""
+  game, roots = cfg5_roots(bsg)
+  eng = bsg.Engine("connect_four", local)
+  out = []
+  t0 = time.perf_counter()
+  for i, st in enumerate(roots[1:]):
+    bot = bsg.NativeMCTSBot(game, 2.0, CFG5_TOTAL_SIMS, eng, n_rollouts=CFG5_ROLLOUTS, solve=True,
+                            seed=ROOT_SEED + 6, shuffle_seed=100 + i, leaf_batch=256)
+    out.append(best_of(bsg, bot.mcts_search(st)))
+    bot.close()
+  secs = time.perf_counter() - t0
+  eng.close()
+  return {"best": out, "seconds": secs,
+          "simulations_per_s": CFG5_TOTAL_SIMS * len(out) / secs}
+
+
+def run_cfg5(bsg, torch, dev, local, rank, world, dist, single_tree):
+  """BASELINE cfg5: connect_four root-parallel MCTS, 1 Mi simulations per move in the whole job,
+  256 rollouts per leaf, ONE int64 ncclAllReduce per search step on the engine's own stream
+  (bsg_forest_merge).  The job always holds 4096 trees of 256 simulations (4096 / N per GPU):
+  tree v is "virtual rank" v whatever the GPU count, so the merged root must not depend on N."""
+  from open_spiel_1_b200.forest import ForestMCTS
+  game, roots = cfg5_roots(bsg)
+  trees = CFG5_TOTAL_SIMS // CFG5_SIMS_PER_TREE // world
+  eng = bsg.Engine("connect_four", local)
+  ev = bsg.GpuRolloutEvaluator(eng, n_rollouts=CFG5_ROLLOUTS, seed=ROOT_SEED + 7)
+  forest = ForestMCTS(game, 2.0, CFG5_TOTAL_SIMS, ev, trees, sims_per_step=CFG5_SIMS_PER_STEP,
+                      solve=True, seed=5, leaf_batch=CFG5_LEAF_BATCH, device=dev)
+
+  def sync():
+    torch.cuda.synchronize(dev)
+    if dist is not None:
+      dist.barrier()
+      torch.cuda.synchronize(dev)
+
+  forest.mcts_search(roots[0])          # warm-up move
+  forest.allreduce_stats()
+  steps0, launches0 = forest.total_steps, forest.info()["launches"]
+  secs, results, sims = [], [], 0
+  for st in roots:
+    sync()
+    t0 = time.perf_counter()
+    root = forest.mcts_search(st)       # returns after the engine's stream has drained
+    secs.append(time.perf_counter() - t0)
+    results.append(root)
+    sims += sum(c.explore_count for c in root.children) + trees * world   # + each tree's first visit (the root)
+  ar = forest.allreduce_stats()
+  game_steps = forest.total_steps - steps0
+  launches = forest.info()["launches"] - launches0 + 4 * forest.n_steps * len(roots)
+  # identical merged root on every rank
+  tab = np.array([[c.action, c.explore_count, int(round(c.total_reward * CFG5_ROLLOUTS))]
+                  for r in results for c in sorted(r.children, key=lambda c: c.action)], np.int64)
+  tot_secs = float(sum(secs))
+  same = True
+  if dist is not None:
+    t = torch.tensor([tot_secs, float(game_steps)], dtype=torch.float64, device=dev)
+    mx = t.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    sm = t.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+    tot_secs, game_steps = float(mx[0]), float(sm[1])
+    ref = torch.from_numpy(tab).to(dev); mine = ref.clone()
+    dist.broadcast(ref, 0)
+    flag = torch.tensor([int(torch.equal(ref, mine))], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    same = bool(flag.item())
+  best = [best_of(bsg, r) for r in results]
+  out = {
+      "workload": "connect_four root-parallel MCTS: %d simulations per move in the whole job, %d "
+                  "rollouts/leaf, from the empty board and 16 fixed mid-game roots (d~U{8..20}); "
+                  "%d trees x %d simulations per GPU, leaf_batch %d, %d simulations per tree per "
+                  "search step" % (CFG5_TOTAL_SIMS, CFG5_ROLLOUTS, trees, CFG5_SIMS_PER_TREE,
+                                   CFG5_LEAF_BATCH, CFG5_SIMS_PER_STEP),
+      "n_gpus": world, "trees_per_gpu": trees, "moves": len(roots),
+      "simulations": sims, "seconds": tot_secs,
+      "ms_per_move": 1e3 * tot_secs / len(roots),
+      "simulations_per_s": sims / tot_secs,
+      "playouts_per_s": game_steps and sims * CFG5_ROLLOUTS / tot_secs,
+      "game_steps_per_s": game_steps / tot_secs,
+      "all_reduces": ar["count"] if world > 1 else 0, "search_steps": forest.n_steps * len(roots),
+      "allreduce_mean_us": ar["mean_us"], "allreduce_max_us": ar["max_us"],
+      "collective": ("ncclAllReduce(int64 sum, %d B) on the engine's own communicator and stream "
+                     "(bsg_forest_merge), CUDA events around it" % (7 * 5 * 8)) if world > 1 else
+                    "world size 1: no collective",
+      "merged_root_identical_on_all_ranks": same,
+      "best_actions": [b[0] for b in best],
+      "root_table_checksum": int(np.bitwise_xor.reduce((tab * np.array([1, 1000003, 7919], np.int64)).sum(1))),
+      "trade_off": "1 Mi simulations per move = trees x simulations per tree: 4096 x 256 keeps a "
+                   "real budget per tree (the alternative, 16384 x 64, fills the GPU better and searches "
+                   "worse); one tree with the whole budget is the quality yardstick below",
+      "gpu_launches": int(launches),
+  }
+  if single_tree is not None:
+    agree = sum(1 for a, b in zip(best[1:], single_tree["best"]) if a[0] == b[0])
+    dq = [abs(a[1] - b[1]) for a, b in zip(best[1:], single_tree["best"])]
+    out["quality_vs_one_1Mi_simulation_tree"] = {
+        "roots": len(single_tree["best"]), "best_action_agreement": agree,
+        "mean_abs_diff_of_best_child_value": float(np.mean(dq)), "max_abs_diff": float(np.max(dq)),
+        "single_tree_best_actions": [b[0] for b in single_tree["best"]],
+        "single_tree_simulations_per_s": single_tree["simulations_per_s"],
+        "note": "one native host tree (the reference's MCTSBot search, csrc/bsg_mcts.cuh) with all "
+                "1 Mi simulations per root, 256 rollouts/leaf, leaf_batch 256, on one GPU"}
+  forest.close()
+  eng.close()
+  return out
+
+
+def cpu_mcts_baselines():
+  """the reference's own MCTS on the box's host cores.  C++
+  MCTSBot + RandomRolloutEvaluator (algorithms/mcts.cc) one bot per thread for the cfg1 and cfg5
+  shapes (ref_mcts_selfplay), and the unmodified python/algorithms/mcts.py for cfg1 exactly as
+  python/examples/mcts.py runs it.  Bounded samples; rates in simulations/s."""
+  from oracle_lib import Reference, reference_path, reference_python
+  out = {"kind": "reference", "unit": "simulations/s"}
+  if not os.path.exists(reference_path()):
+    return {"kind": "port", "unavailable": "oracle/_ref/libspiel_ref.so not built"}
+  ref = Reference()
+  threads = os.cpu_count() or 1
+  out["cores"] = threads
+  secs, mv, sims, _ = ref.mcts_selfplay("tic_tac_toe", 20, 1000, 1, threads=1)
+  out["cfg1_cpp_1_thread"] = sims / secs
+  secs, mv, sims, _ = ref.mcts_selfplay("tic_tac_toe", 20, 1000, 1, threads=threads)
+  out["cfg1_cpp_all_threads"] = sims / secs
+  secs, mv, sims, _ = ref.mcts_selfplay("connect_four", 1, 128, CFG5_ROLLOUTS, threads=threads)
+  out["cfg5_cpp_all_threads"] = sims / secs
+  out["cfg5_cpp_playouts_per_s"] = sims * CFG5_ROLLOUTS / secs
+  out["sample"] = ("cfg1: 20 self-play games of tic_tac_toe per thread, 1000 sims/move, n_rollouts=1, "
+                   "uct_c=2; cfg5 shape: one self-play game of connect_four per thread at 128 "
+                   "sims/move x 256 rollouts/leaf (the reference has no root-parallel mode: one "
+                   "independent bot per thread, rate summed)")
+  mods = reference_python()
+  if mods is not None:
+    pyspiel, ref_mcts = mods
+    rgame = pyspiel.load_game("tic_tac_toe")
+    ev = ref_mcts.RandomRolloutEvaluator(1, np.random.RandomState(7))
+    sims = 0
+    t0 = time.perf_counter()
+    for g in range(2):
+      bot = ref_mcts.MCTSBot(rgame, 2.0, 1000, ev, solve=True, random_state=np.random.RandomState(3 + g))
+      state = rgame.new_initial_state()
+      while not state.is_terminal():
+        root = bot.mcts_search(state)
+        sims += root.explore_count
+        state.apply_action(root.best_child().action)
+    out["cfg1_python_mcts_py_1_process"] = sims / (time.perf_counter() - t0)
+  return out
+
+
 def run_ours(args):
   import torch
   import open_spiel_1_b200 as bsg
   from open_spiel_1_b200.roots import make_roots, ROOT_DEPTHS
 
   rank, world, local = dist_env()
+  torch.cuda.set_device(local)
+  dev = torch.device("cuda", local)
+  game = args.game
+  # ---- rank 0 only, BEFORE the process group exists (the other ranks wait in the rendezvous,
+  # not in an NCCL barrier that would keep their GPUs spinning): the CPU arms and the one-tree
+  # quality yardstick of cfg5
+  pre = {}
+  if rank == 0:
+    if not args.no_cpu_baseline:
+      pre["cpu_baseline"] = cpu_baseline_block(args)
+      try:
+        pre["cpu_baseline"]["mcts"] = cpu_mcts_baselines()
+      except Exception as ex:
+        pre["cpu_baseline"]["mcts"] = {"error": repr(ex)}
+    if not args.no_extras and game == "connect_four":
+      try:
+        pre["single_tree"] = cfg5_single_tree_reference(bsg, local)
+        if world == 1:
+          import bench_mcts
+          pre["mcts_cfg1"] = bench_mcts.run_cfg1(argparse.Namespace(sims=1000, games=3, leaf_batch=256), bsg, local)
+      except Exception as ex:
+        pre["pre_error"] = repr(ex)
   if world > 1:
     import torch.distributed as dist
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
   else:
     dist = None
-  torch.cuda.set_device(local)
-  dev = torch.device("cuda", local)
-  game = args.game
   eng = bsg.Engine(game, local)
   n = int(args.playouts)
   dmin, dmax = ROOT_DEPTHS[game]
@@ -236,6 +438,14 @@ def run_ours(args):
     if dist is not None:
       dist.barrier()
     torch.cuda.synchronize(dev)
+
+  def reduce_max_sum(vals):
+    t = torch.tensor(vals, dtype=torch.float64, device=dev)
+    if dist is None:
+      return t.tolist(), t.tolist()
+    mx = t.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    sm = t.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+    return mx.tolist(), sm.tolist()
 
   def one_step(i):
     eng.playouts(states, n, 1, seed=ROOT_SEED, first_playout=first + i * n, ret0=ret0,
@@ -260,42 +470,22 @@ def run_ours(args):
   clocks = sampler.stop() if rank == 0 else None
   gpu_launches = eng.launches - launches0
   tot = totals.cpu().numpy().astype(np.int64)
-  stats = torch.tensor([ms, float(tot[0]), float(tot[1])], dtype=torch.float64, device=dev)
-  if dist is not None:
-    mx = stats.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-    sm = stats.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-    ms_max, playouts, steps = float(mx[0]), float(sm[1]), float(sm[2])
-  else:
-    ms_max, playouts, steps = ms, float(tot[0]), float(tot[1])
+  mx, sm = reduce_max_sum([ms, float(tot[0]), float(tot[1])])
+  ms_max, playouts, steps = mx[0], sm[1], sm[2]
   value = steps / (ms_max * 1e-3)
 
-  # ---- e2e through the host-buffer C-ABI call (pinned host roots, copies in the timed region)
-  host_roots = torch.empty(states.numel(), dtype=torch.uint8, pin_memory=True)
-  host_roots.copy_(states)
-  torch.cuda.synchronize(dev)
-  host_np = host_roots.numpy()
-  e2e_steps_n = max(2, min(args.steps, 5))
-  for i in range(2):
-    eng.playouts_host(host_np, n, 1, seed=ROOT_SEED, first_playout=first + i * n)
-  barrier()
-  t0 = time.perf_counter()
-  e2e_game_steps = 0
-  for i in range(e2e_steps_n):
-    t, _, _ = eng.playouts_host(host_np, n, 1, seed=ROOT_SEED, first_playout=first + (args.warmup + i) * n)
-    e2e_game_steps += int(t[1])
-  torch.cuda.synchronize(dev)
-  e2e_s = time.perf_counter() - t0
-  e2e_stats = torch.tensor([e2e_s, float(e2e_game_steps)], dtype=torch.float64, device=dev)
-  if dist is not None:
-    mx = e2e_stats.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-    sm = e2e_stats.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-    e2e_value = float(sm[1]) / float(mx[0])
-  else:
-    e2e_value = e2e_game_steps / e2e_s
+  e2e = e2e_block(args, eng, torch, dev, states, n, first, barrier, reduce_max_sum, world)
 
   extras = {}
+  if not args.no_extras:
+    extras.update(side_numbers(args, eng, torch, dev, rank, world, reduce_max_sum))
+    if game == "connect_four":
+      try:
+        extras["mcts_cfg5"] = run_cfg5(bsg, torch, dev, local, rank, world, dist, pre.get("single_tree"))
+      except Exception as ex:   # a side block must never kill the headline line
+        extras["mcts_cfg5"] = {"error": repr(ex)}
   if rank == 0:
-    extras = rank0_extras(args, eng, torch, dev, value / world, ms_max / args.steps, n)
+    extras.update(roofline_block(args, eng, value / world, ms_max / args.steps, n))
   if dist is not None:
     dist.barrier()
     dist.destroy_process_group()
@@ -317,12 +507,17 @@ def run_ours(args):
                  "l2_policy": "inputs larger than L2 (%d MB of roots per step)" % (states.numel() >> 20),
                  "parallelism": "playouts sharded by root across %d GPU(s), no data-path collective" % world},
       "clocks": clocks,
-      "e2e": {"value": e2e_value, "unit": "game-steps/s",
-              "h2d_bytes_per_step": int(states.numel()), "d2h_bytes_per_step": 32,
-              "api": "bsg_playouts_host (C ABI, pinned host roots in, totals out)"},
+      "e2e": e2e,
       "gpu_launches": gpu_launches,
   }
   line.update(extras)
+  line.pop("_peak_int", None)
+  if "cpu_baseline" in pre:
+    line["cpu_baseline"] = pre["cpu_baseline"]
+  if "mcts_cfg1" in pre:
+    line["mcts_cfg1"] = pre["mcts_cfg1"]
+  if "pre_error" in pre:
+    line["pre_error"] = pre["pre_error"]
   print(json.dumps(line))
   return 0
 
@@ -340,16 +535,104 @@ def time_kernel(torch, dev, fn, reps=5, warm=2):
   return e0.elapsed_time(e1) / reps
 
 
-def rank0_extras(args, eng, torch, dev, steps_per_s_per_gpu, kernel_ms, n):
-  """roofline, cpu_baseline and side numbers; rank 0 only, outside the headline timed region."""
-  import open_spiel_1_b200 as bsg
-  from open_spiel_1_b200.roots import make_roots, ROOT_DEPTHS
-  out = {}
-  peaks_path = os.path.join(REPO, "MEASURED_PEAKS.json")
-  hbm_peak, hbm_src = 6650.0, "fallback (B200_PROFILING.md)"
-  if os.path.exists(peaks_path):
-    with open(peaks_path) as f:
-      hbm_peak, hbm_src = float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+def e2e_block(args, eng, torch, dev, states, n, first, barrier, reduce_max_sum, world):
+  """The same metric through the host-buffer C-ABI call (pinned host roots, copies inside the
+  timed region), max over ranks; plus what bounds it: the H2D bandwidth of the very same pinned
+  buffer measured in the same job at this N, and a variant that returns per-root results (what
+  evaluate_batch consumes) instead of the 32-byte totals."""
+  host_roots = torch.empty(states.numel(), dtype=torch.uint8, pin_memory=True)
+  host_roots.copy_(states)
+  torch.cuda.synchronize(dev)
+  host_np = host_roots.numpy()
+  reps = max(2, min(args.steps, 5))
+  for i in range(2):
+    eng.playouts_host(host_np, n, 1, seed=ROOT_SEED, first_playout=first + i * n)
+  barrier()
+  t0 = time.perf_counter()
+  game_steps = 0
+  for i in range(reps):
+    t, _, _ = eng.playouts_host(host_np, n, 1, seed=ROOT_SEED, first_playout=first + (args.warmup + i) * n)
+    game_steps += int(t[1])
+  torch.cuda.synchronize(dev)
+  secs = time.perf_counter() - t0
+  mx, sm = reduce_max_sum([secs, float(game_steps)])
+  out = {"value": sm[1] / mx[0], "unit": "game-steps/s",
+         "h2d_bytes_per_step": int(states.numel()), "d2h_bytes_per_step": 32,
+         "api": "bsg_playouts_host (C ABI, pinned host roots in, totals out)"}
+  # H2D alone: the same pinned buffer, all ranks at once (what caps e2e when N GPUs share one
+  # host's memory system)
+  scratch = torch.empty_like(states)
+  scratch.copy_(host_roots, non_blocking=True)
+  barrier()
+  e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+  e0.record()
+  for _ in range(reps):
+    scratch.copy_(host_roots, non_blocking=True)
+  e1.record()
+  torch.cuda.synchronize(dev)
+  h2d_ms = e0.elapsed_time(e1) / reps
+  mx, _ = reduce_max_sum([h2d_ms])
+  gbs = states.numel() / (mx[0] * 1e-3) / 1e9
+  out["h2d_only_gbs"] = gbs * world
+  out["h2d_only_gbs_per_gpu"] = gbs
+  out["h2d_only_ceiling_game_steps_per_s"] = sm[1] / reps / (mx[0] * 1e-3)
+  out["numa_nodes"] = numa_summary(eng.device)
+  del scratch
+  # per-root results
+  try:
+    for i in range(2):
+      eng.playouts_host(host_np, n, 1, seed=ROOT_SEED, first_playout=first + i * n, want_root_sums=True)
+    barrier()
+    t0 = time.perf_counter()
+    game_steps = 0
+    d2h = 0
+    for i in range(reps):
+      t, rr, rs = eng.playouts_host(host_np, n, 1, seed=ROOT_SEED, first_playout=first + (args.warmup + i) * n,
+                                    want_root_sums=True)
+      game_steps += int(t[1])
+      d2h = rr.nbytes + rs.nbytes + 32
+    torch.cuda.synchronize(dev)
+    secs = time.perf_counter() - t0
+    mx, sm = reduce_max_sum([secs, float(game_steps)])
+    out["per_root_results"] = {"value": sm[1] / mx[0], "unit": "game-steps/s",
+                               "h2d_bytes_per_step": int(states.numel()), "d2h_bytes_per_step": int(d2h),
+                               "api": "bsg_playouts_host with per-root return and step sums copied back"}
+  except Exception as ex:
+    out["per_root_results"] = {"error": repr(ex)}
+  del host_roots
+  return out
+
+
+def numa_summary(device):
+  """NUMA node of this GPU and the node count of the host, from sysfs (best effort)."""
+  try:
+    import glob
+    nodes = len(glob.glob("/sys/devices/system/node/node[0-9]*"))
+    bus = subprocess.check_output(["nvidia-smi", "-i", str(device), "--query-gpu=pci.bus_id",
+                                   "--format=csv,noheader"], text=True).strip().lower()
+    path = "/sys/bus/pci/devices/%s/numa_node" % bus[-12:]
+    node = open(path).read().strip() if os.path.exists(path) else "?"
+    return {"host_nodes": nodes, "gpu_node": node}
+  except Exception:
+    return None
+
+
+def cpu_baseline_block(args):
+  threads = os.cpu_count() or 1
+  hist = sample_histories(args.game, 4096, ROOT_SEED + 2)
+  v_all = cpu_reference_run(args.game, hist, args.cpu_seconds, threads)
+  v_one = cpu_reference_run(args.game, hist, min(args.cpu_seconds, 4.0), 1)
+  return {
+      "value": v_all[0], "unit": "game-steps/s", "cores": v_all[4], "kind": v_all[3],
+      "sample": "%d playouts from 4096 synthetic mid-game roots (d~U{8..20}), %.1f s, reference "
+                "State::Clone/LegalActions/ApplyAction loop, one std::thread per core" % (v_all[2], v_all[5]),
+      "single_core_value": v_one[0], "playouts_per_s": v_all[1],
+      "cpu_model": cpu_model(),
+  }
+
+
+def roofline_block(args, eng, steps_per_s_per_gpu, kernel_ms, n):
+  """Integer-issue roofline of the playout kernel; rank 0."""
   # integer-issue peak measured live on this GPU: best of ALU-only, IMAD-only and mixed chains
   kinds = {0: "LOP3+IADD3 (ALU pipe)", 1: "IMAD (FMA pipe)", 2: "SHF+LOP3+IMAD 2:1",
            3: "LOP3+IMAD 1:1"}
@@ -357,98 +640,100 @@ def rank0_extras(args, eng, torch, dev, steps_per_s_per_gpu, kernel_ms, n):
   peak_int = max(peaks.values())
   ops = OPS_PER_STEP[args.game]
   achieved = steps_per_s_per_gpu * ops
-  out["roofline"] = {
+  return {"roofline": {
       "bound": "int_issue", "kernel": "playout_kernel<ConnectFour,false>",
       "achieved": achieved / 1e12, "peak": peak_int / 1e12, "unit": "T thread-instr/s",
       "frac": achieved / peak_int, "traffic": ncu_traffic_bytes("playout_kernel<ConnectFour, 0"),
+      "traffic_source": "constant from the newest committed ncu --set full capture under profiles/ "
+                        "(dram__bytes_read.sum + dram__bytes_write.sum of one launch), not measured by this run",
       "algorithmic_ops_per_step": ops,
       "peak_source": "bsg_int_peak microbenchmark, live: " + ", ".join(
           "%s=%.2fT" % (kinds[k], peaks[k] / 1e12) for k in kinds),
       "kernel_ms": kernel_ms,
       "note": "the path is integer/branchy by design (north_star): the bound is the integer "
               "issue rate, not HBM or tensor; algorithmic HBM bytes are 8 B root + 2 B results per "
-              "playout (~1 B/step); traffic = dram read+write bytes of one launch from the newest "
-              "ncu --set full capture under profiles/",
+              "playout (~1 B/step)",
       "hbm_achieved_gbs": n * (eng.state_bytes + 2) / (kernel_ms * 1e-3) / 1e9,
-  }
-  if not args.no_extras:
-    # observation writer: HBM-write bound (breakthrough, 784 algorithmic B/state)
-    side = {}
-    try:
-      e_bt = bsg.Engine("breakthrough", eng.device)
-      n_obs = 1 << 22
-      st, _ = make_roots(e_bt, n_obs, 0, 40, seed=ROOT_SEED + 3)
-      obs = torch.empty((n_obs, 3, 8, 8), dtype=torch.float32, device=dev)
-      ms = time_kernel(torch, dev, lambda: e_bt.observations(st, n_obs, None, out=obs))
-      gbs = n_obs * 784 / (ms * 1e-3) / 1e9
-      out["obs_roofline"] = {"bound": "hbm", "kernel": "expand_kernel<Breakthrough,false>",
-                             "achieved": gbs, "peak": hbm_peak, "unit": "GB/s",
-                             "frac": gbs / hbm_peak, "traffic": ncu_traffic_bytes("expand_kernel<Breakthrough, 0"),
-                             "peak_source": hbm_src,
-                             "states": n_obs, "obs_per_s": n_obs / (ms * 1e-3),
-                             "algorithmic_bytes_per_state": 784}
-      del obs, st
-      e_bt.close()
-      # BASELINE cfg3: breakthrough playouts + ObservationTensor / legal-mask write-out of every
-      # visited state (the AlphaZero actor's records), all on the device
-      e_bt = bsg.Engine("breakthrough", eng.device)
-      n_tr = 1 << 18
-      st, _ = make_roots(e_bt, n_tr, 0, 40, seed=ROOT_SEED + 5)
-      rec = {}
+  }, "_peak_int": peak_int}
 
-      def run_traj():
-        rec["t"] = e_bt.trajectories(st, n_tr, 1, seed=9, want_actions=True)
-      # two warm-up calls: each call allocates ~18 GB of outputs while the previous call's are
-      # still referenced, so only from the third call on does the caching allocator reuse blocks
-      ms = time_kernel(torch, dev, run_traj, reps=3, warm=2)
-      total = rec["t"]["total"]
-      out["trajectory_cfg3"] = {
-          "workload": "breakthrough: %d playouts, observation [3,8,8] f32 + legal mask [768] u8 + "
-                      "action of every decision point" % n_tr,
-          "records": total, "ms": ms, "records_per_s": total / (ms * 1e-3),
-          "bytes_written_per_record": 768 + 768 + 20,
-          "output_gb_per_s": total * (768 + 768 + 20) / (ms * 1e-3) / 1e9}
-      rec.clear()
-      del st
-      e_bt.close()
-      torch.cuda.empty_cache()
-      for g, npl in (("tic_tac_toe", 1 << 24), ("breakthrough", 1 << 22), ("hex", 1 << 20),
-                     ("pentago", 1 << 22), ("othello", 1 << 21), ("y", 1 << 21)):
-        e_g = bsg.Engine(g, eng.device)
-        dmin, dmax = ROOT_DEPTHS[g]
-        st, _ = make_roots(e_g, npl, dmin, dmax, seed=ROOT_SEED + 4)
-        tot = torch.zeros(4, dtype=torch.int64, device=dev)
-        ms = time_kernel(torch, dev, lambda: e_g.playouts(st, npl, 1, seed=7, totals=tot), reps=3, warm=1)
-        t = tot.cpu().numpy()
-        steps_per_launch = float(t[1]) / 4.0
-        side[g] = {"playouts": npl, "ms": ms, "game_steps_per_s": steps_per_launch / (ms * 1e-3),
-                   "playouts_per_s": npl / (ms * 1e-3),
-                   "int_roofline_frac": steps_per_launch / (ms * 1e-3) * OPS_PER_STEP[g] / peak_int}
-        if g in ("hex", "y"):
-          # value-only launch (bsg_playout_io.value_only): same returns, plain stones to a full
-          # board + one reading of the winner; what an Evaluator needs
-          tot.zero_()
-          ms_v = time_kernel(torch, dev, lambda: e_g.playouts(st, npl, 1, seed=7, totals=tot, value_only=True),
-                             reps=3, warm=1)
-          side[g]["value_only"] = {"ms": ms_v, "playouts_per_s": npl / (ms_v * 1e-3),
-                                   "speedup_in_playouts": ms / ms_v,
-                                   "sum_ret0_equal": bool(int(tot.cpu().numpy()[2]) == int(t[2]))}
-        e_g.close()
-    except Exception as ex:  # side numbers must never kill the headline line
-      side["error"] = repr(ex)
-    out["other_games"] = side
-  if not args.no_cpu_baseline:
-    threads = os.cpu_count() or 1
-    hist = sample_histories(args.game, 4096, ROOT_SEED + 2)
-    v_all = cpu_reference_run(args.game, hist, args.cpu_seconds, threads)
-    v_one = cpu_reference_run(args.game, hist, min(args.cpu_seconds, 4.0), 1)
-    out["cpu_baseline"] = {
-        "value": v_all[0], "unit": "game-steps/s", "cores": v_all[4], "kind": v_all[3],
-        "sample": "%d playouts from 4096 synthetic mid-game roots (d~U{8..20}), %.1f s, reference "
-                  "State::Clone/LegalActions/ApplyAction loop, one std::thread per core" % (v_all[2], v_all[5]),
-        "single_core_value": v_one[0], "playouts_per_s": v_all[1],
-        "cpu_model": cpu_model(),
-    }
+
+def side_numbers(args, eng, torch, dev, rank, world, reduce_max_sum):
+  """Side numbers on EVERY rank (weak scaling, reduced: max time, summed work): observation
+  writer roofline, cfg3 trajectory write-out, cfg3 / cfg4 and the other games' playout rates."""
+  import open_spiel_1_b200 as bsg
+  from open_spiel_1_b200.roots import make_roots, ROOT_DEPTHS
+  out, side = {}, {}
+  peaks_path = os.path.join(REPO, "MEASURED_PEAKS.json")
+  hbm_peak, hbm_src = 6650.0, "fallback (B200_PROFILING.md)"
+  if os.path.exists(peaks_path):
+    with open(peaks_path) as f:
+      hbm_peak, hbm_src = float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+  peak_int = max(eng.int_peak(k, 2000) for k in (2, 3))
+  try:
+    # observation writer: HBM-write bound (breakthrough, 784 algorithmic B/state, SURVEY 8d)
+    e_bt = bsg.Engine("breakthrough", eng.device)
+    n_obs = 1 << 22
+    st, _ = make_roots(e_bt, n_obs, 0, 40, seed=ROOT_SEED + 3 + 1000 * rank)
+    obs = torch.empty((n_obs, 3, 8, 8), dtype=torch.float32, device=dev)
+    ms = time_kernel(torch, dev, lambda: e_bt.observations(st, n_obs, None, out=obs))
+    mx, _ = reduce_max_sum([ms])
+    gbs = n_obs * 784 / (mx[0] * 1e-3) / 1e9
+    out["obs_roofline"] = {"bound": "hbm", "kernel": "expand_kernel<Breakthrough,false>",
+                           "achieved": gbs, "peak": hbm_peak, "unit": "GB/s",
+                           "frac": gbs / hbm_peak, "traffic": ncu_traffic_bytes("expand_kernel<Breakthrough, 0"),
+                           "traffic_source": "constant from the newest committed ncu capture under profiles/",
+                           "peak_source": hbm_src, "per_gpu": True, "n_gpus": world,
+                           "states": n_obs, "obs_per_s": n_obs * world / (mx[0] * 1e-3),
+                           "algorithmic_bytes_per_state": 784}
+    del obs, st
+    # BASELINE cfg3: breakthrough playouts + ObservationTensor / legal-mask write-out of every
+    # visited state (the AlphaZero actor's records), all on the device
+    n_tr = 1 << 18
+    st, _ = make_roots(e_bt, n_tr, 0, 40, seed=ROOT_SEED + 5 + 1000 * rank)
+    rec = {}
+
+    def run_traj():
+      rec["t"] = e_bt.trajectories(st, n_tr, 1, seed=9, want_actions=True)
+    ms = time_kernel(torch, dev, run_traj, reps=3, warm=2)
+    total = rec["t"]["total"]
+    mx, sm = reduce_max_sum([ms, float(total)])
+    out["trajectory_cfg3"] = {
+        "workload": "breakthrough: %d playouts per GPU, observation [3,8,8] f32 + legal mask [768] u8 + "
+                    "action of every decision point" % n_tr,
+        "n_gpus": world, "records": sm[1], "ms": mx[0], "records_per_s": sm[1] / (mx[0] * 1e-3),
+        "bytes_written_per_record": 768 + 768 + 20,
+        "output_gb_per_s": sm[1] * (768 + 768 + 20) / (mx[0] * 1e-3) / 1e9}
+    rec.clear()
+    del st
+    e_bt.close()
+    torch.cuda.empty_cache()
+    for g, npl in (("tic_tac_toe", 1 << 24), ("breakthrough", 1 << 22), ("hex", 1 << 20),
+                   ("pentago", 1 << 22), ("othello", 1 << 21), ("y", 1 << 21)):
+      e_g = bsg.Engine(g, eng.device)
+      dmin, dmax = ROOT_DEPTHS[g]
+      st, _ = make_roots(e_g, npl, dmin, dmax, seed=ROOT_SEED + 4 + 1000 * rank)
+      tot = torch.zeros(4, dtype=torch.int64, device=dev)
+      ms = time_kernel(torch, dev, lambda: e_g.playouts(st, npl, 1, seed=7, totals=tot), reps=3, warm=1)
+      t = tot.cpu().numpy()
+      mx, sm = reduce_max_sum([ms, float(t[1]) / 4.0])
+      rate = sm[1] / (mx[0] * 1e-3)
+      side[g] = {"playouts_per_gpu": npl, "n_gpus": world, "ms": mx[0], "game_steps_per_s": rate,
+                 "playouts_per_s": npl * world / (mx[0] * 1e-3),
+                 "int_roofline_frac": rate / world * OPS_PER_STEP[g] / peak_int}
+      if g in ("hex", "y"):
+        # value-only launch (bsg_playout_io.value_only): same returns, plain stones to a full
+        # board + one reading of the winner; what an Evaluator needs
+        tot.zero_()
+        ms_v = time_kernel(torch, dev, lambda: e_g.playouts(st, npl, 1, seed=7, totals=tot, value_only=True),
+                           reps=3, warm=1)
+        mxv, _ = reduce_max_sum([ms_v])
+        side[g]["value_only"] = {"ms": mxv[0], "playouts_per_s": npl * world / (mxv[0] * 1e-3),
+                                 "speedup_in_playouts": mx[0] / mxv[0],
+                                 "sum_ret0_equal": bool(int(tot.cpu().numpy()[2]) == int(t[2]))}
+      e_g.close()
+  except Exception as ex:  # side numbers must never kill the headline line
+    side["error"] = repr(ex)
+  out["other_games"] = side
   return out
 
 

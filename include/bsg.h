@@ -57,6 +57,7 @@ extern "C" {
 #define BSG_ERR_CUDA (-4)
 #define BSG_ERR_NO_DEVICE (-5)
 #define BSG_ERR_STUCK_LANE (-6) /* a non-terminal state without legal actions was met */
+#define BSG_ERR_NCCL (-7)       /* libnccl could not be loaded, or an NCCL call failed */
 
 #define BSG_TERMINAL_PLAYER (-4) /* kTerminalPlayerId, open_spiel/spiel.h:48 */
 
@@ -277,6 +278,28 @@ int bsg_forest_search(bsg_forest* f, const void* root_host, int64_t simulations_
  * all-reduce over ranks). */
 int bsg_forest_pack_root(bsg_forest* f, const int64_t* base_dev, int64_t* out_dev);
 int bsg_forest_install_root(bsg_forest* f, const int64_t* base_dev, const int64_t* summed_dev);
+/* Root-parallel search over several GPUs without torch ("one
+ * ncclAllReduce per search step").  The engine owns an NCCL communicator of its own; NCCL is
+ * loaded with dlopen("libnccl.so.2") at the first call, so the library has no link-time
+ * dependency on it.  bsg_comm_unique_id is ncclGetUniqueId (call it on one rank and hand the 128
+ * bytes to the others by any means: MPI, a file, torch.distributed, a socket); bsg_comm_init is
+ * ncclCommInitRank with the engine's device current (collective: every rank calls it).
+ * bsg_comm_ranks is 1 without a communicator. */
+int bsg_comm_unique_id(uint8_t id_out[128]);
+int bsg_comm_init(bsg_engine* e, int n_ranks, int rank, const uint8_t id[128]);
+int bsg_comm_destroy(bsg_engine* e);
+int bsg_comm_ranks(const bsg_engine* e);
+/* The merge of one search step (python/algorithms/mcts.py:116-122 statistics of the root's
+ * children, summed over all trees of all ranks), stream-ordered on the engine's stream with no
+ * host synchronisation: pack the deltas since the last merge, ONE int64 ncclAllReduce(sum) over
+ * the engine's communicator (none = world size 1 = no collective), install the global
+ * statistics into every tree.  first_step != 0 starts a new move (the base is zeroed).  The
+ * forest keeps base and sum buffers itself; bsg_forest_pack_root / _install_root below remain
+ * for callers that run the collective themselves. */
+int bsg_forest_merge(bsg_forest* f, int first_step);
+/* Synchronises and reports the all-reduces issued by bsg_forest_merge since the last call:
+ * {count, mean microseconds, max microseconds}, timed with CUDA events on the engine's stream. */
+int bsg_forest_allreduce_stats(bsg_forest* f, double stats_out[3]);
 /* Root children of one tree (as bsg_mcts_root_children); info = {root visits, root solved,
  * root returns[0], nodes used}.  Returns the number of children. */
 int bsg_forest_tree_root(bsg_forest* f, int32_t tree, int capacity, int64_t* actions, int64_t* visits,

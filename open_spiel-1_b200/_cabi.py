@@ -14,8 +14,8 @@ vp = ctypes.c_void_p
 i32, i64, u32, u64 = ctypes.c_int32, ctypes.c_int64, ctypes.c_uint32, ctypes.c_uint64
 
 OK = 0
-ERR_BAD_GAME, ERR_BAD_ARG, ERR_ILLEGAL_ACTION, ERR_CUDA, ERR_NO_DEVICE, ERR_STUCK_LANE = (
-    -1, -2, -3, -4, -5, -6)
+ERR_BAD_GAME, ERR_BAD_ARG, ERR_ILLEGAL_ACTION, ERR_CUDA, ERR_NO_DEVICE, ERR_STUCK_LANE, ERR_NCCL = (
+    -1, -2, -3, -4, -5, -6, -7)
 TERMINAL_PLAYER = -4
 
 TIC_TAC_TOE, CONNECT_FOUR, BREAKTHROUGH, HEX, HEX5_HOST_ONLY, PENTAGO, OTHELLO, Y, Y9_HOST_ONLY = 0, 1, 2, 3, 4, 5, 6, 7, 8
@@ -109,6 +109,12 @@ def _load():
       "bsg_forest_install_root": (ctypes.c_int, [vp, vp, vp]),
       "bsg_forest_tree_root": (ctypes.c_int, [vp, i32, ctypes.c_int, vp, vp, vp, vp, vp]),
       "bsg_forest_info": (ctypes.c_int, [vp, vp]),
+      "bsg_comm_unique_id": (ctypes.c_int, [vp]),
+      "bsg_comm_init": (ctypes.c_int, [vp, ctypes.c_int, ctypes.c_int, vp]),
+      "bsg_comm_destroy": (ctypes.c_int, [vp]),
+      "bsg_comm_ranks": (ctypes.c_int, [vp]),
+      "bsg_forest_merge": (ctypes.c_int, [vp, ctypes.c_int]),
+      "bsg_forest_allreduce_stats": (ctypes.c_int, [vp, vp]),
       "bsg_forest_selftest": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                              ctypes.c_int, ctypes.c_int, ctypes.c_int, u64, vp, ctypes.c_int]),
   }

@@ -264,6 +264,148 @@ struct ForestTree {
     F.n_pending[v] = 0;
   }
 
+#if defined(__CUDACC__)
+  // ---- the same two halves of a round with one WARP per tree (device only).  The search is
+  // unchanged — the lanes only share the work inside a step of it: the children of a node are
+  // scored in parallel (one child per lane, strided when a node has more than 32) and an ordered
+  // butterfly reduction returns what the sequential scan of descend() returns — the first
+  // unvisited child if there is one, else the lowest-index child of maximal value; the virtual
+  // visits of a path and the plain (unsolved) backups touch distinct nodes and run one node per
+  // lane.  Expansion (the Philox shuffle) and solver backups stay on lane 0.  Every branch below
+  // is warp-uniform: all lanes read the same memory after a __syncwarp().
+  struct Pick { double val; int32_t idx; int32_t inf; };
+  __device__ static bool pick_beats(const Pick& a, const Pick& b) {   // a before b in the scan's order
+    if (b.idx < 0) return a.idx >= 0;
+    if (a.idx < 0) return false;
+    if (a.inf != b.inf) return a.inf != 0;
+    if (a.inf) return a.idx < b.idx;
+    if (a.val != b.val) return a.val > b.val;
+    return a.idx < b.idx;
+  }
+  __device__ static void descend_warp(const ForestView& F, int v, const Tables& tab) {
+    const unsigned full = 0xFFFFFFFFu;
+    const int lane = (int)(threadIdx.x & 31);
+    MctsNode* nodes = F.nodes + (size_t)v * F.cap;
+    int n_nodes = F.n_nodes[v];
+    const int B = F.batch;
+    const int64_t left = F.sims_left[v];
+    const int k = (int)(left < B ? left : B);
+    State root_state;
+    G::load(root_state, F.root, 1, 0);
+    const bool batched = B > 1;
+    int n_pending = 0, n_leaves = 0;
+    const uint64_t base = F.next_playout[v];
+    for (int i = 0; i < k; ++i) {
+      int32_t* path = F.paths + ((size_t)v * B + i) * F.depth;
+      int len = 1;
+      if (lane == 0) path[0] = 0;
+      State working = root_state;
+      int32_t node = 0;
+      for (;;) {
+        MctsNode nd = nodes[node];
+        if (G::terminal(working) || (nd.explore + nd.virt) <= 0) break;
+        if (nd.n_children == 0 && nd.first_child < 0) {
+          if (lane == 0) expand(F, v, nodes, n_nodes, node, working);
+          __syncwarp();
+          n_nodes = __shfl_sync(full, n_nodes, 0);
+          nd = nodes[node];
+          if (nd.first_child < 0) break;          // node pool exhausted (*F.error is set)
+        }
+        const int64_t parent_n = nd.explore + nd.virt;
+        if (parent_n >= F.logtab_n) { if (lane == 0) *F.error = 2; break; }
+        const double log_pn = F.logtab[parent_n];
+        const double log_pn2 = parent_n > 2 ? log_pn : F.logtab[2];
+        Pick mine;
+        mine.val = 0.0; mine.idx = -1; mine.inf = 0;
+        for (int c = lane; c < nd.n_children; c += 32) {
+          bool inf;
+          const double val = value_of(F, nodes[nd.first_child + c], log_pn, log_pn2, batched, inf);
+          Pick cand;
+          cand.val = val; cand.idx = nd.first_child + c; cand.inf = inf ? 1 : 0;
+          if (pick_beats(cand, mine)) mine = cand;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          Pick other;
+          other.val = __shfl_xor_sync(full, mine.val, o);
+          other.idx = __shfl_xor_sync(full, mine.idx, o);
+          other.inf = __shfl_xor_sync(full, mine.inf, o);
+          if (pick_beats(other, mine)) mine = other;
+        }
+        const int32_t best = mine.idx;
+        if (best < 0) break;
+        forest_apply<G>(working, nodes[best].action, tab, 0);
+        node = best;
+        if (len < F.depth) { if (lane == 0) path[len] = node; ++len; }
+        else { if (lane == 0) *F.error = 3; break; }
+      }
+      __syncwarp();
+      for (int p = lane; p < len; p += 32) nodes[path[p]].virt += 1;   // distinct nodes
+      __syncwarp();
+      const bool term = G::terminal(working);
+      if (lane == 0) {
+        F.path_len[(size_t)v * B + i] = len;
+        if (term) {
+          F.leaf_kind[(size_t)v * B + i] = 2;
+          F.leaf_out0[(size_t)v * B + i] = (double)outcome_ret0(G::outcome(working));
+        } else {
+          F.leaf_kind[(size_t)v * B + i] = 1;
+          const size_t slot = (size_t)v * B + n_leaves;
+          G::store(working, F.leaf_states, (int64_t)F.n_trees * B, (int64_t)slot);
+          F.leaf_base[slot] = base + (uint64_t)n_leaves * (uint64_t)F.n_rollouts;
+        }
+      }
+      if (!term) ++n_leaves;
+      ++n_pending;
+      if (term && F.solve) break;
+    }
+    for (int i = n_leaves + lane; i < B; i += 32) F.leaf_base[(size_t)v * B + i] = kSkipRoot;
+    if (lane == 0) {
+      F.next_playout[v] = base + (uint64_t)n_leaves * (uint64_t)F.n_rollouts;
+      F.n_pending[v] = n_pending;
+      F.n_nodes[v] = n_nodes;
+    }
+  }
+
+  __device__ static void finish_round_warp(const ForestView& F, int v) {
+    const int lane = (int)(threadIdx.x & 31);
+    MctsNode* nodes = F.nodes + (size_t)v * F.cap;
+    const int B = F.batch;
+    const int n_pending = F.n_pending[v];
+    int vi = 0;
+    for (int i = 0; i < n_pending; ++i) {
+      const int32_t* path = F.paths + ((size_t)v * B + i) * F.depth;
+      const int len = F.path_len[(size_t)v * B + i];
+      if (F.leaf_kind[(size_t)v * B + i] == 2) {
+        if (lane == 0) {
+          for (int p = 0; p < len; ++p) nodes[path[p]].virt -= 1;
+          const double r0 = F.leaf_out0[(size_t)v * B + i];
+          MctsNode& last = nodes[path[len - 1]];
+          last.has_outcome = 1;
+          last.out0 = r0;
+          backup(nodes, path, len, r0, F.solve != 0);
+        }
+      } else {
+        // backup(.., solved = false): every node of the path gets the same three updates
+        const double r0 = (double)F.leaf_ret[(size_t)v * B + vi] / (double)F.n_rollouts;
+        for (int p = lane; p < len; p += 32) {
+          MctsNode& nd = nodes[path[p]];
+          nd.virt -= 1;
+          nd.reward += ret_of(r0, nd.player);
+          nd.explore += 1;
+        }
+        ++vi;
+      }
+      __syncwarp();
+    }
+    if (lane == 0) {
+      F.sims_left[v] -= n_pending;
+      if (nodes[0].has_outcome) F.sims_left[v] = 0;
+      F.n_pending[v] = 0;
+    }
+  }
+#endif
+
   // A tree that ran no simulation still joins the merge with an expanded root
   // (parallel.RootParallelMCTS._search_tree / MctsTree::expand_root).
   BSG_HD static void expand_root(const ForestView& F, int v) {

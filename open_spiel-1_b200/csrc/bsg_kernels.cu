@@ -15,6 +15,8 @@
 //    state); only the bookkeeping is predicated.
 #include <type_traits>
 #include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>   // types and enums only: the library is loaded with dlopen (bsg_comm_*)
 #include <stdio.h>
 
 #include <mutex>
@@ -576,6 +578,8 @@ struct bsg_engine {
   cudaStream_t own_stream = nullptr;
   cudaStream_t aux_stream = nullptr;   // second lane of the chunked host path (copy/compute overlap)
   cudaEvent_t ev_a = nullptr, ev_b = nullptr;
+  ncclComm_t comm = nullptr;           // bsg_comm_init: this engine's own NCCL communicator
+  int comm_ranks = 1, comm_rank = 0;
   std::string err;
 };
 
@@ -634,17 +638,21 @@ __global__ void forest_reset_kernel(ForestView F) {
   const int v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v < F.n_trees) ForestTree<G>::reset(F, v);
 }
+// descend / finish: one WARP per tree (ForestTree::descend_warp); the other forest kernels are
+// one thread per tree.
+constexpr int kForestWarpThreads = 128;   // 4 trees per CTA
 template <class G>
-__global__ void forest_descend_kernel(ForestView F, const typename G::Tables* __restrict__ tab) {
-  const int v = blockIdx.x * blockDim.x + threadIdx.x;
-  if (v >= F.n_trees) return;
-  if (F.sims_left[v] > 0) atomicAdd(F.active, 1u);
-  ForestTree<G>::descend(F, v, *tab);
+__global__ void __launch_bounds__(kForestWarpThreads)
+forest_descend_kernel(ForestView F, const typename G::Tables* __restrict__ tab) {
+  const int v = (blockIdx.x * kForestWarpThreads + threadIdx.x) >> 5;
+  if (v >= F.n_trees) return;           // whole warps leave
+  if ((threadIdx.x & 31) == 0 && F.sims_left[v] > 0) atomicAdd(F.active, 1u);
+  ForestTree<G>::descend_warp(F, v, *tab);
 }
 template <class G>
-__global__ void forest_finish_kernel(ForestView F) {
-  const int v = blockIdx.x * blockDim.x + threadIdx.x;
-  if (v < F.n_trees) ForestTree<G>::finish_round(F, v);
+__global__ void __launch_bounds__(kForestWarpThreads) forest_finish_kernel(ForestView F) {
+  const int v = (blockIdx.x * kForestWarpThreads + threadIdx.x) >> 5;
+  if (v < F.n_trees) ForestTree<G>::finish_round_warp(F, v);
 }
 template <class G>
 __global__ void forest_expand_root_kernel(ForestView F) {
@@ -662,6 +670,46 @@ __global__ void forest_pack_kernel(ForestView F, const int64_t* base, unsigned l
 __global__ void forest_install_kernel(ForestView F, const int64_t* base, const int64_t* summed) {
   const int v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v < F.n_trees) forest_install_root(F, v, base, summed);
+}
+
+__global__ void forest_totals_kernel(const uint64_t* step_totals, uint64_t* acc) {
+  if (threadIdx.x < 4) acc[threadIdx.x] += step_totals[threadIdx.x];
+}
+__global__ void forest_base_add_kernel(int64_t* base, const int64_t* summed, int n_actions) {
+  const int a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a < n_actions) {
+    base[2 * a] += summed[a * bsg::kMergeFields];
+    base[2 * a + 1] += summed[a * bsg::kMergeFields + 1];
+  }
+}
+
+// NCCL, loaded at run time (a torch process already has libnccl.so.2 mapped; any other host
+// gets the system library).  Only the five calls the root merge needs.
+struct NcclApi {
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+  bool ok = false;
+  std::string why;
+};
+const NcclApi& nccl_api() {
+  static NcclApi api = [] {
+    NcclApi a;
+    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) { a.why = std::string("dlopen(libnccl.so.2): ") + dlerror(); return a; }
+    a.GetUniqueId = (decltype(a.GetUniqueId))dlsym(h, "ncclGetUniqueId");
+    a.CommInitRank = (decltype(a.CommInitRank))dlsym(h, "ncclCommInitRank");
+    a.CommDestroy = (decltype(a.CommDestroy))dlsym(h, "ncclCommDestroy");
+    a.AllReduce = (decltype(a.AllReduce))dlsym(h, "ncclAllReduce");
+    a.GetErrorString = (decltype(a.GetErrorString))dlsym(h, "ncclGetErrorString");
+    a.ok = a.GetUniqueId && a.CommInitRank && a.CommDestroy && a.AllReduce && a.GetErrorString;
+    if (!a.ok) a.why = "libnccl lacks a required symbol";
+    return a;
+  }();
+  return api;
 }
 
 template <class G, bool kFull, bool kBase = false, bool kFill = false>
@@ -792,6 +840,7 @@ const char* bsg_error_string(int code) {
     case BSG_ERR_CUDA: return "CUDA error";
     case BSG_ERR_NO_DEVICE: return "no CUDA device";
     case BSG_ERR_STUCK_LANE: return "non-terminal state without legal actions";
+    case BSG_ERR_NCCL: return "NCCL error";
     default: return "unknown error";
   }
 }
@@ -924,6 +973,7 @@ int bsg_create(int game, int device, bsg_engine** out) {
 void bsg_destroy(bsg_engine* e) {
   if (!e) return;
   if (e->device >= 0) cudaSetDevice(e->device);
+  if (e->comm && nccl_api().ok) nccl_api().CommDestroy(e->comm);
   if (e->tables_dev) cudaFree(e->tables_dev);
   if (e->d_roots) cudaFree(e->d_roots);
   if (e->d_out) cudaFree(e->d_out);
@@ -1191,8 +1241,20 @@ struct bsg_forest {
   uint64_t* d_totals = nullptr;
   uint64_t eval_seed = 0;
   int64_t rounds = 0, launches = 0, game_steps = 0;
+  // bsg_forest_merge: dense per-action buffers {base [A][2], summed [A][5]} and the CUDA events
+  // around every all-reduce (read by bsg_forest_allreduce_stats)
+  int64_t* d_base = nullptr;
+  int64_t* d_merge = nullptr;
+  uint64_t* d_step_totals = nullptr;    // {playouts, game steps, sum ret0, stuck lanes} of all searches so far
+  int num_actions = 0;
+  std::vector<cudaEvent_t> ar_events;   // pairs, in issue order
+  size_t ar_used = 0;
+  int64_t merges = 0;
   std::string err;
-  ~bsg_forest() { for (void* p : allocs) cudaFree(p); }
+  ~bsg_forest() {
+    for (void* p : allocs) cudaFree(p);
+    for (cudaEvent_t ev : ar_events) cudaEventDestroy(ev);
+  }
 };
 
 namespace {
@@ -1293,19 +1355,57 @@ struct ForestSelfTestOp {
 };
 
 struct ForestSearchOp {
-  bsg_forest* f; int resume;
+  bsg_forest* f; int resume; int64_t max_left;   // max_left: the largest per-tree budget of this step
+  template <class G> int launch_leaves(cudaStream_t st) const {
+    bsg_engine* e = f->e;
+    const bsg::ForestView& F = f->F;
+    const int64_t slots = (int64_t)F.n_trees * F.batch;
+    PlayoutArgs a;
+    memset(&a, 0, sizeof(a));
+    a.roots = F.leaf_states; a.n_roots = slots; a.root0 = 0;
+    a.n_playouts = (uint32_t)(slots * F.n_rollouts); a.rollouts = (uint32_t)F.n_rollouts;
+    a.first_playout = 0;
+    bsg::philox_schedule(f->eval_seed, a.keys);
+    a.io.root_sum_ret0 = F.leaf_ret;
+    a.io.totals = f->d_totals;
+    a.io.root_playout_base = F.leaf_base;
+    int rc;
+    if constexpr (fillable<G>::value) {   // bsg_engine_set_value_only: same leaf values, fewer instructions
+      a.io.value_only = e->value_only;
+      rc = e->value_only ? launch_playouts<G, false, true, true>(e, a, st) : launch_playouts<G, false, true>(e, a, st);
+    } else {
+      rc = launch_playouts<G, false, true>(e, a, st);
+    }
+    f->launches += 3 + (a.io.value_only ? 1 : 0);   // descend + playouts (+ fill_resolve) + finish
+    return rc;
+  }
   template <class G> int operator()() const {
     bsg_engine* e = f->e;
     cudaStream_t st = e->own_stream;
     const bsg::ForestView& F = f->F;
     const int grid = forest_grid(f);
+    const int wgrid = (F.n_trees * 32 + kForestWarpThreads - 1) / kForestWarpThreads;
     if (!resume) forest_reset_kernel<G><<<grid, kForestThreads, 0, st>>>(F);
     BSG_CUDA(e, cudaMemsetAsync(f->d_totals, 0, 4 * sizeof(uint64_t), st));
     const int64_t slots = (int64_t)F.n_trees * F.batch;
+    // A tree with k simulations left needs ceil(k / batch) rounds unless a solved terminal leaf
+    // cut one of its rounds short, so that many rounds are enqueued back to back with no host
+    // synchronisation (a tree that is done idles through them: its slots are skipped by the
+    // playout kernel); after them the loop below asks once per round whether any tree is still
+    // searching — normally the first answer is "none".
+    const int64_t burst = (max_left + F.batch - 1) / F.batch;
+    int rc;
+    for (int64_t r = 0; r < burst; ++r) {
+      BSG_CUDA(e, cudaMemsetAsync(F.leaf_ret, 0, (size_t)slots * sizeof(int32_t), st));
+      forest_descend_kernel<G><<<wgrid, kForestWarpThreads, 0, st>>>(F, (const typename G::Tables*)e->tables_dev);
+      if ((rc = launch_leaves<G>(st)) != BSG_OK) return rc;
+      forest_finish_kernel<G><<<wgrid, kForestWarpThreads, 0, st>>>(F);
+      f->rounds += 1;
+    }
     for (;;) {
       BSG_CUDA(e, cudaMemsetAsync(F.active, 0, sizeof(uint32_t), st));
       BSG_CUDA(e, cudaMemsetAsync(F.leaf_ret, 0, (size_t)slots * sizeof(int32_t), st));
-      forest_descend_kernel<G><<<grid, kForestThreads, 0, st>>>(F, (const typename G::Tables*)e->tables_dev);
+      forest_descend_kernel<G><<<wgrid, kForestWarpThreads, 0, st>>>(F, (const typename G::Tables*)e->tables_dev);
       uint32_t hdr[2] = {0, 0};   // {active trees, error}
       BSG_CUDA(e, cudaMemcpyAsync(&hdr[0], F.active, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
       BSG_CUDA(e, cudaMemcpyAsync(&hdr[1], F.error, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
@@ -1315,35 +1415,16 @@ struct ForestSearchOp {
                : (hdr[1] == 2 ? "forest: log table exhausted (raise max_visits)" : "forest: path deeper than the game allows");
         return BSG_ERR_BAD_ARG;
       }
-      if (hdr[0] == 0) break;
-      PlayoutArgs a;
-      memset(&a, 0, sizeof(a));
-      a.roots = F.leaf_states; a.n_roots = slots; a.root0 = 0;
-      a.n_playouts = (uint32_t)(slots * F.n_rollouts); a.rollouts = (uint32_t)F.n_rollouts;
-      a.first_playout = 0;
-      bsg::philox_schedule(f->eval_seed, a.keys);
-      a.io.root_sum_ret0 = F.leaf_ret;
-      a.io.totals = f->d_totals;
-      a.io.root_playout_base = F.leaf_base;
-      int rc;
-      if constexpr (fillable<G>::value) {   // bsg_engine_set_value_only: same leaf values, fewer instructions
-        a.io.value_only = e->value_only;
-        rc = e->value_only ? launch_playouts<G, false, true, true>(e, a, st) : launch_playouts<G, false, true>(e, a, st);
-      } else {
-        rc = launch_playouts<G, false, true>(e, a, st);
-      }
-      if (rc != BSG_OK) return rc;
-      forest_finish_kernel<G><<<grid, kForestThreads, 0, st>>>(F);
+      if (hdr[0] == 0) { f->launches += 1; break; }   // the descent that found nothing to do
+      if ((rc = launch_leaves<G>(st)) != BSG_OK) return rc;
+      forest_finish_kernel<G><<<wgrid, kForestWarpThreads, 0, st>>>(F);
       f->rounds += 1;
-      f->launches += 3 + (a.io.value_only ? 1 : 0);   // + fill_resolve_kernel
     }
     forest_expand_root_kernel<G><<<grid, kForestThreads, 0, st>>>(F);
-    uint64_t tot[4];
-    BSG_CUDA(e, cudaMemcpyAsync(tot, f->d_totals, sizeof(tot), cudaMemcpyDeviceToHost, st));
-    BSG_CUDA(e, cudaStreamSynchronize(st));
+    // totals of this step's playouts (game steps, stuck lanes): accumulated on the device, read
+    // by bsg_forest_info / the next synchronising call
+    forest_totals_kernel<<<1, 32, 0, st>>>(f->d_totals, f->d_step_totals);
     BSG_CUDA(e, cudaGetLastError());
-    f->game_steps += (int64_t)tot[1];
-    if (tot[3] != 0) { f->err = "forest: non-terminal state without legal actions"; return BSG_ERR_STUCK_LANE; }
     return BSG_OK;
   }
 };
@@ -1395,6 +1476,10 @@ int bsg_forest_create(bsg_engine* e, int32_t n_trees, int32_t node_capacity, int
   if (rc == BSG_OK) rc = forest_alloc(f, &d_root, (size_t)bsg_state_bytes(e->game) + 64);
   if (rc == BSG_OK) rc = forest_alloc(f, &f->d_per_tree, T);
   if (rc == BSG_OK) rc = forest_alloc(f, &f->d_totals, 4);
+  f->num_actions = bsg_num_distinct_actions(e->game);
+  if (rc == BSG_OK) rc = forest_alloc(f, &f->d_step_totals, 4);
+  if (rc == BSG_OK) rc = forest_alloc(f, &f->d_base, (size_t)f->num_actions * 2);
+  if (rc == BSG_OK) rc = forest_alloc(f, &f->d_merge, (size_t)f->num_actions * bsg::kMergeFields);
   if (rc != BSG_OK) { e->err = f->err; delete f; return rc; }
   F.leaf_states = leaf_states;
   F.root = d_root;
@@ -1434,7 +1519,12 @@ int bsg_forest_search(bsg_forest* f, const void* root_host, int64_t simulations_
                                 cudaMemcpyHostToDevice, st));
   forest_fill_kernel<<<forest_grid(f), kForestThreads, 0, st>>>(
       f->F.sims_left, simulations_per_tree, per_tree_host ? f->d_per_tree : nullptr, f->F.n_trees);
-  return dispatch_device_game(e->game, ForestSearchOp{f, resume});
+  int64_t max_left = simulations_per_tree;
+  if (per_tree_host) {
+    max_left = 0;
+    for (int32_t v = 0; v < f->F.n_trees; ++v) if (per_tree_host[v] > max_left) max_left = per_tree_host[v];
+  }
+  return dispatch_device_game(e->game, ForestSearchOp{f, resume, max_left});
 }
 int bsg_forest_pack_root(bsg_forest* f, const int64_t* base_dev, int64_t* out_dev) {
   if (!f || !base_dev || !out_dev) return BSG_ERR_BAD_ARG;
@@ -1453,11 +1543,97 @@ int bsg_forest_install_root(bsg_forest* f, const int64_t* base_dev, const int64_
   BSG_CUDA(e, cudaStreamSynchronize(e->own_stream));
   return BSG_OK;
 }
+// ---- the engine's own NCCL communicator + the root merge on the engine's stream
+int bsg_comm_unique_id(uint8_t id_out[128]) {
+  if (!id_out) return BSG_ERR_BAD_ARG;
+  const NcclApi& api = nccl_api();
+  if (!api.ok) return BSG_ERR_NCCL;
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+  ncclUniqueId id;
+  if (api.GetUniqueId(&id) != ncclSuccess) return BSG_ERR_NCCL;
+  memcpy(id_out, &id, 128);
+  return BSG_OK;
+}
+int bsg_comm_init(bsg_engine* e, int n_ranks, int rank, const uint8_t id[128]) {
+  if (!e || !id || n_ranks < 1 || rank < 0 || rank >= n_ranks) return BSG_ERR_BAD_ARG;
+  const NcclApi& api = nccl_api();
+  if (!api.ok) return fail(e, BSG_ERR_NCCL, api.why);
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  if (e->comm) { api.CommDestroy(e->comm); e->comm = nullptr; }
+  ncclUniqueId uid;
+  memcpy(&uid, id, 128);
+  ncclResult_t st = api.CommInitRank(&e->comm, n_ranks, uid, rank);
+  if (st != ncclSuccess) { e->comm = nullptr; return fail(e, BSG_ERR_NCCL, std::string("ncclCommInitRank: ") + api.GetErrorString(st)); }
+  e->comm_ranks = n_ranks; e->comm_rank = rank;
+  return BSG_OK;
+}
+int bsg_comm_destroy(bsg_engine* e) {
+  if (!e) return BSG_ERR_BAD_ARG;
+  if (e->comm && nccl_api().ok) { cudaSetDevice(e->device); nccl_api().CommDestroy(e->comm); }
+  e->comm = nullptr; e->comm_ranks = 1; e->comm_rank = 0;
+  return BSG_OK;
+}
+int bsg_comm_ranks(const bsg_engine* e) { return e ? (e->comm ? e->comm_ranks : 1) : BSG_ERR_BAD_ARG; }
+
+// One search step's root merge, entirely on the engine's stream: zero the sum buffer, pack the
+// trees' root-child deltas since `base`, ONE int64 ncclAllReduce(sum) over the engine's
+// communicator (skipped without one: world size 1), install base + sum into every tree, advance
+// base.  No host synchronisation.
+int bsg_forest_merge(bsg_forest* f, int first_step) {
+  if (!f) return BSG_ERR_BAD_ARG;
+  bsg_engine* e = f->e;
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  cudaStream_t st = e->own_stream;
+  const int A = f->num_actions;
+  if (first_step) BSG_CUDA(e, cudaMemsetAsync(f->d_base, 0, (size_t)A * 2 * sizeof(int64_t), st));
+  BSG_CUDA(e, cudaMemsetAsync(f->d_merge, 0, (size_t)A * bsg::kMergeFields * sizeof(int64_t), st));
+  forest_pack_kernel<<<forest_grid(f), kForestThreads, 0, st>>>(f->F, f->d_base, (unsigned long long*)f->d_merge);
+  if (e->comm) {
+    if (f->ar_used + 2 > f->ar_events.size()) {
+      for (int k = 0; k < 2; ++k) {
+        cudaEvent_t ev;
+        BSG_CUDA(e, cudaEventCreate(&ev));
+        f->ar_events.push_back(ev);
+      }
+    }
+    BSG_CUDA(e, cudaEventRecord(f->ar_events[f->ar_used], st));
+    ncclResult_t rs = nccl_api().AllReduce(f->d_merge, f->d_merge, (size_t)A * bsg::kMergeFields, ncclInt64, ncclSum, e->comm, st);
+    if (rs != ncclSuccess) return fail(e, BSG_ERR_NCCL, std::string("ncclAllReduce: ") + nccl_api().GetErrorString(rs));
+    BSG_CUDA(e, cudaEventRecord(f->ar_events[f->ar_used + 1], st));
+    f->ar_used += 2;
+  }
+  forest_install_kernel<<<forest_grid(f), kForestThreads, 0, st>>>(f->F, f->d_base, f->d_merge);
+  forest_base_add_kernel<<<(A + 127) / 128, 128, 0, st>>>(f->d_base, f->d_merge, A);
+  BSG_CUDA(e, cudaGetLastError());
+  f->merges += 1;
+  return BSG_OK;
+}
+// Synchronises the engine's stream and reports the all-reduces issued by bsg_forest_merge since
+// the last call: stats = {count, mean microseconds, max microseconds} (CUDA events on the
+// engine's stream around each ncclAllReduce).
+int bsg_forest_allreduce_stats(bsg_forest* f, double stats[3]) {
+  if (!f || !stats) return BSG_ERR_BAD_ARG;
+  bsg_engine* e = f->e;
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  BSG_CUDA(e, cudaStreamSynchronize(e->own_stream));
+  double sum = 0, mx = 0;
+  const size_t n = f->ar_used / 2;
+  for (size_t i = 0; i < n; ++i) {
+    float ms = 0;
+    BSG_CUDA(e, cudaEventElapsedTime(&ms, f->ar_events[2 * i], f->ar_events[2 * i + 1]));
+    sum += ms * 1e3;
+    if (ms * 1e3 > mx) mx = ms * 1e3;
+  }
+  stats[0] = (double)n; stats[1] = n ? sum / (double)n : 0.0; stats[2] = mx;
+  f->ar_used = 0;
+  return BSG_OK;
+}
 int bsg_forest_tree_root(bsg_forest* f, int32_t tree, int capacity, int64_t* actions, int64_t* visits,
                          double* reward, int32_t* outcome, double info[4]) {
   if (!f || tree < 0 || tree >= f->F.n_trees) return BSG_ERR_BAD_ARG;
   bsg_engine* e = f->e;
   BSG_CUDA(e, cudaSetDevice(e->device));
+  BSG_CUDA(e, cudaStreamSynchronize(e->own_stream));   // a merge may still be in flight
   bsg::MctsNode root;
   const bsg::MctsNode* nodes = f->F.nodes + (size_t)tree * f->F.cap;
   BSG_CUDA(e, cudaMemcpy(&root, nodes, sizeof(root), cudaMemcpyDeviceToHost));
@@ -1487,6 +1663,15 @@ int bsg_forest_selftest(int game, int n_trees, int sims, int sims_resume, int le
 }
 int bsg_forest_info(bsg_forest* f, double info[4]) {
   if (!f || !info) return BSG_ERR_BAD_ARG;
+  {
+    bsg_engine* e = f->e;
+    BSG_CUDA(e, cudaSetDevice(e->device));
+    uint64_t tot[4];
+    BSG_CUDA(e, cudaMemcpyAsync(tot, f->d_step_totals, sizeof(tot), cudaMemcpyDeviceToHost, e->own_stream));
+    BSG_CUDA(e, cudaStreamSynchronize(e->own_stream));
+    f->game_steps = (int64_t)tot[1];
+    if (tot[3] != 0) { f->err = "forest: non-terminal state without legal actions"; return BSG_ERR_STUCK_LANE; }
+  }
   info[0] = (double)f->game_steps; info[1] = (double)f->launches; info[2] = (double)f->rounds;
   info[3] = (double)f->F.n_trees;
   return BSG_OK;

@@ -32,9 +32,19 @@ class ForestMCTS:
   `evaluator` supplies the engine, n_rollouts, the Philox seed and the playout-id base."""
 
   def __init__(self, game, uct_c, max_simulations, evaluator, n_trees, sims_per_step=None,
-               solve=True, seed=0, leaf_batch=32, device=None, group=None, node_capacity=None):
+               solve=True, seed=0, leaf_batch=32, device=None, group=None, node_capacity=None,
+               merge="engine"):
+    """merge = "engine" (default): the per-step root merge runs inside the library on the
+    engine's stream — pack, one ncclAllReduce over the ENGINE'S OWN communicator, install — with
+    no host synchronisation (bsg_forest_merge; the communicator is created here from a unique id
+    broadcast over torch.distributed, any other transport works).  merge = "torch": the
+    collective is torch.distributed.all_reduce around bsg_forest_pack_root / _install_root
+    (same result; kept for hosts that want to run the collective themselves)."""
     self.rank, self.world = _world(group)
     self.group = group
+    self.merge = merge
+    if merge not in ("engine", "torch"):
+      raise ValueError("merge must be 'engine' or 'torch'")
     self.device = device
     self.engine = evaluator.engine
     self.trees = int(n_trees)
@@ -62,6 +72,32 @@ class ForestMCTS:
     self._h = h
     self.all_reduces = 0
     self.last_root = None
+    if merge == "engine" and self.world > 1 and C.lib.bsg_comm_ranks(self.engine._h) != self.world:
+      self._init_engine_comm()
+
+  def _init_engine_comm(self):
+    """ncclGetUniqueId on rank 0, the 128 bytes broadcast over the existing process group,
+    ncclCommInitRank on every rank (bsg_comm_*)."""
+    import torch
+    import torch.distributed as dist
+    uid = np.zeros(128, np.uint8)
+    if self.rank == 0:
+      C.check(C.lib.bsg_comm_unique_id(uid.ctypes.data), self.engine._h)
+    backend = dist.get_backend(self.group)
+    t = torch.from_numpy(uid)
+    if backend == "nccl":
+      t = t.to(self.engine.torch_device)
+    src = dist.get_global_rank(self.group, 0) if self.group is not None else 0
+    dist.broadcast(t, src, group=self.group)
+    uid = t.cpu().numpy().copy()
+    C.check(C.lib.bsg_comm_init(self.engine._h, self.world, self.rank, uid.ctypes.data), self.engine._h)
+
+  def allreduce_stats(self):
+    """{count, mean_us, max_us} of the all-reduces bsg_forest_merge issued since the last call
+    (CUDA events on the engine's stream around each ncclAllReduce)."""
+    out = np.zeros(3, np.float64)
+    self._check(C.lib.bsg_forest_allreduce_stats(self._h, out.ctypes.data))
+    return {"count": int(out[0]), "mean_us": float(out[1]), "max_us": float(out[2])}
 
   def close(self):
     if getattr(self, "_h", None):
@@ -115,29 +151,38 @@ class ForestMCTS:
   def mcts_search(self, state):
     """Runs the sharded search; returns tree 0's root with the GLOBAL child statistics (equal
     in every tree of every rank)."""
-    import torch
     from .evaluator import _packed_of
-    dev = self.engine.torch_device
     packed = np.ascontiguousarray(_packed_of(self.engine.gid, state))
-    base = torch.zeros((self.num_actions, 2), dtype=torch.int64, device=dev)
     left = self.tree_simulations.copy()
-    for step in range(self.n_steps):
-      ks = np.minimum(left, self.sims_per_step).astype(np.int64)
-      left -= ks
-      self._check(C.lib.bsg_forest_search(self._h, packed.ctypes.data, 0, ks.ctypes.data,
-                                          1 if step else 0))
-      out = torch.zeros((self.num_actions, _MERGE_FIELDS), dtype=torch.int64, device=dev)
+    if self.merge == "engine":
+      for step in range(self.n_steps):
+        ks = np.minimum(left, self.sims_per_step).astype(np.int64)
+        left -= ks
+        self._check(C.lib.bsg_forest_search(self._h, packed.ctypes.data, 0, ks.ctypes.data,
+                                            1 if step else 0))
+        self._check(C.lib.bsg_forest_merge(self._h, 0 if step else 1))   # stream-ordered, no sync
+        self.all_reduces += 1
+    else:
+      import torch
+      dev = self.engine.torch_device
+      base = torch.zeros((self.num_actions, 2), dtype=torch.int64, device=dev)
+      for step in range(self.n_steps):
+        ks = np.minimum(left, self.sims_per_step).astype(np.int64)
+        left -= ks
+        self._check(C.lib.bsg_forest_search(self._h, packed.ctypes.data, 0, ks.ctypes.data,
+                                            1 if step else 0))
+        out = torch.zeros((self.num_actions, _MERGE_FIELDS), dtype=torch.int64, device=dev)
+        torch.cuda.synchronize(dev)
+        self._check(C.lib.bsg_forest_pack_root(self._h, base.data_ptr(), out.data_ptr()))
+        if self.world > 1:
+          import torch.distributed as dist
+          dist.all_reduce(out, group=self.group)     # int64 sums: order-independent
+        self.all_reduces += 1
+        torch.cuda.synchronize(dev)
+        self._check(C.lib.bsg_forest_install_root(self._h, base.data_ptr(), out.data_ptr()))
+        base += out[:, :2]
       torch.cuda.synchronize(dev)
-      self._check(C.lib.bsg_forest_pack_root(self._h, base.data_ptr(), out.data_ptr()))
-      if self.world > 1:
-        import torch.distributed as dist
-        dist.all_reduce(out, group=self.group)     # int64 sums: order-independent
-      self.all_reduces += 1
-      torch.cuda.synchronize(dev)
-      self._check(C.lib.bsg_forest_install_root(self._h, base.data_ptr(), out.data_ptr()))
-      base += out[:, :2]
-    torch.cuda.synchronize(dev)
-    self.last_root = self.tree_root(0, state.current_player())
+    self.last_root = self.tree_root(0, state.current_player())   # synchronises the engine's stream
     return self.last_root
 
   def step_with_policy(self, state):

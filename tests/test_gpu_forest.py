@@ -92,7 +92,8 @@ def test_large_forest_accounts_for_every_simulation(bsg):
   assert sum(c.explore_count for c in root.children) == trees * per_tree - trees   # first visit = the root itself
   assert forest.all_reduces == 2
   info = forest.info()
-  assert info["rounds"] <= 8 and info["launches"] == 3 * info["rounds"]
+  # per search step: the rounds enqueued back to back, then one descent that finds nothing left
+  assert info["rounds"] <= 8 and info["launches"] == 3 * info["rounds"] + forest.n_steps
   t0 = table(root, 32)
   for v in (1, 777, trees - 1):
     assert table(forest.tree_root(v, 0), 32) == t0
@@ -117,7 +118,36 @@ def test_forest_with_value_only_leaves_builds_the_same_trees(bsg, game, history)
     forest = ForestMCTS(g, UCT_C, 600, ev, 4, sims_per_step=50, solve=True, seed=9, leaf_batch=4)
     roots.append(table(forest.mcts_search(state), 16))
     info = forest.info()
-    assert info["launches"] == (4 if vo else 3) * info["rounds"]
+    assert info["launches"] == (4 if vo else 3) * info["rounds"] + forest.n_steps
     forest.close()
     eng.close()
   assert roots[0] == roots[1]
+
+
+def test_engine_side_merge_equals_the_torch_merge(bsg):
+  """bsg_forest_merge (pack, all-reduce, install, base advance on the engine's stream with no
+  host synchronisation) gives the root the caller-run merge gives, step for step, also when a
+  forest is used for a second move; world size 1 has no communicator and no collective."""
+  from open_spiel_1_b200.forest import ForestMCTS
+  from open_spiel_1_b200 import _cabi as C
+  g = bsg.load_game("connect_four")
+  tabs = {}
+  for merge in ("engine", "torch"):
+    eng = bsg.Engine("connect_four", 0)
+    assert C.lib.bsg_comm_ranks(eng._h) == 1
+    ev = bsg.GpuRolloutEvaluator(eng, n_rollouts=16, seed=4)
+    forest = ForestMCTS(g, UCT_C, 64 * 96, ev, 64, sims_per_step=24, solve=True, seed=2, leaf_batch=8,
+                        merge=merge)
+    state = g.new_initial_state()
+    out = []
+    for _ in range(3):                                  # three moves on one forest
+      root = forest.mcts_search(state)
+      out.append(table(root, 16))
+      state.apply_action(forest.step_with_policy(state)[1])
+    assert forest.all_reduces == 4 * 6                  # 96 / 24 steps, two searches per move
+    if merge == "engine":
+      assert forest.allreduce_stats()["count"] == 0     # no communicator, no collective
+    tabs[merge] = out
+    forest.close()
+    eng.close()
+  assert tabs["engine"] == tabs["torch"]
