@@ -578,25 +578,29 @@ def e2e_block(args, eng, torch, dev, states, n, first, barrier, reduce_max_sum, 
   out["h2d_only_ceiling_game_steps_per_s"] = sm[1] / reps / (mx[0] * 1e-3)
   out["numa_nodes"] = numa_summary(eng.device)
   del scratch
-  # per-root results
+  # per-playout results: (int)Returns()[0] and the move count of every playout copied back into
+  # page-locked host arrays (2 B per playout) — what evaluate_batch consumes
   try:
+    h_ret = torch.zeros(n, dtype=torch.int8, pin_memory=True)
+    h_len = torch.zeros(n, dtype=torch.uint8, pin_memory=True)
+    r_np, l_np = h_ret.numpy(), h_len.numpy()
     for i in range(2):
-      eng.playouts_host(host_np, n, 1, seed=ROOT_SEED, first_playout=first + i * n, want_root_sums=True)
+      eng.playouts_host_results(host_np, n, 1, seed=ROOT_SEED, first_playout=first + i * n, ret0=r_np, length=l_np)
     barrier()
     t0 = time.perf_counter()
     game_steps = 0
-    d2h = 0
     for i in range(reps):
-      t, rr, rs = eng.playouts_host(host_np, n, 1, seed=ROOT_SEED, first_playout=first + (args.warmup + i) * n,
-                                    want_root_sums=True)
+      t, _, _ = eng.playouts_host_results(host_np, n, 1, seed=ROOT_SEED, first_playout=first + (args.warmup + i) * n,
+                                          ret0=r_np, length=l_np)
       game_steps += int(t[1])
-      d2h = rr.nbytes + rs.nbytes + 32
     torch.cuda.synchronize(dev)
     secs = time.perf_counter() - t0
     mx, sm = reduce_max_sum([secs, float(game_steps)])
     out["per_root_results"] = {"value": sm[1] / mx[0], "unit": "game-steps/s",
-                               "h2d_bytes_per_step": int(states.numel()), "d2h_bytes_per_step": int(d2h),
-                               "api": "bsg_playouts_host with per-root return and step sums copied back"}
+                               "h2d_bytes_per_step": int(states.numel()), "d2h_bytes_per_step": 2 * n + 32,
+                               "checksum_ok": bool(int(l_np.astype(np.int64).sum()) == int(t[1])),
+                               "api": "bsg_playouts_host_results (C ABI): pinned host roots in, int8 return + "
+                                      "uint8 length per playout out, copied back behind each chunk's kernel"}
   except Exception as ex:
     out["per_root_results"] = {"error": repr(ex)}
   del host_roots

@@ -211,6 +211,15 @@ int bsg_playouts_host(bsg_engine* e, const void* roots_host, int64_t n_roots,
                       int32_t rollouts_per_root, uint64_t seed, uint64_t first_playout,
                       int64_t totals_out[4], int32_t* root_sum_ret0_host,
                       int32_t* root_sum_steps_host);
+/* bsg_playouts_host with PER-PLAYOUT results in host memory: ret0_host[p] = (int)Returns()[0]
+ * and length_host[p] = moves played by playout p (n_roots * rollouts_per_root entries each;
+ * either may be NULL) — the 2 bytes per playout a consumer of every root's value reads, e.g.
+ * RandomRolloutEvaluator.evaluate for a batch of leaves (python/algorithms/mcts.py:58-74) or a
+ * data pipeline.  Results of a chunk are copied back behind its kernel while the next chunk's
+ * roots are still arriving; page-locked caller buffers are used in place. */
+int bsg_playouts_host_results(bsg_engine* e, const void* roots_host, int64_t n_roots,
+                              int32_t rollouts_per_root, uint64_t seed, uint64_t first_playout,
+                              int64_t totals_out[4], int8_t* ret0_host, uint8_t* length_host);
 int bsg_observations_host(bsg_engine* e, const void* states_host, int64_t n,
                           const uint8_t* players_host, float* obs_host,
                           uint8_t* legal_mask_host);

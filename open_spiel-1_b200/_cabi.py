@@ -86,6 +86,7 @@ def _load():
       "bsg_observations": (ctypes.c_int, [vp, vp, i64, vp, vp, vp, vp]),
       "bsg_playouts_host": (ctypes.c_int, [vp, vp, i64, i32, u64, u64, vp, vp, vp]),
       "bsg_observations_host": (ctypes.c_int, [vp, vp, i64, vp, vp, vp]),
+      "bsg_playouts_host_results": (ctypes.c_int, [vp, vp, i64, i32, u64, u64, vp, vp, vp]),
       "bsg_int_peak": (ctypes.c_int, [vp, ctypes.c_int, ctypes.c_int, vp]),
       "bsg_noalloc_max_playouts": (ctypes.c_int, [ctypes.c_int]),
       "bsg_playouts_value_only_noalloc": (ctypes.c_int, [vp, vp, i64, i32, u64, u64, vp, vp, vp, vp, vp, vp]),

@@ -34,6 +34,7 @@ constexpr int kThreads = 256;
 constexpr int kChunkPlayouts = 128;   // playouts per work-counter draw of a warp
 constexpr int kWorkSlots = 1024;      // launches that may be in flight at once, per engine
 constexpr int kMaxDevices = 64;       // per-device caches of function attributes
+constexpr size_t kSmallCallBytes = 64 << 10;   // bsg_playouts_host: roots up to this size take the lean single-stream path
 
 struct PlayoutArgs {
   const void* roots;
@@ -738,9 +739,13 @@ int launch_playouts(bsg_engine* e, const PlayoutArgs& a, cudaStream_t st) {
   if (grid < 1) grid = 1;
   PlayoutArgs b = a;
   b.out_flags = out_flags_of(a.io);
-  // work counter of this launch: next slot of the engine's ring, zeroed in stream order
-  b.work_counter = e->d_work + (e->work_slot++ % kWorkSlots);
-  BSG_CUDA(e, cudaMemsetAsync(b.work_counter, 0, sizeof(uint32_t), st));
+  if (!b.work_counter) {
+    // work counter of this launch: next slot of the engine's ring, zeroed in stream order
+    // (a caller that already zeroed a counter of its own passes it in: bsg_playouts_host's
+    // small-call path folds it into its one memset)
+    b.work_counter = e->d_work + (e->work_slot++ % kWorkSlots);
+    BSG_CUDA(e, cudaMemsetAsync(b.work_counter, 0, sizeof(uint32_t), st));
+  }
   if constexpr (kFill) {
     // (the chunked host path sized the buffer for the whole call, so this does not reallocate
     // under a chunk that is still running)
@@ -1049,6 +1054,42 @@ int bsg_playouts_host(bsg_engine* e, const void* roots_host, int64_t n_roots, in
   size_t in_bytes = (size_t)n_roots * (size_t)bsg_state_bytes(e->game);
   size_t out_elems = (root_ret_host ? n_roots : 0) + (root_steps_host ? n_roots : 0);
   int rc;
+  if (in_bytes <= kSmallCallBytes && !e->value_only) {
+    // Small call (one leaf, or a batch of leaves of an MCTS round): fixed cost is what matters.
+    // One stream, no events, no pointer query (the roots are staged: copying <= 64 KB is
+    // cheaper than asking), ONE memset for {totals, work counter, root sums}, ONE copy back.
+    // Device layout of d_out here: [0,32) totals, [32,36) work counter, [64, ...) root sums.
+    const size_t res_bytes = 64 + out_elems * 4;
+    if ((rc = ensure(e, &e->d_roots, &e->d_roots_bytes, in_bytes, false)) != BSG_OK) return rc;
+    if ((rc = ensure(e, &e->d_out, &e->d_out_bytes, res_bytes, false)) != BSG_OK) return rc;
+    if ((rc = ensure(e, &e->h_pinned, &e->h_pinned_bytes, res_bytes + in_bytes + 64, true)) != BSG_OK) return rc;
+    char* h_res = (char*)e->h_pinned;
+    char* stage = h_res + ((res_bytes + 63) & ~(size_t)63);
+    memcpy(stage, roots_host, in_bytes);
+    cudaStream_t st = e->own_stream;
+    BSG_CUDA(e, cudaMemcpyAsync(e->d_roots, stage, in_bytes, cudaMemcpyHostToDevice, st));
+    BSG_CUDA(e, cudaMemsetAsync(e->d_out, 0, res_bytes, st));
+    PlayoutArgs a;
+    memset(&a, 0, sizeof(a));
+    a.roots = e->d_roots; a.n_roots = n_roots; a.root0 = 0;
+    a.n_playouts = (uint32_t)(n_roots * rollouts); a.rollouts = (uint32_t)rollouts;
+    a.first_playout = first_playout;
+    philox_schedule(seed, a.keys);
+    a.io.totals = (uint64_t*)e->d_out;
+    a.work_counter = (uint32_t*)((char*)e->d_out + 32);
+    int32_t* d_sums = (int32_t*)((char*)e->d_out + 64);
+    a.io.root_sum_ret0 = root_ret_host ? d_sums : nullptr;
+    a.io.root_sum_steps = root_steps_host ? d_sums + (root_ret_host ? n_roots : 0) : nullptr;
+    if ((rc = dispatch_device_game(e->game, PlayoutOp{e, a, st})) != BSG_OK) return rc;
+    BSG_CUDA(e, cudaMemcpyAsync(h_res, e->d_out, res_bytes, cudaMemcpyDeviceToHost, st));
+    BSG_CUDA(e, cudaStreamSynchronize(st));
+    const uint64_t* h_tot = (const uint64_t*)h_res;
+    for (int i = 0; i < 4; ++i) totals_out[i] = (int64_t)h_tot[i];
+    if (root_ret_host) memcpy(root_ret_host, h_res + 64, (size_t)n_roots * 4);
+    if (root_steps_host) memcpy(root_steps_host, h_res + 64 + (root_ret_host ? (size_t)n_roots * 4 : 0), (size_t)n_roots * 4);
+    if (totals_out[3] != 0) return fail(e, BSG_ERR_STUCK_LANE, "non-terminal state without legal actions");
+    return BSG_OK;
+  }
   if ((rc = ensure(e, &e->d_roots, &e->d_roots_bytes, in_bytes, false)) != BSG_OK) return rc;
   if ((rc = ensure(e, &e->d_out, &e->d_out_bytes, out_elems * 4 + 16, false)) != BSG_OK) return rc;
   // Page-locked caller memory (e.g. a torch pin_memory() tensor) is copied from directly;
@@ -1116,6 +1157,101 @@ int bsg_playouts_host(bsg_engine* e, const void* roots_host, int64_t n_roots, in
   for (int i = 0; i < 4; ++i) totals_out[i] = (int64_t)h_tot[i];
   if (root_ret_host) memcpy(root_ret_host, h_res + 32, (size_t)n_roots * 4);
   if (root_steps_host) memcpy(root_steps_host, h_res + 32 + (root_ret_host ? (size_t)n_roots * 4 : 0), (size_t)n_roots * 4);
+  if (totals_out[3] != 0) return fail(e, BSG_ERR_STUCK_LANE, "non-terminal state without legal actions");
+  return BSG_OK;
+}
+
+// Host-buffer playouts that return PER-PLAYOUT results — (int)Returns()[0] and the move count,
+// 2 bytes per playout — instead of totals only: what a caller that
+// consumes every root's value (evaluate_batch at rollouts = 1, a data pipeline) needs.  Same
+// two-stream chunking as bsg_playouts_host; each chunk's results are copied back in its own
+// stream right behind its kernel, so the D2H traffic rides under the next chunk's H2D copy (PCIe
+// is full duplex).  Page-locked caller buffers are read and written in place.
+int bsg_playouts_host_results(bsg_engine* e, const void* roots_host, int64_t n_roots, int32_t rollouts,
+                              uint64_t seed, uint64_t first_playout, int64_t totals_out[4],
+                              int8_t* ret0_host, uint8_t* length_host) {
+  if (!e) return BSG_ERR_BAD_ARG;
+  if (!roots_host || n_roots < 1 || rollouts < 1 || !totals_out || (!ret0_host && !length_host))
+    return fail(e, BSG_ERR_BAD_ARG, "bad host playout arguments");
+  if (e->value_only) return fail(e, BSG_ERR_BAD_ARG, "per-playout results need the exact kernels (value_only is set)");
+  const int64_t n_play = n_roots * (int64_t)rollouts;
+  if (n_play >= ((int64_t)1 << 32) - (1 << 24))
+    return fail(e, BSG_ERR_BAD_ARG, "more than 2^32-2^24 playouts in one call");
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  int plane_bytes[8];
+  const int n_planes = dispatch_device_game(e->game, PlaneOp{plane_bytes});
+  if (n_planes < 1) return fail(e, BSG_ERR_BAD_GAME, "no device kernels for this game");
+  const size_t in_bytes = (size_t)n_roots * (size_t)bsg_state_bytes(e->game);
+  const size_t out_bytes = (size_t)n_play * ((ret0_host ? 1 : 0) + (length_host ? 1 : 0));
+  int rc;
+  if ((rc = ensure(e, &e->d_roots, &e->d_roots_bytes, in_bytes, false)) != BSG_OK) return rc;
+  if ((rc = ensure(e, &e->d_out, &e->d_out_bytes, out_bytes + 64, false)) != BSG_OK) return rc;
+  auto is_pinned = [](const void* p) {
+    cudaPointerAttributes attr;
+    bool pinned = cudaPointerGetAttributes(&attr, p) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    return pinned;
+  };
+  const bool pin_in = is_pinned(roots_host);
+  const bool pin_out = (!ret0_host || is_pinned(ret0_host)) && (!length_host || is_pinned(length_host));
+  const size_t pin_need = 128 + (pin_in ? 0 : in_bytes + 64) + (pin_out ? 0 : out_bytes + 64);
+  if ((rc = ensure(e, &e->h_pinned, &e->h_pinned_bytes, pin_need, true)) != BSG_OK) return rc;
+  char* h_res = (char*)e->h_pinned;
+  char* h_in = h_res + 128;
+  char* h_out = h_in + (pin_in ? 0 : ((in_bytes + 63) & ~(size_t)63));
+  const char* src = (const char*)roots_host;
+  if (!pin_in) { memcpy(h_in, roots_host, in_bytes); src = h_in; }
+  int8_t* h_ret = ret0_host;
+  uint8_t* h_len = length_host;
+  if (!pin_out) {
+    h_ret = ret0_host ? (int8_t*)h_out : nullptr;
+    h_len = length_host ? (uint8_t*)h_out + (ret0_host ? n_play : 0) : nullptr;
+  }
+  int8_t* d_ret = ret0_host ? (int8_t*)e->d_out : nullptr;
+  uint8_t* d_len = length_host ? (uint8_t*)e->d_out + (ret0_host ? n_play : 0) : nullptr;
+  cudaStream_t sa = e->own_stream, sb = e->aux_stream;
+  BSG_CUDA(e, cudaMemsetAsync(e->d_totals, 0, 4 * sizeof(uint64_t), sa));
+  BSG_CUDA(e, cudaEventRecord(e->ev_a, sa));
+  BSG_CUDA(e, cudaStreamWaitEvent(sb, e->ev_a, 0));
+  int64_t n_chunks = (int64_t)(in_bytes >> 21);
+  n_chunks = n_chunks < 1 ? 1 : (n_chunks > 16 ? 16 : n_chunks);
+  PhiloxKeys keys;
+  philox_schedule(seed, keys);
+  for (int64_t c = 0; c < n_chunks; ++c) {
+    const int64_t lo = n_roots * c / n_chunks, hi = n_roots * (c + 1) / n_chunks;
+    if (hi <= lo) continue;
+    cudaStream_t st = (c & 1) ? sb : sa;
+    size_t plane_off = 0;
+    for (int p = 0; p < n_planes; ++p) {
+      const size_t pb = (size_t)plane_bytes[p];
+      BSG_CUDA(e, cudaMemcpyAsync((char*)e->d_roots + plane_off + (size_t)lo * pb, src + plane_off + (size_t)lo * pb,
+                                  (size_t)(hi - lo) * pb, cudaMemcpyHostToDevice, st));
+      plane_off += (size_t)n_roots * pb;
+    }
+    const int64_t p_lo = lo * rollouts, p_n = (hi - lo) * rollouts;
+    PlayoutArgs a;
+    memset(&a, 0, sizeof(a));
+    a.roots = e->d_roots; a.n_roots = n_roots; a.root0 = lo;
+    a.n_playouts = (uint32_t)p_n; a.rollouts = (uint32_t)rollouts;
+    a.first_playout = first_playout + (uint64_t)p_lo;
+    a.keys = keys;
+    a.io.totals = e->d_totals;
+    a.io.ret0 = d_ret ? d_ret + p_lo : nullptr;
+    a.io.length = d_len ? d_len + p_lo : nullptr;
+    if ((rc = dispatch_device_game(e->game, PlayoutOp{e, a, st})) != BSG_OK) return rc;
+    if (d_ret) BSG_CUDA(e, cudaMemcpyAsync(h_ret + p_lo, d_ret + p_lo, (size_t)p_n, cudaMemcpyDeviceToHost, st));
+    if (d_len) BSG_CUDA(e, cudaMemcpyAsync(h_len + p_lo, d_len + p_lo, (size_t)p_n, cudaMemcpyDeviceToHost, st));
+  }
+  BSG_CUDA(e, cudaEventRecord(e->ev_b, sb));
+  BSG_CUDA(e, cudaStreamWaitEvent(sa, e->ev_b, 0));
+  uint64_t* h_tot = (uint64_t*)h_res;
+  BSG_CUDA(e, cudaMemcpyAsync(h_tot, e->d_totals, 32, cudaMemcpyDeviceToHost, sa));
+  BSG_CUDA(e, cudaStreamSynchronize(sa));
+  for (int i = 0; i < 4; ++i) totals_out[i] = (int64_t)h_tot[i];
+  if (!pin_out) {
+    if (ret0_host) memcpy(ret0_host, h_ret, (size_t)n_play);
+    if (length_host) memcpy(length_host, h_len, (size_t)n_play);
+  }
   if (totals_out[3] != 0) return fail(e, BSG_ERR_STUCK_LANE, "non-terminal state without legal actions");
   return BSG_OK;
 }

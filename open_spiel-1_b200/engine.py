@@ -281,6 +281,25 @@ class Engine:
     self.launches += 1
     return totals, rr, rs
 
+  def playouts_host_results(self, packed, n_roots, rollouts=1, seed=0, first_playout=0, ret0=None,
+                            length=None):
+    """bsg_playouts_host_results: packed numpy roots in; totals and the per-playout return for
+    player 0 (int8) and move count (uint8) out, as numpy arrays of n_roots * rollouts entries.
+    Pass page-locked arrays as `ret0` / `length` to have them written in place."""
+    packed = np.ascontiguousarray(packed)
+    n = int(n_roots) * int(rollouts)
+    totals = np.zeros(4, np.int64)
+    if ret0 is None:
+      ret0 = np.empty(n, np.int8)
+    if length is None:
+      length = np.empty(n, np.uint8)
+    C.check(C.lib.bsg_playouts_host_results(self._h, packed.ctypes.data, int(n_roots), int(rollouts),
+                                            int(seed) & (2**64 - 1), int(first_playout),
+                                            totals.ctypes.data, ret0.ctypes.data, length.ctypes.data),
+            self._h)
+    self.launches += 1
+    return totals, ret0, length
+
   def observations_host(self, packed, n, players=None, want_mask=False):
     packed = np.ascontiguousarray(packed)
     obs = np.empty((n,) + tuple(self.obs_shape), np.float32)

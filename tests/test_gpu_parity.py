@@ -333,6 +333,66 @@ def test_host_buffer_chunked_path_equals_device_path(game, n, torch):
   eng.close()
 
 
+@pytest.mark.parametrize("game,n", [("connect_four", 700000), ("breakthrough", 250000), ("hex", 70000),
+                                    ("tic_tac_toe", 1100000), ("connect_four", 37), ("hex", 5)])
+def test_host_results_entry_point_equals_device_path(game, n, torch):
+  """bsg_playouts_host_results: per-playout return and move count in host memory (several
+  chunks on two streams with the copy back behind each kernel; one chunk for the small cases)
+  equal the device-buffer launch, for pageable and page-locked caller buffers."""
+  from open_spiel_1_b200.roots import make_roots, ROOT_DEPTHS
+  eng = _engine(game)
+  dev = eng.torch_device
+  dmin, dmax = ROOT_DEPTHS[game]
+  states, _ = make_roots(eng, n, dmin, dmax, seed=78)
+  R = 2
+  ret0 = torch.zeros(n * R, dtype=torch.int8, device=dev)
+  length = torch.zeros(n * R, dtype=torch.uint8, device=dev)
+  totals = torch.zeros(4, dtype=torch.int64, device=dev)
+  eng.playouts(states, n, R, seed=6, first_playout=321, ret0=ret0, length=length, totals=totals)
+  torch.cuda.synchronize()
+  want_t, want_r, want_l = totals.cpu().numpy(), ret0.cpu().numpy(), length.cpu().numpy()
+  host = states.cpu().numpy()
+  t, r, l = eng.playouts_host_results(host, n, R, seed=6, first_playout=321)       # pageable in and out
+  assert np.array_equal(t, want_t) and np.array_equal(r, want_r) and np.array_equal(l, want_l)
+  pin_in = torch.empty(states.numel(), dtype=torch.uint8, pin_memory=True)
+  pin_in.copy_(states)
+  pr = torch.zeros(n * R, dtype=torch.int8, pin_memory=True)
+  pl = torch.zeros(n * R, dtype=torch.uint8, pin_memory=True)
+  torch.cuda.synchronize()
+  t, r, l = eng.playouts_host_results(pin_in.numpy(), n, R, seed=6, first_playout=321,
+                                      ret0=pr.numpy(), length=pl.numpy())          # page-locked, in place
+  assert np.array_equal(t, want_t)
+  assert np.array_equal(pr.numpy(), want_r) and np.array_equal(pl.numpy(), want_l)
+  eng.close()
+
+
+@pytest.mark.parametrize("game", GAMES)
+def test_small_host_calls_equal_device_path(game, torch):
+  """bsg_playouts_host below 64 KB of roots takes the lean path (one stream, one memset for
+  totals + work counter + root sums, one copy back): same totals and per-root sums as the
+  device launch, call after call on one engine, with and without root sums, and next to a
+  large chunked call."""
+  from open_spiel_1_b200.roots import make_roots, ROOT_DEPTHS
+  eng = _engine(game)
+  dev = eng.torch_device
+  dmin, dmax = ROOT_DEPTHS[game]
+  for n, R in ((1, 1), (1, 64), (33, 5), (64 * 1024 // eng.state_bytes, 2), (64 * 1024 // eng.state_bytes + 1, 2)):
+    states, _ = make_roots(eng, n, dmin, dmax, seed=100 + n)
+    totals = torch.zeros(4, dtype=torch.int64, device=dev)
+    rr = torch.zeros(n, dtype=torch.int32, device=dev)
+    rs = torch.zeros(n, dtype=torch.int32, device=dev)
+    eng.playouts(states, n, R, seed=8, first_playout=77, root_sum_ret0=rr, root_sum_steps=rs, totals=totals)
+    torch.cuda.synchronize()
+    host = states.cpu().numpy()
+    for _ in range(2):
+      t, r, s_ = eng.playouts_host(host, n, R, seed=8, first_playout=77, want_root_sums=True)
+      assert np.array_equal(t, totals.cpu().numpy())
+      assert np.array_equal(r, rr.cpu().numpy()) and np.array_equal(s_, rs.cpu().numpy())
+      t, r, s_ = eng.playouts_host(host, n, R, seed=8, first_playout=77)
+      assert np.array_equal(t, totals.cpu().numpy()) and r is None
+  eng.close()
+
+
 @pytest.mark.parametrize("game", GAMES)
 def test_trajectory_records_match_oracle(game, torch):
   """Engine.trajectories: every decision point of every playout — observation of the player to
