@@ -199,6 +199,18 @@ struct ConnectFour {
   //   [0] = floor(2^32 / n) | (u64)(-n) << 32   (n = popc L: the fast-modulo constants),
   //   [1 + k] = for k < n the 64-bit cell mask of the k-th open column, ascending.
   // Nine words per row: rows of different L start in different shared-memory banks.
+#ifndef BSG_C4_GROUP
+#define BSG_C4_GROUP 4
+#endif
+  static constexpr int kGroupSteps = BSG_C4_GROUP;   // steps between two refills of the lean kernel
+#ifndef BSG_C4_LAZY_DRAW
+#define BSG_C4_LAZY_DRAW 1
+#endif
+  // A full board has no open column: table row 0 hands step() an empty column mask, nothing is
+  // placed, and neither side can own a line (a line ends the game when it is made) — so the lean
+  // kernel finds draws from the move count once per group (playout_kernel, kLazyDraw).
+  static constexpr bool kInertWhenFull = BSG_C4_LAZY_DRAW != 0;
+  BSG_HD static u32 moves_left(const State& s) { return s.left; }
   static constexpr int kRowWords = 9;
   struct Tables { u64 row[128][kRowWords]; };
   static constexpr u64 kColumn = 0x0000010101010101ull;  // the six cells of column 0

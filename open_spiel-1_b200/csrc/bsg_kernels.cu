@@ -60,6 +60,20 @@ inline uint32_t out_flags_of(const bsg_playout_io& io) {
 template <class G, class = void> struct min_blocks : std::integral_constant<int, 1> {};
 template <class G> struct min_blocks<G, std::enable_if_t<(G::kMinBlocks > 1)>> : std::integral_constant<int, G::kMinBlocks> {};
 
+// Steps per group of the lean kernel (one Philox block per four steps; lanes refill only at group
+// boundaries).  4 unless the game says otherwise (G::kGroupSteps, a multiple of 4).
+template <class G, class = void> struct group_steps : std::integral_constant<int, 4> {};
+template <class G> struct group_steps<G, std::enable_if_t<(G::kGroupSteps > 4)>> : std::integral_constant<int, G::kGroupSteps> {};
+
+// Games whose full board is inert (G::kInertWhenFull): a step on a full board places nothing and
+// cannot report a win, so the lean kernel need not test for the draw in every step — a playout
+// that has made as many moves as its root had empty cells is over, which one comparison per
+// GROUP finds out (the steps in between are dead steps on an unchanged board).
+template <class G, class = void> struct inert_when_full : std::false_type {};
+template <class G> struct inert_when_full<G, std::enable_if_t<G::kInertWhenFull>> : std::true_type {};
+template <class G, bool kOn> struct moves_left_of { BSG_HD static u32 get(const typename G::State&) { return 0xFFFFFFFFu; } };
+template <class G> struct moves_left_of<G, true> { BSG_HD static u32 get(const typename G::State& s) { return G::moves_left(s); } };
+
 // Indirection so that the kernel body only names the fill functions of a game that has them.
 template <class G, bool kOn> struct fill_words : std::integral_constant<int, 4> {};
 template <class G> struct fill_words<G, true> : std::integral_constant<int, G::kFillWords> {};
@@ -114,6 +128,8 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
   // (fin_lose: only in a game whose mover can lose by moving — pentago.)
   u32 live = 0, have = 0, fin_term = 0, fin_win = 0, fin_lose = 0;
   u32 lid = 0, t = 0, limit = 0xFFFFFFFFu, root_mv = 0;
+  constexpr bool kLazyDraw = inert_when_full<G>::value && !kFull && !kFill && !kAsync;
+  u32 left0 = 0xFFFFFFFFu;   // kLazyDraw: empty cells of the root = the most moves the playout can make
   unsigned long long pid0 = a.first_playout;   // playout id = pid0 + lid (per root with root_playout_base)
   u32 my_steps = 0, my_done = 0, my_stuck = 0;
   int my_ret = 0;
@@ -177,6 +193,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         t = 0;
         nblk = 0xFFFFFFFFu;
         root_mv = (u32)G::mover(s);
+        if constexpr (kLazyDraw) left0 = moves_left_of<G, kLazyDraw>::get(s);
         if (kFull) {
           limit = a.io.max_steps > 0 ? (u32)a.io.max_steps : 0xFFFFFFFFu;
           if (a.io.step_limit) limit = min(limit, (u32)a.io.step_limit[lid]);
@@ -204,6 +221,9 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
 
     const unsigned long long pid = (kBase ? pid0 : a.first_playout) + lid;
     u32 rr[4];
+    constexpr int kSteps = (kFull || kAsync || kFill) ? 4 : group_steps<G>::value;
+    const u32 live_in = live;   // (kLazyDraw) lanes that play in this group
+    static_assert(kSteps % 4 == 0, "a group is a whole number of Philox blocks");
     if constexpr (!kAsync) {
       philox4x32_10((u32)pid, (u32)(pid >> 32), t >> 2, 0u, a.keys, rr);
     } else {
@@ -220,10 +240,13 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
       philox4x32_10((u32)pid, (u32)(pid >> 32), nblk, 0u, a.keys, rnew);
     }
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < kSteps; ++j) {
       u32 r, can = live;   // can: this lane makes a move in this iteration
       if constexpr (!kAsync) {
-        r = rr[j];
+        // a live lane entered the group with t = 0 (mod kSteps) and has moved j times since:
+        // its next block is t >> 2 (a finished lane's t is frozen: it draws garbage for its dead steps)
+        if (kSteps > 4 && j > 0 && (j & 3) == 0) philox4x32_10((u32)pid, (u32)(pid >> 32), t >> 2, 0u, a.keys, rr);
+        r = rr[j & 3];
       } else {
         G::ring(s);
         can = G::pending(s) ? 0u : live;
@@ -269,6 +292,10 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
             }
           }
         }
+      } else if constexpr (kLazyDraw) {
+        // only a win ends the playout inside the group; the draw is found at the group's end
+        t += live;
+        live = G::won(s) ? 0u : live;
       } else {
         // lean bookkeeping: t counts the moves of the live playout and freezes when it ends;
         // fin_win was cleared at the claim and can only be set by the (single) ending move
@@ -279,6 +306,12 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         if constexpr (G::kLazyEnd) t += can & made; else t += can;
         live &= (can & term) ^ 1u;
       }
+    }
+    if constexpr (kLazyDraw) {
+      // a lane that entered the group live and is dead here was stopped by a win; then the draw:
+      // the board filled up somewhere in this group and the moves counted past that were dead steps
+      fin_win |= live_in & (live ^ 1u);
+      if (t >= left0) { t = left0; live = 0u; }
     }
   }
 
