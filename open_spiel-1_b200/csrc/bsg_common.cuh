@@ -65,6 +65,62 @@ BSG_HD u32 fshr(u32 lo, u32 hi, int s) {  // low word of (hi:lo) >> s
 }
 
 // ---------------------------------------------------------------------------------------
+// Multi-word shifts on the MULTIPLIER pipe (device only; an A/B switch, OFF by default because it
+// measured slower — see BSG_MULSHIFT below).  The flood kernels (hex, y) are bound
+// by the ALU pipe — LOP3 / SHF at 88-93 % with the multiplier pipe at 4-14 % (profiles/r1f, r1s)
+// — and a third of a dilation ring is funnel shifts.  A shift is a multiplication by a power of
+// two: (f[w] << k) | (f[w-1] >> (32-k)) = f[w] * 2^k + hi32(f[w-1] * 2^k), one IMAD.HI and one
+// IMAD with the addend folded in, no ALU instruction.  The multipliers are read from a
+// __constant__ table (host-writable, hence opaque to ptxas, which otherwise turns multiplications
+// by visible powers of two back into SHF / LEA) and travel in uniform registers.
+// ---------------------------------------------------------------------------------------
+#ifndef BSG_MULSHIFT
+#define BSG_MULSHIFT 0   // measured on B200: hex 71.8 -> 68.1, y 23.9 -> 23.5 G steps/s with it (IMAD.HI is quarter rate)
+#endif
+#if defined(__CUDACC__)
+static __constant__ u32 g_pow2[33] = {
+    1u << 0, 1u << 1, 1u << 2, 1u << 3, 1u << 4, 1u << 5, 1u << 6, 1u << 7, 1u << 8, 1u << 9, 1u << 10,
+    1u << 11, 1u << 12, 1u << 13, 1u << 14, 1u << 15, 1u << 16, 1u << 17, 1u << 18, 1u << 19, 1u << 20,
+    1u << 21, 1u << 22, 1u << 23, 1u << 24, 1u << 25, 1u << 26, 1u << 27, 1u << 28, 1u << 29, 1u << 30,
+    1u << 31, 0u};
+#endif
+// o = f shifted towards HIGHER bit indices by K (0 < K < 32) over W words (bits leaving the top
+// word are dropped).
+template <int K, int W> BSG_HD void shl_words(const u32* f, u32* o) {
+#if defined(__CUDA_ARCH__) && BSG_MULSHIFT
+  const u32 m = g_pow2[K];
+  u32 carry = 0;
+#pragma unroll
+  for (int w = 0; w < W; ++w) {
+    u32 r, h = 0;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(f[w]), "r"(m), "r"(carry));
+    if (w < W - 1) asm("mul.hi.u32 %0, %1, %2;" : "=r"(h) : "r"(f[w]), "r"(m));
+    o[w] = r;
+    carry = h;
+  }
+#else
+#pragma unroll
+  for (int w = W - 1; w >= 0; --w) o[w] = w == 0 ? f[0] << K : fshl(f[w - 1], f[w], K);
+#endif
+}
+// o = f shifted towards LOWER bit indices by K (0 < K < 32) over W words.
+template <int K, int W> BSG_HD void shr_words(const u32* f, u32* o) {
+#if defined(__CUDA_ARCH__) && BSG_MULSHIFT
+  const u32 m = g_pow2[32 - K];
+#pragma unroll
+  for (int w = 0; w < W; ++w) {
+    u32 lo = 0, r;
+    if (w < W - 1) asm("mul.lo.u32 %0, %1, %2;" : "=r"(lo) : "r"(f[w + 1]), "r"(m));
+    asm("mad.hi.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(f[w]), "r"(m), "r"(lo));
+    o[w] = r;
+  }
+#else
+#pragma unroll
+  for (int w = 0; w < W; ++w) o[w] = w == W - 1 ? f[w] >> K : fshr(f[w], f[w + 1], K);
+#endif
+}
+
+// ---------------------------------------------------------------------------------------
 // Philox4x32-10, counter based.  Replay contract of this engine (see include/bsg.h):
 //   r(seed, playout, t) = philox4x32_10(ctr = {playout_lo, playout_hi, t >> 2, 0},
 //                                       key = {seed_lo, seed_hi})[t & 3]

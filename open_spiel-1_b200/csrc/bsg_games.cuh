@@ -629,6 +629,10 @@ struct HexT {
   BSG_HD static int plane_bytes(int p) { (void)p; return 16; }
   static constexpr bool kCanStick = false;
   static constexpr bool kAsync = true;
+#ifndef BSG_HEX_MINBLOCKS
+#define BSG_HEX_MINBLOCKS 1   // A/B switch: resident CTAs per SM the lean kernel is register-capped for
+#endif
+  static constexpr int kMinBlocks = BSG_HEX_MINBLOCKS;
   static constexpr bool kMoverCanLose = false;
   static constexpr bool kLazyEnd = false;       // the lean kernel sees a terminal state in the step that reaches it (see Othello)
   struct State {
@@ -764,21 +768,19 @@ struct HexT {
   // wrap masked; the two northern neighbours (r-1,c), (r-1,c+1) are (f | east) shifted one row
   // down in index, the two southern ones (f | west) shifted one row up.
   BSG_HD static void dilate_within(const u32 f[4], const u32 within[4], u32 out[4]) {
-    u32 E[4], W[4], fe[4], fw[4];
-    E[0] = f[0] << 1; E[1] = fshl(f[0], f[1], 1); E[2] = fshl(f[1], f[2], 1); E[3] = fshl(f[2], f[3], 1);
-    W[0] = fshr(f[0], f[1], 1); W[1] = fshr(f[1], f[2], 1); W[2] = fshr(f[2], f[3], 1); W[3] = f[3] >> 1;
+    u32 E[4], W[4], fe[4], fw[4], nn[4], ss[4];
+    shl_words<1, 4>(f, E);
+    shr_words<1, 4>(f, W);
 #pragma unroll
     for (int w = 0; w < 4; ++w) {
-      E[w] &= not_col0(w);          // a stone in the last column has no east neighbour
-      W[w] &= not_col_last(w);      // a stone in column 0 has no west neighbour
-      fe[w] = f[w] | E[w];
-      fw[w] = f[w] | W[w];
+      fe[w] = f[w] | (E[w] & not_col0(w));          // a stone in the last column has no east neighbour
+      fw[w] = f[w] | (W[w] & not_col_last(w));      // a stone in column 0 has no west neighbour
     }
-    u32 nn[4], ss[4];
-    nn[0] = fshr(fe[0], fe[1], N); nn[1] = fshr(fe[1], fe[2], N); nn[2] = fshr(fe[2], fe[3], N); nn[3] = fe[3] >> N;
-    ss[0] = fw[0] << N; ss[1] = fshl(fw[0], fw[1], N); ss[2] = fshl(fw[1], fw[2], N); ss[3] = fshl(fw[2], fw[3], N);
+    shr_words<N, 4>(fe, nn);
+    shl_words<N, 4>(fw, ss);
+    // (f itself rides along in fe | fw: every caller's `within` excludes the frontier)
 #pragma unroll
-    for (int w = 0; w < 4; ++w) out[w] = (E[w] | W[w] | nn[w] | ss[w]) & within[w];
+    for (int w = 0; w < 4; ++w) out[w] = (fe[w] | fw[w] | nn[w] | ss[w]) & within[w];
   }
   // The pending flood (hex.cc:158-182, one ring per call): label the frontier, then the next
   // frontier is its ring of neighbours among the stones that are still plain.
@@ -810,6 +812,13 @@ struct HexT {
     bool tA = (hitA != 0) || (flags & 1u), tB = (hitB != 0) || (flags & 2u);
     u32 toA = tA ? 0xFFFFFFFFu : 0u, toB = tB ? 0xFFFFFFFFu : 0u;
     u32 go = (tA != tB) ? 0xFFFFFFFFu : 0u;   // exactly one label: it spreads through plain stones
+#if defined(__CUDA_ARCH__) && BSG_HEX_OPAQUE_MASKS
+    // keep the three masks in registers: a | (m & mask) is then ONE 3-input LOP3 per word instead
+    // of a select on the predicate followed by an OR
+    asm("" : "+r"(toA));
+    asm("" : "+r"(toB));
+    asm("" : "+r"(go));
+#endif
     u32 nO[4], nA[4], nB[4];
 #pragma unroll
     for (int w = 0; w < 4; ++w) {
@@ -829,6 +838,9 @@ struct HexT {
     s.left -= 1u;
   }
   BSG_HD static u32 empty_word(const State& s, int w) { return ~(s.cO[w] | s.oO[w]) & board_word(w); }
+#ifndef BSG_HEX_OPAQUE_MASKS
+#define BSG_HEX_OPAQUE_MASKS 1
+#endif
   // k-th (ascending) empty cell, k < left.  Word by prefix popcounts, then halves of the word,
   // then a byte table.
   BSG_HD static int select_empty(const State& s, u32 k, const Tables& tab) {
@@ -1607,27 +1619,24 @@ struct YT {
   // board).  x+1 / x-1 are shifts by one with the row wrap masked; (x, y-1) and (x+1, y-1) are
   // (f | east) shifted down by N, (x, y+1) and (x-1, y+1) are (f | west) shifted up by N.
   BSG_HD static void dilate_within(const u32 f[W], const u32 within[W], u32 out[W]) {
-    u32 fe[W], fw[W], ew[W];
+    u32 e[W], x[W], fe[W], fw[W], nn[W], ss[W];
+    shl_words<1, W>(f, e);
+    shr_words<1, W>(f, x);
+    // f lies on the board, so the only shifts by one that wrap onto a board cell are
+    // (N-1, 0) -> (0, 1) and back: bits N and N - 1 of word 0; every other stray bit lands
+    // off the board and is dropped by `within`
+    e[0] &= ~(1u << N);
+    x[0] &= ~(1u << (N - 1));
 #pragma unroll
     for (int w = 0; w < W; ++w) {
-      // f lies on the board, so the only shifts by one that wrap onto a board cell are
-      // (N-1, 0) -> (0, 1) and back: bits N and N - 1 of word 0; every other stray bit lands
-      // off the board and is dropped by `within`
-      u32 e = w == 0 ? f[0] << 1 : fshl(f[w - 1], f[w], 1);
-      u32 x = w == W - 1 ? f[w] >> 1 : fshr(f[w], f[w + 1], 1);
-      if (w == 0) { e &= ~(1u << N); x &= ~(1u << (N - 1)); }
-      fe[w] = f[w] | e;
-      fw[w] = f[w] | x;
-      ew[w] = e | x;
+      fe[w] = f[w] | e[w];
+      fw[w] = f[w] | x[w];
     }
-    constexpr int q = N >> 5, r = N & 31;   // N < 32 here: q = 0
-    static_assert(q == 0 && r != 0, "row shifts are written for N < 32");
+    static_assert(N < 32, "row shifts are written for N < 32");
+    shr_words<N, W>(fe, nn);
+    shl_words<N, W>(fw, ss);
 #pragma unroll
-    for (int w = 0; w < W; ++w) {
-      const u32 nn = w == W - 1 ? fe[w] >> r : fshr(fe[w], fe[w + 1], r);
-      const u32 ss = w == 0 ? fw[0] << r : fshl(fw[w - 1], fw[w], r);
-      out[w] = (ew[w] | nn | ss) & within[w];
-    }
+    for (int w = 0; w < W; ++w) out[w] = (fe[w] | fw[w] | nn[w] | ss[w]) & within[w];
   }
   // The pending flood, one ring per call: the frontier takes the labels being spread, the next
   // frontier is its ring among the owner's stones that still lack one of them.
