@@ -711,6 +711,37 @@ def side_numbers(args, eng, torch, dev, rank, world, reduce_max_sum):
     del st
     e_bt.close()
     torch.cuda.empty_cache()
+    # the AlphaZero actor proper (alpha_zero.py:196-228): MCTS self-play, many games in flight,
+    # policy = root visit counts, records written into a device replay buffer
+    try:
+      from open_spiel_1_b200.actor import ForestActor
+      e_c4 = bsg.Engine("connect_four", eng.device)
+      g_c4 = bsg.load_game("connect_four")
+      n_games, sims, roll = 4096, 64, 16
+      ev = bsg.GpuRolloutEvaluator(e_c4, n_rollouts=roll, seed=ROOT_SEED + 8)
+      actor = ForestActor(g_c4, ev, n_games, uct_c=2.0, max_simulations=sims, temperature=1.0,
+                          temperature_drop=10, solve=False, seed=1000 * rank, sample_seed=ROOT_SEED + 9 + rank,
+                          leaf_batch=8)
+      rbuf = bsg.DeviceReplayBuffer(1 << 18, e_c4.obs_size, e_c4.num_actions, dev)
+      actor.play_batch(buffer=rbuf)
+      torch.cuda.synchronize(dev)
+      t0 = time.perf_counter()
+      res = actor.play_batch(buffer=rbuf)
+      torch.cuda.synchronize(dev)
+      secs = time.perf_counter() - t0
+      mx, sm = reduce_max_sum([secs, float(res["total"])])
+      out["trajectory_actor"] = {
+          "workload": "connect_four MCTS self-play: %d games in flight per GPU, %d simulations/move, "
+                      "%d rollouts/leaf, temperature 1, temperature_drop 10; records (observation, "
+                      "legal mask, visit-count policy, final return) into a device replay buffer"
+                      % (n_games, sims, roll),
+          "n_gpus": world, "records": sm[1], "seconds": mx[0], "records_per_s": sm[1] / mx[0],
+          "games_per_s": n_games * world / mx[0], "moves": int(res["moves"]),
+          "simulations_per_s": sm[1] * sims / mx[0]}
+      actor.close()
+      e_c4.close()
+    except Exception as ex:
+      out["trajectory_actor"] = {"error": repr(ex)}
     for g, npl in (("tic_tac_toe", 1 << 24), ("breakthrough", 1 << 22), ("hex", 1 << 20),
                    ("pentago", 1 << 22), ("othello", 1 << 21), ("y", 1 << 21)):
       e_g = bsg.Engine(g, eng.device)

@@ -287,6 +287,62 @@ int bsg_forest_search(bsg_forest* f, const void* root_host, int64_t simulations_
  * all-reduce over ranks). */
 int bsg_forest_pack_root(bsg_forest* f, const int64_t* base_dev, int64_t* out_dev);
 int bsg_forest_install_root(bsg_forest* f, const int64_t* base_dev, const int64_t* summed_dev);
+/* ---- self-play actor on the forest: MANY games in flight, game v
+ * = tree v.  Stands in for _play_game of python/algorithms/alpha_zero/alpha_zero.py:196-228 —
+ * per move one search, policy target = root children's explore_count ** (1 / temperature)
+ * normalised, action = best_child() (mcts.py:144-162) once `temperature_drop` moves were made,
+ * else sampled from the policy; record = (state, action, policy, root.total_reward /
+ * root.explore_count) — and for the learner's filing of the records with value = the game's
+ * final returns[0] (alpha_zero.py:366-369).  Everything stays in device memory.
+ *
+ * bsg_forest_search_roots: searches tree v from root v of a packed DEVICE buffer (capacity
+ * n_trees), `simulations_per_tree` each; trees whose alive_dev[v] is 0 (NULL = all alive) get
+ * none.  Shuffle counters and playout ids of a tree run on from move to move, as a bot object
+ * reused for a whole game does.
+ * bsg_forest_actor_step: one move of every running game from the finished search (all pointers
+ * device memory of the caller; logs are move-major, record (m, v) at m * n_games + v).  The
+ * sampled action of move m of game v uses the draw r(sample_seed, game_id_base + v, m) through
+ * the inverse CDF over ascending action ids; at temperature 1 exactly (integer visit counts).
+ * *n_alive_out (host, may be NULL = no synchronisation) = games still running.
+ * bsg_actor_emit: the records game-major (row offsets[v] + m), packed states compacted to
+ * capacity `total` (feed them to bsg_observations for the planes and masks), value = final
+ * returns[0] of the record's game. */
+typedef struct bsg_actor_io {
+  void* states;             /* packed SoA, capacity n_games: current positions, updated in place */
+  uint8_t* alive;           /* [n_games] */
+  int32_t* length;          /* [n_games] moves made */
+  int32_t* outcome;         /* [n_games] (int)returns[0] of finished games */
+  uint32_t* n_alive_dev;    /* one device counter */
+  void* state_log;          /* packed SoA, capacity max_moves * n_games: the state before each move */
+  float* policy_log;        /* [max_moves * n_games][NumDistinctActions] */
+  float* est_log;           /* [max_moves * n_games] root value estimate */
+  int32_t* action_log;      /* [max_moves * n_games] */
+  double* weights;          /* scratch [n_games][NumDistinctActions] */
+  int32_t n_games, max_moves, move, temperature_drop;
+  double temperature;
+  uint64_t sample_seed, game_id_base;
+} bsg_actor_io;
+typedef struct bsg_actor_emit_io {
+  const void* state_log; const float* policy_log; const float* est_log; const int32_t* action_log;
+  const int32_t* length; const int32_t* outcome;
+  const int64_t* offsets;   /* [n_games] exclusive prefix sum of length */
+  void* out_states;         /* packed SoA, capacity total */
+  float* out_policy;        /* [total][NumDistinctActions] */
+  float* out_value;         /* [total] */
+  float* out_est;           /* [total] or NULL */
+  int32_t* out_action;      /* [total] or NULL */
+  int32_t* out_player;      /* [total] or NULL: current player of the record */
+  int32_t n_games, max_moves;
+  int64_t total;
+} bsg_actor_emit_io;
+int bsg_forest_search_roots(bsg_forest* f, const void* roots_dev, const uint8_t* alive_dev,
+                            int64_t simulations_per_tree);
+int bsg_forest_actor_step(bsg_forest* f, const bsg_actor_io* io, uint32_t* n_alive_out);
+int bsg_actor_emit(bsg_engine* e, const bsg_actor_emit_io* io);
+/* The engine's own CUDA stream (cudaStream_t as void*): where bsg_forest_* and bsg_actor_* work
+ * is ordered, for callers that want to order their own work behind it. */
+void* bsg_engine_stream(bsg_engine* e);
+
 /* Root-parallel search over several GPUs without torch ("one
  * ncclAllReduce per search step").  The engine owns an NCCL communicator of its own; NCCL is
  * loaded with dlopen("libnccl.so.2") at the first call, so the library has no link-time

@@ -11,6 +11,7 @@ on-disk name `open_spiel-1_b200` is not a Python identifier).
   evaluate_bots.evaluate_bots    the reference's bot-vs-bot loop (+ play_match over many roots)
   replay.DeviceReplayBuffer      the AlphaZero learner's replay buffer as device tensors
   forest.ForestMCTS              root-parallel MCTS with the trees resident on the GPU
+  actor.ForestActor              AlphaZero-style self-play, many games in flight, records on the device
 
 The CUDA extension (libbsg.so) is mandatory: importing this package without it raises.
 """
@@ -22,7 +23,8 @@ from .mcts import MCTSBot, SearchNode, NativeMCTSBot, PhiloxShuffle
 from .parallel import RootParallelMCTS, ShardedPlayouts, shard_range
 from .evaluate_bots import evaluate_bots, play_match, UniformRandomBot
 from .replay import DeviceReplayBuffer, TrainInput
+from .actor import ForestActor
 
 __all__ = ["Engine", "game_id", "pack_histories", "draw", "Evaluator", "GpuRolloutEvaluator", "AlphaZeroEvaluator",
            "load_game", "Game", "State", "GameType", "PlayerId", "MCTSBot", "SearchNode", "NativeMCTSBot", "PhiloxShuffle",
-           "RootParallelMCTS", "ShardedPlayouts", "shard_range", "evaluate_bots", "play_match", "UniformRandomBot", "DeviceReplayBuffer", "TrainInput"]
+           "RootParallelMCTS", "ShardedPlayouts", "shard_range", "evaluate_bots", "play_match", "UniformRandomBot", "DeviceReplayBuffer", "TrainInput", "ForestActor"]

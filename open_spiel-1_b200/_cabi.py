@@ -47,6 +47,22 @@ class PlayoutIO(ctypes.Structure):
   ]
 
 
+class ActorIO(ctypes.Structure):
+  """struct bsg_actor_io (include/bsg.h)."""
+  _fields_ = [("states", vp), ("alive", vp), ("length", vp), ("outcome", vp), ("n_alive_dev", vp),
+              ("state_log", vp), ("policy_log", vp), ("est_log", vp), ("action_log", vp), ("weights", vp),
+              ("n_games", i32), ("max_moves", i32), ("move", i32), ("temperature_drop", i32),
+              ("temperature", ctypes.c_double), ("sample_seed", u64), ("game_id_base", u64)]
+
+
+class ActorEmitIO(ctypes.Structure):
+  """struct bsg_actor_emit_io (include/bsg.h)."""
+  _fields_ = [("state_log", vp), ("policy_log", vp), ("est_log", vp), ("action_log", vp),
+              ("length", vp), ("outcome", vp), ("offsets", vp), ("out_states", vp), ("out_policy", vp),
+              ("out_value", vp), ("out_est", vp), ("out_action", vp), ("out_player", vp),
+              ("n_games", i32), ("max_moves", i32), ("total", i64)]
+
+
 def _load():
   if not os.path.exists(LIB_PATH):
     raise ImportError(
@@ -110,6 +126,10 @@ def _load():
       "bsg_forest_install_root": (ctypes.c_int, [vp, vp, vp]),
       "bsg_forest_tree_root": (ctypes.c_int, [vp, i32, ctypes.c_int, vp, vp, vp, vp, vp]),
       "bsg_forest_info": (ctypes.c_int, [vp, vp]),
+      "bsg_forest_search_roots": (ctypes.c_int, [vp, vp, vp, i64]),
+      "bsg_forest_actor_step": (ctypes.c_int, [vp, ctypes.POINTER(ActorIO), vp]),
+      "bsg_actor_emit": (ctypes.c_int, [vp, ctypes.POINTER(ActorEmitIO)]),
+      "bsg_engine_stream": (vp, [vp]),
       "bsg_comm_unique_id": (ctypes.c_int, [vp]),
       "bsg_comm_init": (ctypes.c_int, [vp, ctypes.c_int, ctypes.c_int, vp]),
       "bsg_comm_destroy": (ctypes.c_int, [vp]),

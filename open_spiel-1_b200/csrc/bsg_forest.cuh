@@ -44,7 +44,8 @@ struct ForestView {
   const double* logtab;     // log(n), n < logtab_n (built on the host: the host tree's libm)
   int32_t* error;           // != 0: node pool or log table exhausted
   uint32_t* active;         // trees that descended at least once in this round
-  const void* root;         // packed root state (capacity 1)
+  const void* root;         // packed root state (capacity 1), or one root per tree (capacity n_trees)
+  int32_t root_per_tree;    // != 0: tree v searches root v of `root` (self-play actors: one game per tree)
   uint64_t shuffle_seed0;   // tree v shuffles with seed shuffle_seed0 + v
   int32_t n_trees, cap, batch, depth, n_rollouts, solve, logtab_n;
   double uct_c;
@@ -155,7 +156,7 @@ struct ForestTree {
     const int64_t left = F.sims_left[v];   // (a solved root ends the search AFTER a round, as on the host)
     const int k = (int)(left < B ? left : B);
     State root_state;
-    G::load(root_state, F.root, 1, 0);
+    G::load(root_state, F.root, F.root_per_tree ? F.n_trees : 1, F.root_per_tree ? v : 0);
     const bool batched = B > 1;
     int n_pending = 0, n_leaves = 0;
     const uint64_t base = F.next_playout[v];
@@ -291,7 +292,7 @@ struct ForestTree {
     const int64_t left = F.sims_left[v];
     const int k = (int)(left < B ? left : B);
     State root_state;
-    G::load(root_state, F.root, 1, 0);
+    G::load(root_state, F.root, F.root_per_tree ? F.n_trees : 1, F.root_per_tree ? v : 0);
     const bool batched = B > 1;
     int n_pending = 0, n_leaves = 0;
     const uint64_t base = F.next_playout[v];
@@ -411,7 +412,7 @@ struct ForestTree {
   BSG_HD static void expand_root(const ForestView& F, int v) {
     MctsNode* nodes = F.nodes + (size_t)v * F.cap;
     State root_state;
-    G::load(root_state, F.root, 1, 0);
+    G::load(root_state, F.root, F.root_per_tree ? F.n_trees : 1, F.root_per_tree ? v : 0);
     if (nodes[0].first_child < 0 && !G::terminal(root_state)) {
       int n_nodes = F.n_nodes[v];
       expand(F, v, nodes, n_nodes, 0, root_state);
@@ -422,7 +423,7 @@ struct ForestTree {
   BSG_HD static void reset(const ForestView& F, int v) {
     MctsNode* nodes = F.nodes + (size_t)v * F.cap;
     State root_state;
-    G::load(root_state, F.root, 1, 0);
+    G::load(root_state, F.root, F.root_per_tree ? F.n_trees : 1, F.root_per_tree ? v : 0);
     MctsNode r;
     r.action = -1; r.player = G::mover(root_state); r.explore = 0; r.reward = 0.0; r.virt = 0;
     r.has_outcome = 0; r.out0 = 0.0; r.first_child = -1; r.n_children = 0;

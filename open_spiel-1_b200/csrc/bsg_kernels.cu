@@ -27,6 +27,7 @@
 #include "bsg_host.cuh"
 #include "bsg_mcts.cuh"
 #include "bsg_forest.cuh"
+#include "bsg_actor.cuh"
 
 namespace bsg {
 
@@ -731,6 +732,20 @@ template <class G>
 __global__ void forest_expand_root_kernel(ForestView F) {
   const int v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v < F.n_trees) ForestTree<G>::expand_root(F, v);
+}
+__global__ void forest_fill_alive_kernel(int64_t* dst, int64_t value, const uint8_t* alive, int n) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v < n) dst[v] = (!alive || alive[v]) ? value : 0;
+}
+template <class G>
+__global__ void actor_step_kernel(ForestView F, ActorView A, const typename G::Tables* __restrict__ tab) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v < A.n_games) Actor<G>::step(F, A, v, *tab);
+}
+template <class G>
+__global__ void actor_emit_kernel(EmitView E) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < (int64_t)E.n_games * E.max_moves) actor_emit_one<G>(E, (int)(i % E.n_games), (int)(i / E.n_games));
 }
 __global__ void forest_fill_kernel(int64_t* dst, int64_t value, const int64_t* per_tree, int n) {
   const int v = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1751,6 +1766,88 @@ int bsg_forest_install_root(bsg_forest* f, const int64_t* base_dev, const int64_
   BSG_CUDA(e, cudaStreamSynchronize(e->own_stream));
   return BSG_OK;
 }
+// ---- self-play actor on the forest (bsg_actor.cuh): one game per tree
+}  // extern "C"
+namespace {
+struct ActorStepOp {
+  bsg_forest* f; ActorView A;
+  template <class G> int operator()() const {
+    bsg_engine* e = f->e;
+    actor_step_kernel<G><<<(A.n_games + kForestThreads - 1) / kForestThreads, kForestThreads, 0, e->own_stream>>>(
+        f->F, A, (const typename G::Tables*)e->tables_dev);
+    BSG_CUDA(e, cudaGetLastError());
+    return BSG_OK;
+  }
+};
+struct ActorEmitOp {
+  bsg_engine* e; EmitView E;
+  template <class G> int operator()() const {
+    const int64_t n = (int64_t)E.n_games * E.max_moves;
+    actor_emit_kernel<G><<<(unsigned)((n + 127) / 128), 128, 0, e->own_stream>>>(E);
+    BSG_CUDA(e, cudaGetLastError());
+    return BSG_OK;
+  }
+};
+}  // namespace
+extern "C" {
+
+int bsg_forest_search_roots(bsg_forest* f, const void* roots_dev, const uint8_t* alive_dev,
+                            int64_t simulations_per_tree) {
+  if (!f || !roots_dev || simulations_per_tree < 0) return BSG_ERR_BAD_ARG;
+  bsg_engine* e = f->e;
+  f->err.clear();
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  forest_fill_alive_kernel<<<forest_grid(f), kForestThreads, 0, e->own_stream>>>(
+      f->F.sims_left, simulations_per_tree, alive_dev, f->F.n_trees);
+  f->F.root = roots_dev;
+  f->F.root_per_tree = 1;
+  const int rc = dispatch_device_game(e->game, ForestSearchOp{f, 0, simulations_per_tree});
+  f->F.root = f->d_root;
+  f->F.root_per_tree = 0;
+  return rc;
+}
+
+int bsg_forest_actor_step(bsg_forest* f, const bsg_actor_io* io, uint32_t* n_alive_out) {
+  if (!f || !io || !io->states || !io->alive || !io->length || !io->outcome || !io->state_log ||
+      !io->policy_log || !io->est_log || !io->action_log || !io->weights || !io->n_alive_dev)
+    return BSG_ERR_BAD_ARG;
+  if (io->n_games != f->F.n_trees || io->move < 0 || io->move >= io->max_moves || !(io->temperature > 0.0))
+    return fail(f->e, BSG_ERR_BAD_ARG, "actor step: one game per tree, 0 <= move < max_moves, temperature > 0");
+  bsg_engine* e = f->e;
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  ActorView A;
+  A.states = io->states; A.alive = io->alive; A.length = io->length; A.outcome = io->outcome;
+  A.n_alive = io->n_alive_dev; A.state_log = io->state_log; A.policy_log = io->policy_log;
+  A.est_log = io->est_log; A.action_log = io->action_log; A.weights = io->weights;
+  A.n_games = io->n_games; A.max_moves = io->max_moves; A.move = io->move;
+  A.temperature_drop = io->temperature_drop; A.temperature = io->temperature;
+  A.sample_seed = io->sample_seed; A.game_id_base = io->game_id_base;
+  BSG_CUDA(e, cudaMemsetAsync(A.n_alive, 0, sizeof(uint32_t), e->own_stream));
+  int rc = dispatch_device_game(e->game, ActorStepOp{f, A});
+  if (rc != BSG_OK) return rc;
+  if (n_alive_out) {
+    BSG_CUDA(e, cudaMemcpyAsync(n_alive_out, A.n_alive, sizeof(uint32_t), cudaMemcpyDeviceToHost, e->own_stream));
+    BSG_CUDA(e, cudaStreamSynchronize(e->own_stream));
+  }
+  return BSG_OK;
+}
+
+int bsg_actor_emit(bsg_engine* e, const bsg_actor_emit_io* io) {
+  if (!e || !io || !io->state_log || !io->policy_log || !io->est_log || !io->action_log || !io->length ||
+      !io->outcome || !io->offsets || !io->out_states || !io->out_policy || !io->out_value)
+    return BSG_ERR_BAD_ARG;
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  EmitView E;
+  E.state_log = io->state_log; E.policy_log = io->policy_log; E.est_log = io->est_log;
+  E.action_log = io->action_log; E.length = io->length; E.outcome = io->outcome; E.offsets = io->offsets;
+  E.out_states = io->out_states; E.out_policy = io->out_policy; E.out_value = io->out_value;
+  E.out_est = io->out_est; E.out_action = io->out_action; E.out_player = io->out_player;
+  E.n_games = io->n_games; E.max_moves = io->max_moves; E.total = io->total;
+  if (E.total < 1 || E.n_games < 1 || E.max_moves < 1) return BSG_OK;
+  return dispatch_device_game(e->game, ActorEmitOp{e, E});
+}
+void* bsg_engine_stream(bsg_engine* e) { return e ? (void*)e->own_stream : nullptr; }
+
 // ---- the engine's own NCCL communicator + the root merge on the engine's stream
 int bsg_comm_unique_id(uint8_t id_out[128]) {
   if (!id_out) return BSG_ERR_BAD_ARG;
