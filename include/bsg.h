@@ -187,6 +187,10 @@ typedef struct bsg_playout_io {
    * the win.  What RandomRolloutEvaluator::Evaluate (mcts.cc:42-71) needs is only the returns.
    * Excludes max_steps / step_limit / r_table / actions / final_states / state_log. */
   int32_t value_only;
+  /* Alternative to state_log_off: a fixed stride — the state before move t of playout p goes to
+   * slot p * state_log_stride + t (state_log_off must then be NULL; moves t >= stride are not
+   * logged).  One pass, no earlier launch needed; bsg_trajectory_* compacts the log. */
+  int64_t state_log_stride;
 } bsg_playout_io;
 
 /* The hot path.  Stands in for RandomRolloutEvaluator::Evaluate's playout loop
@@ -287,6 +291,20 @@ int bsg_forest_search(bsg_forest* f, const void* root_host, int64_t simulations_
  * all-reduce over ranks). */
 int bsg_forest_pack_root(bsg_forest* f, const int64_t* base_dev, int64_t* out_dev);
 int bsg_forest_install_root(bsg_forest* f, const int64_t* base_dev, const int64_t* summed_dev);
+/* ---- trajectories of random playouts in ONE pass (the record of every decision point,
+ * alpha_zero.py:196-228 / 214-217, for uniform-random self-play): bsg_playouts with
+ * io.state_log_stride (and io.actions) logs at a fixed stride per playout; bsg_trajectory_scan
+ * turns the lengths into dense offsets (off_dev has n + 1 entries, off[n] = total records; the
+ * total is also returned through *total_out after a stream synchronisation);
+ * bsg_trajectory_compact gathers record r = off[p] + t: packed state -> out_states (capacity
+ * total, ready for bsg_observations), action, owner playout and move number (each may be NULL). */
+int bsg_trajectory_scan(bsg_engine* e, const uint8_t* length_dev, int64_t n, int64_t* off_dev,
+                        int64_t* total_out, void* stream);
+int bsg_trajectory_compact(bsg_engine* e, const void* strided_states_dev, int64_t n, int64_t stride,
+                           const int64_t* off_dev, int64_t total, const int16_t* strided_actions_dev,
+                           int32_t actions_stride, void* out_states_dev, int64_t* out_actions_dev,
+                           int64_t* out_playout_dev, int64_t* out_step_dev, void* stream);
+
 /* ---- self-play actor on the forest: MANY games in flight, game v
  * = tree v.  Stands in for _play_game of python/algorithms/alpha_zero/alpha_zero.py:196-228 —
  * per move one search, policy target = root children's explore_count ** (1 / temperature)

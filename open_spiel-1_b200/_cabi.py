@@ -44,6 +44,7 @@ class PlayoutIO(ctypes.Structure):
       ("state_log_off", vp),
       ("root_playout_base", vp),
       ("value_only", i32),
+      ("state_log_stride", i64),
   ]
 
 
@@ -126,6 +127,8 @@ def _load():
       "bsg_forest_install_root": (ctypes.c_int, [vp, vp, vp]),
       "bsg_forest_tree_root": (ctypes.c_int, [vp, i32, ctypes.c_int, vp, vp, vp, vp, vp]),
       "bsg_forest_info": (ctypes.c_int, [vp, vp]),
+      "bsg_trajectory_scan": (ctypes.c_int, [vp, vp, i64, vp, vp, vp]),
+      "bsg_trajectory_compact": (ctypes.c_int, [vp, vp, i64, i64, vp, i64, vp, i32, vp, vp, vp, vp, vp]),
       "bsg_forest_search_roots": (ctypes.c_int, [vp, vp, vp, i64]),
       "bsg_forest_actor_step": (ctypes.c_int, [vp, ctypes.POINTER(ActorIO), vp]),
       "bsg_actor_emit": (ctypes.c_int, [vp, ctypes.POINTER(ActorEmitIO)]),

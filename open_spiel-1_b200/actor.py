@@ -186,7 +186,8 @@ class ForestActor:
     out_states = torch.zeros(total * e.state_bytes, dtype=torch.uint8, device=dev)
     offsets = torch.from_numpy(offsets_np).to(dev)
     # write straight into the replay buffer when the rows are contiguous there
-    direct = buffer is not None and buffer._head + total <= buffer.max_size and total <= buffer.max_size
+    direct = (buffer is not None and buffer._head + total <= buffer.max_size and total <= buffer.max_size and
+              (buffer._head * e.obs_size * 4) % 16 == 0)     # the batched writer stores 16 bytes at a time
     if direct:
       rows = slice(buffer._head, buffer._head + total)
       obs, policy, value = buffer.observation[rows], buffer.policy[rows], buffer.value[rows]

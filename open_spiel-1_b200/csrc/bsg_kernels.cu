@@ -300,7 +300,11 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         if (a.io.r_table && can) r = a.io.r_table[(size_t)lid * a.io.r_stride + min(t, (u32)a.io.r_stride - 1)];
         if (can) {
           prev = s;
-          if (a.io.state_log) G::store(s, a.io.state_log, a.io.state_log_cap, a.io.state_log_off[lid] + t);
+          if (a.io.state_log) {
+            if (a.io.state_log_off) G::store(s, a.io.state_log, a.io.state_log_cap, a.io.state_log_off[lid] + t);
+            else if ((int64_t)t < a.io.state_log_stride)
+              G::store(s, a.io.state_log, a.io.state_log_cap, (int64_t)lid * a.io.state_log_stride + t);
+          }
         }
       }
       int action = 0;
@@ -446,11 +450,23 @@ __device__ __forceinline__ u32 gather_bits(const u32* __restrict__ sm, int st, i
 }
 
 // Dynamic shared memory of expand_kernel: the staging ring + one bit-string row per state.
+// Aligned fast path (BSG_OBS_LUT): when a state's bit string is a whole number of 32-bit words
+// (breakthrough 192 planes bits / 768 mask bits, othello 192) the rows are stored unpadded, the
+// chunk's bits are ONE contiguous string, vector j is bits [4j, 4j+4) (planes) or [16j, 16j+16)
+// (mask) of it, and its 16 output bytes come from a shared-memory table: planes 16 x uint4
+// (nibble -> four floats), mask 256 x 8 bytes (byte -> eight 0/1 bytes).
+#ifndef BSG_OBS_LUT
+#define BSG_OBS_LUT 1
+#endif
+template <class G, bool kMask> struct expand_aligned_t {
+  static constexpr bool value = BSG_OBS_LUT && BSG_OBS_TMA && ((kMask ? G::kNumActions : G::kObsSize) % 32 == 0);
+};
 template <class G, bool kMask> constexpr size_t expand_smem_bytes() {
   constexpr int kWords = kMask ? G::kMaskWords : G::kObsWords;
-  constexpr int kRow = (kWords + 1) | 1;
+  constexpr int kRow = expand_aligned_t<G, kMask>::value ? kWords : ((kWords + 1) | 1);
 #if BSG_OBS_TMA
-  return (size_t)3 * BSG_OBS_TILE * 16 + (size_t)kChunk * kRow * 4;
+  return (size_t)3 * BSG_OBS_TILE * 16 + (size_t)kChunk * kRow * 4 + 16 +
+         (expand_aligned_t<G, kMask>::value ? (kMask ? 2048 : 256) : 0);
 #else
   return 0;
 #endif
@@ -463,7 +479,8 @@ expand_kernel(const void* __restrict__ states, int64_t n, const uint8_t* __restr
               void* __restrict__ out_) {
   constexpr int kBits = kMask ? G::kNumActions : G::kObsSize;
   constexpr int kWords = kMask ? G::kMaskWords : G::kObsWords;
-  constexpr int kRow = (kWords + 1) | 1;            // + one zero word for the funnel read; odd
+  constexpr bool kAligned = expand_aligned_t<G, kMask>::value;
+  constexpr int kRow = kAligned ? kWords : ((kWords + 1) | 1);   // general: + one zero word for the funnel read; odd
   constexpr int kPer = kMask ? 16 : 4;              // output elements per 16-byte store
 #if BSG_OBS_TMA
   // dynamic shared memory: [three staging tiles][kChunk rows]  (expand_smem_bytes below)
@@ -481,6 +498,23 @@ expand_kernel(const void* __restrict__ states, int64_t n, const uint8_t* __restr
   constexpr bool kTma = true;
   uint4* const stage = reinterpret_cast<uint4*>(expand_smem);
   int tsel = 0;
+  // look-up table of the aligned path, behind the rows (16-byte aligned)
+  unsigned char* const lut_raw = expand_smem + 3 * BSG_OBS_TILE * 16 + (((size_t)kChunk * kRow * 4 + 15) & ~(size_t)15);
+  if constexpr (kAligned) {
+    if constexpr (kMask) {
+      uint2* lut = reinterpret_cast<uint2*>(lut_raw);
+      const u32 b = threadIdx.x;   // kChunk = 256 threads: one entry each
+      lut[b] = make_uint2(((b & 15u) * 0x00204081u) & 0x01010101u, ((b >> 4) * 0x00204081u) & 0x01010101u);
+    } else {
+      uint4* lut = reinterpret_cast<uint4*>(lut_raw);
+      if (threadIdx.x < 16) {
+        const u32 x = threadIdx.x;
+        lut[x] = make_uint4((x & 1u) * 0x3F800000u, ((x >> 1) & 1u) * 0x3F800000u, ((x >> 2) & 1u) * 0x3F800000u,
+                            ((x >> 3) & 1u) * 0x3F800000u);
+      }
+    }
+    __syncthreads();
+  }
 #else
   constexpr bool kTma = false;
 #endif
@@ -519,7 +553,21 @@ expand_kernel(const void* __restrict__ states, int64_t n, const uint8_t* __restr
 #pragma unroll
         for (int q = 0; q < kTileVec / kChunk; ++q) {
           const int j = t * kTileVec + q * kChunk + threadIdx.x;
-          if (j < n16) {
+          if constexpr (kAligned) {
+            if (j < n16) {
+              uint4 v;
+              if constexpr (kMask) {
+                const u32 x = (sm[j >> 1] >> ((j & 1) * 16)) & 0xFFFFu;
+                const uint2* lut = reinterpret_cast<const uint2*>(lut_raw);
+                const uint2 lo = lut[x & 255u], hi = lut[x >> 8];
+                v = make_uint4(lo.x, lo.y, hi.x, hi.y);
+              } else {
+                const u32 x = (sm[j >> 3] >> ((j & 7) * 4)) & 15u;
+                v = reinterpret_cast<const uint4*>(lut_raw)[x];
+              }
+              sbuf[q * kChunk + threadIdx.x] = v;
+            }
+          } else if (j < n16) {
             const int e0 = j * kPer;
             const int st = e0 / kBits, r = e0 - st * kBits;
             u32 x = gather_bits<kBits, kRow>(sm, st, r, kPer, nst);
@@ -644,6 +692,7 @@ struct bsg_engine {
   void* d_roots = nullptr; size_t d_roots_bytes = 0;
   void* d_out = nullptr; size_t d_out_bytes = 0;
   void* d_fill = nullptr; size_t d_fill_bytes = 0;   // parked boards of value-only launches
+  void* d_scan = nullptr; size_t d_scan_bytes = 0;   // tile sums / offsets of bsg_trajectory_scan
   int value_only = 0;                                // bsg_engine_set_value_only: the *_host playouts
   void* h_pinned = nullptr; size_t h_pinned_bytes = 0;
   uint64_t* d_totals = nullptr;
@@ -732,6 +781,102 @@ template <class G>
 __global__ void forest_expand_root_kernel(ForestView F) {
   const int v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v < F.n_trees) ForestTree<G>::expand_root(F, v);
+}
+// Trajectory log compaction (bsg_trajectory_*).  Exclusive scan of the one-byte lengths in three
+// small kernels: per-CTA sums of 4096 lengths (16 per thread, one 16-byte load), one CTA scans the
+// CTA sums, every CTA rescans its tile and writes its offsets.
+constexpr int kScanTile = 4096;
+__device__ __forceinline__ u32 scan_bytes_sum(u32 x) {       // sum of the four bytes of x
+  return (x & 0xFFu) + ((x >> 8) & 0xFFu) + ((x >> 16) & 0xFFu) + (x >> 24);
+}
+__device__ __forceinline__ void scan_load16(const uint8_t* len, int64_t n, int64_t i0, u32 w[4]) {
+  if (i0 + 16 <= n && (((uintptr_t)(len + i0)) & 15) == 0) {
+    const uint4 v = *reinterpret_cast<const uint4*>(len + i0);
+    w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
+  } else {
+    for (int k = 0; k < 4; ++k) {
+      u32 x = 0;
+      for (int j = 0; j < 4; ++j) { const int64_t i = i0 + 4 * k + j; if (i < n) x |= (u32)len[i] << (8 * j); }
+      w[k] = x;
+    }
+  }
+}
+__device__ __forceinline__ u32 scan_block_exclusive(u32 mine, u32* sm, u32* total) {   // 256 threads
+  const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  u32 inc = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const u32 v = __shfl_up_sync(0xFFFFFFFFu, inc, o); if (lane >= (u32)o) inc += v; }
+  if (lane == 31) sm[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    u32 w = lane < 8 ? sm[lane] : 0u, winc = w;
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) { const u32 v = __shfl_up_sync(0xFFFFFFFFu, winc, o); if (lane >= (u32)o) winc += v; }
+    if (lane < 8) sm[lane] = winc - w;
+    if (lane == 7) sm[8] = winc;
+  }
+  __syncthreads();
+  if (total) *total = sm[8];
+  return sm[warp] + inc - mine;
+}
+__global__ void __launch_bounds__(256) traj_tile_sums_kernel(const uint8_t* len, int64_t n, u32* tile_sums) {
+  __shared__ u32 sm[9];
+  u32 w[4];
+  scan_load16(len, n, (int64_t)blockIdx.x * kScanTile + threadIdx.x * 16, w);
+  const u32 mine = scan_bytes_sum(w[0]) + scan_bytes_sum(w[1]) + scan_bytes_sum(w[2]) + scan_bytes_sum(w[3]);
+  u32 total;
+  scan_block_exclusive(mine, sm, &total);
+  if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+__global__ void __launch_bounds__(256) traj_tile_scan_kernel(const u32* tile_sums, int n_tiles, int64_t* tile_off, int64_t* off_n) {
+  __shared__ u32 sm[9];
+  __shared__ long long carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int base = 0; base < n_tiles; base += 256) {
+    const int i = base + threadIdx.x;
+    const u32 mine = i < n_tiles ? tile_sums[i] : 0u;
+    u32 total;
+    const u32 ex = scan_block_exclusive(mine, sm, &total);
+    if (i < n_tiles) tile_off[i] = carry + ex;
+    __syncthreads();
+    if (threadIdx.x == 0) carry += total;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *off_n = carry;
+}
+__global__ void __launch_bounds__(256) traj_tile_offsets_kernel(const uint8_t* len, int64_t n, const int64_t* tile_off, int64_t* off) {
+  __shared__ u32 sm[9];
+  u32 w[4];
+  const int64_t i0 = (int64_t)blockIdx.x * kScanTile + threadIdx.x * 16;
+  scan_load16(len, n, i0, w);
+  const u32 mine = scan_bytes_sum(w[0]) + scan_bytes_sum(w[1]) + scan_bytes_sum(w[2]) + scan_bytes_sum(w[3]);
+  long long run = tile_off[blockIdx.x] + scan_block_exclusive(mine, sm, nullptr);
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    const int64_t i = i0 + k;
+    if (i < n) off[i] = run;
+    run += (w[k >> 2] >> (8 * (k & 3))) & 0xFFu;
+  }
+}
+template <class G>
+__global__ void traj_compact_kernel(const void* strided, int64_t n, int64_t stride, const int64_t* off, int64_t total,
+                                    const int16_t* acts, int32_t acts_stride, void* out_states,
+                                    int64_t* out_actions, int64_t* out_playout, int64_t* out_step) {
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < total; r += (int64_t)gridDim.x * blockDim.x) {
+    int64_t lo = 0, hi = n;                      // the playout p with off[p] <= r < off[p + 1]
+    while (hi - lo > 1) {
+      const int64_t mid = (lo + hi) >> 1;
+      if (off[mid] <= r) lo = mid; else hi = mid;
+    }
+    const int64_t t = r - off[lo];
+    typename G::State s;
+    G::load(s, strided, n * stride, lo * stride + t);
+    G::store(s, out_states, total, r);
+    if (out_actions) out_actions[r] = acts ? (int64_t)acts[lo * acts_stride + t] : -1;
+    if (out_playout) out_playout[r] = lo;
+    if (out_step) out_step[r] = t;
+  }
 }
 __global__ void forest_fill_alive_kernel(int64_t* dst, int64_t value, const uint8_t* alive, int n) {
   const int v = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1070,6 +1215,7 @@ void bsg_destroy(bsg_engine* e) {
   if (e->d_roots) cudaFree(e->d_roots);
   if (e->d_out) cudaFree(e->d_out);
   if (e->d_fill) cudaFree(e->d_fill);
+  if (e->d_scan) cudaFree(e->d_scan);
   if (e->h_pinned) cudaFreeHost(e->h_pinned);
   if (e->d_totals) cudaFree(e->d_totals);
   if (e->d_work) cudaFree(e->d_work);
@@ -1106,8 +1252,11 @@ int bsg_playouts(bsg_engine* e, const void* roots, int64_t n_roots, int32_t roll
   if (io) a.io = *io;
   if (a.io.r_table && a.io.r_stride < 1) return fail(e, BSG_ERR_BAD_ARG, "r_table needs r_stride >= 1");
   if (a.io.actions && a.io.actions_stride < 1) return fail(e, BSG_ERR_BAD_ARG, "actions needs actions_stride >= 1");
-  if (a.io.state_log && (!a.io.state_log_off || a.io.state_log_cap < 1))
-    return fail(e, BSG_ERR_BAD_ARG, "state_log needs state_log_off and state_log_cap >= 1");
+  if (a.io.state_log && ((!a.io.state_log_off && a.io.state_log_stride < 1) || a.io.state_log_cap < 1 ||
+                         (a.io.state_log_off && a.io.state_log_stride != 0)))
+    return fail(e, BSG_ERR_BAD_ARG, "state_log needs state_log_cap >= 1 and either state_log_off or state_log_stride");
+  if (a.io.state_log && !a.io.state_log_off && (int64_t)total * a.io.state_log_stride > a.io.state_log_cap)
+    return fail(e, BSG_ERR_BAD_ARG, "state_log_cap is smaller than playouts * state_log_stride");
   BSG_CUDA(e, cudaSetDevice(e->device));
   return dispatch_device_game(e->game, PlayoutOp{e, a, (cudaStream_t)stream});
 }
@@ -1766,6 +1915,56 @@ int bsg_forest_install_root(bsg_forest* f, const int64_t* base_dev, const int64_
   BSG_CUDA(e, cudaStreamSynchronize(e->own_stream));
   return BSG_OK;
 }
+// ---- one-pass trajectories
+}  // extern "C"
+namespace {
+struct TrajCompactOp {
+  bsg_engine* e; const void* strided; int64_t n, stride; const int64_t* off; int64_t total;
+  const int16_t* acts; int32_t acts_stride; void* out_states; int64_t* oa; int64_t* op; int64_t* os; cudaStream_t st;
+  template <class G> int operator()() const {
+    const int64_t blocks = (total + 255) / 256;
+    const int grid = (int)(blocks < (int64_t)e->sm_count * 16 ? blocks : (int64_t)e->sm_count * 16);
+    traj_compact_kernel<G><<<grid < 1 ? 1 : grid, 256, 0, st>>>(strided, n, stride, off, total, acts, acts_stride,
+                                                              out_states, oa, op, os);
+    BSG_CUDA(e, cudaGetLastError());
+    return BSG_OK;
+  }
+};
+}  // namespace
+extern "C" {
+int bsg_trajectory_scan(bsg_engine* e, const uint8_t* length_dev, int64_t n, int64_t* off_dev,
+                        int64_t* total_out, void* stream) {
+  if (!e || !length_dev || !off_dev || n < 1) return BSG_ERR_BAD_ARG;
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int n_tiles = (int)((n + kScanTile - 1) / kScanTile);
+  // tile sums (u32) and tile offsets (int64) live in the engine's result scratch
+  int rc = ensure(e, &e->d_scan, &e->d_scan_bytes, (size_t)n_tiles * 12 + 96, false);
+  if (rc != BSG_OK) return rc;
+  int64_t* tile_off = (int64_t*)e->d_scan;
+  u32* tile_sums = (u32*)((char*)e->d_scan + (((size_t)n_tiles * 8 + 15) & ~(size_t)15));
+  traj_tile_sums_kernel<<<n_tiles, 256, 0, st>>>(length_dev, n, tile_sums);
+  traj_tile_scan_kernel<<<1, 256, 0, st>>>(tile_sums, n_tiles, tile_off, off_dev + n);
+  traj_tile_offsets_kernel<<<n_tiles, 256, 0, st>>>(length_dev, n, tile_off, off_dev);
+  BSG_CUDA(e, cudaGetLastError());
+  if (total_out) {
+    BSG_CUDA(e, cudaMemcpyAsync(total_out, off_dev + n, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+    BSG_CUDA(e, cudaStreamSynchronize(st));
+  }
+  return BSG_OK;
+}
+int bsg_trajectory_compact(bsg_engine* e, const void* strided_states_dev, int64_t n, int64_t stride,
+                           const int64_t* off_dev, int64_t total, const int16_t* strided_actions_dev,
+                           int32_t actions_stride, void* out_states_dev, int64_t* out_actions_dev,
+                           int64_t* out_playout_dev, int64_t* out_step_dev, void* stream) {
+  if (!e || !strided_states_dev || !off_dev || !out_states_dev || n < 1 || stride < 1 || total < 0) return BSG_ERR_BAD_ARG;
+  if (total == 0) return BSG_OK;
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  return dispatch_device_game(e->game, TrajCompactOp{e, strided_states_dev, n, stride, off_dev, total, strided_actions_dev,
+                                                     actions_stride, out_states_dev, out_actions_dev, out_playout_dev,
+                                                     out_step_dev, (cudaStream_t)stream});
+}
+
 // ---- self-play actor on the forest (bsg_actor.cuh): one game per tree
 }  // extern "C"
 namespace {

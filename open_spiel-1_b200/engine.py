@@ -167,7 +167,8 @@ class Engine:
                length=None, terminal=None, actions=None, root_sum_ret0=None,
                root_sum_steps=None, totals=None, max_steps=0, step_limit=None, r_table=None,
                final_states=None, final_before_terminal=False, state_log=None,
-               state_log_off=None, root_playout_base=None, value_only=False, stream=None):
+               state_log_off=None, root_playout_base=None, value_only=False, state_log_stride=0,
+               stream=None):
     """Launches n_roots * rollouts random playouts (bsg_playouts).  All tensors are device
     tensors owned by the caller; see include/bsg.h for their meaning.  Asynchronous."""
     io = C.PlayoutIO()
@@ -190,6 +191,7 @@ class Engine:
     io.state_log_off = self._p(state_log_off)
     io.root_playout_base = self._p(root_playout_base)
     io.value_only = 1 if value_only else 0   # hex / y: fill the board, read the winner off it
+    io.state_log_stride = int(state_log_stride)
     C.check(C.lib.bsg_playouts(self._h, self._p(roots), int(n_roots), int(rollouts),
                                int(seed) & (2**64 - 1), int(first_playout), ctypes.byref(io),
                                self._stream_ptr(stream)), self._h)
@@ -229,40 +231,76 @@ class Engine:
     self.launches += 1 + (1 if legal_mask is not None else 0)
     return out, legal_mask
 
+  def _traj_buffer(self, store, name, numel, dtype):
+    """A cached device tensor of at least `numel` elements (grown, never shrunk)."""
+    torch = _torch()
+    t = store.get(name)
+    if t is None or t.numel() < numel or t.dtype != dtype:
+      t = torch.empty(max(int(numel), 1), dtype=dtype, device=self.torch_device)
+      store[name] = t
+    return t
+
   def trajectories(self, roots, n_roots, rollouts=1, seed=0, first_playout=0, want_mask=True,
-                   want_actions=True):
+                   want_actions=True, out=None):
     """Self-play records of every decision point of n_roots * rollouts random playouts, as
     the AlphaZero actor keeps them (python/algorithms/alpha_zero/alpha_zero.py:196-228):
     observation of the player to move, legal-action mask, the action taken and the final
-    return for player 0.  Everything stays on the device: launch 1 plays the playouts and
-    returns their lengths, an exclusive prefix sum gives dense offsets, launch 2 replays them
-    (playouts are deterministic functions of (seed, playout id, root)) writing the packed
-    state before every move, and the batched writer expands the log.
+    return for player 0.  Everything stays on the device and every playout is played ONCE:
+    the launch logs the packed state before every move (and the action) at a fixed stride per
+    playout, a scan of the lengths gives dense offsets, a compaction kernel gathers record
+    off[p] + t, and the batched writer expands the compact log (bsg_trajectory_*; no PyTorch
+    operator runs between the first launch and the last).
+
+    `out`: a dict returned by an earlier call — its tensors are reused when they are large
+    enough (a steady-state actor loop then allocates nothing).
 
     Returns a dict of device tensors: obs [T, C, H, W] f32, mask [T, A] u8 (or None),
     actions [T] int64 (or None), playout [T] / step [T] int64 (owner and move number of each
-    record), ret0 [n] int8, length [n] int64, offsets [n] int64, states (packed log, capacity T)."""
+    record), ret0 [n] int8, length [n] uint8, offsets [n] int64, states (packed log, capacity T).
+    The tensors are views of buffers the engine (or `out`) owns: copy what must outlive the
+    next call."""
     torch = _torch()
     dev = self.torch_device
     n = int(n_roots) * int(rollouts)
-    ret0 = torch.zeros(n, dtype=torch.int8, device=dev)
-    length8 = torch.zeros(n, dtype=torch.uint8, device=dev)
-    self.playouts(roots, n_roots, rollouts, seed, first_playout, ret0=ret0, length=length8)
-    length = length8.to(torch.int64)
-    offsets = torch.cumsum(length, 0) - length
-    total = int(length.sum().item())
-    states = torch.zeros(max(total, 1) * self.state_bytes, dtype=torch.uint8, device=dev)
-    acts = None
-    if want_actions:
-      acts = torch.full((n, max(int(length8.max().item()), 1)), -1, dtype=torch.int16, device=dev)
-    self.playouts(roots, n_roots, rollouts, seed, first_playout, state_log=states,
-                  state_log_off=offsets, actions=acts)
-    owner = torch.repeat_interleave(torch.arange(n, device=dev), length)
-    step = torch.arange(total, device=dev) - offsets[owner]
-    obs, mask = self.observations(states, total, None, want_mask=want_mask) if total else (None, None)
-    actions = acts[owner, step].to(torch.int64) if want_actions and total else None
-    return {"obs": obs, "mask": mask, "actions": actions, "playout": owner, "step": step,
-            "ret0": ret0, "length": length, "offsets": offsets, "states": states, "total": total}
+    stride = 120 if self.gid == C.OTHELLO else int(self.max_len)   # othello: placements + passes
+    sc = self.__dict__.setdefault("_traj_scratch", {})
+    ret0 = self._traj_buffer(sc, "ret0", n, torch.int8)[:n]
+    length = self._traj_buffer(sc, "length", n, torch.uint8)[:n]
+    strided = self._traj_buffer(sc, "strided", n * stride * self.state_bytes, torch.uint8)[:n * stride * self.state_bytes]
+    acts = self._traj_buffer(sc, "acts", n * stride, torch.int16)[:n * stride].view(n, stride) if want_actions else None
+    off = self._traj_buffer(sc, "off", n + 1, torch.int64)[:n + 1]
+    stream = self._stream_ptr(None)
+    self.playouts(roots, n_roots, rollouts, seed, first_playout, ret0=ret0, length=length,
+                  state_log=strided, state_log_stride=stride, actions=acts)
+    total_c = ctypes.c_int64(0)
+    C.check(C.lib.bsg_trajectory_scan(self._h, self._p(length), n, self._p(off), ctypes.byref(total_c),
+                                      stream), self._h)
+    total = int(total_c.value)
+    store = out if out is not None else self.__dict__.setdefault("_traj_out", {})
+    store = store.setdefault("_buffers", {}) if out is not None else store
+    t1 = max(total, 1)
+    states = self._traj_buffer(store, "states", t1 * self.state_bytes, torch.uint8)[:t1 * self.state_bytes]
+    obs = self._traj_buffer(store, "obs", t1 * self.obs_size, torch.float32)[:t1 * self.obs_size].view(
+        (t1,) + tuple(self.obs_shape))
+    mask = self._traj_buffer(store, "mask", t1 * self.num_actions, torch.uint8)[:t1 * self.num_actions].view(
+        t1, self.num_actions) if want_mask else None
+    actions = self._traj_buffer(store, "actions", t1, torch.int64)[:t1] if want_actions else None
+    owner = self._traj_buffer(store, "playout", t1, torch.int64)[:t1]
+    step = self._traj_buffer(store, "step", t1, torch.int64)[:t1]
+    if total:
+      C.check(C.lib.bsg_trajectory_compact(self._h, self._p(strided), n, stride, self._p(off), total,
+                                           self._p(acts), stride if want_actions else 0,
+                                           self._p(states), self._p(actions), self._p(owner),
+                                           self._p(step), stream), self._h)
+      self.observations(states, total, None, out=obs, legal_mask=mask)
+      self.launches += 2
+    res = {"obs": obs[:total] if total else None, "mask": mask[:total] if (want_mask and total) else None,
+           "actions": actions[:total] if (want_actions and total) else None,
+           "playout": owner[:total], "step": step[:total], "ret0": ret0, "length": length,
+           "offsets": off[:n], "states": states, "total": total}
+    if out is not None:
+      res["_buffers"] = store
+    return res
 
   # ---- host-buffer entry points (copies inside the call; synchronous)
   def playouts_host(self, packed, n_roots, rollouts=1, seed=0, first_playout=0,
