@@ -61,6 +61,9 @@ def parse_args():
   ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline sample budget")
   ap.add_argument("--no-cpu-baseline", action="store_true")
   ap.add_argument("--no-extras", action="store_true", help="skip obs / other-game side numbers")
+  ap.add_argument("--no-quality", action="store_true",
+                  help="skip the one-tree quality yardstick of cfg5 and the cfg1 block (tens of thousands of "
+                       "tiny launches: keeps an ncu launch list readable)")
   return ap.parse_args()
 
 
@@ -345,6 +348,33 @@ def run_cfg5(bsg, torch, dev, local, rank, world, dist, single_tree):
         "note": "one native host tree (the reference's MCTSBot search, csrc/bsg_mcts.cuh) with all "
                 "1 Mi simulations per root, 256 rollouts/leaf, leaf_batch 256, on one GPU"}
   forest.close()
+  # weak-scaling companion: the SAME per-GPU forest at every N (4096 trees x 256 simulations per
+  # GPU, so N Mi simulations per move in the job), one all-reduce per search step as above
+  if world > 1:
+    trees_w = CFG5_TOTAL_SIMS // CFG5_SIMS_PER_TREE
+    ev_w = bsg.GpuRolloutEvaluator(eng, n_rollouts=CFG5_ROLLOUTS, seed=ROOT_SEED + 7)
+    fw = ForestMCTS(game, 2.0, CFG5_TOTAL_SIMS * world, ev_w, trees_w, sims_per_step=CFG5_SIMS_PER_STEP,
+                    solve=True, seed=5, leaf_batch=CFG5_LEAF_BATCH, device=dev)
+    fw.mcts_search(roots[0])
+    fw.allreduce_stats()
+    secs_w, sims_w = 0.0, 0
+    for st in roots[:5]:
+      sync()
+      t0 = time.perf_counter()
+      root = fw.mcts_search(st)
+      secs_w += time.perf_counter() - t0
+      sims_w += sum(c.explore_count for c in root.children) + trees_w * world
+    arw = fw.allreduce_stats()
+    if dist is not None:
+      t = torch.tensor([secs_w], dtype=torch.float64, device=dev)
+      dist.all_reduce(t, op=dist.ReduceOp.MAX)
+      secs_w = float(t[0])
+    out["weak_scaling"] = {
+        "workload": "the 1-GPU forest on every GPU: %d trees x %d simulations per GPU = %d simulations "
+                    "per move in the job, 5 roots" % (trees_w, CFG5_SIMS_PER_TREE, CFG5_TOTAL_SIMS * world),
+        "simulations": sims_w, "seconds": secs_w, "simulations_per_s": sims_w / secs_w,
+        "ms_per_move": 1e3 * secs_w / 5, "all_reduces": arw["count"], "allreduce_mean_us": arw["mean_us"]}
+    fw.close()
   eng.close()
   return out
 
@@ -410,7 +440,7 @@ def run_ours(args):
         pre["cpu_baseline"]["mcts"] = cpu_mcts_baselines()
       except Exception as ex:
         pre["cpu_baseline"]["mcts"] = {"error": repr(ex)}
-    if not args.no_extras and game == "connect_four":
+    if not args.no_extras and not args.no_quality and game == "connect_four":
       try:
         pre["single_tree"] = cfg5_single_tree_reference(bsg, local)
         if world == 1:

@@ -203,6 +203,10 @@ struct ConnectFour {
 #define BSG_C4_GROUP 4
 #endif
   static constexpr int kGroupSteps = BSG_C4_GROUP;   // steps between two refills of the lean kernel
+#ifndef BSG_C4_MINBLOCKS
+#define BSG_C4_MINBLOCKS 1
+#endif
+  static constexpr int kMinBlocks = BSG_C4_MINBLOCKS;   // A/B switch: register cap of the lean kernel
 #ifndef BSG_C4_LAZY_DRAW
 #define BSG_C4_LAZY_DRAW 1
 #endif

@@ -34,6 +34,9 @@ namespace bsg {
 #ifndef BSG_SMEM_DRAWS
 #define BSG_SMEM_DRAWS 1    // measured on B200: hex 71.8 -> 73.9, y 23.9 -> 25.5 G steps/s
 #endif
+#ifndef BSG_STAGE_ROOTS
+#define BSG_STAGE_ROOTS 0   // A/B switch: chunk roots staged in shared memory (lean, single-plane games); measured slower on B200: connect_four 264.1 -> 260.8 G steps/s (46 -> 56 registers)
+#endif
 #ifndef BSG_EXTRA_RINGS
 #define BSG_EXTRA_RINGS 0   // A/B switch: up to this many warp-voted extra flood rings per iteration
 #endif
@@ -126,6 +129,17 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
   const u32 lane_lt = (1u << lane) - 1u;
   u32 begin = 0, count = 0, cursor = 0;
   bool drained = false;
+  // Root staging (lean launches of single-plane games at one playout per root): when a warp
+  // draws a chunk it copies the chunk's roots into shared memory with one coalesced load per
+  // lane, so a claim — divergent code that runs in almost every group — reads its root with an
+  // LDS instead of stalling on a dependent global load.  Two buffers per warp: lanes may still
+  // claim the tail of the old chunk in the very claim that draws the new one.
+  constexpr bool kStage = BSG_STAGE_ROOTS && !kFull && !kBase && !kFill && G::kPlanes == 1 &&
+                          G::kStateBytes <= 16 && (kChunkPlayouts * G::kStateBytes) % 16 == 0;
+  constexpr int kStageBytes = kStage ? kChunkPlayouts * G::kStateBytes : 16;
+  __shared__ __align__(16) unsigned char root_sm[kStage ? kThreads / 32 : 1][2][kStageBytes];
+  const bool stage = kStage && a.rollouts == 1u;   // launch-uniform
+  u32 par = 0;                                      // buffer of the chunk (begin, count)
 
   typename G::State s;
   G::init(s);
@@ -164,6 +178,21 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
       nbegin = min(nb, a.n_playouts);
       ncount = min((u32)kChunkPlayouts, a.n_playouts - nbegin);
       drained = ncount == 0;
+      if constexpr (kStage) {
+        if (stage && ncount) {
+          // chunks start at multiples of kChunkPlayouts: the source is 16-byte aligned whenever
+          // the root buffer is (cudaMalloc / torch); fall back to words otherwise
+          const char* src = (const char*)a.roots + (size_t)(a.root0 + nbegin) * G::kStateBytes;
+          unsigned char* dst = root_sm[threadIdx.x >> 5][par ^ 1u];
+          const u32 bytes = ncount * G::kStateBytes;
+          if ((((uintptr_t)src) & 15) == 0 && (bytes & 15u) == 0) {
+            for (u32 i = lane; i < bytes / 16; i += 32) reinterpret_cast<uint4*>(dst)[i] = reinterpret_cast<const uint4*>(src)[i];
+          } else {
+            for (u32 i = lane; i < bytes / 4; i += 32) reinterpret_cast<u32*>(dst)[i] = reinterpret_cast<const u32*>(src)[i];
+          }
+          __syncwarp();
+        }
+      }
     }
     if (live == 0) {
       if (have) {  // publish the finished playout
@@ -193,13 +222,14 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         my_done += 1;
       }
       u32 idx = cursor + __popc(want & lane_lt);
-      u32 base = begin, cnt = count;
-      if (idx >= count) { idx -= count; base = nbegin; cnt = ncount; }
+      u32 base = begin, cnt = count, buf = par;
+      if (idx >= count) { idx -= count; base = nbegin; cnt = ncount; buf = par ^ 1u; }
       have = idx < cnt ? 1u : 0u;
       if (have) {  // claim the next playout
         lid = base + idx;
         u32 root = a.rollouts == 1 ? lid : lid / a.rollouts;
-        G::load(s, a.roots, a.n_roots, a.root0 + root);
+        if (kStage && stage) G::load(s, root_sm[threadIdx.x >> 5][buf], kChunkPlayouts, idx);
+        else G::load(s, a.roots, a.n_roots, a.root0 + root);
         bool skip = false;
         if (kBase) {
           const unsigned long long rb = a.io.root_playout_base[a.root0 + root];
@@ -229,7 +259,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
       }
     }
     cursor += nwant;
-    if (grab) { cursor = cursor > count ? cursor - count : 0u; begin = nbegin; count = ncount; }
+    if (grab) { cursor = cursor > count ? cursor - count : 0u; begin = nbegin; count = ncount; par ^= 1u; }
     if (!__any_sync(0xFFFFFFFFu, live != 0)) {
       if (!__any_sync(0xFFFFFFFFu, have != 0)) break;
       continue;
