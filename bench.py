@@ -608,6 +608,27 @@ def e2e_block(args, eng, torch, dev, states, n, first, barrier, reduce_max_sum, 
   out["h2d_only_ceiling_game_steps_per_s"] = sm[1] / reps / (mx[0] * 1e-3)
   out["numa_nodes"] = numa_summary(eng.device)
   del scratch
+  # the same call with the roots in WRITE-COMBINED page-locked memory (bsg_host_alloc)
+  try:
+    from open_spiel_1_b200.engine import HostBuffer
+    wc = HostBuffer(states.numel(), write_combined=True)
+    wc.array[:] = host_np
+    for i in range(2):
+      eng.playouts_host(wc.array, n, 1, seed=ROOT_SEED, first_playout=first + i * n)
+    barrier()
+    t0 = time.perf_counter()
+    game_steps = 0
+    for i in range(reps):
+      t, _, _ = eng.playouts_host(wc.array, n, 1, seed=ROOT_SEED, first_playout=first + (args.warmup + i) * n)
+      game_steps += int(t[1])
+    torch.cuda.synchronize(dev)
+    secs = time.perf_counter() - t0
+    mxw, smw = reduce_max_sum([secs, float(game_steps)])
+    out["write_combined_roots"] = {"value": smw[1] / mxw[0], "unit": "game-steps/s",
+                                   "api": "bsg_playouts_host, roots in cudaHostAllocWriteCombined memory (bsg_host_alloc)"}
+    wc.close()
+  except Exception as ex:
+    out["write_combined_roots"] = {"error": repr(ex)}
   # per-playout results: (int)Returns()[0] and the move count of every playout copied back into
   # page-locked host arrays (2 B per playout) — what evaluate_batch consumes
   try:

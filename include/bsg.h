@@ -357,6 +357,12 @@ int bsg_forest_search_roots(bsg_forest* f, const void* roots_dev, const uint8_t*
                             int64_t simulations_per_tree);
 int bsg_forest_actor_step(bsg_forest* f, const bsg_actor_io* io, uint32_t* n_alive_out);
 int bsg_actor_emit(bsg_engine* e, const bsg_actor_emit_io* io);
+/* Page-locked host memory for root / result buffers of the *_host entry points (cudaHostAlloc,
+ * portable).  write_combined != 0 asks for write-combined pages: the CPU must only WRITE them
+ * (reads are uncached and very slow), in exchange the device's DMA reads skip cache snooping —
+ * the right kind for roots that the host fills once and the GPU consumes.  NULL on failure. */
+void* bsg_host_alloc(size_t bytes, int write_combined);
+void bsg_host_free(void* p);
 /* The engine's own CUDA stream (cudaStream_t as void*): where bsg_forest_* and bsg_actor_* work
  * is ordered, for callers that want to order their own work behind it. */
 void* bsg_engine_stream(bsg_engine* e);

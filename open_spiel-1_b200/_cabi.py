@@ -133,6 +133,8 @@ def _load():
       "bsg_forest_actor_step": (ctypes.c_int, [vp, ctypes.POINTER(ActorIO), vp]),
       "bsg_actor_emit": (ctypes.c_int, [vp, ctypes.POINTER(ActorEmitIO)]),
       "bsg_engine_stream": (vp, [vp]),
+      "bsg_host_alloc": (vp, [ctypes.c_size_t, ctypes.c_int]),
+      "bsg_host_free": (None, [vp]),
       "bsg_comm_unique_id": (ctypes.c_int, [vp]),
       "bsg_comm_init": (ctypes.c_int, [vp, ctypes.c_int, ctypes.c_int, vp]),
       "bsg_comm_destroy": (ctypes.c_int, [vp]),

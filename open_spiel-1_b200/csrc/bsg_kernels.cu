@@ -2076,6 +2076,13 @@ int bsg_actor_emit(bsg_engine* e, const bsg_actor_emit_io* io) {
   return dispatch_device_game(e->game, ActorEmitOp{e, E});
 }
 void* bsg_engine_stream(bsg_engine* e) { return e ? (void*)e->own_stream : nullptr; }
+void* bsg_host_alloc(size_t bytes, int write_combined) {
+  void* p = nullptr;
+  const unsigned flags = cudaHostAllocPortable | (write_combined ? cudaHostAllocWriteCombined : 0u);
+  if (cudaHostAlloc(&p, bytes ? bytes : 1, flags) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  return p;
+}
+void bsg_host_free(void* p) { if (p) cudaFreeHost(p); }
 
 // ---- the engine's own NCCL communicator + the root merge on the engine's stream
 int bsg_comm_unique_id(uint8_t id_out[128]) {

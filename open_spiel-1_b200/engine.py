@@ -94,6 +94,31 @@ def draw(seed, playout, t):
   return int(C.lib.bsg_draw(seed, playout, t))
 
 
+class HostBuffer:
+  """Page-locked host memory from bsg_host_alloc as a numpy uint8 array (`.array`); freed by
+  close() / garbage collection.  write_combined=True: fill it with ONE sequential write
+  (`buf.array[:] = data`) and do not read it back."""
+
+  def __init__(self, nbytes, write_combined=False):
+    self.nbytes = int(nbytes)
+    self.ptr = C.lib.bsg_host_alloc(self.nbytes, 1 if write_combined else 0)
+    if not self.ptr:
+      raise RuntimeError("bsg: cudaHostAlloc of %d bytes failed" % self.nbytes)
+    self.array = np.ctypeslib.as_array((ctypes.c_uint8 * self.nbytes).from_address(self.ptr))
+
+  def close(self):
+    if getattr(self, "ptr", None):
+      self.array = None
+      C.lib.bsg_host_free(self.ptr)
+      self.ptr = None
+
+  def __del__(self):
+    try:
+      self.close()
+    except Exception:  # pragma: no cover
+      pass
+
+
 def _torch():
   import torch  # local: only device paths need it
   return torch
