@@ -34,7 +34,7 @@ extern "C" {
 /* Game ids.  Strings accepted by bsg_game_id are the reference's game strings
  * (open_spiel/spiel.h:792-803): "tic_tac_toe", "connect_four", "breakthrough",
  * "breakthrough(rows=8,columns=8)", "hex", "hex(board_size=11)", "pentago", "othello", "y",
- * "y(board_size=19)". */
+ * "y(board_size=19)", "havannah", "havannah(board_size=8)". */
 #define BSG_TIC_TAC_TOE 0
 #define BSG_CONNECT_FOUR 1
 #define BSG_BREAKTHROUGH 2
@@ -49,6 +49,9 @@ extern "C" {
 #define BSG_Y 7       /* open_spiel/games/y.cc, board_size = 19 (the reference's default), same row */
 /* Host-helper-only id for the reference's y(board_size=9) golden playthrough; no kernels. */
 #define BSG_Y9_HOST_ONLY 8
+#define BSG_HAVANNAH 9 /* open_spiel/games/havannah.cc, board_size = 8 (the reference's default), same row */
+/* Host-helper-only id for the reference's havannah(board_size=4) golden playthrough; no kernels. */
+#define BSG_HAVANNAH4_HOST_ONLY 10
 
 #define BSG_OK 0
 #define BSG_ERR_BAD_GAME (-1)

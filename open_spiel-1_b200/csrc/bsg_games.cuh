@@ -1842,3 +1842,5 @@ typedef YT<19> Y;
 
 
 }  // namespace bsg
+
+#include "bsg_havannah.cuh"

@@ -15,6 +15,7 @@ namespace bsg {
 
 typedef HexT<5> Hex5;
 typedef YT<9> Y9;
+typedef HavannahT<4> Havannah4;
 constexpr int kMaxLegal = 320;   // pentago: 36 cells x 8 rotations
 
 template <class G> struct TablesOf {
@@ -35,6 +36,8 @@ template <> inline bool apply_any<Hex5>(Hex5::State& s, int a) { return Hex5::ap
 template <> inline bool apply_any<Pentago>(Pentago::State& s, int a) { return Pentago::apply(s, a, TablesOf<Pentago>::get()); }
 template <> inline bool apply_any<Y>(Y::State& s, int a) { return Y::apply(s, a, TablesOf<Y>::get()); }
 template <> inline bool apply_any<Y9>(Y9::State& s, int a) { return Y9::apply(s, a, TablesOf<Y9>::get()); }
+template <> inline bool apply_any<Havannah>(Havannah::State& s, int a) { return Havannah::apply(s, a, TablesOf<Havannah>::get()); }
+template <> inline bool apply_any<Havannah4>(Havannah4::State& s, int a) { return Havannah4::apply(s, a, TablesOf<Havannah4>::get()); }
 
 // Calls f.template operator()<G>() for the game id; returns BSG_ERR_BAD_GAME otherwise.
 template <class F> inline int dispatch_game(int game, F&& f) {
@@ -48,6 +51,8 @@ template <class F> inline int dispatch_game(int game, F&& f) {
     case BSG_OTHELLO: return f.template operator()<Othello>();
     case BSG_Y: return f.template operator()<Y>();
     case BSG_Y9_HOST_ONLY: return f.template operator()<Y9>();
+    case BSG_HAVANNAH: return f.template operator()<Havannah>();
+    case BSG_HAVANNAH4_HOST_ONLY: return f.template operator()<Havannah4>();
     default: break;
   }
   return BSG_ERR_BAD_GAME;
@@ -62,6 +67,7 @@ template <class F> inline int dispatch_device_game(int game, F&& f) {
     case BSG_PENTAGO: return f.template operator()<Pentago>();
     case BSG_OTHELLO: return f.template operator()<Othello>();
     case BSG_Y: return f.template operator()<Y>();
+    case BSG_HAVANNAH: return f.template operator()<Havannah>();
     default: break;
   }
   return BSG_ERR_BAD_GAME;
@@ -422,6 +428,38 @@ template <int N> struct Text<YT<N>> {  // y.cc:155-225 (plain output: ansi_color
         out += !stone ? '.' : (p1 ? '@' : 'O');
       }
       if (found_last) out += ']';
+      out += '\n';
+    }
+    return out;
+  }
+  static bool has_board_format() { return false; }
+  static std::string serialize(const typename G::State&) { return std::string(); }
+  static int deserialize(typename G::State&, const char*) { return BSG_ERR_BAD_ARG; }
+};
+
+template <int S> struct Text<HavannahT<S>> {  // havannah.cc:197-267 (plain output: ansi_color_output = false)
+  typedef HavannahT<S> G;
+  static std::string to_string(const typename G::State& s) {
+    const int D = G::D;
+    std::string out(S + 3, ' ');
+    for (int x = 0; x < S; ++x) { out += ' '; out += (char)('a' + x); }
+    out += '\n';
+    const int last = (int)s.last - 1;
+    for (int y = 0; y < D; ++y) {
+      const int indent = (S - 1 - y < 0 ? y - (S - 1) : S - 1 - y) + 1 + ((y + 1) < 10 ? 1 : 0);
+      out += std::string(indent, ' ');
+      out += std::to_string(y + 1);                          // leading y coordinate
+      bool found_last = false;
+      const int start_x = y < S ? 0 : y - S + 1, end_x = y < S ? S + y : D;
+      for (int x = start_x; x < end_x; ++x) {
+        const int cell = x + y * D;
+        if (found_last) { out += ']'; found_last = false; }
+        else if (cell == last) { out += '['; found_last = true; }
+        else out += ' ';
+        out += G::has(s.st[0], cell) ? 'O' : (G::has(s.st[1], cell) ? '@' : '.');
+      }
+      if (found_last) out += ']';
+      if (y < S - 1) { out += ' '; out += (char)('a' + S + y); }   // trailing x coordinate
       out += '\n';
     }
     return out;

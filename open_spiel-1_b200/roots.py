@@ -17,6 +17,7 @@ ROOT_DEPTHS = {  # cfg2 U{8..20}, cfg3 U{0..40}, cfg4 U{0..60}
     "pentago": (0, 20),
     "othello": (0, 40),
     "y": (0, 80),
+    "havannah": (0, 60),
 }
 
 

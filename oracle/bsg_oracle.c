@@ -38,6 +38,7 @@ int orc_num_distinct_actions(int game, int n) {
     case ORC_PENTAGO: return 36 * 8; /* pentago.h:40-42 */
     case ORC_OTHELLO: return 65;     /* othello.h:128: 64 cells + pass */
     case ORC_Y: return n * n;        /* y.h:174-178: the cut-off corner is never legal */
+    case ORC_HAVANNAH: return (2 * n - 1) * (2 * n - 1);   /* havannah.h:196-200 */
     default: return n * n;
   }
 }
@@ -49,6 +50,7 @@ int orc_max_game_length(int game, int n) {
     case ORC_PENTAGO: return 36; /* pentago.h:109-113 */
     case ORC_OTHELLO: return 64; /* othello.h:142 */
     case ORC_Y: return n * (n + 1) / 2; /* y.h:192-197 */
+    case ORC_HAVANNAH: return (2 * n - 1) * (2 * n - 1) - n * (n - 1); /* havannah.h:212-217 */
     default: return n * n;
   }
 }
@@ -60,6 +62,7 @@ int orc_obs_size(int game, int n) {
     case ORC_PENTAGO: return 3 * 36; /* pentago.h:106-108 */
     case ORC_OTHELLO: return 3 * 64; /* othello.h:139-141 */
     case ORC_Y: return 3 * n * n;    /* y.h:189-191 */
+    case ORC_HAVANNAH: return 3 * (2 * n - 1) * (2 * n - 1); /* havannah.h:209-211 */
     default: return 9 * n * n;
   }
 }
@@ -447,6 +450,118 @@ static int y_apply(orc_state* s, int a) {
   return 0;
 }
 
+/* ---------------------------------------------------------------- havannah (radius S, grid (2S-1)^2) */
+enum { HV_P0 = 0, HV_P1 = 1, HV_NONE = 2, HV_INVALID = 4 };   /* havannah.h:44-50 */
+static int hv_diam(const orc_state* s) { return 2 * s->board_size - 1; }
+/* havannah.h:60-69 */
+static int hv_xy(int x, int y, int size) {
+  int d = 2 * size - 1;
+  return (x >= 0 && y >= 0 && x < d && y < d && (y - x < size) && (x - y < size)) ? x + y * d : -1;
+}
+/* havannah.cc:112-126 */
+static int hv_corner(int x, int y, int size) {
+  int m = size - 1, e = m * 2;
+  if (hv_xy(x, y, size) < 0) return 0;
+  if (x == 0 && y == 0) return 1 << 0;
+  if (x == m && y == 0) return 1 << 1;
+  if (x == e && y == m) return 1 << 2;
+  if (x == e && y == e) return 1 << 3;
+  if (x == m && y == e) return 1 << 4;
+  if (x == 0 && y == m) return 1 << 5;
+  return 0;
+}
+/* havannah.cc:128-143 */
+static int hv_edge(int x, int y, int size) {
+  int m = size - 1, e = m * 2;
+  if (hv_xy(x, y, size) < 0) return 0;
+  if (y == 0 && x != 0 && x != m) return 1 << 0;
+  if (x - y == m && x != m && x != e) return 1 << 1;
+  if (x == e && y != m && y != e) return 1 << 2;
+  if (y == e && x != e && x != m) return 1 << 3;
+  if (y - x == m && x != m && x != 0) return 1 << 4;
+  if (x == 0 && y != m && y != 0) return 1 << 5;
+  return 0;
+}
+/* havannah.cc:61-75: neighbour offsets, clockwise from the upper left */
+static const int kHvNb[6][2] = {{-1, -1}, {0, -1}, {1, 0}, {1, 1}, {0, 1}, {-1, 0}};
+static int hv_neighbour(const orc_state* s, int cell, int dir) {
+  int d = hv_diam(s);
+  return hv_xy(cell % d + kHvNb[dir][0], cell / d + kHvNb[dir][1], s->board_size);
+}
+static int hv_bits(int v) { int n = 0; while (v) { n += v & 1; v >>= 1; } return n; }
+/* havannah.cc:159-179 */
+static void hv_init(orc_state* s) {
+  int d = hv_diam(s);
+  for (int i = 0; i < d * d; ++i) {
+    int x = i % d, y = i / d;
+    s->cells[i] = hv_xy(x, y, s->board_size) >= 0 ? HV_NONE : HV_INVALID;
+    s->parent[i] = (int16_t)i;
+    s->size[i] = 1;
+    s->corner[i] = (uint8_t)hv_corner(x, y, s->board_size);
+    s->edge[i] = (uint8_t)hv_edge(x, y, s->board_size);
+    s->mark[i] = 0;
+  }
+}
+/* havannah.cc:351-362 */
+static int hv_find(orc_state* s, int cell) {
+  int parent = s->parent[cell];
+  if (parent != cell) {
+    do {
+      parent = s->parent[parent];
+    } while (parent != s->parent[parent]);
+    s->parent[cell] = (int16_t)parent;
+  }
+  return parent;
+}
+/* havannah.cc:364-383: returns 1 when the cells were in one group already */
+static int hv_join(orc_state* s, int a, int b) {
+  int la = hv_find(s, a), lb = hv_find(s, b);
+  if (la == lb) return 1;
+  if (s->size[la] < s->size[lb]) { int t = la; la = lb; lb = t; }
+  s->parent[lb] = (int16_t)la;
+  s->size[la] = (int16_t)(s->size[la] + s->size[lb]);
+  s->corner[la] |= s->corner[lb];
+  s->edge[la] |= s->edge[lb];
+  return 0;
+}
+/* havannah.cc:385-399 */
+static int hv_ring_dfs(orc_state* s, int cell, int left, int right) {
+  if (cell < 0) return 0;
+  if (s->cells[cell] != s->cur_player) return 0;
+  if (s->mark[cell]) return 1;
+  s->mark[cell] = 1;
+  int success = 0;
+  for (int i = left; !success && i <= right; ++i) {
+    int dir = (i + 6) % 6;
+    success = hv_ring_dfs(s, hv_neighbour(s, cell, dir), dir - 1, dir + 1);
+  }
+  s->mark[cell] = 0;
+  return success;
+}
+/* havannah.cc:314-349 */
+static int hv_apply(orc_state* s, int a) {
+  int d = hv_diam(s);
+  if (a < 0 || a >= d * d || s->cells[a] != HV_NONE) return -1;
+  s->cells[a] = s->cur_player;
+  s->num_moves += 1;
+  int already = 0, skip = 0;
+  for (int dir = 0; dir < 6; ++dir) {
+    if (skip) { skip = 0; continue; }
+    int m = hv_neighbour(s, a, dir);
+    if (m >= 0 && s->cells[m] == s->cur_player) {
+      already |= hv_join(s, a, m);
+      skip = 1;
+    }
+  }
+  int g = hv_find(s, a);
+  if (hv_bits(s->edge[g]) >= 3 || hv_bits(s->corner[g]) >= 2 || (already && hv_ring_dfs(s, a, 0, 3)))
+    s->outcome = s->cur_player;
+  else if (s->num_moves == orc_max_game_length(ORC_HAVANNAH, s->board_size))
+    s->outcome = 2;
+  s->cur_player = 1 - s->cur_player;
+  return 0;
+}
+
 /* ---------------------------------------------------------------- generic API */
 void orc_init(orc_state* s, int game, int board_size) {
   memset(s, 0, sizeof(*s));
@@ -458,6 +573,12 @@ void orc_init(orc_state* s, int game, int board_size) {
      * passed by a caller that does not care about the size means "the default". */
     s->board_size = (board_size > 0 && board_size != 11) ? board_size : 19;
     y_init(s);
+  }
+  if (game == ORC_HAVANNAH) {
+    /* havannah.h:39: radius 8 by default; the reference's playthrough uses 4 (a hex-style
+     * default of 11 passed by a caller that does not care means "the default") */
+    s->board_size = (board_size > 0 && board_size != 11) ? board_size : 8;
+    hv_init(s);
   }
   if (game == ORC_OTHELLO) {
     /* othello.cc:263-269: white on d4/e5, black on e4/d5; black (player 0) moves first */
@@ -481,6 +602,7 @@ int orc_is_terminal(const orc_state* s) {
     case ORC_PENTAGO: return s->outcome != -1;                      /* pentago.h:62 */
     case ORC_OTHELLO: return s->outcome != -1;                      /* othello.cc:284-286 */
     case ORC_Y: return s->outcome != -1;                            /* y.h:129 */
+    case ORC_HAVANNAH: return s->outcome != -1;                     /* havannah.h:146 */
     default: return s->outcome != -1;                               /* hex.cc:248 */
   }
 }
@@ -509,6 +631,10 @@ int orc_legal_actions(const orc_state* s, int* out) {
       for (int c = 0; c < s->board_size * s->board_size; ++c)
         if (s->cells[c] == Y_NONE) out[n++] = c;
       return n;
+    case ORC_HAVANNAH: /* havannah.cc:182-194 */
+      for (int c = 0; c < hv_diam(s) * hv_diam(s); ++c)
+        if (s->cells[c] == HV_NONE) out[n++] = c;
+      return n;
     default: /* hex.cc:186-196 */
       for (int c = 0; c < s->board_size * s->board_size; ++c)
         if (s->cells[c] == HX_EMPTY) out[n++] = c;
@@ -525,6 +651,7 @@ int orc_apply(orc_state* s, int a) {
     case ORC_PENTAGO: return pg_apply(s, a);
     case ORC_OTHELLO: return ot_apply(s, a);
     case ORC_Y: return y_apply(s, a);
+    case ORC_HAVANNAH: return hv_apply(s, a);
     default: return hex_apply(s, a);
   }
 }
@@ -581,6 +708,17 @@ void orc_observation(const orc_state* s, int player, uint8_t* out) {
         int v = s->cells[c];
         if (v == Y_INVALID) continue;
         plane = v == Y_NONE ? 2 : (v == player ? 0 : 1);
+        out[plane * ncell + c] = 1;
+      }
+      return;
+    case ORC_HAVANNAH: /* havannah.cc:284-312: plane 0 the observer's stones, 1 the other's, 2
+                        * empty; the cut-off corners stay zero in every plane */
+      ncell = hv_diam(s) * hv_diam(s);
+      memset(out, 0, 3 * ncell);
+      for (int c = 0; c < ncell; ++c) {
+        int v = s->cells[c];
+        if (v == HV_INVALID) continue;
+        plane = v == HV_NONE ? 2 : (v == player ? 0 : 1);
         out[plane * ncell + c] = 1;
       }
       return;

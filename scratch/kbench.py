@@ -5,7 +5,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import open_spiel_1_b200 as bsg
 from open_spiel_1_b200.roots import make_roots, ROOT_DEPTHS
-DEF = {"connect_four": 1 << 24, "tic_tac_toe": 1 << 24, "breakthrough": 1 << 22, "hex": 1 << 20,
+DEF = {"havannah": 1 << 20, "connect_four": 1 << 24, "tic_tac_toe": 1 << 24, "breakthrough": 1 << 22, "hex": 1 << 20,
        "pentago": 1 << 22, "othello": 1 << 21, "y": 1 << 21}
 out = {}
 for spec in sys.argv[1:] or ["connect_four"]:
@@ -13,7 +13,7 @@ for spec in sys.argv[1:] or ["connect_four"]:
   n = int(n) if n else DEF[g]
   eng = bsg.Engine(g, 0)
   dmin, dmax = ROOT_DEPTHS[g]
-  st, _ = make_roots(eng, n, dmin, dmax, seed=20240611 + (2 if g == "connect_four" else 4))
+  st, _ = make_roots(eng, n, dmin, dmax, seed=20240611 + (2 if g == "connect_four" else 4))  # bench.py seeds
   dev = eng.torch_device
   ret0 = torch.zeros(n, dtype=torch.int8, device=dev)
   length = torch.zeros(n, dtype=torch.uint8, device=dev)

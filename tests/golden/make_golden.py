@@ -3,7 +3,7 @@
 
 Sources (all under /root/reference, read in place, never copied verbatim):
   * open_spiel/integration_tests/playthroughs/{tic_tac_toe,connect_four,breakthrough,
-    hex(board_size=5),pentago,othello,y(board_size=9)}.txt — the reference's own golden playthroughs; per state we keep the
+    hex(board_size=5),pentago,othello,y(board_size=9),havannah(board_size=4)}.txt — the reference's own golden playthroughs; per state we keep the
     action history, LegalActions(), CurrentPlayer(), IsTerminal(), Returns() and both
     players' ObservationTensor planes (as flat 0/1 lists in CHW order).
   * open_spiel/games/connect_four_test.cc:33-80 — FastLoss / DeserializeDraw known answers.
@@ -34,6 +34,7 @@ GAMES = {
     "pentago": ("pentago.txt", (3, 6, 6)),
     "othello": ("othello.txt", (3, 8, 8)),
     "y9": ("y(board_size=9).txt", (3, 9, 9)),
+    "havannah4": ("havannah(board_size=4).txt", (3, 7, 7)),
 }
 
 
