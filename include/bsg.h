@@ -190,9 +190,11 @@ typedef struct bsg_playout_io {
    * the win.  What RandomRolloutEvaluator::Evaluate (mcts.cc:42-71) needs is only the returns.
    * Excludes max_steps / step_limit / r_table / actions / final_states / state_log. */
   int32_t value_only;
-  /* Alternative to state_log_off: a fixed stride — the state before move t of playout p goes to
-   * slot p * state_log_stride + t (state_log_off must then be NULL; moves t >= stride are not
-   * logged).  One pass, no earlier launch needed; bsg_trajectory_* compacts the log. */
+  /* Alternative to state_log_off: a fixed number of moves per playout — the state before move t
+   * of playout p goes to slot t * n_playouts + p (move-major: lanes at the same move number write
+   * adjacent elements) of a log with capacity n_playouts * state_log_stride; state_log_off must
+   * then be NULL and moves t >= state_log_stride are not logged.  One pass, no earlier launch
+   * needed; bsg_trajectory_* compacts the log. */
   int64_t state_log_stride;
 } bsg_playout_io;
 

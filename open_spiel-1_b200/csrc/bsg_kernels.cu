@@ -108,10 +108,14 @@ template <class G> struct fillable<G, std::enable_if_t<G::kFillable>> : std::tru
 // kFill: value-only launch of a fillable game — the lanes play plain stones until the board is
 // full (no labels, no flood, no waiting) and park the board for fill_resolve_kernel, which
 // reads the winner off it and publishes ret0 / per-root sums / totals[2].
-template <class G, bool kFull, bool kBase, bool kFill = false>
+// kLog: a lean launch that also logs the packed state before every move (and the action) at a
+// fixed stride per playout (bsg_playout_io.state_log_stride) — the one-pass trajectory path;
+// everything else the kFull variant offers (step limits, r_table, final states) stays there.
+template <class G, bool kFull, bool kBase, bool kFill = false, bool kLog = false>
 __global__ void __launch_bounds__(kThreads, kFull ? 1 : (kFill ? 4 : min_blocks<G>::value))
 playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab) {
   static_assert(!kFill || !kFull, "value-only playouts are a lean launch");
+  static_assert(!kLog || (!kFull && !kBase && !kFill), "the logging variant is a plain lean launch");
   constexpr bool kAsync = G::kAsync && !kFill;
   __shared__ __align__(16) typename G::Tables tab;
   {
@@ -333,13 +337,17 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
           if (a.io.state_log) {
             if (a.io.state_log_off) G::store(s, a.io.state_log, a.io.state_log_cap, a.io.state_log_off[lid] + t);
             else if ((int64_t)t < a.io.state_log_stride)
-              G::store(s, a.io.state_log, a.io.state_log_cap, (int64_t)lid * a.io.state_log_stride + t);
+              G::store(s, a.io.state_log, a.io.state_log_cap, (int64_t)t * a.n_playouts + lid);
           }
         }
       }
       int action = 0;
       u32 nlegal = 1;
       u32 made = 1;   // kLazyEnd: 0 in the iteration that only finds the game over
+      if constexpr (kLog) {
+        if (can && (int64_t)t < a.io.state_log_stride)
+          G::store(s, a.io.state_log, a.io.state_log_cap, (int64_t)t * a.n_playouts + lid);
+      }
       if constexpr (kFill) {
         nlegal = fill_ops<G, kFill>::step(s, r, tab, action);
       } else if constexpr (G::kLazyEnd && !kFull) {
@@ -367,12 +375,20 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
           }
         }
       } else if constexpr (kLazyDraw) {
+        if constexpr (kLog) {
+          if (live && a.io.actions && t < (u32)a.io.actions_stride)
+            a.io.actions[(size_t)lid * a.io.actions_stride + t] = (int16_t)action;
+        }
         // only a win ends the playout inside the group; the draw is found at the group's end
         t += live;
         live = G::won(s) ? 0u : live;
       } else {
         // lean bookkeeping: t counts the moves of the live playout and freezes when it ends;
         // fin_win was cleared at the claim and can only be set by the (single) ending move
+        if constexpr (kLog) {
+          if (can && made && a.io.actions && t < (u32)a.io.actions_stride)
+            a.io.actions[(size_t)lid * a.io.actions_stride + t] = (int16_t)action;
+        }
         const u32 term = (kFill ? fill_ops<G, kFill>::done(s) : G::terminal(s)) ? 1u : 0u;
         const u32 won = (!kFill && G::won(s)) ? 1u : 0u;
         fin_win |= can & won;
@@ -901,7 +917,7 @@ __global__ void traj_compact_kernel(const void* strided, int64_t n, int64_t stri
     }
     const int64_t t = r - off[lo];
     typename G::State s;
-    G::load(s, strided, n * stride, lo * stride + t);
+    G::load(s, strided, n * stride, t * n + lo);      // move-major log: slot = t * n + playout
     G::store(s, out_states, total, r);
     if (out_actions) out_actions[r] = acts ? (int64_t)acts[lo * acts_stride + t] : -1;
     if (out_playout) out_playout[r] = lo;
@@ -975,7 +991,7 @@ const NcclApi& nccl_api() {
   return api;
 }
 
-template <class G, bool kFull, bool kBase = false, bool kFill = false>
+template <class G, bool kFull, bool kBase = false, bool kFill = false, bool kLog = false>
 int launch_playouts(bsg_engine* e, const PlayoutArgs& a, cudaStream_t st) {
   // function attributes belong to the current device: one cached answer per device, set under a
   // lock (RootParallelMCTS walks several engines of one process from a thread pool)
@@ -988,9 +1004,9 @@ int launch_playouts(bsg_engine* e, const PlayoutArgs& a, cudaStream_t st) {
     if (slot == 0) {
       int b = 0;
       // all of the L1/shared array as shared memory: the tables of every resident CTA must fit
-      BSG_CUDA(e, cudaFuncSetAttribute(playout_kernel<G, kFull, kBase, kFill>, cudaFuncAttributePreferredSharedMemoryCarveout,
+      BSG_CUDA(e, cudaFuncSetAttribute(playout_kernel<G, kFull, kBase, kFill, kLog>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                        cudaSharedmemCarveoutMaxShared));
-      BSG_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, playout_kernel<G, kFull, kBase, kFill>, kThreads, 0));
+      BSG_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, playout_kernel<G, kFull, kBase, kFill, kLog>, kThreads, 0));
       slot = b > 0 ? b : 1;
     }
     blocks_per_sm = slot;
@@ -1015,7 +1031,7 @@ int launch_playouts(bsg_engine* e, const PlayoutArgs& a, cudaStream_t st) {
     if (rc != BSG_OK) return rc;
     b.fill_boards = (uint32_t*)e->d_fill + (size_t)a.fill_base * G::kFillWords;
   }
-  playout_kernel<G, kFull, kBase, kFill><<<grid, kThreads, 0, st>>>(b, (const typename G::Tables*)e->tables_dev);
+  playout_kernel<G, kFull, kBase, kFill, kLog><<<grid, kThreads, 0, st>>>(b, (const typename G::Tables*)e->tables_dev);
   BSG_CUDA(e, cudaGetLastError());
   if constexpr (kFill) {
     int rgrid = (int)(need < (int64_t)e->sm_count * 8 ? need : (int64_t)e->sm_count * 8);
@@ -1043,6 +1059,10 @@ struct PlayoutOp {
     const bsg_playout_io& io = a.io;
     bool full = io.max_steps > 0 || io.step_limit || io.r_table || io.actions || io.final_states || io.state_log;
     if (io.value_only) return launch_value_only<G>(e, a, st, full);
+    // the one-pass trajectory launch: a strided state log (+ actions), nothing else of kFull
+    const bool log_only = io.state_log && !io.state_log_off && io.state_log_stride > 0 && !io.root_playout_base &&
+                          !(io.max_steps > 0 || io.step_limit || io.r_table || io.final_states);
+    if (log_only) return launch_playouts<G, false, false, false, true>(e, a, st);
     if (io.root_playout_base)
       return full ? launch_playouts<G, true, true>(e, a, st) : launch_playouts<G, false, true>(e, a, st);
     return full ? launch_playouts<G, true>(e, a, st) : launch_playouts<G, false>(e, a, st);
