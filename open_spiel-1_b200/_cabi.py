@@ -104,6 +104,10 @@ def _load():
       "bsg_playouts_host": (ctypes.c_int, [vp, vp, i64, i32, u64, u64, vp, vp, vp]),
       "bsg_observations_host": (ctypes.c_int, [vp, vp, i64, vp, vp, vp]),
       "bsg_playouts_host_results": (ctypes.c_int, [vp, vp, i64, i32, u64, u64, vp, vp, vp]),
+      "bsg_compact_state_bytes": (ctypes.c_int, [ctypes.c_int]),
+      "bsg_compact_roots": (ctypes.c_int, [ctypes.c_int, vp, i64, vp]),
+      "bsg_expand_roots": (ctypes.c_int, [ctypes.c_int, vp, i64, vp]),
+      "bsg_playouts_host_compact": (ctypes.c_int, [vp, vp, i64, i32, u64, u64, vp, vp, vp]),
       "bsg_int_peak": (ctypes.c_int, [vp, ctypes.c_int, ctypes.c_int, vp]),
       "bsg_noalloc_max_playouts": (ctypes.c_int, [ctypes.c_int]),
       "bsg_playouts_value_only_noalloc": (ctypes.c_int, [vp, vp, i64, i32, u64, u64, vp, vp, vp, vp, vp, vp]),

@@ -246,6 +246,36 @@ struct ConnectFour {
     s.left = top >> 26;
     s.win = (top >> 25) & 1u;
   }
+  // Compact root format for host -> device transfers (bsg_playouts_host_compact): the low SEVEN
+  // bytes of the packed u64 (bits 0..54: the mover's stones | one marker per column), 7 bytes
+  // per root back to back.  The meta byte is derived: empty cells from the occupancy, "the last
+  // move made four in a row" from the line test on the side that moved last.  The copy of the
+  // roots over PCIe is the end-to-end bound of the path, so an eighth of it is an eighth of the time.
+  static constexpr int kCompactBytes = 7;
+  BSG_HD static void load_compact(State& s, const void* base, int64_t i) {
+    const int64_t off = 7 * i;
+    const u32* p = (const u32*)base + (off >> 2);          // (the buffer has >= 8 bytes of slack behind it)
+    const int sh = (int)(off & 3) * 8;
+    const u32 w0 = p[0], w1 = p[1], w2 = p[2];
+    const u32 lo = sh ? fshr(w0, w1, sh) : w0;
+    const u32 hi = (sh ? fshr(w1, w2, sh) : w1) & 0x00FFFFFFu;
+    const u64 key = (u64)lo | ((u64)hi << 32);
+    u64 sm = key;
+    sm |= sm >> 8;
+    sm |= sm >> 16;
+    sm |= sm >> 32;
+    const u64 occ = sm >> 8;
+    s.cur = key & occ;
+    s.opp = occ & ~key;
+    s.left = 42u - (u32)popc64(occ);
+    s.win = has_line(s.opp) ? 1u : 0u;
+  }
+  BSG_HD static void store_compact(const State& s, void* base, int64_t i) {
+    u64 tmp = 0;
+    store(s, &tmp, 1, 0);
+    unsigned char* b = (unsigned char*)base + 7 * i;
+    for (int k = 0; k < 7; ++k) b[k] = (unsigned char)(tmp >> (8 * k));
+  }
   BSG_HD static void store(const State& s, void* base, int64_t n, int64_t i) {
     (void)n;
     u64 occ = s.cur | s.opp, markers = 0;

@@ -60,6 +60,7 @@ struct PlayoutArgs {
   bsg_playout_io io;
   uint32_t* work_counter;  // zeroed before the launch; warps draw chunks of playouts from it
   uint32_t out_flags;  // kOut* bits: which optional per-playout outputs of io are present
+  uint32_t compact;    // != 0: `roots` is in the game's compact format (compact_bytes<G> per root)
   uint32_t* fill_boards;  // value-only launches: kFillWords words per playout for fill_resolve_kernel
   uint64_t fill_base;     // host path: this launch parks its boards from playout slot fill_base on
 };
@@ -86,6 +87,18 @@ template <class G, class = void> struct inert_when_full : std::false_type {};
 template <class G> struct inert_when_full<G, std::enable_if_t<G::kInertWhenFull>> : std::true_type {};
 template <class G, bool kOn> struct moves_left_of { BSG_HD static u32 get(const typename G::State&) { return 0xFFFFFFFFu; } };
 template <class G> struct moves_left_of<G, true> { BSG_HD static u32 get(const typename G::State& s) { return G::moves_left(s); } };
+
+// Games with a compact root format for host -> device transfers (G::kCompactBytes, G::load_compact).
+template <class G, class = void> struct compact_bytes : std::integral_constant<int, 0> {};
+template <class G> struct compact_bytes<G, std::enable_if_t<(G::kCompactBytes > 0)>> : std::integral_constant<int, G::kCompactBytes> {};
+template <class G, bool kOn> struct compact_ops {
+  BSG_HD static void load(typename G::State&, const void*, int64_t) {}
+  BSG_HD static void store(const typename G::State&, void*, int64_t) {}
+};
+template <class G> struct compact_ops<G, true> {
+  BSG_HD static void load(typename G::State& s, const void* b, int64_t i) { G::load_compact(s, b, i); }
+  BSG_HD static void store(const typename G::State& s, void* b, int64_t i) { G::store_compact(s, b, i); }
+};
 
 // Indirection so that the kernel body only names the fill functions of a game that has them.
 template <class G, bool kOn> struct fill_words : std::integral_constant<int, 4> {};
@@ -142,7 +155,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
                           G::kStateBytes <= 16 && (kChunkPlayouts * G::kStateBytes) % 16 == 0;
   constexpr int kStageBytes = kStage ? kChunkPlayouts * G::kStateBytes : 16;
   __shared__ __align__(16) unsigned char root_sm[kStage ? kThreads / 32 : 1][2][kStageBytes];
-  const bool stage = kStage && a.rollouts == 1u;   // launch-uniform
+  const bool stage = kStage && a.rollouts == 1u && !a.compact;   // launch-uniform
   u32 par = 0;                                      // buffer of the chunk (begin, count)
 
   typename G::State s;
@@ -233,6 +246,8 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         lid = base + idx;
         u32 root = a.rollouts == 1 ? lid : lid / a.rollouts;
         if (kStage && stage) G::load(s, root_sm[threadIdx.x >> 5][buf], kChunkPlayouts, idx);
+        else if ((compact_bytes<G>::value > 0) && a.compact)
+          compact_ops<G, (compact_bytes<G>::value > 0)>::load(s, a.roots, a.root0 + root);
         else G::load(s, a.roots, a.n_roots, a.root0 + root);
         bool skip = false;
         if (kBase) {
@@ -1525,6 +1540,137 @@ int bsg_playouts_host_results(bsg_engine* e, const void* roots_host, int64_t n_r
     PlayoutArgs a;
     memset(&a, 0, sizeof(a));
     a.roots = e->d_roots; a.n_roots = n_roots; a.root0 = lo;
+    a.n_playouts = (uint32_t)p_n; a.rollouts = (uint32_t)rollouts;
+    a.first_playout = first_playout + (uint64_t)p_lo;
+    a.keys = keys;
+    a.io.totals = e->d_totals;
+    a.io.ret0 = d_ret ? d_ret + p_lo : nullptr;
+    a.io.length = d_len ? d_len + p_lo : nullptr;
+    if ((rc = dispatch_device_game(e->game, PlayoutOp{e, a, st})) != BSG_OK) return rc;
+    if (d_ret) BSG_CUDA(e, cudaMemcpyAsync(h_ret + p_lo, d_ret + p_lo, (size_t)p_n, cudaMemcpyDeviceToHost, st));
+    if (d_len) BSG_CUDA(e, cudaMemcpyAsync(h_len + p_lo, d_len + p_lo, (size_t)p_n, cudaMemcpyDeviceToHost, st));
+  }
+  BSG_CUDA(e, cudaEventRecord(e->ev_b, sb));
+  BSG_CUDA(e, cudaStreamWaitEvent(sa, e->ev_b, 0));
+  uint64_t* h_tot = (uint64_t*)h_res;
+  BSG_CUDA(e, cudaMemcpyAsync(h_tot, e->d_totals, 32, cudaMemcpyDeviceToHost, sa));
+  BSG_CUDA(e, cudaStreamSynchronize(sa));
+  for (int i = 0; i < 4; ++i) totals_out[i] = (int64_t)h_tot[i];
+  if (!pin_out) {
+    if (ret0_host) memcpy(ret0_host, h_ret, (size_t)n_play);
+    if (length_host) memcpy(length_host, h_len, (size_t)n_play);
+  }
+  if (totals_out[3] != 0) return fail(e, BSG_ERR_STUCK_LANE, "non-terminal state without legal actions");
+  return BSG_OK;
+}
+
+// ---- compact roots (connect_four: 7 bytes per root)
+}  // extern "C"
+namespace {
+struct CompactBytesOp {
+  template <class G> int operator()() const { return compact_bytes<G>::value > 0 ? compact_bytes<G>::value : G::kStateBytes; }
+};
+struct CompactConvertOp {
+  const void* in; void* out; int64_t n; int to_compact;
+  template <class G> int operator()() const {
+    if constexpr (compact_bytes<G>::value > 0) {
+      // expanding reads three words per root: work on a padded copy of the compact buffer
+      std::vector<unsigned char> padded;
+      const void* src = in;
+      if (!to_compact) {
+        padded.assign((size_t)n * compact_bytes<G>::value + 16, 0);
+        memcpy(padded.data(), in, (size_t)n * compact_bytes<G>::value);
+        src = padded.data();
+      }
+      for (int64_t i = 0; i < n; ++i) {
+        typename G::State s;
+        if (to_compact) { G::load(s, src, n, i); compact_ops<G, true>::store(s, out, i); }
+        else { compact_ops<G, true>::load(s, src, i); G::store(s, out, n, i); }
+      }
+      return BSG_OK;
+    } else {
+      memcpy(out, in, (size_t)n * G::kStateBytes);   // no compact format: the packed one
+      return BSG_OK;
+    }
+  }
+};
+}  // namespace
+extern "C" {
+int bsg_compact_state_bytes(int game) { return dispatch_game(game, CompactBytesOp{}); }
+int bsg_compact_roots(int game, const void* packed_host, int64_t n, void* compact_out) {
+  if (!packed_host || !compact_out || n < 0) return BSG_ERR_BAD_ARG;
+  return dispatch_game(game, CompactConvertOp{packed_host, compact_out, n, 1});
+}
+int bsg_expand_roots(int game, const void* compact_host, int64_t n, void* packed_out) {
+  if (!compact_host || !packed_out || n < 0) return BSG_ERR_BAD_ARG;
+  return dispatch_game(game, CompactConvertOp{compact_host, packed_out, n, 0});
+}
+
+// bsg_playouts_host_results for roots in the compact format: the same two-stream chunking, an
+// eighth less to copy for connect_four.  ret0_host / length_host may both be NULL (totals only).
+int bsg_playouts_host_compact(bsg_engine* e, const void* roots_compact_host, int64_t n_roots, int32_t rollouts,
+                              uint64_t seed, uint64_t first_playout, int64_t totals_out[4],
+                              int8_t* ret0_host, uint8_t* length_host) {
+  if (!e) return BSG_ERR_BAD_ARG;
+  if (!roots_compact_host || n_roots < 1 || rollouts < 1 || !totals_out)
+    return fail(e, BSG_ERR_BAD_ARG, "bad host playout arguments");
+  if (e->value_only) return fail(e, BSG_ERR_BAD_ARG, "compact roots run the exact kernels (value_only is set)");
+  const int cb = bsg_compact_state_bytes(e->game);
+  if (cb == bsg_state_bytes(e->game))   // no compact format for this game: the packed path
+    return (ret0_host || length_host)
+               ? bsg_playouts_host_results(e, roots_compact_host, n_roots, rollouts, seed, first_playout, totals_out, ret0_host, length_host)
+               : bsg_playouts_host(e, roots_compact_host, n_roots, rollouts, seed, first_playout, totals_out, nullptr, nullptr);
+  const int64_t n_play = n_roots * (int64_t)rollouts;
+  if (n_play >= ((int64_t)1 << 32) - (1 << 24))
+    return fail(e, BSG_ERR_BAD_ARG, "more than 2^32-2^24 playouts in one call");
+  BSG_CUDA(e, cudaSetDevice(e->device));
+  const size_t in_bytes = (size_t)n_roots * (size_t)cb;
+  const size_t out_bytes = (size_t)n_play * ((ret0_host ? 1 : 0) + (length_host ? 1 : 0));
+  int rc;
+  if ((rc = ensure(e, &e->d_roots, &e->d_roots_bytes, in_bytes + 16, false)) != BSG_OK) return rc;
+  if ((rc = ensure(e, &e->d_out, &e->d_out_bytes, out_bytes + 64, false)) != BSG_OK) return rc;
+  auto is_pinned = [](const void* p) {
+    cudaPointerAttributes attr;
+    bool pinned = cudaPointerGetAttributes(&attr, p) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    return pinned;
+  };
+  const bool pin_in = is_pinned(roots_compact_host);
+  const bool pin_out = (!ret0_host || is_pinned(ret0_host)) && (!length_host || is_pinned(length_host));
+  const size_t pin_need = 128 + (pin_in ? 0 : in_bytes + 64) + (pin_out ? 0 : out_bytes + 64);
+  if ((rc = ensure(e, &e->h_pinned, &e->h_pinned_bytes, pin_need, true)) != BSG_OK) return rc;
+  char* h_res = (char*)e->h_pinned;
+  char* h_in = h_res + 128;
+  char* h_out = h_in + (pin_in ? 0 : ((in_bytes + 63) & ~(size_t)63));
+  const char* src = (const char*)roots_compact_host;
+  if (!pin_in) { memcpy(h_in, roots_compact_host, in_bytes); src = h_in; }
+  int8_t* h_ret = ret0_host;
+  uint8_t* h_len = length_host;
+  if (!pin_out) {
+    h_ret = ret0_host ? (int8_t*)h_out : nullptr;
+    h_len = length_host ? (uint8_t*)h_out + (ret0_host ? n_play : 0) : nullptr;
+  }
+  int8_t* d_ret = ret0_host ? (int8_t*)e->d_out : nullptr;
+  uint8_t* d_len = length_host ? (uint8_t*)e->d_out + (ret0_host ? n_play : 0) : nullptr;
+  cudaStream_t sa = e->own_stream, sb = e->aux_stream;
+  BSG_CUDA(e, cudaMemsetAsync(e->d_totals, 0, 4 * sizeof(uint64_t), sa));
+  BSG_CUDA(e, cudaEventRecord(e->ev_a, sa));
+  BSG_CUDA(e, cudaStreamWaitEvent(sb, e->ev_a, 0));
+  int64_t n_chunks = (int64_t)(in_bytes >> 21);
+  n_chunks = n_chunks < 1 ? 1 : (n_chunks > 16 ? 16 : n_chunks);
+  PhiloxKeys keys;
+  philox_schedule(seed, keys);
+  for (int64_t c = 0; c < n_chunks; ++c) {
+    // chunk boundaries at multiples of 4 roots: 4 * 7 bytes keeps every chunk's first byte word-aligned
+    int64_t lo = (n_roots * c / n_chunks) & ~(int64_t)3, hi = c + 1 == n_chunks ? n_roots : ((n_roots * (c + 1) / n_chunks) & ~(int64_t)3);
+    if (hi <= lo) continue;
+    cudaStream_t st = (c & 1) ? sb : sa;
+    BSG_CUDA(e, cudaMemcpyAsync((char*)e->d_roots + (size_t)lo * cb, src + (size_t)lo * cb, (size_t)(hi - lo) * cb,
+                                cudaMemcpyHostToDevice, st));
+    const int64_t p_lo = lo * rollouts, p_n = (hi - lo) * rollouts;
+    PlayoutArgs a;
+    memset(&a, 0, sizeof(a));
+    a.roots = e->d_roots; a.n_roots = n_roots; a.root0 = lo; a.compact = 1;
     a.n_playouts = (uint32_t)p_n; a.rollouts = (uint32_t)rollouts;
     a.first_playout = first_playout + (uint64_t)p_lo;
     a.keys = keys;

@@ -363,6 +363,38 @@ class Engine:
     self.launches += 1
     return totals, ret0, length
 
+  def compact_roots(self, packed, n_roots):
+    """Packed roots -> the game's compact transfer format (connect_four: 7 bytes per root)."""
+    packed = np.ascontiguousarray(packed)
+    out = np.zeros(int(n_roots) * C.check(C.lib.bsg_compact_state_bytes(self.gid)), np.uint8)
+    C.check(C.lib.bsg_compact_roots(self.gid, packed.ctypes.data, int(n_roots), out.ctypes.data))
+    return out
+
+  def expand_roots(self, compact, n_roots):
+    """The inverse of compact_roots, through the decode the kernel runs."""
+    compact = np.ascontiguousarray(compact)
+    out = np.zeros(int(n_roots) * self.state_bytes, np.uint8)
+    C.check(C.lib.bsg_expand_roots(self.gid, compact.ctypes.data, int(n_roots), out.ctypes.data))
+    return out
+
+  def playouts_host_compact(self, compact, n_roots, rollouts=1, seed=0, first_playout=0, ret0=None,
+                            length=None, want_results=False):
+    """bsg_playouts_host_compact: compact numpy roots in; totals (and, with want_results or
+    given arrays, the per-playout int8 return / uint8 move count) out."""
+    compact = np.ascontiguousarray(compact)
+    n = int(n_roots) * int(rollouts)
+    totals = np.zeros(4, np.int64)
+    if want_results and ret0 is None:
+      ret0 = np.empty(n, np.int8)
+    if want_results and length is None:
+      length = np.empty(n, np.uint8)
+    C.check(C.lib.bsg_playouts_host_compact(self._h, compact.ctypes.data, int(n_roots), int(rollouts),
+                                            int(seed) & (2**64 - 1), int(first_playout), totals.ctypes.data,
+                                            None if ret0 is None else ret0.ctypes.data,
+                                            None if length is None else length.ctypes.data), self._h)
+    self.launches += 1
+    return totals, ret0, length
+
   def observations_host(self, packed, n, players=None, want_mask=False):
     packed = np.ascontiguousarray(packed)
     obs = np.empty((n,) + tuple(self.obs_shape), np.float32)

@@ -367,6 +367,50 @@ def test_host_results_entry_point_equals_device_path(game, n, torch):
   eng.close()
 
 
+@pytest.mark.parametrize("n,R", [(900001, 1), (5, 3), (70000, 2)])
+def test_compact_root_entry_point_equals_device_path(n, R, torch):
+  """bsg_playouts_host_compact: connect_four roots as 7 bytes each — totals and per-playout
+  results equal the device launch over the packed roots, terminal roots included, for pageable
+  and page-locked buffers; a game without a compact format takes its packed roots."""
+  import open_spiel_1_b200 as bsg
+  from open_spiel_1_b200.roots import make_roots, ROOT_DEPTHS
+  eng = _engine("connect_four")
+  dev = eng.torch_device
+  states, _ = make_roots(eng, n, 0, 42, seed=81)            # depth 0..42: long roots end by themselves
+  oracle = Oracle()
+  host = states.cpu().numpy().copy()
+  for i in range(min(n, 4)):                                 # and a few finished games for certain
+    a, _, _ = oracle.replay("connect_four", [], seed=3, playout=i)
+    host[8 * i: 8 * i + 8] = bsg.pack_histories("connect_four", [a])
+  states = eng.to_device(host)
+  ret0 = torch.zeros(n * R, dtype=torch.int8, device=dev)
+  length = torch.zeros(n * R, dtype=torch.uint8, device=dev)
+  totals = torch.zeros(4, dtype=torch.int64, device=dev)
+  eng.playouts(states, n, R, seed=6, first_playout=55, ret0=ret0, length=length, totals=totals)
+  torch.cuda.synchronize()
+  comp = eng.compact_roots(host, n)
+  assert comp.nbytes == 7 * n and np.array_equal(eng.expand_roots(comp, n), host)
+  t, r, l = eng.playouts_host_compact(comp, n, R, seed=6, first_playout=55, want_results=True)
+  assert np.array_equal(t, totals.cpu().numpy())
+  assert np.array_equal(r, ret0.cpu().numpy()) and np.array_equal(l, length.cpu().numpy())
+  t2, _, _ = eng.playouts_host_compact(comp, n, R, seed=6, first_playout=55)       # totals only
+  assert np.array_equal(t2, t)
+  pin = torch.empty(comp.nbytes, dtype=torch.uint8, pin_memory=True)
+  pin.numpy()[:] = comp
+  pr = torch.zeros(n * R, dtype=torch.int8, pin_memory=True)
+  pl = torch.zeros(n * R, dtype=torch.uint8, pin_memory=True)
+  t3, _, _ = eng.playouts_host_compact(pin.numpy(), n, R, seed=6, first_playout=55, ret0=pr.numpy(), length=pl.numpy())
+  assert np.array_equal(t3, t) and np.array_equal(pr.numpy(), r) and np.array_equal(pl.numpy(), l)
+  eng.close()
+  e2 = _engine("hex")
+  st, _ = make_roots(e2, 1000, 0, 60, seed=2)
+  hh = st.cpu().numpy()
+  want, _, _ = e2.playouts_host(hh, 1000, 2, seed=4)
+  got, _, _ = e2.playouts_host_compact(e2.compact_roots(hh, 1000), 1000, 2, seed=4)
+  assert np.array_equal(want, got)
+  e2.close()
+
+
 @pytest.mark.parametrize("game", GAMES)
 def test_small_host_calls_equal_device_path(game, torch):
   """bsg_playouts_host below 64 KB of roots takes the lean path (one stream, one memset for

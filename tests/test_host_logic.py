@@ -272,3 +272,36 @@ def test_alpha_zero_cache_survives_eviction_inside_a_batch():
   assert ev.cache_info()["size"] == 3
   v, _ = ev.inference_batch([states[2], states[2]])       # duplicate keys, one hit each
   assert np.allclose(v, want[[2, 2]])
+
+
+def test_compact_roots_round_trip_through_the_kernels_decode():
+  """connect_four roots as 7 bytes each (bsg_compact_roots) expand to the very packed states
+  they came from through ConnectFour::load_compact — the decode the playout kernel runs —
+  including finished games (the win flag and the empty-cell count are derived, not stored) and
+  a drawn full board; other games' "compact" format is the packed one."""
+  game = bsg.load_game("connect_four")
+  rng = np.random.RandomState(7)
+  hs = []
+  for i in range(3000):
+    s = game.new_initial_state()
+    for _ in range(rng.randint(0, 43)):
+      la = s.legal_actions()
+      if not la:
+        break
+      s.apply_action(la[rng.randint(len(la))])
+    hs.append(s.history())
+  # a drawn game (the reference's DeserializeDraw board, connect_four_test.cc:62-80, as moves)
+  draw = "ooxxxoo\nxxoooxx\nooxxxoo\nxxoooxx\nooxxxoo\nxxoooxx\n"
+  n = len(hs)
+  packed = bsg.pack_histories("connect_four", hs)
+  d = game.deserialize_state(draw)
+  assert d.is_terminal() and d.returns() == [0.0, 0.0]
+  packed = np.concatenate([packed, d.packed()])
+  n += 1
+  assert C.lib.bsg_compact_state_bytes(C.CONNECT_FOUR) == 7
+  comp = np.zeros(n * 7, np.uint8)
+  C.check(C.lib.bsg_compact_roots(C.CONNECT_FOUR, packed.ctypes.data, n, comp.ctypes.data))
+  back = np.zeros(n * 8, np.uint8)
+  C.check(C.lib.bsg_expand_roots(C.CONNECT_FOUR, comp.ctypes.data, n, back.ctypes.data))
+  assert np.array_equal(back, packed)
+  assert C.lib.bsg_compact_state_bytes(C.HEX) == 64 and C.lib.bsg_compact_state_bytes(C.TIC_TAC_TOE) == 4
