@@ -830,13 +830,17 @@ __global__ void __launch_bounds__(kForestWarpThreads)
 forest_descend_kernel(ForestView F, const typename G::Tables* __restrict__ tab) {
   const int v = (blockIdx.x * kForestWarpThreads + threadIdx.x) >> 5;
   if (v >= F.n_trees) return;           // whole warps leave
-  if ((threadIdx.x & 31) == 0 && F.sims_left[v] > 0) atomicAdd(F.active, 1u);
   ForestTree<G>::descend_warp(F, v, *tab);
 }
 template <class G>
 __global__ void __launch_bounds__(kForestWarpThreads) forest_finish_kernel(ForestView F) {
   const int v = (blockIdx.x * kForestWarpThreads + threadIdx.x) >> 5;
-  if (v < F.n_trees) ForestTree<G>::finish_round_warp(F, v);
+  if (v >= F.n_trees) return;
+  ForestTree<G>::finish_round_warp(F, v);
+  __syncwarp();
+  // trees that still have simulations to run after this round (the host reads the counter
+  // after the last enqueued round of a search step)
+  if ((threadIdx.x & 31) == 0 && F.sims_left[v] > 0) atomicAdd(F.active, 1u);
 }
 template <class G>
 __global__ void forest_expand_root_kernel(ForestView F) {
@@ -1966,34 +1970,31 @@ struct ForestSearchOp {
     // A tree with k simulations left needs ceil(k / batch) rounds unless a solved terminal leaf
     // cut one of its rounds short, so that many rounds are enqueued back to back with no host
     // synchronisation (a tree that is done idles through them: its slots are skipped by the
-    // playout kernel); after them the loop below asks once per round whether any tree is still
-    // searching — normally the first answer is "none".
+    // playout kernel); the last of them — and every round after it — has the backup kernel count
+    // the trees that still have simulations left: normally the first answer is "none".
     const int64_t burst = (max_left + F.batch - 1) / F.batch;
     int rc;
-    for (int64_t r = 0; r < burst; ++r) {
+    uint32_t hdr[2] = {0, 0};   // {trees still searching, error}
+    for (int64_t r = 0;; ++r) {
+      const bool enqueued = r < burst;            // the rounds known to be needed: no host sync between them
+      if (!enqueued && hdr[0] == 0) break;
       BSG_CUDA(e, cudaMemsetAsync(F.leaf_ret, 0, (size_t)slots * sizeof(int32_t), st));
       forest_descend_kernel<G><<<wgrid, kForestWarpThreads, 0, st>>>(F, (const typename G::Tables*)e->tables_dev);
       if ((rc = launch_leaves<G>(st)) != BSG_OK) return rc;
+      const bool ask = r + 1 >= burst;            // the backup kernel counts the trees with simulations left
+      if (ask) BSG_CUDA(e, cudaMemsetAsync(F.active, 0, sizeof(uint32_t), st));
       forest_finish_kernel<G><<<wgrid, kForestWarpThreads, 0, st>>>(F);
       f->rounds += 1;
-    }
-    for (;;) {
-      BSG_CUDA(e, cudaMemsetAsync(F.active, 0, sizeof(uint32_t), st));
-      BSG_CUDA(e, cudaMemsetAsync(F.leaf_ret, 0, (size_t)slots * sizeof(int32_t), st));
-      forest_descend_kernel<G><<<wgrid, kForestWarpThreads, 0, st>>>(F, (const typename G::Tables*)e->tables_dev);
-      uint32_t hdr[2] = {0, 0};   // {active trees, error}
-      BSG_CUDA(e, cudaMemcpyAsync(&hdr[0], F.active, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-      BSG_CUDA(e, cudaMemcpyAsync(&hdr[1], F.error, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-      BSG_CUDA(e, cudaStreamSynchronize(st));
-      if (hdr[1]) {
-        f->err = hdr[1] == 1 ? "forest: node pool exhausted (raise node_capacity)"
-               : (hdr[1] == 2 ? "forest: log table exhausted (raise max_visits)" : "forest: path deeper than the game allows");
-        return BSG_ERR_BAD_ARG;
+      if (ask) {
+        BSG_CUDA(e, cudaMemcpyAsync(&hdr[0], F.active, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        BSG_CUDA(e, cudaMemcpyAsync(&hdr[1], F.error, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        BSG_CUDA(e, cudaStreamSynchronize(st));
+        if (hdr[1]) {
+          f->err = hdr[1] == 1 ? "forest: node pool exhausted (raise node_capacity)"
+                 : (hdr[1] == 2 ? "forest: log table exhausted (raise max_visits)" : "forest: path deeper than the game allows");
+          return BSG_ERR_BAD_ARG;
+        }
       }
-      if (hdr[0] == 0) { f->launches += 1; break; }   // the descent that found nothing to do
-      if ((rc = launch_leaves<G>(st)) != BSG_OK) return rc;
-      forest_finish_kernel<G><<<wgrid, kForestWarpThreads, 0, st>>>(F);
-      f->rounds += 1;
     }
     forest_expand_root_kernel<G><<<grid, kForestThreads, 0, st>>>(F);
     // totals of this step's playouts (game steps, stuck lanes): accumulated on the device, read
