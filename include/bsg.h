@@ -34,7 +34,7 @@ extern "C" {
 /* Game ids.  Strings accepted by bsg_game_id are the reference's game strings
  * (open_spiel/spiel.h:792-803): "tic_tac_toe", "connect_four", "breakthrough",
  * "breakthrough(rows=8,columns=8)", "hex", "hex(board_size=11)", "pentago", "othello", "y",
- * "y(board_size=19)", "havannah", "havannah(board_size=8)". */
+ * "y(board_size=19)", "havannah", "havannah(board_size=8)", "go(board_size=9)". */
 #define BSG_TIC_TAC_TOE 0
 #define BSG_CONNECT_FOUR 1
 #define BSG_BREAKTHROUGH 2
@@ -52,6 +52,12 @@ extern "C" {
 #define BSG_HAVANNAH 9 /* open_spiel/games/havannah.cc, board_size = 8 (the reference's default), same row */
 /* Host-helper-only id for the reference's havannah(board_size=4) golden playthrough; no kernels. */
 #define BSG_HAVANNAH4_HOST_ONLY 10
+/* open_spiel/games/go.cc at board_size = 9, komi 7.5, no handicap (same row).  The reference's
+ * default board is 19 x 19: its games run to 722 moves (the playout ABI counts moves in uint8) and
+ * its pseudo-liberty sums are 16-bit, exact only on small boards — see csrc/bsg_go.cuh. */
+#define BSG_GO 11
+/* Host-helper-only id for the reference's go(board_size=7,komi=4.5) golden playthrough. */
+#define BSG_GO7_HOST_ONLY 12
 
 #define BSG_OK 0
 #define BSG_ERR_BAD_GAME (-1)

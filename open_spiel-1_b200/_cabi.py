@@ -18,8 +18,8 @@ ERR_BAD_GAME, ERR_BAD_ARG, ERR_ILLEGAL_ACTION, ERR_CUDA, ERR_NO_DEVICE, ERR_STUC
     -1, -2, -3, -4, -5, -6, -7)
 TERMINAL_PLAYER = -4
 
-TIC_TAC_TOE, CONNECT_FOUR, BREAKTHROUGH, HEX, HEX5_HOST_ONLY, PENTAGO, OTHELLO, Y, Y9_HOST_ONLY, HAVANNAH, HAVANNAH4_HOST_ONLY = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10
-DEVICE_GAMES = (TIC_TAC_TOE, CONNECT_FOUR, BREAKTHROUGH, HEX, PENTAGO, OTHELLO, Y, HAVANNAH)   # games with CUDA kernels
+TIC_TAC_TOE, CONNECT_FOUR, BREAKTHROUGH, HEX, HEX5_HOST_ONLY, PENTAGO, OTHELLO, Y, Y9_HOST_ONLY, HAVANNAH, HAVANNAH4_HOST_ONLY, GO, GO7_HOST_ONLY = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12
+DEVICE_GAMES = (TIC_TAC_TOE, CONNECT_FOUR, BREAKTHROUGH, HEX, PENTAGO, OTHELLO, Y, HAVANNAH, GO)   # games with CUDA kernels
 
 
 class PlayoutIO(ctypes.Structure):

@@ -182,6 +182,6 @@ BSG_HD int select32(u32 x, int k) {
 enum : int { kOutcomeP0 = 0, kOutcomeP1 = 1, kOutcomeDraw = 2, kOutcomeNone = 3 };
 BSG_HD int outcome_ret0(int outcome) { return outcome == kOutcomeP0 ? 1 : (outcome == kOutcomeP1 ? -1 : 0); }
 
-enum : int { kGameTicTacToe = 0, kGameConnectFour = 1, kGameBreakthrough = 2, kGameHex = 3, kGamePentago = 5, kGameOthello = 6, kGameY = 7, kGameHavannah = 9 };
+enum : int { kGameTicTacToe = 0, kGameConnectFour = 1, kGameBreakthrough = 2, kGameHex = 3, kGamePentago = 5, kGameOthello = 6, kGameY = 7, kGameHavannah = 9, kGameGo = 11 };
 
 }  // namespace bsg

@@ -1874,3 +1874,4 @@ typedef YT<19> Y;
 }  // namespace bsg
 
 #include "bsg_havannah.cuh"
+#include "bsg_go.cuh"

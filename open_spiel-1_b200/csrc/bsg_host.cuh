@@ -16,6 +16,7 @@ namespace bsg {
 typedef HexT<5> Hex5;
 typedef YT<9> Y9;
 typedef HavannahT<4> Havannah4;
+typedef GoT<7, 9> Go7;      // the playthrough's go(board_size=7,komi=4.5)
 constexpr int kMaxLegal = 320;   // pentago: 36 cells x 8 rotations
 
 template <class G> struct TablesOf {
@@ -53,6 +54,8 @@ template <class F> inline int dispatch_game(int game, F&& f) {
     case BSG_Y9_HOST_ONLY: return f.template operator()<Y9>();
     case BSG_HAVANNAH: return f.template operator()<Havannah>();
     case BSG_HAVANNAH4_HOST_ONLY: return f.template operator()<Havannah4>();
+    case BSG_GO: return f.template operator()<Go>();
+    case BSG_GO7_HOST_ONLY: return f.template operator()<Go7>();
     default: break;
   }
   return BSG_ERR_BAD_GAME;
@@ -68,6 +71,7 @@ template <class F> inline int dispatch_device_game(int game, F&& f) {
     case BSG_OTHELLO: return f.template operator()<Othello>();
     case BSG_Y: return f.template operator()<Y>();
     case BSG_HAVANNAH: return f.template operator()<Havannah>();
+    case BSG_GO: return f.template operator()<Go>();
     default: break;
   }
   return BSG_ERR_BAD_GAME;
@@ -462,6 +466,35 @@ template <int S> struct Text<HavannahT<S>> {  // havannah.cc:197-267 (plain outp
       if (y < S - 1) { out += ' '; out += (char)('a' + S + y); }   // trailing x coordinate
       out += '\n';
     }
+    return out;
+  }
+  static bool has_board_format() { return false; }
+  static std::string serialize(const typename G::State&) { return std::string(); }
+  static int deserialize(typename G::State&, const char*) { return BSG_ERR_BAD_ARG; }
+};
+
+template <int N, int K2> struct Text<GoT<N, K2>> {   // go.cc:150-156 + go_board.cc:478-493
+  typedef GoT<N, K2> G;
+  static std::string to_string(const typename G::State& s) {
+    std::string out = "GoState(komi=";
+    out += std::to_string(K2 / 2);
+    if (K2 & 1) out += ".5";
+    out += ", to_play=";
+    out += s.mv ? "W" : "B";
+    out += ", history.size()=" + std::to_string(s.moves) + ")\n\n";
+    for (int row = N - 1; row >= 0; --row) {
+      if (row + 1 < 10) out += ' ';
+      out += std::to_string(row + 1);
+      out += ' ';
+      for (int col = 0; col < N; ++col) {
+        const int c = row * N + col;
+        out += G::has(s.st[0], c) ? 'X' : (G::has(s.st[1], c) ? 'O' : '+');
+      }
+      out += '\n';
+    }
+    out += "   ";
+    out += std::string("ABCDEFGHJKLMNOPQRST").substr(0, N);
+    out += '\n';
     return out;
   }
   static bool has_board_format() { return false; }

@@ -1170,6 +1170,9 @@ int bsg_game_id(const char* g) {
   if (s == "havannah" || s == "havannah()" || s == "havannah(board_size=8)" ||
       s == "havannah(ansi_color_output=False,board_size=8)" || s == "havannah(ansi_color_output=false,board_size=8)")
     return BSG_HAVANNAH;
+  if (s == "go(board_size=9)" || s == "go(board_size=9,komi=7.5)" || s == "go(board_size=9,handicap=0,komi=7.5)" ||
+      s == "go(board_size=9,handicap=0)") return BSG_GO;
+  if (s == "go(board_size=7,komi=4.5)" || s == "go(board_size=7,handicap=0,komi=4.5)") return BSG_GO7_HOST_ONLY;
   if (s == "havannah(board_size=4)" || s == "havannah(ansi_color_output=False,board_size=4)" ||
       s == "havannah(ansi_color_output=false,board_size=4)") return BSG_HAVANNAH4_HOST_ONLY;
   return BSG_ERR_BAD_GAME;
@@ -1201,6 +1204,8 @@ int bsg_observation_shape(int game, int shape[3]) {
     case BSG_Y9_HOST_ONLY: shape[0] = 3; shape[1] = 9; shape[2] = 9; return BSG_OK;
     case BSG_HAVANNAH: shape[0] = 3; shape[1] = 15; shape[2] = 15; return BSG_OK;     // havannah.h:209-211
     case BSG_HAVANNAH4_HOST_ONLY: shape[0] = 3; shape[1] = 7; shape[2] = 7; return BSG_OK;
+    case BSG_GO: shape[0] = 4; shape[1] = 9; shape[2] = 9; return BSG_OK;               // go.h:141-145
+    case BSG_GO7_HOST_ONLY: shape[0] = 4; shape[1] = 7; shape[2] = 7; return BSG_OK;
     default: return BSG_ERR_BAD_GAME;
   }
 }
@@ -1261,7 +1266,8 @@ uint32_t bsg_draw(uint64_t seed, uint64_t playout, uint32_t t) {
 int bsg_create(int game, int device, bsg_engine** out) {
   if (!out) return BSG_ERR_BAD_ARG;
   *out = nullptr;
-  if (game < 0 || game == BSG_HEX5_HOST_ONLY || game == BSG_Y9_HOST_ONLY || game > BSG_HAVANNAH) return BSG_ERR_BAD_GAME;
+  if (game < 0 || game == BSG_HEX5_HOST_ONLY || game == BSG_Y9_HOST_ONLY || game == BSG_HAVANNAH4_HOST_ONLY || game > BSG_GO)
+    return BSG_ERR_BAD_GAME;
   int count = 0;
   if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return BSG_ERR_NO_DEVICE;
   if (device < 0 || device >= count) return BSG_ERR_BAD_ARG;

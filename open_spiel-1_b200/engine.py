@@ -10,7 +10,7 @@ import numpy as np
 
 from . import _cabi as C
 
-GAME_NAMES = ("tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y", "havannah")
+GAME_NAMES = ("tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y", "havannah", "go(board_size=9)")
 
 
 def game_id(game):
@@ -22,7 +22,7 @@ def game_id(game):
   gid = C.lib.bsg_game_id(game.encode())
   if gid < 0:
     raise RuntimeError("bsg: unsupported game '%s' (supported: tic_tac_toe, connect_four, "
-                       "breakthrough 8x8, hex 11x11, pentago, othello, y 19, havannah 8)" % game)
+                       "breakthrough 8x8, hex 11x11, pentago, othello, y 19, havannah 8, go 9x9)" % game)
   return gid
 
 

@@ -21,7 +21,7 @@ from .mcts import SearchNode
 from .parallel import _world, shard_range
 
 # upper bounds on the legal actions of one state (children per expansion)
-_MAX_CHILDREN = {C.TIC_TAC_TOE: 9, C.CONNECT_FOUR: 7, C.BREAKTHROUGH: 48, C.HEX: 121, C.PENTAGO: 288, C.OTHELLO: 34, C.Y: 190, C.HAVANNAH: 169}
+_MAX_CHILDREN = {C.TIC_TAC_TOE: 9, C.CONNECT_FOUR: 7, C.BREAKTHROUGH: 48, C.HEX: 121, C.PENTAGO: 288, C.OTHELLO: 34, C.Y: 190, C.HAVANNAH: 169, C.GO: 82}
 _MERGE_FIELDS = 5
 
 

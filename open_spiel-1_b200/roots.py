@@ -18,6 +18,7 @@ ROOT_DEPTHS = {  # cfg2 U{8..20}, cfg3 U{0..40}, cfg4 U{0..60}
     "othello": (0, 40),
     "y": (0, 80),
     "havannah": (0, 60),
+    "go(board_size=9)": (0, 60),
 }
 
 

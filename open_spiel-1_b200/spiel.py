@@ -50,11 +50,12 @@ _CANONICAL = {C.TIC_TAC_TOE: "tic_tac_toe()", C.CONNECT_FOUR: "connect_four()",
               C.HEX5_HOST_ONLY: "hex(board_size=5)", C.PENTAGO: "pentago(ansi_color_output=False)", C.OTHELLO: "othello()",
               C.Y: "y(ansi_color_output=False,board_size=19)", C.Y9_HOST_ONLY: "y(ansi_color_output=False,board_size=9)",
               C.HAVANNAH: "havannah(ansi_color_output=False,board_size=8)",
-              C.HAVANNAH4_HOST_ONLY: "havannah(ansi_color_output=False,board_size=4)"}
+              C.HAVANNAH4_HOST_ONLY: "havannah(ansi_color_output=False,board_size=4)",
+              C.GO: "go(board_size=9,handicap=0,komi=7.5)", C.GO7_HOST_ONLY: "go(board_size=7,handicap=0,komi=4.5)"}
 _SHORT = {C.TIC_TAC_TOE: "tic_tac_toe", C.CONNECT_FOUR: "connect_four",
           C.BREAKTHROUGH: "breakthrough", C.HEX: "hex", C.HEX5_HOST_ONLY: "hex",
           C.PENTAGO: "pentago", C.OTHELLO: "othello", C.Y: "y", C.Y9_HOST_ONLY: "y",
-          C.HAVANNAH: "havannah", C.HAVANNAH4_HOST_ONLY: "havannah"}
+          C.HAVANNAH: "havannah", C.HAVANNAH4_HOST_ONLY: "havannah", C.GO: "go", C.GO7_HOST_ONLY: "go"}
 
 
 class Game:

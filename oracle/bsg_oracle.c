@@ -39,6 +39,7 @@ int orc_num_distinct_actions(int game, int n) {
     case ORC_OTHELLO: return 65;     /* othello.h:128: 64 cells + pass */
     case ORC_Y: return n * n;        /* y.h:174-178: the cut-off corner is never legal */
     case ORC_HAVANNAH: return (2 * n - 1) * (2 * n - 1);   /* havannah.h:196-200 */
+    case ORC_GO: return n * n + 1;   /* go.h:52-54 */
     default: return n * n;
   }
 }
@@ -51,6 +52,7 @@ int orc_max_game_length(int game, int n) {
     case ORC_OTHELLO: return 64; /* othello.h:142 */
     case ORC_Y: return n * (n + 1) / 2; /* y.h:192-197 */
     case ORC_HAVANNAH: return (2 * n - 1) * (2 * n - 1) - n * (n - 1); /* havannah.h:212-217 */
+    case ORC_GO: return n * n * 2;   /* go.h:59 */
     default: return n * n;
   }
 }
@@ -63,6 +65,7 @@ int orc_obs_size(int game, int n) {
     case ORC_OTHELLO: return 3 * 64; /* othello.h:139-141 */
     case ORC_Y: return 3 * n * n;    /* y.h:189-191 */
     case ORC_HAVANNAH: return 3 * (2 * n - 1) * (2 * n - 1); /* havannah.h:209-211 */
+    case ORC_GO: return 4 * n * n;   /* go.h:141-143, go.cc:108 */
     default: return 9 * n * n;
   }
 }
@@ -562,6 +565,141 @@ static int hv_apply(orc_state* s, int a) {
   return 0;
 }
 
+/* ---------------------------------------------------------------- go (N x N, N <= 9) */
+enum { GO_BLACK = 0, GO_WHITE = 1, GO_EMPTY = 2 };   /* go_board.h: GoColor */
+/* go_board.cc:28-34: the neighbours in the reference's order (row + 1, col + 1, col - 1, row - 1) */
+static int go_nb(const orc_state* s, int cell, int d) {
+  int n = s->board_size, r = cell / n, c = cell % n;
+  int r2 = r + (d == 0 ? 1 : (d == 3 ? -1 : 0)), c2 = c + (d == 1 ? 1 : (d == 2 ? -1 : 0));
+  return (r2 >= 0 && r2 < n && c2 >= 0 && c2 < n) ? r2 * n + c2 : -1;
+}
+/* Walks the chain of `cell`, marking its stones in seen[] (1) and its distinct liberties (2);
+ * returns the number of distinct liberties.  (The reference tracks pseudo-liberty sums per
+ * chain, go_board.h:173-192; in_atari() there means exactly one distinct liberty.) */
+static int go_chain(const orc_state* s, int cell, uint8_t* seen) {
+  int colour = s->cells[cell], libs = 0;
+  seen[cell] = 1;
+  for (int d = 0; d < 4; ++d) {
+    int q = go_nb(s, cell, d);
+    if (q < 0 || seen[q]) continue;
+    if (s->cells[q] == GO_EMPTY) { seen[q] = 2; ++libs; }
+    else if (s->cells[q] == colour) libs += go_chain(s, q, seen);
+  }
+  return libs;
+}
+static int go_liberties(const orc_state* s, int cell, uint8_t* seen) {
+  memset(seen, 0, 81);
+  return go_chain(s, cell, seen);
+}
+/* go_board.cc:416-441 */
+static int go_is_legal(const orc_state* s, int p, int c) {
+  uint8_t seen[81];
+  if (s->cells[p] != GO_EMPTY || p == s->ko_point) return 0;
+  for (int d = 0; d < 4; ++d) {           /* chain(p).num_pseudo_liberties > 0: an empty neighbour */
+    int q = go_nb(s, p, d);
+    if (q >= 0 && s->cells[q] == GO_EMPTY) return 1;
+  }
+  for (int d = 0; d < 4; ++d) {           /* connects to a friendly chain that is not in atari */
+    int q = go_nb(s, p, d);
+    if (q >= 0 && s->cells[q] == c && go_liberties(s, q, seen) != 1) return 1;
+  }
+  for (int d = 0; d < 4; ++d) {           /* kills an enemy chain that is in atari */
+    int q = go_nb(s, p, d);
+    if (q >= 0 && s->cells[q] == 1 - c && go_liberties(s, q, seen) == 1) return 1;
+  }
+  return 0;
+}
+static int go_legal(const orc_state* s, int* out) {      /* go.cc:127-137 */
+  int n = 0, cells = s->board_size * s->board_size;
+  for (int p = 0; p < cells; ++p) if (go_is_legal(s, p, s->cur_player)) out[n++] = p;
+  out[n++] = cells;                                      /* the pass, always */
+  return n;
+}
+/* go_board.cc:525-553 */
+static int go_surrounded(const orc_state* s, int p, uint8_t* marked, int* rb, int* rw) {
+  if (marked[p] || (*rb && *rw)) return 0;
+  marked[p] = 1;
+  int n = 1;
+  for (int d = 0; d < 4; ++d) {
+    int q = go_nb(s, p, d);
+    if (q < 0) continue;
+    if (s->cells[q] == GO_BLACK) *rb = 1;
+    else if (s->cells[q] == GO_WHITE) *rw = 1;
+    else n += go_surrounded(s, q, marked, rb, rw);
+  }
+  return n;
+}
+/* go_board.cc:555-598, times two (komi2 = 2 * komi) */
+static int go_score2(const orc_state* s) {
+  uint8_t marked[81];
+  int delta = 0, cells = s->board_size * s->board_size;
+  memset(marked, 0, sizeof(marked));
+  for (int p = 0; p < cells; ++p) {
+    if (s->cells[p] == GO_BLACK) ++delta;
+    else if (s->cells[p] == GO_WHITE) --delta;
+    else if (!marked[p]) {
+      int rb = 0, rw = 0;
+      int n = go_surrounded(s, p, marked, &rb, &rw);
+      if (rb && !rw) delta += n;
+      else if (!rb && rw) delta -= n;
+    }
+  }
+  return 2 * delta - s->komi2;
+}
+static int go_terminal(const orc_state* s) {             /* go.cc:166-172 */
+  int cells = s->board_size * s->board_size;
+  if (s->num_moves < 2) return 0;
+  return s->num_moves >= 2 * cells || s->superko || (s->last_action == cells && s->prev_action == cells);
+}
+static void go_remove_chain(orc_state* s, int cell, int colour, int* captured, int* where) {
+  s->cells[cell] = GO_EMPTY;
+  *captured += 1;
+  *where = cell;
+  for (int d = 0; d < 4; ++d) {
+    int q = go_nb(s, cell, d);
+    if (q >= 0 && s->cells[q] == colour) go_remove_chain(s, q, colour, captured, where);
+  }
+}
+/* go.cc:201-211 + go_board.cc:257-289 */
+static int go_apply(orc_state* s, int a) {
+  int cells = s->board_size * s->board_size, c = s->cur_player;
+  uint8_t seen[81];
+  if (a < 0 || a > cells) return -1;
+  if (a == cells) {
+    s->ko_point = -1;
+  } else {
+    if (!go_is_legal(s, a, c)) return -1;
+    int eye = 1;                                         /* played in an enemy eye? */
+    for (int d = 0; d < 4; ++d) {
+      int q = go_nb(s, a, d);
+      if (q >= 0 && (s->cells[q] == c || s->cells[q] == GO_EMPTY)) eye = 0;
+    }
+    s->cells[a] = c;
+    int captured = 0, where = -1;
+    for (int d = 0; d < 4; ++d) {                        /* CaptureDeadChains */
+      int q = go_nb(s, a, d);
+      if (q >= 0 && s->cells[q] == 1 - c && go_liberties(s, q, seen) == 0)
+        go_remove_chain(s, q, 1 - c, &captured, &where);
+    }
+    s->ko_point = (eye && captured == 1) ? where : -1;
+  }
+  s->prev_action = s->last_action;
+  s->last_action = a;
+  s->cur_player = 1 - c;
+  /* repetitions_: every position so far; a non-pass move that recreates one is a superko */
+  int k = s->num_moves + 1;
+  for (int p = 0; p < cells; ++p) s->past[k][p] = (uint8_t)s->cells[p];
+  if (a != cells)
+    for (int j = 0; j < k && !s->superko; ++j)
+      if (memcmp(s->past[j], s->past[k], (size_t)cells) == 0) s->superko = 1;
+  s->num_moves = k;
+  if (go_terminal(s)) {                                  /* go.cc:174-199 */
+    if (s->superko) s->outcome = 2;
+    else { int sc = go_score2(s); s->outcome = sc > 0 ? 0 : (sc < 0 ? 1 : 2); }
+  }
+  return 0;
+}
+
 /* ---------------------------------------------------------------- generic API */
 void orc_init(orc_state* s, int game, int board_size) {
   memset(s, 0, sizeof(*s));
@@ -573,6 +711,14 @@ void orc_init(orc_state* s, int game, int board_size) {
      * passed by a caller that does not care about the size means "the default". */
     s->board_size = (board_size > 0 && board_size != 11) ? board_size : 19;
     y_init(s);
+  }
+  if (game == ORC_GO) {
+    /* go.h:34-36: komi 7.5 by default; the device game is 9 x 9; the reference's playthrough is
+     * go(board_size=7,komi=4.5) */
+    s->board_size = (board_size == 7) ? 7 : 9;
+    s->komi2 = s->board_size == 7 ? 9 : 15;
+    s->ko_point = -1; s->last_action = -1; s->prev_action = -1;
+    for (int p = 0; p < s->board_size * s->board_size; ++p) { s->cells[p] = GO_EMPTY; s->past[0][p] = GO_EMPTY; }
   }
   if (game == ORC_HAVANNAH) {
     /* havannah.h:39: radius 8 by default; the reference's playthrough uses 4 (a hex-style
@@ -603,6 +749,7 @@ int orc_is_terminal(const orc_state* s) {
     case ORC_OTHELLO: return s->outcome != -1;                      /* othello.cc:284-286 */
     case ORC_Y: return s->outcome != -1;                            /* y.h:129 */
     case ORC_HAVANNAH: return s->outcome != -1;                     /* havannah.h:146 */
+    case ORC_GO: return go_terminal(s);
     default: return s->outcome != -1;                               /* hex.cc:248 */
   }
 }
@@ -631,6 +778,8 @@ int orc_legal_actions(const orc_state* s, int* out) {
       for (int c = 0; c < s->board_size * s->board_size; ++c)
         if (s->cells[c] == Y_NONE) out[n++] = c;
       return n;
+    case ORC_GO:
+      return go_legal(s, out);
     case ORC_HAVANNAH: /* havannah.cc:182-194 */
       for (int c = 0; c < hv_diam(s) * hv_diam(s); ++c)
         if (s->cells[c] == HV_NONE) out[n++] = c;
@@ -652,6 +801,7 @@ int orc_apply(orc_state* s, int a) {
     case ORC_OTHELLO: return ot_apply(s, a);
     case ORC_Y: return y_apply(s, a);
     case ORC_HAVANNAH: return hv_apply(s, a);
+    case ORC_GO: return go_apply(s, a);
     default: return hex_apply(s, a);
   }
 }
@@ -710,6 +860,12 @@ void orc_observation(const orc_state* s, int player, uint8_t* out) {
         plane = v == Y_NONE ? 2 : (v == player ? 0 : 1);
         out[plane * ncell + c] = 1;
       }
+      return;
+    case ORC_GO: /* go.cc:104-125: black, white, empty, then ones when white is to play */
+      ncell = s->board_size * s->board_size;
+      memset(out, 0, 4 * ncell);
+      for (int c = 0; c < ncell; ++c) out[s->cells[c] * ncell + c] = 1;
+      if (s->cur_player == 1) memset(out + 3 * ncell, 1, ncell);
       return;
     case ORC_HAVANNAH: /* havannah.cc:284-312: plane 0 the observer's stones, 1 the other's, 2
                         * empty; the cut-off corners stay zero in every plane */

@@ -18,7 +18,7 @@
 extern "C" {
 #endif
 
-enum { ORC_TTT = 0, ORC_C4 = 1, ORC_BT = 2, ORC_HEX = 3, ORC_PENTAGO = 5, ORC_OTHELLO = 6, ORC_Y = 7, ORC_HAVANNAH = 9 };
+enum { ORC_TTT = 0, ORC_C4 = 1, ORC_BT = 2, ORC_HEX = 3, ORC_PENTAGO = 5, ORC_OTHELLO = 6, ORC_Y = 7, ORC_HAVANNAH = 9, ORC_GO = 11 };
 #define ORC_MAX_LEGAL 320 /* pentago: 36 cells x 8 rotations = 288 */
 #define ORC_MAX_CELLS 361 /* y: 19 x 19 grid (y.h:37) */
 #define ORC_TERMINAL_PLAYER (-4) /* kTerminalPlayerId, open_spiel/spiel.h:48 */
@@ -30,12 +30,16 @@ typedef struct {
   int outcome;              /* -1 none/unknown, 0 player 0 won, 1 player 1 won, 2 draw */
   int num_moves;
   int pieces[2];            /* breakthrough piece counters */
-  int board_size;           /* hex N (11 default; 5 for the playthrough); y N (19 default; 9); havannah radius (8 default; 4) */
+  int board_size;           /* hex N (11 default; 5 for the playthrough); y N (19 default; 9); havannah radius (8 default; 4); go N (9; 7) */
   /* y: the union-find embedded in the cell array (y.h:96-117) */
   int16_t parent[ORC_MAX_CELLS], size[ORC_MAX_CELLS];
   uint8_t edge[ORC_MAX_CELLS];
   /* havannah: corner sets at the leaders and the ring search's marks (havannah.h:96-131) */
   uint8_t corner[ORC_MAX_CELLS], mark[ORC_MAX_CELLS];
+  /* go (board sizes up to 9): komi * 2, ko point (-1: none), the last two actions, superko flag,
+   * and every earlier position of the game, cell by cell (go.cc:204-211 keeps hashes of them) */
+  int komi2, ko_point, last_action, prev_action, superko;
+  uint8_t past[2 * 81 + 1][81];
 } orc_state;
 
 int orc_num_distinct_actions(int game, int board_size);

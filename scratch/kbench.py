@@ -5,7 +5,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import open_spiel_1_b200 as bsg
 from open_spiel_1_b200.roots import make_roots, ROOT_DEPTHS
-DEF = {"havannah": 1 << 20, "connect_four": 1 << 24, "tic_tac_toe": 1 << 24, "breakthrough": 1 << 22, "hex": 1 << 20,
+DEF = {"go(board_size=9)": 1 << 18, "havannah": 1 << 20, "connect_four": 1 << 24, "tic_tac_toe": 1 << 24, "breakthrough": 1 << 22, "hex": 1 << 20,
        "pentago": 1 << 22, "othello": 1 << 21, "y": 1 << 21}
 out = {}
 for spec in sys.argv[1:] or ["connect_four"]:

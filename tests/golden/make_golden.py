@@ -35,6 +35,7 @@ GAMES = {
     "othello": ("othello.txt", (3, 8, 8)),
     "y9": ("y(board_size=9).txt", (3, 9, 9)),
     "havannah4": ("havannah(board_size=4).txt", (3, 7, 7)),
+    "go7": ("go.txt", (4, 7, 7)),
 }
 
 

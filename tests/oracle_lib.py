@@ -12,8 +12,8 @@ import numpy as np
 
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(REPO, "oracle")
-GAME_IDS = {"tic_tac_toe": 0, "connect_four": 1, "breakthrough": 2, "hex": 3, "pentago": 5, "othello": 6, "y": 7, "havannah": 9}
-OBS_SIZE = {"tic_tac_toe": 27, "connect_four": 126, "breakthrough": 192, "hex": 1089, "pentago": 108, "othello": 192, "y": 1083, "havannah": 675}
+GAME_IDS = {"tic_tac_toe": 0, "connect_four": 1, "breakthrough": 2, "hex": 3, "pentago": 5, "othello": 6, "y": 7, "havannah": 9, "go": 11, "go(board_size=9)": 11}
+OBS_SIZE = {"tic_tac_toe": 27, "connect_four": 126, "breakthrough": 192, "hex": 1089, "pentago": 108, "othello": 192, "y": 1083, "havannah": 675, "go": 324, "go(board_size=9)": 324}
 vp = ctypes.c_void_p
 
 
@@ -26,6 +26,9 @@ def obs_size(game, board_size=11):
   if game == "havannah":
     n = 8 if board_size == 11 else board_size
     return 3 * (2 * n - 1) * (2 * n - 1)
+  if game.startswith("go"):
+    n = 7 if board_size == 7 else 9
+    return 4 * n * n
   return OBS_SIZE[game]
 
 
@@ -184,6 +187,8 @@ class Reference:
   def game_string(game, board_size=11):
     if game == "y":   # default 19 (y.h:38); callers that pass the hex default mean "default"
       return ("y(board_size=%d)" % (19 if board_size == 11 else board_size)).encode()
+    if game.startswith("go"):   # the device game is 9 x 9 at the default komi; the playthrough is 7 x 7 at komi 4.5
+      return b"go(board_size=7,komi=4.5)" if board_size == 7 else b"go(board_size=9)"
     if game == "havannah":   # default 8 (havannah.h:39)
       return ("havannah(board_size=%d)" % (8 if board_size == 11 else board_size)).encode()
     return ("hex(board_size=%d)" % board_size if game == "hex" else game).encode()

@@ -33,7 +33,8 @@ def test_static_facts_match_reference_constants():
            "breakthrough": (768, 209, 192, [3, 8, 8]), "hex": (121, 121, 1089, [9, 11, 11]),
            "pentago": (288, 36, 108, [3, 6, 6]), "othello": (65, 64, 192, [3, 8, 8]),
            "y": (361, 190, 1083, [3, 19, 19]), "y(board_size=9)": (81, 45, 243, [3, 9, 9]),
-           "havannah": (225, 169, 675, [3, 15, 15]), "havannah(board_size=4)": (49, 37, 147, [3, 7, 7])}
+           "havannah": (225, 169, 675, [3, 15, 15]), "havannah(board_size=4)": (49, 37, 147, [3, 7, 7]),
+           "go(board_size=9)": (82, 162, 324, [4, 9, 9]), "go(board_size=7,komi=4.5)": (50, 98, 196, [4, 7, 7])}
   for name, (na, ml, osz, shape) in facts.items():
     g = bsg.load_game(name)
     assert g.num_distinct_actions() == na

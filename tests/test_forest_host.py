@@ -17,7 +17,7 @@ from open_spiel_1_b200 import _cabi as C
     ("connect_four", [3, 3, 2], 500, 16), ("connect_four", [], 200, 1),
     ("breakthrough", [], 150, 8), ("hex", [60, 48], 120, 4), ("pentago", [112, 3], 150, 8),
     ("othello", [19, 18], 200, 8), ("y", [40, 41], 120, 4),
-    ("havannah", [112, 97], 150, 4)])
+    ("havannah", [112, 97], 150, 4), ("go(board_size=9)", [40, 41, 81], 120, 4)])
 def test_forest_trees_equal_host_trees(game, history, sims, batch):
   gid = bsg.game_id(game)
   h = np.asarray(history, np.int64)

@@ -10,7 +10,7 @@ from oracle_lib import Oracle, reference_python
 
 pytestmark = pytest.mark.gpu
 UCT_C = 2.0
-GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex(board_size=11)", "pentago", "othello", "y", "havannah"]
+GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex(board_size=11)", "pentago", "othello", "y", "havannah", "go(board_size=9)"]
 
 
 @pytest.fixture(scope="module")

@@ -10,7 +10,7 @@ import pytest
 from oracle_lib import Oracle
 
 pytestmark = pytest.mark.gpu
-GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y", "havannah"]
+GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y", "havannah", "go(board_size=9)"]
 
 
 @pytest.fixture(scope="module")

@@ -28,7 +28,7 @@ def table(root, scale):
     ("hex", [60, 48], 3, 450, 50, 4),
     ("breakthrough", [], 3, 450, 75, 8),
     ("othello", [19, 18], 3, 450, 75, 8), ("y", [40, 41], 3, 240, 60, 4),
-    ("havannah", [112, 97], 3, 300, 60, 4)])
+    ("havannah", [112, 97], 3, 300, 60, 4), ("go(board_size=9)", [40, 41, 81], 3, 240, 60, 4)])
 def test_forest_equals_host_tree_root_parallel(bsg, game, history, trees, sims, step, batch):
   from open_spiel_1_b200.forest import ForestMCTS
   from open_spiel_1_b200.parallel import RootParallelMCTS

@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 pytestmark = pytest.mark.gpu
-GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y", "havannah"]
+GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y", "havannah", "go(board_size=9)"]
 CANARY = 0xA5
 PAD = 4096
 

@@ -18,7 +18,7 @@ def bsg():
 def test_evaluate_matches_oracle_rollouts(bsg):
   """evaluate() = mean of the oracle's replays of the very playout ids it consumed."""
   oracle = Oracle()
-  for game in ("tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y", "havannah"):
+  for game in ("tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y", "havannah", "go(board_size=9)"):
     ev = bsg.GpuRolloutEvaluator(game, n_rollouts=64, seed=123)
     g = bsg.load_game(game)
     state = g.new_initial_state()
@@ -130,7 +130,7 @@ def _root_stats(root):
 
 @pytest.mark.parametrize("game,moves,leaf_batch", [
     ("tic_tac_toe", 0, 1), ("tic_tac_toe", 2, 8), ("connect_four", 6, 1), ("connect_four", 9, 16),
-    ("breakthrough", 10, 8), ("hex", 30, 4), ("pentago", 8, 8), ("othello", 12, 8), ("y", 30, 4), ("havannah", 30, 4)])
+    ("breakthrough", 10, 8), ("hex", 30, 4), ("pentago", 8, 8), ("othello", 12, 8), ("y", 30, 4), ("havannah", 30, 4), ("go(board_size=9)", 30, 4)])
 def test_native_tree_equals_python_mirror(bsg, game, moves, leaf_batch):
   """The native host tree (csrc/bsg_mcts.cuh) builds the same tree as the Python mirror — the
   specification, itself a restatement of mcts.py:199-443 — visit for visit: same shuffles
@@ -208,7 +208,7 @@ class _TinyModel(object):
     return value, torch.softmax(logits, dim=1)
 
 
-@pytest.mark.parametrize("game", ["tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y", "havannah"])
+@pytest.mark.parametrize("game", ["tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y", "havannah", "go(board_size=9)"])
 def test_alpha_zero_evaluator_matches_host_observations(bsg, game):
   """AlphaZeroEvaluator (evaluator.py:38-83 of the reference) over the GPU observation writer:
   same value / prior as feeding the model the host mirror's observation_tensor() and

@@ -13,11 +13,11 @@ from oracle_lib import Oracle, Reference, reference_path
 
 pytestmark = pytest.mark.gpu
 
-GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y", "havannah"]
+GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y", "havannah", "go(board_size=9)"]
 # replay-parity sizes: >= 1e5 ROOTS per game, two rollouts per root where
 # the checker is cheap so that the rollouts > 1 indexing is in the same comparison
 N_ROOTS = {g: 100000 for g in GAMES}
-ROLLOUTS = {"tic_tac_toe": 2, "connect_four": 2, "breakthrough": 1, "hex": 1, "pentago": 2, "othello": 1, "y": 1, "havannah": 1}
+ROLLOUTS = {"tic_tac_toe": 2, "connect_four": 2, "breakthrough": 1, "hex": 1, "pentago": 2, "othello": 1, "y": 1, "havannah": 1, "go(board_size=9)": 1}
 
 
 @pytest.fixture(scope="module")
@@ -132,7 +132,10 @@ def test_observations_and_masks_bit_exact(game, checker, torch):
   mask = mask.cpu().numpy()
   assert set(np.unique(obs).tolist()) <= {0.0, 1.0}
   cells = {"y": 190, "havannah": 169}.get(game, eng.obs_size // eng.obs_shape[0])   # y, havannah: cut-off corners
-  assert np.all(obs.sum(1) == cells)  # exactly one plane per board cell
+  if game.startswith("go"):   # black / white / empty planes, plus a plane of ones when white is to move
+    assert np.all(obs[:, :3 * 81].sum(1) == 81) and set(np.unique(obs[:, 3 * 81:].sum(1)).tolist()) <= {0.0, 81.0}
+  else:
+    assert np.all(obs.sum(1) == cells)  # exactly one plane per board cell
   obs8 = obs.astype(np.uint8)
   if isinstance(checker, Reference):
     d = checker.state_dump_log(game, log, lens, pl, threads=os.cpu_count() or 1)
@@ -195,7 +198,7 @@ def test_native_rng_win_rates_within_binomial_ci(game, checker, torch):
   # >= 1e6 reference playouts per game where the reference plays them in
   # seconds (all host cores); breakthrough / hex / y at what ~5 s of the reference buys
   n_ref = {"tic_tac_toe": 1 << 20, "connect_four": 1 << 20, "breakthrough": 200000, "hex": 100000,
-           "pentago": 400000, "othello": 40000, "y": 60000, "havannah": 60000}[game]
+           "pentago": 400000, "othello": 40000, "y": 60000, "havannah": 60000, "go(board_size=9)": 60000}[game]
   if isinstance(checker, Reference):
     # reference's own mt19937 stream; per-outcome counts via replay batch are Philox-tied, so
     # use random_playouts for the mean and replay_batch (different seed) for the outcome split
@@ -233,6 +236,7 @@ def test_native_rng_win_rates_within_binomial_ci(game, checker, torch):
     ("othello", 1 << 22, 120, 1, 1 << 16),
     ("y", 1 << 20, 190, 1, 1 << 18),
     ("havannah", 1 << 20, 169, 1, 1 << 17),
+    ("go(board_size=9)", 1 << 18, 162, 1, 1 << 17),
 ])
 def test_full_size_properties(game, n, max_len, min_len, n_check, checker, torch):
   """BASELINE configuration sizes.  (1) The lean kernel's per-playout results (length, return)
@@ -303,7 +307,7 @@ def test_full_size_properties(game, n, max_len, min_len, n_check, checker, torch
 
 @pytest.mark.parametrize("game,n", [("connect_four", 800000), ("breakthrough", 330000),
                                     ("hex", 110000), ("tic_tac_toe", 1100000),
-                                    ("pentago", 300000), ("othello", 330000), ("y", 60000), ("havannah", 70000)])
+                                    ("pentago", 300000), ("othello", 330000), ("y", 60000), ("havannah", 70000), ("go(board_size=9)", 25000)])
 def test_host_buffer_chunked_path_equals_device_path(game, n, torch):
   """bsg_playouts_host cuts large inputs into chunks on two streams (H2D overlapping the
   kernel); totals and per-root sums must equal one device-buffer launch over the same roots,

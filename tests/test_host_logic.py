@@ -21,7 +21,8 @@ GAMES = [("tic_tac_toe", "tic_tac_toe", 11), ("connect_four", "connect_four", 11
          ("breakthrough", "breakthrough", 11), ("hex", "hex", 11), ("hex(board_size=5)", "hex", 5),
          ("pentago", "pentago", 11), ("othello", "othello", 11),
          ("y", "y", 11), ("y(board_size=9)", "y", 9),
-         ("havannah", "havannah", 11), ("havannah(board_size=4)", "havannah", 4)]   # oracle: 11 = the default size, 19
+         ("havannah", "havannah", 11), ("havannah(board_size=4)", "havannah", 4),
+         ("go(board_size=9)", "go", 9), ("go(board_size=7,komi=4.5)", "go", 7)]   # oracle: 11 = the default size, 19
 
 
 @pytest.fixture(scope="module")
@@ -47,7 +48,8 @@ def check_state(oracle, st, oname, bs, hist):
                                           ("hex5", "hex(board_size=5)"),
                                           ("pentago", "pentago"), ("othello", "othello"),
                                           ("y9", "y(board_size=9)"),
-                                          ("havannah4", "havannah(board_size=4)")])
+                                          ("havannah4", "havannah(board_size=4)"),
+                                          ("go7", "go(board_size=7,komi=4.5)")])
 def test_golden_playthroughs(fixture, name):
   with open(os.path.join(GOLD, "playthrough_%s.json" % fixture)) as f:
     data = json.load(f)
@@ -183,7 +185,7 @@ def test_value_only_fill_gives_the_exact_playouts_winner(oracle, name, oname, bs
 def test_plane_table_comes_from_the_abi():
   """bsg_plane_bytes: the packed SoA plane sizes sum to the state size for every game id."""
   from open_spiel_1_b200 import engine as E
-  for gid in range(11):
+  for gid in range(13):
     planes = E.plane_bytes(gid)
     assert planes and sum(planes) == E.state_bytes(gid)
   assert E.plane_bytes(C.CONNECT_FOUR) == [8] and E.plane_bytes(C.BREAKTHROUGH) == [16, 4]

@@ -14,7 +14,8 @@ pytestmark = pytest.mark.skipif(not os.path.exists(reference_path()),
 
 CASES = [("tic_tac_toe", 11, 400), ("connect_four", 11, 400), ("breakthrough", 11, 150),
          ("hex", 11, 60), ("hex", 5, 200), ("pentago", 11, 300), ("othello", 11, 150),
-         ("y", 11, 60), ("y", 9, 200), ("havannah", 11, 150), ("havannah", 4, 400)]   # y: 11 stands for the default size 19
+         ("y", 11, 60), ("y", 9, 200), ("havannah", 11, 150), ("havannah", 4, 400),
+         ("go", 9, 200), ("go", 7, 400)]   # y: 11 stands for the default size 19
 
 
 @pytest.fixture(scope="module")
@@ -69,7 +70,7 @@ def _log_of(histories, stride):
   return log, lens
 
 
-@pytest.mark.parametrize("game", ["tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y", "havannah"])
+@pytest.mark.parametrize("game", ["tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y", "havannah", "go(board_size=9)"])
 def test_dense_log_entry_points_equal_the_per_state_ones(libs, game):
   """ref_replay_log / ref_state_dump_log (the BASELINE-size checker calls of the GPU tests) =
   ref_replay_batch / ref_state_dump on the same roots, terminal states included, and the oracle

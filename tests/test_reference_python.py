@@ -12,7 +12,7 @@ import pytest
 from oracle_lib import reference_python
 
 UCT_C = 2.0
-GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex(board_size=11)", "pentago", "othello", "y", "havannah"]
+GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex(board_size=11)", "pentago", "othello", "y", "havannah", "go(board_size=9)"]
 
 
 @pytest.fixture(scope="module")
@@ -61,7 +61,7 @@ def test_mirror_bot_builds_the_reference_bots_tree(refpy, game):
     for a in rs.history():
       ms.apply_action(a)
     assert str(ms) == str(rs)
-    sims = 300 if game.startswith("hex") else (100 if game in ("y", "havannah") else 600)   # y: ~170 steps per rollout
+    sims = 300 if game.startswith("hex") else (100 if game in ("y", "havannah") or game.startswith("go") else 600)   # y: ~170 steps per rollout
     r_bot = ref_mcts.MCTSBot(rg, UCT_C, sims, ref_mcts.RandomRolloutEvaluator(2, np.random.RandomState(7)),
                              solve=True, random_state=np.random.RandomState(3))
     m_bot = bsg.MCTSBot(mg, UCT_C, sims, ref_mcts.RandomRolloutEvaluator(2, np.random.RandomState(7)),

@@ -12,7 +12,7 @@ from oracle_lib import Reference, reference_path
 pytestmark = pytest.mark.skipif(not os.path.exists(reference_path()),
                                 reason="reference library not built")
 
-GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y", "havannah"]
+GAMES = ["tic_tac_toe", "connect_four", "breakthrough", "hex", "pentago", "othello", "y", "havannah", "go(board_size=9)"]
 
 
 @pytest.fixture(scope="module")
@@ -36,7 +36,7 @@ def test_to_string_and_serialize_match_reference(ref, game):
   import open_spiel_1_b200 as bsg
   from open_spiel_1_b200 import spiel
   rng = np.random.RandomState(7)
-  max_moves = {"tic_tac_toe": 9, "connect_four": 42, "breakthrough": 120, "hex": 121, "pentago": 36, "othello": 120, "y": 190, "havannah": 169}[game]
+  max_moves = {"tic_tac_toe": 9, "connect_four": 42, "breakthrough": 120, "hex": 121, "pentago": 36, "othello": 120, "y": 190, "havannah": 169, "go(board_size=9)": 162}[game]
   for _ in range(60):
     g, s = random_history(bsg, game, rng, max_moves)
     h = s.history()
@@ -53,7 +53,7 @@ def test_deserialize_matches_reference(ref, game):
   import open_spiel_1_b200 as bsg
   from open_spiel_1_b200 import spiel
   rng = np.random.RandomState(11)
-  max_moves = {"tic_tac_toe": 9, "connect_four": 42, "breakthrough": 120, "hex": 121, "pentago": 36, "othello": 120, "y": 190, "havannah": 169}[game]
+  max_moves = {"tic_tac_toe": 9, "connect_four": 42, "breakthrough": 120, "hex": 121, "pentago": 36, "othello": 120, "y": 190, "havannah": 169, "go(board_size=9)": 162}[game]
   for _ in range(60):
     g, s = random_history(bsg, game, rng, max_moves)
     text = ref.to_string(game, s.history(), serialize=True)
@@ -61,7 +61,7 @@ def test_deserialize_matches_reference(ref, game):
     # feeds the empty last field to std::stol (spiel.cc:406-419), so the reference itself only
     # reads that form back through DeserializeGameAndState, which strips one trailing newline
     # (spiel.cc:479-486).  Hand the reference the stripped form; ours accepts both.
-    if game in ("tic_tac_toe", "hex", "pentago", "othello", "y", "havannah") and text.endswith("\n"):
+    if game in ("tic_tac_toe", "hex", "pentago", "othello", "y", "havannah", "go(board_size=9)") and text.endswith("\n"):
       assert str(g.deserialize_state(text)) == str(g.deserialize_state(text[:-1]))
       text = text[:-1]
     want = ref.deserialize_dump(game, text)
