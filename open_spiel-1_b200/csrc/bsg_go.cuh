@@ -44,6 +44,7 @@ struct GoT {
   static_assert(W <= 4 && kCells <= 120, "written for boards up to 10 x 10");
   static constexpr int kNumActions = kCells + 1, kMaxLen = 2 * kCells, kMaxDepth = kMaxLen, kObsSize = 4 * kCells;
   static constexpr int kHistBytes = (kMaxLen + 15) / 16 * 16;
+  static constexpr int kSeenSlots = kMaxLen <= 85 ? 128 : (kMaxLen <= 170 ? 256 : 512);   // load factor <= 2/3
   static constexpr int kStateBytes = 16 + 16 + 4 + kHistBytes;
   static constexpr int kObsWords = (kObsSize + 31) / 32, kMaskWords = (kNumActions + 31) / 32;
   static constexpr int kPlanes = 4;
@@ -60,7 +61,7 @@ struct GoT {
     u32 last_pass, two_pass, superko;
     u32 outc;                      // kOutcomeNone until the game is over
     u64 hash;                      // of the stones on the board
-    u64 seen[kMaxLen + 1];         // hash after every action (and of the empty board)
+    u64 seen[kSeenSlots];          // open-addressed set of the hashes of every earlier non-empty position (0: free)
     unsigned char acts[kHistBytes];
   };
   struct Tables {
@@ -89,8 +90,43 @@ struct GoT {
   BSG_HD static u32 board_word(int w) { constexpr u32 m[4] = {word_mask(0, 0), word_mask(1, 0), word_mask(2, 0), word_mask(3, 0)}; return m[w]; }
   BSG_HD static u32 not_col0(int w) { constexpr u32 m[4] = {word_mask(0, 1), word_mask(1, 1), word_mask(2, 1), word_mask(3, 1)}; return m[w]; }
   BSG_HD static u32 not_col_last(int w) { constexpr u32 m[4] = {word_mask(0, 2), word_mask(1, 2), word_mask(2, 2), word_mask(3, 2)}; return m[w]; }
-  BSG_HD static bool has(const u32* set, int cell) { return (set[cell >> 5] >> (cell & 31)) & 1u; }
-  BSG_HD static void set_bit(u32* set, int cell) { set[cell >> 5] |= 1u << (cell & 31); }
+  // Word / bit access by selects: a set indexed with a run-time word number would be forced out
+  // of registers into local memory (every lane of the playout kernel carries several sets).
+  BSG_HD static u32 word_of(const u32* set, int w) {
+    u32 x = set[0];
+#pragma unroll
+    for (int j = 1; j < W; ++j) x = (w == j) ? set[j] : x;
+    return x;
+  }
+  BSG_HD static bool has(const u32* set, int cell) { return (word_of(set, cell >> 5) >> (cell & 31)) & 1u; }
+  BSG_HD static void set_bit(u32* set, int cell) {
+    const u32 b = 1u << (cell & 31);
+    const int w = cell >> 5;
+#pragma unroll
+    for (int j = 0; j < W; ++j) set[j] |= (w == j) ? b : 0u;
+  }
+  BSG_HD static void clear_bit(u32* set, int cell) {
+    const u32 b = 1u << (cell & 31);
+    const int w = cell >> 5;
+#pragma unroll
+    for (int j = 0; j < W; ++j) set[j] &= (w == j) ? ~b : ~0u;
+  }
+  // Lowest cell of a non-empty set.
+  BSG_HD static int first_cell(const u32* set) {
+    int c = 0;
+    bool found = false;
+#pragma unroll
+    for (int j = 0; j < W; ++j) {
+      const bool here = !found && set[j] != 0u;
+      c = here ? 32 * j + ctz64((u64)set[j]) : c;
+      found = found || here;
+    }
+    return c;
+  }
+  BSG_HD static void stones_of(const State& s, u32 player, u32* out) {
+#pragma unroll
+    for (int w = 0; w < W; ++w) out[w] = player ? s.st[1][w] : s.st[0][w];
+  }
   BSG_HD static int count(const u32* set) { int n = 0; for (int w = 0; w < W; ++w) n += popc32(set[w]); return n; }
   BSG_HD static bool any(const u32* set) { u32 a = 0; for (int w = 0; w < W; ++w) a |= set[w]; return a != 0; }
 
@@ -118,6 +154,27 @@ struct GoT {
         out[w] = g;
       }
       if (!grew) break;
+    }
+  }
+  // The same flood, stopped as soon as the chain is known to have `enough` liberties: returns
+  // min(liberties, enough).  `out` is the whole chain only when the result is below `enough`;
+  // otherwise it is the part flooded so far (still stones of that one chain).
+  BSG_HD static int chain_liberties_capped(const u32* set, int cell, const u32* empty, int enough, u32* out) {
+    for (int w = 0; w < W; ++w) out[w] = 0;
+    set_bit(out, cell);
+    for (;;) {
+      u32 d[W];
+      nb4(out, d);
+      int libs = 0;
+      u32 grew = 0;
+      for (int w = 0; w < W; ++w) {
+        libs += popc32(d[w] & empty[w]);
+        const u32 g = (out[w] | d[w]) & set[w];
+        grew |= g ^ out[w];
+        out[w] = g;
+      }
+      if (libs >= enough) return enough;
+      if (!grew) return libs;
     }
   }
   BSG_HD static int liberties(const u32* chain, const u32* empty) {
@@ -148,30 +205,36 @@ struct GoT {
     u32 e[W], ne[W];
     empties(s, e);
     nb4(e, ne);
-    const u32* mine = s.st[s.mv];
-    const u32* theirs = s.st[s.mv ^ 1u];
+    u32 mine[W], theirs[W];
+    stones_of(s, s.mv, mine);
+    stones_of(s, s.mv ^ 1u, theirs);
     u32 rest[W];
     for (int w = 0; w < W; ++w) { out[w] = e[w] & ne[w]; rest[w] = e[w] & ~ne[w]; }
     // points without an empty neighbour: legal next to a friendly chain that is not in atari or
-    // next to an enemy chain that is (its one liberty is this point)
-    for (int w = 0; w < W; ++w) {
-      u32 m = rest[w];
-      while (m) {
-        const int bit = ctz64((u64)m);
-        m &= m - 1u;
-        const int p = 32 * w + bit;
-        bool ok = false;
-        for (int d = 0; d < 4 && !ok; ++d) {
-          const int q = neighbour(p, d);
-          if (q < 0) continue;
-          u32 ch[W];
-          if (has(mine, q)) { chain_of(mine, q, ch); ok = liberties(ch, e) >= 2; }
-          else if (has(theirs, q)) { chain_of(theirs, q, ch); ok = liberties(ch, e) == 1; }
-        }
-        if (ok) out[w] |= 1u << bit;
+    // next to an enemy chain that is (its one liberty is then this point).  Neither property
+    // depends on the point, so every chain that touches such a point is flooded ONCE and the
+    // verdicts are applied to all of them together.
+    if (any(rest)) {
+      u32 cand[W], known[W], good[W];
+      nb4(rest, cand);
+      for (int w = 0; w < W; ++w) { cand[w] &= mine[w] | theirs[w]; known[w] = 0; good[w] = 0; }
+      for (;;) {
+        u32 todo[W];
+        for (int w = 0; w < W; ++w) todo[w] = cand[w] & ~known[w];
+        if (!any(todo)) break;
+        const int q = first_cell(todo);
+        const bool friendly = has(mine, q);
+        u32 own[W], ch[W];
+        for (int w = 0; w < W; ++w) own[w] = friendly ? mine[w] : theirs[w];
+        const int libs = chain_liberties_capped(own, q, e, 2, ch);   // a partial chain is fine: the
+        const bool ok = friendly ? libs >= 2 : libs == 1;            // rest of it is looked at again
+        for (int j = 0; j < W; ++j) { known[j] |= ch[j]; good[j] |= ok ? ch[j] : 0u; }
       }
+      u32 ng[W];
+      nb4(good, ng);
+      for (int w = 0; w < W; ++w) out[w] |= rest[w] & ng[w];
     }
-    if (s.ko) out[(s.ko - 1u) >> 5] &= ~(1u << ((s.ko - 1u) & 31u));
+    if (s.ko) clear_bit(out, (int)s.ko - 1);
   }
 
   // NumSurroundedPoints / TrompTaylorScore (go_board.cc:525-598): black's area minus white's,
@@ -227,9 +290,9 @@ struct GoT {
       s.two_pass = s.last_pass;
       s.last_pass = 1;
     } else {
-      u32* mine = s.st[me];
-      u32* theirs = s.st[me ^ 1u];
-      u32 e[W];
+      u32 mine[W], theirs[W], e[W];
+      stones_of(s, me, mine);
+      stones_of(s, me ^ 1u, theirs);
       empties(s, e);
       // played in an enemy eye: no neighbour is friendly or empty (the border counts as enemy)
       bool eye = true;
@@ -239,35 +302,48 @@ struct GoT {
       }
       set_bit(mine, a);
       s.hash ^= zobrist(a, me);
-      e[a >> 5] &= ~(1u << (a & 31));
+      clear_bit(e, a);
       int captured = 0, cap_cell = 0;
-      for (int d = 0; d < 4; ++d) {
-        const int q = neighbour(a, d);
-        if (q < 0 || !has(theirs, q)) continue;
+      // enemy stones next to the new one that have no liberty of their own: only their chains can
+      // have been left without liberties (the order of the captures does not matter: the hash is
+      // a XOR and the ko point is only set when exactly one stone was taken)
+      u32 at[W], cand[W], ne[W];
+      for (int w = 0; w < W; ++w) at[w] = 0;
+      set_bit(at, a);
+      nb4(at, cand);
+      nb4(e, ne);
+      for (int w = 0; w < W; ++w) cand[w] &= theirs[w] & ~ne[w];
+      while (any(cand)) {
+        const int q = first_cell(cand);
         u32 ch[W];
-        chain_of(theirs, q, ch);
-        if (liberties(ch, e) != 0) continue;
-        for (int w = 0; w < W; ++w) {                    // RemoveChain
-          theirs[w] &= ~ch[w];
-          u32 m = ch[w];
-          while (m) {
-            const int bit = ctz64((u64)m);
-            m &= m - 1u;
-            s.hash ^= zobrist(32 * w + bit, me ^ 1u);
-            cap_cell = 32 * w + bit;
-            ++captured;
-          }
+        const int libs = chain_liberties_capped(theirs, q, e, 1, ch);
+        for (int w = 0; w < W; ++w) cand[w] &= ~ch[w];
+        if (libs != 0) continue;
+        for (int w = 0; w < W; ++w) { theirs[w] &= ~ch[w]; e[w] |= ch[w]; }   // RemoveChain
+        while (any(ch)) {
+          cap_cell = first_cell(ch);
+          clear_bit(ch, cap_cell);
+          s.hash ^= zobrist(cap_cell, me ^ 1u);
+          ++captured;
         }
-        empties(s, e);
+      }
+      for (int w = 0; w < W; ++w) {
+        s.st[0][w] = me ? theirs[w] : mine[w];
+        s.st[1][w] = me ? mine[w] : theirs[w];
       }
       s.ko = (eye && captured == 1) ? (u32)cap_cell + 1u : 0u;
       s.last_pass = 0;
-      // superko: a non-pass move that recreates an earlier position
-      for (u32 i = 0; i <= s.moves; ++i)
-        if (s.seen[i] == s.hash) { s.superko = 1; break; }
+      // superko: a non-pass move that recreates an earlier position (never the empty board: a
+      // stone was just played).  One probe sequence both looks the new position up and files it;
+      // at most kMaxLen positions are ever filed, so a free slot always ends the sequence.
+      const u64 key = s.hash | (u64)(s.hash == 0);             // 0 marks a free slot
+      for (u32 slot = (u32)(key >> 40);; ++slot) {
+        const u64 k = s.seen[slot & (u32)(kSeenSlots - 1)];
+        if (k == key) { s.superko = 1; break; }
+        if (k == 0) { s.seen[slot & (u32)(kSeenSlots - 1)] = key; break; }
+      }
     }
     s.moves += 1u;
-    if (s.moves <= (u32)kMaxLen) s.seen[s.moves] = s.hash;
     s.mv = me ^ 1u;
     settle(s);
   }
@@ -277,7 +353,7 @@ struct GoT {
     s.mv = 0; s.ko = 0; s.moves = 0; s.last_pass = 0; s.two_pass = 0; s.superko = 0;
     s.outc = kOutcomeNone;
     s.hash = 0;
-    s.seen[0] = 0;
+    for (int i = 0; i < kSeenSlots; ++i) s.seen[i] = 0;
     for (int i = 0; i < kHistBytes; ++i) s.acts[i] = 0;
   }
   // A packed state is its move history (plane 3): replaying it rebuilds the position AND the set

@@ -27,6 +27,6 @@ for spec in sys.argv[1:] or ["connect_four"]:
   e1.record(); torch.cuda.synchronize()
   ms = e0.elapsed_time(e1) / 5
   t = tot.cpu().numpy()
-  out[g] = {"ms": round(ms, 4), "gsteps_per_s": round(float(t[1]) / 5 / ms / 1e6, 2), "sum_ret": int(t[2])}
+  out[spec] = {"ms": round(ms, 4), "gsteps_per_s": round(float(t[1]) / 5 / ms / 1e6, 2), "sum_ret": int(t[2])}
   eng.close()
 print(os.environ.get("BSG_LIB", "default"), json.dumps(out))
