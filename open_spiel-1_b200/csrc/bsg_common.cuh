@@ -39,6 +39,13 @@ BSG_HD int ctz64(u64 x) {  // index of the lowest set bit; 64 for x = 0
   return x ? __builtin_ctzll(x) : 64;
 #endif
 }
+BSG_HD int ctz32(u32 x) {  // index of the lowest set bit of a non-zero word
+#if defined(__CUDA_ARCH__)
+  return __ffs((int)x) - 1;
+#else
+  return __builtin_ctz(x);
+#endif
+}
 BSG_HD u32 umulhi32(u32 a, u32 b) {
 #if defined(__CUDA_ARCH__)
   return __umulhi(a, b);

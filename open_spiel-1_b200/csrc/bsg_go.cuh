@@ -33,6 +33,16 @@
 #pragma once
 #include "bsg_common.cuh"
 
+#ifndef BSG_GO_BULK_FLOOD
+#define BSG_GO_BULK_FLOOD 1
+#endif
+#ifndef BSG_GO_ROLLED
+#define BSG_GO_ROLLED 1
+#endif
+#ifndef BSG_GO_MINBLOCKS
+#define BSG_GO_MINBLOCKS 1
+#endif
+
 namespace bsg {
 
 template <int N, int K2>   // K2 = 2 * komi
@@ -53,17 +63,25 @@ struct GoT {
   static constexpr bool kAsync = false;
   static constexpr bool kMoverCanLose = true;   // the winner is decided by counting
   static constexpr bool kLazyEnd = false;
+  static constexpr bool kRolledGroup = BSG_GO_ROLLED;   // the step loop of the playout kernel is not unrolled
+  static constexpr int kMinBlocks = BSG_GO_MINBLOCKS;   // lean kernel: resident blocks per SM asked of the compiler
   struct State {
     u32 st[2][W];                  // black / white stones
     u32 mv;                        // player to move (0 black)
     u32 ko;                        // ko point + 1 (0: none)
     u32 moves;                     // actions made (passes included)
     u32 last_pass, two_pass, superko;
+    u32 replay, replay_on;         // playout kernel only: history moves still to replay / this group replays (load_lazy)
     u32 outc;                      // kOutcomeNone until the game is over
     u64 hash;                      // of the stones on the board
     u64 seen[kSeenSlots];          // open-addressed set of the hashes of every earlier non-empty position (0: free)
-    unsigned char acts[kHistBytes];
+    __align__(4) unsigned char acts[kHistBytes];
   };
+  // The playout kernel does not replay a root's history inside the claim (a few lanes at work,
+  // the rest of the warp waiting): load_lazy() only copies the history and the lane then replays
+  // one move per iteration of the step loop, beside the other lanes' ordinary steps, in whole
+  // groups so that its first real step starts a Philox block (see playout_kernel).
+  static constexpr bool kReplayLoad = true;
   struct Tables {
     u32 modM[128];
     unsigned char sel8[256][8];
@@ -118,7 +136,7 @@ struct GoT {
 #pragma unroll
     for (int j = 0; j < W; ++j) {
       const bool here = !found && set[j] != 0u;
-      c = here ? 32 * j + ctz64((u64)set[j]) : c;
+      c = here ? 32 * j + ctz32(set[j]) : c;
       found = found || here;
     }
     return c;
@@ -218,6 +236,31 @@ struct GoT {
       u32 cand[W], known[W], good[W];
       nb4(rest, cand);
       for (int w = 0; w < W; ++w) { cand[w] &= mine[w] | theirs[w]; known[w] = 0; good[w] = 0; }
+#if BSG_GO_BULK_FLOOD
+      // First every chain with a liberty that is NOT a surrounded point, both colours in one flood
+      // that all lanes of a warp run together: such a friendly chain has that liberty and the
+      // point (>= 2), such an enemy chain is not captured there.  What is left for the per-chain
+      // loop are chains whose liberties are all surrounded points.
+      {
+        u32 fa[W], fb[W], nbo[W];
+        nb4(out, nbo);                                   // out: the empty points with an empty neighbour
+        for (int w = 0; w < W; ++w) { fa[w] = mine[w] & nbo[w]; fb[w] = theirs[w] & nbo[w]; }
+        for (;;) {
+          u32 da[W], db[W];
+          nb4(fa, da);
+          nb4(fb, db);
+          u32 grew = 0;
+          for (int w = 0; w < W; ++w) {
+            const u32 na = (fa[w] | da[w]) & mine[w], nb = (fb[w] | db[w]) & theirs[w];
+            grew |= (na ^ fa[w]) | (nb ^ fb[w]);
+            fa[w] = na;
+            fb[w] = nb;
+          }
+          if (!grew) break;
+        }
+        for (int w = 0; w < W; ++w) { known[w] = fa[w] | fb[w]; good[w] = fa[w]; }
+      }
+#endif
       for (;;) {
         u32 todo[W];
         for (int w = 0; w < W; ++w) todo[w] = cand[w] & ~known[w];
@@ -240,14 +283,40 @@ struct GoT {
   // NumSurroundedPoints / TrompTaylorScore (go_board.cc:525-598): black's area minus white's,
   // with the reference's order-dependent early stop; returns 2 * score (komi included).
   BSG_HD static int score2(const State& s) {
-    u32 mark[W];
-    for (int w = 0; w < W; ++w) mark[w] = 0;
-    int delta = 0;
+    // Regions of empty points that touch one colour only (or none) are searched to the end by the
+    // reference whatever the order, so they are counted with two floods; only the regions that
+    // touch BOTH colours go through the order-dependent search below.
+    u32 e[W], eb[W], ew[W], mark[W];
+    empties(s, e);
+    nb4(s.st[0], eb);
+    nb4(s.st[1], ew);
+    for (int w = 0; w < W; ++w) { eb[w] &= e[w]; ew[w] &= e[w]; }
+    for (;;) {
+      u32 db[W], dw[W];
+      nb4(eb, db);
+      nb4(ew, dw);
+      u32 grew = 0;
+      for (int w = 0; w < W; ++w) {
+        const u32 nb = (eb[w] | db[w]) & e[w], nw = (ew[w] | dw[w]) & e[w];
+        grew |= (nb ^ eb[w]) | (nw ^ ew[w]);
+        eb[w] = nb;
+        ew[w] = nw;
+      }
+      if (!grew) break;
+    }
+    int delta = count(s.st[0]) - count(s.st[1]);
+    u32 both[W];
+    for (int w = 0; w < W; ++w) {
+      delta += popc32(eb[w] & ~ew[w]) - popc32(ew[w] & ~eb[w]);
+      both[w] = eb[w] & ew[w];
+      mark[w] = 0;
+    }
     unsigned char cell[kCells + 1], dir[kCells + 1];
-    for (int p = 0; p < kCells; ++p) {
-      if (has(s.st[0], p)) { ++delta; continue; }
-      if (has(s.st[1], p)) { --delta; continue; }
-      if (has(mark, p)) continue;
+    for (;;) {
+      u32 todo[W];
+      for (int w = 0; w < W; ++w) todo[w] = both[w] & ~mark[w];
+      if (!any(todo)) break;
+      const int p = first_cell(todo);                // the reference's scan order: ascending points
       bool rb = false, rw = false;
       int n = 1, top = 0;
       set_bit(mark, p);
@@ -294,23 +363,20 @@ struct GoT {
       stones_of(s, me, mine);
       stones_of(s, me ^ 1u, theirs);
       empties(s, e);
+      u32 at[W], cand[W], ne[W];
+      for (int w = 0; w < W; ++w) at[w] = 0;
+      set_bit(at, a);
+      nb4(at, cand);                                      // the neighbours of the new stone
       // played in an enemy eye: no neighbour is friendly or empty (the border counts as enemy)
-      bool eye = true;
-      for (int d = 0; d < 4; ++d) {
-        const int q = neighbour(a, d);
-        if (q >= 0 && (has(mine, q) || has(e, q))) eye = false;
-      }
-      set_bit(mine, a);
+      u32 open = 0;
+      for (int w = 0; w < W; ++w) open |= cand[w] & (mine[w] | e[w]);
+      const bool eye = open == 0u;
+      for (int w = 0; w < W; ++w) { mine[w] |= at[w]; e[w] &= ~at[w]; }
       s.hash ^= zobrist(a, me);
-      clear_bit(e, a);
       int captured = 0, cap_cell = 0;
       // enemy stones next to the new one that have no liberty of their own: only their chains can
       // have been left without liberties (the order of the captures does not matter: the hash is
       // a XOR and the ko point is only set when exactly one stone was taken)
-      u32 at[W], cand[W], ne[W];
-      for (int w = 0; w < W; ++w) at[w] = 0;
-      set_bit(at, a);
-      nb4(at, cand);
       nb4(e, ne);
       for (int w = 0; w < W; ++w) cand[w] &= theirs[w] & ~ne[w];
       while (any(cand)) {
@@ -351,6 +417,7 @@ struct GoT {
   BSG_HD static void init(State& s) {
     for (int w = 0; w < W; ++w) s.st[0][w] = s.st[1][w] = 0;
     s.mv = 0; s.ko = 0; s.moves = 0; s.last_pass = 0; s.two_pass = 0; s.superko = 0;
+    s.replay = 0; s.replay_on = 0;
     s.outc = kOutcomeNone;
     s.hash = 0;
     for (int i = 0; i < kSeenSlots; ++i) s.seen[i] = 0;
@@ -366,6 +433,22 @@ struct GoT {
     init(s);
     for (u32 k = 0; k < moves && k < (u32)kMaxLen; ++k) play(s, h[k]);
   }
+  // The lazy load: an empty board that still has `moves` history moves to replay; what the kernel
+  // needs of the ROOT at once (its mover and outcome) comes from the meta word.
+  BSG_HD static void load_lazy(State& s, const void* base, int64_t n, int64_t i, u32& root_mover, u32& root_outcome) {
+    const u32 meta = ((const u32*)((const char*)base + (int64_t)32 * n))[i];
+    const u32* h = (const u32*)((const char*)base + (int64_t)36 * n + i * kHistBytes);
+    u32 moves = (meta >> 16) & 0xFFu;
+    moves = moves < (u32)kMaxLen ? moves : (u32)kMaxLen;
+    init(s);
+    u32* dst = (u32*)s.acts;
+    for (u32 k = 0; 4u * k < moves; ++k) dst[k] = h[k];
+    s.replay = moves;
+    root_mover = meta & 1u;
+    root_outcome = meta >> 24;
+  }
+  // Called at the start of every group: does this lane spend the group replaying?
+  BSG_HD static u32 group_begin(State& s) { s.replay_on = s.replay ? 1u : 0u; return s.replay_on; }
   BSG_HD static void store(const State& s, void* base, int64_t n, int64_t i) {
     u32* p0 = (u32*)base + i * 4;
     u32* p1 = (u32*)((char*)base + (int64_t)16 * n) + i * 4;
@@ -401,13 +484,22 @@ struct GoT {
     return (int)(cell < (u32)kCells ? cell : 0u);
   }
   BSG_HD static u32 step(State& s, u32 r, const Tables& tab, int& action) {
-    if (terminal(s)) { action = kPass; return 1u; }      // a finished lane leaves at once
-    u32 L[W];
-    legal_points(s, L);
-    const u32 np = (u32)count(L), n = np + 1u;           // go.cc:127-137: the legal points, then the pass
-    const u32 k = fastmod(r, n, tab.modM[n & 127u]);
-    action = k == np ? kPass : select_bit(L, k, tab);
-    play(s, action);
+    // One call of play() serves the lanes that step and the lanes that replay (load_lazy): the
+    // replaying ones sit out the legality search and join the others for the move itself.
+    int a = -1;                                          // -1: nothing to play in this iteration
+    u32 n = 1u;
+    if (s.replay_on) {                                   // a replaying group: one history move
+      if (s.replay) { a = s.acts[s.moves]; --s.replay; }
+    } else if (!terminal(s)) {                           // (a finished lane runs dead iterations)
+      u32 L[W];
+      legal_points(s, L);
+      const u32 np = (u32)count(L);
+      n = np + 1u;                                       // go.cc:127-137: the legal points, then the pass
+      const u32 k = fastmod(r, n, tab.modM[n & 127u]);
+      a = k == np ? kPass : select_bit(L, k, tab);
+    }
+    if (a >= 0) play(s, a);
+    action = a >= 0 ? a : kPass;
     return n;
   }
   BSG_HD static int legal(const State& s, int* out) {

@@ -79,6 +79,10 @@ template <class G> struct min_blocks<G, std::enable_if_t<(G::kMinBlocks > 1)>> :
 template <class G, class = void> struct group_steps : std::integral_constant<int, 4> {};
 template <class G> struct group_steps<G, std::enable_if_t<(G::kGroupSteps > 4)>> : std::integral_constant<int, G::kGroupSteps> {};
 
+// Games whose step is too long to unroll the group (G::kRolledGroup), see the step loop.
+template <class G, class = void> struct rolled_group : std::false_type {};
+template <class G> struct rolled_group<G, std::enable_if_t<G::kRolledGroup>> : std::true_type {};
+
 // Games whose full board is inert (G::kInertWhenFull): a step on a full board places nothing and
 // cannot report a win, so the lean kernel need not test for the draw in every step — a playout
 // that has made as many moves as its root had empty cells is over, which one comparison per
@@ -87,6 +91,19 @@ template <class G, class = void> struct inert_when_full : std::false_type {};
 template <class G> struct inert_when_full<G, std::enable_if_t<G::kInertWhenFull>> : std::true_type {};
 template <class G, bool kOn> struct moves_left_of { BSG_HD static u32 get(const typename G::State&) { return 0xFFFFFFFFu; } };
 template <class G> struct moves_left_of<G, true> { BSG_HD static u32 get(const typename G::State& s) { return G::moves_left(s); } };
+
+// Games whose packed state must be replayed to be loaded (G::kReplayLoad, G::load_lazy,
+// G::group_begin): the lean kernel spreads the replay over the step loop.
+template <class G, class = void> struct replay_load : std::false_type {};
+template <class G> struct replay_load<G, std::enable_if_t<G::kReplayLoad>> : std::true_type {};
+template <class G, bool kOn> struct replay_ops {
+  BSG_HD static void load(typename G::State&, const void*, int64_t, int64_t, u32&, u32&) {}
+  BSG_HD static u32 group_begin(typename G::State&) { return 0u; }
+};
+template <class G> struct replay_ops<G, true> {
+  BSG_HD static void load(typename G::State& s, const void* b, int64_t n, int64_t i, u32& mv, u32& oc) { G::load_lazy(s, b, n, i, mv, oc); }
+  BSG_HD static u32 group_begin(typename G::State& s) { return G::group_begin(s); }
+};
 
 // Games with a compact root format for host -> device transfers (G::kCompactBytes, G::load_compact).
 template <class G, class = void> struct compact_bytes : std::integral_constant<int, 0> {};
@@ -170,6 +187,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
   u32 live = 0, have = 0, fin_term = 0, fin_win = 0, fin_lose = 0;
   u32 lid = 0, t = 0, limit = 0xFFFFFFFFu, root_mv = 0;
   constexpr bool kLazyDraw = inert_when_full<G>::value && !kFull && !kFill && !kAsync;
+  constexpr bool kReplay = replay_load<G>::value && !kFull && !kFill && !kAsync;   // see replay_load
   u32 left0 = 0xFFFFFFFFu;   // kLazyDraw: empty cells of the root = the most moves the playout can make
   unsigned long long pid0 = a.first_playout;   // playout id = pid0 + lid (per root with root_playout_base)
   u32 my_steps = 0, my_done = 0, my_stuck = 0;
@@ -248,7 +266,10 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         if (kStage && stage) G::load(s, root_sm[threadIdx.x >> 5][buf], kChunkPlayouts, idx);
         else if ((compact_bytes<G>::value > 0) && a.compact)
           compact_ops<G, (compact_bytes<G>::value > 0)>::load(s, a.roots, a.root0 + root);
+        else if constexpr (kReplay) {}
         else G::load(s, a.roots, a.n_roots, a.root0 + root);
+        u32 lazy_mv = 0, lazy_oc = kOutcomeNone;
+        if constexpr (kReplay) replay_ops<G, kReplay>::load(s, a.roots, a.n_roots, a.root0 + root, lazy_mv, lazy_oc);
         bool skip = false;
         if (kBase) {
           const unsigned long long rb = a.io.root_playout_base[a.root0 + root];
@@ -257,18 +278,24 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         }
         t = 0;
         nblk = 0xFFFFFFFFu;
-        root_mv = (u32)G::mover(s);
+        root_mv = kReplay ? lazy_mv : (u32)G::mover(s);
         if constexpr (kLazyDraw) left0 = moves_left_of<G, kLazyDraw>::get(s);
         if (kFull) {
           limit = a.io.max_steps > 0 ? (u32)a.io.max_steps : 0xFFFFFFFFu;
           if (a.io.step_limit) limit = min(limit, (u32)a.io.step_limit[lid]);
           prev = s;
         }
-        const bool term = (kFill ? fill_ops<G, kFill>::done(s) : G::terminal(s)) || (kBase && skip);
+        const bool term = (kReplay ? lazy_oc != (u32)kOutcomeNone
+                                   : (kFill ? fill_ops<G, kFill>::done(s) : G::terminal(s))) || (kBase && skip);
         live = (!term && (!kFull || limit > 0)) ? 1u : 0u;
         fin_term = (kFull && !term) ? 0u : 1u;   // a lean playout always runs to a terminal state
-        fin_win = G::won(s) ? 1u : 0u;
-        if constexpr (G::kMoverCanLose) fin_lose = G::lost(s) ? 1u : 0u;
+        if constexpr (kReplay) {                 // the ROOT's result, from its meta word
+          fin_win = lazy_oc == (lazy_mv ^ 1u) ? 1u : 0u;
+          if constexpr (G::kMoverCanLose) fin_lose = lazy_oc == lazy_mv ? 1u : 0u;
+        } else {
+          fin_win = G::won(s) ? 1u : 0u;
+          if constexpr (G::kMoverCanLose) fin_lose = G::lost(s) ? 1u : 0u;
+        }
         if (kBase && skip) { fin_win = 0; fin_lose = 0; }   // a skipped slot holds no state
         if constexpr (G::kCanStick) {
           // non-terminal root without a legal action: only a root can be (see the game's note)
@@ -288,6 +315,10 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
     u32 rr[4];
     constexpr int kSteps = (kFull || kAsync || kFill) ? 4 : group_steps<G>::value;
     const u32 live_in = live;   // (kLazyDraw) lanes that play in this group
+    // kReplay: a lane that still replays its root's history spends the WHOLE group on it (one
+    // history move per iteration, idle once it runs out), so t stays 0 until a group boundary
+    u32 replaying = 0;
+    if constexpr (kReplay) replaying = replay_ops<G, kReplay>::group_begin(s);
     static_assert(kSteps % 4 == 0, "a group is a whole number of Philox blocks");
     if constexpr (!kAsync) {
       philox4x32_10((u32)pid, (u32)(pid >> 32), t >> 2, 0u, a.keys, rr);
@@ -315,10 +346,20 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
       philox4x32_10((u32)pid, (u32)(pid >> 32), nblk, 0u, a.keys, rnew);
 #endif
     }
-#pragma unroll
+    // Games with a long step (G::kRolledGroup: go, whose step is ~1300 instructions) keep the
+    // group as a real loop: four unrolled copies do not fit the instruction cache, and a warp
+    // whose lanes diverge inside a step then waits for instruction fetches most of the time
+    // (ncu: "no instruction" was the top stall, 6.9 warps per issue).
+    constexpr int kUnroll = rolled_group<G>::value ? 1 : kSteps;
+#pragma unroll (kUnroll)
     for (int j = 0; j < kSteps; ++j) {
       u32 r, can = live;   // can: this lane makes a move in this iteration
-      if constexpr (!kAsync) {
+      if constexpr (kReplay) can = live & (replaying ^ 1u);
+      if constexpr (!kAsync && rolled_group<G>::value) {
+        if (kSteps > 4 && j > 0 && (j & 3) == 0) philox4x32_10((u32)pid, (u32)(pid >> 32), t >> 2, 0u, a.keys, rr);
+        const u32 lo2 = (j & 1) ? rr[1] : rr[0], hi2 = (j & 1) ? rr[3] : rr[2];   // no run-time register index
+        r = (j & 2) ? hi2 : lo2;
+      } else if constexpr (!kAsync) {
         // a live lane entered the group with t = 0 (mod kSteps) and has moved j times since:
         // its next block is t >> 2 (a finished lane's t is frozen: it draws garbage for its dead steps)
         if (kSteps > 4 && j > 0 && (j & 3) == 0) philox4x32_10((u32)pid, (u32)(pid >> 32), t >> 2, 0u, a.keys, rr);
