@@ -21,6 +21,12 @@
 // Semantics follow the reference rules cited per function; the representation does not.
 #pragma once
 #include "bsg_common.cuh"
+#ifndef BSG_Y_ROLLED
+#define BSG_Y_ROLLED 1
+#endif
+#ifndef BSG_OTHELLO_ROLLED
+#define BSG_OTHELLO_ROLLED 0
+#endif
 
 namespace bsg {
 
@@ -1047,6 +1053,7 @@ typedef HexT<11> Hex;
 // =========================================================================================
 struct Othello {
   static constexpr int kId = kGameOthello;
+  static constexpr bool kRolledGroup = BSG_OTHELLO_ROLLED;   // playout kernel: step group not unrolled (A/B)
   static constexpr int kNumActions = 65, kMaxLen = 64, kMaxDepth = 120, kObsSize = 192, kStateBytes = 20;
   static constexpr int kObsWords = 6, kMaskWords = 3;
   static constexpr int kPlanes = 2;
@@ -1504,6 +1511,7 @@ struct Pentago {
 template <int N>
 struct YT {
   static constexpr int kId = kGameY;
+  static constexpr bool kRolledGroup = BSG_Y_ROLLED;   // playout kernel: step group not unrolled (A/B)
   static constexpr int kGrid = N * N;
   static constexpr int kCells = N * (N + 1) / 2;
   static constexpr int kBits = N * (N - 1) + 1;          // highest on-board cell index + 1

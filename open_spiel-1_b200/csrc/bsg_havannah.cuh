@@ -27,12 +27,16 @@
 //   mover | outcome << 1 | (last move + 1) << 8.
 #pragma once
 #include "bsg_common.cuh"
+#ifndef BSG_HV_ROLLED
+#define BSG_HV_ROLLED 0
+#endif
 
 namespace bsg {
 
 template <int S>
 struct HavannahT {
   static constexpr int kId = kGameHavannah;
+  static constexpr bool kRolledGroup = BSG_HV_ROLLED;   // playout kernel: step group not unrolled (A/B)
   static constexpr int D = 2 * S - 1;
   static constexpr int kGrid = D * D;
   static constexpr int kCells = D * D - S * (S - 1);     // havannah.cc:166-168
@@ -198,6 +202,79 @@ struct HavannahT {
   BSG_HD static int mover(const State& s) { return (int)s.mv; }
   BSG_HD static int outcome(const State& s) { return (int)s.outc; }
 
+  // Board cells of word w with a neighbour off the board (compile time).
+  BSG_HDC static u32 rim_mask(int w) {
+    u32 m = 0;
+    for (int b = 0; b < 32; ++b) {
+      const int cell = 32 * w + b;
+      if (cell >= kGrid) break;
+      const int x = cell % D, y = cell / D;
+      if (!on_board(x, y)) continue;
+      const bool inner = on_board(x - 1, y - 1) && on_board(x, y - 1) && on_board(x + 1, y) &&
+                         on_board(x + 1, y + 1) && on_board(x, y + 1) && on_board(x - 1, y);
+      if (!inner) m |= 1u << b;
+    }
+    return m;
+  }
+  BSG_HD static u32 rim_word(int w) {
+    constexpr u32 m[8] = {rim_mask(0), rim_mask(1), rim_mask(2), rim_mask(3),
+                          rim_mask(4), rim_mask(5), rim_mask(6), rim_mask(7)};
+    return m[w];
+  }
+  // The six neighbours of every cell of a set of board cells, as shifts of the x + y * D grid by
+  // 1, D and D + 1.  A shift that leaves a row lands off the board (the board is a hexagon in
+  // the grid: (D - 1, y) on the board means (0, y + 1) and (0, y + 2) are not, and the same at
+  // the other end), so the board mask is all the clipping there is.
+  BSG_HD static void nb6(const u32* f, u32* out) {
+    u32 a[W], b[W], c[W], d[W], e[W], g[W];
+    shl_words<1, W>(f, a);
+    shr_words<1, W>(f, b);
+    shl_words<D, W>(f, c);
+    shr_words<D, W>(f, d);
+    shl_words<D + 1, W>(f, e);
+    shr_words<D + 1, W>(f, g);
+    for (int w = 0; w < W; ++w) out[w] = (a[w] | b[w] | c[w] | d[w] | e[w] | g[w]) & board_word(w);
+  }
+  // Can `mine` hold a ring at all?  The reference's search (below) finds a closed walk that turns
+  // by at most 60 degrees per step except where it closes; a closed walk on the triangular
+  // lattice with at most one sharper corner has a lattice point inside it (the walks without one
+  // are width-one strips and the side-two triangle: two or three sharp corners).  That cell is
+  // either not the mover's — then it cannot reach the rim through cells that are not the
+  // mover's — or every cell inside is the mover's and one of them has six neighbours of the
+  // mover's.  Both tests are set arithmetic in registers; the search, a backtracking walk over
+  // local-memory stacks, runs only when one of them says a ring is possible.
+  BSG_HD static bool ring_possible(const u32* mine_in) {
+    u32 mine[W], t0[W], t1[W];
+#pragma unroll
+    for (int w = 0; w < W; ++w) mine[w] = mine_in[w];
+    u32 solid = 0;
+    {
+      u32 a[W], b[W], c[W], d[W], e[W], g[W];
+      shl_words<1, W>(mine, a);
+      shr_words<1, W>(mine, b);
+      shl_words<D, W>(mine, c);
+      shr_words<D, W>(mine, d);
+      shl_words<D + 1, W>(mine, e);
+      shr_words<D + 1, W>(mine, g);
+      for (int w = 0; w < W; ++w) solid |= mine[w] & a[w] & b[w] & c[w] & d[w] & e[w] & g[w];
+    }
+    if (solid) return true;
+    for (int w = 0; w < W; ++w) t0[w] = rim_word(w) & ~mine[w];
+    for (;;) {
+      nb6(t0, t1);
+      u32 grew = 0;
+      for (int w = 0; w < W; ++w) {
+        const u32 n = (t0[w] | t1[w]) & ~mine[w];
+        grew |= n ^ t0[w];
+        t0[w] = n;
+      }
+      if (!grew) break;
+    }
+    u32 enclosed = 0;
+    for (int w = 0; w < W; ++w) enclosed |= board_word(w) & ~mine[w] & ~t0[w];
+    return enclosed != 0u;
+  }
+
   // CheckRingDFS(move, 0, 3) (havannah.cc:385-399) as a loop over the recursion's frames
   // (cell, next direction to try, last direction).  A frame is entered on an unmarked stone of
   // `mine`; meeting a marked one — a cell of the current path — is a ring.
@@ -248,7 +325,7 @@ struct HavannahT {
       }
     }
     const u32 g = s.ec[find(s, c)];
-    const bool win = popc32(g >> 6) >= 3 || popc32(g & 63u) >= 2 || (already && ring_from(s.st[me], c, t));
+    const bool win = popc32(g >> 6) >= 3 || popc32(g & 63u) >= 2 || (already && ring_possible(s.st[me]) && ring_from(s.st[me], c, t));
     if (win) s.outc = me;
     else if (s.left == 0) s.outc = (u32)kOutcomeDraw;
     s.mv = me ^ 1u;
