@@ -63,6 +63,7 @@ struct GoT {
   static constexpr bool kAsync = false;
   static constexpr bool kMoverCanLose = true;   // the winner is decided by counting
   static constexpr bool kLazyEnd = false;
+  static constexpr bool kLocalHeavy = true;   // playout kernel: L1 over shared memory (the state is local memory)
   static constexpr bool kRolledGroup = BSG_GO_ROLLED;   // the step loop of the playout kernel is not unrolled
   static constexpr int kMinBlocks = BSG_GO_MINBLOCKS;   // lean kernel: resident blocks per SM asked of the compiler
   struct State {

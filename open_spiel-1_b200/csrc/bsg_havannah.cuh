@@ -28,7 +28,7 @@
 #pragma once
 #include "bsg_common.cuh"
 #ifndef BSG_HV_ROLLED
-#define BSG_HV_ROLLED 0
+#define BSG_HV_ROLLED 1
 #endif
 
 namespace bsg {
@@ -36,6 +36,7 @@ namespace bsg {
 template <int S>
 struct HavannahT {
   static constexpr int kId = kGameHavannah;
+  static constexpr bool kLocalHeavy = true;   // playout kernel: L1 over shared memory (the state is local memory)
   static constexpr bool kRolledGroup = BSG_HV_ROLLED;   // playout kernel: step group not unrolled (A/B)
   static constexpr int D = 2 * S - 1;
   static constexpr int kGrid = D * D;
@@ -54,8 +55,8 @@ struct HavannahT {
   static constexpr bool kLazyEnd = false;
   struct State {
     u32 st[2][W];                    // stones of player 0 / player 1
-    unsigned char parent[kGrid];     // union-find over the cells (havannah.h:96-131)
-    unsigned short ec[kGrid];        // at a leader: corners (bits 0..5) | edges (bits 6..11) of its group
+    __align__(4) unsigned char parent[(kGrid + 3) / 4 * 4];   // union-find over the cells (havannah.h:96-131)
+    __align__(4) unsigned short ec[(kGrid + 1) / 2 * 2];      // at a leader: corners (bits 0..5) | edges (bits 6..11) of its group
     u32 left;                        // empty cells
     u32 mv;                          // player to move
     u32 outc;                        // kOutcomeNone / kOutcomeP0 / kOutcomeP1 / kOutcomeDraw
@@ -151,30 +152,46 @@ struct HavannahT {
     return false;
   }
 
-  BSG_HD static void reset_groups(State& s) {            // every cell its own group (havannah.cc:170-176)
-    for (int c = 0; c < kGrid; ++c) {
-      const int x = c % D, y = c / D;
-      s.parent[c] = (unsigned char)c;
-      s.ec[c] = on_board(x, y) ? (unsigned short)(corner_of(x, y) | (edge_of(x, y) << 6)) : (unsigned short)0;
+  // Corner and edge bits of every cell, two cells to a word (compile time; read through the
+  // constant bank).  A group starts as one cell (havannah.cc:170-176).
+  struct Ec0 {
+    u32 v[(kGrid + 1) / 2];
+    constexpr Ec0() : v() {
+      for (int c = 0; c < kGrid; ++c) {
+        const int x = c % D, y = c / D;
+        const u32 e = on_board(x, y) ? (u32)(corner_of(x, y) | (edge_of(x, y) << 6)) : 0u;
+        v[c >> 1] |= e << (16 * (c & 1));
+      }
     }
+  };
+  BSG_HD static void reset_groups(State& s) {            // every cell its own group
+    constexpr Ec0 ec0;
+    u32* par = (u32*)s.parent;
+    for (int k = 0; k < (kGrid + 3) / 4; ++k) par[k] = 0x03020100u + 0x04040404u * (u32)k;
+    u32* ec = (u32*)s.ec;
+    for (int k = 0; k < (kGrid + 1) / 2; ++k) ec[k] = ec0.v[k];
   }
   BSG_HD static void init(State& s) {
     for (int w = 0; w < W; ++w) s.st[0][w] = s.st[1][w] = 0;
     reset_groups(s);
     s.left = kCells; s.mv = 0; s.outc = kOutcomeNone; s.last = 0;
   }
-  // Groups from the stones: every stone joins its three lower-index neighbours of its colour.
+  // Groups from the stones: every stone joins its three lower-index neighbours of its colour
+  // (directions 5, 1, 0: cells c - 1, c - D, c - D - 1; a subtraction that leaves the row lands
+  // off the board, where no stone is — see nb6).
   BSG_HD static void rebuild_groups(State& s) {
     reset_groups(s);
-    for (int c = 0; c < kGrid; ++c) {
-      const int p = has(s.st[0], c) ? 0 : (has(s.st[1], c) ? 1 : -1);
-      if (p < 0) continue;
-      const int lower[3] = {0, 1, 5};
-      for (int k = 0; k < 3; ++k) {
-        const int m = neighbour(c, lower[k]);
-        if (m >= 0 && has(s.st[p], m)) join(s, c, m);
+    for (int p = 0; p < 2; ++p)
+      for (int w = 0; w < W; ++w) {
+        u32 m = s.st[p][w];
+        while (m) {
+          const int c = 32 * w + ctz32(m);
+          m &= m - 1u;
+          const int lower[3] = {c - 1, c - D, c - D - 1};
+          for (int k = 0; k < 3; ++k)
+            if (lower[k] >= 0 && has(s.st[p], lower[k])) join(s, c, lower[k]);
+        }
       }
-    }
   }
   BSG_HD static void load(State& s, const void* base, int64_t n, int64_t i) {
     const u32* p0 = (const u32*)base + i * PW;

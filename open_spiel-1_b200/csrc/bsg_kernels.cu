@@ -79,6 +79,13 @@ template <class G> struct min_blocks<G, std::enable_if_t<(G::kMinBlocks > 1)>> :
 template <class G, class = void> struct group_steps : std::integral_constant<int, 4> {};
 template <class G> struct group_steps<G, std::enable_if_t<(G::kGroupSteps > 4)>> : std::integral_constant<int, G::kGroupSteps> {};
 
+// Games whose per-lane state is mostly local memory (G::kLocalHeavy), see PlayoutOp.
+template <class G, class = void> struct local_heavy : std::false_type {};
+template <class G> struct local_heavy<G, std::enable_if_t<G::kLocalHeavy>> : std::true_type {};
+#ifndef BSG_LOCAL_CARVEOUT
+#define BSG_LOCAL_CARVEOUT 15
+#endif
+
 // Games whose step is too long to unroll the group (G::kRolledGroup), see the step loop.
 template <class G, class = void> struct rolled_group : std::false_type {};
 template <class G> struct rolled_group<G, std::enable_if_t<G::kRolledGroup>> : std::true_type {};
@@ -1063,9 +1070,11 @@ int launch_playouts(bsg_engine* e, const PlayoutArgs& a, cudaStream_t st) {
     int& slot = per_device[e->device % kMaxDevices];
     if (slot == 0) {
       int b = 0;
-      // all of the L1/shared array as shared memory: the tables of every resident CTA must fit
+      // all of the L1/shared array as shared memory: the tables of every resident CTA must fit.
+      // Games whose state lives in local memory (G::kLocalHeavy: havannah, go) have small tables
+      // and want the array as L1 instead (BSG_LOCAL_CARVEOUT per cent of it stay shared memory).
       BSG_CUDA(e, cudaFuncSetAttribute(playout_kernel<G, kFull, kBase, kFill, kLog>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                       cudaSharedmemCarveoutMaxShared));
+                                       local_heavy<G>::value ? BSG_LOCAL_CARVEOUT : (int)cudaSharedmemCarveoutMaxShared));
       BSG_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, playout_kernel<G, kFull, kBase, kFill, kLog>, kThreads, 0));
       slot = b > 0 ? b : 1;
     }
