@@ -144,11 +144,13 @@ struct HavannahT {
     return c;
   }
   // havannah.cc:364-383; true when the two cells were in one group already
+  // (a's group goes under b's leader: a cell that joins an existing group points straight at
+  // its leader, so the trees stay flat and find() is one or two hops)
   BSG_HD static bool join(State& s, int a, int b) {
     const int la = find(s, a), lb = find(s, b);
     if (la == lb) return true;
-    s.parent[lb] = (unsigned char)la;
-    s.ec[la] = (unsigned short)(s.ec[la] | s.ec[lb]);
+    s.parent[la] = (unsigned char)lb;
+    s.ec[lb] = (unsigned short)(s.ec[lb] | s.ec[la]);
     return false;
   }
 
@@ -333,15 +335,24 @@ struct HavannahT {
     s.left -= 1u;
     s.last = (u32)c + 1u;
     bool already = false, skip = false;
+    // c is a fresh one-cell group: it goes under the leader L of the first friendly neighbour, the
+    // leaders of further neighbours go under L too, and the group's corner / edge bits are
+    // gathered in a register and written once.  `already`: a neighbour that is in c's group
+    // before it is joined (havannah.cc:364-383 returns that).
+    int L = -1;
+    u32 g = s.ec[c];
     for (int d = 0; d < 6; ++d) {
       if (skip) { skip = false; continue; }
       const int m = t.nb[c][d];
       if (m != kOff && has(s.st[me], m)) {
-        already |= join(s, c, m);
+        const int lb = find(s, m);
+        if (L < 0) { L = lb; s.parent[c] = (unsigned char)lb; g |= s.ec[lb]; }
+        else if (lb == L) already = true;
+        else { s.parent[lb] = (unsigned char)L; g |= s.ec[lb]; }
         skip = true;     // the next neighbour touches this one: same group or a sharp corner
       }
     }
-    const u32 g = s.ec[find(s, c)];
+    if (L >= 0) s.ec[L] = (unsigned short)g;
     const bool win = popc32(g >> 6) >= 3 || popc32(g & 63u) >= 2 || (already && ring_possible(s.st[me]) && ring_from(s.st[me], c, t));
     if (win) s.outc = me;
     else if (s.left == 0) s.outc = (u32)kOutcomeDraw;
