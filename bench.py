@@ -51,9 +51,9 @@ OPS_PER_STEP = {"tic_tac_toe": 48, "connect_four": 96, "breakthrough": 140, "hex
                 # + link), win test 10, amortised ring search 20, loop 4
                 "havannah": 202,
                 # go 9 x 9 (3-word sets): legal points 3 dilations 60 + ~1 chain flood 90, popc 3, rng 25, mod 4,
-                # rank-select 25, place 6, four neighbour chains (flood + liberties) 4 x 60, hash + superko scan
-                # ~80 compares 160, loop 4
-                "go(board_size=9)": 617}
+                # rank-select 25, place 6, four neighbour chains (flood + liberties) 4 x 60, hash 30 + probe of
+                # the position set 10, loop 4
+                "go(board_size=9)": 497}
 ROOT_SEED = 20240611
 METRIC = "connect_four game-steps/s (uniform-random playouts from mid-game roots)"
 
@@ -833,7 +833,7 @@ def side_numbers(args, eng, torch, dev, rank, world, reduce_max_sum):
     except Exception as ex:
       out["trajectory_actor"] = {"error": repr(ex)}
     for g, npl in (("tic_tac_toe", 1 << 24), ("breakthrough", 1 << 22), ("hex", 1 << 20),
-                   ("pentago", 1 << 22), ("othello", 1 << 21), ("y", 1 << 21), ("havannah", 1 << 20), ("go(board_size=9)", 1 << 18)):
+                   ("pentago", 1 << 22), ("othello", 1 << 21), ("y", 1 << 21), ("havannah", 1 << 20), ("go(board_size=9)", 1 << 20)):
       e_g = bsg.Engine(g, eng.device)
       dmin, dmax = ROOT_DEPTHS[g]
       st, _ = make_roots(e_g, npl, dmin, dmax, seed=ROOT_SEED + 4 + 1000 * rank)

@@ -178,22 +178,46 @@ struct HavannahT {
     reset_groups(s);
     s.left = kCells; s.mv = 0; s.outc = kOutcomeNone; s.last = 0;
   }
-  // Groups from the stones: every stone joins its three lower-index neighbours of its colour
-  // (directions 5, 1, 0: cells c - 1, c - D, c - D - 1; a subtraction that leaves the row lands
-  // off the board, where no stone is — see nb6).
+  // Cell c, fresh (L < 0) or already under the leader L, meets its friendly neighbour m.
+  BSG_HD static int attach(State& s, int c, int m, int L) {
+    const int lb = find(s, m);
+    if (L < 0) {
+      s.parent[c] = (unsigned char)lb;
+      s.ec[lb] = (unsigned short)(s.ec[lb] | s.ec[c]);
+      return lb;
+    }
+    if (lb != L) {
+      s.parent[lb] = (unsigned char)L;
+      s.ec[L] = (unsigned short)(s.ec[L] | s.ec[lb]);
+    }
+    return L;
+  }
+  // Groups from the stones: in ascending order every stone meets its lower-index neighbours of
+  // its colour (directions 5, 1, 0: cells c - 1, c - D, c - D - 1; a subtraction that leaves the
+  // row lands off the board, where no stone is — see nb6).  c - D - 1 touches the other two, so
+  // when it is there it is the only one to meet.  Which neighbours are there is read off three
+  // shifted copies of the stones in registers.
   BSG_HD static void rebuild_groups(State& s) {
     reset_groups(s);
-    for (int p = 0; p < 2; ++p)
+    for (int p = 0; p < 2; ++p) {
+      u32 st[W], f1[W], fd[W], fd1[W];
+      for (int w = 0; w < W; ++w) st[w] = s.st[p][w];
+      shl_words<1, W>(st, f1);
+      shl_words<D, W>(st, fd);
+      shl_words<D + 1, W>(st, fd1);
       for (int w = 0; w < W; ++w) {
-        u32 m = s.st[p][w];
+        u32 m = st[w];
         while (m) {
-          const int c = 32 * w + ctz32(m);
+          const int bit = ctz32(m);
+          const int c = 32 * w + bit;
           m &= m - 1u;
-          const int lower[3] = {c - 1, c - D, c - D - 1};
-          for (int k = 0; k < 3; ++k)
-            if (lower[k] >= 0 && has(s.st[p], lower[k])) join(s, c, lower[k]);
+          if ((fd1[w] >> bit) & 1u) { attach(s, c, c - D - 1, -1); continue; }
+          int L = -1;
+          if ((f1[w] >> bit) & 1u) L = attach(s, c, c - 1, L);
+          if ((fd[w] >> bit) & 1u) L = attach(s, c, c - D, L);
         }
       }
+    }
   }
   BSG_HD static void load(State& s, const void* base, int64_t n, int64_t i) {
     const u32* p0 = (const u32*)base + i * PW;
