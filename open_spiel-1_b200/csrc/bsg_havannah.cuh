@@ -27,6 +27,9 @@
 //   mover | outcome << 1 | (last move + 1) << 8.
 #pragma once
 #include "bsg_common.cuh"
+#ifndef BSG_HV_MINBLOCKS
+#define BSG_HV_MINBLOCKS 4
+#endif
 #ifndef BSG_HV_ROLLED
 #define BSG_HV_ROLLED 1
 #endif
@@ -37,6 +40,7 @@ template <int S>
 struct HavannahT {
   static constexpr int kId = kGameHavannah;
   static constexpr bool kLocalHeavy = true;   // playout kernel: L1 over shared memory (the state is local memory)
+  static constexpr int kMinBlocks = BSG_HV_MINBLOCKS;   // lean kernel: resident blocks per SM asked of the compiler
   static constexpr bool kRolledGroup = BSG_HV_ROLLED;   // playout kernel: step group not unrolled (A/B)
   static constexpr int D = 2 * S - 1;
   static constexpr int kGrid = D * D;
@@ -58,6 +62,7 @@ struct HavannahT {
     __align__(4) unsigned char parent[(kGrid + 3) / 4 * 4];   // union-find over the cells (havannah.h:96-131)
     __align__(4) unsigned short ec[(kGrid + 1) / 2 * 2];      // at a leader: corners (bits 0..5) | edges (bits 6..11) of its group
     u32 left;                        // empty cells
+    u32 comps;                       // groups of player 0 | groups of player 1 << 16 (for ring_possible)
     u32 mv;                          // player to move
     u32 outc;                        // kOutcomeNone / kOutcomeP0 / kOutcomeP1 / kOutcomeDraw
     u32 last;                        // last move + 1 (0: none)
@@ -176,11 +181,12 @@ struct HavannahT {
   BSG_HD static void init(State& s) {
     for (int w = 0; w < W; ++w) s.st[0][w] = s.st[1][w] = 0;
     reset_groups(s);
-    s.left = kCells; s.mv = 0; s.outc = kOutcomeNone; s.last = 0;
+    s.left = kCells; s.mv = 0; s.outc = kOutcomeNone; s.last = 0; s.comps = 0;
   }
   // Cell c, fresh (L < 0) or already under the leader L, meets its friendly neighbour m.
-  BSG_HD static int attach(State& s, int c, int m, int L) {
+  BSG_HD static int attach(State& s, int c, int m, int L, u32& merges) {
     const int lb = find(s, m);
+    merges += (L < 0 || lb != L) ? 1u : 0u;
     if (L < 0) {
       s.parent[c] = (unsigned char)lb;
       s.ec[lb] = (unsigned short)(s.ec[lb] | s.ec[c]);
@@ -199,7 +205,9 @@ struct HavannahT {
   // shifted copies of the stones in registers.
   BSG_HD static void rebuild_groups(State& s) {
     reset_groups(s);
+    s.comps = 0;
     for (int p = 0; p < 2; ++p) {
+      u32 merges = 0, stones = 0;
       u32 st[W], f1[W], fd[W], fd1[W];
       for (int w = 0; w < W; ++w) st[w] = s.st[p][w];
       shl_words<1, W>(st, f1);
@@ -211,12 +219,14 @@ struct HavannahT {
           const int bit = ctz32(m);
           const int c = 32 * w + bit;
           m &= m - 1u;
-          if ((fd1[w] >> bit) & 1u) { attach(s, c, c - D - 1, -1); continue; }
+          stones += 1u;
+          if ((fd1[w] >> bit) & 1u) { attach(s, c, c - D - 1, -1, merges); continue; }
           int L = -1;
-          if ((f1[w] >> bit) & 1u) L = attach(s, c, c - 1, L);
-          if ((fd[w] >> bit) & 1u) L = attach(s, c, c - D, L);
+          if ((f1[w] >> bit) & 1u) L = attach(s, c, c - 1, L, merges);
+          if ((fd[w] >> bit) & 1u) L = attach(s, c, c - D, L, merges);
         }
       }
+      s.comps |= (stones - merges) << (16 * p);
     }
   }
   BSG_HD static void load(State& s, const void* base, int64_t n, int64_t i) {
@@ -245,25 +255,6 @@ struct HavannahT {
   BSG_HD static int mover(const State& s) { return (int)s.mv; }
   BSG_HD static int outcome(const State& s) { return (int)s.outc; }
 
-  // Board cells of word w with a neighbour off the board (compile time).
-  BSG_HDC static u32 rim_mask(int w) {
-    u32 m = 0;
-    for (int b = 0; b < 32; ++b) {
-      const int cell = 32 * w + b;
-      if (cell >= kGrid) break;
-      const int x = cell % D, y = cell / D;
-      if (!on_board(x, y)) continue;
-      const bool inner = on_board(x - 1, y - 1) && on_board(x, y - 1) && on_board(x + 1, y) &&
-                         on_board(x + 1, y + 1) && on_board(x, y + 1) && on_board(x - 1, y);
-      if (!inner) m |= 1u << b;
-    }
-    return m;
-  }
-  BSG_HD static u32 rim_word(int w) {
-    constexpr u32 m[8] = {rim_mask(0), rim_mask(1), rim_mask(2), rim_mask(3),
-                          rim_mask(4), rim_mask(5), rim_mask(6), rim_mask(7)};
-    return m[w];
-  }
   // The six neighbours of every cell of a set of board cells, as shifts of the x + y * D grid by
   // 1, D and D + 1.  A shift that leaves a row lands off the board (the board is a hexagon in
   // the grid: (D - 1, y) on the board means (0, y + 1) and (0, y + 2) are not, and the same at
@@ -282,40 +273,41 @@ struct HavannahT {
   // by at most 60 degrees per step except where it closes; a closed walk on the triangular
   // lattice with at most one sharper corner has a lattice point inside it (the walks without one
   // are width-one strips and the side-two triangle: two or three sharp corners).  That cell is
-  // either not the mover's — then it cannot reach the rim through cells that are not the
-  // mover's — or every cell inside is the mover's and one of them has six neighbours of the
-  // mover's.  Both tests are set arithmetic in registers; the search, a backtracking walk over
-  // local-memory stacks, runs only when one of them says a ring is possible.
-  BSG_HD static bool ring_possible(const u32* mine_in) {
-    u32 mine[W], t0[W], t1[W];
+  // either not the mover's — then the mover's stones have a HOLE — or every cell inside is the
+  // mover's and one of them has six neighbours of the mover's.  Holes are counted without a
+  // search: the stones with their adjacencies and their filled triangles are a complex in the
+  // plane with Euler characteristic V - E + F = groups - holes, the groups are counted as they
+  // merge (State::comps), and V, E, F are popcounts of the set and-ed with shifted copies of
+  // itself.  All of it is set arithmetic in registers; the search, a backtracking walk over
+  // local-memory stacks, runs only when a ring is possible.
+  BSG_HD static bool ring_possible(const u32* mine_in, u32 groups) {
+    // (one shifted copy at a time besides the c - D - 1 one: few live registers)
+    u32 mine[W], e[W], sol[W], t[W];
 #pragma unroll
     for (int w = 0; w < W; ++w) mine[w] = mine_in[w];
+    int chi = 0;
+    shl_words<D + 1, W>(mine, e);      // the stone at c - D - 1 (touches the next two)
+    for (int w = 0; w < W; ++w) { sol[w] = mine[w] & e[w]; chi += popc32(mine[w]) - popc32(sol[w]); }
+    shl_words<1, W>(mine, t);          // c - 1
+    for (int w = 0; w < W; ++w) {
+      const u32 m = mine[w] & t[w];
+      chi += popc32(m & e[w]) - popc32(m);
+      sol[w] &= t[w];
+    }
+    shl_words<D, W>(mine, t);          // c - D
+    for (int w = 0; w < W; ++w) {
+      const u32 m = mine[w] & t[w];
+      chi += popc32(m & e[w]) - popc32(m);
+      sol[w] &= t[w];
+    }
+    shr_words<1, W>(mine, t);
+    for (int w = 0; w < W; ++w) sol[w] &= t[w];
+    shr_words<D, W>(mine, t);
+    for (int w = 0; w < W; ++w) sol[w] &= t[w];
+    shr_words<D + 1, W>(mine, t);
     u32 solid = 0;
-    {
-      u32 a[W], b[W], c[W], d[W], e[W], g[W];
-      shl_words<1, W>(mine, a);
-      shr_words<1, W>(mine, b);
-      shl_words<D, W>(mine, c);
-      shr_words<D, W>(mine, d);
-      shl_words<D + 1, W>(mine, e);
-      shr_words<D + 1, W>(mine, g);
-      for (int w = 0; w < W; ++w) solid |= mine[w] & a[w] & b[w] & c[w] & d[w] & e[w] & g[w];
-    }
-    if (solid) return true;
-    for (int w = 0; w < W; ++w) t0[w] = rim_word(w) & ~mine[w];
-    for (;;) {
-      nb6(t0, t1);
-      u32 grew = 0;
-      for (int w = 0; w < W; ++w) {
-        const u32 n = (t0[w] | t1[w]) & ~mine[w];
-        grew |= n ^ t0[w];
-        t0[w] = n;
-      }
-      if (!grew) break;
-    }
-    u32 enclosed = 0;
-    for (int w = 0; w < W; ++w) enclosed |= board_word(w) & ~mine[w] & ~t0[w];
-    return enclosed != 0u;
+    for (int w = 0; w < W; ++w) solid |= sol[w] & t[w];
+    return solid != 0u || (int)groups - chi > 0;
   }
 
   // CheckRingDFS(move, 0, 3) (havannah.cc:385-399) as a loop over the recursion's frames
@@ -364,20 +356,23 @@ struct HavannahT {
     // gathered in a register and written once.  `already`: a neighbour that is in c's group
     // before it is joined (havannah.cc:364-383 returns that).
     int L = -1;
-    u32 g = s.ec[c];
+    u32 g = s.ec[c], merges = 0;
     for (int d = 0; d < 6; ++d) {
       if (skip) { skip = false; continue; }
       const int m = t.nb[c][d];
       if (m != kOff && has(s.st[me], m)) {
         const int lb = find(s, m);
-        if (L < 0) { L = lb; s.parent[c] = (unsigned char)lb; g |= s.ec[lb]; }
+        if (L < 0) { L = lb; s.parent[c] = (unsigned char)lb; g |= s.ec[lb]; ++merges; }
         else if (lb == L) already = true;
-        else { s.parent[lb] = (unsigned char)L; g |= s.ec[lb]; }
+        else { s.parent[lb] = (unsigned char)L; g |= s.ec[lb]; ++merges; }
         skip = true;     // the next neighbour touches this one: same group or a sharp corner
       }
     }
     if (L >= 0) s.ec[L] = (unsigned short)g;
-    const bool win = popc32(g >> 6) >= 3 || popc32(g & 63u) >= 2 || (already && ring_possible(s.st[me]) && ring_from(s.st[me], c, t));
+    s.comps += (1u - merges) << (16u * me);              // (two's complement: the other half is not touched
+                                                         //  as long as this half stays >= 0, which it does)
+    const bool win = popc32(g >> 6) >= 3 || popc32(g & 63u) >= 2 ||
+                     (already && ring_possible(s.st[me], (s.comps >> (16u * me)) & 0xFFFFu) && ring_from(s.st[me], c, t));
     if (win) s.outc = me;
     else if (s.left == 0) s.outc = (u32)kOutcomeDraw;
     s.mv = me ^ 1u;
