@@ -170,6 +170,14 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
   const u32 lane_lt = (1u << lane) - 1u;
   u32 begin = 0, count = 0, cursor = 0;
   bool drained = false;
+  // kBase (forest leaves, evaluator batches: many rollouts per root): root of a playout without a
+  // division per claim and per result.  A chunk holds at most kChunkPlayouts consecutive
+  // playouts, so with rollouts >= kChunkPlayouts it spans at most two roots: one warp-uniform
+  // division when the chunk is drawn (root and remainder of its first playout), one comparison
+  // per claim; the lane keeps its root for the result (ncu: the two divisions were 11 % of the
+  // warp instructions of the forest's leaf launches).
+  u32 croot = 0, crem = 0;     // root of playout `begin`, and begin - croot * rollouts
+  u32 my_root = 0;
   // Root staging (lean launches of single-plane games at one playout per root): when a warp
   // draws a chunk it copies the chunk's roots into shared memory with one coalesced load per
   // lane, so a claim — divergent code that runs in almost every group — reads its root with an
@@ -211,7 +219,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
   for (;;) {
     const u32 want = __ballot_sync(0xFFFFFFFFu, live == 0);
     const u32 nwant = __popc(want);
-    u32 nbegin = 0, ncount = 0;
+    u32 nbegin = 0, ncount = 0, nroot = 0, nrem = 0;
     const bool grab = !drained && cursor + nwant > count;  // warp-uniform: the chunk runs out in this claim
     if (grab) {
       u32 nb = 0;
@@ -220,6 +228,10 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
       nbegin = min(nb, a.n_playouts);
       ncount = min((u32)kChunkPlayouts, a.n_playouts - nbegin);
       drained = ncount == 0;
+      if constexpr (kBase) {
+        nroot = nbegin / a.rollouts;
+        nrem = nbegin - nroot * a.rollouts;
+      }
       if constexpr (kStage) {
         if (stage && ncount) {
           // chunks start at multiples of kChunkPlayouts: the source is 16-byte aligned whenever
@@ -255,7 +267,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         if (out & kOutLength) a.io.length[lid] = (uint8_t)t;
         if (out & kOutTerminal) a.io.terminal[lid] = (uint8_t)fin_term;
         if (out & kOutRootSums) {
-          u32 root = a.rollouts == 1 ? lid : lid / a.rollouts;
+          u32 root = a.rollouts == 1 ? lid : (kBase ? my_root : lid / a.rollouts);
           if (!kFill && a.io.root_sum_ret0 && ret != 0) atomicAdd(a.io.root_sum_ret0 + root, ret);
           if (a.io.root_sum_steps) atomicAdd(a.io.root_sum_steps + root, (int)t);
         }
@@ -264,12 +276,19 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
         my_done += 1;
       }
       u32 idx = cursor + __popc(want & lane_lt);
-      u32 base = begin, cnt = count, buf = par;
-      if (idx >= count) { idx -= count; base = nbegin; cnt = ncount; buf = par ^ 1u; }
+      u32 base = begin, cnt = count, buf = par, broot = croot, brem = crem;
+      if (idx >= count) { idx -= count; base = nbegin; cnt = ncount; buf = par ^ 1u; broot = nroot; brem = nrem; }
       have = idx < cnt ? 1u : 0u;
       if (have) {  // claim the next playout
         lid = base + idx;
-        u32 root = a.rollouts == 1 ? lid : lid / a.rollouts;
+        u32 root;
+        if constexpr (kBase) {
+          if (a.rollouts >= (u32)kChunkPlayouts) root = broot + ((brem + idx >= a.rollouts) ? 1u : 0u);
+          else root = a.rollouts == 1 ? lid : lid / a.rollouts;
+          my_root = root;
+        } else {
+          root = a.rollouts == 1 ? lid : lid / a.rollouts;
+        }
         if (kStage && stage) G::load(s, root_sm[threadIdx.x >> 5][buf], kChunkPlayouts, idx);
         else if ((compact_bytes<G>::value > 0) && a.compact)
           compact_ops<G, (compact_bytes<G>::value > 0)>::load(s, a.roots, a.root0 + root);
@@ -312,7 +331,7 @@ playout_kernel(const PlayoutArgs a, const typename G::Tables* __restrict__ gtab)
       }
     }
     cursor += nwant;
-    if (grab) { cursor = cursor > count ? cursor - count : 0u; begin = nbegin; count = ncount; par ^= 1u; }
+    if (grab) { cursor = cursor > count ? cursor - count : 0u; begin = nbegin; count = ncount; par ^= 1u; croot = nroot; crem = nrem; }
     if (!__any_sync(0xFFFFFFFFu, live != 0)) {
       if (!__any_sync(0xFFFFFFFFu, have != 0)) break;
       continue;
