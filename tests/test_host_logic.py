@@ -97,6 +97,9 @@ def test_kernel_step_path_matches_oracle_replay(oracle, name, oname, bs):
   whole action sequence, length, terminal flag and return with the oracle's replay."""
   gid = bsg.game_id(name)
   n = 25 if bs == 11 and oname in ("hex", "breakthrough", "y") else 150
+  if oname == "go" and bs == 7:
+    n = 1200        # enough 7 x 7 games for a few that end by superko (asserted below)
+  superko = 0
   for playout in range(n):
     seed = 20240611
     packed = bsg.pack_histories(name, [[]]).copy()
@@ -116,6 +119,10 @@ def test_kernel_step_path_matches_oracle_replay(oracle, name, oname, bs):
     o_acts, o_term, o_ret = oracle.replay(oname, [], seed=seed, playout=playout, board_size=bs)
     assert acts == o_acts, (name, playout)
     assert o_term == 1 and ret0.value == o_ret
+    if oname == "go" and len(acts) < 2 * bs * bs and not (acts[-1] == bs * bs and acts[-2] == bs * bs):
+      superko += 1  # neither two passes nor the length cap: a position came back
+  if oname == "go" and bs == 7:
+    assert superko >= 1
 
 
 def test_draw_matches_oracle(oracle):
