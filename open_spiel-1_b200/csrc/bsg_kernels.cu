@@ -12,7 +12,10 @@
 //  * the refill code runs whenever a lane waits (measured and rejected: waiting until >= 4..16
 //    lanes are idle; it was slower for all four games);
 //  * a step is unconditional straight-line code (finished lanes run dead steps on a dead
-//    state); only the bookkeeping is predicated.
+//    state); only the bookkeeping is predicated;
+//  * per-game launch traits (members of the game struct, trait templates below): group length,
+//    resident blocks, rolled step group (long steps: instruction cache), L1 carve-out (games
+//    whose state is local memory), lockstep replay of a root's move history (go).
 #include <type_traits>
 #include <cuda_runtime.h>
 #include <dlfcn.h>
