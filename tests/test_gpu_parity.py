@@ -572,3 +572,37 @@ def test_value_only_playouts_return_the_exact_results(game, n, R, torch):
     eng2 = _engine(game)
     eng2.playouts(states, n, 1, totals=torch.zeros(4, dtype=torch.int64, device=dev), max_steps=3, value_only=True)
   e2.close()
+
+
+@pytest.mark.parametrize("game,rollouts", [("connect_four", 96), ("connect_four", 128), ("connect_four", 160),
+                                           ("connect_four", 256), ("go(board_size=9)", 130)])
+def test_per_root_playout_bases_give_the_plain_launchs_playouts(game, rollouts, torch):
+  """The launch with a playout-id base per root (forest leaves, evaluator batches) finds a
+  playout's root from the chunk's first root and a comparison (rollouts >= 128) or a division
+  (below); with base[i] = F + i * rollouts it must play exactly the playouts of the plain launch
+  — the other code path — result for result, chunks that straddle two roots included."""
+  from open_spiel_1_b200.roots import make_roots, ROOT_DEPTHS
+  eng = _engine(game)
+  dev = eng.torch_device
+  n_roots, R, F = 777, rollouts, (1 << 35) + 12345
+  dmin, dmax = ROOT_DEPTHS[game]
+  states, _ = make_roots(eng, n_roots, dmin, dmax, seed=77)
+  n = n_roots * R
+  outs = []
+  for with_base in (False, True):
+    ret0 = torch.zeros(n, dtype=torch.int8, device=dev)
+    length = torch.zeros(n, dtype=torch.uint8, device=dev)
+    sums = torch.zeros(n_roots, dtype=torch.int32, device=dev)
+    steps = torch.zeros(n_roots, dtype=torch.int32, device=dev)
+    totals = torch.zeros(4, dtype=torch.int64, device=dev)
+    base = None
+    if with_base:
+      base = (torch.arange(n_roots, dtype=torch.int64, device=dev) * R + F).view(torch.int64)
+    eng.playouts(states, n_roots, R, seed=5, first_playout=0 if with_base else F, ret0=ret0, length=length,
+                 root_sum_ret0=sums, root_sum_steps=steps, totals=totals, root_playout_base=base)
+    torch.cuda.synchronize()
+    outs.append((ret0, length, sums, steps, totals))
+  for a, b in zip(*outs):
+    assert torch.equal(a, b)
+  assert int(outs[0][4][0]) == n
+  eng.close()
