@@ -597,7 +597,7 @@ def e2e_block(args, eng, torch, dev, states, n, first, barrier, reduce_max_sum, 
   out = {"value": sm[1] / mx[0], "unit": "game-steps/s",
          "h2d_bytes_per_step": int(states.numel()), "d2h_bytes_per_step": 32,
          "api": "bsg_playouts_host (C ABI, pinned host roots in, totals out)"}
-  # the same through the compact root format (connect_four: 7 bytes per root instead of 8): the
+  # the same through the compact root format (connect_four: 49 bits per root instead of 64): the
   # H2D copy is what bounds the call, so this is the API path a throughput caller takes
   try:
     comp_np = eng.compact_roots(host_np, n)
@@ -619,7 +619,7 @@ def e2e_block(args, eng, torch, dev, states, n, first, barrier, reduce_max_sum, 
       out["packed8"] = {"value": out["value"], "h2d_bytes_per_step": out["h2d_bytes_per_step"], "api": out["api"]}
       out["value"] = smc[1] / mxc[0]
       out["h2d_bytes_per_step"] = int(comp_np.nbytes)
-      out["api"] = ("bsg_playouts_host_compact (C ABI, pinned host roots in the 7-byte compact format in, totals "
+      out["api"] = ("bsg_playouts_host_compact (C ABI, pinned host roots in the 49-bit compact format in, totals "
                     "out); same playouts and totals as the packed call (checked: %s)" % (game_steps_c == game_steps))
       del comp
   except Exception as ex:

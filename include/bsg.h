@@ -236,15 +236,18 @@ int bsg_playouts_host_results(bsg_engine* e, const void* roots_host, int64_t n_r
                               int32_t rollouts_per_root, uint64_t seed, uint64_t first_playout,
                               int64_t totals_out[4], int8_t* ret0_host, uint8_t* length_host);
 /* Compact root format for host -> device transfers.  The copy of the roots over PCIe is the
- * end-to-end bound of the path; a connect_four position needs 49 bits, so its roots also travel
- * as SEVEN bytes each, back to back (the low seven bytes of the packed u64; empty-cell count and
- * win flag are derived on the device).  bsg_compact_state_bytes: bytes per compact root (=
+ * end-to-end bound of the path; a connect_four position needs 49 bits (seven rows of seven
+ * columns: the mover's stones | one marker per column), so its roots also travel as 49-bit
+ * strings back to back, root i at bit 49 * i of the buffer, little endian (empty-cell count and
+ * win flag are derived on the device).  bsg_compact_state_bits: bits per compact root (= 8 *
  * bsg_state_bytes for a game without a compact format, whose "compact" buffers are the packed
- * ones).  bsg_compact_roots / bsg_expand_roots convert on the host (expand runs the very decode
+ * ones); bsg_compact_buffer_bytes: bytes of a buffer of n compact roots, (n * bits + 7) / 8.
+ * bsg_compact_roots / bsg_expand_roots convert on the host (expand runs the very decode
  * the kernel runs).  bsg_playouts_host_compact is bsg_playouts_host_results for compact roots;
  * ret0_host and length_host may both be NULL (totals only).  Stands in for the same reference
  * loop (algorithms/mcts.cc:42-71, examples/benchmark_game.cc:31-97). */
-int bsg_compact_state_bytes(int game);
+int bsg_compact_state_bits(int game);
+int64_t bsg_compact_buffer_bytes(int game, int64_t n);
 int bsg_compact_roots(int game, const void* packed_host, int64_t n, void* compact_out);
 int bsg_expand_roots(int game, const void* compact_host, int64_t n, void* packed_out);
 int bsg_playouts_host_compact(bsg_engine* e, const void* roots_compact_host, int64_t n_roots,

@@ -104,7 +104,8 @@ def _load():
       "bsg_playouts_host": (ctypes.c_int, [vp, vp, i64, i32, u64, u64, vp, vp, vp]),
       "bsg_observations_host": (ctypes.c_int, [vp, vp, i64, vp, vp, vp]),
       "bsg_playouts_host_results": (ctypes.c_int, [vp, vp, i64, i32, u64, u64, vp, vp, vp]),
-      "bsg_compact_state_bytes": (ctypes.c_int, [ctypes.c_int]),
+      "bsg_compact_state_bits": (ctypes.c_int, [ctypes.c_int]),
+      "bsg_compact_buffer_bytes": (ctypes.c_int64, [ctypes.c_int, ctypes.c_int64]),
       "bsg_compact_roots": (ctypes.c_int, [ctypes.c_int, vp, i64, vp]),
       "bsg_expand_roots": (ctypes.c_int, [ctypes.c_int, vp, i64, vp]),
       "bsg_playouts_host_compact": (ctypes.c_int, [vp, vp, i64, i32, u64, u64, vp, vp, vp]),

@@ -252,19 +252,26 @@ struct ConnectFour {
     s.left = top >> 26;
     s.win = (top >> 25) & 1u;
   }
-  // Compact root format for host -> device transfers (bsg_playouts_host_compact): the low SEVEN
-  // bytes of the packed u64 (bits 0..54: the mover's stones | one marker per column), 7 bytes
-  // per root back to back.  The meta byte is derived: empty cells from the occupancy, "the last
-  // move made four in a row" from the line test on the side that moved last.  The copy of the
-  // roots over PCIe is the end-to-end bound of the path, so an eighth of it is an eighth of the time.
-  static constexpr int kCompactBytes = 7;
+  // Compact root format for host -> device transfers (bsg_playouts_host_compact): a position is
+  // the mover's stones | one marker per column, seven rows of seven columns = 49 bits.  The packed
+  // u64 spends a byte per row; the compact format drops every row's unused eighth bit and stores
+  // the 49-bit strings back to back (root i at bit 49 * i, little endian).  The meta byte is
+  // derived: empty cells from the occupancy, "the last move made four in a row" from the line
+  // test on the side that moved last.  The copy of the roots over PCIe is the end-to-end bound
+  // of the path, so 49 bits instead of 64 is a quarter off the time.
+  static constexpr int kCompactBits = 49;
   BSG_HD static void load_compact(State& s, const void* base, int64_t i) {
-    const int64_t off = 7 * i;
-    const u32* p = (const u32*)base + (off >> 2);          // (the buffer has >= 8 bytes of slack behind it)
-    const int sh = (int)(off & 3) * 8;
+    const int64_t bit = 49 * i;
+    const u32* p = (const u32*)base + (bit >> 5);          // (the buffer has >= 8 bytes of slack behind it)
+    const int sh = (int)(bit & 31);
     const u32 w0 = p[0], w1 = p[1], w2 = p[2];
-    const u32 lo = sh ? fshr(w0, w1, sh) : w0;
-    const u32 hi = (sh ? fshr(w1, w2, sh) : w1) & 0x00FFFFFFu;
+    const u32 v0 = fshr(w0, w1, sh), v1 = fshr(w1, w2, sh);      // bits 0..31 and 32..63 of the string
+    // rows 0..3 (28 bits) and rows 4..6 (21 bits), then every row from its 7-bit slot to its byte
+    u32 lo = v0 & 0x0FFFFFFFu, hi = fshr(v0, v1, 28) & 0x001FFFFFu;
+    lo = (lo & 0x00003FFFu) | ((lo & 0x0FFFC000u) << 2);
+    hi = (hi & 0x00003FFFu) | ((hi & 0x0FFFC000u) << 2);
+    lo = (lo & 0x007F007Fu) | ((lo & 0x3F803F80u) << 1);
+    hi = (hi & 0x007F007Fu) | ((hi & 0x3F803F80u) << 1);
     const u64 key = (u64)lo | ((u64)hi << 32);
     u64 sm = key;
     sm |= sm >> 8;
@@ -276,11 +283,18 @@ struct ConnectFour {
     s.left = 42u - (u32)popc64(occ);
     s.win = has_line(s.opp) ? 1u : 0u;
   }
+  // (host side; the buffer starts zeroed and the roots are stored in ascending order)
   BSG_HD static void store_compact(const State& s, void* base, int64_t i) {
     u64 tmp = 0;
     store(s, &tmp, 1, 0);
-    unsigned char* b = (unsigned char*)base + 7 * i;
-    for (int k = 0; k < 7; ++k) b[k] = (unsigned char)(tmp >> (8 * k));
+    u64 str = 0;
+    for (int r = 0; r < 7; ++r) str |= ((tmp >> (8 * r)) & 0x7Full) << (7 * r);
+    unsigned char* b = (unsigned char*)base + ((49 * i) >> 3);
+    const int sh = (int)((49 * i) & 7);
+    for (int k = 0; k < 8; ++k) {                         // 49 + 7 bits span at most 7 bytes
+      const unsigned v = (unsigned)((k == 0 ? (str << sh) : (str >> (8 * k - sh))) & 0xFFu);
+      if (v) b[k] = (unsigned char)(b[k] | v);
+    }
   }
   BSG_HD static void store(const State& s, void* base, int64_t n, int64_t i) {
     (void)n;

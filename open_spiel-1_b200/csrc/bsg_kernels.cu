@@ -63,7 +63,7 @@ struct PlayoutArgs {
   bsg_playout_io io;
   uint32_t* work_counter;  // zeroed before the launch; warps draw chunks of playouts from it
   uint32_t out_flags;  // kOut* bits: which optional per-playout outputs of io are present
-  uint32_t compact;    // != 0: `roots` is in the game's compact format (compact_bytes<G> per root)
+  uint32_t compact;    // != 0: `roots` is in the game's compact format (compact_bits<G> per root)
   uint32_t* fill_boards;  // value-only launches: kFillWords words per playout for fill_resolve_kernel
   uint64_t fill_base;     // host path: this launch parks its boards from playout slot fill_base on
 };
@@ -115,9 +115,12 @@ template <class G> struct replay_ops<G, true> {
   BSG_HD static u32 group_begin(typename G::State& s) { return G::group_begin(s); }
 };
 
-// Games with a compact root format for host -> device transfers (G::kCompactBytes, G::load_compact).
+// Games with a compact root format for host -> device transfers (G::kCompactBits per root, bit
+// strings back to back; G::load_compact / store_compact).  compact_bytes<G>::value > 0 says "has one".
 template <class G, class = void> struct compact_bytes : std::integral_constant<int, 0> {};
-template <class G> struct compact_bytes<G, std::enable_if_t<(G::kCompactBytes > 0)>> : std::integral_constant<int, G::kCompactBytes> {};
+template <class G> struct compact_bytes<G, std::enable_if_t<(G::kCompactBits > 0)>> : std::integral_constant<int, (G::kCompactBits + 7) / 8> {};
+template <class G, class = void> struct compact_bits : std::integral_constant<int, 8 * G::kStateBytes> {};
+template <class G> struct compact_bits<G, std::enable_if_t<(G::kCompactBits > 0)>> : std::integral_constant<int, G::kCompactBits> {};
 template <class G, bool kOn> struct compact_ops {
   BSG_HD static void load(typename G::State&, const void*, int64_t) {}
   BSG_HD static void store(const typename G::State&, void*, int64_t) {}
@@ -1649,8 +1652,8 @@ int bsg_playouts_host_results(bsg_engine* e, const void* roots_host, int64_t n_r
 // ---- compact roots (connect_four: 7 bytes per root)
 }  // extern "C"
 namespace {
-struct CompactBytesOp {
-  template <class G> int operator()() const { return compact_bytes<G>::value > 0 ? compact_bytes<G>::value : G::kStateBytes; }
+struct CompactBitsOp {
+  template <class G> int operator()() const { return compact_bits<G>::value; }
 };
 struct CompactConvertOp {
   const void* in; void* out; int64_t n; int to_compact;
@@ -1659,10 +1662,13 @@ struct CompactConvertOp {
       // expanding reads three words per root: work on a padded copy of the compact buffer
       std::vector<unsigned char> padded;
       const void* src = in;
+      const size_t cbytes = ((size_t)n * compact_bits<G>::value + 7) / 8;
       if (!to_compact) {
-        padded.assign((size_t)n * compact_bytes<G>::value + 16, 0);
-        memcpy(padded.data(), in, (size_t)n * compact_bytes<G>::value);
+        padded.assign(cbytes + 16, 0);
+        memcpy(padded.data(), in, cbytes);
         src = padded.data();
+      } else {
+        memset(out, 0, cbytes);                  // store_compact ORs its bits in
       }
       for (int64_t i = 0; i < n; ++i) {
         typename G::State s;
@@ -1678,7 +1684,11 @@ struct CompactConvertOp {
 };
 }  // namespace
 extern "C" {
-int bsg_compact_state_bytes(int game) { return dispatch_game(game, CompactBytesOp{}); }
+int bsg_compact_state_bits(int game) { return dispatch_game(game, CompactBitsOp{}); }
+int64_t bsg_compact_buffer_bytes(int game, int64_t n) {
+  const int bits = bsg_compact_state_bits(game);
+  return bits < 0 || n < 0 ? (int64_t)BSG_ERR_BAD_ARG : (n * bits + 7) / 8;
+}
 int bsg_compact_roots(int game, const void* packed_host, int64_t n, void* compact_out) {
   if (!packed_host || !compact_out || n < 0) return BSG_ERR_BAD_ARG;
   return dispatch_game(game, CompactConvertOp{packed_host, compact_out, n, 1});
@@ -1697,8 +1707,8 @@ int bsg_playouts_host_compact(bsg_engine* e, const void* roots_compact_host, int
   if (!roots_compact_host || n_roots < 1 || rollouts < 1 || !totals_out)
     return fail(e, BSG_ERR_BAD_ARG, "bad host playout arguments");
   if (e->value_only) return fail(e, BSG_ERR_BAD_ARG, "compact roots run the exact kernels (value_only is set)");
-  const int cb = bsg_compact_state_bytes(e->game);
-  if (cb == bsg_state_bytes(e->game))   // no compact format for this game: the packed path
+  const int bits = bsg_compact_state_bits(e->game);
+  if (bits == 8 * bsg_state_bytes(e->game))   // no compact format for this game: the packed path
     return (ret0_host || length_host)
                ? bsg_playouts_host_results(e, roots_compact_host, n_roots, rollouts, seed, first_playout, totals_out, ret0_host, length_host)
                : bsg_playouts_host(e, roots_compact_host, n_roots, rollouts, seed, first_playout, totals_out, nullptr, nullptr);
@@ -1706,7 +1716,7 @@ int bsg_playouts_host_compact(bsg_engine* e, const void* roots_compact_host, int
   if (n_play >= ((int64_t)1 << 32) - (1 << 24))
     return fail(e, BSG_ERR_BAD_ARG, "more than 2^32-2^24 playouts in one call");
   BSG_CUDA(e, cudaSetDevice(e->device));
-  const size_t in_bytes = (size_t)n_roots * (size_t)cb;
+  const size_t in_bytes = ((size_t)n_roots * (size_t)bits + 7) / 8;
   const size_t out_bytes = (size_t)n_play * ((ret0_host ? 1 : 0) + (length_host ? 1 : 0));
   int rc;
   if ((rc = ensure(e, &e->d_roots, &e->d_roots_bytes, in_bytes + 16, false)) != BSG_OK) return rc;
@@ -1743,12 +1753,13 @@ int bsg_playouts_host_compact(bsg_engine* e, const void* roots_compact_host, int
   PhiloxKeys keys;
   philox_schedule(seed, keys);
   for (int64_t c = 0; c < n_chunks; ++c) {
-    // chunk boundaries at multiples of 4 roots: 4 * 7 bytes keeps every chunk's first byte word-aligned
-    int64_t lo = (n_roots * c / n_chunks) & ~(int64_t)3, hi = c + 1 == n_chunks ? n_roots : ((n_roots * (c + 1) / n_chunks) & ~(int64_t)3);
+    // chunk boundaries at multiples of 32 roots: whatever the bits per root, a chunk then starts
+    // on a word of the bit string (the device copy sits at the same offsets as the host buffer)
+    int64_t lo = (n_roots * c / n_chunks) & ~(int64_t)31, hi = c + 1 == n_chunks ? n_roots : ((n_roots * (c + 1) / n_chunks) & ~(int64_t)31);
     if (hi <= lo) continue;
     cudaStream_t st = (c & 1) ? sb : sa;
-    BSG_CUDA(e, cudaMemcpyAsync((char*)e->d_roots + (size_t)lo * cb, src + (size_t)lo * cb, (size_t)(hi - lo) * cb,
-                                cudaMemcpyHostToDevice, st));
+    const size_t b_lo = (size_t)lo * bits / 8, b_hi = c + 1 == n_chunks ? in_bytes : (size_t)hi * bits / 8;
+    BSG_CUDA(e, cudaMemcpyAsync((char*)e->d_roots + b_lo, src + b_lo, b_hi - b_lo, cudaMemcpyHostToDevice, st));
     const int64_t p_lo = lo * rollouts, p_n = (hi - lo) * rollouts;
     PlayoutArgs a;
     memset(&a, 0, sizeof(a));

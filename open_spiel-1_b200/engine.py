@@ -364,9 +364,10 @@ class Engine:
     return totals, ret0, length
 
   def compact_roots(self, packed, n_roots):
-    """Packed roots -> the game's compact transfer format (connect_four: 7 bytes per root)."""
+    """Packed roots -> the game's compact transfer format (connect_four: 49 bits per root, back
+    to back)."""
     packed = np.ascontiguousarray(packed)
-    out = np.zeros(int(n_roots) * C.check(C.lib.bsg_compact_state_bytes(self.gid)), np.uint8)
+    out = np.zeros(int(C.check(C.lib.bsg_compact_buffer_bytes(self.gid, int(n_roots)))), np.uint8)
     C.check(C.lib.bsg_compact_roots(self.gid, packed.ctypes.data, int(n_roots), out.ctypes.data))
     return out
 

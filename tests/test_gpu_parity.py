@@ -373,7 +373,7 @@ def test_host_results_entry_point_equals_device_path(game, n, torch):
 
 @pytest.mark.parametrize("n,R", [(900001, 1), (5, 3), (70000, 2)])
 def test_compact_root_entry_point_equals_device_path(n, R, torch):
-  """bsg_playouts_host_compact: connect_four roots as 7 bytes each — totals and per-playout
+  """bsg_playouts_host_compact: connect_four roots as 49 bits each — totals and per-playout
   results equal the device launch over the packed roots, terminal roots included, for pageable
   and page-locked buffers; a game without a compact format takes its packed roots."""
   import open_spiel_1_b200 as bsg
@@ -393,7 +393,7 @@ def test_compact_root_entry_point_equals_device_path(n, R, torch):
   eng.playouts(states, n, R, seed=6, first_playout=55, ret0=ret0, length=length, totals=totals)
   torch.cuda.synchronize()
   comp = eng.compact_roots(host, n)
-  assert comp.nbytes == 7 * n and np.array_equal(eng.expand_roots(comp, n), host)
+  assert comp.nbytes == (49 * n + 7) // 8 and np.array_equal(eng.expand_roots(comp, n), host)
   t, r, l = eng.playouts_host_compact(comp, n, R, seed=6, first_playout=55, want_results=True)
   assert np.array_equal(t, totals.cpu().numpy())
   assert np.array_equal(r, ret0.cpu().numpy()) and np.array_equal(l, length.cpu().numpy())

@@ -307,10 +307,18 @@ def test_compact_roots_round_trip_through_the_kernels_decode():
   assert d.is_terminal() and d.returns() == [0.0, 0.0]
   packed = np.concatenate([packed, d.packed()])
   n += 1
-  assert C.lib.bsg_compact_state_bytes(C.CONNECT_FOUR) == 7
-  comp = np.zeros(n * 7, np.uint8)
+  assert C.lib.bsg_compact_state_bits(C.CONNECT_FOUR) == 49
+  assert C.lib.bsg_compact_buffer_bytes(C.CONNECT_FOUR, n) == (n * 49 + 7) // 8
+  comp = np.full((n * 49 + 7) // 8, 0xA5, np.uint8)        # (the converter clears the buffer itself)
   C.check(C.lib.bsg_compact_roots(C.CONNECT_FOUR, packed.ctypes.data, n, comp.ctypes.data))
   back = np.zeros(n * 8, np.uint8)
   C.check(C.lib.bsg_expand_roots(C.CONNECT_FOUR, comp.ctypes.data, n, back.ctypes.data))
   assert np.array_equal(back, packed)
-  assert C.lib.bsg_compact_state_bytes(C.HEX) == 64 and C.lib.bsg_compact_state_bytes(C.TIC_TAC_TOE) == 4
+  # root i is the 49-bit string at bit 49 * i: seven rows of seven columns, bit 7 of every row byte dropped
+  bits = np.unpackbits(comp, bitorder="little")
+  for i in (0, 1, n // 2, n - 1):
+    key = int.from_bytes(packed[8 * i:8 * i + 7].tobytes(), "little")
+    want = sum(((key >> (8 * r)) & 0x7F) << (7 * r) for r in range(7))
+    got = sum(int(b) << k for k, b in enumerate(bits[49 * i:49 * i + 49]))
+    assert got == want
+  assert C.lib.bsg_compact_state_bits(C.HEX) == 8 * 64 and C.lib.bsg_compact_state_bits(C.TIC_TAC_TOE) == 8 * 4
