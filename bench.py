@@ -75,8 +75,62 @@ def parse_args():
   return ap.parse_args()
 
 
+class NvmlClockSampler:
+  """SM clock and throttle reasons of one GPU, read through NVML from a thread every millisecond
+  of the timed region (the region is ~12 ms: nvidia-smi -lms 100 often delivers its first sample
+  after it, always so on an eight-GPU box).  start() returns False when NVML is unavailable."""
+
+  def __init__(self, torch_device):
+    self.dev = torch_device
+    self.samples = []
+    self.stop_flag = False
+    self.thread = None
+
+  def start(self):
+    try:
+      import pynvml
+      import torch
+      pynvml.nvmlInit()
+      p = torch.cuda.get_device_properties(self.dev)
+      bus = "%08X:%02X:%02X.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+      h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+      self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+      pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+    except Exception:
+      return False
+    names = [("hw_slowdown", pynvml.nvmlClocksThrottleReasonHwSlowdown),
+             ("hw_thermal_slowdown", pynvml.nvmlClocksThrottleReasonHwThermalSlowdown),
+             ("sw_thermal_slowdown", pynvml.nvmlClocksThrottleReasonSwThermalSlowdown),
+             ("sw_power_cap", pynvml.nvmlClocksThrottleReasonSwPowerCap)]
+
+    def pump():
+      while not self.stop_flag:
+        try:
+          mhz = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+          bits = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+          self.samples.append((float(mhz), [n for n, b in names if bits & b]))
+        except Exception:
+          pass
+        time.sleep(0.001)
+
+    self.thread = threading.Thread(target=pump, daemon=True)
+    self.thread.start()
+    return True
+
+  def stop(self):
+    self.stop_flag = True
+    if self.thread:
+      self.thread.join(timeout=1)
+    if not self.samples:
+      return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+    reasons = sorted({r for _, rs in self.samples for r in rs})
+    return {"sm_mhz": float(np.median([m for m, _ in self.samples])), "sm_max_mhz": self.max_mhz,
+            "reasons": reasons, "samples": len(self.samples), "source": "nvml, 1 ms period"}
+
+
 class ClockSampler:
-  """Samples nvidia-smi clocks and throttle reasons during the timed region."""
+  """Samples nvidia-smi clocks and throttle reasons during the timed region (the fallback when
+  NVML cannot be loaded into this process)."""
   QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
            "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -494,8 +548,9 @@ def run_ours(args):
   barrier()
   totals.zero_()
   launches0 = eng.launches
-  sampler = ClockSampler(local)
-  if rank == 0:
+  sampler = NvmlClockSampler(dev)
+  if rank == 0 and not sampler.start():
+    sampler = ClockSampler(local)
     sampler.start()
   barrier()
   ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
