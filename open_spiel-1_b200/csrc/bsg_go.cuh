@@ -13,12 +13,15 @@
 //
 //   The reference keeps chains as linked lists with pseudo-liberty sums.  Here a position is two
 //   N^2-bit sets; a chain is a 4-neighbourhood flood of a set, its liberties one more dilation.
-//   Legality is bit-parallel for every point with an empty neighbour and falls back to flooding
-//   the adjacent chains only for fully surrounded points.  Two things have to be reproduced, not
-//   just re-derived:
-//    * superko needs every earlier position of the game: the state carries a 64-bit hash of each
-//      (any collision-free hash gives the reference's answers; its own is a Zobrist table of
-//      another library), and a PACKED state carries the move history and is replayed at load;
+//   Legality is bit-parallel for every point with an empty neighbour; for fully surrounded
+//   points one flood finds every chain with a liberty that is not such a point, and only the
+//   chains that are left are flooded one by one, each once, up to the liberty count that decides.
+//   Two things have to be reproduced, not just re-derived:
+//    * superko needs every earlier position of the game: the state carries an open-addressed set
+//      of their 64-bit hashes (any collision-free hash gives the reference's answers; its own is
+//      a Zobrist table of another library), and a PACKED state carries the move history and is
+//      replayed at load — by the playout kernel in lockstep with the other lanes' steps
+//      (kReplayLoad, load_lazy);
 //    * the reference's territory search stops exploring a region as soon as it has seen both
 //      colours and leaves the rest unmarked, so a later start inside the same region may see only
 //      one colour and count that part (go_board.cc:525-553): the order-dependent search is
@@ -33,9 +36,6 @@
 #pragma once
 #include "bsg_common.cuh"
 
-#ifndef BSG_GO_BULK_FLOOD
-#define BSG_GO_BULK_FLOOD 1
-#endif
 #ifndef BSG_GO_ROLLED
 #define BSG_GO_ROLLED 1
 #endif
@@ -159,24 +159,8 @@ struct GoT {
     for (int w = 0; w < W; ++w)
       out[w] = ((e[w] & not_col0(w)) | (x[w] & not_col_last(w)) | up[w] | dn[w]) & board_word(w);
   }
-  // The chain of `set` that contains the cell (a 4-neighbourhood flood).
-  BSG_HD static void chain_of(const u32* set, int cell, u32* out) {
-    for (int w = 0; w < W; ++w) out[w] = 0;
-    set_bit(out, cell);
-    for (;;) {
-      u32 d[W];
-      nb4(out, d);
-      u32 grew = 0;
-      for (int w = 0; w < W; ++w) {
-        const u32 g = (out[w] | d[w]) & set[w];
-        grew |= g ^ out[w];
-        out[w] = g;
-      }
-      if (!grew) break;
-    }
-  }
-  // The same flood, stopped as soon as the chain is known to have `enough` liberties: returns
-  // min(liberties, enough).  `out` is the whole chain only when the result is below `enough`;
+  // The chain of `set` that contains the cell — a 4-neighbourhood flood — stopped as soon as the
+  // chain is known to have `enough` liberties: returns min(liberties, enough).  `out` is the whole chain only when the result is below `enough`;
   // otherwise it is the part flooded so far (still stones of that one chain).
   BSG_HD static int chain_liberties_capped(const u32* set, int cell, const u32* empty, int enough, u32* out) {
     for (int w = 0; w < W; ++w) out[w] = 0;
@@ -195,13 +179,6 @@ struct GoT {
       if (libs >= enough) return enough;
       if (!grew) return libs;
     }
-  }
-  BSG_HD static int liberties(const u32* chain, const u32* empty) {
-    u32 d[W];
-    nb4(chain, d);
-    int n = 0;
-    for (int w = 0; w < W; ++w) n += popc32(d[w] & empty[w]);
-    return n;
   }
   // Neighbour of a cell in the reference's order (row + 1, col + 1, col - 1, row - 1), -1 off the board.
   BSG_HD static int neighbour(int cell, int d) {
@@ -237,7 +214,6 @@ struct GoT {
       u32 cand[W], known[W], good[W];
       nb4(rest, cand);
       for (int w = 0; w < W; ++w) { cand[w] &= mine[w] | theirs[w]; known[w] = 0; good[w] = 0; }
-#if BSG_GO_BULK_FLOOD
       // First every chain with a liberty that is NOT a surrounded point, both colours in one flood
       // that all lanes of a warp run together: such a friendly chain has that liberty and the
       // point (>= 2), such an enemy chain is not captured there.  What is left for the per-chain
@@ -261,7 +237,6 @@ struct GoT {
         }
         for (int w = 0; w < W; ++w) { known[w] = fa[w] | fb[w]; good[w] = fa[w]; }
       }
-#endif
       for (;;) {
         u32 todo[W];
         for (int w = 0; w < W; ++w) todo[w] = cand[w] & ~known[w];
