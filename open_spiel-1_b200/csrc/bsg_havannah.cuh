@@ -14,9 +14,11 @@
 //   cell of its own path (CheckRingDFS, havannah.cc:385-399, started in directions 0..3).
 //   Group identities are therefore kept the way the reference keeps them, as a union-find over
 //   the cells — one byte per cell, in the lane's local memory — with the corner / edge sets at
-//   the leaders; which cell leads a group has no influence on any result, so the union is by
-//   index, not by size.  The ring search runs as an explicit-stack loop over the same
-//   (cell, first direction, last direction) frames as the reference's recursion.
+//   the leaders; which cell leads a group has no influence on any result, so a stone that joins
+//   a group simply points at that group's leader (flat trees, short finds).  The ring search runs
+//   as an explicit-stack loop over the same (cell, first direction, last direction) frames as
+//   the reference's recursion — and only when the mover's stones CAN hold a ring: a solid hexagon,
+//   or a hole, counted by Euler characteristic from popcounts (ring_possible).
 //   Stones are also kept as bit sets (W words per colour) for the empty-cell rank-select, the
 //   observation planes and the packed state.
 //
