@@ -21,6 +21,9 @@
 // Semantics follow the reference rules cited per function; the representation does not.
 #pragma once
 #include "bsg_common.cuh"
+#ifndef BSG_TTT_LAZY_DRAW
+#define BSG_TTT_LAZY_DRAW 1
+#endif
 #ifndef BSG_Y_ROLLED
 #define BSG_Y_ROLLED 1
 #endif
@@ -46,6 +49,12 @@ struct TicTacToe {
   static constexpr bool kAsync = false;     // a step completes within the step (see HexT)
   static constexpr bool kMoverCanLose = false;  // a move never ends the game in the mover's disfavour (see Pentago)
   static constexpr bool kLazyEnd = false;       // the lean kernel sees a terminal state in the step that reaches it (see Othello)
+  // A full board is inert for the lean kernel's bookkeeping (see ConnectFour::kInertWhenFull): the
+  // row of the empty mask 0 names "cell 9", a bit outside the board, so a dead step on a full
+  // board places nothing on it and — the board being a draw — neither side's marks hold a line;
+  // the line table covers that tenth bit.  A playout that has made as many moves as its root had
+  // empty cells is over: one comparison per group instead of a terminal test per step.
+  static constexpr bool kInertWhenFull = BSG_TTT_LAZY_DRAW != 0;
   struct State {
     u32 cur, opp;   // marks of the player to move / of the other player (9-bit masks)
     u32 left;       // empty cells; parity = player to move (x = player 0 first, 9 cells)
@@ -58,7 +67,7 @@ struct TicTacToe {
   //   instructions (no popcount, no rank-select, no shifts over the eight lines).
   struct Tables {
     u32 row[512][6];
-    unsigned char line[512];
+    unsigned char line[1024];       // indexed by a 9-bit mask, or one with the dead step's tenth bit
   };
   static void fill_tables(Tables& t) {
     for (u32 e = 0; e < 512; ++e) {
@@ -67,13 +76,15 @@ struct TicTacToe {
       u32 n = 0;
       for (u32 c = 0; c < 9; ++c) if ((e >> c) & 1) cells[n++] = (unsigned char)c;
       u32 nn = n ? n : 1;   // e = 0 only on finished lanes running dead steps
+      if (!n) cells[0] = 9; // ... which then mark a bit outside the board
       t.row[e][0] = modM_entry(nn);
       t.row[e][1] = 0u - nn;
-      t.line[e] = has_line(e) ? 1 : 0;
+      t.line[e] = t.line[e | 512u] = has_line(e) ? 1 : 0;
     }
   }
 
   BSG_HD static void init(State& s) { s.cur = 0; s.opp = 0; s.left = 9; s.win = 0; }
+  BSG_HD static u32 moves_left(const State& s) { return s.left; }
   BSG_HD static void load(State& s, const void* base, int64_t n, int64_t i) {
     (void)n;
     u32 w = ((const u32*)base)[i];
